@@ -1,0 +1,238 @@
+// extern "C" surface of libdlwp_b200.so (include/dlwp_b200.h).  Nothing here throws.
+#include <new>
+
+#include "plan.cuh"
+
+using namespace dlwp;
+
+namespace {
+
+int check_device(int device) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    return fail(DLWP_ERR_NO_DEVICE, "no CUDA device is usable (%s); this library has no CPU fallback",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  }
+  if (device < 0 || device >= n) return fail(DLWP_ERR_INVALID, "device %d out of range [0, %d)", device, n);
+  cudaDeviceProp prop;
+  DLWP_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(DLWP_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device,
+                prop.major, prop.minor);
+  DLWP_CUDA(cudaSetDevice(device));
+  return DLWP_OK;
+}
+
+void free_plan(dlwp_plan* p) {
+  if (!p) return;
+  cudaSetDevice(p->device);
+  for (void* q : p->owned) cudaFree(q);
+  for (auto& kv : p->tensors) cudaFree(kv.second.data);
+  for (int i = 0; i < 4; ++i)
+    if (p->stage[i]) cudaFree(p->stage[i]);
+  delete p;
+}
+
+// Frame bookkeeping of the autoregressive loop (fno.py:78-100 in the working form of
+// fourcastnet.py:489-521): which NCHW planes make up x_t and prognostic_t[:, -1].
+void rollout_io(const dlwp_plan* p, const float* constants, const float* prescribed, const float* prognostic,
+                float* outs, int T, int t, StepIO* io) {
+  const dlwp_model_desc& d = p->d;
+  const long long HW = (long long)d.height * d.width;
+  const int ctx = d.context_size, Cc = d.constant_channels, Cp = d.prescribed_channels,
+            Cg = d.prognostic_channels, steps = T - ctx;
+  int g = 0;
+  if (constants && Cc > 0) io->grp[g++] = SrcGroup{constants, Cc * HW, Cc};
+  if (prescribed && Cp > 0)
+    io->grp[g++] = SrcGroup{prescribed + (long long)(t - ctx) * Cp * HW, (long long)T * Cp * HW, ctx * Cp};
+  const int own = (t - ctx) < ctx ? (t - ctx) : ctx;  // frames taken from the model's own outputs
+  const int gt = ctx - own;                           // ground-truth context frames still in use
+  if (gt > 0)
+    io->grp[g++] = SrcGroup{prognostic + (long long)(t - ctx) * Cg * HW, (long long)T * Cg * HW, gt * Cg};
+  if (own > 0)
+    io->grp[g++] = SrcGroup{outs + (long long)(t - ctx - own) * Cg * HW, (long long)steps * Cg * HW, own * Cg};
+  io->ngrp = g;
+  io->out = outs + (long long)(t - ctx) * Cg * HW;
+  io->out_bstride = (long long)steps * Cg * HW;
+  if (own > 0) {
+    io->last = outs + (long long)(t - ctx - 1) * Cg * HW;
+    io->last_bstride = (long long)steps * Cg * HW;
+  } else {
+    io->last = prognostic + (long long)(ctx - 1) * Cg * HW;
+    io->last_bstride = (long long)T * Cg * HW;
+  }
+}
+
+int grow(dlwp_plan* p, int slot, size_t bytes) {
+  if (bytes <= p->stage_bytes[slot]) return DLWP_OK;
+  if (p->stage[slot]) cudaFree(p->stage[slot]);
+  p->stage[slot] = nullptr;
+  p->stage_bytes[slot] = 0;
+  DLWP_CUDA(cudaMalloc(&p->stage[slot], bytes));
+  p->stage_bytes[slot] = bytes;
+  return DLWP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dlwp_abi_version(void) { return DLWP_ABI_VERSION; }
+const char* dlwp_last_error(void) { return g_last_error.c_str(); }
+int64_t dlwp_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int dlwp_plan_create(const dlwp_model_desc* desc, int device, dlwp_plan** out) {
+  if (!desc || !out) return fail(DLWP_ERR_INVALID, "dlwp_plan_create: null argument");
+  *out = nullptr;
+  DLWP_TRY(check_device(device));
+  dlwp_plan* p = new (std::nothrow) dlwp_plan();
+  if (!p) return fail(DLWP_ERR_INVALID, "out of host memory");
+  p->d = *desc;
+  p->device = device;
+  int rc = plan_build(p);
+  if (rc != DLWP_OK) {
+    free_plan(p);
+    return rc;
+  }
+  *out = p;
+  return DLWP_OK;
+}
+
+int dlwp_plan_destroy(dlwp_plan* plan) {
+  free_plan(plan);
+  return DLWP_OK;
+}
+
+int dlwp_plan_workspace_bytes(const dlwp_plan* plan, size_t* bytes) {
+  if (!plan || !bytes) return fail(DLWP_ERR_INVALID, "dlwp_plan_workspace_bytes: null argument");
+  *bytes = plan->workspace_bytes;
+  return DLWP_OK;
+}
+
+int dlwp_plan_set_tensor(dlwp_plan* plan, const char* name, const void* data, int ndim, const int64_t* shape,
+                         void* stream) {
+  if (!plan || !name || !data || ndim < 0 || (ndim > 0 && !shape))
+    return fail(DLWP_ERR_INVALID, "dlwp_plan_set_tensor: null argument");
+  DLWP_CUDA(cudaSetDevice(plan->device));
+  int64_t n = 1;
+  for (int i = 0; i < ndim; ++i) {
+    DLWP_REQUIRE(shape[i] >= 0, "tensor '%s': negative dimension", name);
+    n *= shape[i];
+  }
+  NamedTensor& t = plan->tensors[name];
+  if (t.numel != n || !t.data) {
+    if (t.data) cudaFree(t.data);
+    t.data = nullptr;
+    DLWP_CUDA(cudaMalloc((void**)&t.data, (size_t)(n > 0 ? n : 1) * sizeof(float)));
+  }
+  t.numel = n;
+  t.shape.assign(shape, shape + ndim);
+  if (n > 0)
+    DLWP_CUDA(cudaMemcpyAsync(t.data, data, (size_t)n * sizeof(float), cudaMemcpyDefault, (cudaStream_t)stream));
+  plan->committed = false;
+  return DLWP_OK;
+}
+
+int dlwp_plan_commit_weights(dlwp_plan* plan, void* stream) {
+  if (!plan) return fail(DLWP_ERR_INVALID, "dlwp_plan_commit_weights: null plan");
+  DLWP_CUDA(cudaSetDevice(plan->device));
+  return plan_commit(plan, (cudaStream_t)stream);
+}
+
+int dlwp_step(dlwp_plan* plan, const float* x, float* y, int batch, void* stream) {
+  if (!plan || !x || !y) return fail(DLWP_ERR_INVALID, "dlwp_step: null argument");
+  const long long HW = (long long)plan->d.height * plan->d.width;
+  StepIO io;
+  io.grp[0] = SrcGroup{x, plan->Cin * HW, plan->Cin};
+  io.ngrp = 1;
+  io.out = y;
+  io.out_bstride = plan->d.prognostic_channels * HW;
+  return plan_backbone(plan, io, batch, (cudaStream_t)stream);
+}
+
+int dlwp_rollout(dlwp_plan* plan, const float* constants, const float* prescribed, const float* prognostic,
+                 int batch, int T, float* outs, void* stream) {
+  if (!plan || !prognostic || !outs) return fail(DLWP_ERR_INVALID, "dlwp_rollout: null prognostic / outs");
+  const dlwp_model_desc& d = plan->d;
+  DLWP_REQUIRE(T > d.context_size, "sequence length %d must exceed context_size %d", T, d.context_size);
+  DLWP_REQUIRE((d.constant_channels == 0) == (constants == nullptr),
+               "constants pointer does not match constant_channels=%d", d.constant_channels);
+  DLWP_REQUIRE((d.prescribed_channels == 0) == (prescribed == nullptr),
+               "prescribed pointer does not match prescribed_channels=%d", d.prescribed_channels);
+  for (int t = d.context_size; t < T; ++t) {
+    StepIO io;
+    rollout_io(plan, constants, prescribed, prognostic, outs, T, t, &io);
+    DLWP_TRY(plan_backbone(plan, io, batch, (cudaStream_t)stream));
+  }
+  return DLWP_OK;
+}
+
+int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* prescribed, const float* prognostic,
+                      int batch, int T, float* outs, void* stream) {
+  if (!plan || !prognostic || !outs) return fail(DLWP_ERR_INVALID, "dlwp_rollout_host: null prognostic / outs");
+  const dlwp_model_desc& d = plan->d;
+  DLWP_REQUIRE(batch > 0 && batch <= d.max_batch, "batch %d outside [1, max_batch=%d]", batch, d.max_batch);
+  DLWP_REQUIRE(T > d.context_size, "sequence length %d must exceed context_size %d", T, d.context_size);
+  DLWP_CUDA(cudaSetDevice(plan->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t HW = (size_t)d.height * d.width, B = (size_t)batch;
+  const size_t nb[4] = {constants ? B * d.constant_channels * HW * sizeof(float) : 0,
+                        prescribed ? B * T * d.prescribed_channels * HW * sizeof(float) : 0,
+                        B * T * d.prognostic_channels * HW * sizeof(float),
+                        B * (T - d.context_size) * d.prognostic_channels * HW * sizeof(float)};
+  const void* src[3] = {constants, prescribed, prognostic};
+  for (int i = 0; i < 4; ++i) DLWP_TRY(grow(plan, i, nb[i]));
+  for (int i = 0; i < 3; ++i)
+    if (nb[i]) DLWP_CUDA(cudaMemcpyAsync(plan->stage[i], src[i], nb[i], cudaMemcpyHostToDevice, st));
+  DLWP_TRY(dlwp_rollout(plan, constants ? (const float*)plan->stage[0] : nullptr,
+                        prescribed ? (const float*)plan->stage[1] : nullptr, (const float*)plan->stage[2], batch, T,
+                        (float*)plan->stage[3], stream));
+  DLWP_CUDA(cudaMemcpyAsync(outs, plan->stage[3], nb[3], cudaMemcpyDeviceToHost, st));
+  DLWP_CUDA(cudaStreamSynchronize(st));
+  return DLWP_OK;
+}
+
+int dlwp_metrics_accumulate(const float* outputs, const float* targets, const float* climatology,
+                            const float* lat_weights, int batch, int T, int C, int H, int W, double* sums,
+                            void* stream) {
+  if (!outputs || !targets || !lat_weights || !sums)
+    return fail(DLWP_ERR_INVALID, "dlwp_metrics_accumulate: null argument");
+  return launch_metrics(outputs, targets, climatology, lat_weights, batch, T, C, H, W, sums, (cudaStream_t)stream);
+}
+
+int dlwp_spectral_conv2d(const float* x, const float* weight, const float* bias, float* y, int batch, int Ci,
+                         int Co, int H, int W, int n_rows, int n_cols, const int32_t* rows_in,
+                         const int32_t* rows_out, int fft_norm, void* stream) {
+  if (!x || !weight || !y || !rows_in || !rows_out)
+    return fail(DLWP_ERR_INVALID, "dlwp_spectral_conv2d: null argument");
+  DLWP_REQUIRE(Ci == Co, "dlwp_spectral_conv2d: Ci != Co is not supported by the stand-alone entry (%d vs %d)", Ci, Co);
+  // a throw-away FNO-kind plan supplies bases and workspace; this entry is a convenience for
+  // tests and single-layer users, not the graph-capturable hot path
+  dlwp_model_desc d{};
+  d.kind = DLWP_MODEL_FNO; d.precision = DLWP_PREC_FP32; d.max_batch = batch; d.height = H; d.width = W;
+  d.prognostic_channels = Co; d.context_size = 1; d.fft_norm = fft_norm; d.n_rows = n_rows; d.n_cols = n_cols;
+  d.rows_in = rows_in; d.rows_out = rows_out; d.hidden_channels = Ci; d.projection_channels = 1; d.n_layers = 1;
+  int dev = 0;
+  DLWP_CUDA(cudaGetDevice(&dev));
+  dlwp_plan* p = nullptr;
+  DLWP_TRY(dlwp_plan_create(&d, dev, &p));
+  cudaStream_t st = (cudaStream_t)stream;
+  float2* wm = nullptr;
+  int rc = DLWP_OK;
+  const size_t wn = (size_t)Ci * Co * n_rows * n_cols;
+  if (cudaMalloc((void**)&wm, wn * sizeof(float2)) != cudaSuccess) {
+    rc = fail(DLWP_ERR_CUDA, "cudaMalloc failed for the packed spectral weight");
+  }
+  if (rc == DLWP_OK) rc = launch_pack_modes(reinterpret_cast<const float2*>(weight), wm, Ci, Co, n_rows, n_cols, st);
+  if (rc == DLWP_OK) rc = launch_nchw_to_nhwc(x, p->act0, batch, Ci, H * W, st);
+  if (rc == DLWP_OK) rc = spectral_layer(p, p->act0, p->act1, wm, 0, nullptr, nullptr, bias, 0, batch, st);
+  if (rc == DLWP_OK) rc = launch_nhwc_to_nchw(p->act1, y, batch, Co, H * W, st);
+  cudaStreamSynchronize(st);
+  if (wm) cudaFree(wm);
+  free_plan(p);
+  return rc;
+}
+
+}  // extern "C"

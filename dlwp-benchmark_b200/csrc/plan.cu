@@ -1,0 +1,441 @@
+// Plan construction, weight packing and the per-step kernel sequence (fp32 path).
+//
+// Reference lines replaced: module construction fno.py:36-47,131-146 and
+// fourcastnet.py:236-268; one backbone evaluation `self.fno(x_t)` (fno.py:103; neuralop
+// FNO.forward = lifting -> n_layers x (spectral conv + 1x1 skip, GELU) -> projection) and
+// forward_features + head + un-patchify (fourcastnet.py:283-293,345-357).
+#include "plan.cuh"
+
+#include <cmath>
+#include <cstring>
+
+namespace dlwp {
+
+thread_local std::string g_last_error;
+std::atomic<int64_t> g_launches{0};
+
+static int dev_alloc(dlwp_plan* p, void** out, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  DLWP_CUDA(cudaMalloc(out, bytes));
+  p->owned.push_back(*out);
+  p->workspace_bytes += bytes;
+  return DLWP_OK;
+}
+
+// ---- truncated-DFT bases, fp64 on the host ------------------------------------------
+//   Fw [Kc, W]  : forward along W,  s * exp(-2 pi i kx w / W)
+//   Fh [R, H]   : forward along H,      exp(-2 pi i rows_in[j] h / H)
+//   Gh [H, R]   : inverse along H,      exp(+2 pi i rows_out[j] h / H)
+//   Gw [W, Kc]  : inverse along W (C2R), t * c_kx * exp(+2 pi i kx w / W), c = 1 for the DC
+//                 and Nyquist columns, 2 otherwise; taking the real part of Gw . Z drops the
+//                 imaginary part of those two columns exactly as irfft2 does.
+static void twiddle(long long k, long long n, long long N, double sign, double scale, float2* out) {
+  long long r = (k * n) % N;
+  if (r < 0) r += N;
+  const double ang = sign * 2.0 * M_PI * (double)r / (double)N;
+  *out = make_float2((float)(scale * std::cos(ang)), (float)(scale * std::sin(ang)));
+}
+
+static int build_bases(dlwp_plan* p) {
+  const int H = p->gh, W = p->gw, R = (int)p->rows_in.size(), Kc = p->d.n_cols;
+  double s = 1.0, t = 1.0;
+  const double hw = (double)H * (double)W;
+  switch (p->d.fft_norm) {
+    case DLWP_FFT_NORM_BACKWARD: t = 1.0 / hw; break;
+    case DLWP_FFT_NORM_FORWARD: s = 1.0 / hw; break;
+    case DLWP_FFT_NORM_ORTHO: s = t = 1.0 / std::sqrt(hw); break;
+    default: return fail(DLWP_ERR_INVALID, "unknown fft_norm %d", p->d.fft_norm);
+  }
+  std::vector<float2> fw((size_t)Kc * W), fh((size_t)R * H), gh((size_t)H * R), gw((size_t)W * Kc);
+  for (int k = 0; k < Kc; ++k)
+    for (int w = 0; w < W; ++w) twiddle(k, w, W, -1.0, s, &fw[(size_t)k * W + w]);
+  for (int j = 0; j < R; ++j)
+    for (int h = 0; h < H; ++h) twiddle(p->rows_in[j], h, H, -1.0, 1.0, &fh[(size_t)j * H + h]);
+  for (int h = 0; h < H; ++h)
+    for (int j = 0; j < R; ++j) twiddle(p->rows_out[j], h, H, +1.0, 1.0, &gh[(size_t)h * R + j]);
+  for (int w = 0; w < W; ++w)
+    for (int k = 0; k < Kc; ++k) {
+      const bool self_conj = (k == 0) || (W % 2 == 0 && k == W / 2);
+      twiddle(k, w, W, +1.0, t * (self_conj ? 1.0 : 2.0), &gw[(size_t)w * Kc + k]);
+    }
+  DLWP_TRY(dev_alloc(p, (void**)&p->Fw, fw.size() * sizeof(float2)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->Fh, fh.size() * sizeof(float2)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->Gh, gh.size() * sizeof(float2)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->Gw, gw.size() * sizeof(float2)));
+  DLWP_CUDA(cudaMemcpy(p->Fw, fw.data(), fw.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  DLWP_CUDA(cudaMemcpy(p->Fh, fh.data(), fh.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  DLWP_CUDA(cudaMemcpy(p->Gh, gh.data(), gh.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  DLWP_CUDA(cudaMemcpy(p->Gw, gw.data(), gw.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  return DLWP_OK;
+}
+
+int plan_build(dlwp_plan* p) {
+  const dlwp_model_desc& d = p->d;
+  DLWP_REQUIRE(d.kind == DLWP_MODEL_FNO || d.kind == DLWP_MODEL_AFNO, "unknown model kind %d", d.kind);
+  DLWP_REQUIRE(d.precision == DLWP_PREC_FP32, "precision mode %d is not built into this library yet",
+               d.precision);
+  DLWP_REQUIRE(d.max_batch > 0 && d.height > 0 && d.width > 0, "max_batch/height/width must be positive");
+  DLWP_REQUIRE(d.constant_channels >= 0 && d.prescribed_channels >= 0 && d.prognostic_channels > 0 &&
+                   d.context_size > 0,
+               "bad channel counts / context_size");
+  p->Cin = d.constant_channels + (d.prescribed_channels + d.prognostic_channels) * d.context_size;
+  int p1 = 1, p2 = 1;
+  if (d.kind == DLWP_MODEL_AFNO) {
+    p1 = d.patch_h; p2 = d.patch_w;
+    DLWP_REQUIRE(p1 > 0 && p2 > 0 && d.height % p1 == 0 && d.width % p2 == 0,
+                 "patch size %dx%d does not divide the %dx%d grid", p1, p2, d.height, d.width);
+    DLWP_REQUIRE(d.embed_dim > 0 && d.depth > 0 && d.num_blocks > 0 && d.embed_dim % d.num_blocks == 0,
+                 "hidden_size %d should be divisble by num_blocks %d", d.embed_dim, d.num_blocks);
+    DLWP_REQUIRE(d.mlp_hidden > 0 && d.hidden_size_factor > 0, "mlp_hidden / hidden_size_factor must be positive");
+    p->C = d.embed_dim;
+    p->n_spec = d.depth;
+  } else {
+    DLWP_REQUIRE(d.hidden_channels > 0 && d.n_layers > 0 && d.projection_channels > 0 && d.lifting_channels >= 0,
+                 "bad FNO widths");
+    p->C = d.hidden_channels;
+    p->n_spec = d.n_layers;
+  }
+  p->gh = d.height / p1;
+  p->gw = d.width / p2;
+  DLWP_REQUIRE(d.n_rows >= 0 && d.n_cols >= 0 && d.n_rows <= p->gh && d.n_cols <= p->gw / 2 + 1,
+               "retained bins %dx%d exceed the %dx%d half spectrum", d.n_rows, d.n_cols, p->gh, p->gw / 2 + 1);
+  DLWP_REQUIRE(d.n_rows == 0 || (d.rows_in && d.rows_out), "rows_in / rows_out are required");
+  p->rows_in.assign(d.rows_in, d.rows_in + d.n_rows);
+  p->rows_out.assign(d.rows_out, d.rows_out + d.n_rows);
+  p->d.rows_in = p->rows_in.data();
+  p->d.rows_out = p->rows_out.data();
+  std::vector<char> seen(p->gh, 0);
+  for (int j = 0; j < d.n_rows; ++j) {
+    DLWP_REQUIRE(p->rows_in[j] >= 0 && p->rows_in[j] < p->gh && p->rows_out[j] >= 0 && p->rows_out[j] < p->gh,
+                 "row bin out of range");
+    DLWP_REQUIRE(!seen[p->rows_out[j]], "rows_out holds bin %d twice", p->rows_out[j]);
+    seen[p->rows_out[j]] = 1;
+  }
+  DLWP_TRY(build_bases(p));
+
+  // workspace
+  const size_t B = (size_t)d.max_batch, tokens = (size_t)p->gh * p->gw, P = B * tokens, C = (size_t)p->C;
+  size_t hidw = d.kind == DLWP_MODEL_AFNO
+                    ? (size_t)d.mlp_hidden
+                    : (size_t)(d.lifting_channels > d.projection_channels ? d.lifting_channels
+                                                                          : d.projection_channels);
+  DLWP_TRY(dev_alloc(p, (void**)&p->act0, P * C * sizeof(float)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->act1, P * C * sizeof(float)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->act2, P * C * sizeof(float)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->act3, P * C * sizeof(float)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->hid, P * hidw * sizeof(float)));
+  const size_t R = (size_t)d.n_rows, Kc = (size_t)d.n_cols;
+  DLWP_TRY(dev_alloc(p, (void**)&p->specA, B * p->gh * Kc * C * sizeof(float2)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->specZ, B * p->gh * Kc * C * sizeof(float2)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->specX, R * Kc * B * C * sizeof(float2)));
+  DLWP_TRY(dev_alloc(p, (void**)&p->specY, R * Kc * B * C * sizeof(float2)));
+  return DLWP_OK;
+}
+
+}  // namespace dlwp
+
+namespace dlwp {
+
+// ---- weight lookup --------------------------------------------------------------------
+static const NamedTensor* find(const dlwp_plan* p, const std::string& name) {
+  auto it = p->tensors.find(name);
+  return it == p->tensors.end() ? nullptr : &it->second;
+}
+
+static int need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out) {
+  const NamedTensor* t = find(p, name);
+  if (!t) return fail(DLWP_ERR_MISSING, "weight tensor '%s' was not set", name.c_str());
+  if (t->numel != numel)
+    return fail(DLWP_ERR_INVALID, "weight tensor '%s' has %lld elements, expected %lld", name.c_str(),
+                (long long)t->numel, (long long)numel);
+  *out = t->data;
+  return DLWP_OK;
+}
+
+static std::string idx(const char* pre, int i, const char* post) {
+  return std::string(pre) + std::to_string(i) + post;
+}
+
+// ---- commit: pack spectral weights (dense or Tucker) mode-major ---------------------------
+static int commit_fno(dlwp_plan* p, cudaStream_t st) {
+  const dlwp_model_desc& d = p->d;
+  const int C = p->C, R = d.n_rows, Kc = d.n_cols;
+  const int64_t dense_n = (int64_t)C * C * R * Kc;
+  const float* dummy;
+  if (d.lifting_channels > 0) {
+    DLWP_TRY(need(p, "lifting.fcs.0.weight", (int64_t)d.lifting_channels * p->Cin, &dummy));
+    DLWP_TRY(need(p, "lifting.fcs.0.bias", d.lifting_channels, &dummy));
+    DLWP_TRY(need(p, "lifting.fcs.1.weight", (int64_t)C * d.lifting_channels, &dummy));
+    DLWP_TRY(need(p, "lifting.fcs.1.bias", C, &dummy));
+  } else {
+    DLWP_TRY(need(p, "lifting.fcs.0.weight", (int64_t)C * p->Cin, &dummy));
+    DLWP_TRY(need(p, "lifting.fcs.0.bias", C, &dummy));
+  }
+  DLWP_TRY(need(p, "projection.fcs.0.weight", (int64_t)d.projection_channels * C, &dummy));
+  DLWP_TRY(need(p, "projection.fcs.0.bias", d.projection_channels, &dummy));
+  DLWP_TRY(need(p, "projection.fcs.1.weight", (int64_t)d.prognostic_channels * d.projection_channels, &dummy));
+  DLWP_TRY(need(p, "projection.fcs.1.bias", d.prognostic_channels, &dummy));
+  DLWP_TRY(need(p, "fno_blocks.convs.bias", (int64_t)d.n_layers * C, &dummy));
+
+  if (p->wm.empty()) {
+    p->wm.resize(d.n_layers, nullptr);
+    for (int l = 0; l < d.n_layers; ++l)
+      DLWP_TRY(dev_alloc(p, (void**)&p->wm[l], (size_t)(dense_n > 0 ? dense_n : 1) * sizeof(float2)));
+  }
+  float2* dense_tmp = nullptr;
+  double2* scratch = nullptr;
+  for (int l = 0; l < d.n_layers; ++l) {
+    DLWP_TRY(need(p, idx("fno_blocks.fno_skips.", l, ".weight"), (int64_t)C * C, &dummy));
+    if (dense_n == 0) continue;
+    const std::string base = idx("fno_blocks.convs.weight.", l, "");
+    const float* src = nullptr;
+    if (find(p, base + ".tensor")) {
+      DLWP_TRY(need(p, base + ".tensor", dense_n * 2, &src));
+    } else if (find(p, base + ".core")) {
+      const NamedTensor* core = find(p, base + ".core");
+      DLWP_REQUIRE(core->shape.size() == 5 && core->shape[4] == 2,
+                   "'%s.core' must be a complex real view [r_i, r_o, r_x, r_y, 2]", base.c_str());
+      const int dims[4] = {C, C, R, Kc};
+      int ranks[4];
+      const float2* U[4];
+      for (int k = 0; k < 4; ++k) {
+        ranks[k] = (int)core->shape[k];
+        const float* f;
+        DLWP_TRY(need(p, base + ".factors.factor_" + std::to_string(k), (int64_t)dims[k] * ranks[k] * 2, &f));
+        U[k] = reinterpret_cast<const float2*>(f);
+      }
+      if (!dense_tmp) DLWP_CUDA(cudaMalloc((void**)&dense_tmp, (size_t)dense_n * sizeof(float2)));
+      const size_t se = tucker_scratch_elems(dims, ranks);
+      double2* sc = nullptr;
+      DLWP_CUDA(cudaMalloc((void**)&sc, 2 * se * sizeof(double2)));
+      int rc = launch_tucker_to_dense(reinterpret_cast<const float2*>(core->data), U, dims, ranks, sc, dense_tmp, st);
+      cudaStreamSynchronize(st);
+      cudaFree(sc);
+      if (rc != DLWP_OK) { cudaFree(dense_tmp); return rc; }
+      src = reinterpret_cast<const float*>(dense_tmp);
+    } else {
+      if (dense_tmp) cudaFree(dense_tmp);
+      return fail(DLWP_ERR_MISSING, "spectral weight of layer %d: neither '%s.tensor' nor '%s.core' was set", l,
+                  base.c_str(), base.c_str());
+    }
+    int rc = launch_pack_modes(reinterpret_cast<const float2*>(src), p->wm[l], C, C, R, Kc, st);
+    if (rc != DLWP_OK) { if (dense_tmp) cudaFree(dense_tmp); return rc; }
+  }
+  (void)scratch;
+  if (dense_tmp) {
+    cudaStreamSynchronize(st);
+    cudaFree(dense_tmp);
+  }
+  return DLWP_OK;
+}
+
+static int commit_afno(dlwp_plan* p, cudaStream_t) {
+  const dlwp_model_desc& d = p->d;
+  const int E = d.embed_dim, nb = d.num_blocks, bs = E / nb, f = d.hidden_size_factor;
+  const int pp = d.patch_h * d.patch_w;
+  const float* dummy;
+  DLWP_TRY(need(p, "patch_embed.proj.weight", (int64_t)E * p->Cin * pp, &dummy));
+  DLWP_TRY(need(p, "patch_embed.proj.bias", E, &dummy));
+  if (d.use_pos_embed) DLWP_TRY(need(p, "pos_embed", (int64_t)p->gh * p->gw * E, &dummy));
+  DLWP_TRY(need(p, "head.weight", (int64_t)d.prognostic_channels * pp * E, &dummy));
+  for (int i = 0; i < d.depth; ++i) {
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm1.weight"), E, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm1.bias"), E, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm2.weight"), E, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm2.bias"), E, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".filter.w1"), (int64_t)2 * nb * bs * bs * f, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".filter.b1"), (int64_t)2 * nb * bs * f, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".filter.w2"), (int64_t)2 * nb * bs * f * bs, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".filter.b2"), (int64_t)2 * nb * bs, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.weight"), (int64_t)d.mlp_hidden * E, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.bias"), d.mlp_hidden, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc2.weight"), (int64_t)E * d.mlp_hidden, &dummy));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc2.bias"), E, &dummy));
+  }
+  return DLWP_OK;
+}
+
+int plan_commit(dlwp_plan* p, cudaStream_t st) {
+  p->committed = false;
+  if (p->d.kind == DLWP_MODEL_FNO) DLWP_TRY(commit_fno(p, st));
+  else DLWP_TRY(commit_afno(p, st));
+  p->committed = true;
+  return DLWP_OK;
+}
+
+}  // namespace dlwp
+
+namespace dlwp {
+
+// ---- one spectral layer on channels-last activations -----------------------------------
+//   y = act( Re irfft2( mix( rfft2(x)[rows_in, :Kc] ) -> [rows_out, :Kc] ) + add1 + add2 + bias )
+// FNO: mix = dense per-mode C x C complex product (wm); AFNO: block-diagonal MLP (layer idx).
+int spectral_layer(dlwp_plan* p, const float* x, float* y, const float2* wm, int layer, const float* add1,
+                   const float* add2, const float* bias, int act, int B, cudaStream_t st) {
+  const int H = p->gh, W = p->gw, C = p->C, R = p->d.n_rows, Kc = p->d.n_cols;
+  TdftArgs a{};
+  // forward along W: x [B, H, W, C] real -> A [B, H, Kc, C]
+  a.in = x; a.out = p->specA; a.T = p->Fw; a.N = W; a.K = Kc; a.C = C; a.nb0 = B; a.nb1 = H;
+  a.in_sn = C; a.in_sb0 = (long long)H * W * C; a.in_sb1 = (long long)W * C;
+  a.out_sk = C; a.out_sb0 = (long long)H * Kc * C; a.out_sb1 = (long long)Kc * C;
+  a.in_complex = false; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  // forward along H: A -> X [R, Kc, B, C]
+  a = TdftArgs{};
+  a.in = p->specA; a.out = p->specX; a.T = p->Fh; a.N = H; a.K = R; a.C = C; a.nb0 = B; a.nb1 = Kc;
+  a.in_sn = (long long)Kc * C; a.in_sb0 = (long long)H * Kc * C; a.in_sb1 = C;
+  a.out_sk = (long long)Kc * B * C; a.out_sb0 = C; a.out_sb1 = (long long)B * C;
+  a.in_complex = true; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  // channel mixing per retained mode
+  if (p->d.kind == DLWP_MODEL_FNO) {
+    DLWP_TRY(launch_mix_dense(p->specX, wm, p->specY, R * Kc, B, C, C, st));
+  } else {
+    const float *w1, *b1, *w2, *b2;
+    const int nb = p->d.num_blocks, bs = C / nb, f = p->d.hidden_size_factor;
+    DLWP_TRY(need(p, idx("blocks.", layer, ".filter.w1"), (int64_t)2 * nb * bs * bs * f, &w1));
+    DLWP_TRY(need(p, idx("blocks.", layer, ".filter.b1"), (int64_t)2 * nb * bs * f, &b1));
+    DLWP_TRY(need(p, idx("blocks.", layer, ".filter.w2"), (int64_t)2 * nb * bs * f * bs, &w2));
+    DLWP_TRY(need(p, idx("blocks.", layer, ".filter.b2"), (int64_t)2 * nb * bs, &b2));
+    DLWP_TRY(launch_mix_afno(p->specX, p->specY, w1, b1, w2, b2, R * Kc, B, nb, bs, f, p->d.sparsity_threshold, st));
+  }
+  // inverse along H: Y [R, Kc, B, C] -> Z [B, H, Kc, C]
+  a = TdftArgs{};
+  a.in = p->specY; a.out = p->specZ; a.T = p->Gh; a.N = R; a.K = H; a.C = C; a.nb0 = B; a.nb1 = Kc;
+  a.in_sn = (long long)Kc * B * C; a.in_sb0 = C; a.in_sb1 = (long long)B * C;
+  a.out_sk = (long long)Kc * C; a.out_sb0 = (long long)H * Kc * C; a.out_sb1 = C;
+  a.in_complex = true; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  // inverse along W (C2R) with the fused epilogue: Z -> y [B, H, W, C]
+  a = TdftArgs{};
+  a.in = p->specZ; a.out = y; a.T = p->Gw; a.N = Kc; a.K = W; a.C = C; a.nb0 = B; a.nb1 = H;
+  a.in_sn = C; a.in_sb0 = (long long)H * Kc * C; a.in_sb1 = (long long)Kc * C;
+  a.out_sk = C; a.out_sb0 = (long long)H * W * C; a.out_sb1 = (long long)W * C;
+  a.in_complex = true; a.out_complex = false;
+  a.add1 = add1; a.add2 = add2; a.bias = bias; a.act = act;
+  DLWP_TRY(launch_tdft(a, st));
+  return DLWP_OK;
+}
+
+static PwArgs pw_plain(const float* in, const float* Wt, const float* bias, float* out, int P, int K, int N,
+                       int tokens, int act) {
+  PwArgs a{};
+  a.in = in; a.Wt = Wt; a.bias = bias; a.out = out; a.P = P; a.K = K; a.N = N; a.tokens = tokens; a.act = act;
+  a.p1 = a.p2 = 1;
+  return a;
+}
+
+static void pw_set_gather(PwArgs& a, const StepIO& io, int H, int W, int p1, int p2) {
+  a.in = nullptr;
+  a.ngrp = io.ngrp;
+  for (int g = 0; g < io.ngrp; ++g) a.grp[g] = io.grp[g];
+  a.H = H; a.W = W; a.p1 = p1; a.p2 = p2;
+}
+
+static void pw_set_unpatch(PwArgs& a, const StepIO& io, int H, int W, int p1, int p2, int Cg) {
+  a.unpatch = 1; a.H = H; a.W = W; a.p1 = p1; a.p2 = p2; a.Cg = Cg;
+  a.out = io.out; a.out_bstride = io.out_bstride; a.last = io.last; a.last_bstride = io.last_bstride;
+}
+
+static int backbone_fno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
+  const dlwp_model_desc& d = p->d;
+  const int H = d.height, W = d.width, HW = H * W, P = B * HW, C = p->C, L = d.lifting_channels,
+            Pj = d.projection_channels, Cg = d.prognostic_channels;
+  const float *w, *b;
+  float* cur = p->act0;
+  float* nxt = p->act1;
+  // lifting (neuralop MLP: 1x1 conv -> GELU -> 1x1 conv), input gathered from the NCHW sources
+  if (L > 0) {
+    DLWP_TRY(need(p, "lifting.fcs.0.weight", (int64_t)L * p->Cin, &w));
+    DLWP_TRY(need(p, "lifting.fcs.0.bias", L, &b));
+    PwArgs a = pw_plain(nullptr, w, b, p->hid, P, p->Cin, L, HW, 1);
+    pw_set_gather(a, io, H, W, 1, 1);
+    DLWP_TRY(launch_pw_linear(a, st));
+    DLWP_TRY(need(p, "lifting.fcs.1.weight", (int64_t)C * L, &w));
+    DLWP_TRY(need(p, "lifting.fcs.1.bias", C, &b));
+    DLWP_TRY(launch_pw_linear(pw_plain(p->hid, w, b, cur, P, L, C, HW, 0), st));
+  } else {
+    DLWP_TRY(need(p, "lifting.fcs.0.weight", (int64_t)C * p->Cin, &w));
+    DLWP_TRY(need(p, "lifting.fcs.0.bias", C, &b));
+    PwArgs a = pw_plain(nullptr, w, b, cur, P, p->Cin, C, HW, 0);
+    pw_set_gather(a, io, H, W, 1, 1);
+    DLWP_TRY(launch_pw_linear(a, st));
+  }
+  // FNO blocks: x = gelu(spectral(x) + bias_l + skip_l(x)), no GELU after the last block
+  const float* cbias;
+  DLWP_TRY(need(p, "fno_blocks.convs.bias", (int64_t)d.n_layers * C, &cbias));
+  for (int l = 0; l < d.n_layers; ++l) {
+    DLWP_TRY(need(p, idx("fno_blocks.fno_skips.", l, ".weight"), (int64_t)C * C, &w));
+    DLWP_TRY(launch_pw_linear(pw_plain(cur, w, nullptr, p->act2, P, C, C, HW, 0), st));
+    const int act = l < d.n_layers - 1 ? 1 : 0;
+    if (d.n_rows > 0 && d.n_cols > 0) {
+      DLWP_TRY(spectral_layer(p, cur, nxt, p->wm[l], l, p->act2, nullptr, cbias + (size_t)l * C, act, B, st));
+    } else {
+      return fail(DLWP_ERR_INVALID, "a spectral layer without retained modes is not supported");
+    }
+    float* t = cur; cur = nxt; nxt = t;
+  }
+  // projection + residual on the last context frame, written straight into the NCHW output
+  DLWP_TRY(need(p, "projection.fcs.0.weight", (int64_t)Pj * C, &w));
+  DLWP_TRY(need(p, "projection.fcs.0.bias", Pj, &b));
+  DLWP_TRY(launch_pw_linear(pw_plain(cur, w, b, p->hid, P, C, Pj, HW, 1), st));
+  DLWP_TRY(need(p, "projection.fcs.1.weight", (int64_t)Cg * Pj, &w));
+  DLWP_TRY(need(p, "projection.fcs.1.bias", Cg, &b));
+  PwArgs a = pw_plain(p->hid, w, b, nullptr, P, Pj, Cg, HW, 0);
+  pw_set_unpatch(a, io, H, W, 1, 1, Cg);
+  DLWP_TRY(launch_pw_linear(a, st));
+  return DLWP_OK;
+}
+
+static int backbone_afno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
+  const dlwp_model_desc& d = p->d;
+  const int H = d.height, W = d.width, p1 = d.patch_h, p2 = d.patch_w, tokens = p->gh * p->gw, P = B * tokens,
+            E = d.embed_dim, Hd = d.mlp_hidden, Cg = d.prognostic_channels, pp = p1 * p2;
+  const float *w, *b, *g1, *be1, *g2, *be2;
+  float* t = p->act0;   // residual stream
+  float* u = p->act1;   // LayerNorm output
+  float* t2 = p->act2;  // after the filter + skips
+  // patch embedding (+ position embedding), fourcastnet.py:285-289,537-542
+  DLWP_TRY(need(p, "patch_embed.proj.weight", (int64_t)E * p->Cin * pp, &w));
+  DLWP_TRY(need(p, "patch_embed.proj.bias", E, &b));
+  {
+    PwArgs a = pw_plain(nullptr, w, b, t, P, p->Cin * pp, E, tokens, 0);
+    pw_set_gather(a, io, H, W, p1, p2);
+    if (d.use_pos_embed) DLWP_TRY(need(p, "pos_embed", (int64_t)tokens * E, &a.pos));
+    DLWP_TRY(launch_pw_linear(a, st));
+  }
+  for (int i = 0; i < d.depth; ++i) {
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm1.weight"), E, &g1));
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm1.bias"), E, &be1));
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm2.weight"), E, &g2));
+    DLWP_TRY(need(p, idx("blocks.", i, ".norm2.bias"), E, &be2));
+    // x = filter(norm1(x)) + x : AFNO2D adds its own input back (:127) and Block adds the
+    // pre-norm residual again (double_skip, :185-187)
+    DLWP_TRY(launch_layernorm(t, u, g1, be1, P, E, d.layernorm_eps, st));
+    DLWP_TRY(spectral_layer(p, u, t2, nullptr, i, u, t, nullptr, 0, B, st));
+    // x = mlp(norm2(x)) + x
+    DLWP_TRY(launch_layernorm(t2, u, g2, be2, P, E, d.layernorm_eps, st));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.weight"), (int64_t)Hd * E, &w));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.bias"), Hd, &b));
+    DLWP_TRY(launch_pw_linear(pw_plain(u, w, b, p->hid, P, E, Hd, tokens, 1), st));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc2.weight"), (int64_t)E * Hd, &w));
+    DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc2.bias"), E, &b));
+    PwArgs a = pw_plain(p->hid, w, b, t, P, Hd, E, tokens, 0);
+    a.resid = t2;
+    DLWP_TRY(launch_pw_linear(a, st));
+  }
+  // head (no bias, the final self.norm is not applied) + un-patchify + last-frame residual
+  DLWP_TRY(need(p, "head.weight", (int64_t)Cg * pp * E, &w));
+  PwArgs a = pw_plain(t, w, nullptr, nullptr, P, E, Cg * pp, tokens, 0);
+  pw_set_unpatch(a, io, H, W, p1, p2, Cg);
+  DLWP_TRY(launch_pw_linear(a, st));
+  return DLWP_OK;
+}
+
+int plan_backbone(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
+  if (!p->committed) return fail(DLWP_ERR_STATE, "dlwp_plan_commit_weights has not been called");
+  DLWP_REQUIRE(B > 0 && B <= p->d.max_batch, "batch %d outside [1, max_batch=%d]", B, p->d.max_batch);
+  return p->d.kind == DLWP_MODEL_FNO ? backbone_fno(p, io, B, st) : backbone_afno(p, io, B, st);
+}
+
+}  // namespace dlwp

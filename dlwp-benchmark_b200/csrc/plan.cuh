@@ -1,0 +1,67 @@
+// Plan object behind the C ABI (include/dlwp_b200.h): owns the model description, the
+// truncated-DFT bases, the packed weights and every workspace buffer.
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace dlwp {
+
+struct NamedTensor {
+  std::vector<int64_t> shape;
+  float* data = nullptr;  // device, plan-owned
+  int64_t numel = 0;
+};
+
+// Where one backbone evaluation reads its input from and writes its output to.
+struct StepIO {
+  SrcGroup grp[4];
+  int ngrp = 0;
+  float* out = nullptr;        // NCHW frame(s): out[b * out_bstride + (c, y, x)]
+  long long out_bstride = 0;
+  const float* last = nullptr; // residual frame (prognostic_t[:, -1]) or null
+  long long last_bstride = 0;
+};
+
+}  // namespace dlwp
+
+struct dlwp_plan {
+  dlwp_model_desc d{};
+  int device = 0;
+  int Cin = 0;          // Cc + (Cp + Cg) * ctx
+  int gh = 0, gw = 0;   // grid the spectral transform runs on (tokens: H/p1, W/p2)
+  int C = 0;            // channel width of the spectral layers (hidden_channels | embed_dim)
+  int n_spec = 0;       // number of spectral layers (n_layers | depth)
+  std::vector<int32_t> rows_in, rows_out;
+  bool committed = false;
+
+  std::map<std::string, dlwp::NamedTensor> tensors;
+  std::vector<void*> owned;   // every cudaMalloc of this plan except `tensors` and staging
+  size_t workspace_bytes = 0;
+
+  // truncated-DFT bases (float2, built in fp64)
+  float2 *Fw = nullptr, *Fh = nullptr, *Gh = nullptr, *Gw = nullptr;
+
+  // FNO: mode-major spectral weights per layer [R, Kc, C, C]
+  std::vector<float2*> wm;
+
+  // workspace
+  float *act0 = nullptr, *act1 = nullptr, *act2 = nullptr, *act3 = nullptr;  // [P, C]
+  float* hid = nullptr;                                                    // [P, max hidden]
+  float2 *specA = nullptr, *specZ = nullptr;                               // [B, gh, Kc, C]
+  float2 *specX = nullptr, *specY = nullptr;                               // [R, Kc, B, C]
+
+  // host-entry staging (dlwp_rollout_host)
+  void* stage[4] = {nullptr, nullptr, nullptr, nullptr};
+  size_t stage_bytes[4] = {0, 0, 0, 0};
+};
+
+namespace dlwp {
+int plan_build(dlwp_plan* p);                                  // bases + workspace
+int plan_commit(dlwp_plan* p, cudaStream_t st);                // pack weights
+int plan_backbone(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
+int spectral_layer(dlwp_plan* p, const float* x, float* y, const float2* wm_or_null, int layer,
+                   const float* add1, const float* add2, const float* bias, int act, int B, cudaStream_t st);
+}  // namespace dlwp

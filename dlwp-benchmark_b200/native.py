@@ -1,0 +1,99 @@
+"""ctypes binding of ``libdlwp_b200.so`` (C ABI in ``include/dlwp_b200.h``).
+
+There is no CPU fallback: if the library has not been built, or no sm_100 device is present,
+the calls raise.  Build it with ``python -c "import __graft_entry__ as g; g.build()"`` or
+``python dlwp-benchmark_b200/build.py``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libdlwp_b200.so")
+
+ABI_VERSION = 1
+MODEL_FNO, MODEL_AFNO = 0, 1
+PREC_FP32, PREC_FP32_TC, PREC_BF16 = 0, 1, 2
+FFT_NORM_BACKWARD, FFT_NORM_FORWARD, FFT_NORM_ORTHO = 0, 1, 2
+
+
+class ModelDesc(C.Structure):
+    """Mirror of ``dlwp_model_desc`` (field order and types must match the header)."""
+    _fields_ = [
+        ("kind", C.c_int32), ("precision", C.c_int32), ("max_batch", C.c_int32),
+        ("height", C.c_int32), ("width", C.c_int32),
+        ("constant_channels", C.c_int32), ("prescribed_channels", C.c_int32),
+        ("prognostic_channels", C.c_int32), ("context_size", C.c_int32),
+        ("fft_norm", C.c_int32), ("n_rows", C.c_int32), ("n_cols", C.c_int32),
+        ("rows_in", C.POINTER(C.c_int32)), ("rows_out", C.POINTER(C.c_int32)),
+        ("hidden_channels", C.c_int32), ("lifting_channels", C.c_int32),
+        ("projection_channels", C.c_int32), ("n_layers", C.c_int32),
+        ("embed_dim", C.c_int32), ("depth", C.c_int32), ("num_blocks", C.c_int32),
+        ("mlp_hidden", C.c_int32), ("patch_h", C.c_int32), ("patch_w", C.c_int32),
+        ("use_pos_embed", C.c_int32), ("hidden_size_factor", C.c_int32),
+        ("sparsity_threshold", C.c_float), ("layernorm_eps", C.c_float),
+    ]
+
+
+# name -> (restype, argtypes); every symbol the header declares
+_P = C.c_void_p
+SYMBOLS = {
+    "dlwp_abi_version": (C.c_int, []),
+    "dlwp_last_error": (C.c_char_p, []),
+    "dlwp_plan_create": (C.c_int, [C.POINTER(ModelDesc), C.c_int, C.POINTER(_P)]),
+    "dlwp_plan_destroy": (C.c_int, [_P]),
+    "dlwp_plan_workspace_bytes": (C.c_int, [_P, C.POINTER(C.c_size_t)]),
+    "dlwp_plan_set_tensor": (C.c_int, [_P, C.c_char_p, _P, C.c_int, C.POINTER(C.c_int64), _P]),
+    "dlwp_plan_commit_weights": (C.c_int, [_P, _P]),
+    "dlwp_step": (C.c_int, [_P, _P, _P, C.c_int, _P]),
+    "dlwp_rollout": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    "dlwp_rollout_host": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    "dlwp_metrics_accumulate": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "dlwp_spectral_conv2d": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
+    "dlwp_launch_count": (C.c_int64, []),
+}
+
+_lib = None
+_lock = threading.Lock()
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load the shared library once; raise (never fall back) when it is missing."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.isfile(LIB_PATH):
+                    raise NativeError(
+                        f"{LIB_PATH} is missing: build the CUDA extension first (__graft_entry__.build()). "
+                        "dlwp_benchmark_b200 has no CPU or PyTorch fallback.")
+                handle = C.CDLL(LIB_PATH)
+                for name, (res, args) in SYMBOLS.items():
+                    fn = getattr(handle, name)
+                    fn.restype, fn.argtypes = res, args
+                if handle.dlwp_abi_version() != ABI_VERSION:
+                    raise NativeError(f"ABI mismatch: library {handle.dlwp_abi_version()}, binding {ABI_VERSION}")
+                _lib = handle
+    return _lib
+
+
+def check(status: int, what: str = ""):
+    if status != 0:
+        msg = lib().dlwp_last_error().decode("utf-8", "replace")
+        raise NativeError(f"{what or 'dlwp call'} failed ({status}): {msg}")
+
+
+def launch_count() -> int:
+    return int(lib().dlwp_launch_count())
+
+
+def int32_array(values):
+    arr = (C.c_int32 * max(len(values), 1))(*values)
+    return arr

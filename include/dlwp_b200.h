@@ -1,0 +1,154 @@
+/*
+ * dlwp_b200.h -- C ABI of the B200-native rollout forward pass for dlwp-benchmark's
+ * Fourier-neural-operator backbones (FNO2D / TFNO2D / FourCastNet-AFNO).
+ *
+ * The reference (AnneLouisedb/dlwp-benchmark) is pure Python and has no FFI of its own:
+ * the seam it offers is the nn.Module contract of
+ *   src/dlwpbench/models/fno/fno.py:12-146            (FNO2DModule, TFNO2DModule)
+ *   src/dlwpbench/models/fourcastnet/fourcastnet.py:214-361 (AFNONet = "FourCastNet")
+ * Each entry point below states which reference lines it replaces.  The Python front end
+ * (dlwp_benchmark_b200.models) binds these with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative dlwp_status otherwise; nothing
+ *     throws, aborts, exits or prints.  dlwp_last_error() gives the message (thread-local).
+ *   - tensors are raw pointers + sizes; fp32 unless stated; no torch types.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - the caller owns every buffer it passes; the plan owns packed weights, DFT bases and
+ *     workspace, all allocated in plan_create / commit_weights.  dlwp_step, dlwp_rollout and
+ *     dlwp_metrics_accumulate never allocate, never synchronise and only use `stream`, so
+ *     they can be captured in a CUDA graph.  A plan is not thread-safe.
+ *   - there is no CPU fallback: without a usable sm_100 device plan_create fails.
+ */
+#ifndef DLWP_B200_H
+#define DLWP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLWP_ABI_VERSION 1
+
+typedef enum {
+  DLWP_OK = 0,
+  DLWP_ERR_INVALID = -1,      /* bad argument / unsupported shape      */
+  DLWP_ERR_CUDA = -2,         /* a CUDA runtime call failed            */
+  DLWP_ERR_STATE = -3,        /* call order (weights not committed...) */
+  DLWP_ERR_MISSING = -4,      /* a required weight tensor is missing   */
+  DLWP_ERR_NO_DEVICE = -5     /* no CUDA device / not sm_100           */
+} dlwp_status;
+
+typedef enum {
+  DLWP_MODEL_FNO = 0,         /* neuralop FNO (dense) and TFNO (Tucker, densified at load) */
+  DLWP_MODEL_AFNO = 1         /* FourCastNet AFNONet with the AFNO2D filter                */
+} dlwp_model_kind;
+
+typedef enum {
+  DLWP_PREC_FP32 = 0,         /* fp32 storage, fp32 FMA arithmetic (parity mode, <=1e-4)   */
+  DLWP_PREC_FP32_TC = 1,      /* fp32 storage, split-bf16 tensor-core GEMMs, fp32 accumulate */
+  DLWP_PREC_BF16 = 2          /* bf16 operands on tensor cores, fp32 accumulate            */
+} dlwp_precision;
+
+typedef enum {
+  DLWP_FFT_NORM_BACKWARD = 0, /* forward unscaled, inverse 1/(H*W)   (unet.py:49,68)       */
+  DLWP_FFT_NORM_FORWARD = 1,  /* forward 1/(H*W), inverse unscaled   (neuralop fft_norm)   */
+  DLWP_FFT_NORM_ORTHO = 2     /* 1/sqrt(H*W) both ways               (fourcastnet.py:85,124) */
+} dlwp_fft_norm;
+
+/* Model description = the reference constructor kwargs after the front end resolved them.
+ * FNO fields mirror fno.py:18-47 (and the neuralop defaults they imply); AFNO fields mirror
+ * fourcastnet.py:215-268.  Unused fields of the other kind are ignored. */
+typedef struct {
+  int32_t kind;                 /* dlwp_model_kind */
+  int32_t precision;            /* dlwp_precision  */
+  int32_t max_batch;            /* workspace is sized for this many samples per call */
+  int32_t height, width;        /* grid H, W */
+  int32_t constant_channels;    /* Cc */
+  int32_t prescribed_channels;  /* Cp */
+  int32_t prognostic_channels;  /* Cg */
+  int32_t context_size;         /* ctx; in_channels = Cc + (Cp + Cg) * ctx  (fno.py:36) */
+
+  /* spectral transform: which rfft2 bins the layer reads / writes */
+  int32_t fft_norm;             /* dlwp_fft_norm */
+  int32_t n_rows;               /* number of retained row bins  */
+  int32_t n_cols;               /* retained column bins 0..n_cols-1 of the W/2+1 half spectrum */
+  const int32_t* rows_in;       /* [n_rows] unshifted FFT row bin read for weight row j  */
+  const int32_t* rows_out;      /* [n_rows] unshifted FFT row bin written by weight row j */
+
+  /* FNO / TFNO */
+  int32_t hidden_channels, lifting_channels, projection_channels, n_layers;
+
+  /* AFNO */
+  int32_t embed_dim, depth, num_blocks, mlp_hidden, patch_h, patch_w, use_pos_embed;
+  int32_t hidden_size_factor;   /* AFNO2D hidden_size_factor (1 in the reference) */
+  float sparsity_threshold;     /* softshrink lambda */
+  float layernorm_eps;          /* 1e-6 (fourcastnet.py:245) */
+} dlwp_model_desc;
+
+typedef struct dlwp_plan dlwp_plan;
+
+int dlwp_abi_version(void);
+const char* dlwp_last_error(void);
+
+/* Replaces module construction (fno.py:38-47,136-146; fourcastnet.py:247-268): validates the
+ * description, builds the truncated-DFT bases in fp64, allocates workspace on `device`. */
+int dlwp_plan_create(const dlwp_model_desc* desc, int device, dlwp_plan** out);
+int dlwp_plan_destroy(dlwp_plan* plan);
+int dlwp_plan_workspace_bytes(const dlwp_plan* plan, size_t* bytes);
+
+/* Replaces load_state_dict (scripts/evaluate.py:148-149).  `name` is the reference
+ * state_dict key without the wrapper prefix "fno." (e.g. "lifting.fcs.0.weight",
+ * "fno_blocks.convs.weight.0.tensor" | ".core" | ".factors.factor_2", "blocks.1.filter.w1").
+ * `data` may be a host or a device pointer (fp32, contiguous); it is copied before return
+ * of the stream work, the caller keeps ownership.  Complex tensors are passed as real views
+ * with a trailing dimension of 2. */
+int dlwp_plan_set_tensor(dlwp_plan* plan, const char* name, const void* data, int ndim,
+                         const int64_t* shape, void* stream);
+/* Packs what set_tensor collected into kernel layouts (mode-major spectral weights,
+ * Tucker -> dense, transposed pointwise weights).  Must be called before step / rollout. */
+int dlwp_plan_commit_weights(dlwp_plan* plan, void* stream);
+
+/* One backbone evaluation y = net(x): `self.fno(x_t)` (fno.py:103) or
+ * forward_features + head + un-patchify (fourcastnet.py:345-357).
+ * x: device [B, Cin, H, W]; y: device [B, Cg, H, W]. */
+int dlwp_step(dlwp_plan* plan, const float* x, float* y, int batch, void* stream);
+
+/* The whole autoregressive loop (fno.py:78-106 / fourcastnet.py:323-361, working form
+ * :489-527): for t = ctx .. T-1: out_t = prog_t[:, -1] + net(cat(constants, prescribed
+ * [t-ctx:t], prog_t)).  Device pointers; constants [B,1,Cc,H,W] or NULL, prescribed
+ * [B,T,Cp,H,W] or NULL, prognostic [B,T,Cg,H,W]; outs [B, T-ctx, Cg, H, W] stays on device. */
+int dlwp_rollout(dlwp_plan* plan, const float* constants, const float* prescribed,
+                 const float* prognostic, int batch, int T, float* outs, void* stream);
+
+/* Same call with HOST buffers (pinned or pageable): copies inputs to plan-owned staging,
+ * runs the rollout, copies outs back and synchronises `stream`.  This is the entry the
+ * end-to-end benchmark times.  May grow the staging buffers on first use. */
+int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* prescribed,
+                      const float* prognostic, int batch, int T, float* outs, void* stream);
+
+/* Latitude-weighted error sums (scripts/evaluate.py:790-820): adds, per lead time and
+ * variable, sum w*(o-t)^2, sum w*(o-c)(t-c), sum w*(o-c)^2, sum w*(t-c)^2 over (sample,
+ * lat, lon) into sums[T, C, 4] (device, fp64, caller zeroes).  outputs/targets: device
+ * [B, T, C, H, W]; climatology: device [C, H, W] or NULL (= 0); lat_weights: device [H]. */
+int dlwp_metrics_accumulate(const float* outputs, const float* targets, const float* climatology,
+                            const float* lat_weights, int batch, int T, int C, int H, int W,
+                            double* sums, void* stream);
+
+/* Stand-alone dense Fourier layer y = irfft2(mix(rfft2(x)[bins])) for NCHW tensors:
+ * unet.py:19-69 (SpectralConv2d) and the neuralop SpectralConv.  weight: device complex
+ * (real view) [Ci, Co, n_rows, n_cols, 2]; bias: device [Co] or NULL. */
+int dlwp_spectral_conv2d(const float* x, const float* weight, const float* bias, float* y,
+                         int batch, int Ci, int Co, int H, int W, int n_rows, int n_cols,
+                         const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
+                         void* stream);
+
+/* Number of kernels this library has launched in this process (for bench "gpu_launches"). */
+int64_t dlwp_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLWP_B200_H */
