@@ -1,0 +1,121 @@
+"""CPU: the oracle against the committed golden vectors (generated from the unmodified
+reference source by tests/golden/make_golden.py) and, where /root/reference exists, against
+the reference source itself."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import afno as oafno
+from oracle import metrics as ometrics
+from oracle import neuralop_fno as ofno
+from oracle import ref_loader, spectral2d as ospec, wrappers as owrap
+
+from helpers import golden_state_dict, load_golden, max_rel
+
+
+@pytest.mark.parametrize("name", ["afno_c3", "afno_small", "afno_patch"])
+def test_afno_oracle_matches_reference_golden(name):
+    g = load_golden(name)
+    model = oafno.AFNONet(**g["kwargs"]).eval()
+    model.load_state_dict(golden_state_dict(g), strict=True)
+    t = lambda k: torch.from_numpy(g[k])
+    ctx = g["kwargs"]["context_size"]
+    with torch.no_grad():
+        roll = model(constants=t("constants"), prescribed=t("prescribed"), prognostic=t("prognostic"))
+        one = model(constants=t("constants"), prescribed=t("prescribed")[:, :ctx + 1],
+                    prognostic=t("prognostic")[:, :ctx + 1])
+    assert roll.shape == g["rollout"].shape
+    assert max_rel(one, t("one_step")) < 2e-5
+    assert max_rel(roll, t("rollout")) < 5e-5
+
+
+def test_spectral2d_oracle_matches_reference_golden():
+    g = load_golden("spectral2d")
+    conv = ospec.SpectralConv2d(8, 12, 6, 5)
+    conv.load_state_dict({k[5:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("conv/")})
+    blk = ospec.FourierResidualBlock(8, 12, 6, 5)
+    blk.load_state_dict({k[6:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("block/")})
+    x = torch.from_numpy(g["x"])
+    with torch.no_grad():
+        assert max_rel(conv(x), torch.from_numpy(g["y_conv"])) < 1e-5
+        assert max_rel(blk(x), torch.from_numpy(g["y_block"])) < 1e-5
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="/root/reference is not on this machine")
+def test_afno_oracle_matches_live_reference():
+    ref = ref_loader.load_fourcastnet()
+    kw = dict(img_height=16, img_width=32, patch_size=[1, 1], constant_channels=2, prescribed_channels=1,
+              prognostic_channels=2, embed_dim=32, filter="AFNO2D", depth=2, mlp_ratio=4.0, num_blocks=4,
+              sparsity_threshold=0.01, hard_thresholding_fraction=0.7, context_size=1, use_pos_embed=True)
+    torch.manual_seed(3)
+    rm = ref.AFNONet(**kw).eval()
+    with torch.no_grad():
+        for n, p in rm.named_parameters():
+            if "filter" in n:
+                p.mul_(6.0)
+    om = oafno.AFNONet(**kw).eval()
+    om.load_state_dict(rm.state_dict(), strict=True)
+    x = torch.randn(2, rm.in_chans, 16, 32)
+    with torch.no_grad():
+        assert max_rel(om.backbone(x), ref_loader.reference_afno_backbone(rm, x)) < 2e-5
+
+
+def test_fno_restatement_fft_vs_truncated_dft_identity():
+    """The restated neuralop layer equals an explicit truncated DFT over the bins that
+    neuralop_row_bins reports (even and odd H)."""
+    torch.manual_seed(0)
+    for H, W, m in ((32, 64, (12, 12)), (15, 20, (6, 8))):
+        conv = ofno.SpectralConvLayers(4, 4, m, 1).double()
+        x = torch.randn(2, 4, H, W, dtype=torch.float64)
+        rin, rout = ofno.neuralop_row_bins(H, m[0])
+        kc = conv.n_modes[1]
+        Wd = conv.dense_weight(0, torch.complex128)
+        X = torch.fft.rfft2(x, norm="forward")[:, :, rin, :kc]
+        Y = torch.einsum("bixy,ioxy->boxy", X, Wd)
+        full = torch.zeros(2, 4, H, W // 2 + 1, dtype=torch.complex128)
+        full[:, :, rout, :kc] = Y
+        y = torch.fft.irfft2(full, s=(H, W), norm="forward") + conv.bias[0]
+        assert max_rel(conv(x, 0), y) < 1e-12
+
+
+def test_tucker_equals_dense_contraction():
+    torch.manual_seed(1)
+    w = ofno.TuckerSpectralWeight((6, 6, 5, 4), 0.8, 0.3)
+    x = torch.randn(2, 6, 5, 4, dtype=torch.cfloat)
+    dense = torch.einsum("bixy,ioxy->boxy", x, w.to_dense())
+    assert max_rel(torch.view_as_real(w.contract(x)), torch.view_as_real(dense)) < 1e-5
+
+
+def test_fno_param_count_cross_check():
+    """fno2d64m_cyl_d307 (scripts/plot_results.py:27): 4 layers of 307^2 x 12 x 7 complex = 63.3M."""
+    m = ofno.FNO(n_modes=[12, 12], hidden_channels=307, in_channels=13, out_channels=8, n_layers=1)
+    n_spec = sum(p.numel() for n, p in m.named_parameters() if "convs.weight" in n)
+    assert n_spec * 4 == 307 * 307 * 12 * 7 * 2 * 4
+
+
+def test_rollout_context_blending():
+    """ctx=2: step 2 uses one ground-truth frame and one own output (fourcastnet.py:502-506)."""
+    calls = []
+
+    def backbone(x):
+        calls.append(x.clone())
+        return torch.zeros(x.shape[0], 1, *x.shape[2:])
+
+    prog = torch.arange(5.0).view(1, 5, 1, 1, 1).expand(1, 5, 1, 2, 2).clone()
+    out = owrap.rollout(backbone, 2, None, None, prog)
+    assert out.shape == (1, 3, 1, 2, 2)
+    assert calls[0][0, :, 0, 0].tolist() == [0.0, 1.0]
+    assert calls[1][0, :, 0, 0].tolist() == [1.0, 1.0]      # gt frame 1, own out_0 (= frame 1 + 0)
+    assert calls[2][0, :, 0, 0].tolist() == [1.0, 1.0]      # own out_0, out_1
+
+
+def test_metrics_oracle_definitions():
+    torch.manual_seed(2)
+    o, t = torch.randn(3, 2, 2, 8, 16), torch.randn(3, 2, 2, 8, 16)
+    c = torch.randn(2, 8, 16)
+    rmse, acc = ometrics.rmse_acc(o, t, c)
+    w = ometrics.lat_weights(8).view(1, 1, 1, 8, 1)
+    ref = torch.sqrt((w * (o.double() - t.double()) ** 2).mean(dim=(0, 3, 4)))
+    assert torch.allclose(rmse, ref, rtol=1e-12)
+    assert acc.shape == (2, 2) and bool((acc.abs() <= 1).all())
+    assert abs(float(ometrics.lat_weights(32).mean()) - 1.0) < 1e-12
