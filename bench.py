@@ -1,0 +1,466 @@
+#!/usr/bin/env python
+"""Benchmark of the rollout hot path (BASELINE.json metric: rollout samples*steps/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One bench "step" = one full autoregressive rollout (all lead times) of this rank's shard of
+ensemble members, inputs resident in HBM, followed by the on-device RMSE/ACC partial sums and
+(N > 1) the single all-reduce of those partials.  ``value`` = members * lead_steps * K / time
+summed over all ranks (weak scaling: every GPU rolls out ``--members`` members).  ``e2e`` is
+the same rollout through ``dlwp_rollout_host`` with pinned HOST buffers: H2D of the inputs
+and D2H of the whole forecast inside the timed region.
+
+``--impl reference`` times the reference's CPU path for the same model (the oracle: the
+reference's own AFNO source restated for FourCastNet, the neuralop restatement for FNO/TFNO)
+on the host cores, on a bounded sample of the members.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+TFNO_C2 = dict(n_modes=[12, 12], constant_channels=4, prescribed_channels=1, prognostic_channels=8,
+               hidden_channels=32, lifting_channels=256, projection_channels=256, n_layers=4, rank=0.8,
+               bias=True, context_size=1)
+FNO_C1 = dict(n_modes=[12, 12], constant_channels=0, prescribed_channels=0, prognostic_channels=1,
+              hidden_channels=32, lifting_channels=256, projection_channels=256, n_layers=4, context_size=1)
+AFNO_C3 = dict(img_height=32, img_width=64, patch_size=[1, 1], constant_channels=4, prescribed_channels=1,
+               prognostic_channels=3, embed_dim=64, filter="AFNO2D", depth=4, mlp_ratio=4.0, num_blocks=4,
+               sparsity_threshold=0.01, hard_thresholding_fraction=1.0, context_size=1, use_pos_embed=True)
+FNO_C5 = dict(n_modes=[64, 64], constant_channels=4, prescribed_channels=1, prognostic_channels=8,
+              hidden_channels=128, lifting_channels=256, projection_channels=256, n_layers=4, context_size=1)
+
+# name -> (class, kwargs, H, W, lead steps, default members per GPU, description)
+WORKLOADS = {
+    "c4": ("TFNO2DModule", TFNO_C2, 32, 64, 20, 256,
+           "BASELINE configs[3]: TFNO2D (configs/model/fno.yaml, rank 0.8) 32x64, 20 lead steps (5 days, 6-hourly), "
+           "256 ensemble members per GPU"),
+    "c2": ("TFNO2DModule", TFNO_C2, 32, 64, 20, 8, "BASELINE configs[1]: TFNO2D 32x64, batch 8, 20 lead steps"),
+    "c1": ("FNO2DModule", FNO_C1, 64, 64, 50, 8, "BASELINE configs[0]: FNO2D 64x64, batch 8, 50 lead steps"),
+    "c3": ("FourCastNet", AFNO_C3, 32, 64, 5, 8, "BASELINE configs[2]: FourCastNet AFNO 32x64, batch 8, 5 lead steps"),
+    "c5": ("FNO2DModule", FNO_C5, 721, 1440, 8, 1,
+           "BASELINE configs[4]: FNO2D 721x1440, 128 channels, 64x64 modes, 8 lead steps"),
+}
+
+
+def synthetic_inputs(kw, members, T, H, W, seed, pin):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+
+    def field(*shape):
+        t = torch.randn(*shape, generator=g)
+        return t.pin_memory() if pin else t
+
+    const = field(members, 1, kw["constant_channels"], H, W) if kw["constant_channels"] else None
+    presc = field(members, T, kw["prescribed_channels"], H, W) if kw["prescribed_channels"] else None
+    prog = field(members, T, kw["prognostic_channels"], H, W)
+    return const, presc, prog
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        return False
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------
+# algorithmic work (DESIGN.md "Measurement")
+# ----------------------------------------------------------------------------------------
+def fno_dims(kw, H, W):
+    m1 = min(kw["n_modes"][0], H)
+    m2 = min(kw["n_modes"][1] // 2 + 1, W // 2 + 1)
+    cin = kw["constant_channels"] + (kw["prescribed_channels"] + kw["prognostic_channels"]) * kw["context_size"]
+    return cin, kw["hidden_channels"], kw["lifting_channels"], kw["projection_channels"], kw["prognostic_channels"], \
+        kw["n_layers"], m1, m2
+
+
+def step_flops(cls, kw, B, H, W):
+    """Real flops of one model evaluation on B samples (truncated-DFT-GEMM count)."""
+    S = H * W
+    if cls != "FourCastNet":
+        cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
+        lift = 2 * B * S * (cin * L + L * C)
+        proj = 2 * B * S * (C * P + P * Cg)
+        dftw = 2 * (B * C * H) * W * (2 * m2)
+        dfth = 8 * B * C * m2 * H * m1
+        mix = 8 * B * C * C * m1 * m2
+        spectral = 2 * dftw + 2 * dfth + mix
+        return {"step": lift + proj + N * (spectral + 2 * B * S * C * C), "spectral_block": spectral}
+    p1, p2 = kw["patch_size"]
+    h, w = H // p1, W // p2
+    E, nb = kw["embed_dim"], kw["num_blocks"]
+    cin = kw["constant_channels"] + (kw["prescribed_channels"] + kw["prognostic_channels"]) * kw["context_size"]
+    total = h // 2 + 1
+    kept = int(total * kw["hard_thresholding_fraction"])
+    rows, cols = min(2 * kept, h), min(kept, w // 2 + 1)
+    tok = B * h * w
+    dftw = 2 * (B * E * h) * w * (2 * cols)
+    dfth = 8 * B * E * cols * h * rows
+    mix = 2 * 8 * B * rows * cols * nb * (E // nb) ** 2
+    spectral = 2 * dftw + 2 * dfth + mix
+    mlp = 4 * tok * E * int(E * kw["mlp_ratio"])
+    return {"step": 2 * tok * cin * E * p1 * p2 + 2 * tok * E * kw["prognostic_channels"] * p1 * p2
+            + kw["depth"] * (spectral + mlp), "spectral_block": spectral}
+
+
+def step_bytes(cls, kw, B, H, W, b=4):
+    """Algorithmic HBM bytes of one model evaluation with per-layer fusion: every layer reads its
+    input once and writes its output once, MLP hiddens stay on chip, weights are read once."""
+    S = H * W
+    if cls != "FourCastNet":
+        cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
+        act = B * S * b * (cin + C + 2 * N * C + C + Cg)
+        wts = N * (2 * C * C * m1 * m2 + C * C + C) * b + (cin * L + L + L * C + C + C * P + P + P * Cg + Cg) * b
+        return act + wts
+    p1, p2 = kw["patch_size"]
+    E, D = kw["embed_dim"], kw["depth"]
+    tok = B * (H // p1) * (W // p2)
+    cin = kw["constant_channels"] + (kw["prescribed_channels"] + kw["prognostic_channels"]) * kw["context_size"]
+    hid = int(E * kw["mlp_ratio"])
+    act = B * S * b * (cin + 2 * kw["prognostic_channels"]) + tok * E * b * (1 + 4 * D + 1)
+    wts = b * (cin * p1 * p2 * E + E + tok // B * E + D * (4 * E + 4 * (E // kw["num_blocks"]) * E + 4 * E
+                                                         + 2 * E * hid + hid + E) + E * kw["prognostic_channels"] * p1 * p2)
+    return act + wts
+
+
+def kernel_bytes(cls, kw, B, H, W, name):
+    """Algorithmic bytes ONE model evaluation moves through the kernel called `name` (sum over
+    its launches in the step), or None when bench.py has no model for that kernel."""
+    S, b = H * W, 4
+    if cls == "FourCastNet":
+        p1, p2 = kw["patch_size"]
+        tok = B * (H // p1) * (W // p2)
+        E, D, hid, Cg = kw["embed_dim"], kw["depth"], int(kw["embed_dim"] * kw["mlp_ratio"]), kw["prognostic_channels"]
+        cin = kw["constant_channels"] + (kw["prescribed_channels"] + Cg) * kw["context_size"]
+        if name == "pw_linear_kernel":
+            return b * (B * S * cin + tok * E + D * (tok * E + tok * hid + tok * hid + 2 * tok * E)
+                        + tok * E + 2 * B * S * Cg)
+        if name == "layernorm_kernel":
+            return b * D * 2 * 2 * tok * E
+        return None
+    cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
+    px = B * S
+    if name == "pw_linear_kernel":      # lifting 1+2, N skips, projection 1+2 (unfused fp32 path)
+        return b * px * ((cin + L) + (L + C) + N * 2 * C + (C + P) + (P + 2 * Cg))
+    if name == "tdft_kernel":           # 4 truncated-DFT passes per layer
+        half = B * H * m2 * C * 2       # complex [B, H, Kc, C]
+        modes = B * m1 * m2 * C * 2
+        return b * N * ((px * C + half) + (half + modes) + (modes + half) + (half + 2 * px * C + px * C))
+    if name == "mix_dense_kernel":
+        return b * N * (2 * B * m1 * m2 * C * 2 + m1 * m2 * C * C * 2)
+    if name == "fno_lift_kernel":       # fused lifting MLP (+ forward W-DFT of its output)
+        return b * px * (cin + C) + b * B * H * m2 * C * 2
+    if name == "fno_layer_kernel":      # fused inverse W-DFT + skip + GELU (+ forward W-DFT), per layer
+        return b * (N - 1) * (2 * px * C + 2 * B * H * m2 * C * 2)
+    if name == "fno_mid_kernel":        # H-DFT, mode mixing, inverse H-DFT on the retained columns
+        return b * N * (2 * B * H * m2 * C * 2 + m1 * m2 * C * C * 2)
+    if name == "fno_tail_kernel":       # last layer + projection MLP + residual
+        return b * (px * C + B * H * m2 * C * 2 + 2 * px * Cg)
+    return None
+
+
+# ----------------------------------------------------------------------------------------
+# CPU arm: the oracle on the host cores (cpu_baseline leg and --impl reference)
+# ----------------------------------------------------------------------------------------
+def oracle_module(cls, kw):
+    import torch
+    from oracle import afno as oafno, wrappers as owrap
+    torch.manual_seed(1234)
+    if cls == "FourCastNet":
+        return oafno.AFNONet(**kw).eval()
+    return getattr(owrap, cls)(**kw).eval()
+
+
+def cpu_rollout_rate(cls, kw, H, W, lead, sample_members, repeats, warmup):
+    """samples*steps/s of the CPU oracle on `sample_members` members x `lead` lead steps."""
+    import torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    model = oracle_module(cls, kw)
+    ctx = kw["context_size"]
+    const, presc, prog = synthetic_inputs(kw, sample_members, ctx + lead, H, W, 1234, pin=False)
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + repeats):
+            t0 = time.perf_counter()
+            model(constants=const, prescribed=presc, prognostic=prog)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+    total = sum(times)
+    return sample_members * lead * len(times) / total, total / len(times), cores
+
+
+def run_reference(args, wl):
+    cls, kw, H, W, lead, members_default, desc = wl
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    members = min(args.cpu_members, args.members or members_default)
+    if args.workload == "c5":
+        lead = 1
+    rate, sec, cores = cpu_rollout_rate(cls, kw, H, W, lead, members, max(args.steps, 1), min(args.warmup, 1))
+    sample = f"{members} members x {lead} lead steps per bench step (bounded sample of the workload), fp32, torch CPU"
+    line = {
+        "impl": "reference", "metric": "rollout samples*steps/s", "value": rate, "unit": "samples*steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_block(args, wl, args.members or members_default),
+        "cpu_baseline": {"value": rate, "unit": "samples*steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "samples*steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference CPU path = oracle/ (AFNO: restatement pinned to the reference source; FNO/TFNO: "
+                "restatement of the un-vendored neuralop, parity unpinned); the reference is pure Python, "
+                "so there is no oracle/_ref binary",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def config_block(args, wl, members):
+    cls, kw, H, W, lead, _, desc = wl
+    return {"workload": f"{args.workload}: {desc}", "model_class": cls, "grid": [H, W], "lead_steps": lead,
+            "members_per_gpu": members, "members_total": members * args.gpus,
+            "parallelism": f"ensemble-sharded x{args.gpus}, no data-path collective; one all-reduce of [T,C,4] fp64 "
+                           "metric partials per rollout",
+            "l2": "inputs larger than L2" if members * (lead + 1) * kw["prognostic_channels"] * H * W * 4 > 126e6
+                  else "L2 flushed between timed rollouts (256 MiB write)",
+            "precision_mode": args.precision}
+
+
+# ----------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), float(p.get("bf16_tflops_sustained", p.get("bf16_tflops"))), "measured"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, 1400.0, "fallback"
+
+
+def run_ours(args, wl):
+    import torch
+    import torch.distributed as dist
+    cls, kw, H, W, lead, members_default, desc = wl
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import __graft_entry__ as entry
+    if rank == 0:
+        entry.build()
+    if world > 1:
+        dist.barrier()
+    import dlwp_benchmark_b200 as pkg
+    from dlwp_benchmark_b200 import metrics as M, native
+
+    members = args.members or members_default
+    ctx = kw["context_size"]
+    T = ctx + lead
+    torch.manual_seed(1234)                                   # identical random-init weights on every rank
+    mod = getattr(pkg, cls)(**kw).to(dev).eval()
+    mod.precision = {"fp32": native.PREC_FP32, "fp32_tc": native.PREC_FP32_TC, "bf16": native.PREC_BF16}[args.precision]
+    const_h, presc_h, prog_h = synthetic_inputs(kw, members, T, H, W, 1234 + rank, pin=True)
+    Cg = kw["prognostic_channels"]
+    g = torch.Generator().manual_seed(99 + rank)
+    target = torch.randn(members, lead, Cg, H, W, generator=g).to(dev)
+    clim = (0.3 * torch.randn(Cg, H, W, generator=torch.Generator().manual_seed(7))).to(dev)
+    const, presc, prog = (None if t is None else t.to(dev) for t in (const_h, presc_h, prog_h))
+    in_bytes = sum(t.numel() * 4 for t in (const_h, presc_h, prog_h) if t is not None)
+    out_bytes = members * lead * Cg * H * W * 4
+    flush = None if in_bytes > 126e6 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def step():
+        out = mod(constants=const, prescribed=presc, prognostic=prog)
+        sums = M.partial_sums(out, target, clim)
+        sums, count = M.reduce_sums(sums, members * H * W)
+        return out, sums, count
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    with torch.no_grad():
+        for _ in range(max(args.warmup, 3)):
+            out, sums, count = step()
+        barrier()
+        n0 = native.launch_count()
+        pairs = []
+        with ClockSampler(local) as clk:
+            for _ in range(args.steps):
+                if flush is not None:
+                    flush.fill_(1)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                out, sums, count = step()
+                e1.record(stream)
+                pairs.append((e0, e1))
+            barrier()
+        launches = native.launch_count() - n0
+        ms_total = sum(a.elapsed_time(b) for a, b in pairs)
+        rmse, acc = M.finalize(sums, count)
+
+        # end to end through the C ABI with HOST buffers (H2D + rollout + D2H inside the call)
+        out_h = torch.empty(members, lead, Cg, H, W, dtype=torch.float32, pin_memory=True)
+        for _ in range(2):
+            mod.forward_host(constants=const_h, prescribed=presc_h, prognostic=prog_h, out=out_h)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            mod.forward_host(constants=const_h, prescribed=presc_h, prognostic=prog_h, out=out_h)
+        barrier()
+        e2e_s = time.perf_counter() - t0
+
+        # per-kernel device times of one rollout (events after every launch; separate pass)
+        with native.kernel_profile(stream.cuda_stream) as prof:
+            step()
+    t = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_s = float(t[0]), float(t[1])
+    if rank == 0:
+        hbm_peak, tc_peak, which = measured_peaks()
+        units = members * lead * args.steps * world
+        ms_step = ms_total / args.steps
+        entries = prof.entries
+        name, (kms, kn) = max(entries.items(), key=lambda kv: kv[1][0])
+        kb = kernel_bytes(cls, kw, members, H, W, name)
+        total_prof = sum(v[0] for v in entries.values())
+        roof = {"bound": "hbm", "kernel": name, "achieved": None, "peak": hbm_peak, "unit": "GB/s", "frac": None,
+                "traffic": None, "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
+                "kernel_ms_per_launch": kms / kn, "kernel_launches_per_rollout": kn,
+                "kernel_share_of_rollout": kms / total_prof}
+        if kb is not None:
+            per_launch = kb * lead / kn
+            roof["achieved"] = per_launch / (kms / kn * 1e-3) / 1e9
+            roof["frac"] = roof["achieved"] / hbm_peak
+            roof["algorithmic_bytes_per_launch"] = per_launch
+        fl = step_flops(cls, kw, members, H, W)
+        sb = step_bytes(cls, kw, members, H, W)
+        spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel")]
+        spec_ms = sum(entries[n][0] for n in spec_names)
+        layers = kw.get("n_layers", kw.get("depth"))
+        line = {
+            "metric": "rollout samples*steps/s", "value": units / (ms_total * 1e-3), "unit": "samples*steps/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp32": "f32", "fp32_tc": "f32 (split-bf16 tensor-core products, fp32 accumulate)",
+                      "bf16": "bf16"}[args.precision],
+            "data": "synthetic N(0,1) fields, random-init weights (seed 1234)",
+            "config": config_block(args, wl, members),
+            "e2e": {"value": units / e2e_s, "unit": "samples*steps/s", "h2d_bytes_per_step": in_bytes,
+                    "d2h_bytes_per_step": out_bytes, "ms_per_step": e2e_s / args.steps * 1e3,
+                    "api": "dlwp_rollout_host (pinned host buffers; whole forecast copied back)"},
+            "gpu_launches": launches,
+            "roofline": roof,
+            "step_roofline": {"algorithmic_bytes_per_rollout": sb * lead, "achieved_gbs": sb * lead / (ms_step * 1e-3) / 1e9,
+                              "frac_of_hbm_peak": sb * lead / (ms_step * 1e-3) / 1e9 / hbm_peak,
+                              "tflops": fl["step"] * lead / (ms_step * 1e-3) / 1e12},
+            "spectral_block": {"kernels": spec_names, "tflops": (fl["spectral_block"] * layers * lead / (spec_ms * 1e-3) / 1e12)
+                               if spec_ms > 0 else None, "peak_tflops": tc_peak,
+                               "note": "profiled pass; includes the events' launch gaps"},
+            "kernel_ms_per_rollout": {n: round(v[0], 4) for n, v in sorted(entries.items(), key=lambda kv: -kv[1][0])},
+            "clocks": clk.summary(),
+            "rmse_lead1_lastlead": [float(rmse[0].mean()), float(rmse[-1].mean())],
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cm = min(args.cpu_members, members)
+            cl = 1 if args.workload == "c5" else lead
+            rate, sec, cores = cpu_rollout_rate(cls, kw, H, W, cl, cm, 1, 0)
+            line["cpu_baseline"] = {"value": rate, "unit": "samples*steps/s", "cores": cores, "kind": "port",
+                                    "sample": f"{cm} members x {cl} lead steps, one rollout ({sec:.1f} s), "
+                                              "oracle/ in torch fp32 on all host threads"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c4")
+    ap.add_argument("--members", type=int, default=0, help="ensemble members per GPU (0 = the workload's default)")
+    ap.add_argument("--precision", choices=["fp32", "fp32_tc", "bf16"], default="fp32")
+    ap.add_argument("--cpu-members", type=int, default=64, help="members in the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

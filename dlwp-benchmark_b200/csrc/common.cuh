@@ -17,6 +17,9 @@ namespace dlwp {
 // ---- error plumbing ----------------------------------------------------------------
 extern thread_local std::string g_last_error;
 extern std::atomic<int64_t> g_launches;
+// per-kernel CUDA-event profiler (dlwp_profile_begin / _end); off on the hot path
+extern bool g_prof_on;
+void prof_mark(const char* name, cudaStream_t st);
 
 inline int fail(int code, const char* fmt, ...) {
   char buf[1024];
@@ -51,6 +54,7 @@ inline int fail(int code, const char* fmt, ...) {
 #define DLWP_LAUNCHED(name)                                                                   \
   do {                                                                                        \
     ::dlwp::g_launches.fetch_add(1, std::memory_order_relaxed);                               \
+    if (::dlwp::g_prof_on) ::dlwp::prof_mark(name, st);                                       \
     cudaError_t _e = cudaPeekAtLastError();                                                   \
     if (_e != cudaSuccess)                                                                    \
       return ::dlwp::fail(DLWP_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(_e)); \

@@ -54,6 +54,10 @@ SYMBOLS = {
     "dlwp_spectral_conv2d": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
     "dlwp_launch_count": (C.c_int64, []),
+    "dlwp_profile_begin": (C.c_int, [_P]),
+    "dlwp_profile_end": (C.c_int, [_P]),
+    "dlwp_profile_count": (C.c_int, []),
+    "dlwp_profile_entry": (C.c_int, [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
 }
 
 _lib = None
@@ -97,3 +101,24 @@ def launch_count() -> int:
 def int32_array(values):
     arr = (C.c_int32 * max(len(values), 1))(*values)
     return arr
+
+
+class kernel_profile:
+    """``with kernel_profile(stream_ptr) as prof: ...`` -> ``prof.entries`` = {kernel name:
+    (total device ms, launches)} for every kernel the library launched inside the block."""
+
+    def __init__(self, stream: int):
+        self._stream = C.c_void_p(stream)
+        self.entries = {}
+
+    def __enter__(self):
+        check(lib().dlwp_profile_begin(self._stream), "dlwp_profile_begin")
+        return self
+
+    def __exit__(self, *exc):
+        check(lib().dlwp_profile_end(self._stream), "dlwp_profile_end")
+        name, ms, n = C.c_char_p(), C.c_double(), C.c_int64()
+        for i in range(lib().dlwp_profile_count()):
+            check(lib().dlwp_profile_entry(i, C.byref(name), C.byref(ms), C.byref(n)))
+            self.entries[name.value.decode()] = (float(ms.value), int(n.value))
+        return False

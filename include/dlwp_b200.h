@@ -148,6 +148,15 @@ int dlwp_spectral_conv2d(const float* x, const float* weight, const float* bias,
 /* Number of kernels this library has launched in this process (for bench "gpu_launches"). */
 int64_t dlwp_launch_count(void);
 
+/* Per-kernel device timing for bench.py's roofline figure (new; no reference counterpart).
+ * Between _begin and _end every kernel this library launches is followed by a CUDA event on
+ * its stream; _end synchronises `stream` and aggregates event-to-event times by kernel name.
+ * Not for the hot path: a profiled region is not graph-capturable. */
+int dlwp_profile_begin(void* stream);
+int dlwp_profile_end(void* stream);
+int dlwp_profile_count(void);
+int dlwp_profile_entry(int index, const char** name, double* total_ms, int64_t* launches);
+
 #ifdef __cplusplus
 }
 #endif
