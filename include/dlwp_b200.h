@@ -157,6 +157,11 @@ int dlwp_profile_end(void* stream);
 int dlwp_profile_count(void);
 int dlwp_profile_entry(int index, const char** name, double* total_ms, int64_t* launches);
 
+/* Diagnostic: one tcgen05.mma tile D[M x N] = A[M x K] * B[N x K]^T (operands rounded to bf16,
+ * fp32 accumulate in tensor memory); writes the raw 128-lane x N-column TMEM image to `d_raw`
+ * (device, [128, N] fp32).  Used by the GPU tests to pin the descriptor encodings. */
+int dlwp_selftest_umma(const float* a, const float* b, float* d_raw, int M, int N, int K, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

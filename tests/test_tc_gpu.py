@@ -1,0 +1,27 @@
+"""GPU: the tcgen05 building blocks (descriptor encodings, TMEM accumulator layout)."""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _umma(a, b, M, N, K):
+    from dlwp_benchmark_b200 import native
+    d = torch.full((128, N), float("nan"), device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    native.check(native.lib().dlwp_selftest_umma(C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()),
+                                                 C.c_void_p(d.data_ptr()), M, N, K, st))
+    torch.cuda.synchronize()
+    return d
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 32, 16), (128, 32, 64), (128, 256, 48), (128, 128, 32), (128, 16, 32)])
+def test_umma_m128_matches_bf16_matmul(built_lib, M, N, K):
+    torch.manual_seed(M + N + K)
+    a, b = torch.randn(M, K, device="cuda"), torch.randn(N, K, device="cuda")
+    want = a.bfloat16().float() @ b.bfloat16().float().t()
+    got = _umma(a.contiguous(), b.contiguous(), M, N, K)
+    err = float((got - want).abs().max())
+    assert err < 1e-3, f"max abs err {err}"
