@@ -111,6 +111,12 @@ int dlwp_plan_workspace_bytes(const dlwp_plan* plan, size_t* bytes) {
   return DLWP_OK;
 }
 
+int dlwp_plan_uses_tensor_cores(const dlwp_plan* plan, int* out) {
+  if (!plan || !out) return fail(DLWP_ERR_INVALID, "dlwp_plan_uses_tensor_cores: null argument");
+  *out = plan->tc ? 1 : 0;
+  return DLWP_OK;
+}
+
 int dlwp_plan_set_tensor(dlwp_plan* plan, const char* name, const void* data, int ndim, const int64_t* shape,
                          void* stream) {
   if (!plan || !name || !data || ndim < 0 || (ndim > 0 && !shape))

@@ -14,7 +14,9 @@ namespace dlwp {
 thread_local std::string g_last_error;
 std::atomic<int64_t> g_launches{0};
 
-static int dev_alloc(dlwp_plan* p, void** out, size_t bytes) {
+int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);
+static int dev_alloc(dlwp_plan* p, void** out, size_t bytes) { return plan_dev_alloc(p, out, bytes); }
+int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes) {
   if (bytes == 0) bytes = 16;
   DLWP_CUDA(cudaMalloc(out, bytes));
   p->owned.push_back(*out);
@@ -72,8 +74,8 @@ static int build_bases(dlwp_plan* p) {
 int plan_build(dlwp_plan* p) {
   const dlwp_model_desc& d = p->d;
   DLWP_REQUIRE(d.kind == DLWP_MODEL_FNO || d.kind == DLWP_MODEL_AFNO, "unknown model kind %d", d.kind);
-  DLWP_REQUIRE(d.precision == DLWP_PREC_FP32, "precision mode %d is not built into this library yet",
-               d.precision);
+  DLWP_REQUIRE(d.precision == DLWP_PREC_FP32 || d.precision == DLWP_PREC_FP32_TC,
+               "precision mode %d is not built into this library yet", d.precision);
   DLWP_REQUIRE(d.max_batch > 0 && d.height > 0 && d.width > 0, "max_batch/height/width must be positive");
   DLWP_REQUIRE(d.constant_channels >= 0 && d.prescribed_channels >= 0 && d.prognostic_channels > 0 &&
                    d.context_size > 0,
@@ -129,6 +131,7 @@ int plan_build(dlwp_plan* p) {
   DLWP_TRY(dev_alloc(p, (void**)&p->specZ, B * p->gh * Kc * C * sizeof(float2)));
   DLWP_TRY(dev_alloc(p, (void**)&p->specX, R * Kc * B * C * sizeof(float2)));
   DLWP_TRY(dev_alloc(p, (void**)&p->specY, R * Kc * B * C * sizeof(float2)));
+  if (d.precision == DLWP_PREC_FP32_TC) DLWP_TRY(plan_tc_build(p));
   return DLWP_OK;
 }
 
@@ -143,6 +146,9 @@ static const NamedTensor* find(const dlwp_plan* p, const std::string& name) {
 }
 
 static int need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out) {
+  return plan_need(p, name, numel, out);
+}
+int plan_need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out) {
   const NamedTensor* t = find(p, name);
   if (!t) return fail(DLWP_ERR_MISSING, "weight tensor '%s' was not set", name.c_str());
   if (t->numel != numel)
@@ -259,6 +265,7 @@ int plan_commit(dlwp_plan* p, cudaStream_t st) {
   p->committed = false;
   if (p->d.kind == DLWP_MODEL_FNO) DLWP_TRY(commit_fno(p, st));
   else DLWP_TRY(commit_afno(p, st));
+  if (p->tc) DLWP_TRY(plan_tc_commit(p, st));
   p->committed = true;
   return DLWP_OK;
 }
@@ -435,6 +442,7 @@ static int backbone_afno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st)
 int plan_backbone(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   if (!p->committed) return fail(DLWP_ERR_STATE, "dlwp_plan_commit_weights has not been called");
   DLWP_REQUIRE(B > 0 && B <= p->d.max_batch, "batch %d outside [1, max_batch=%d]", B, p->d.max_batch);
+  if (p->tc) return backbone_fno_tc(p, io, B, st);
   return p->d.kind == DLWP_MODEL_FNO ? backbone_fno(p, io, B, st) : backbone_afno(p, io, B, st);
 }
 

@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "tc_fno.cuh"
 
 namespace dlwp {
 
@@ -53,6 +54,14 @@ struct dlwp_plan {
   float2 *specA = nullptr, *specZ = nullptr;                               // [B, gh, Kc, C]
   float2 *specX = nullptr, *specY = nullptr;                               // [R, Kc, B, C]
 
+  // tensor-core path (tc_fno.cuh): used when precision == DLWP_PREC_FP32_TC and the shape fits
+  bool tc = false;
+  dlwp::TcGeom tcg{};
+  uint8_t* tc_img[2] = {nullptr, nullptr};              // activation tile images (ping-pong)
+  uint8_t *tc_G = nullptr, *tc_F = nullptr;             // inverse / forward W-DFT operand images
+  uint8_t *tc_liftW1 = nullptr, *tc_liftW2 = nullptr, *tc_projW1 = nullptr, *tc_projW2 = nullptr;
+  std::vector<uint8_t*> tc_skip;                        // per layer skip-conv images
+
   // host-entry staging (dlwp_rollout_host)
   void* stage[4] = {nullptr, nullptr, nullptr, nullptr};
   size_t stage_bytes[4] = {0, 0, 0, 0};
@@ -62,6 +71,11 @@ namespace dlwp {
 int plan_build(dlwp_plan* p);                                  // bases + workspace
 int plan_commit(dlwp_plan* p, cudaStream_t st);                // pack weights
 int plan_backbone(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
+int plan_tc_build(dlwp_plan* p);                               // tc_plan.cu: eligibility + DFT operand images
+int plan_tc_commit(dlwp_plan* p, cudaStream_t st);             // tc_plan.cu: weight images
+int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
+int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);
+int plan_need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out);
 int spectral_layer(dlwp_plan* p, const float* x, float* y, const float2* wm_or_null, int layer,
                    const float* add1, const float* add2, const float* bias, int act, int B, cudaStream_t st);
 }  // namespace dlwp

@@ -1,0 +1,93 @@
+// Tensor-core (tcgen05) kernel set for the FNO / TFNO step at hidden width 32.
+//
+// Activations between kernels live in HBM as "tile images": 128 consecutive pixels x 32
+// channels, split into bf16 hi and lo parts (v = hi + lo), each part stored in exactly the
+// chunk-major shared-memory layout the UMMA descriptors read (tc_common.cuh).  One tile is
+// 16 KB (8 KB hi image, then 8 KB lo image) = the bytes of the same tile in fp32; a consumer
+// brings it in with one bulk async copy and feeds it to tcgen05.mma without touching it.
+// Every fp32 product a*b is evaluated as a_hi*b_hi + a_lo*b_hi + a_hi*b_lo on the bf16 tensor
+// cores with fp32 accumulation in tensor memory (error ~2^-17 relative per product).
+//
+// Per model evaluation (reference: neuralop FNO.forward as called from fno.py:103):
+//   fno_lift_kernel    gather x_t from the NCHW sources (fno.py:49-62) -> lifting MLP
+//                      (1x1 conv, GELU, 1x1 conv; hidden stays in TMEM/SMEM) -> tile image
+//                      + forward truncated W-DFT of the result (a third MMA on the same tile)
+//   [H-DFT, per-mode mixing, inverse H-DFT on the retained columns: kernels_fp32.cu]
+//   fno_layer_kernel   inverse truncated W-DFT GEMM K-concatenated with the 1x1 skip conv,
+//                      + bias, GELU -> tile image + forward W-DFT for the next layer
+//   fno_proj_kernel    projection MLP + residual on the last context frame -> NCHW output
+#pragma once
+#include "kernels.cuh"
+
+namespace dlwp {
+
+constexpr int kTcTile = 128;      // pixels per tile (UMMA M)
+constexpr int kTcC = 32;          // hidden channels of the tensor-core path
+constexpr int kTcImgBytes = kTcTile * kTcC * 2;   // one bf16 image (hi or lo) of a tile: 8 KB
+
+// geometry shared by the three kernels
+struct TcGeom {
+  int ntiles;          // B * H * W / 128
+  int HW;              // pixels per sample
+  int W;               // grid width (128 % W == 0)
+  int RT;              // grid rows per tile = 128 / W
+  int KXP;             // padded real columns per grid row = 32 / RT  (2 * Kc <= KXP)
+  int Kc;              // retained half-spectrum columns
+};
+
+struct TcLiftArgs {
+  TcGeom g;
+  SrcGroup grp[4];     // NCHW sources of x_t
+  int ngrp;
+  int Cin;             // <= 15 (column Cin of the first GEMM carries the bias)
+  int hid;             // lifting width: 128 or 256
+  const uint8_t* W1img;   // [hi | lo] images, R = hid rows, K = 16
+  const uint8_t* W2img;   // [hi | lo] images, R = 32 rows, K = hid
+  const float* b2;        // [32]
+  const uint8_t* Fimg;    // forward W-DFT operand image, R = 64, K = 128
+  uint8_t* y_img;         // tile images out
+  float2* Aout;           // [B*H, Kc, 32] forward W-DFT of the output
+};
+
+struct TcLayerArgs {
+  TcGeom g;
+  const uint8_t* x_img;
+  uint8_t* y_img;
+  const float2* Z;        // [B*H, Kc, 32] spectrum after the inverse H-DFT
+  float2* Aout;           // forward W-DFT of the output, or null (last layer)
+  const uint8_t* Gimg;    // inverse W-DFT operand [hi | lo] images, R = 128, K = 32
+  const uint8_t* Fimg;
+  const uint8_t* Wsimg;   // skip conv [hi | lo] images, R = 32, K = 32
+  const float* bias;      // [32] spectral-conv bias of this layer
+  int gelu;
+};
+
+struct TcProjArgs {
+  TcGeom g;
+  const uint8_t* x_img;
+  int hid;                // projection width: 128 or 256
+  int Cg;                 // output channels <= 16
+  const uint8_t* W1img;   // [hi | lo] images, R = hid rows, K = 32
+  const float* b1;        // [hid]
+  const uint8_t* W2img;   // [hi | lo] images, R = 16 rows, K = hid
+  const float* b2;        // [Cg]
+  float* out;             // NCHW frame(s): out[b * out_bstride + (c, y, x)]
+  long long out_bstride;
+  const float* last;      // residual frame or null
+  long long last_bstride;
+};
+
+int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st);
+int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st);
+int launch_tc_proj(const TcProjArgs& a, cudaStream_t st);
+
+// ---- host-side packing (plan_commit) ----------------------------------------------------
+// Chunk-major [hi | lo] bf16 images of a row-major fp32 matrix `m` [rows, cols] padded to
+// R x K (zeros); returns 2 * R * K * 2 bytes.  `lo` is the bf16 of (v - hi).
+void tc_pack_images(const float* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
+// same from fp64 (DFT bases)
+void tc_pack_images_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
+// a single bf16 image whose rows [0, R/2) are hi parts and [R/2, R) lo parts of the R/2 x K matrix
+void tc_pack_stacked_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
+
+}  // namespace dlwp

@@ -1,0 +1,202 @@
+// Plan-side glue of the tensor-core FNO path: eligibility, constant operand images, weight
+// images, and the per-step kernel sequence (reference: neuralop FNO.forward behind fno.py:103).
+#include <cmath>
+#include <vector>
+
+#include "plan.cuh"
+
+namespace dlwp {
+
+// The tcgen05 kernels cover the reference's FNO2D / TFNO2D configurations (hidden width 32,
+// 256-wide lifting / projection, grids whose rows divide a 128-pixel tile).  Anything else
+// keeps the fp32 kernel set of kernels_fp32.cu.
+int plan_tc_build(dlwp_plan* p) {
+  const dlwp_model_desc& d = p->d;
+  p->tc = false;
+  if (d.kind != DLWP_MODEL_FNO || p->C != kTcC) return DLWP_OK;
+  const int H = d.height, W = d.width, Kc = d.n_cols;
+  if (W > kTcTile || kTcTile % W != 0 || (H * W) % kTcTile != 0) return DLWP_OK;
+  const int RT = kTcTile / W;
+  if (RT > 4) return DLWP_OK;
+  const int KXP = 32 / RT;
+  if (Kc < 1 || 2 * Kc > KXP || d.n_rows < 1) return DLWP_OK;
+  if ((d.lifting_channels != 128 && d.lifting_channels != 256) ||
+      (d.projection_channels != 128 && d.projection_channels != 256))
+    return DLWP_OK;
+  if (p->Cin < 1 || p->Cin > 15 || d.prognostic_channels > 16) return DLWP_OK;
+
+  p->tcg = TcGeom{0, H * W, W, RT, KXP, Kc};
+  double s = 1.0, t = 1.0;
+  const double hw = (double)H * (double)W;
+  if (d.fft_norm == DLWP_FFT_NORM_BACKWARD) t = 1.0 / hw;
+  else if (d.fft_norm == DLWP_FFT_NORM_FORWARD) s = 1.0 / hw;
+  else s = t = 1.0 / std::sqrt(hw);
+
+  // inverse W-DFT operand G'[(h2, w), (h2', kx')]: y[w] = sum_kx Re(Gw[w, kx] * Z[kx]) with
+  // Gw = t * c_kx * exp(+2 pi i kx w / W) (c = 1 for the self-conjugate columns, else 2);
+  // forward operand F''[(h2, kx'), (h2', w)] with Fw = s * exp(-2 pi i kx w / W)
+  std::vector<double> G((size_t)128 * 32, 0.0), F((size_t)32 * 128, 0.0);
+  for (int h2 = 0; h2 < RT; ++h2)
+    for (int w = 0; w < W; ++w)
+      for (int kx = 0; kx < Kc; ++kx) {
+        const long long r = ((long long)kx * w) % W;
+        const double ang = 2.0 * M_PI * (double)r / (double)W;
+        const bool self_conj = (kx == 0) || (W % 2 == 0 && kx == W / 2);
+        const double ck = t * (self_conj ? 1.0 : 2.0);
+        const int m = h2 * W + w, k = h2 * KXP + 2 * kx;
+        G[(size_t)m * 32 + k] = ck * std::cos(ang);
+        G[(size_t)m * 32 + k + 1] = -ck * std::sin(ang);
+        F[(size_t)k * 128 + m] = s * std::cos(ang);
+        F[(size_t)(k + 1) * 128 + m] = -s * std::sin(ang);
+      }
+  std::vector<uint8_t> gi(2 * kTcImgBytes), fi(64 * 128 * 2);
+  tc_pack_images_f64(G.data(), 128, 32, 32, 128, 32, gi.data());
+  tc_pack_stacked_f64(F.data(), 32, 128, 128, 64, 128, fi.data());
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_G, gi.size()));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_F, fi.size()));
+  DLWP_CUDA(cudaMemcpy(p->tc_G, gi.data(), gi.size(), cudaMemcpyHostToDevice));
+  DLWP_CUDA(cudaMemcpy(p->tc_F, fi.data(), fi.size(), cudaMemcpyHostToDevice));
+
+  const size_t img = (size_t)d.max_batch * H * W * kTcC * 4;
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_img[0], img));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_img[1], img));
+  const int L = d.lifting_channels, Pj = d.projection_channels;
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_liftW1, (size_t)L * 16 * 4));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_liftW2, (size_t)32 * L * 4));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_projW1, (size_t)Pj * 32 * 4));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_projW2, (size_t)16 * Pj * 4));
+  p->tc_skip.assign(d.n_layers, nullptr);
+  for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_skip[l], 4096));
+  p->tc = true;
+  return DLWP_OK;
+}
+
+static int fetch(const dlwp_plan* p, const std::string& name, int64_t numel, std::vector<float>* out) {
+  const float* dev;
+  DLWP_TRY(plan_need(p, name, numel, &dev));
+  out->resize((size_t)numel);
+  DLWP_CUDA(cudaMemcpy(out->data(), dev, (size_t)numel * sizeof(float), cudaMemcpyDeviceToHost));
+  return DLWP_OK;
+}
+
+static int upload(uint8_t* dst, const std::vector<uint8_t>& src) {
+  DLWP_CUDA(cudaMemcpy(dst, src.data(), src.size(), cudaMemcpyHostToDevice));
+  return DLWP_OK;
+}
+
+int plan_tc_commit(dlwp_plan* p, cudaStream_t st) {
+  const dlwp_model_desc& d = p->d;
+  const int L = d.lifting_channels, Pj = d.projection_channels, Cin = p->Cin, Cg = d.prognostic_channels;
+  DLWP_CUDA(cudaStreamSynchronize(st));
+  std::vector<float> w, b;
+  std::vector<uint8_t> img;
+  // lifting fcs.0: [L, Cin] weights with the bias as column Cin (the activations carry a 1 there)
+  DLWP_TRY(fetch(p, "lifting.fcs.0.weight", (int64_t)L * Cin, &w));
+  DLWP_TRY(fetch(p, "lifting.fcs.0.bias", L, &b));
+  {
+    std::vector<float> m((size_t)L * 16, 0.f);
+    for (int h = 0; h < L; ++h) {
+      for (int c = 0; c < Cin; ++c) m[(size_t)h * 16 + c] = w[(size_t)h * Cin + c];
+      m[(size_t)h * 16 + Cin] = b[h];
+    }
+    img.assign((size_t)L * 16 * 4, 0);
+    tc_pack_images(m.data(), L, 16, 16, L, 16, img.data());
+    DLWP_TRY(upload(p->tc_liftW1, img));
+  }
+  DLWP_TRY(fetch(p, "lifting.fcs.1.weight", (int64_t)kTcC * L, &w));
+  img.assign((size_t)32 * L * 4, 0);
+  tc_pack_images(w.data(), kTcC, L, L, 32, L, img.data());
+  DLWP_TRY(upload(p->tc_liftW2, img));
+  for (int l = 0; l < d.n_layers; ++l) {
+    DLWP_TRY(fetch(p, "fno_blocks.fno_skips." + std::to_string(l) + ".weight", (int64_t)kTcC * kTcC, &w));
+    img.assign(4096, 0);
+    tc_pack_images(w.data(), 32, 32, 32, 32, 32, img.data());
+    DLWP_TRY(upload(p->tc_skip[l], img));
+  }
+  DLWP_TRY(fetch(p, "projection.fcs.0.weight", (int64_t)Pj * kTcC, &w));
+  img.assign((size_t)Pj * 32 * 4, 0);
+  tc_pack_images(w.data(), Pj, 32, 32, Pj, 32, img.data());
+  DLWP_TRY(upload(p->tc_projW1, img));
+  DLWP_TRY(fetch(p, "projection.fcs.1.weight", (int64_t)Cg * Pj, &w));
+  img.assign((size_t)16 * Pj * 4, 0);
+  tc_pack_images(w.data(), Cg, Pj, Pj, 16, Pj, img.data());
+  DLWP_TRY(upload(p->tc_projW2, img));
+  return DLWP_OK;
+}
+
+// One model evaluation on the tensor-core path.
+int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
+  const dlwp_model_desc& d = p->d;
+  const int H = d.height, C = kTcC, R = d.n_rows, Kc = d.n_cols, N = d.n_layers;
+  TcGeom g = p->tcg;
+  g.ntiles = (int)((long long)B * g.HW / kTcTile);
+  const float *b2, *cbias, *pb1, *pb2;
+  DLWP_TRY(plan_need(p, "lifting.fcs.1.bias", C, &b2));
+  DLWP_TRY(plan_need(p, "fno_blocks.convs.bias", (int64_t)N * C, &cbias));
+  DLWP_TRY(plan_need(p, "projection.fcs.0.bias", d.projection_channels, &pb1));
+  DLWP_TRY(plan_need(p, "projection.fcs.1.bias", d.prognostic_channels, &pb2));
+
+  TcLiftArgs la{};
+  la.g = g;
+  la.ngrp = io.ngrp;
+  for (int i = 0; i < io.ngrp; ++i) la.grp[i] = io.grp[i];
+  la.Cin = p->Cin;
+  la.hid = d.lifting_channels;
+  la.W1img = p->tc_liftW1;
+  la.W2img = p->tc_liftW2;
+  la.b2 = b2;
+  la.Fimg = p->tc_F;
+  la.y_img = p->tc_img[0];
+  la.Aout = p->specA;
+  DLWP_TRY(launch_tc_lift(la, st));
+
+  int cur = 0;
+  for (int l = 0; l < N; ++l) {
+    // H-DFT on the retained columns, per-mode channel mixing, inverse H-DFT (fp32 FMA kernels)
+    TdftArgs a{};
+    a.in = p->specA; a.out = p->specX; a.T = p->Fh; a.N = H; a.K = R; a.C = C; a.nb0 = B; a.nb1 = Kc;
+    a.in_sn = (long long)Kc * C; a.in_sb0 = (long long)H * Kc * C; a.in_sb1 = C;
+    a.out_sk = (long long)Kc * B * C; a.out_sb0 = C; a.out_sb1 = (long long)B * C;
+    a.in_complex = true; a.out_complex = true;
+    DLWP_TRY(launch_tdft(a, st));
+    DLWP_TRY(launch_mix_dense(p->specX, p->wm[l], p->specY, R * Kc, B, C, C, st));
+    a = TdftArgs{};
+    a.in = p->specY; a.out = p->specZ; a.T = p->Gh; a.N = R; a.K = H; a.C = C; a.nb0 = B; a.nb1 = Kc;
+    a.in_sn = (long long)Kc * B * C; a.in_sb0 = C; a.in_sb1 = (long long)B * C;
+    a.out_sk = (long long)Kc * C; a.out_sb0 = (long long)H * Kc * C; a.out_sb1 = C;
+    a.in_complex = true; a.out_complex = true;
+    DLWP_TRY(launch_tdft(a, st));
+
+    TcLayerArgs ya{};
+    ya.g = g;
+    ya.x_img = p->tc_img[cur];
+    ya.y_img = p->tc_img[cur ^ 1];
+    ya.Z = p->specZ;
+    ya.Aout = l < N - 1 ? p->specA : nullptr;
+    ya.Gimg = p->tc_G;
+    ya.Fimg = p->tc_F;
+    ya.Wsimg = p->tc_skip[l];
+    ya.bias = cbias + (size_t)l * C;
+    ya.gelu = l < N - 1 ? 1 : 0;
+    DLWP_TRY(launch_tc_layer(ya, st));
+    cur ^= 1;
+  }
+
+  TcProjArgs pa{};
+  pa.g = g;
+  pa.x_img = p->tc_img[cur];
+  pa.hid = d.projection_channels;
+  pa.Cg = d.prognostic_channels;
+  pa.W1img = p->tc_projW1;
+  pa.b1 = pb1;
+  pa.W2img = p->tc_projW2;
+  pa.b2 = pb2;
+  pa.out = io.out;
+  pa.out_bstride = io.out_bstride;
+  pa.last = io.last;
+  pa.last_bstride = io.last_bstride;
+  DLWP_TRY(launch_tc_proj(pa, st));
+  return DLWP_OK;
+}
+
+}  // namespace dlwp

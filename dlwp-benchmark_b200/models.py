@@ -46,7 +46,7 @@ class _NativeRollout(nn.Module):
         return tuple((p.data_ptr(), p._version) for p in self.parameters())
 
     def _plan_for(self, device, B, H, W) -> NativePlan:
-        key = (device.index if device.index is not None else torch.cuda.current_device(), H, W)
+        key = (device.index if device.index is not None else torch.cuda.current_device(), H, W, self.precision)
         plan = self._plans.get(key)
         if plan is None or plan.max_batch < B:
             if plan is not None:

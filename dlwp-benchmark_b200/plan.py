@@ -78,6 +78,11 @@ class NativePlan:
         native.check(self._lib.dlwp_plan_workspace_bytes(self._h, C.byref(n)))
         return int(n.value)
 
+    def uses_tensor_cores(self) -> bool:
+        n = C.c_int()
+        native.check(self._lib.dlwp_plan_uses_tensor_cores(self._h, C.byref(n)))
+        return bool(n.value)
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 

@@ -98,6 +98,9 @@ const char* dlwp_last_error(void);
 int dlwp_plan_create(const dlwp_model_desc* desc, int device, dlwp_plan** out);
 int dlwp_plan_destroy(dlwp_plan* plan);
 int dlwp_plan_workspace_bytes(const dlwp_plan* plan, size_t* bytes);
+/* *out = 1 when the plan runs the tcgen05 tensor-core kernel set (DLWP_PREC_FP32_TC on a shape
+ * it covers), 0 when it runs the fp32 FMA kernel set. */
+int dlwp_plan_uses_tensor_cores(const dlwp_plan* plan, int* out);
 
 /* Replaces load_state_dict (scripts/evaluate.py:148-149).  `name` is the reference
  * state_dict key without the wrapper prefix "fno." (e.g. "lifting.fcs.0.weight",

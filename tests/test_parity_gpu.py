@@ -148,6 +148,39 @@ def test_fno_rollout_tracks_oracle_rmse_curve(pkg, case, steps):
     assert max_rel(got[:, 0], want[:, 0]) < TOL_STEP
 
 
+# tensor-core mode (DLWP_PREC_FP32_TC): split-bf16 products on tcgen05, same 1e-4 bound
+@pytest.mark.parametrize("case,steps", [("C2", 1), ("C1", 1), ("C2", 20), ("C1", 50)])
+def test_fno_tensor_core_path_matches_oracle(pkg, case, steps):
+    from dlwp_benchmark_b200 import native
+    ref, mod, kw, (B, H, W) = _fno_pair(pkg, case)
+    mod.precision = native.PREC_FP32_TC
+    ctx = kw["context_size"]
+    const, presc, prog = synthetic(B, ctx + steps, kw["constant_channels"], kw["prescribed_channels"],
+                                   kw["prognostic_channels"], H, W, smooth=steps > 1)
+    with torch.no_grad():
+        want = ref(constants=const, prescribed=presc, prognostic=prog)
+        got = mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog)).cpu()
+    assert all(p.uses_tensor_cores() for p in mod._plans.values()), "tcgen05 path was not taken"
+    assert torch.isfinite(got).all()
+    assert max_rel(got[:, 0], want[:, 0]) < TOL_STEP
+    if steps > 1:
+        tgt = synthetic(B, steps, 0, 0, kw["prognostic_channels"], H, W, seed=77)[2]
+        rw, rg = _rmse_curve(want, tgt), _rmse_curve(got, tgt)
+        assert float(((rg - rw).abs() / rw).max()) < TOL_CURVE
+
+
+def test_tensor_core_mode_falls_back_to_fp32_kernels_on_other_shapes(pkg):
+    from dlwp_benchmark_b200 import native
+    ref, mod, kw, (B, H, W) = _fno_pair(pkg, "odd")
+    mod.precision = native.PREC_FP32_TC
+    const, presc, prog = synthetic(B, 3, 1, 0, 2, H, W)
+    with torch.no_grad():
+        want = ref(constants=const, prescribed=presc, prognostic=prog)
+        got = mod(constants=_dev(const), prescribed=None, prognostic=_dev(prog))
+    assert not any(p.uses_tensor_cores() for p in mod._plans.values())
+    assert max_rel(got, want) < TOL_STEP
+
+
 def test_fno_rejects_grad_and_cpu_inputs(pkg):
     _, mod, kw, (B, H, W) = _fno_pair(pkg, "odd")
     const, presc, prog = synthetic(B, 3, 1, 0, 2, H, W)
