@@ -36,19 +36,47 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return fmaf(hx, copysignf(erf_abs, x), hx);
 }
 
-// ---- common tail of the lift and layer kernels ------------------------------------------------
-// v[32] = the 32 output channels of this thread's pixel (tile row = tid).  Writes the tile
-// image to HBM and, when `Aout` is set, the forward truncated W-DFT of the tile:
-//   D3[(part, h2, kx'), c] = sum_{px} F''[(part, h2, kx'), px] * v[px, c]
-// as one more M=64 UMMA whose B operand is the tile transposed through shared memory.
-__device__ __forceinline__ void finish_tile(const float (&v)[32], int tid, int tile, const TcGeom& g, uint8_t* y_img,
-                                            float2* Aout, uint8_t* sF, uint8_t* sXT, float* stage, uint32_t tmem_d3,
-                                            uint64_t* bar, uint32_t& phase) {
+}  // namespace
+
+// =============================================================================================
+// CTA organisation shared by the three kernels (persistent, one CTA per SM, 320 threads)
+//   warps 0-3 : epilogue group of worker 0      warp 8 : control warp of worker 0
+//   warps 4-7 : epilogue group of worker 1      warp 9 : control warp of worker 1
+// A worker owns every second tile of its CTA.  Its control warp issues the bulk copies and all
+// tcgen05.mma of the worker (one lane) and never touches data; its 128 epilogue threads own
+// one accumulator row (= pixel) each, move TMEM -> registers -> SMEM / HBM and never wait for
+// an MMA round trip they did not have a full pass of work to hide behind.  The two sides meet
+// only on mbarriers:
+//   *_full  : producer -> consumer ("data is there"): tcgen05.commit (count 1), a bulk copy's
+//             complete_tx (count 1 + bytes) or 128 epilogue arrivals
+//   *_empty : consumer -> producer ("buffer may be overwritten")
+// Ring slot of use u on a ring of depth 2: u & 1; full parity (u >> 1) & 1; empty parity
+// ((u >> 1) & 1) ^ 1 (so the first two uses pass immediately on fresh barriers).
+// Constant operands (weights, DFT matrices) are loaded once per CTA and shared by both workers.
+// TMEM: 512 columns per CTA, 256 per worker.
+// =============================================================================================
+namespace {
+
+constexpr int kEpi = 128;                    // epilogue threads per worker
+constexpr int kCta = 2 * kEpi + 2 * 32;      // 320
+
+__device__ __forceinline__ uint32_t full_par(uint32_t u) { return (u >> 1) & 1u; }
+__device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1u) ^ 1u; }
+
+// ---- common tail of the lift and layer epilogues ------------------------------------------------
+// v[32] = the 32 output channels of this thread's pixel (tile row t).  Writes the tile image to
+// HBM and, when `Aout` is set, hands the transposed tile to the control warp, which runs the
+// forward truncated W-DFT as one more M=64 UMMA
+//   D3[(part, h2, kx'), c] = sum_{px} F''[(part, h2, kx'), px] * v[px, c];
+// the result is folded (hi + lo rows) through `stage` (aliases the transposed tile) into Aout.
+__device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int w, int tile, const TcGeom& g,
+                                            uint8_t* y_img, float2* Aout, uint8_t* sXT, uint32_t tmem_d3,
+                                            uint64_t* xt_full, uint64_t* d3_full, uint32_t& n3) {
   {
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) split2(v[2 * j], v[2 * j + 1], hi[j], lo[j]);
-    uint8_t* dst = y_img + (size_t)tile * kTileBytes + tid * 16;
+    uint8_t* dst = y_img + (size_t)tile * kTileBytes + t * 16;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       *reinterpret_cast<uint4*>(dst + q * 2048) = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
@@ -59,7 +87,7 @@ __device__ __forceinline__ void finish_tile(const float (&v)[32], int tid, int t
   if (Aout == nullptr) return;
 
   // transposed tile [channel][pixel]: lanes pair up so that each store holds two adjacent pixels
-  const int odd = tid & 1, me = tid & ~1;
+  const int odd = t & 1, me = t & ~1;
   uint8_t* xt = sXT + (me >> 3) * kLboXT + (me & 7) * 2;
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
@@ -75,36 +103,25 @@ __device__ __forceinline__ void finish_tile(const float (&v)[32], int tid, int t
   }
   fence_async_smem();
   tc_fence_before();
-  __syncthreads();
-  if (tid == 0) {
-    tc_fence_after();
-    const uint32_t idesc = idesc_bf16(64, 32);
-    const uint32_t aF = smem_u32(sF), aXT = smem_u32(sXT);
-#pragma unroll
-    for (int part = 0; part < 2; ++part)
-#pragma unroll
-      for (int k0 = 0; k0 < 128; k0 += 16)
-        umma_bf16(tmem_d3, chunk_desc(aF, 64, k0), smem_desc(aXT + part * kXTBytes + (k0 >> 3) * kLboXT, kLboXT, 128),
-                  idesc, (part | k0) != 0);
-    umma_commit(bar);
-  }
-  mbar_wait(bar, phase);
-  phase ^= 1;
+  mbar_arrive(xt_full);
+  mbar_wait(d3_full, n3 & 1u);
+  ++n3;
   tc_fence_after();
 
-  // an M=64 accumulator keeps row r in TMEM lane 32 * (r / 16) + r % 16: warp w holds rows 16w..16w+15
-  const int warp = tid >> 5, lane = tid & 31;
+  // an M=64 accumulator keeps row r in TMEM lane 32 * (r / 16) + r % 16: warp q holds rows 16q..16q+15
+  const int q4 = (t >> 5), lane = t & 31;
+  float* stage = reinterpret_cast<float*>(sXT);
   uint32_t r[32];
-  tmem_ld32(tmem_d3 + ((uint32_t)(warp * 32) << 16), r);
+  tmem_ld32(tmem_d3 + ((uint32_t)(q4 * 32) << 16), r);
   tmem_ld_wait();
   if (lane < 16) {
-    float* s = stage + ((warp >> 1) * 32 + (warp & 1) * 16 + lane) * kStageLd;
+    float* s = stage + ((q4 >> 1) * 32 + (q4 & 1) * 16 + lane) * kStageLd;
 #pragma unroll
     for (int c = 0; c < 32; ++c) s[c] = __uint_as_float(r[c]);
   }
-  __syncthreads();
+  bar_sync(1 + w, kEpi);
   const int n = g.RT * g.Kc * 32;
-  for (int e = tid; e < n; e += 128) {
+  for (int e = t; e < n; e += kEpi) {
     const int c = e & 31, q = e >> 5;
     const int kx = q % g.Kc, h2 = q / g.Kc;
     const int idx = h2 * g.KXP + 2 * kx;
@@ -112,6 +129,22 @@ __device__ __forceinline__ void finish_tile(const float (&v)[32], int tid, int t
     const float im = stage[(idx + 1) * kStageLd + c] + stage[(33 + idx) * kStageLd + c];
     Aout[((size_t)(tile * g.RT + h2) * g.Kc + kx) * 32 + c] = make_float2(re, im);
   }
+  bar_sync(1 + w, kEpi);    // stage (= transposed-tile storage) is free again
+}
+
+// control warp, one lane: forward W-DFT UMMAs of one tile
+__device__ __forceinline__ void issue_fwd_dft(uint32_t aF, uint32_t aXT, uint32_t tmem_d3, uint64_t* xt_full,
+                                              uint64_t* d3_full, uint32_t n3) {
+  mbar_wait(xt_full, n3 & 1u);
+  tc_fence_after();
+  const uint32_t idesc = idesc_bf16(64, 32);
+#pragma unroll
+  for (int part = 0; part < 2; ++part)
+#pragma unroll
+    for (int k0 = 0; k0 < 128; k0 += 16)
+      umma_bf16(tmem_d3, chunk_desc(aF, 64, k0), smem_desc(aXT + part * kXTBytes + (k0 >> 3) * kLboXT, kLboXT, 128), idesc,
+                (part | k0) != 0);
+  umma_commit(d3_full);
 }
 
 }  // namespace
@@ -120,109 +153,159 @@ __device__ __forceinline__ void finish_tile(const float (&v)[32], int tid, int t
 // fno_layer_kernel: y = act( irfft_W(Z) + skip(x) + bias ) on 128-pixel tiles
 //   D[128 px, 32 ch] = G'[128, 32] * Z'^T  +  X[128, 32] * Ws^T      (12 UMMAs, split-bf16)
 // G' is block-diagonal over the grid rows of the tile; Z' holds (Re, Im) of the retained
-// columns of those rows for every channel.
+// columns of those rows for every channel.  The control warp prefetches the next tile image
+// (bulk copy) and gathers the next Z' while the epilogue group works on the current tile.
 // =============================================================================================
 namespace {
 struct LayerSmem {
-  static constexpr int G = 0, F = G + 2 * kImg, Ws = F + 64 * 128 * 2, X = Ws + 4096, Z = X + kTileBytes,
-                       XT = Z + 4096, Stage = XT + 2 * kXTBytes, Bias = Stage + kStageBytes, Total = Bias + 128;
+  static constexpr int G = 0, F = G + 2 * kImg, Ws = F + 64 * 128 * 2, Bias = Ws + 4096, Worker = Bias + 128;
+  static constexpr int X = 0, Z = X + 2 * kTileBytes, XT = Z + 2 * 4096, WorkerBytes = XT + 2 * kXTBytes;
+  static constexpr int Total = Worker + 2 * WorkerBytes;
 };
+enum { LB_XFULL = 0, LB_DFULL = 2, LB_DEMPTY = 4, LB_XTFULL = 6, LB_D3FULL = 7, LB_PER = 8 };
 }  // namespace
 
-__global__ void __launch_bounds__(128) fno_layer_kernel(const TcLayerArgs a) {
+__global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ uint64_t bar_const, bar_x, bar_mma;
+  __shared__ uint64_t bars[2 * LB_PER + 1];
   __shared__ uint32_t tmem_s;
-  uint8_t *sG = smem + LayerSmem::G, *sF = smem + LayerSmem::F, *sWs = smem + LayerSmem::Ws, *sX = smem + LayerSmem::X,
-          *sZ = smem + LayerSmem::Z, *sXT = smem + LayerSmem::XT;
-  float* stage = reinterpret_cast<float*>(smem + LayerSmem::Stage);
-  float* sBias = reinterpret_cast<float*>(smem + LayerSmem::Bias);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const TcGeom g = a.g;
+  float* sBias = reinterpret_cast<float*>(smem + LayerSmem::Bias);
+  uint64_t* bar_const = &bars[2 * LB_PER];
 
   if (tid == 0) {
-    mbar_init(&bar_const, 1);
-    mbar_init(&bar_x, 1);
-    mbar_init(&bar_mma, 1);
+    for (int w = 0; w < 2; ++w) {
+      uint64_t* b = bars + w * LB_PER;
+      mbar_init(&b[LB_XFULL], 1);
+      mbar_init(&b[LB_XFULL + 1], 1);
+      mbar_init(&b[LB_DFULL], 1);
+      mbar_init(&b[LB_DFULL + 1], 1);
+      mbar_init(&b[LB_DEMPTY], kEpi);
+      mbar_init(&b[LB_DEMPTY + 1], kEpi);
+      mbar_init(&b[LB_XTFULL], kEpi);
+      mbar_init(&b[LB_D3FULL], 1);
+    }
+    mbar_init(bar_const, 1);
     fence_mbar_init();
   }
-  if (warp == 0) {
-    tmem_alloc(&tmem_s, 64);
+  if (warp == 8) {
+    tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
-  for (int i = tid; i < 1024; i += 128) reinterpret_cast<uint32_t*>(sZ)[i] = 0u;   // pad columns stay zero
+  for (int w = 0; w < 2; ++w) {   // pad columns of Z' stay zero
+    uint32_t* z = reinterpret_cast<uint32_t*>(smem + LayerSmem::Worker + w * LayerSmem::WorkerBytes + LayerSmem::Z);
+    for (int i = tid; i < 2048; i += kCta) z[i] = 0u;
+  }
   if (tid < 32) sBias[tid] = a.bias ? a.bias[tid] : 0.f;
+  fence_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_d = tmem_s, tmem_d3 = tmem_s + 32;
   if (tid == 0) {
-    mbar_arrive_expect_tx(&bar_const, 2 * kImg + 64 * 128 * 2 + 4096);
-    bulk_g2s(sG, a.Gimg, 2 * kImg, &bar_const);
-    bulk_g2s(sF, a.Fimg, 64 * 128 * 2, &bar_const);
-    bulk_g2s(sWs, a.Wsimg, 4096, &bar_const);
+    mbar_arrive_expect_tx(bar_const, 2 * kImg + 64 * 128 * 2 + 4096);
+    bulk_g2s(smem + LayerSmem::G, a.Gimg, 2 * kImg, bar_const);
+    bulk_g2s(smem + LayerSmem::F, a.Fimg, 64 * 128 * 2, bar_const);
+    bulk_g2s(smem + LayerSmem::Ws, a.Wsimg, 4096, bar_const);
   }
-  mbar_wait(&bar_const, 0);
-  uint32_t ph_x = 0, ph_mma = 0;
+  const int stride = gridDim.x * 2;
 
-  for (int tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x) {
-    if (tid == 0) {
-      mbar_arrive_expect_tx(&bar_x, kTileBytes);
-      bulk_g2s(sX, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &bar_x);
+  if (warp >= 8) {
+    // ------------------------------ control warp ------------------------------
+    const int w = warp - 8;
+    uint64_t* b = bars + w * LB_PER;
+    uint8_t* ws = smem + LayerSmem::Worker + w * LayerSmem::WorkerBytes;
+    const uint32_t tmem = tmem_s + 256u * w;
+    const uint32_t aG = smem_u32(smem + LayerSmem::G), aF = smem_u32(smem + LayerSmem::F),
+                   aW = smem_u32(smem + LayerSmem::Ws), aXT = smem_u32(ws + LayerSmem::XT);
+    const int first = blockIdx.x * 2 + w;
+    mbar_wait(bar_const, 0);
+
+    auto load_inputs = [&](int tile, uint32_t u) {
+      const int s = u & 1;
+      mbar_wait(&b[LB_DFULL + s], empty_par(u));   // the UMMAs that read X[s] / Z'[s] two tiles ago are done
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&b[LB_XFULL + s], kTileBytes);
+        bulk_g2s(ws + LayerSmem::X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[LB_XFULL + s]);
+      }
+      uint8_t* z = ws + LayerSmem::Z + s * 4096;
+      const float2* src = a.Z + (size_t)tile * g.RT * g.Kc * 32 + lane;
+      const int nq = g.RT * g.Kc;
+#pragma unroll 4
+      for (int q = 0; q < nq; ++q) {
+        const int h2 = q / g.Kc, kx = q - h2 * g.Kc;
+        const float2 v = src[(size_t)q * 32];
+        uint32_t h, l;
+        split2(v.x, v.y, h, l);
+        const int k = h2 * g.KXP + 2 * kx;
+        const int off = (k >> 3) * 512 + lane * 16 + (k & 7) * 2;
+        *reinterpret_cast<uint32_t*>(z + off) = h;
+        *reinterpret_cast<uint32_t*>(z + 2048 + off) = l;
+      }
+      fence_async_smem();
+      __syncwarp();
+    };
+
+    if (first < g.ntiles) load_inputs(first, 0);
+    uint32_t u = 0;
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+      const int s = u & 1;
+      if (lane == 0) {
+        mbar_wait(&b[LB_XFULL + s], full_par(u));
+        mbar_wait(&b[LB_DEMPTY + s], empty_par(u));
+        tc_fence_after();
+        const uint32_t idesc = idesc_bf16(128, 32);
+        const uint32_t aX = smem_u32(ws + LayerSmem::X + s * kTileBytes), aZ = smem_u32(ws + LayerSmem::Z + s * 4096);
+        const uint32_t d = tmem + 32u * s;
+        uint32_t acc = 0;
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
+          const uint32_t ao = term == 1 ? kImg : 0, bo = term == 2 ? 2048 : 0;
+#pragma unroll
+          for (int k0 = 0; k0 < 32; k0 += 16) {
+            umma_bf16(d, chunk_desc(aG + ao, 128, k0), chunk_desc(aZ + bo, 32, k0), idesc, acc);
+            acc = 1;
+            umma_bf16(d, chunk_desc(aX + ao, 128, k0), chunk_desc(aW + bo, 32, k0), idesc, acc);
+          }
+        }
+        umma_commit(&b[LB_DFULL + s]);
+      }
+      __syncwarp();
+      if (tile + stride < g.ntiles) load_inputs(tile + stride, u + 1);
+      if (a.Aout != nullptr && lane == 0) issue_fwd_dft(aF, aXT, tmem + 64, &b[LB_XTFULL], &b[LB_D3FULL], u);
+      __syncwarp();
     }
-    // Z'[ch, (h2, kx')] <- Z[(row, kx), ch] (fp32 complex), split into bf16 hi / lo
-    for (int q = warp; q < g.RT * g.Kc; q += 4) {
-      const int h2 = q / g.Kc, kx = q - h2 * g.Kc;
-      const float2 z = a.Z[((size_t)(tile * g.RT + h2) * g.Kc + kx) * 32 + lane];
-      uint32_t h, l;
-      split2(z.x, z.y, h, l);
-      const int k = h2 * g.KXP + 2 * kx;
-      const int off = (k >> 3) * 512 + lane * 16 + (k & 7) * 2;
-      *reinterpret_cast<uint32_t*>(sZ + off) = h;
-      *reinterpret_cast<uint32_t*>(sZ + 2048 + off) = l;
-    }
-    fence_async_smem();
-    mbar_wait(&bar_x, ph_x);
-    ph_x ^= 1;
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
+  } else {
+    // ------------------------------ epilogue group ------------------------------
+    const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
+    uint64_t* b = bars + w * LB_PER;
+    uint8_t* ws = smem + LayerSmem::Worker + w * LayerSmem::WorkerBytes;
+    const uint32_t tmem = tmem_s + 256u * w + ((uint32_t)(q4 * 32) << 16);
+    uint32_t u = 0, n3 = 0;
+    for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
+      const int s = u & 1;
+      mbar_wait(&b[LB_DFULL + s], full_par(u));
       tc_fence_after();
-      const uint32_t idesc = idesc_bf16(128, 32);
-      const uint32_t aG = smem_u32(sG), aZ = smem_u32(sZ), aX = smem_u32(sX), aW = smem_u32(sWs);
-      uint32_t acc = 0;
+      float v[32];
+      {
+        uint32_t r[32];
+        tmem_ld32(tmem + 32u * s, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(&b[LB_DEMPTY + s]);
 #pragma unroll
-      for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
-        const uint32_t ao = term == 1 ? kImg : 0, bo = term == 2 ? 2048 : 0;
-#pragma unroll
-        for (int k0 = 0; k0 < 32; k0 += 16) {
-          umma_bf16(tmem_d, chunk_desc(aG + ao, 128, k0), chunk_desc(aZ + bo, 32, k0), idesc, acc);
-          acc = 1;
-          umma_bf16(tmem_d, chunk_desc(aX + ao, 128, k0), chunk_desc(aW + bo, 32, k0), idesc, acc);
+        for (int c = 0; c < 32; ++c) {
+          const float x = __uint_as_float(r[c]) + sBias[c];
+          v[c] = a.gelu ? gelu_fast(x) : x;
         }
       }
-      umma_commit(&bar_mma);
+      finish_tile(v, t, w, tile, g, a.y_img, a.Aout, ws + LayerSmem::XT, tmem_s + 256u * w + 64, &b[LB_XTFULL],
+                  &b[LB_D3FULL], n3);
     }
-    mbar_wait(&bar_mma, ph_mma);
-    ph_mma ^= 1;
-    tc_fence_after();
-
-    float v[32];
-    {
-      uint32_t r[32];
-      tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16), r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        const float t = __uint_as_float(r[c]) + sBias[c];
-        v[c] = a.gelu ? gelu_fast(t) : t;
-      }
-    }
-    finish_tile(v, tid, tile, g, a.y_img, a.Aout, sF, sXT, stage, tmem_d3, &bar_mma, ph_mma);
-    tc_fence_before();
-    __syncthreads();
   }
-  if (warp == 0) tmem_dealloc(tmem_s, 64);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem_s, 512);
 }
 
 int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
@@ -233,68 +316,120 @@ int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
     DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     DLWP_CUDA(cudaFuncSetAttribute(fno_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LayerSmem::Total));
   }
-  const int grid = a.g.ntiles < 2 * sms ? a.g.ntiles : 2 * sms;
-  fno_layer_kernel<<<grid, 128, LayerSmem::Total, st>>>(a);
+  const int want = (a.g.ntiles + 1) / 2;
+  const int grid = want < sms ? want : sms;
+  fno_layer_kernel<<<grid, kCta, LayerSmem::Total, st>>>(a);
   DLWP_LAUNCHED("fno_layer_kernel");
   return DLWP_OK;
 }
 
 // =============================================================================================
-// Fused 2-layer pointwise MLP on one 128-pixel tile (neuralop MLP: 1x1 conv, GELU, 1x1 conv)
-//   D1[128, 128] = A1 * W1[pass]^T              (hidden columns, 128 at a time, in TMEM)
-//   A2 = split(GELU(D1 + b1))                   (32 columns at a time, double-buffered in SMEM)
-//   D2[128, N2] += A2 * W2[:, cols]^T
-// The hidden activations never leave the SM.
+// Fused 2-layer pointwise MLP (neuralop MLP: 1x1 conv, GELU, 1x1 conv) on 128-pixel tiles
+//   D1[128, 64]  = A1 * W1[pass]^T                 hidden columns, 64 per pass, double-buffered in TMEM
+//   A2           = split(GELU(D1 + b1))            32 columns per chunk, double-buffered in SMEM
+//   D2[128, N2] += A2 * W2[:, chunk]^T             double-buffered across tiles
+// The hidden activations never leave the SM.  The control lane runs one pass ahead of the
+// epilogue group, so the group only ever waits for data that had a full pass of time to arrive.
+// Worker TMEM columns: D1 at +0 / +64, D2 at +128 / +160, D3 (lift only) at +192.
 // =============================================================================================
 namespace {
 
-struct MlpBars {
-  uint64_t* d1;
-  uint64_t* a2;        // [2]
-  uint32_t ph_d1;
-  uint32_t ph_a2[2];
-};
+enum { MB_A1FULL = 0, MB_A1EMPTY = 2, MB_D1FULL = 4, MB_D1EMPTY = 6, MB_A2FULL = 8, MB_A2EMPTY = 10, MB_D2FULL = 12,
+       MB_D2EMPTY = 14, MB_XTFULL = 16, MB_D3FULL = 17, MB_PER = 18 };
 
-template <int K1, int N2, bool kBias1>
-__device__ __forceinline__ void mlp_tile(int tid, uint32_t aA1, uint32_t aW1, int hid, const float* sB1, uint32_t aW2,
-                                         uint8_t* sA2, uint32_t tmem_d1, uint32_t tmem_d2, MlpBars& bars) {
-  const int warp = tid >> 5;
-  const uint32_t a1_lo = aA1 + 128 * K1 * 2, w1_lo = aW1 + (uint32_t)hid * K1 * 2, w2_lo = aW2 + (uint32_t)N2 * hid * 2;
-  const uint32_t aA2 = smem_u32(sA2);
-  int cg = 0;     // chunk counter within this tile
-  for (int p = 0; p < hid / 128; ++p) {
-    if (tid == 0) {
+__device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_count) {
+  for (int i = 0; i < 2; ++i) {
+    mbar_init(&b[MB_A1FULL + i], a1_full_count);
+    mbar_init(&b[MB_A1EMPTY + i], 1);
+    mbar_init(&b[MB_D1FULL + i], 1);
+    mbar_init(&b[MB_D1EMPTY + i], kEpi);
+    mbar_init(&b[MB_A2FULL + i], kEpi);
+    mbar_init(&b[MB_A2EMPTY + i], 1);
+    mbar_init(&b[MB_D2FULL + i], 1);
+    mbar_init(&b[MB_D2EMPTY + i], kEpi);
+  }
+  mbar_init(&b[MB_XTFULL], kEpi);
+  mbar_init(&b[MB_D3FULL], 1);
+}
+
+struct MlpIssuer {
+  uint64_t* b;
+  uint32_t aA1;        // two A1 buffers, `a1_stride` bytes apart; lo image at +128*K1*2
+  uint32_t a1_stride;
+  uint32_t aW1, aW2, aA2, tmem;
+  int hid, P;
+  uint32_t nc;         // chunks issued so far
+
+  template <int K1>
+  __device__ __forceinline__ void mma1(uint32_t u, int p, uint32_t gp) {
+    const int db = gp & 1, ub = u & 1;
+    mbar_wait(&b[MB_D1EMPTY + db], empty_par(gp));
+    if (p == 0) mbar_wait(&b[MB_A1FULL + ub], full_par(u));
+    tc_fence_after();
+    const uint32_t idesc = idesc_bf16(128, 64);
+    const uint32_t a_hi = aA1 + ub * a1_stride, a_lo = a_hi + 128 * K1 * 2, w_lo = aW1 + (uint32_t)hid * K1 * 2;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int term = 0; term < 3; ++term) {
+      const uint32_t aa = term == 1 ? a_lo : a_hi, ww = term == 2 ? w_lo : aW1;
+#pragma unroll
+      for (int k0 = 0; k0 < K1; k0 += 16) {
+        umma_bf16(tmem + 64u * db, chunk_desc(aa, 128, k0),
+                  smem_desc(ww + (uint32_t)(k0 >> 3) * hid * 16 + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128), idesc, acc);
+        acc = 1;
+      }
+    }
+    umma_commit(&b[MB_D1FULL + db]);
+    if (p == P - 1) umma_commit(&b[MB_A1EMPTY + ub]);
+  }
+
+  template <int N2>
+  __device__ __forceinline__ void mma2(uint32_t u, int p) {
+    const uint32_t idesc = idesc_bf16(128, N2);
+    const uint32_t w_lo = aW2 + (uint32_t)N2 * hid * 2;
+    const uint32_t d2 = tmem + 128u + 32u * (u & 1);
+#pragma unroll
+    for (int j = 0; j < 2; ++j, ++nc) {
+      const int ab = nc & 1;
+      mbar_wait(&b[MB_A2FULL + ab], full_par(nc));
+      if (p == 0 && j == 0) mbar_wait(&b[MB_D2EMPTY + (u & 1)], empty_par(u));
       tc_fence_after();
-      const uint32_t idesc = idesc_bf16(128, 128);
-      uint32_t acc = 0;
+      const uint32_t a2 = aA2 + ab * kTileBytes;
+      const int hcol0 = p * 64 + 32 * j;
 #pragma unroll
       for (int term = 0; term < 3; ++term) {
-        const uint32_t a = term == 1 ? a1_lo : aA1, w = term == 2 ? w1_lo : aW1;
+        const uint32_t aa = term == 1 ? a2 + kImg : a2, ww = term == 2 ? w_lo : aW2;
 #pragma unroll
-        for (int k0 = 0; k0 < K1; k0 += 16) {
-          umma_bf16(tmem_d1, chunk_desc(a, 128, k0),
-                    smem_desc(w + (uint32_t)(k0 >> 3) * hid * 16 + (uint32_t)p * 128 * 16, (uint32_t)hid * 16, 128), idesc,
-                    acc);
-          acc = 1;
-        }
+        for (int kk = 0; kk < 32; kk += 16)
+          umma_bf16(d2, chunk_desc(aa, 128, kk), chunk_desc(ww, N2, hcol0 + kk), idesc, (p | j | term | kk) != 0);
       }
-      umma_commit(bars.d1);
+      umma_commit(&b[MB_A2EMPTY + ab]);
     }
-    mbar_wait(bars.d1, bars.ph_d1);
-    bars.ph_d1 ^= 1;
+    if (p == P - 1) umma_commit(&b[MB_D2FULL + (u & 1)]);
+  }
+};
+
+// epilogue side of one tile's MLP; `after_pass0()` runs once after the first pass
+template <bool kBias1, class Hook>
+__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, int t, uint32_t tmem_lane, int P, const float* sB1,
+                                             uint8_t* sA2, uint32_t& gp, uint32_t& nc, Hook after_pass0) {
+  for (int p = 0; p < P; ++p, ++gp) {
+    const int db = gp & 1;
+    mbar_wait(&b[MB_D1FULL + db], full_par(gp));
     tc_fence_after();
 #pragma unroll 1
-    for (int j = 0; j < 4; ++j, ++cg) {
-      const int buf = cg & 1;
+    for (int j = 0; j < 2; ++j, ++nc) {
       uint32_t r[32];
-      tmem_ld32(tmem_d1 + ((uint32_t)(warp * 32) << 16) + 32 * j, r);
+      tmem_ld32(tmem_lane + 64u * db + 32u * j, r);
       tmem_ld_wait();
-      if (cg >= 2) {      // the UMMAs that read this A2 buffer two chunks ago must be done
-        mbar_wait(&bars.a2[buf], bars.ph_a2[buf]);
-        bars.ph_a2[buf] ^= 1;
+      if (j == 1) {
+        tc_fence_before();
+        mbar_arrive(&b[MB_D1EMPTY + db]);
       }
-      uint8_t* dst = sA2 + buf * kTileBytes + tid * 16;
-      const int hcol0 = p * 128 + 32 * j;
+      const int ab = nc & 1;
+      mbar_wait(&b[MB_A2EMPTY + ab], empty_par(nc));
+      uint8_t* dst = sA2 + ab * kTileBytes + t * 16;
+      const int hcol0 = p * 64 + 32 * j;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         uint32_t h[4], l[4];
@@ -311,30 +446,10 @@ __device__ __forceinline__ void mlp_tile(int tid, uint32_t aA1, uint32_t aW1, in
         *reinterpret_cast<uint4*>(dst + kImg + q * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
       }
       fence_async_smem();
-      tc_fence_before();
-      __syncthreads();
-      if (tid == 0) {
-        tc_fence_after();
-        const uint32_t idesc2 = idesc_bf16(128, N2);
-        const uint32_t a2 = aA2 + buf * kTileBytes;
-#pragma unroll
-        for (int term = 0; term < 3; ++term) {
-          const uint32_t a = term == 1 ? a2 + kImg : a2, w = term == 2 ? w2_lo : aW2;
-#pragma unroll
-          for (int kk = 0; kk < 32; kk += 16)
-            umma_bf16(tmem_d2, chunk_desc(a, 128, kk), chunk_desc(w, N2, hcol0 + kk), idesc2, (cg | term | kk) != 0);
-        }
-        umma_commit(&bars.a2[buf]);
-      }
+      mbar_arrive(&b[MB_A2FULL + ab]);
     }
+    if (p == 0) after_pass0();
   }
-  // drain: both buffers' last commits (the second one covers every UMMA of this tile)
-  const int last = cg - 1;
-  mbar_wait(&bars.a2[(last - 1) & 1], bars.ph_a2[(last - 1) & 1]);
-  bars.ph_a2[(last - 1) & 1] ^= 1;
-  mbar_wait(&bars.a2[last & 1], bars.ph_a2[last & 1]);
-  bars.ph_a2[last & 1] ^= 1;
-  tc_fence_after();
 }
 
 }  // namespace
@@ -343,78 +458,109 @@ __device__ __forceinline__ void mlp_tile(int tid, uint32_t aA1, uint32_t aW1, in
 // fno_proj_kernel: out = last + W2 * GELU(W1 * x + b1) + b2, tile image in, NCHW frame out
 // =============================================================================================
 namespace {
-struct ProjSmem {   // for hid = 256
-  static constexpr int X = 0, W1 = X + kTileBytes, W2 = W1 + 256 * 32 * 4, A2 = W2 + 16 * 256 * 4, B1 = A2 + 2 * kTileBytes,
-                       B2 = B1 + 1024, Total = B2 + 64;
+struct ProjSmem {   // sized for hid = 256
+  static constexpr int W1 = 0, W2 = W1 + 256 * 32 * 4, B1 = W2 + 16 * 256 * 4, B2 = B1 + 1024, Worker = B2 + 64;
+  static constexpr int X = 0, A2 = X + 2 * kTileBytes, WorkerBytes = A2 + 2 * kTileBytes;
+  static constexpr int Total = Worker + 2 * WorkerBytes;
 };
 }  // namespace
 
-__global__ void __launch_bounds__(128) fno_proj_kernel(const TcProjArgs a) {
+__global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ uint64_t bar_const, bar_x, bar_d1, bar_a2[2];
+  __shared__ uint64_t bars[2 * MB_PER + 1];
   __shared__ uint32_t tmem_s;
-  uint8_t *sX = smem + ProjSmem::X, *sW1 = smem + ProjSmem::W1, *sW2 = smem + ProjSmem::W2, *sA2 = smem + ProjSmem::A2;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const TcGeom g = a.g;
+  const int hid = a.hid, P = hid / 64;
   float* sB1 = reinterpret_cast<float*>(smem + ProjSmem::B1);
   float* sB2 = reinterpret_cast<float*>(smem + ProjSmem::B2);
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const TcGeom g = a.g;
-  const int hid = a.hid;
+  uint64_t* bar_const = &bars[2 * MB_PER];
 
   if (tid == 0) {
-    mbar_init(&bar_const, 1);
-    mbar_init(&bar_x, 1);
-    mbar_init(&bar_d1, 1);
-    mbar_init(&bar_a2[0], 1);
-    mbar_init(&bar_a2[1], 1);
+    mlp_init_barriers(bars, 1);
+    mlp_init_barriers(bars + MB_PER, 1);
+    mbar_init(bar_const, 1);
     fence_mbar_init();
   }
-  if (warp == 0) {
-    tmem_alloc(&tmem_s, 256);
+  if (warp == 8) {
+    tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
-  for (int i = tid; i < hid; i += 128) sB1[i] = a.b1[i];
+  for (int i = tid; i < hid; i += kCta) sB1[i] = a.b1[i];
   if (tid < 16) sB2[tid] = tid < a.Cg ? a.b2[tid] : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_d1 = tmem_s, tmem_d2 = tmem_s + 128;
   const uint32_t w1_bytes = (uint32_t)hid * 32 * 4, w2_bytes = 16u * hid * 4;
   if (tid == 0) {
-    mbar_arrive_expect_tx(&bar_const, w1_bytes + w2_bytes);
-    bulk_g2s(sW1, a.W1img, w1_bytes, &bar_const);
-    bulk_g2s(sW2, a.W2img, w2_bytes, &bar_const);
+    mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes);
+    bulk_g2s(smem + ProjSmem::W1, a.W1img, w1_bytes, bar_const);
+    bulk_g2s(smem + ProjSmem::W2, a.W2img, w2_bytes, bar_const);
   }
-  mbar_wait(&bar_const, 0);
-  uint32_t ph_x = 0;
-  MlpBars bars{&bar_d1, bar_a2, 0u, {0u, 0u}};
+  const int stride = gridDim.x * 2;
 
-  for (int tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x) {
-    if (tid == 0) {
-      mbar_arrive_expect_tx(&bar_x, kTileBytes);
-      bulk_g2s(sX, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &bar_x);
-    }
-    mbar_wait(&bar_x, ph_x);
-    ph_x ^= 1;
-    mlp_tile<32, 16, true>(tid, smem_u32(sX), smem_u32(sW1), hid, sB1, smem_u32(sW2), sA2, tmem_d1, tmem_d2, bars);
-
-    uint32_t r[16];
-    tmem_ld16(tmem_d2 + ((uint32_t)(warp * 32) << 16), r);
-    tmem_ld_wait();
-    const long long p = (long long)tile * kTcTile + tid;
-    const long long b = p / g.HW, pix = p - b * g.HW;
-    float* o = a.out + b * a.out_bstride + pix;
-    const float* lastp = a.last ? a.last + b * a.last_bstride + pix : nullptr;
-#pragma unroll
-    for (int c = 0; c < 16; ++c)
-      if (c < a.Cg) {
-        float val = __uint_as_float(r[c]) + sB2[c];
-        if (lastp) val += lastp[(long long)c * g.HW];
-        o[(long long)c * g.HW] = val;
+  if (warp >= 8) {
+    if (lane == 0) {
+      const int w = warp - 8;
+      uint64_t* b = bars + w * MB_PER;
+      uint8_t* ws = smem + ProjSmem::Worker + w * ProjSmem::WorkerBytes;
+      MlpIssuer is{b, smem_u32(ws + ProjSmem::X), (uint32_t)kTileBytes, smem_u32(smem + ProjSmem::W1),
+                   smem_u32(smem + ProjSmem::W2), smem_u32(ws + ProjSmem::A2), tmem_s + 256u * w, hid, P, 0u};
+      const int first = blockIdx.x * 2 + w;
+      mbar_wait(bar_const, 0);
+      auto load_x = [&](int tile, uint32_t u) {
+        const int s = u & 1;
+        mbar_wait(&b[MB_A1EMPTY + s], empty_par(u));
+        mbar_arrive_expect_tx(&b[MB_A1FULL + s], kTileBytes);
+        bulk_g2s(ws + ProjSmem::X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[MB_A1FULL + s]);
+      };
+      if (first < g.ntiles) {
+        load_x(first, 0);
+        is.mma1<32>(0, 0, 0);
       }
-    tc_fence_before();
-    __syncthreads();
+      uint32_t u = 0;
+      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+        const bool has_next = tile + stride < g.ntiles;
+        if (has_next) load_x(tile + stride, u + 1);
+        for (int p = 0; p < P; ++p) {
+          const uint32_t gp = u * P + p;
+          if (p + 1 < P) is.mma1<32>(u, p + 1, gp + 1);
+          else if (has_next) is.mma1<32>(u + 1, 0, gp + 1);
+          is.mma2<16>(u, p);
+        }
+      }
+    }
+  } else {
+    const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
+    uint64_t* b = bars + w * MB_PER;
+    uint8_t* ws = smem + ProjSmem::Worker + w * ProjSmem::WorkerBytes;
+    const uint32_t tmem_lane = tmem_s + 256u * w + ((uint32_t)(q4 * 32) << 16);
+    uint32_t u = 0, gp = 0, nc = 0;
+    for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
+      epi_mlp_tile<true>(b, t, tmem_lane, P, sB1, ws + ProjSmem::A2, gp, nc, [] {});
+      mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
+      tc_fence_after();
+      uint32_t r[16];
+      tmem_ld16(tmem_lane + 128u + 32u * (u & 1), r);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
+      const long long p = (long long)tile * kTcTile + t;
+      const long long bb = p / g.HW, pix = p - bb * g.HW;
+      float* o = a.out + bb * a.out_bstride + pix;
+      const float* lastp = a.last ? a.last + bb * a.last_bstride + pix : nullptr;
+#pragma unroll
+      for (int c = 0; c < 16; ++c)
+        if (c < a.Cg) {
+          float val = __uint_as_float(r[c]) + sB2[c];
+          if (lastp) val += lastp[(long long)c * g.HW];
+          o[(long long)c * g.HW] = val;
+        }
+    }
   }
-  if (warp == 0) tmem_dealloc(tmem_s, 256);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem_s, 512);
 }
 
 int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
@@ -426,8 +572,9 @@ int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
     DLWP_CUDA(cudaFuncSetAttribute(fno_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ProjSmem::Total));
   }
   DLWP_REQUIRE(a.hid == 128 || a.hid == 256, "tensor-core projection needs width 128 or 256, got %d", a.hid);
-  const int grid = a.g.ntiles < 2 * sms ? a.g.ntiles : 2 * sms;
-  fno_proj_kernel<<<grid, 128, ProjSmem::Total, st>>>(a);
+  const int want = (a.g.ntiles + 1) / 2;
+  const int grid = want < sms ? want : sms;
+  fno_proj_kernel<<<grid, kCta, ProjSmem::Total, st>>>(a);
   DLWP_LAUNCHED("fno_proj_kernel");
   return DLWP_OK;
 }
@@ -436,96 +583,143 @@ int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
 // fno_lift_kernel: x_t gathered from the NCHW sources -> lifting MLP -> tile image + W-DFT
 // =============================================================================================
 namespace {
-struct LiftSmem {   // for hid = 256; XT / Stage reuse the A2 buffers once the MLP of the tile is done
-  static constexpr int A1 = 0, W1 = A1 + 128 * 16 * 4, W2 = W1 + 256 * 16 * 4, A2 = W2 + 32 * 256 * 4, XT = A2,
-                       Stage = XT + 2 * kXTBytes, F = A2 + 2 * kTileBytes, B2 = F + 64 * 128 * 2, Total = B2 + 128;
-  static_assert(Stage + kStageBytes <= F, "transposed tile + stage must fit in the A2 buffers");
+struct LiftSmem {   // sized for hid = 256; the transposed tile / stage reuse the A2 buffers
+  static constexpr int W1 = 0, W2 = W1 + 256 * 16 * 4, F = W2 + 32 * 256 * 4, B2 = F + 64 * 128 * 2, Worker = B2 + 128;
+  static constexpr int A1 = 0, A2 = A1 + 2 * 8192, XT = A2, WorkerBytes = A2 + 2 * kTileBytes;
+  static constexpr int Total = Worker + 2 * WorkerBytes;
+  static_assert(2 * kXTBytes <= 2 * kTileBytes, "transposed tile must fit in the A2 buffers");
 };
 }  // namespace
 
-__global__ void __launch_bounds__(128) fno_lift_kernel(const TcLiftArgs a) {
+__global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ uint64_t bar_const, bar_d1, bar_a2[2], bar_d3;
+  __shared__ uint64_t bars[2 * MB_PER + 1];
   __shared__ uint32_t tmem_s;
-  uint8_t *sA1 = smem + LiftSmem::A1, *sW1 = smem + LiftSmem::W1, *sW2 = smem + LiftSmem::W2, *sA2 = smem + LiftSmem::A2,
-          *sXT = smem + LiftSmem::XT, *sF = smem + LiftSmem::F;
-  float* stage = reinterpret_cast<float*>(smem + LiftSmem::Stage);
-  float* sB2 = reinterpret_cast<float*>(smem + LiftSmem::B2);
-  const int tid = threadIdx.x, warp = tid >> 5;
+  __shared__ const float* kptr[16];     // per input channel: plane base and batch stride
+  __shared__ long long kbs[16];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const TcGeom g = a.g;
-  const int hid = a.hid;
+  const int hid = a.hid, P = hid / 64;
+  float* sB2 = reinterpret_cast<float*>(smem + LiftSmem::B2);
+  uint64_t* bar_const = &bars[2 * MB_PER];
 
   if (tid == 0) {
-    mbar_init(&bar_const, 1);
-    mbar_init(&bar_d1, 1);
-    mbar_init(&bar_a2[0], 1);
-    mbar_init(&bar_a2[1], 1);
-    mbar_init(&bar_d3, 1);
+    mlp_init_barriers(bars, kEpi);
+    mlp_init_barriers(bars + MB_PER, kEpi);
+    mbar_init(bar_const, 1);
     fence_mbar_init();
+    int k = 0;     // channel order: constants | prescribed (t, c) | prognostic (t, c)  (fno.py:58-62)
+    for (int gi = 0; gi < a.ngrp; ++gi)
+      for (int ch = 0; ch < a.grp[gi].nch && k < 16; ++ch, ++k) {
+        kptr[k] = a.grp[gi].base + (long long)ch * g.HW;
+        kbs[k] = a.grp[gi].bstride;
+      }
+    for (; k < 16; ++k) {
+      kptr[k] = a.grp[0].base;
+      kbs[k] = 0;
+    }
   }
-  if (warp == 0) {
-    tmem_alloc(&tmem_s, 256);
+  if (warp == 8) {
+    tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
   if (tid < 32) sB2[tid] = a.b2[tid];
-  {
-    // constant columns of A1: column Cin is 1 (it multiplies the bias row of W1), the rest 0
-    uint4* z = reinterpret_cast<uint4*>(sA1);
-    for (int i = tid; i < 128 * 16 * 4 / 16; i += 128) z[i] = make_uint4(0, 0, 0, 0);
-  }
-  __syncthreads();
-  *reinterpret_cast<uint16_t*>(sA1 + (a.Cin >> 3) * 2048 + tid * 16 + (a.Cin & 7) * 2) = 0x3F80;   // bf16(1.0), hi part
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_d1 = tmem_s, tmem_d2 = tmem_s + 128, tmem_d3 = tmem_s + 160;
   const uint32_t w1_bytes = (uint32_t)hid * 16 * 4, w2_bytes = 32u * hid * 4;
   if (tid == 0) {
-    mbar_arrive_expect_tx(&bar_const, w1_bytes + w2_bytes + 64 * 128 * 2);
-    bulk_g2s(sW1, a.W1img, w1_bytes, &bar_const);
-    bulk_g2s(sW2, a.W2img, w2_bytes, &bar_const);
-    bulk_g2s(sF, a.Fimg, 64 * 128 * 2, &bar_const);
+    mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + 64 * 128 * 2);
+    bulk_g2s(smem + LiftSmem::W1, a.W1img, w1_bytes, bar_const);
+    bulk_g2s(smem + LiftSmem::W2, a.W2img, w2_bytes, bar_const);
+    bulk_g2s(smem + LiftSmem::F, a.Fimg, 64 * 128 * 2, bar_const);
   }
-  mbar_wait(&bar_const, 0);
-  uint32_t ph_d3 = 0;
-  MlpBars bars{&bar_d1, bar_a2, 0u, {0u, 0u}};
+  const int stride = gridDim.x * 2;
 
-  for (int tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x) {
-    // gather: channel order constants | prescribed (t, c) | prognostic (t, c)  (fno.py:58-62)
-    {
-      const long long p = (long long)tile * kTcTile + tid;
-      const long long b = p / g.HW, pix = p - b * g.HW;
-      int k = 0;
-      for (int gi = 0; gi < a.ngrp; ++gi) {
-        const float* src = a.grp[gi].base + b * a.grp[gi].bstride + pix;
-        for (int ch = 0; ch < a.grp[gi].nch; ++ch, ++k) {
-          const float val = src[(long long)ch * g.HW];
-          const __nv_bfloat16 h = __float2bfloat16_rn(val);
-          const __nv_bfloat16 l = __float2bfloat16_rn(val - __bfloat162float(h));
-          uint8_t* d = sA1 + (k >> 3) * 2048 + tid * 16 + (k & 7) * 2;
-          *reinterpret_cast<__nv_bfloat16*>(d) = h;
-          *reinterpret_cast<__nv_bfloat16*>(d + 4096) = l;
+  if (warp >= 8) {
+    if (lane == 0) {
+      const int w = warp - 8;
+      uint64_t* b = bars + w * MB_PER;
+      uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
+      MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
+                   smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u};
+      const uint32_t aF = smem_u32(smem + LiftSmem::F), aXT = smem_u32(ws + LiftSmem::XT), d3 = tmem_s + 256u * w + 192u;
+      const int first = blockIdx.x * 2 + w;
+      const bool dft = a.Aout != nullptr;
+      mbar_wait(bar_const, 0);
+      if (first < g.ntiles) is.mma1<16>(0, 0, 0);
+      uint32_t u = 0;
+      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+        const bool has_next = tile + stride < g.ntiles;
+        for (int p = 0; p < P; ++p) {
+          const uint32_t gp = u * P + p;
+          if (p + 1 < P) is.mma1<16>(u, p + 1, gp + 1);
+          else if (has_next) is.mma1<16>(u + 1, 0, gp + 1);
+          if (p == 0 && u > 0 && dft) issue_fwd_dft(aF, aXT, d3, &b[MB_XTFULL], &b[MB_D3FULL], u - 1);
+          is.mma2<32>(u, p);
         }
       }
+      if (u > 0 && dft) issue_fwd_dft(aF, aXT, d3, &b[MB_XTFULL], &b[MB_D3FULL], u - 1);
     }
-    fence_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    mlp_tile<16, 32, false>(tid, smem_u32(sA1), smem_u32(sW1), hid, nullptr, smem_u32(sW2), sA2, tmem_d1, tmem_d2, bars);
+  } else {
+    const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
+    uint64_t* b = bars + w * MB_PER;
+    uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
+    const uint32_t tmem_w = tmem_s + 256u * w, tmem_lane = tmem_w + ((uint32_t)(q4 * 32) << 16);
+    const int Cin = a.Cin;
 
-    float v[32];
-    {
-      uint32_t r[32];
-      tmem_ld32(tmem_d2 + ((uint32_t)(warp * 32) << 16), r);
-      tmem_ld_wait();
+    auto gather = [&](int tile, float (&x)[16]) {
+      const long long p = (long long)tile * kTcTile + t;
+      const long long bb = p / g.HW, pix = p - bb * g.HW;
 #pragma unroll
-      for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]) + sB2[c];
+      for (int k = 0; k < 16; ++k) x[k] = k < Cin ? kptr[k][bb * kbs[k] + pix] : (k == Cin ? 1.0f : 0.0f);
+    };
+    auto store_a1 = [&](uint32_t u, const float (&x)[16]) {   // column Cin carries the 1 that multiplies the bias
+      const int s = u & 1;
+      mbar_wait(&b[MB_A1EMPTY + s], empty_par(u));
+      uint32_t h[8], l[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) split2(x[2 * j], x[2 * j + 1], h[j], l[j]);
+      uint8_t* d = ws + LiftSmem::A1 + s * 8192 + t * 16;
+      *reinterpret_cast<uint4*>(d) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(d + 2048) = make_uint4(h[4], h[5], h[6], h[7]);
+      *reinterpret_cast<uint4*>(d + 4096) = make_uint4(l[0], l[1], l[2], l[3]);
+      *reinterpret_cast<uint4*>(d + 6144) = make_uint4(l[4], l[5], l[6], l[7]);
+      fence_async_smem();
+      mbar_arrive(&b[MB_A1FULL + s]);
+    };
+
+    const int first = blockIdx.x * 2 + w;
+    float nx[16];
+    if (first < g.ntiles) {
+      gather(first, nx);
+      store_a1(0, nx);
     }
-    finish_tile(v, tid, tile, g, a.y_img, a.Aout, sF, sXT, stage, tmem_d3, &bar_d3, ph_d3);
-    tc_fence_before();
-    __syncthreads();
+    uint32_t u = 0, gp = 0, nc = 0, n3 = 0;
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+      const bool has_next = tile + stride < g.ntiles;
+      if (has_next) gather(tile + stride, nx);      // loads in flight while the first pass is processed
+      epi_mlp_tile<false>(b, t, tmem_lane, P, nullptr, ws + LiftSmem::A2, gp, nc, [&] {
+        if (has_next) store_a1(u + 1, nx);
+      });
+      mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
+      tc_fence_after();
+      float v[32];
+      {
+        uint32_t r[32];
+        tmem_ld32(tmem_lane + 128u + 32u * (u & 1), r);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]) + sB2[c];
+      }
+      finish_tile(v, t, w, tile, g, a.y_img, a.Aout, ws + LiftSmem::XT, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], n3);
+    }
   }
-  if (warp == 0) tmem_dealloc(tmem_s, 256);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem_s, 512);
 }
 
 int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
@@ -537,9 +731,10 @@ int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
     DLWP_CUDA(cudaFuncSetAttribute(fno_lift_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LiftSmem::Total));
   }
   DLWP_REQUIRE(a.hid == 128 || a.hid == 256, "tensor-core lifting needs width 128 or 256, got %d", a.hid);
-  DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 15, "tensor-core lifting needs 1..15 input channels, got %d", a.Cin);
-  const int grid = a.g.ntiles < 2 * sms ? a.g.ntiles : 2 * sms;
-  fno_lift_kernel<<<grid, 128, LiftSmem::Total, st>>>(a);
+  DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 15 && a.ngrp >= 1, "tensor-core lifting needs 1..15 input channels, got %d", a.Cin);
+  const int want = (a.g.ntiles + 1) / 2;
+  const int grid = want < sms ? want : sms;
+  fno_lift_kernel<<<grid, kCta, LiftSmem::Total, st>>>(a);
   DLWP_LAUNCHED("fno_lift_kernel");
   return DLWP_OK;
 }
