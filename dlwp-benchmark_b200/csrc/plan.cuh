@@ -59,7 +59,8 @@ struct dlwp_plan {
   dlwp::TcGeom tcg{};
   uint8_t* tc_img[2] = {nullptr, nullptr};              // activation tile images (ping-pong)
   uint8_t *tc_G = nullptr, *tc_F = nullptr;             // inverse / forward W-DFT operand images
-  uint8_t *tc_liftW1 = nullptr, *tc_liftW2 = nullptr, *tc_projW1 = nullptr, *tc_projW2 = nullptr;
+  uint8_t *tc_liftW1 = nullptr, *tc_liftW2 = nullptr, *tc_projW1 = nullptr, *tc_projW2 = nullptr,
+          *tc_projW1x = nullptr;
   std::vector<uint8_t*> tc_skip;                        // per layer skip-conv images
 
   // host-entry staging (dlwp_rollout_host)

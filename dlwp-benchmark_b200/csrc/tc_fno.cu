@@ -36,6 +36,42 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return fmaf(hx, copysignf(erf_abs, x), hx);
 }
 
+// The same GELU on two values at once with the packed fp32x2 pipe of sm_100 (FFMA2 / FMUL2):
+//   gelu(x) = x/2 + |x|/2 * erf(|x| / sqrt 2),   erf(z) = 1 - (a1 t + .. + a5 t^5) exp(-z^2),  t = 1 / (1 + p z)
+// 9 issue slots per element instead of 15 (the MUFU ops stay scalar).
+__device__ __forceinline__ float2 gelu2(float2 x) {
+  const float kR = 0.70710678118654752f;
+  const float2 z = make_float2(fabsf(x.x) * kR, fabsf(x.y) * kR);
+  const float2 den = __ffma2_rn(make_float2(0.3275911f, 0.3275911f), z, make_float2(1.0f, 1.0f));
+  float2 t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.x) : "f"(den.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.y) : "f"(den.y));
+  // negated polynomial: q = -(a1 t + ... + a5 t^5)
+  float2 q = __ffma2_rn(make_float2(-1.061405429f, -1.061405429f), t, make_float2(1.453152027f, 1.453152027f));
+  q = __ffma2_rn(q, t, make_float2(-1.421413741f, -1.421413741f));
+  q = __ffma2_rn(q, t, make_float2(0.284496736f, 0.284496736f));
+  q = __ffma2_rn(q, t, make_float2(-0.254829592f, -0.254829592f));
+  q = __fmul2_rn(q, t);
+  float2 w = __fmul2_rn(x, x);
+  w = __fmul2_rn(w, make_float2(-0.72134752044448170f, -0.72134752044448170f));   // -z^2 * log2(e)
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(w.x));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(w.y));
+  const float2 erf_abs = __ffma2_rn(q, e, make_float2(1.0f, 1.0f));
+  const float2 ahx = __fmul2_rn(z, make_float2(kR, kR));          // |x| / 2
+  const float2 hx = __fmul2_rn(x, make_float2(0.5f, 0.5f));
+  return __ffma2_rn(ahx, erf_abs, hx);
+}
+
+// v = hi + lo for a pair, residual through one packed FMA
+__device__ __forceinline__ void split2p(float2 v, uint32_t& hi, uint32_t& lo) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+  hi = *reinterpret_cast<uint32_t*>(&h);
+  const float2 hf = make_float2(__uint_as_float(hi << 16), __uint_as_float(hi & 0xffff0000u));
+  const float2 d = __ffma2_rn(hf, make_float2(-1.0f, -1.0f), v);
+  __nv_bfloat162 l = __floats2bfloat162_rn(d.x, d.y);
+  lo = *reinterpret_cast<uint32_t*>(&l);
+}
+
 }  // namespace
 
 // =============================================================================================
@@ -359,6 +395,7 @@ struct MlpIssuer {
   uint32_t aW1, aW2, aA2, tmem;
   int hid, P;
   uint32_t nc;         // chunks issued so far
+  uint32_t aOnes, aW1x;   // optional bias term of the first GEMM: Ones[128,16] * W1x[hid,16]^T (0 = none)
 
   template <int K1>
   __device__ __forceinline__ void mma1(uint32_t u, int p, uint32_t gp) {
@@ -379,6 +416,9 @@ struct MlpIssuer {
         acc = 1;
       }
     }
+    if (aW1x != 0)
+      umma_bf16(tmem + 64u * db, chunk_desc(aOnes, 128, 0), smem_desc(aW1x + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128),
+                idesc, 1);
     umma_commit(&b[MB_D1FULL + db]);
     if (p == P - 1) umma_commit(&b[MB_A1EMPTY + ub]);
   }
@@ -410,9 +450,9 @@ struct MlpIssuer {
 };
 
 // epilogue side of one tile's MLP; `after_pass0()` runs once after the first pass
-template <bool kBias1, class Hook>
-__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, int t, uint32_t tmem_lane, int P, const float* sB1,
-                                             uint8_t* sA2, uint32_t& gp, uint32_t& nc, Hook after_pass0) {
+template <class Hook>
+__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, int t, uint32_t tmem_lane, int P, uint8_t* sA2, uint32_t& gp,
+                                             uint32_t& nc, Hook after_pass0) {
   for (int p = 0; p < P; ++p, ++gp) {
     const int db = gp & 1;
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
@@ -429,19 +469,13 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, int t, uint32_t tmem_l
       const int ab = nc & 1;
       mbar_wait(&b[MB_A2EMPTY + ab], empty_par(nc));
       uint8_t* dst = sA2 + ab * kTileBytes + t * 16;
-      const int hcol0 = p * 64 + 32 * j;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         uint32_t h[4], l[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          float f0 = __uint_as_float(r[8 * q + 2 * e]), f1 = __uint_as_float(r[8 * q + 2 * e + 1]);
-          if (kBias1) {
-            f0 += sB1[hcol0 + 8 * q + 2 * e];
-            f1 += sB1[hcol0 + 8 * q + 2 * e + 1];
-          }
-          split2(gelu_fast(f0), gelu_fast(f1), h[e], l[e]);
-        }
+        for (int e = 0; e < 4; ++e)
+          split2p(gelu2(make_float2(__uint_as_float(r[8 * q + 2 * e]), __uint_as_float(r[8 * q + 2 * e + 1]))), h[e],
+                  l[e]);
         *reinterpret_cast<uint4*>(dst + q * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
         *reinterpret_cast<uint4*>(dst + kImg + q * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
       }
@@ -459,7 +493,8 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, int t, uint32_t tmem_l
 // =============================================================================================
 namespace {
 struct ProjSmem {   // sized for hid = 256
-  static constexpr int W1 = 0, W2 = W1 + 256 * 32 * 4, B1 = W2 + 16 * 256 * 4, B2 = B1 + 1024, Worker = B2 + 64;
+  static constexpr int W1 = 0, W2 = W1 + 256 * 32 * 4, W1x = W2 + 16 * 256 * 4, Ones = W1x + 256 * 16 * 2, B2 = Ones + 4096,
+                       Worker = B2 + 64;
   static constexpr int X = 0, A2 = X + 2 * kTileBytes, WorkerBytes = A2 + 2 * kTileBytes;
   static constexpr int Total = Worker + 2 * WorkerBytes;
 };
@@ -472,7 +507,6 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const TcGeom g = a.g;
   const int hid = a.hid, P = hid / 64;
-  float* sB1 = reinterpret_cast<float*>(smem + ProjSmem::B1);
   float* sB2 = reinterpret_cast<float*>(smem + ProjSmem::B2);
   uint64_t* bar_const = &bars[2 * MB_PER];
 
@@ -486,16 +520,21 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
     tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
-  for (int i = tid; i < hid; i += kCta) sB1[i] = a.b1[i];
+  {   // Ones[128, 16]: columns 0 and 1 are 1 (they multiply the hi and lo halves of the bias in W1x)
+    uint32_t* o = reinterpret_cast<uint32_t*>(smem + ProjSmem::Ones);
+    for (int i = tid; i < 1024; i += kCta) o[i] = (i < 512 && (i & 3) == 0) ? 0x3F803F80u : 0u;
+  }
+  fence_async_smem();
   if (tid < 16) sB2[tid] = tid < a.Cg ? a.b2[tid] : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t w1_bytes = (uint32_t)hid * 32 * 4, w2_bytes = 16u * hid * 4;
+  const uint32_t w1_bytes = (uint32_t)hid * 32 * 4, w2_bytes = 16u * hid * 4, w1x_bytes = (uint32_t)hid * 16 * 2;
   if (tid == 0) {
-    mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes);
+    mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + w1x_bytes);
     bulk_g2s(smem + ProjSmem::W1, a.W1img, w1_bytes, bar_const);
     bulk_g2s(smem + ProjSmem::W2, a.W2img, w2_bytes, bar_const);
+    bulk_g2s(smem + ProjSmem::W1x, a.W1ximg, w1x_bytes, bar_const);
   }
   const int stride = gridDim.x * 2;
 
@@ -505,7 +544,8 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + ProjSmem::Worker + w * ProjSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + ProjSmem::X), (uint32_t)kTileBytes, smem_u32(smem + ProjSmem::W1),
-                   smem_u32(smem + ProjSmem::W2), smem_u32(ws + ProjSmem::A2), tmem_s + 256u * w, hid, P, 0u};
+                   smem_u32(smem + ProjSmem::W2), smem_u32(ws + ProjSmem::A2), tmem_s + 256u * w, hid, P, 0u,
+                   smem_u32(smem + ProjSmem::Ones), smem_u32(smem + ProjSmem::W1x)};
       const int first = blockIdx.x * 2 + w;
       mbar_wait(bar_const, 0);
       auto load_x = [&](int tile, uint32_t u) {
@@ -537,7 +577,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
     const uint32_t tmem_lane = tmem_s + 256u * w + ((uint32_t)(q4 * 32) << 16);
     uint32_t u = 0, gp = 0, nc = 0;
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
-      epi_mlp_tile<true>(b, t, tmem_lane, P, sB1, ws + ProjSmem::A2, gp, nc, [] {});
+      epi_mlp_tile(b, t, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [] {});
       mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
       tc_fence_after();
       uint32_t r[16];
@@ -642,7 +682,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
-                   smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u};
+                   smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u};
       const uint32_t aF = smem_u32(smem + LiftSmem::F), aXT = smem_u32(ws + LiftSmem::XT), d3 = tmem_s + 256u * w + 192u;
       const int first = blockIdx.x * 2 + w;
       const bool dft = a.Aout != nullptr;
@@ -699,7 +739,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
     for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
       const bool has_next = tile + stride < g.ntiles;
       if (has_next) gather(tile + stride, nx);      // loads in flight while the first pass is processed
-      epi_mlp_tile<false>(b, t, tmem_lane, P, nullptr, ws + LiftSmem::A2, gp, nc, [&] {
+      epi_mlp_tile(b, t, tmem_lane, P, ws + LiftSmem::A2, gp, nc, [&] {
         if (has_next) store_a1(u + 1, nx);
       });
       mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
@@ -784,6 +824,15 @@ void tc_pack_images(const float* m, int rows, int cols, int ld, int R, int K, ui
       put(out, r, k, R, h);
       put(out + part, r, k, R, l);
     }
+}
+
+void tc_pack_bias_image(const float* bias, int n, int R, uint8_t* out) {
+  std::memset(out, 0, (size_t)R * 16 * 2);
+  for (int r = 0; r < n; ++r) {
+    const uint16_t h = f2bf(bias[r]);
+    put(out, r, 0, R, h);
+    put(out, r, 1, R, f2bf(bias[r] - bf2f(h)));
+  }
 }
 
 void tc_pack_stacked_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out) {

@@ -68,7 +68,7 @@ struct TcProjArgs {
   int hid;                // projection width: 128 or 256
   int Cg;                 // output channels <= 16
   const uint8_t* W1img;   // [hi | lo] images, R = hid rows, K = 32
-  const float* b1;        // [hid]
+  const uint8_t* W1ximg;  // one bf16 image, R = hid rows, K = 16: columns 0 / 1 = hi / lo of the first bias
   const uint8_t* W2img;   // [hi | lo] images, R = 16 rows, K = hid
   const float* b2;        // [Cg]
   float* out;             // NCHW frame(s): out[b * out_bstride + (c, y, x)]
@@ -87,6 +87,8 @@ int launch_tc_proj(const TcProjArgs& a, cudaStream_t st);
 void tc_pack_images(const float* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
 // same from fp64 (DFT bases)
 void tc_pack_images_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
+// one bf16 image [R, 16] with columns 0 / 1 = hi / lo parts of bias[r] (multiplied by a ones operand)
+void tc_pack_bias_image(const float* bias, int n, int R, uint8_t* out);
 // a single bf16 image whose rows [0, R/2) are hi parts and [R/2, R) lo parts of the R/2 x K matrix
 void tc_pack_stacked_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
 

@@ -65,6 +65,7 @@ int plan_tc_build(dlwp_plan* p) {
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_liftW2, (size_t)32 * L * 4));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_projW1, (size_t)Pj * 32 * 4));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_projW2, (size_t)16 * Pj * 4));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_projW1x, (size_t)Pj * 16 * 2));
   p->tc_skip.assign(d.n_layers, nullptr);
   for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_skip[l], 4096));
   p->tc = true;
@@ -117,6 +118,10 @@ int plan_tc_commit(dlwp_plan* p, cudaStream_t st) {
   img.assign((size_t)Pj * 32 * 4, 0);
   tc_pack_images(w.data(), Pj, 32, 32, Pj, 32, img.data());
   DLWP_TRY(upload(p->tc_projW1, img));
+  DLWP_TRY(fetch(p, "projection.fcs.0.bias", Pj, &b));
+  img.assign((size_t)Pj * 16 * 2, 0);
+  tc_pack_bias_image(b.data(), Pj, Pj, img.data());
+  DLWP_TRY(upload(p->tc_projW1x, img));
   DLWP_TRY(fetch(p, "projection.fcs.1.weight", (int64_t)Cg * Pj, &w));
   img.assign((size_t)16 * Pj * 4, 0);
   tc_pack_images(w.data(), Cg, Pj, Pj, 16, Pj, img.data());
@@ -130,10 +135,9 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   const int H = d.height, C = kTcC, R = d.n_rows, Kc = d.n_cols, N = d.n_layers;
   TcGeom g = p->tcg;
   g.ntiles = (int)((long long)B * g.HW / kTcTile);
-  const float *b2, *cbias, *pb1, *pb2;
+  const float *b2, *cbias, *pb2;
   DLWP_TRY(plan_need(p, "lifting.fcs.1.bias", C, &b2));
   DLWP_TRY(plan_need(p, "fno_blocks.convs.bias", (int64_t)N * C, &cbias));
-  DLWP_TRY(plan_need(p, "projection.fcs.0.bias", d.projection_channels, &pb1));
   DLWP_TRY(plan_need(p, "projection.fcs.1.bias", d.prognostic_channels, &pb2));
 
   TcLiftArgs la{};
@@ -188,7 +192,7 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   pa.hid = d.projection_channels;
   pa.Cg = d.prognostic_channels;
   pa.W1img = p->tc_projW1;
-  pa.b1 = pb1;
+  pa.W1ximg = p->tc_projW1x;
   pa.W2img = p->tc_projW2;
   pa.b2 = pb2;
   pa.out = io.out;
