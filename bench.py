@@ -208,8 +208,8 @@ def kernel_bytes(cls, kw, B, H, W, name):
         return b * N * (2 * B * m1 * m2 * C * 2 + m1 * m2 * C * C * 2)
     if name == "fno_lift_kernel":       # fused lifting MLP (+ forward W-DFT of its output)
         return b * px * (cin + C) + b * B * H * m2 * C * 2
-    if name == "fno_layer_kernel":      # fused inverse W-DFT + skip + GELU (+ forward W-DFT), per layer
-        return b * (N - 1) * (2 * px * C + 2 * B * H * m2 * C * 2)
+    if name == "fno_layer_kernel":      # fused inverse W-DFT + skip + GELU (+ forward W-DFT, not after the last layer)
+        return b * (N * 2 * px * C + (2 * N - 1) * B * H * m2 * C * 2)
     if name == "fno_mid_kernel":        # H-DFT, mode mixing, inverse H-DFT on the retained columns
         return b * N * (2 * B * H * m2 * C * 2 + m1 * m2 * C * C * 2)
     if name == "fno_tail_kernel":       # last layer + projection MLP + residual
@@ -451,7 +451,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c4")
     ap.add_argument("--members", type=int, default=0, help="ensemble members per GPU (0 = the workload's default)")
-    ap.add_argument("--precision", choices=["fp32", "fp32_tc", "bf16"], default="fp32")
+    ap.add_argument("--precision", choices=["fp32", "fp32_tc", "bf16"], default="fp32_tc")
     ap.add_argument("--cpu-members", type=int, default=64, help="members in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -59,6 +59,7 @@ struct dlwp_plan {
   dlwp::TcGeom tcg{};
   uint8_t* tc_img[2] = {nullptr, nullptr};              // activation tile images (ping-pong)
   uint8_t *tc_G = nullptr, *tc_F = nullptr;             // inverse / forward W-DFT operand images
+  uint8_t* tc_Z = nullptr;                              // Z' operand images between fno_mid_kernel and fno_layer_kernel
   uint8_t *tc_liftW1 = nullptr, *tc_liftW2 = nullptr, *tc_projW1 = nullptr, *tc_projW2 = nullptr,
           *tc_projW1x = nullptr;
   std::vector<uint8_t*> tc_skip;                        // per layer skip-conv images

@@ -187,17 +187,29 @@ __device__ __forceinline__ void issue_fwd_dft(uint32_t aF, uint32_t aXT, uint32_
 
 // =============================================================================================
 // fno_layer_kernel: y = act( irfft_W(Z) + skip(x) + bias ) on 128-pixel tiles
-//   D[128 px, 32 ch] = G'[128, 32] * Z'^T  +  X[128, 32] * Ws^T      (12 UMMAs, split-bf16)
-// G' is block-diagonal over the grid rows of the tile; Z' holds (Re, Im) of the retained
-// columns of those rows for every channel.  The control warp prefetches the next tile image
-// (bulk copy) and gathers the next Z' while the epilogue group works on the current tile.
+//   D[128 px, 32 ch] = G'[128, KZ] * Z'^T  +  X[128, 32] * Ws^T      (split-bf16: 3 terms each)
+// G' is block-diagonal over the grid rows of the tile; Z' (one 8-wide K chunk per retained
+// column: (Re, Im) of that column for each grid row of the tile) arrives from fno_mid_kernel
+// as a ready operand image.  The control lane keeps two tiles (activation image + Z' image,
+// one bulk copy each) in flight per worker while the epilogue group works on the current one.
 // =============================================================================================
 namespace {
-struct LayerSmem {
-  static constexpr int G = 0, F = G + 2 * kImg, Ws = F + 64 * 128 * 2, Bias = Ws + 4096, Worker = Bias + 128;
-  static constexpr int X = 0, Z = X + 2 * kTileBytes, XT = Z + 2 * 4096, WorkerBytes = XT + 2 * kXTBytes;
-  static constexpr int Total = Worker + 2 * WorkerBytes;
+struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
+  int G, F, Ws, Bias, Worker, X, Z, XT, WorkerBytes, Total;
+  __host__ __device__ explicit LayerSmem(int KZ) {
+    G = 0;
+    F = G + 2 * 128 * KZ * 2;
+    Ws = F + 64 * 128 * 2;
+    Bias = Ws + 4096;
+    Worker = Bias + 128;
+    X = 0;
+    Z = X + 2 * kTileBytes;
+    XT = Z + 2 * KZ * 128;
+    WorkerBytes = XT + 2 * kXTBytes;
+    Total = Worker + 2 * WorkerBytes;
+  }
 };
+constexpr int kLayerSmemMax = 226 * 1024;   // 227 KB per CTA minus the kernel's static shared memory
 enum { LB_XFULL = 0, LB_DFULL = 2, LB_DEMPTY = 4, LB_XTFULL = 6, LB_D3FULL = 7, LB_PER = 8 };
 }  // namespace
 
@@ -207,7 +219,8 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const TcGeom g = a.g;
-  float* sBias = reinterpret_cast<float*>(smem + LayerSmem::Bias);
+  const LayerSmem L(g.KZ);
+  float* sBias = reinterpret_cast<float*>(smem + L.Bias);
   uint64_t* bar_const = &bars[2 * LB_PER];
 
   if (tid == 0) {
@@ -229,93 +242,74 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
     tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
-  for (int w = 0; w < 2; ++w) {   // pad columns of Z' stay zero
-    uint32_t* z = reinterpret_cast<uint32_t*>(smem + LayerSmem::Worker + w * LayerSmem::WorkerBytes + LayerSmem::Z);
-    for (int i = tid; i < 2048; i += kCta) z[i] = 0u;
-  }
   if (tid < 32) sBias[tid] = a.bias ? a.bias[tid] : 0.f;
-  fence_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  const uint32_t g_bytes = 2u * 128u * (uint32_t)g.KZ * 2u, z_bytes = (uint32_t)g.KZ * 128u;
   if (tid == 0) {
-    mbar_arrive_expect_tx(bar_const, 2 * kImg + 64 * 128 * 2 + 4096);
-    bulk_g2s(smem + LayerSmem::G, a.Gimg, 2 * kImg, bar_const);
-    bulk_g2s(smem + LayerSmem::F, a.Fimg, 64 * 128 * 2, bar_const);
-    bulk_g2s(smem + LayerSmem::Ws, a.Wsimg, 4096, bar_const);
+    mbar_arrive_expect_tx(bar_const, g_bytes + 64 * 128 * 2 + 4096);
+    bulk_g2s(smem + L.G, a.Gimg, g_bytes, bar_const);
+    bulk_g2s(smem + L.F, a.Fimg, 64 * 128 * 2, bar_const);
+    bulk_g2s(smem + L.Ws, a.Wsimg, 4096, bar_const);
   }
   const int stride = gridDim.x * 2;
 
   if (warp >= 8) {
-    // ------------------------------ control warp ------------------------------
-    const int w = warp - 8;
-    uint64_t* b = bars + w * LB_PER;
-    uint8_t* ws = smem + LayerSmem::Worker + w * LayerSmem::WorkerBytes;
-    const uint32_t tmem = tmem_s + 256u * w;
-    const uint32_t aG = smem_u32(smem + LayerSmem::G), aF = smem_u32(smem + LayerSmem::F),
-                   aW = smem_u32(smem + LayerSmem::Ws), aXT = smem_u32(ws + LayerSmem::XT);
-    const int first = blockIdx.x * 2 + w;
-    mbar_wait(bar_const, 0);
+    // ------------------------------ control warp (one lane) ------------------------------
+    if (lane == 0) {
+      const int w = warp - 8;
+      uint64_t* b = bars + w * LB_PER;
+      uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
+      const uint32_t tmem = tmem_s + 256u * w;
+      const uint32_t aG = smem_u32(smem + L.G), aF = smem_u32(smem + L.F), aW = smem_u32(smem + L.Ws),
+                     aXT = smem_u32(ws + L.XT);
+      const int first = blockIdx.x * 2 + w;
 
-    auto load_inputs = [&](int tile, uint32_t u) {
-      const int s = u & 1;
-      mbar_wait(&b[LB_DFULL + s], empty_par(u));   // the UMMAs that read X[s] / Z'[s] two tiles ago are done
-      if (lane == 0) {
-        mbar_arrive_expect_tx(&b[LB_XFULL + s], kTileBytes);
-        bulk_g2s(ws + LayerSmem::X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[LB_XFULL + s]);
-      }
-      uint8_t* z = ws + LayerSmem::Z + s * 4096;
-      const float2* src = a.Z + (size_t)tile * g.RT * g.Kc * 32 + lane;
-      const int nq = g.RT * g.Kc;
-#pragma unroll 4
-      for (int q = 0; q < nq; ++q) {
-        const int h2 = q / g.Kc, kx = q - h2 * g.Kc;
-        const float2 v = src[(size_t)q * 32];
-        uint32_t h, l;
-        split2(v.x, v.y, h, l);
-        const int k = h2 * g.KXP + 2 * kx;
-        const int off = (k >> 3) * 512 + lane * 16 + (k & 7) * 2;
-        *reinterpret_cast<uint32_t*>(z + off) = h;
-        *reinterpret_cast<uint32_t*>(z + 2048 + off) = l;
-      }
-      fence_async_smem();
-      __syncwarp();
-    };
+      auto load_inputs = [&](int tile, uint32_t u) {
+        const int s = u & 1;
+        mbar_wait(&b[LB_DFULL + s], empty_par(u));   // the UMMAs that read slot s two tiles ago are done
+        mbar_arrive_expect_tx(&b[LB_XFULL + s], kTileBytes + z_bytes);
+        bulk_g2s(ws + L.X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[LB_XFULL + s]);
+        bulk_g2s(ws + L.Z + s * z_bytes, a.Zimg + (size_t)tile * z_bytes, z_bytes, &b[LB_XFULL + s]);
+      };
 
-    if (first < g.ntiles) load_inputs(first, 0);
-    uint32_t u = 0;
-    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
-      const int s = u & 1;
-      if (lane == 0) {
+      if (first < g.ntiles) load_inputs(first, 0);
+      if (first + stride < g.ntiles) load_inputs(first + stride, 1);
+      mbar_wait(bar_const, 0);
+      const uint32_t idesc = idesc_bf16(128, 32);
+      const uint32_t g_lo = 128u * (uint32_t)g.KZ * 2u, z_lo = (uint32_t)g.KZ * 64u;
+      uint32_t u = 0;
+      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+        const int s = u & 1;
         mbar_wait(&b[LB_XFULL + s], full_par(u));
         mbar_wait(&b[LB_DEMPTY + s], empty_par(u));
         tc_fence_after();
-        const uint32_t idesc = idesc_bf16(128, 32);
-        const uint32_t aX = smem_u32(ws + LayerSmem::X + s * kTileBytes), aZ = smem_u32(ws + LayerSmem::Z + s * 4096);
+        const uint32_t aX = smem_u32(ws + L.X + s * kTileBytes), aZ = smem_u32(ws + L.Z + s * z_bytes);
         const uint32_t d = tmem + 32u * s;
         uint32_t acc = 0;
 #pragma unroll
         for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
-          const uint32_t ao = term == 1 ? kImg : 0, bo = term == 2 ? 2048 : 0;
-#pragma unroll
-          for (int k0 = 0; k0 < 32; k0 += 16) {
-            umma_bf16(d, chunk_desc(aG + ao, 128, k0), chunk_desc(aZ + bo, 32, k0), idesc, acc);
+          const uint32_t ga = term == 1 ? g_lo : 0u, zb = term == 2 ? z_lo : 0u;
+          const uint32_t xa = term == 1 ? (uint32_t)kImg : 0u, wb = term == 2 ? 2048u : 0u;
+          for (int k0 = 0; k0 < g.KZ; k0 += 16) {
+            umma_bf16(d, chunk_desc(aG + ga, 128, k0), chunk_desc(aZ + zb, 32, k0), idesc, acc);
             acc = 1;
-            umma_bf16(d, chunk_desc(aX + ao, 128, k0), chunk_desc(aW + bo, 32, k0), idesc, acc);
           }
+#pragma unroll
+          for (int k0 = 0; k0 < 32; k0 += 16)
+            umma_bf16(d, chunk_desc(aX + xa, 128, k0), chunk_desc(aW + wb, 32, k0), idesc, 1);
         }
         umma_commit(&b[LB_DFULL + s]);
+        if (tile + 2 * stride < g.ntiles) load_inputs(tile + 2 * stride, u + 2);
+        if (a.Aout != nullptr) issue_fwd_dft(aF, aXT, tmem + 64, &b[LB_XTFULL], &b[LB_D3FULL], u);
       }
-      __syncwarp();
-      if (tile + stride < g.ntiles) load_inputs(tile + stride, u + 1);
-      if (a.Aout != nullptr && lane == 0) issue_fwd_dft(aF, aXT, tmem + 64, &b[LB_XTFULL], &b[LB_D3FULL], u);
-      __syncwarp();
     }
   } else {
     // ------------------------------ epilogue group ------------------------------
     const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
     uint64_t* b = bars + w * LB_PER;
-    uint8_t* ws = smem + LayerSmem::Worker + w * LayerSmem::WorkerBytes;
+    uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
     const uint32_t tmem = tmem_s + 256u * w + ((uint32_t)(q4 * 32) << 16);
     uint32_t u = 0, n3 = 0;
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
@@ -335,7 +329,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
           v[c] = a.gelu ? gelu_fast(x) : x;
         }
       }
-      finish_tile(v, t, w, tile, g, a.y_img, a.Aout, ws + LayerSmem::XT, tmem_s + 256u * w + 64, &b[LB_XTFULL],
+      finish_tile(v, t, w, tile, g, a.y_img, a.Aout, ws + L.XT, tmem_s + 256u * w + 64, &b[LB_XTFULL],
                   &b[LB_D3FULL], n3);
     }
   }
@@ -350,11 +344,13 @@ int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
     int dev = 0;
     DLWP_CUDA(cudaGetDevice(&dev));
     DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DLWP_CUDA(cudaFuncSetAttribute(fno_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LayerSmem::Total));
+    DLWP_CUDA(cudaFuncSetAttribute(fno_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLayerSmemMax));
   }
+  const LayerSmem L(a.g.KZ);
+  DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
-  fno_layer_kernel<<<grid, kCta, LayerSmem::Total, st>>>(a);
+  fno_layer_kernel<<<grid, kCta, L.Total, st>>>(a);
   DLWP_LAUNCHED("fno_layer_kernel");
   return DLWP_OK;
 }

@@ -12,7 +12,8 @@
 //   fno_lift_kernel    gather x_t from the NCHW sources (fno.py:49-62) -> lifting MLP
 //                      (1x1 conv, GELU, 1x1 conv; hidden stays in TMEM/SMEM) -> tile image
 //                      + forward truncated W-DFT of the result (a third MMA on the same tile)
-//   [H-DFT, per-mode mixing, inverse H-DFT on the retained columns: kernels_fp32.cu]
+//   fno_mid_kernel     H-DFT, per-mode channel mixing, inverse H-DFT on the retained columns
+//                      (fp32 FMA, weights in registers) -> split-bf16 operand image of Z
 //   fno_layer_kernel   inverse truncated W-DFT GEMM K-concatenated with the 1x1 skip conv,
 //                      + bias, GELU -> tile image + forward W-DFT for the next layer
 //   fno_proj_kernel    projection MLP + residual on the last context frame -> NCHW output
@@ -33,6 +34,7 @@ struct TcGeom {
   int RT;              // grid rows per tile = 128 / W
   int KXP;             // padded real columns per grid row = 32 / RT  (2 * Kc <= KXP)
   int Kc;              // retained half-spectrum columns
+  int KZ;              // K extent of the inverse W-DFT operands: 8 per retained column, padded to 16
 };
 
 struct TcLiftArgs {
@@ -53,9 +55,9 @@ struct TcLayerArgs {
   TcGeom g;
   const uint8_t* x_img;
   uint8_t* y_img;
-  const float2* Z;        // [B*H, Kc, 32] spectrum after the inverse H-DFT
+  const uint8_t* Zimg;    // per tile: split-bf16 operand image of the spectrum after the inverse H-DFT (tc_mid.cu)
   float2* Aout;           // forward W-DFT of the output, or null (last layer)
-  const uint8_t* Gimg;    // inverse W-DFT operand [hi | lo] images, R = 128, K = 32
+  const uint8_t* Gimg;    // inverse W-DFT operand [hi | lo] images, R = 128, K = KZ
   const uint8_t* Fimg;
   const uint8_t* Wsimg;   // skip conv [hi | lo] images, R = 32, K = 32
   const float* bias;      // [32] spectral-conv bias of this layer
@@ -76,6 +78,19 @@ struct TcProjArgs {
   const float* last;      // residual frame or null
   long long last_bstride;
 };
+
+// H-DFT, per-mode channel mixing and inverse H-DFT on the retained columns (tc_mid.cu)
+constexpr int kTcMidSamples = 4;   // samples one CTA pass works on
+struct TcMidArgs {
+  const float2* A;        // [B*H, Kc, 32] forward W-DFT of the layer input
+  const float2* Wm;       // [R, Kc, 32, 32] mode-major spectral weights of the layer
+  const float2* Fh;       // [R, H] forward H-DFT rows
+  const float2* Gh;       // [H, R] inverse H-DFT columns
+  uint8_t* Zimg;          // [B*H/RT] operand images of KZ * 128 bytes
+  int B, H, R, Kc, RT, KZ;
+};
+size_t tc_mid_smem_bytes(int H, int R);
+int launch_tc_mid(const TcMidArgs& a, cudaStream_t st);
 
 int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st);
 int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st);

@@ -1,0 +1,238 @@
+// fno_mid_kernel: everything a spectral layer does on the retained columns, in one launch:
+//   X[b, r, kx, i] = sum_h  Fh[r, h] * A[b, h, kx, i]            forward truncated DFT along H
+//   Y[b, r, kx, o] = sum_i  X[b, r, kx, i] * W[i, o, r, kx]      einsum("bixy,ioxy->boxy"), unet.py:15-17
+//   Z[b, h, kx, o] = sum_r  Gh[h, r] * Y[b, r, kx, o]            inverse DFT along H
+// A is what the forward W-DFT of the lift / layer kernels left in HBM ([B*H, Kc, 32] complex);
+// Z leaves as the split-bf16 operand image the next fno_layer_kernel feeds to tcgen05.mma
+// without touching it (layout below).  fp32 FMA arithmetic: 3 x 12 k complex MACs per (sample,
+// column) is 0.26 GFMA per layer at the reference sizes -- far below the cost of staging these
+// skinny products for the tensor cores.
+//
+// Work split: CTA = one retained column kx x a strided set of sample quads; warp r of the CTA
+// keeps W[:, :, r, kx] (32 x 32 complex, this lane's output channel) in REGISTERS for the
+// whole launch, so the per-mode weights are read from L2 exactly once per CTA.  Per quad:
+//   phase 1  item = (sample, 4 rows r): lane = input channel; A rows stream from shared memory
+//            (bulk-copied, double buffered), Fh is read as warp-broadcast 16-byte loads
+//   phase 2  warp r: lane = output channel; X is read as warp-broadcast 16-byte loads
+//   phase 3  item = (sample, 8 grid rows h): lane = output channel; split to bf16 hi / lo and
+//            stored as 16-byte chunks, 512 contiguous bytes per warp store
+//
+// Z operand image of one 128-pixel tile (RT grid rows), K index k = kx * 8 + h2 * 2 + (re | im):
+//   byte offset = part * (KZ * 64) + kx * 512 + c * 16 + (h2 * 2 + reim) * 2,   part 0 = hi, 1 = lo
+// i.e. the chunk-major [32 rows = channels] x [KZ] K-major UMMA operand of tc_common.cuh; every
+// retained column owns one 8-wide K chunk (slots >= 2 * RT stay zero).
+#include "tc_common.cuh"
+#include "tc_fno.cuh"
+
+namespace dlwp {
+
+using namespace tc;
+
+namespace {
+
+constexpr int kNB = kTcMidSamples;   // samples per pass
+
+__device__ __forceinline__ void cmac(float2& acc, float gx, float gy, float2 v) {
+  acc.x = fmaf(gx, v.x, acc.x);
+  acc.x = fmaf(-gy, v.y, acc.x);
+  acc.y = fmaf(gx, v.y, acc.y);
+  acc.y = fmaf(gy, v.x, acc.y);
+}
+
+template <int RT>
+__global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint64_t bars[2];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
+  const int H = a.H, R = a.R, Rp = (R + 3) & ~3, Kc = a.Kc, B = a.B;
+  const int kx = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
+  const int nquads = (B + kNB - 1) / kNB;
+
+  float2* sA = reinterpret_cast<float2*>(smem);            // [2][kNB][H][32]
+  float2* sX = sA + 2 * kNB * H * 32;                       // [kNB][Rp][32]
+  float2* sY = sX + kNB * Rp * 32;                          // [kNB][R][32]
+  float2* sF = sY + kNB * R * 32;                           // [H][Rp]   Fh transposed, pad rows zero
+  float2* sG = sF + H * Rp;                                 // [R][H]    Gh transposed
+
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+  }
+  for (int i = tid; i < H * Rp; i += blockDim.x) {
+    const int h = i / Rp, r = i - h * Rp;
+    sF[i] = r < R ? a.Fh[r * H + h] : make_float2(0.f, 0.f);
+  }
+  for (int i = tid; i < R * H; i += blockDim.x) {
+    const int r = i / H, h = i - r * H;
+    sG[i] = a.Gh[h * R + r];
+  }
+  // this thread's slice of the mode weights: W[r = warp, kx, i, o = lane]
+  float2 w[32];
+  if (warp < R) {
+    const float2* wp = a.Wm + ((size_t)(warp * Kc + kx) * 32) * 32 + lane;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) w[i] = wp[i * 32];
+  }
+  __syncthreads();
+
+  auto issue_load = [&](int q, int s) {   // warp 0: rows of quad q -> stage s
+    const int b0 = q * kNB;
+    const int nb = B - b0 < kNB ? B - b0 : kNB;
+    if (lane == 0) mbar_arrive_expect_tx(&bars[s], (uint32_t)(nb * H * 256));
+    __syncwarp();
+    for (int i = lane; i < nb * H; i += 32) {
+      const int bl = i / H, h = i - bl * H;
+      bulk_g2s(sA + ((s * kNB + bl) * H + h) * 32, a.A + ((size_t)((b0 + bl) * H + h) * Kc + kx) * 32, 256, &bars[s]);
+    }
+  };
+
+  if (warp == 0 && chunk < nquads) issue_load(chunk, 0);
+  uint32_t p = 0;
+  for (int q = chunk; q < nquads; q += nchunks, ++p) {
+    const int s = p & 1;
+    if (warp == 0 && q + nchunks < nquads) issue_load(q + nchunks, s ^ 1);
+    mbar_wait(&bars[s], (p >> 1) & 1u);
+
+    // ---- phase 1: forward H-DFT, 4 retained rows per item ----
+    const int ngrp = Rp >> 2;
+    for (int item = warp; item < kNB * ngrp; item += nw) {
+      const int bl = item / ngrp, rg = item - bl * ngrp;
+      const float2* Ab = sA + (s * kNB + bl) * H * 32 + lane;
+      const float4* F4 = reinterpret_cast<const float4*>(sF) + rg * 2;
+      float2 acc[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[j] = make_float2(0.f, 0.f);
+#pragma unroll 4
+      for (int h = 0; h < H; ++h) {
+        const float2 v = Ab[h * 32];
+        const float4 f01 = F4[h * (Rp >> 1)], f23 = F4[h * (Rp >> 1) + 1];
+        cmac(acc[0], f01.x, f01.y, v);
+        cmac(acc[1], f01.z, f01.w, v);
+        cmac(acc[2], f23.x, f23.y, v);
+        cmac(acc[3], f23.z, f23.w, v);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sX[(bl * Rp + rg * 4 + j) * 32 + lane] = acc[j];
+    }
+    __syncthreads();
+
+    // ---- phase 2: per-mode channel mixing with the register-resident weights ----
+    if (warp < R) {
+#pragma unroll
+      for (int bl = 0; bl < kNB; ++bl) {
+        const float4* X4 = reinterpret_cast<const float4*>(sX + (bl * Rp + warp) * 32);
+        float2 y = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int i2 = 0; i2 < 16; ++i2) {
+          const float4 x = X4[i2];
+          cmac(y, x.x, x.y, w[2 * i2]);
+          cmac(y, x.z, x.w, w[2 * i2 + 1]);
+        }
+        sY[(bl * R + warp) * 32 + lane] = y;
+      }
+    }
+    __syncthreads();
+
+    // ---- phase 3: inverse H-DFT, 8 grid rows per item, split-bf16 operand image out ----
+    const int nhg = H >> 3;
+    for (int item = warp; item < kNB * nhg; item += nw) {
+      const int bl = item / nhg, hg = item - bl * nhg;
+      const int b = q * kNB + bl;
+      if (b >= B) continue;
+      const float2* Yb = sY + bl * R * 32 + lane;
+      float2 z[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) z[j] = make_float2(0.f, 0.f);
+      for (int r = 0; r < R; ++r) {
+        const float2 y = Yb[r * 32];
+        const float4* G4 = reinterpret_cast<const float4*>(sG + r * H + hg * 8);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float4 g = G4[j];
+          cmac(z[2 * j], g.x, g.y, y);
+          cmac(z[2 * j + 1], g.z, g.w, y);
+        }
+      }
+      uint32_t hi[8], lo[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) split2(z[j].x, z[j].y, hi[j], lo[j]);
+      const size_t tile0 = ((size_t)b * H + hg * 8) / RT;
+      const size_t part = (size_t)a.KZ * 64;
+      uint8_t* dst = a.Zimg + tile0 * (2 * part) + (size_t)kx * 512 + lane * 16;
+#pragma unroll
+      for (int t = 0; t < 8 / RT; ++t) {
+        uint4 ch, cl;
+        if (RT == 1) {
+          ch = make_uint4(hi[t], 0u, 0u, 0u);
+          cl = make_uint4(lo[t], 0u, 0u, 0u);
+        } else if (RT == 2) {
+          ch = make_uint4(hi[2 * t], hi[2 * t + 1], 0u, 0u);
+          cl = make_uint4(lo[2 * t], lo[2 * t + 1], 0u, 0u);
+        } else {
+          ch = make_uint4(hi[4 * t], hi[4 * t + 1], hi[4 * t + 2], hi[4 * t + 3]);
+          cl = make_uint4(lo[4 * t], lo[4 * t + 1], lo[4 * t + 2], lo[4 * t + 3]);
+        }
+        *reinterpret_cast<uint4*>(dst + (size_t)t * (2 * part)) = ch;
+        *reinterpret_cast<uint4*>(dst + (size_t)t * (2 * part) + part) = cl;
+      }
+    }
+    // no barrier here: the next pass writes sX only after every warp left phase 2 (second
+    // __syncthreads above) and sY only after the next pass's first __syncthreads
+  }
+}
+
+}  // namespace
+
+size_t tc_mid_smem_bytes(int H, int R) {
+  const int Rp = (R + 3) & ~3;
+  return (size_t)(2 * kNB * H * 32 + kNB * Rp * 32 + kNB * R * 32 + H * Rp + R * H) * sizeof(float2);
+}
+
+int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
+  static int sms = 0;
+  static size_t smem_set[3] = {0, 0, 0};
+  if (!sms) {
+    int dev = 0;
+    DLWP_CUDA(cudaGetDevice(&dev));
+    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  DLWP_REQUIRE(a.R >= 1 && a.R <= 16 && a.H % 8 == 0 && a.Kc >= 1, "fno_mid_kernel: unsupported geometry R=%d H=%d", a.R, a.H);
+  const size_t smem = tc_mid_smem_bytes(a.H, a.R);
+  DLWP_REQUIRE(smem <= 220 * 1024, "fno_mid_kernel: %zu bytes of shared memory needed", smem);
+  const int nquads = (a.B + kNB - 1) / kNB;
+  int nchunks = sms / a.Kc;
+  if (nchunks < 1) nchunks = 1;
+  if (nchunks > nquads) nchunks = nquads;
+  // every CTA runs ceil(nquads / nchunks) passes at most: do not use more CTAs than that needs
+  const int passes = (nquads + nchunks - 1) / nchunks;
+  nchunks = (nquads + passes - 1) / passes;
+  const dim3 grid((unsigned)a.Kc, (unsigned)nchunks);
+  const int threads = 32 * (a.R < 4 ? 4 : a.R);
+  const int slot = a.RT == 1 ? 0 : (a.RT == 2 ? 1 : 2);
+  auto set_smem = [&](auto kern) -> cudaError_t {
+    if (smem_set[slot] >= smem) return cudaSuccess;
+    smem_set[slot] = smem;
+    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  };
+  switch (a.RT) {
+    case 1:
+      DLWP_CUDA(set_smem(fno_mid_kernel<1>));
+      fno_mid_kernel<1><<<grid, threads, smem, st>>>(a);
+      break;
+    case 2:
+      DLWP_CUDA(set_smem(fno_mid_kernel<2>));
+      fno_mid_kernel<2><<<grid, threads, smem, st>>>(a);
+      break;
+    case 4:
+      DLWP_CUDA(set_smem(fno_mid_kernel<4>));
+      fno_mid_kernel<4><<<grid, threads, smem, st>>>(a);
+      break;
+    default:
+      return fail(DLWP_ERR_INVALID, "fno_mid_kernel: %d grid rows per tile", a.RT);
+  }
+  DLWP_LAUNCHED("fno_mid_kernel");
+  return DLWP_OK;
+}
+
+}  // namespace dlwp

@@ -24,18 +24,23 @@ int plan_tc_build(dlwp_plan* p) {
       (d.projection_channels != 128 && d.projection_channels != 256))
     return DLWP_OK;
   if (p->Cin < 1 || p->Cin > 15 || d.prognostic_channels > 16) return DLWP_OK;
+  // fno_mid_kernel: one warp per retained row, 8 grid rows per output item; the layer kernel's
+  // inverse W-DFT operands (8 K slots per retained column) must fit beside its tile buffers
+  const int KZ = (8 * Kc + 15) & ~15;
+  if (d.n_rows > 16 || H % 8 != 0 || KZ > 96 || tc_mid_smem_bytes(H, d.n_rows) > 220 * 1024) return DLWP_OK;
 
-  p->tcg = TcGeom{0, H * W, W, RT, KXP, Kc};
+  p->tcg = TcGeom{0, H * W, W, RT, KXP, Kc, KZ};
   double s = 1.0, t = 1.0;
   const double hw = (double)H * (double)W;
   if (d.fft_norm == DLWP_FFT_NORM_BACKWARD) t = 1.0 / hw;
   else if (d.fft_norm == DLWP_FFT_NORM_FORWARD) s = 1.0 / hw;
   else s = t = 1.0 / std::sqrt(hw);
 
-  // inverse W-DFT operand G'[(h2, w), (h2', kx')]: y[w] = sum_kx Re(Gw[w, kx] * Z[kx]) with
-  // Gw = t * c_kx * exp(+2 pi i kx w / W) (c = 1 for the self-conjugate columns, else 2);
+  // inverse W-DFT operand G'[(h2, w), (kx, h2', re|im)]: y[w] = sum_kx Re(Gw[w, kx] * Z[kx]) with
+  // Gw = t * c_kx * exp(+2 pi i kx w / W) (c = 1 for the self-conjugate columns, else 2), K index
+  // kx * 8 + h2' * 2 + (re|im) as fno_mid_kernel lays Z' out;
   // forward operand F''[(h2, kx'), (h2', w)] with Fw = s * exp(-2 pi i kx w / W)
-  std::vector<double> G((size_t)128 * 32, 0.0), F((size_t)32 * 128, 0.0);
+  std::vector<double> G((size_t)128 * KZ, 0.0), F((size_t)32 * 128, 0.0);
   for (int h2 = 0; h2 < RT; ++h2)
     for (int w = 0; w < W; ++w)
       for (int kx = 0; kx < Kc; ++kx) {
@@ -43,14 +48,14 @@ int plan_tc_build(dlwp_plan* p) {
         const double ang = 2.0 * M_PI * (double)r / (double)W;
         const bool self_conj = (kx == 0) || (W % 2 == 0 && kx == W / 2);
         const double ck = t * (self_conj ? 1.0 : 2.0);
-        const int m = h2 * W + w, k = h2 * KXP + 2 * kx;
-        G[(size_t)m * 32 + k] = ck * std::cos(ang);
-        G[(size_t)m * 32 + k + 1] = -ck * std::sin(ang);
+        const int m = h2 * W + w, k = h2 * KXP + 2 * kx, kz = kx * 8 + h2 * 2;
+        G[(size_t)m * KZ + kz] = ck * std::cos(ang);
+        G[(size_t)m * KZ + kz + 1] = -ck * std::sin(ang);
         F[(size_t)k * 128 + m] = s * std::cos(ang);
         F[(size_t)(k + 1) * 128 + m] = -s * std::sin(ang);
       }
-  std::vector<uint8_t> gi(2 * kTcImgBytes), fi(64 * 128 * 2);
-  tc_pack_images_f64(G.data(), 128, 32, 32, 128, 32, gi.data());
+  std::vector<uint8_t> gi((size_t)2 * 128 * KZ * 2), fi(64 * 128 * 2);
+  tc_pack_images_f64(G.data(), 128, KZ, KZ, 128, KZ, gi.data());
   tc_pack_stacked_f64(F.data(), 32, 128, 128, 64, 128, fi.data());
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_G, gi.size()));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_F, fi.size()));
@@ -60,6 +65,11 @@ int plan_tc_build(dlwp_plan* p) {
   const size_t img = (size_t)d.max_batch * H * W * kTcC * 4;
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_img[0], img));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_img[1], img));
+  // Z' operand images: fno_mid_kernel writes whole 16-byte chunks of the retained columns; the
+  // chunks that pad K to a multiple of 16 stay zero from here on
+  const size_t zimg = (size_t)d.max_batch * H * W / kTcTile * KZ * 128;
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_Z, zimg));
+  DLWP_CUDA(cudaMemset(p->tc_Z, 0, zimg));
   const int L = d.lifting_channels, Pj = d.projection_channels;
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_liftW1, (size_t)L * 16 * 4));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_liftW2, (size_t)32 * L * 4));
@@ -156,26 +166,17 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
 
   int cur = 0;
   for (int l = 0; l < N; ++l) {
-    // H-DFT on the retained columns, per-mode channel mixing, inverse H-DFT (fp32 FMA kernels)
-    TdftArgs a{};
-    a.in = p->specA; a.out = p->specX; a.T = p->Fh; a.N = H; a.K = R; a.C = C; a.nb0 = B; a.nb1 = Kc;
-    a.in_sn = (long long)Kc * C; a.in_sb0 = (long long)H * Kc * C; a.in_sb1 = C;
-    a.out_sk = (long long)Kc * B * C; a.out_sb0 = C; a.out_sb1 = (long long)B * C;
-    a.in_complex = true; a.out_complex = true;
-    DLWP_TRY(launch_tdft(a, st));
-    DLWP_TRY(launch_mix_dense(p->specX, p->wm[l], p->specY, R * Kc, B, C, C, st));
-    a = TdftArgs{};
-    a.in = p->specY; a.out = p->specZ; a.T = p->Gh; a.N = R; a.K = H; a.C = C; a.nb0 = B; a.nb1 = Kc;
-    a.in_sn = (long long)Kc * B * C; a.in_sb0 = C; a.in_sb1 = (long long)B * C;
-    a.out_sk = (long long)Kc * C; a.out_sb0 = (long long)H * Kc * C; a.out_sb1 = C;
-    a.in_complex = true; a.out_complex = true;
-    DLWP_TRY(launch_tdft(a, st));
+    // H-DFT on the retained columns, per-mode channel mixing, inverse H-DFT -> Z' operand images
+    TcMidArgs ma{};
+    ma.A = p->specA; ma.Wm = p->wm[l]; ma.Fh = p->Fh; ma.Gh = p->Gh; ma.Zimg = p->tc_Z;
+    ma.B = B; ma.H = H; ma.R = R; ma.Kc = Kc; ma.RT = g.RT; ma.KZ = g.KZ;
+    DLWP_TRY(launch_tc_mid(ma, st));
 
     TcLayerArgs ya{};
     ya.g = g;
     ya.x_img = p->tc_img[cur];
     ya.y_img = p->tc_img[cur ^ 1];
-    ya.Z = p->specZ;
+    ya.Zimg = p->tc_Z;
     ya.Aout = l < N - 1 ? p->specA : nullptr;
     ya.Gimg = p->tc_G;
     ya.Fimg = p->tc_F;

@@ -29,7 +29,8 @@ class _NativeRollout(nn.Module):
     """Base: lazily builds a native plan per (device, H, W), re-uploads weights when any
     parameter changed, and runs the rollout on torch's current stream."""
 
-    precision = native.PREC_FP32
+    # split-bf16 tcgen05 kernels where the shape is covered (fp32-parity: <= 1e-4), fp32 FMA kernels elsewhere
+    precision = native.PREC_FP32_TC
 
     def _init_native(self):
         self._plans = {}

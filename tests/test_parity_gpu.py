@@ -108,6 +108,7 @@ def _fno_pair(pkg, case):
     ref = getattr(owrap, cls)(**kw).eval()
     mod = getattr(pkg, cls)(**kw).cuda().eval()
     mod.load_state_dict(ref.state_dict(), strict=True)
+    mod.precision = pkg.native.PREC_FP32          # the fp32 FMA kernel set; the tensor-core tests override this
     return ref, mod, kw, (B, H, W)
 
 
