@@ -16,8 +16,7 @@ constexpr int kTileBytes = 2 * kImg;         // hi + lo
 constexpr int kLboXT = 528;                  // chunk stride of the transposed tile: 512 + 16 keeps the
                                              // 4-byte transposing stores of a warp on 32 distinct banks
 constexpr int kXTBytes = 16 * kLboXT;        // one bf16 part of the [32 ch x 128 px] transposed tile
-constexpr int kStageLd = 33;
-constexpr int kStageBytes = 2 * 32 * kStageLd * 4;
+constexpr int kFBytes = 2 * 64 * 128 * 2;     // forward W-DFT operand: [hi | lo] images of 64 rows x 128 pixels
 
 // exact-erf GELU (F.gelu default) through Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7):
 // two MUFU ops and ~13 FMA-pipe ops per element instead of erff's branches
@@ -101,13 +100,41 @@ __device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1
 
 // ---- common tail of the lift and layer epilogues ------------------------------------------------
 // v[32] = the 32 output channels of this thread's pixel (tile row t).  Writes the tile image to
-// HBM and, when `Aout` is set, hands the transposed tile to the control warp, which runs the
-// forward truncated W-DFT as one more M=64 UMMA
-//   D3[(part, h2, kx'), c] = sum_{px} F''[(part, h2, kx'), px] * v[px, c];
-// the result is folded (hi + lo rows) through `stage` (aliases the transposed tile) into Aout.
-__device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int w, int tile, const TcGeom& g,
-                                            uint8_t* y_img, float2* Aout, uint8_t* sXT, uint32_t tmem_d3,
-                                            uint64_t* xt_full, uint64_t* d3_full, uint32_t& n3) {
+// HBM and, when `Aout` is set, hands the transposed tile to the control lane, which runs the
+// forward truncated W-DFT as M=64 UMMAs
+//   D3[(h2, kx', re|im), c] = sum_{px} F''[(h2, kx', re|im), px] * v[px, c]      (rows 32..63 are padding).
+// The accumulator of tile u is drained (drain_d3) while tile u + 1 is in the epilogue, so the
+// UMMA round trip is never waited for: rows (Re | Im of one retained column of one grid row)
+// go straight from TMEM lanes to their 128-byte rows of the planar spectrum
+//   Aout[b][kx][h][re|im][32 channels]  (fp32; what fno_mid_kernel bulk-copies per sample).
+__device__ __forceinline__ void drain_d3(int t, int tile, const TcGeom& g, float* Aout, uint32_t tmem_d3,
+                                         uint64_t* d3_full, uint32_t n) {
+  mbar_wait(d3_full, n & 1u);
+  tc_fence_after();
+  const int q4 = t >> 5, lane = t & 31;
+  if (q4 < 2) {   // an M=64 accumulator keeps row r in TMEM lane 32 * (r / 16) + r % 16
+    uint32_t r[32];
+    tmem_ld32(tmem_d3 + ((uint32_t)(q4 * 32) << 16), r);
+    tmem_ld_wait();
+    const int row = q4 * 16 + lane;
+    const int h2 = row / g.KXP, rem = row - h2 * g.KXP, kx = rem >> 1, reim = rem & 1;
+    if (lane < 16 && h2 < g.RT && kx < g.Kc) {
+      const int grow = tile * g.RT + h2;
+      const int b = grow / g.H, h = grow - b * g.H;
+      float4* dst = reinterpret_cast<float4*>(Aout + ((((size_t)b * g.Kc + kx) * g.H + h) * 2 + reim) * 32);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                             __uint_as_float(r[4 * j + 3]));
+    }
+  }
+  tc_fence_before();
+}
+
+// n3 counts the tiles this worker has handed to the forward W-DFT; prev_tile is the last one
+__device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int tile, const TcGeom& g, uint8_t* y_img,
+                                            float* Aout, uint8_t* sXT, uint32_t tmem_d3, uint64_t* xt_full,
+                                            uint64_t* d3_full, uint32_t& n3, int& prev_tile) {
   {
     uint32_t hi[16], lo[16];
 #pragma unroll
@@ -121,6 +148,8 @@ __device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int w, 
     }
   }
   if (Aout == nullptr) return;
+  // the previous tile's W-DFT must have left the transposed-tile buffer and the accumulator
+  if (n3 > 0) drain_d3(t, prev_tile, g, Aout, tmem_d3, d3_full, n3 - 1);
 
   // transposed tile [channel][pixel]: lanes pair up so that each store holds two adjacent pixels
   const int odd = t & 1, me = t & ~1;
@@ -140,46 +169,24 @@ __device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int w, 
   fence_async_smem();
   tc_fence_before();
   mbar_arrive(xt_full);
-  mbar_wait(d3_full, n3 & 1u);
   ++n3;
-  tc_fence_after();
-
-  // an M=64 accumulator keeps row r in TMEM lane 32 * (r / 16) + r % 16: warp q holds rows 16q..16q+15
-  const int q4 = (t >> 5), lane = t & 31;
-  float* stage = reinterpret_cast<float*>(sXT);
-  uint32_t r[32];
-  tmem_ld32(tmem_d3 + ((uint32_t)(q4 * 32) << 16), r);
-  tmem_ld_wait();
-  if (lane < 16) {
-    float* s = stage + ((q4 >> 1) * 32 + (q4 & 1) * 16 + lane) * kStageLd;
-#pragma unroll
-    for (int c = 0; c < 32; ++c) s[c] = __uint_as_float(r[c]);
-  }
-  bar_sync(1 + w, kEpi);
-  const int n = g.RT * g.Kc * 32;
-  for (int e = t; e < n; e += kEpi) {
-    const int c = e & 31, q = e >> 5;
-    const int kx = q % g.Kc, h2 = q / g.Kc;
-    const int idx = h2 * g.KXP + 2 * kx;
-    const float re = stage[idx * kStageLd + c] + stage[(32 + idx) * kStageLd + c];
-    const float im = stage[(idx + 1) * kStageLd + c] + stage[(33 + idx) * kStageLd + c];
-    Aout[((size_t)(tile * g.RT + h2) * g.Kc + kx) * 32 + c] = make_float2(re, im);
-  }
-  bar_sync(1 + w, kEpi);    // stage (= transposed-tile storage) is free again
+  prev_tile = tile;
 }
 
-// control warp, one lane: forward W-DFT UMMAs of one tile
+// control lane: forward W-DFT UMMAs of the n-th tile handed over (hi*hi, lo*hi, hi*lo)
 __device__ __forceinline__ void issue_fwd_dft(uint32_t aF, uint32_t aXT, uint32_t tmem_d3, uint64_t* xt_full,
-                                              uint64_t* d3_full, uint32_t n3) {
-  mbar_wait(xt_full, n3 & 1u);
+                                              uint64_t* d3_full, uint32_t n) {
+  mbar_wait(xt_full, n & 1u);
   tc_fence_after();
   const uint32_t idesc = idesc_bf16(64, 32);
 #pragma unroll
-  for (int part = 0; part < 2; ++part)
+  for (int term = 0; term < 3; ++term) {
+    const uint32_t fa = term == 1 ? 64u * 128u * 2u : 0u, xp = term == 2 ? (uint32_t)kXTBytes : 0u;
 #pragma unroll
     for (int k0 = 0; k0 < 128; k0 += 16)
-      umma_bf16(tmem_d3, chunk_desc(aF, 64, k0), smem_desc(aXT + part * kXTBytes + (k0 >> 3) * kLboXT, kLboXT, 128), idesc,
-                (part | k0) != 0);
+      umma_bf16(tmem_d3, chunk_desc(aF + fa, 64, k0), smem_desc(aXT + xp + (k0 >> 3) * kLboXT, kLboXT, 128), idesc,
+                (term | k0) != 0);
+  }
   umma_commit(d3_full);
 }
 
@@ -199,7 +206,7 @@ struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
   __host__ __device__ explicit LayerSmem(int KZ) {
     G = 0;
     F = G + 2 * 128 * KZ * 2;
-    Ws = F + 64 * 128 * 2;
+    Ws = F + kFBytes;
     Bias = Ws + 4096;
     Worker = Bias + 128;
     X = 0;
@@ -248,9 +255,9 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
   tc_fence_after();
   const uint32_t g_bytes = 2u * 128u * (uint32_t)g.KZ * 2u, z_bytes = (uint32_t)g.KZ * 128u;
   if (tid == 0) {
-    mbar_arrive_expect_tx(bar_const, g_bytes + 64 * 128 * 2 + 4096);
+    mbar_arrive_expect_tx(bar_const, g_bytes + kFBytes + 4096);
     bulk_g2s(smem + L.G, a.Gimg, g_bytes, bar_const);
-    bulk_g2s(smem + L.F, a.Fimg, 64 * 128 * 2, bar_const);
+    bulk_g2s(smem + L.F, a.Fimg, kFBytes, bar_const);
     bulk_g2s(smem + L.Ws, a.Wsimg, 4096, bar_const);
   }
   const int stride = gridDim.x * 2;
@@ -279,8 +286,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
       mbar_wait(bar_const, 0);
       const uint32_t idesc = idesc_bf16(128, 32);
       const uint32_t g_lo = 128u * (uint32_t)g.KZ * 2u, z_lo = (uint32_t)g.KZ * 64u;
-      uint32_t u = 0;
-      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+      auto main_mma = [&](uint32_t u) {
         const int s = u & 1;
         mbar_wait(&b[LB_XFULL + s], full_par(u));
         mbar_wait(&b[LB_DEMPTY + s], empty_par(u));
@@ -301,6 +307,13 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
             umma_bf16(d, chunk_desc(aX + xa, 128, k0), chunk_desc(aW + wb, 32, k0), idesc, 1);
         }
         umma_commit(&b[LB_DFULL + s]);
+      };
+      // the main UMMAs run one tile ahead of the epilogue group; the forward W-DFT of tile u is
+      // issued when the group has handed over its transposed tile
+      if (first < g.ntiles) main_mma(0);
+      uint32_t u = 0;
+      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+        if (tile + stride < g.ntiles) main_mma(u + 1);
         if (tile + 2 * stride < g.ntiles) load_inputs(tile + 2 * stride, u + 2);
         if (a.Aout != nullptr) issue_fwd_dft(aF, aXT, tmem + 64, &b[LB_XTFULL], &b[LB_D3FULL], u);
       }
@@ -312,6 +325,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
     uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
     const uint32_t tmem = tmem_s + 256u * w + ((uint32_t)(q4 * 32) << 16);
     uint32_t u = 0, n3 = 0;
+    int prev_tile = 0;
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       mbar_wait(&b[LB_DFULL + s], full_par(u));
@@ -329,9 +343,10 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
           v[c] = a.gelu ? gelu_fast(x) : x;
         }
       }
-      finish_tile(v, t, w, tile, g, a.y_img, a.Aout, ws + L.XT, tmem_s + 256u * w + 64, &b[LB_XTFULL],
-                  &b[LB_D3FULL], n3);
+      finish_tile(v, t, tile, g, a.y_img, a.Aout, ws + L.XT, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], n3,
+                  prev_tile);
     }
+    if (n3 > 0) drain_d3(t, prev_tile, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3 - 1);
   }
   tc_fence_before();
   __syncthreads();
@@ -619,11 +634,11 @@ int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
 // fno_lift_kernel: x_t gathered from the NCHW sources -> lifting MLP -> tile image + W-DFT
 // =============================================================================================
 namespace {
-struct LiftSmem {   // sized for hid = 256; the transposed tile / stage reuse the A2 buffers
-  static constexpr int W1 = 0, W2 = W1 + 256 * 16 * 4, F = W2 + 32 * 256 * 4, B2 = F + 64 * 128 * 2, Worker = B2 + 128;
-  static constexpr int A1 = 0, A2 = A1 + 2 * 8192, XT = A2, WorkerBytes = A2 + 2 * kTileBytes;
+struct LiftSmem {   // sized for hid = 256
+  static constexpr int W1 = 0, W2 = W1 + 256 * 16 * 4, F = W2 + 32 * 256 * 4, B2 = F + kFBytes, Worker = B2 + 128;
+  static constexpr int A1 = 0, A2 = A1 + 2 * 8192, XT = A2 + 2 * kTileBytes, WorkerBytes = XT + 2 * kXTBytes;
   static constexpr int Total = Worker + 2 * WorkerBytes;
-  static_assert(2 * kXTBytes <= 2 * kTileBytes, "transposed tile must fit in the A2 buffers");
+  static_assert(Total <= 226 * 1024, "lift kernel shared memory");
 };
 }  // namespace
 
@@ -665,10 +680,10 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   tc_fence_after();
   const uint32_t w1_bytes = (uint32_t)hid * 16 * 4, w2_bytes = 32u * hid * 4;
   if (tid == 0) {
-    mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + 64 * 128 * 2);
+    mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + kFBytes);
     bulk_g2s(smem + LiftSmem::W1, a.W1img, w1_bytes, bar_const);
     bulk_g2s(smem + LiftSmem::W2, a.W2img, w2_bytes, bar_const);
-    bulk_g2s(smem + LiftSmem::F, a.Fimg, 64 * 128 * 2, bar_const);
+    bulk_g2s(smem + LiftSmem::F, a.Fimg, kFBytes, bar_const);
   }
   const int stride = gridDim.x * 2;
 
@@ -732,6 +747,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       store_a1(0, nx);
     }
     uint32_t u = 0, gp = 0, nc = 0, n3 = 0;
+    int prev_tile = 0;
     for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
       const bool has_next = tile + stride < g.ntiles;
       if (has_next) gather(tile + stride, nx);      // loads in flight while the first pass is processed
@@ -750,8 +766,10 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
 #pragma unroll
         for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]) + sB2[c];
       }
-      finish_tile(v, t, w, tile, g, a.y_img, a.Aout, ws + LiftSmem::XT, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], n3);
+      finish_tile(v, t, tile, g, a.y_img, a.Aout, ws + LiftSmem::XT, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], n3,
+                  prev_tile);
     }
+    if (n3 > 0) drain_d3(t, prev_tile, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3 - 1);
   }
   tc_fence_before();
   __syncthreads();

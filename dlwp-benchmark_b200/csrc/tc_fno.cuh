@@ -30,6 +30,7 @@ constexpr int kTcImgBytes = kTcTile * kTcC * 2;   // one bf16 image (hi or lo) o
 struct TcGeom {
   int ntiles;          // B * H * W / 128
   int HW;              // pixels per sample
+  int H;               // grid rows per sample
   int W;               // grid width (128 % W == 0)
   int RT;              // grid rows per tile = 128 / W
   int KXP;             // padded real columns per grid row = 32 / RT  (2 * Kc <= KXP)
@@ -46,9 +47,9 @@ struct TcLiftArgs {
   const uint8_t* W1img;   // [hi | lo] images, R = hid rows, K = 16
   const uint8_t* W2img;   // [hi | lo] images, R = 32 rows, K = hid
   const float* b2;        // [32]
-  const uint8_t* Fimg;    // forward W-DFT operand image, R = 64, K = 128
+  const uint8_t* Fimg;    // forward W-DFT operand [hi | lo] images, R = 64 (32 used), K = 128
   uint8_t* y_img;         // tile images out
-  float2* Aout;           // [B*H, Kc, 32] forward W-DFT of the output
+  float* Aout;            // planar spectrum [B][Kc][H][re|im][32]: forward W-DFT of the output
 };
 
 struct TcLayerArgs {
@@ -56,7 +57,7 @@ struct TcLayerArgs {
   const uint8_t* x_img;
   uint8_t* y_img;
   const uint8_t* Zimg;    // per tile: split-bf16 operand image of the spectrum after the inverse H-DFT (tc_mid.cu)
-  float2* Aout;           // forward W-DFT of the output, or null (last layer)
+  float* Aout;            // forward W-DFT of the output (planar, as above), or null (last layer)
   const uint8_t* Gimg;    // inverse W-DFT operand [hi | lo] images, R = 128, K = KZ
   const uint8_t* Fimg;
   const uint8_t* Wsimg;   // skip conv [hi | lo] images, R = 32, K = 32
@@ -82,7 +83,7 @@ struct TcProjArgs {
 // H-DFT, per-mode channel mixing and inverse H-DFT on the retained columns (tc_mid.cu)
 constexpr int kTcMidSamples = 4;   // samples one CTA pass works on
 struct TcMidArgs {
-  const float2* A;        // [B*H, Kc, 32] forward W-DFT of the layer input
+  const float* A;         // planar spectrum [B][Kc][H][re|im][32]: forward W-DFT of the layer input
   const float2* Wm;       // [R, Kc, 32, 32] mode-major spectral weights of the layer
   const float2* Fh;       // [R, H] forward H-DFT rows
   const float2* Gh;       // [H, R] inverse H-DFT columns

@@ -2,7 +2,8 @@
 //   X[b, r, kx, i] = sum_h  Fh[r, h] * A[b, h, kx, i]            forward truncated DFT along H
 //   Y[b, r, kx, o] = sum_i  X[b, r, kx, i] * W[i, o, r, kx]      einsum("bixy,ioxy->boxy"), unet.py:15-17
 //   Z[b, h, kx, o] = sum_r  Gh[h, r] * Y[b, r, kx, o]            inverse DFT along H
-// A is what the forward W-DFT of the lift / layer kernels left in HBM ([B*H, Kc, 32] complex);
+// A is what the forward W-DFT of the lift / layer kernels left in HBM (planar fp32
+// [B][Kc][H][re|im][32]: one contiguous slab per (sample, column), one bulk copy each);
 // Z leaves as the split-bf16 operand image the next fno_layer_kernel feeds to tcgen05.mma
 // without touching it (layout below).  fp32 FMA arithmetic: 3 x 12 k complex MACs per (sample,
 // column) is 0.26 GFMA per layer at the reference sizes -- far below the cost of staging these
@@ -48,8 +49,8 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   const int kx = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
   const int nquads = (B + kNB - 1) / kNB;
 
-  float2* sA = reinterpret_cast<float2*>(smem);            // [2][kNB][H][32]
-  float2* sX = sA + 2 * kNB * H * 32;                       // [kNB][Rp][32]
+  float* sA = reinterpret_cast<float*>(smem);              // [2][kNB][H][re|im][32]
+  float2* sX = reinterpret_cast<float2*>(smem) + 2 * kNB * H * 32;   // [kNB][Rp][32]
   float2* sY = sX + kNB * Rp * 32;                          // [kNB][R][32]
   float2* sF = sY + kNB * R * 32;                           // [H][Rp]   Fh transposed, pad rows zero
   float2* sG = sF + H * Rp;                                 // [R][H]    Gh transposed
@@ -59,6 +60,18 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     mbar_init(&bars[1], 1);
     fence_mbar_init();
   }
+  __syncthreads();
+  auto issue_load = [&](int q, int s) {   // warp 0: the (sample, kx) slabs of quad q -> stage s
+    const int b0 = q * kNB;
+    const int nb = B - b0 < kNB ? B - b0 : kNB;
+    if (lane == 0) mbar_arrive_expect_tx(&bars[s], (uint32_t)(nb * H * 256));
+    __syncwarp();
+    if (lane < nb)
+      bulk_g2s(sA + (size_t)(s * kNB + lane) * H * 64, a.A + ((size_t)(b0 + lane) * Kc + kx) * H * 64, (uint32_t)(H * 256),
+               &bars[s]);
+  };
+  if (warp == 0 && chunk < nquads) issue_load(chunk, 0);
+
   for (int i = tid; i < H * Rp; i += blockDim.x) {
     const int h = i / Rp, r = i - h * Rp;
     sF[i] = r < R ? a.Fh[r * H + h] : make_float2(0.f, 0.f);
@@ -76,18 +89,6 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   }
   __syncthreads();
 
-  auto issue_load = [&](int q, int s) {   // warp 0: rows of quad q -> stage s
-    const int b0 = q * kNB;
-    const int nb = B - b0 < kNB ? B - b0 : kNB;
-    if (lane == 0) mbar_arrive_expect_tx(&bars[s], (uint32_t)(nb * H * 256));
-    __syncwarp();
-    for (int i = lane; i < nb * H; i += 32) {
-      const int bl = i / H, h = i - bl * H;
-      bulk_g2s(sA + ((s * kNB + bl) * H + h) * 32, a.A + ((size_t)((b0 + bl) * H + h) * Kc + kx) * 32, 256, &bars[s]);
-    }
-  };
-
-  if (warp == 0 && chunk < nquads) issue_load(chunk, 0);
   uint32_t p = 0;
   for (int q = chunk; q < nquads; q += nchunks, ++p) {
     const int s = p & 1;
@@ -98,14 +99,14 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     const int ngrp = Rp >> 2;
     for (int item = warp; item < kNB * ngrp; item += nw) {
       const int bl = item / ngrp, rg = item - bl * ngrp;
-      const float2* Ab = sA + (s * kNB + bl) * H * 32 + lane;
+      const float* Ab = sA + (size_t)(s * kNB + bl) * H * 64 + lane;
       const float4* F4 = reinterpret_cast<const float4*>(sF) + rg * 2;
       float2 acc[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[j] = make_float2(0.f, 0.f);
 #pragma unroll 4
       for (int h = 0; h < H; ++h) {
-        const float2 v = Ab[h * 32];
+        const float2 v = make_float2(Ab[h * 64], Ab[h * 64 + 32]);
         const float4 f01 = F4[h * (Rp >> 1)], f23 = F4[h * (Rp >> 1) + 1];
         cmac(acc[0], f01.x, f01.y, v);
         cmac(acc[1], f01.z, f01.w, v);

@@ -27,9 +27,9 @@ int plan_tc_build(dlwp_plan* p) {
   // fno_mid_kernel: one warp per retained row, 8 grid rows per output item; the layer kernel's
   // inverse W-DFT operands (8 K slots per retained column) must fit beside its tile buffers
   const int KZ = (8 * Kc + 15) & ~15;
-  if (d.n_rows > 16 || H % 8 != 0 || KZ > 96 || tc_mid_smem_bytes(H, d.n_rows) > 220 * 1024) return DLWP_OK;
+  if (d.n_rows > 16 || H % 8 != 0 || KZ > 64 || tc_mid_smem_bytes(H, d.n_rows) > 220 * 1024) return DLWP_OK;
 
-  p->tcg = TcGeom{0, H * W, W, RT, KXP, Kc, KZ};
+  p->tcg = TcGeom{0, H * W, H, W, RT, KXP, Kc, KZ};
   double s = 1.0, t = 1.0;
   const double hw = (double)H * (double)W;
   if (d.fft_norm == DLWP_FFT_NORM_BACKWARD) t = 1.0 / hw;
@@ -54,9 +54,9 @@ int plan_tc_build(dlwp_plan* p) {
         F[(size_t)k * 128 + m] = s * std::cos(ang);
         F[(size_t)(k + 1) * 128 + m] = -s * std::sin(ang);
       }
-  std::vector<uint8_t> gi((size_t)2 * 128 * KZ * 2), fi(64 * 128 * 2);
+  std::vector<uint8_t> gi((size_t)2 * 128 * KZ * 2), fi(2 * 64 * 128 * 2);
   tc_pack_images_f64(G.data(), 128, KZ, KZ, 128, KZ, gi.data());
-  tc_pack_stacked_f64(F.data(), 32, 128, 128, 64, 128, fi.data());
+  tc_pack_images_f64(F.data(), 32, 128, 128, 64, 128, fi.data());
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_G, gi.size()));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_F, fi.size()));
   DLWP_CUDA(cudaMemcpy(p->tc_G, gi.data(), gi.size(), cudaMemcpyHostToDevice));
@@ -161,14 +161,14 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   la.b2 = b2;
   la.Fimg = p->tc_F;
   la.y_img = p->tc_img[0];
-  la.Aout = p->specA;
+  la.Aout = reinterpret_cast<float*>(p->specA);
   DLWP_TRY(launch_tc_lift(la, st));
 
   int cur = 0;
   for (int l = 0; l < N; ++l) {
     // H-DFT on the retained columns, per-mode channel mixing, inverse H-DFT -> Z' operand images
     TcMidArgs ma{};
-    ma.A = p->specA; ma.Wm = p->wm[l]; ma.Fh = p->Fh; ma.Gh = p->Gh; ma.Zimg = p->tc_Z;
+    ma.A = reinterpret_cast<const float*>(p->specA); ma.Wm = p->wm[l]; ma.Fh = p->Fh; ma.Gh = p->Gh; ma.Zimg = p->tc_Z;
     ma.B = B; ma.H = H; ma.R = R; ma.Kc = Kc; ma.RT = g.RT; ma.KZ = g.KZ;
     DLWP_TRY(launch_tc_mid(ma, st));
 
@@ -177,7 +177,7 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
     ya.x_img = p->tc_img[cur];
     ya.y_img = p->tc_img[cur ^ 1];
     ya.Zimg = p->tc_Z;
-    ya.Aout = l < N - 1 ? p->specA : nullptr;
+    ya.Aout = l < N - 1 ? reinterpret_cast<float*>(p->specA) : nullptr;
     ya.Gimg = p->tc_G;
     ya.Fimg = p->tc_F;
     ya.Wsimg = p->tc_skip[l];
