@@ -90,6 +90,9 @@ __device__ __forceinline__ uint64_t chunk_desc(uint32_t saddr, uint32_t R, uint3
 __host__ __device__ constexpr uint32_t idesc_bf16(uint32_t M, uint32_t N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
+// OR into the instruction descriptor when the B operand is MN-major (N contiguous): 8 (k) x 8 (n)
+// core matrices of 8 x 16 bytes; descriptor LBO / SBO then carry the K / N core-matrix strides
+constexpr uint32_t kIdescBMnMajor = 1u << 16;
 // D[tmem] (+)= A[smem] * B[smem]^T, one K=16 slice; issued by ONE thread
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                           uint32_t accumulate) {
@@ -129,6 +132,16 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+
+// bulk async copy shared -> global (bulk_group completion): one thread issues, commits, and waits
+// for the shared-memory reads (`_read`) or for the whole group
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ---- split-bf16 arithmetic ------------------------------------------------------------------
 // v = hi + lo with hi = bf16(v), lo = bf16(v - hi): 16 mantissa bits survive, the products

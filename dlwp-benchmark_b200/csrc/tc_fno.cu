@@ -13,9 +13,6 @@ namespace {
 
 constexpr int kImg = kTcImgBytes;            // 8192: one bf16 part of a [128 x 32] tile
 constexpr int kTileBytes = 2 * kImg;         // hi + lo
-constexpr int kLboXT = 528;                  // chunk stride of the transposed tile: 512 + 16 keeps the
-                                             // 4-byte transposing stores of a warp on 32 distinct banks
-constexpr int kXTBytes = 16 * kLboXT;        // one bf16 part of the [32 ch x 128 px] transposed tile
 constexpr int kFBytes = 2 * 64 * 128 * 2;     // forward W-DFT operand: [hi | lo] images of 64 rows x 128 pixels
 
 // exact-erf GELU (F.gelu default) through Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7):
@@ -99,14 +96,17 @@ __device__ __forceinline__ uint32_t full_par(uint32_t u) { return (u >> 1) & 1u;
 __device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1u) ^ 1u; }
 
 // ---- common tail of the lift and layer epilogues ------------------------------------------------
-// v[32] = the 32 output channels of this thread's pixel (tile row t).  Writes the tile image to
-// HBM and, when `Aout` is set, hands the transposed tile to the control lane, which runs the
-// forward truncated W-DFT as M=64 UMMAs
-//   D3[(h2, kx', re|im), c] = sum_{px} F''[(h2, kx', re|im), px] * v[px, c]      (rows 32..63 are padding).
-// The accumulator of tile u is drained (drain_d3) while tile u + 1 is in the epilogue, so the
-// UMMA round trip is never waited for: rows (Re | Im of one retained column of one grid row)
-// go straight from TMEM lanes to their 128-byte rows of the planar spectrum
-//   Aout[b][kx][h][re|im][32 channels]  (fp32; what fno_mid_kernel bulk-copies per sample).
+// v[32] = the 32 output channels of this thread's pixel (tile row t).  The epilogue group writes
+// the split-bf16 tile image into a shared-memory buffer (same layout as in HBM) and hands it to
+// the control lane (xt_full), which
+//   * stores it to HBM with one bulk copy, and
+//   * when `Aout` is set, runs the forward truncated W-DFT on it as M=64 UMMAs
+//       D3[(h2, kx', re|im), c] = sum_{px} F''[(h2, kx', re|im), px] * v[px, c]   (rows 32..63 are padding)
+//     reading the image in place as an MN-major B operand (pixels = K rows, channels contiguous),
+// then releases the buffer (y_free).  The accumulator of tile u is drained (drain_d3) while
+// tile u + 1 is in the epilogue, so that UMMA round trip is never waited for: rows (Re | Im of
+// one retained column of one grid row) go straight from TMEM lanes to their 128-byte rows of
+// the planar spectrum  Aout[b][kx][h][re|im][32 channels]  (fp32; what fno_mid_kernel bulk-copies).
 __device__ __forceinline__ void drain_d3(int t, int tile, const TcGeom& g, float* Aout, uint32_t tmem_d3,
                                          uint64_t* d3_full, uint32_t n) {
   mbar_wait(d3_full, n & 1u);
@@ -131,40 +131,22 @@ __device__ __forceinline__ void drain_d3(int t, int tile, const TcGeom& g, float
   tc_fence_before();
 }
 
-// n3 counts the tiles this worker has handed to the forward W-DFT; prev_tile is the last one
-__device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int tile, const TcGeom& g, uint8_t* y_img,
-                                            float* Aout, uint8_t* sXT, uint32_t tmem_d3, uint64_t* xt_full,
-                                            uint64_t* d3_full, uint32_t& n3, int& prev_tile) {
-  {
-    uint32_t hi[16], lo[16];
+// n3 counts the tiles this worker has handed over; prev_tile is the last one
+__device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int tile, const TcGeom& g, float* Aout,
+                                            uint8_t* sY, uint32_t tmem_d3, uint64_t* xt_full, uint64_t* d3_full,
+                                            uint64_t* y_free, uint32_t& n3, int& prev_tile) {
+  uint32_t hi[16], lo[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) split2(v[2 * j], v[2 * j + 1], hi[j], lo[j]);
-    uint8_t* dst = y_img + (size_t)tile * kTileBytes + t * 16;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      *reinterpret_cast<uint4*>(dst + q * 2048) = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
-      *reinterpret_cast<uint4*>(dst + kImg + q * 2048) =
-          make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
-    }
+  for (int j = 0; j < 16; ++j) split2(v[2 * j], v[2 * j + 1], hi[j], lo[j]);
+  if (n3 > 0) {   // the previous tile must have left the image buffer (bulk store, UMMAs) and the accumulator
+    mbar_wait(y_free, (n3 - 1) & 1u);
+    if (Aout != nullptr) drain_d3(t, prev_tile, g, Aout, tmem_d3, d3_full, n3 - 1);
   }
-  if (Aout == nullptr) return;
-  // the previous tile's W-DFT must have left the transposed-tile buffer and the accumulator
-  if (n3 > 0) drain_d3(t, prev_tile, g, Aout, tmem_d3, d3_full, n3 - 1);
-
-  // transposed tile [channel][pixel]: lanes pair up so that each store holds two adjacent pixels
-  const int odd = t & 1, me = t & ~1;
-  uint8_t* xt = sXT + (me >> 3) * kLboXT + (me & 7) * 2;
+  uint8_t* dst = sY + t * 16;
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const float send = odd ? v[2 * j] : v[2 * j + 1];
-    const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
-    const float a = odd ? recv : v[2 * j];
-    const float b = odd ? v[2 * j + 1] : recv;
-    uint32_t h, l;
-    split2(a, b, h, l);
-    const int row = 2 * j + odd;
-    *reinterpret_cast<uint32_t*>(xt + row * 16) = h;
-    *reinterpret_cast<uint32_t*>(xt + kXTBytes + row * 16) = l;
+  for (int q = 0; q < 4; ++q) {
+    *reinterpret_cast<uint4*>(dst + q * 2048) = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+    *reinterpret_cast<uint4*>(dst + kImg + q * 2048) = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
   }
   fence_async_smem();
   tc_fence_before();
@@ -173,21 +155,29 @@ __device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int til
   prev_tile = tile;
 }
 
-// control lane: forward W-DFT UMMAs of the n-th tile handed over (hi*hi, lo*hi, hi*lo)
-__device__ __forceinline__ void issue_fwd_dft(uint32_t aF, uint32_t aXT, uint32_t tmem_d3, uint64_t* xt_full,
-                                              uint64_t* d3_full, uint32_t n) {
+// control lane: n-th tile handed over by the epilogue group -> forward W-DFT UMMAs (hi*hi, lo*hi,
+// hi*lo; when `dft`), bulk store of the image, release of the buffer
+__device__ __forceinline__ void ctrl_finish_tile(bool dft, uint32_t aF, uint8_t* sY, uint8_t* y_dst, uint32_t tmem_d3,
+                                                 uint64_t* xt_full, uint64_t* d3_full, uint64_t* y_free, uint32_t n) {
   mbar_wait(xt_full, n & 1u);
   tc_fence_after();
-  const uint32_t idesc = idesc_bf16(64, 32);
+  if (dft) {
+    const uint32_t idesc = idesc_bf16(64, 32) | kIdescBMnMajor;
+    const uint32_t aY = smem_u32(sY);
 #pragma unroll
-  for (int term = 0; term < 3; ++term) {
-    const uint32_t fa = term == 1 ? 64u * 128u * 2u : 0u, xp = term == 2 ? (uint32_t)kXTBytes : 0u;
+    for (int term = 0; term < 3; ++term) {
+      const uint32_t fa = term == 1 ? 64u * 128u * 2u : 0u, yp = term == 2 ? (uint32_t)kImg : 0u;
 #pragma unroll
-    for (int k0 = 0; k0 < 128; k0 += 16)
-      umma_bf16(tmem_d3, chunk_desc(aF + fa, 64, k0), smem_desc(aXT + xp + (k0 >> 3) * kLboXT, kLboXT, 128), idesc,
-                (term | k0) != 0);
+      for (int k0 = 0; k0 < 128; k0 += 16)   // 8x8 core matrices: 128 B apart along pixels, 2048 B along channels
+        umma_bf16(tmem_d3, chunk_desc(aF + fa, 64, k0), smem_desc(aY + yp + k0 * 16, 128, 2048), idesc, (term | k0) != 0);
+    }
+    umma_commit(d3_full);
   }
-  umma_commit(d3_full);
+  bulk_s2g(y_dst, sY, kTileBytes);
+  bulk_commit();
+  bulk_wait_read0();
+  if (dft) umma_commit(y_free);   // arrives when the UMMAs above have read the image too
+  else mbar_arrive(y_free);
 }
 
 }  // namespace
@@ -202,7 +192,7 @@ __device__ __forceinline__ void issue_fwd_dft(uint32_t aF, uint32_t aXT, uint32_
 // =============================================================================================
 namespace {
 struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
-  int G, F, Ws, Bias, Worker, X, Z, XT, WorkerBytes, Total;
+  int G, F, Ws, Bias, Worker, X, Z, Y, WorkerBytes, Total;
   __host__ __device__ explicit LayerSmem(int KZ) {
     G = 0;
     F = G + 2 * 128 * KZ * 2;
@@ -211,13 +201,13 @@ struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
     Worker = Bias + 128;
     X = 0;
     Z = X + 2 * kTileBytes;
-    XT = Z + 2 * KZ * 128;
-    WorkerBytes = XT + 2 * kXTBytes;
+    Y = Z + 2 * KZ * 128;
+    WorkerBytes = Y + kTileBytes;
     Total = Worker + 2 * WorkerBytes;
   }
 };
 constexpr int kLayerSmemMax = 226 * 1024;   // 227 KB per CTA minus the kernel's static shared memory
-enum { LB_XFULL = 0, LB_DFULL = 2, LB_DEMPTY = 4, LB_XTFULL = 6, LB_D3FULL = 7, LB_PER = 8 };
+enum { LB_XFULL = 0, LB_DFULL = 2, LB_DEMPTY = 4, LB_XTFULL = 6, LB_D3FULL = 7, LB_YFREE = 8, LB_PER = 9 };
 }  // namespace
 
 __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a) {
@@ -241,6 +231,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
       mbar_init(&b[LB_DEMPTY + 1], kEpi);
       mbar_init(&b[LB_XTFULL], kEpi);
       mbar_init(&b[LB_D3FULL], 1);
+      mbar_init(&b[LB_YFREE], 1);
     }
     mbar_init(bar_const, 1);
     fence_mbar_init();
@@ -269,8 +260,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
       uint64_t* b = bars + w * LB_PER;
       uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
       const uint32_t tmem = tmem_s + 256u * w;
-      const uint32_t aG = smem_u32(smem + L.G), aF = smem_u32(smem + L.F), aW = smem_u32(smem + L.Ws),
-                     aXT = smem_u32(ws + L.XT);
+      const uint32_t aG = smem_u32(smem + L.G), aF = smem_u32(smem + L.F), aW = smem_u32(smem + L.Ws);
       const int first = blockIdx.x * 2 + w;
 
       auto load_inputs = [&](int tile, uint32_t u) {
@@ -315,8 +305,10 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
       for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
         if (tile + stride < g.ntiles) main_mma(u + 1);
         if (tile + 2 * stride < g.ntiles) load_inputs(tile + 2 * stride, u + 2);
-        if (a.Aout != nullptr) issue_fwd_dft(aF, aXT, tmem + 64, &b[LB_XTFULL], &b[LB_D3FULL], u);
+        ctrl_finish_tile(a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64, &b[LB_XTFULL],
+                         &b[LB_D3FULL], &b[LB_YFREE], u);
       }
+      bulk_wait0();
     }
   } else {
     // ------------------------------ epilogue group ------------------------------
@@ -343,10 +335,10 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
           v[c] = a.gelu ? gelu_fast(x) : x;
         }
       }
-      finish_tile(v, t, tile, g, a.y_img, a.Aout, ws + L.XT, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], n3,
+      finish_tile(v, t, tile, g, a.Aout, ws + L.Y, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], n3,
                   prev_tile);
     }
-    if (n3 > 0) drain_d3(t, prev_tile, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3 - 1);
+    if (n3 > 0 && a.Aout != nullptr) drain_d3(t, prev_tile, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3 - 1);
   }
   tc_fence_before();
   __syncthreads();
@@ -382,7 +374,7 @@ int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
 namespace {
 
 enum { MB_A1FULL = 0, MB_A1EMPTY = 2, MB_D1FULL = 4, MB_D1EMPTY = 6, MB_A2FULL = 8, MB_A2EMPTY = 10, MB_D2FULL = 12,
-       MB_D2EMPTY = 14, MB_XTFULL = 16, MB_D3FULL = 17, MB_PER = 18 };
+       MB_D2EMPTY = 14, MB_XTFULL = 16, MB_D3FULL = 17, MB_YFREE = 18, MB_PER = 19 };
 
 __device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_count) {
   for (int i = 0; i < 2; ++i) {
@@ -397,6 +389,7 @@ __device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_
   }
   mbar_init(&b[MB_XTFULL], kEpi);
   mbar_init(&b[MB_D3FULL], 1);
+  mbar_init(&b[MB_YFREE], 1);
 }
 
 struct MlpIssuer {
@@ -636,7 +629,7 @@ int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
 namespace {
 struct LiftSmem {   // sized for hid = 256
   static constexpr int W1 = 0, W2 = W1 + 256 * 16 * 4, F = W2 + 32 * 256 * 4, B2 = F + kFBytes, Worker = B2 + 128;
-  static constexpr int A1 = 0, A2 = A1 + 2 * 8192, XT = A2 + 2 * kTileBytes, WorkerBytes = XT + 2 * kXTBytes;
+  static constexpr int A1 = 0, A2 = A1 + 2 * 8192, Y = A2 + 2 * kTileBytes, WorkerBytes = Y + kTileBytes;
   static constexpr int Total = Worker + 2 * WorkerBytes;
   static_assert(Total <= 226 * 1024, "lift kernel shared memory");
 };
@@ -694,9 +687,13 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
                    smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u};
-      const uint32_t aF = smem_u32(smem + LiftSmem::F), aXT = smem_u32(ws + LiftSmem::XT), d3 = tmem_s + 256u * w + 192u;
+      const uint32_t aF = smem_u32(smem + LiftSmem::F), d3 = tmem_s + 256u * w + 192u;
       const int first = blockIdx.x * 2 + w;
       const bool dft = a.Aout != nullptr;
+      auto finish = [&](int tile, uint32_t n) {
+        ctrl_finish_tile(dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
+                         &b[MB_YFREE], n);
+      };
       mbar_wait(bar_const, 0);
       if (first < g.ntiles) is.mma1<16>(0, 0, 0);
       uint32_t u = 0;
@@ -706,11 +703,12 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
           const uint32_t gp = u * P + p;
           if (p + 1 < P) is.mma1<16>(u, p + 1, gp + 1);
           else if (has_next) is.mma1<16>(u + 1, 0, gp + 1);
-          if (p == 0 && u > 0 && dft) issue_fwd_dft(aF, aXT, d3, &b[MB_XTFULL], &b[MB_D3FULL], u - 1);
+          if (p == 0 && u > 0) finish(tile - stride, u - 1);
           is.mma2<32>(u, p);
         }
       }
-      if (u > 0 && dft) issue_fwd_dft(aF, aXT, d3, &b[MB_XTFULL], &b[MB_D3FULL], u - 1);
+      if (u > 0) finish(first + (int)(u - 1) * stride, u - 1);
+      bulk_wait0();
     }
   } else {
     const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
@@ -766,10 +764,10 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
 #pragma unroll
         for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]) + sB2[c];
       }
-      finish_tile(v, t, tile, g, a.y_img, a.Aout, ws + LiftSmem::XT, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], n3,
+      finish_tile(v, t, tile, g, a.Aout, ws + LiftSmem::Y, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], &b[MB_YFREE], n3,
                   prev_tile);
     }
-    if (n3 > 0) drain_d3(t, prev_tile, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3 - 1);
+    if (n3 > 0 && a.Aout != nullptr) drain_d3(t, prev_tile, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3 - 1);
   }
   tc_fence_before();
   __syncthreads();

@@ -56,6 +56,7 @@ SYMBOLS = {
                                        C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
     "dlwp_launch_count": (C.c_int64, []),
     "dlwp_selftest_umma": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, _P]),
+    "dlwp_selftest_umma_bmn": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_profile_begin": (C.c_int, [_P]),
     "dlwp_profile_end": (C.c_int, [_P]),
     "dlwp_profile_count": (C.c_int, []),

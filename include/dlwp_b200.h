@@ -164,6 +164,12 @@ int dlwp_profile_entry(int index, const char** name, double* total_ms, int64_t* 
  * fp32 accumulate in tensor memory); writes the raw 128-lane x N-column TMEM image to `d_raw`
  * (device, [128, N] fp32).  Used by the GPU tests to pin the descriptor encodings. */
 int dlwp_selftest_umma(const float* a, const float* b, float* d_raw, int M, int N, int K, void* stream);
+/* Same product with B given as [K, N] row-major and staged the way the kernels keep an activation
+ * tile (k rows, 16-byte chunks of 8 consecutive n), read by tcgen05.mma as an MN-major operand.
+ * variant 1: descriptor LBO = K stride, SBO = N stride of the 8x8 core matrices (what the library
+ * uses); variant 2: swapped (diagnostic). */
+int dlwp_selftest_umma_bmn(const float* a, const float* b_kn, float* d_raw, int M, int N, int K, int variant,
+                           void* stream);
 
 #ifdef __cplusplus
 }
