@@ -15,47 +15,27 @@ constexpr int kImg = kTcImgBytes;            // 8192: one bf16 part of a [128 x 
 constexpr int kTileBytes = 2 * kImg;         // hi + lo
 constexpr int kFBytes = 2 * 64 * 128 * 2;     // forward W-DFT operand: [hi | lo] images of 64 rows x 128 pixels
 
-// exact-erf GELU (F.gelu default) through Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7):
-// two MUFU ops and ~13 FMA-pipe ops per element instead of erff's branches
-__device__ __forceinline__ float gelu_fast(float x) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  float t, e;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  p *= t;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
-  const float erf_abs = fmaf(-p, e, 1.0f);
-  const float hx = 0.5f * x;
-  return fmaf(hx, copysignf(erf_abs, x), hx);
-}
-
-// The same GELU on two values at once with the packed fp32x2 pipe of sm_100 (FFMA2 / FMUL2):
-//   gelu(x) = x/2 + |x|/2 * erf(|x| / sqrt 2),   erf(z) = 1 - (a1 t + .. + a5 t^5) exp(-z^2),  t = 1 / (1 + p z)
-// 9 issue slots per element instead of 15 (the MUFU ops stay scalar).
+// Exact-erf GELU (F.gelu default) with ONE special-function op per element:
+//   gelu(x) = x Phi(x) = x/2 + |x| (1/2 - Phi(-|x|)),   Phi(-a) = erfc(a / sqrt 2) / 2 = 2^(-h(a))
+// h is smooth; a degree-6 polynomial on [0, 6] (tools/fit_gelu.py: minimax on the GELU error,
+// max |error| 5.2e-7 in fp32 Horner arithmetic over [-12, 12]) feeds ex2.approx.  Beyond a = 6 the
+// argument is clamped: 2^(-h(6)) < 1e-9, so the tail is exact to fp32.  Two values at once on the
+// packed fp32x2 pipe (FFMA2 / FMUL2): 9 packed ops + 2 MUFU + 4 ALU ops per pair.
 __device__ __forceinline__ float2 gelu2(float2 x) {
-  const float kR = 0.70710678118654752f;
-  const float2 z = make_float2(fabsf(x.x) * kR, fabsf(x.y) * kR);
-  const float2 den = __ffma2_rn(make_float2(0.3275911f, 0.3275911f), z, make_float2(1.0f, 1.0f));
-  float2 t, e;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.x) : "f"(den.x));
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.y) : "f"(den.y));
-  // negated polynomial: q = -(a1 t + ... + a5 t^5)
-  float2 q = __ffma2_rn(make_float2(-1.061405429f, -1.061405429f), t, make_float2(1.453152027f, 1.453152027f));
-  q = __ffma2_rn(q, t, make_float2(-1.421413741f, -1.421413741f));
-  q = __ffma2_rn(q, t, make_float2(0.284496736f, 0.284496736f));
-  q = __ffma2_rn(q, t, make_float2(-0.254829592f, -0.254829592f));
-  q = __fmul2_rn(q, t);
-  float2 w = __fmul2_rn(x, x);
-  w = __fmul2_rn(w, make_float2(-0.72134752044448170f, -0.72134752044448170f));   // -z^2 * log2(e)
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(w.x));
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(w.y));
-  const float2 erf_abs = __ffma2_rn(q, e, make_float2(1.0f, 1.0f));
-  const float2 ahx = __fmul2_rn(z, make_float2(kR, kR));          // |x| / 2
+  const float2 a = make_float2(fabsf(x.x), fabsf(x.y));
+  const float2 ac = make_float2(fminf(a.x, 6.0f), fminf(a.y, 6.0f));
+  float2 p = __ffma2_rn(make_float2(3.309331151e-05f, 3.309331151e-05f), ac, make_float2(-7.692239389e-04f, -7.692239389e-04f));
+  p = __ffma2_rn(p, ac, make_float2(8.080730059e-03f, 8.080730059e-03f));
+  p = __ffma2_rn(p, ac, make_float2(-5.341212443e-02f, -5.341212443e-02f));
+  p = __ffma2_rn(p, ac, make_float2(-4.587709588e-01f, -4.587709588e-01f));
+  p = __ffma2_rn(p, ac, make_float2(-1.151201707e+00f, -1.151201707e+00f));
+  p = __ffma2_rn(p, ac, make_float2(-9.999930606e-01f, -9.999930606e-01f));      // p = -h(a)
+  float2 e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(p.x));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(p.y));
+  const float2 t = __ffma2_rn(e, make_float2(-1.0f, -1.0f), make_float2(0.5f, 0.5f));
   const float2 hx = __fmul2_rn(x, make_float2(0.5f, 0.5f));
-  return __ffma2_rn(ahx, erf_abs, hx);
+  return __ffma2_rn(a, t, hx);
 }
 
 // v = hi + lo for a pair, residual through one packed FMA
@@ -71,16 +51,18 @@ __device__ __forceinline__ void split2p(float2 v, uint32_t& hi, uint32_t& lo) {
 }  // namespace
 
 // =============================================================================================
-// CTA organisation shared by the three kernels (persistent, one CTA per SM, 320 threads)
-//   warps 0-3 : epilogue group of worker 0      warp 8 : control warp of worker 0
-//   warps 4-7 : epilogue group of worker 1      warp 9 : control warp of worker 1
+// CTA organisation shared by the three kernels (persistent, one CTA per SM, 576 threads)
+//   warps 0-7  : epilogue group of worker 0      warp 16 : control warp of worker 0
+//   warps 8-15 : epilogue group of worker 1      warp 17 : control warp of worker 1
 // A worker owns every second tile of its CTA.  Its control warp issues the bulk copies and all
-// tcgen05.mma of the worker (one lane) and never touches data; its 128 epilogue threads own
-// one accumulator row (= pixel) each, move TMEM -> registers -> SMEM / HBM and never wait for
-// an MMA round trip they did not have a full pass of work to hide behind.  The two sides meet
-// only on mbarriers:
+// tcgen05.mma of the worker (one lane) and never touches data.  Its 256 epilogue threads work
+// in pairs on one accumulator row (= pixel): warps j and j + 4 of the group read the same TMEM
+// lane quarter and take the lower / upper 16 columns of every 32-column block, move TMEM ->
+// registers -> SMEM and never wait for an MMA round trip they did not have a full pass of
+// work to hide behind (four epilogue warps per scheduler keep the FMA / MUFU pipes fed while
+// others sit in tcgen05.ld or a barrier).  The two sides meet only on mbarriers:
 //   *_full  : producer -> consumer ("data is there"): tcgen05.commit (count 1), a bulk copy's
-//             complete_tx (count 1 + bytes) or 128 epilogue arrivals
+//             complete_tx (count 1 + bytes) or 256 epilogue arrivals
 //   *_empty : consumer -> producer ("buffer may be overwritten")
 // Ring slot of use u on a ring of depth 2: u & 1; full parity (u >> 1) & 1; empty parity
 // ((u >> 1) & 1) ^ 1 (so the first two uses pass immediately on fresh barriers).
@@ -89,8 +71,22 @@ __device__ __forceinline__ void split2p(float2 v, uint32_t& hi, uint32_t& lo) {
 // =============================================================================================
 namespace {
 
-constexpr int kEpi = 128;                    // epilogue threads per worker
-constexpr int kCta = 2 * kEpi + 2 * 32;      // 320
+constexpr int kEpi = 256;                    // epilogue threads per worker
+constexpr int kEpiWarps = kEpi / 32;
+constexpr int kCtlWarp = 2 * kEpiWarps;      // first control warp
+constexpr int kCta = 2 * kEpi + 2 * 32;      // 576
+
+// epilogue thread coordinates: tile row (= pixel = TMEM lane), column half, TMEM lane quarter
+struct EpiId {
+  int w, row, half, q4;
+  __device__ __forceinline__ explicit EpiId(int tid) {
+    const int warp = tid >> 5;
+    w = warp / kEpiWarps;
+    q4 = warp & 3;
+    half = (warp >> 2) & 1;
+    row = q4 * 32 + (tid & 31);
+  }
+};
 
 __device__ __forceinline__ uint32_t full_par(uint32_t u) { return (u >> 1) & 1u; }
 __device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1u) ^ 1u; }
@@ -107,23 +103,23 @@ __device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1
 // tile u + 1 is in the epilogue, so that UMMA round trip is never waited for: rows (Re | Im of
 // one retained column of one grid row) go straight from TMEM lanes to their 128-byte rows of
 // the planar spectrum  Aout[b][kx][h][re|im][32 channels]  (fp32; what fno_mid_kernel bulk-copies).
-__device__ __forceinline__ void drain_d3(int t, int tile, const TcGeom& g, float* Aout, uint32_t tmem_d3,
+__device__ __forceinline__ void drain_d3(const EpiId& id, int tile, const TcGeom& g, float* Aout, uint32_t tmem_d3,
                                          uint64_t* d3_full, uint32_t n) {
   mbar_wait(d3_full, n & 1u);
   tc_fence_after();
-  const int q4 = t >> 5, lane = t & 31;
+  const int q4 = id.q4, lane = id.row & 31;
   if (q4 < 2) {   // an M=64 accumulator keeps row r in TMEM lane 32 * (r / 16) + r % 16
-    uint32_t r[32];
-    tmem_ld32(tmem_d3 + ((uint32_t)(q4 * 32) << 16), r);
+    uint32_t r[16];
+    tmem_ld16(tmem_d3 + ((uint32_t)(q4 * 32) << 16) + 16u * id.half, r);
     tmem_ld_wait();
     const int row = q4 * 16 + lane;
     const int h2 = row / g.KXP, rem = row - h2 * g.KXP, kx = rem >> 1, reim = rem & 1;
     if (lane < 16 && h2 < g.RT && kx < g.Kc) {
       const int grow = tile * g.RT + h2;
       const int b = grow / g.H, h = grow - b * g.H;
-      float4* dst = reinterpret_cast<float4*>(Aout + ((((size_t)b * g.Kc + kx) * g.H + h) * 2 + reim) * 32);
+      float4* dst = reinterpret_cast<float4*>(Aout + ((((size_t)b * g.Kc + kx) * g.H + h) * 2 + reim) * 32 + 16 * id.half);
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
+      for (int j = 0; j < 4; ++j)
         dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
                              __uint_as_float(r[4 * j + 3]));
     }
@@ -131,20 +127,21 @@ __device__ __forceinline__ void drain_d3(int t, int tile, const TcGeom& g, float
   tc_fence_before();
 }
 
-// n3 counts the tiles this worker has handed over; prev_tile is the last one
-__device__ __forceinline__ void finish_tile(const float (&v)[32], int t, int tile, const TcGeom& g, float* Aout,
+// n3 counts the tiles this worker has handed over; prev_tile is the last one.
+// v[8] = this thread's 16 output channels (16 * half ..) of its pixel, as pairs
+__device__ __forceinline__ void finish_tile(const float2 (&v)[8], const EpiId& id, int tile, const TcGeom& g, float* Aout,
                                             uint8_t* sY, uint32_t tmem_d3, uint64_t* xt_full, uint64_t* d3_full,
                                             uint64_t* y_free, uint32_t& n3, int& prev_tile) {
-  uint32_t hi[16], lo[16];
+  uint32_t hi[8], lo[8];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) split2(v[2 * j], v[2 * j + 1], hi[j], lo[j]);
+  for (int j = 0; j < 8; ++j) split2p(v[j], hi[j], lo[j]);
   if (n3 > 0) {   // the previous tile must have left the image buffer (bulk store, UMMAs) and the accumulator
     mbar_wait(y_free, (n3 - 1) & 1u);
-    if (Aout != nullptr) drain_d3(t, prev_tile, g, Aout, tmem_d3, d3_full, n3 - 1);
+    if (Aout != nullptr) drain_d3(id, prev_tile, g, Aout, tmem_d3, d3_full, n3 - 1);
   }
-  uint8_t* dst = sY + t * 16;
+  uint8_t* dst = sY + id.row * 16 + id.half * 4096;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
+  for (int q = 0; q < 2; ++q) {
     *reinterpret_cast<uint4*>(dst + q * 2048) = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
     *reinterpret_cast<uint4*>(dst + kImg + q * 2048) = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
   }
@@ -236,7 +233,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
     mbar_init(bar_const, 1);
     fence_mbar_init();
   }
-  if (warp == 8) {
+  if (warp == kCtlWarp) {
     tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
@@ -253,10 +250,10 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
   }
   const int stride = gridDim.x * 2;
 
-  if (warp >= 8) {
+  if (warp >= kCtlWarp) {
     // ------------------------------ control warp (one lane) ------------------------------
     if (lane == 0) {
-      const int w = warp - 8;
+      const int w = warp - kCtlWarp;
       uint64_t* b = bars + w * LB_PER;
       uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
       const uint32_t tmem = tmem_s + 256u * w;
@@ -312,37 +309,40 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
     }
   } else {
     // ------------------------------ epilogue group ------------------------------
-    const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
+    const EpiId id(tid);
+    const int w = id.w;
     uint64_t* b = bars + w * LB_PER;
     uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
-    const uint32_t tmem = tmem_s + 256u * w + ((uint32_t)(q4 * 32) << 16);
+    const uint32_t tmem = tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 16u * id.half;
     uint32_t u = 0, n3 = 0;
     int prev_tile = 0;
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       mbar_wait(&b[LB_DFULL + s], full_par(u));
       tc_fence_after();
-      float v[32];
+      float2 v[8];
       {
-        uint32_t r[32];
-        tmem_ld32(tmem + 32u * s, r);
+        uint32_t r[16];
+        tmem_ld16(tmem + 32u * s, r);
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(&b[LB_DEMPTY + s]);
+        const float2* bias2 = reinterpret_cast<const float2*>(sBias + 16 * id.half);
 #pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          const float x = __uint_as_float(r[c]) + sBias[c];
-          v[c] = a.gelu ? gelu_fast(x) : x;
+        for (int c = 0; c < 8; ++c) {
+          const float2 bb = bias2[c];
+          const float2 x = make_float2(__uint_as_float(r[2 * c]) + bb.x, __uint_as_float(r[2 * c + 1]) + bb.y);
+          v[c] = a.gelu ? gelu2(x) : x;
         }
       }
-      finish_tile(v, t, tile, g, a.Aout, ws + L.Y, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], n3,
+      finish_tile(v, id, tile, g, a.Aout, ws + L.Y, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], n3,
                   prev_tile);
     }
-    if (n3 > 0 && a.Aout != nullptr) drain_d3(t, prev_tile, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3 - 1);
+    if (n3 > 0 && a.Aout != nullptr) drain_d3(id, prev_tile, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3 - 1);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) tmem_dealloc(tmem_s, 512);
+  if (warp == kCtlWarp) tmem_dealloc(tmem_s, 512);
 }
 
 int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
@@ -453,36 +453,35 @@ struct MlpIssuer {
   }
 };
 
-// epilogue side of one tile's MLP; `after_pass0()` runs once after the first pass
+// epilogue side of one tile's MLP; `after_pass0()` runs once after the first pass.  Each thread
+// turns 16 hidden columns of its pixel per 32-column chunk into split-bf16 operand bytes.
 template <class Hook>
-__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, int t, uint32_t tmem_lane, int P, uint8_t* sA2, uint32_t& gp,
-                                             uint32_t& nc, Hook after_pass0) {
+__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint32_t tmem_lane, int P, uint8_t* sA2,
+                                             uint32_t& gp, uint32_t& nc, Hook after_pass0) {
   for (int p = 0; p < P; ++p, ++gp) {
     const int db = gp & 1;
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
     tc_fence_after();
-#pragma unroll 1
+#pragma unroll
     for (int j = 0; j < 2; ++j, ++nc) {
-      uint32_t r[32];
-      tmem_ld32(tmem_lane + 64u * db + 32u * j, r);
+      uint32_t r[16];
+      tmem_ld16(tmem_lane + 64u * db + 32u * j, r);
       tmem_ld_wait();
       if (j == 1) {
         tc_fence_before();
         mbar_arrive(&b[MB_D1EMPTY + db]);
       }
+      uint32_t h[8], l[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        split2p(gelu2(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]))), h[e], l[e]);
       const int ab = nc & 1;
       mbar_wait(&b[MB_A2EMPTY + ab], empty_par(nc));
-      uint8_t* dst = sA2 + ab * kTileBytes + t * 16;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint32_t h[4], l[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e)
-          split2p(gelu2(make_float2(__uint_as_float(r[8 * q + 2 * e]), __uint_as_float(r[8 * q + 2 * e + 1]))), h[e],
-                  l[e]);
-        *reinterpret_cast<uint4*>(dst + q * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4*>(dst + kImg + q * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
-      }
+      uint8_t* dst = sA2 + ab * kTileBytes + id.row * 16 + id.half * 4096;
+      *reinterpret_cast<uint4*>(dst) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(h[4], h[5], h[6], h[7]);
+      *reinterpret_cast<uint4*>(dst + kImg) = make_uint4(l[0], l[1], l[2], l[3]);
+      *reinterpret_cast<uint4*>(dst + kImg + 2048) = make_uint4(l[4], l[5], l[6], l[7]);
       fence_async_smem();
       mbar_arrive(&b[MB_A2FULL + ab]);
     }
@@ -520,7 +519,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
     mbar_init(bar_const, 1);
     fence_mbar_init();
   }
-  if (warp == 8) {
+  if (warp == kCtlWarp) {
     tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
@@ -542,9 +541,9 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   }
   const int stride = gridDim.x * 2;
 
-  if (warp >= 8) {
+  if (warp >= kCtlWarp) {
     if (lane == 0) {
-      const int w = warp - 8;
+      const int w = warp - kCtlWarp;
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + ProjSmem::Worker + w * ProjSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + ProjSmem::X), (uint32_t)kTileBytes, smem_u32(smem + ProjSmem::W1),
@@ -575,36 +574,38 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       }
     }
   } else {
-    const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
+    const EpiId id(tid);
+    const int w = id.w;
     uint64_t* b = bars + w * MB_PER;
     uint8_t* ws = smem + ProjSmem::Worker + w * ProjSmem::WorkerBytes;
-    const uint32_t tmem_lane = tmem_s + 256u * w + ((uint32_t)(q4 * 32) << 16);
+    const uint32_t tmem_lane = tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 16u * id.half;
+    const int c0 = 8 * id.half;      // this thread's 8 output channels
     uint32_t u = 0, gp = 0, nc = 0;
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
-      epi_mlp_tile(b, t, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [] {});
+      // residual frame values: requested now, consumed after the MLP passes
+      const long long p = (long long)tile * kTcTile + id.row;
+      const long long bb = p / g.HW, pix = p - bb * g.HW;
+      float lastv[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        lastv[c] = (a.last != nullptr && c0 + c < a.Cg) ? a.last[bb * a.last_bstride + (long long)(c0 + c) * g.HW + pix] : 0.f;
+      epi_mlp_tile(b, id, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [] {});
       mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
       tc_fence_after();
-      uint32_t r[16];
-      tmem_ld16(tmem_lane + 128u + 32u * (u & 1), r);
+      uint32_t r[8];
+      tmem_ld8(tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 128u + 32u * (u & 1) + (uint32_t)c0, r);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
-      const long long p = (long long)tile * kTcTile + t;
-      const long long bb = p / g.HW, pix = p - bb * g.HW;
       float* o = a.out + bb * a.out_bstride + pix;
-      const float* lastp = a.last ? a.last + bb * a.last_bstride + pix : nullptr;
 #pragma unroll
-      for (int c = 0; c < 16; ++c)
-        if (c < a.Cg) {
-          float val = __uint_as_float(r[c]) + sB2[c];
-          if (lastp) val += lastp[(long long)c * g.HW];
-          o[(long long)c * g.HW] = val;
-        }
+      for (int c = 0; c < 8; ++c)
+        if (c0 + c < a.Cg) o[(long long)(c0 + c) * g.HW] = __uint_as_float(r[c]) + sB2[c0 + c] + lastv[c];
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) tmem_dealloc(tmem_s, 512);
+  if (warp == kCtlWarp) tmem_dealloc(tmem_s, 512);
 }
 
 int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
@@ -663,7 +664,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       kbs[k] = 0;
     }
   }
-  if (warp == 8) {
+  if (warp == kCtlWarp) {
     tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
@@ -680,9 +681,9 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   }
   const int stride = gridDim.x * 2;
 
-  if (warp >= 8) {
+  if (warp >= kCtlWarp) {
     if (lane == 0) {
-      const int w = warp - 8;
+      const int w = warp - kCtlWarp;
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
@@ -711,35 +712,34 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       bulk_wait0();
     }
   } else {
-    const int w = warp >> 2, t = tid & (kEpi - 1), q4 = warp & 3;
+    const EpiId id(tid);
+    const int w = id.w;
     uint64_t* b = bars + w * MB_PER;
     uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
-    const uint32_t tmem_w = tmem_s + 256u * w, tmem_lane = tmem_w + ((uint32_t)(q4 * 32) << 16);
-    const int Cin = a.Cin;
+    const uint32_t tmem_w = tmem_s + 256u * w, tmem_lane = tmem_w + ((uint32_t)(id.q4 * 32) << 16) + 16u * id.half;
+    const int Cin = a.Cin, k0 = 8 * id.half;      // this thread's 8 input columns of its pixel
 
-    auto gather = [&](int tile, float (&x)[16]) {
-      const long long p = (long long)tile * kTcTile + t;
+    auto gather = [&](int tile, float (&x)[8]) {
+      const long long p = (long long)tile * kTcTile + id.row;
       const long long bb = p / g.HW, pix = p - bb * g.HW;
 #pragma unroll
-      for (int k = 0; k < 16; ++k) x[k] = k < Cin ? kptr[k][bb * kbs[k] + pix] : (k == Cin ? 1.0f : 0.0f);
+      for (int k = 0; k < 8; ++k) x[k] = k0 + k < Cin ? kptr[k0 + k][bb * kbs[k0 + k] + pix] : (k0 + k == Cin ? 1.0f : 0.0f);
     };
-    auto store_a1 = [&](uint32_t u, const float (&x)[16]) {   // column Cin carries the 1 that multiplies the bias
+    auto store_a1 = [&](uint32_t u, const float (&x)[8]) {   // column Cin carries the 1 that multiplies the bias
       const int s = u & 1;
       mbar_wait(&b[MB_A1EMPTY + s], empty_par(u));
-      uint32_t h[8], l[8];
+      uint32_t h[4], l[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) split2(x[2 * j], x[2 * j + 1], h[j], l[j]);
-      uint8_t* d = ws + LiftSmem::A1 + s * 8192 + t * 16;
+      for (int j = 0; j < 4; ++j) split2(x[2 * j], x[2 * j + 1], h[j], l[j]);
+      uint8_t* d = ws + LiftSmem::A1 + s * 8192 + id.half * 2048 + id.row * 16;
       *reinterpret_cast<uint4*>(d) = make_uint4(h[0], h[1], h[2], h[3]);
-      *reinterpret_cast<uint4*>(d + 2048) = make_uint4(h[4], h[5], h[6], h[7]);
       *reinterpret_cast<uint4*>(d + 4096) = make_uint4(l[0], l[1], l[2], l[3]);
-      *reinterpret_cast<uint4*>(d + 6144) = make_uint4(l[4], l[5], l[6], l[7]);
       fence_async_smem();
       mbar_arrive(&b[MB_A1FULL + s]);
     };
 
     const int first = blockIdx.x * 2 + w;
-    float nx[16];
+    float nx[8];
     if (first < g.ntiles) {
       gather(first, nx);
       store_a1(0, nx);
@@ -749,29 +749,33 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
     for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
       const bool has_next = tile + stride < g.ntiles;
       if (has_next) gather(tile + stride, nx);      // loads in flight while the first pass is processed
-      epi_mlp_tile(b, t, tmem_lane, P, ws + LiftSmem::A2, gp, nc, [&] {
+      epi_mlp_tile(b, id, tmem_lane, P, ws + LiftSmem::A2, gp, nc, [&] {
         if (has_next) store_a1(u + 1, nx);
       });
       mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
       tc_fence_after();
-      float v[32];
+      float2 v[8];
       {
-        uint32_t r[32];
-        tmem_ld32(tmem_lane + 128u + 32u * (u & 1), r);
+        uint32_t r[16];
+        tmem_ld16(tmem_lane + 128u + 32u * (u & 1), r);
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
+        const float2* bias2 = reinterpret_cast<const float2*>(sB2 + 16 * id.half);
 #pragma unroll
-        for (int c = 0; c < 32; ++c) v[c] = __uint_as_float(r[c]) + sB2[c];
+        for (int c = 0; c < 8; ++c) {
+          const float2 bb = bias2[c];
+          v[c] = make_float2(__uint_as_float(r[2 * c]) + bb.x, __uint_as_float(r[2 * c + 1]) + bb.y);
+        }
       }
-      finish_tile(v, t, tile, g, a.Aout, ws + LiftSmem::Y, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], &b[MB_YFREE], n3,
+      finish_tile(v, id, tile, g, a.Aout, ws + LiftSmem::Y, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], &b[MB_YFREE], n3,
                   prev_tile);
     }
-    if (n3 > 0 && a.Aout != nullptr) drain_d3(t, prev_tile, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3 - 1);
+    if (n3 > 0 && a.Aout != nullptr) drain_d3(id, prev_tile, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3 - 1);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) tmem_dealloc(tmem_s, 512);
+  if (warp == kCtlWarp) tmem_dealloc(tmem_s, 512);
 }
 
 int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
