@@ -13,7 +13,7 @@ namespace {
 
 constexpr int kImg = kTcImgBytes;            // 8192: one bf16 part of a [128 x 32] tile
 constexpr int kTileBytes = 2 * kImg;         // hi + lo
-constexpr int kFBytes = 2 * 64 * 128 * 2;     // forward W-DFT operand: [hi | lo] images of 64 rows x 128 pixels
+constexpr int kFBytes = 2 * 32 * 128 * 2;     // forward W-DFT operand: [hi | lo] images of 32 rows x 128 pixels
 
 // Exact-erf GELU (F.gelu default) with ONE special-function op per element:
 //   gelu(x) = x Phi(x) = x/2 + |x| (1/2 - Phi(-|x|)),   Phi(-a) = erfc(a / sqrt 2) / 2 = 2^(-h(a))
@@ -75,6 +75,7 @@ constexpr int kEpi = 256;                    // epilogue threads per worker
 constexpr int kEpiWarps = kEpi / 32;
 constexpr int kCtlWarp = 2 * kEpiWarps;      // first control warp
 constexpr int kCta = 2 * kEpi + 2 * 32;      // 576
+constexpr int kCtaLayer = kCta + 2 * 32;     // the layer kernel splits control into an issuer and a loader / finisher warp
 
 // epilogue thread coordinates: tile row (= pixel = TMEM lane), column half, TMEM lane quarter
 struct EpiId {
@@ -97,7 +98,7 @@ __device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1
 // the control lane (xt_full), which
 //   * stores it to HBM with one bulk copy, and
 //   * when `Aout` is set, runs the forward truncated W-DFT on it as M=64 UMMAs
-//       D3[(h2, kx', re|im), c] = sum_{px} F''[(h2, kx', re|im), px] * v[px, c]   (rows 32..63 are padding)
+//       D3[(h2, kx', re|im), c] = sum_{px} F''[(h2, kx', re|im), px] * v[px, c]   (accumulator rows 32..63 unused)
 //     reading the image in place as an MN-major B operand (pixels = K rows, channels contiguous),
 // then releases the buffer (y_free).  The accumulator of tile u is drained (drain_d3) while
 // tile u + 1 is in the epilogue, so that UMMA round trip is never waited for: rows (Re | Im of
@@ -163,10 +164,12 @@ __device__ __forceinline__ void ctrl_finish_tile(bool dft, uint32_t aF, uint8_t*
     const uint32_t aY = smem_u32(sY);
 #pragma unroll
     for (int term = 0; term < 3; ++term) {
-      const uint32_t fa = term == 1 ? 64u * 128u * 2u : 0u, yp = term == 2 ? (uint32_t)kImg : 0u;
+      const uint32_t fa = term == 1 ? 32u * 128u * 2u : 0u, yp = term == 2 ? (uint32_t)kImg : 0u;
+      // A: the 32-row image read as M = 64 (rows 32..63 alias the next K chunk: their accumulator
+      // rows are never looked at); B: 8x8 core matrices 128 B apart along pixels, 2048 B along channels
 #pragma unroll
-      for (int k0 = 0; k0 < 128; k0 += 16)   // 8x8 core matrices: 128 B apart along pixels, 2048 B along channels
-        umma_bf16(tmem_d3, chunk_desc(aF + fa, 64, k0), smem_desc(aY + yp + k0 * 16, 128, 2048), idesc, (term | k0) != 0);
+      for (int k0 = 0; k0 < 128; k0 += 16)
+        umma_bf16(tmem_d3, chunk_desc(aF + fa, 32, k0), smem_desc(aY + yp + k0 * 16, 128, 2048), idesc, (term | k0) != 0);
     }
     umma_commit(d3_full);
   }
@@ -207,7 +210,7 @@ constexpr int kLayerSmemMax = 226 * 1024;   // 227 KB per CTA minus the kernel's
 enum { LB_XFULL = 0, LB_DFULL = 2, LB_DEMPTY = 4, LB_XTFULL = 6, LB_D3FULL = 7, LB_YFREE = 8, LB_PER = 9 };
 }  // namespace
 
-__global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a) {
+__global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bars[2 * LB_PER + 1];
   __shared__ uint32_t tmem_s;
@@ -250,14 +253,15 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
   }
   const int stride = gridDim.x * 2;
 
-  if (warp >= kCtlWarp) {
-    // ------------------------------ control warp (one lane) ------------------------------
+  if (warp >= kCtlWarp + 2) {
+    // ---------------- loader / finisher lane: input bulk copies, forward W-DFT, image store ----------------
+    // (its own warp so that a late input never delays handing a finished tile on, and vice versa)
     if (lane == 0) {
-      const int w = warp - kCtlWarp;
+      const int w = warp - kCtlWarp - 2;
       uint64_t* b = bars + w * LB_PER;
       uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
       const uint32_t tmem = tmem_s + 256u * w;
-      const uint32_t aG = smem_u32(smem + L.G), aF = smem_u32(smem + L.F), aW = smem_u32(smem + L.Ws);
+      const uint32_t aF = smem_u32(smem + L.F);
       const int first = blockIdx.x * 2 + w;
 
       auto load_inputs = [&](int tile, uint32_t u) {
@@ -271,9 +275,28 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
       if (first < g.ntiles) load_inputs(first, 0);
       if (first + stride < g.ntiles) load_inputs(first + stride, 1);
       mbar_wait(bar_const, 0);
+      uint32_t u = 0;
+      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+        if (tile + 2 * stride < g.ntiles) load_inputs(tile + 2 * stride, u + 2);
+        ctrl_finish_tile(a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64, &b[LB_XTFULL],
+                         &b[LB_D3FULL], &b[LB_YFREE], u);
+      }
+      bulk_wait0();
+    }
+  } else if (warp >= kCtlWarp) {
+    // ---------------- issuer lane: the main UMMAs, as soon as a tile's inputs and an accumulator are there ----------------
+    if (lane == 0) {
+      const int w = warp - kCtlWarp;
+      uint64_t* b = bars + w * LB_PER;
+      uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
+      const uint32_t tmem = tmem_s + 256u * w;
+      const uint32_t aG = smem_u32(smem + L.G), aW = smem_u32(smem + L.Ws);
+      const int first = blockIdx.x * 2 + w;
+      mbar_wait(bar_const, 0);
       const uint32_t idesc = idesc_bf16(128, 32);
       const uint32_t g_lo = 128u * (uint32_t)g.KZ * 2u, z_lo = (uint32_t)g.KZ * 64u;
-      auto main_mma = [&](uint32_t u) {
+      uint32_t u = 0;
+      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
         const int s = u & 1;
         mbar_wait(&b[LB_XFULL + s], full_par(u));
         mbar_wait(&b[LB_DEMPTY + s], empty_par(u));
@@ -294,18 +317,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_layer_kernel(const TcLayerArgs a)
             umma_bf16(d, chunk_desc(aX + xa, 128, k0), chunk_desc(aW + wb, 32, k0), idesc, 1);
         }
         umma_commit(&b[LB_DFULL + s]);
-      };
-      // the main UMMAs run one tile ahead of the epilogue group; the forward W-DFT of tile u is
-      // issued when the group has handed over its transposed tile
-      if (first < g.ntiles) main_mma(0);
-      uint32_t u = 0;
-      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
-        if (tile + stride < g.ntiles) main_mma(u + 1);
-        if (tile + 2 * stride < g.ntiles) load_inputs(tile + 2 * stride, u + 2);
-        ctrl_finish_tile(a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64, &b[LB_XTFULL],
-                         &b[LB_D3FULL], &b[LB_YFREE], u);
       }
-      bulk_wait0();
     }
   } else {
     // ------------------------------ epilogue group ------------------------------
@@ -357,7 +369,7 @@ int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
-  fno_layer_kernel<<<grid, kCta, L.Total, st>>>(a);
+  fno_layer_kernel<<<grid, kCtaLayer, L.Total, st>>>(a);
   DLWP_LAUNCHED("fno_layer_kernel");
   return DLWP_OK;
 }

@@ -47,7 +47,7 @@ struct TcLiftArgs {
   const uint8_t* W1img;   // [hi | lo] images, R = hid rows, K = 16
   const uint8_t* W2img;   // [hi | lo] images, R = 32 rows, K = hid
   const float* b2;        // [32]
-  const uint8_t* Fimg;    // forward W-DFT operand [hi | lo] images, R = 64 (32 used), K = 128
+  const uint8_t* Fimg;    // forward W-DFT operand [hi | lo] images, R = 32, K = 128
   uint8_t* y_img;         // tile images out
   float* Aout;            // planar spectrum [B][Kc][H][re|im][32]: forward W-DFT of the output
 };

@@ -54,9 +54,9 @@ int plan_tc_build(dlwp_plan* p) {
         F[(size_t)k * 128 + m] = s * std::cos(ang);
         F[(size_t)(k + 1) * 128 + m] = -s * std::sin(ang);
       }
-  std::vector<uint8_t> gi((size_t)2 * 128 * KZ * 2), fi(2 * 64 * 128 * 2);
+  std::vector<uint8_t> gi((size_t)2 * 128 * KZ * 2), fi(2 * 32 * 128 * 2);
   tc_pack_images_f64(G.data(), 128, KZ, KZ, 128, KZ, gi.data());
-  tc_pack_images_f64(F.data(), 32, 128, 128, 64, 128, fi.data());
+  tc_pack_images_f64(F.data(), 32, 128, 128, 32, 128, fi.data());
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_G, gi.size()));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_F, fi.size()));
   DLWP_CUDA(cudaMemcpy(p->tc_G, gi.data(), gi.size(), cudaMemcpyHostToDevice));
