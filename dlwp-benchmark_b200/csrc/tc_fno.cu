@@ -9,6 +9,13 @@ namespace dlwp {
 
 using namespace tc;
 
+#ifdef DLWP_TRACE
+__device__ unsigned long long* g_trace = nullptr;
+#define TR(w, u, ev) do { if (g_trace && blockIdx.x == 0 && (u) < 16) g_trace[((w) * 16 + (u)) * 8 + (ev)] = clock64(); } while (0)
+#else
+#define TR(w, u, ev) do {} while (0)
+#endif
+
 namespace {
 
 constexpr int kImg = kTcImgBytes;            // 8192: one bf16 part of a [128 x 32] tile
@@ -138,6 +145,7 @@ __device__ __forceinline__ void finish_tile(const float2 (&v)[8], const EpiId& i
   for (int j = 0; j < 8; ++j) split2p(v[j], hi[j], lo[j]);
   if (n3 > 0) {   // the previous tile must have left the image buffer (bulk store, UMMAs) and the accumulator
     mbar_wait(y_free, (n3 - 1) & 1u);
+    if ((threadIdx.x & 255) == 0) TR(id.w, n3, 7);
     if (Aout != nullptr) drain_d3(id, prev_tile, g, Aout, tmem_d3, d3_full, n3 - 1);
   }
   uint8_t* dst = sY + id.row * 16 + id.half * 4096;
@@ -149,35 +157,38 @@ __device__ __forceinline__ void finish_tile(const float2 (&v)[8], const EpiId& i
   fence_async_smem();
   tc_fence_before();
   mbar_arrive(xt_full);
+  if ((threadIdx.x & 255) == 0) TR(id.w, n3, 4);
   ++n3;
   prev_tile = tile;
 }
 
-// control lane: n-th tile handed over by the epilogue group -> forward W-DFT UMMAs (hi*hi, lo*hi,
+// control warp: n-th tile handed over by the epilogue group -> forward W-DFT UMMAs (hi*hi, lo*hi,
 // hi*lo; when `dft`), bulk store of the image, release of the buffer
-__device__ __forceinline__ void ctrl_finish_tile(bool dft, uint32_t aF, uint8_t* sY, uint8_t* y_dst, uint32_t tmem_d3,
-                                                 uint64_t* xt_full, uint64_t* d3_full, uint64_t* y_free, uint32_t n) {
+__device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint32_t aF, uint8_t* sY, uint8_t* y_dst,
+                                                 uint32_t tmem_d3, uint64_t* xt_full, uint64_t* d3_full, uint64_t* y_free,
+                                                 uint32_t n) {
   mbar_wait(xt_full, n & 1u);
   tc_fence_after();
   if (dft) {
     const uint32_t idesc = idesc_bf16(64, 32) | kIdescBMnMajor;
-    const uint32_t aY = smem_u32(sY);
+    // A: the 32-row image read as M = 64 (rows 32..63 alias the next K chunk: their accumulator
+    // rows are never looked at); B: 8x8 core matrices 128 B apart along pixels, 2048 B along channels
+    const uint64_t dF = chunk_desc(aF, 32, 0), dY = smem_desc(smem_u32(sY), 128, 2048);
 #pragma unroll
     for (int term = 0; term < 3; ++term) {
       const uint32_t fa = term == 1 ? 32u * 128u * 2u : 0u, yp = term == 2 ? (uint32_t)kImg : 0u;
-      // A: the 32-row image read as M = 64 (rows 32..63 alias the next K chunk: their accumulator
-      // rows are never looked at); B: 8x8 core matrices 128 B apart along pixels, 2048 B along channels
 #pragma unroll
       for (int k0 = 0; k0 < 128; k0 += 16)
-        umma_bf16(tmem_d3, chunk_desc(aF + fa, 32, k0), smem_desc(aY + yp + k0 * 16, 128, 2048), idesc, (term | k0) != 0);
+        umma_bf16_p(leader, tmem_d3, desc_off(dF, fa + (k0 >> 3) * 512), desc_off(dY, yp + k0 * 16), idesc, (term | k0) != 0);
     }
-    umma_commit(d3_full);
+    umma_commit_p(leader, d3_full);
   }
-  bulk_s2g(y_dst, sY, kTileBytes);
+  bulk_s2g_p(leader, y_dst, sY, kTileBytes);
   bulk_commit();
   bulk_wait_read0();
-  if (dft) umma_commit(y_free);   // arrives when the UMMAs above have read the image too
-  else mbar_arrive(y_free);
+  if (dft) umma_commit_p(leader, y_free);   // arrives when the UMMAs above have read the image too
+  else mbar_arrive_p(leader, y_free);
+  __syncwarp();
 }
 
 }  // namespace
@@ -185,12 +196,14 @@ __device__ __forceinline__ void ctrl_finish_tile(bool dft, uint32_t aF, uint8_t*
 // =============================================================================================
 // fno_layer_kernel: y = act( irfft_W(Z) + skip(x) + bias ) on 128-pixel tiles
 //   D[128 px, 32 ch] = G'[128, KZ] * Z'^T  +  X[128, 32] * Ws^T      (split-bf16: 3 terms each)
-// G' is block-diagonal over the grid rows of the tile; Z' (one 8-wide K chunk per retained
-// column: (Re, Im) of that column for each grid row of the tile) arrives from fno_mid_kernel
-// as a ready operand image.  The control lane keeps two tiles (activation image + Z' image,
-// one bulk copy each) in flight per worker while the epilogue group works on the current one.
+// G' is block-diagonal over the grid rows of the tile; Z' (K index = (retained column, grid row of
+// the tile, Re | Im)) arrives from fno_mid_kernel as a ready operand image.  Each worker cycles
+// three input slots (activation image + Z' image, one bulk copy each): a slot is refilled as soon
+// as the UMMAs that read it have completed, so up to three tiles per worker are in flight while
+// the epilogue group works on the current one.
 // =============================================================================================
 namespace {
+constexpr int kLayerSlots = 3;
 struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
   int G, F, Ws, Bias, Worker, X, Z, Y, WorkerBytes, Total;
   __host__ __device__ explicit LayerSmem(int KZ) {
@@ -200,14 +213,14 @@ struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
     Bias = Ws + 4096;
     Worker = Bias + 128;
     X = 0;
-    Z = X + 2 * kTileBytes;
-    Y = Z + 2 * KZ * 128;
+    Z = X + kLayerSlots * kTileBytes;
+    Y = Z + kLayerSlots * KZ * 128;
     WorkerBytes = Y + kTileBytes;
     Total = Worker + 2 * WorkerBytes;
   }
 };
 constexpr int kLayerSmemMax = 226 * 1024;   // 227 KB per CTA minus the kernel's static shared memory
-enum { LB_XFULL = 0, LB_DFULL = 2, LB_DEMPTY = 4, LB_XTFULL = 6, LB_D3FULL = 7, LB_YFREE = 8, LB_PER = 9 };
+enum { LB_XFULL = 0, LB_XFREE = 3, LB_DFULL = 6, LB_DEMPTY = 8, LB_XTFULL = 10, LB_D3FULL = 11, LB_YFREE = 12, LB_PER = 13 };
 }  // namespace
 
 __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerArgs a) {
@@ -223,8 +236,10 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
   if (tid == 0) {
     for (int w = 0; w < 2; ++w) {
       uint64_t* b = bars + w * LB_PER;
-      mbar_init(&b[LB_XFULL], 1);
-      mbar_init(&b[LB_XFULL + 1], 1);
+      for (int i = 0; i < kLayerSlots; ++i) {
+        mbar_init(&b[LB_XFULL + i], 1);
+        mbar_init(&b[LB_XFREE + i], 1);
+      }
       mbar_init(&b[LB_DFULL], 1);
       mbar_init(&b[LB_DFULL + 1], 1);
       mbar_init(&b[LB_DEMPTY], kEpi);
@@ -256,7 +271,8 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
   if (warp >= kCtlWarp + 2) {
     // ---------------- loader / finisher lane: input bulk copies, forward W-DFT, image store ----------------
     // (its own warp so that a late input never delays handing a finished tile on, and vice versa)
-    if (lane == 0) {
+    {
+      const uint32_t leader = elect_one();
       const int w = warp - kCtlWarp - 2;
       uint64_t* b = bars + w * LB_PER;
       uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
@@ -265,58 +281,70 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
       const int first = blockIdx.x * 2 + w;
 
       auto load_inputs = [&](int tile, uint32_t u) {
-        const int s = u & 1;
-        mbar_wait(&b[LB_DFULL + s], empty_par(u));   // the UMMAs that read slot s two tiles ago are done
-        mbar_arrive_expect_tx(&b[LB_XFULL + s], kTileBytes + z_bytes);
-        bulk_g2s(ws + L.X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[LB_XFULL + s]);
-        bulk_g2s(ws + L.Z + s * z_bytes, a.Zimg + (size_t)tile * z_bytes, z_bytes, &b[LB_XFULL + s]);
+        const int s = u % kLayerSlots;
+        mbar_wait(&b[LB_XFREE + s], ((u / kLayerSlots) & 1u) ^ 1u);   // the UMMAs that read this slot last are done
+        TR(w, u, 0);
+        mbar_arrive_expect_tx_p(leader, &b[LB_XFULL + s], kTileBytes + z_bytes);
+        bulk_g2s_p(leader, ws + L.X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[LB_XFULL + s]);
+        bulk_g2s_p(leader, ws + L.Z + s * z_bytes, a.Zimg + (size_t)tile * z_bytes, z_bytes, &b[LB_XFULL + s]);
       };
 
-      if (first < g.ntiles) load_inputs(first, 0);
-      if (first + stride < g.ntiles) load_inputs(first + stride, 1);
+      for (int i = 0; i < kLayerSlots; ++i)
+        if (first + i * stride < g.ntiles) load_inputs(first + i * stride, i);
       mbar_wait(bar_const, 0);
       uint32_t u = 0;
       for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
-        if (tile + 2 * stride < g.ntiles) load_inputs(tile + 2 * stride, u + 2);
-        ctrl_finish_tile(a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64, &b[LB_XTFULL],
-                         &b[LB_D3FULL], &b[LB_YFREE], u);
+        if (tile + kLayerSlots * stride < g.ntiles) load_inputs(tile + kLayerSlots * stride, u + kLayerSlots);
+        mbar_wait(&b[LB_XTFULL], u & 1u);
+        TR(w, u, 5);
+        ctrl_finish_tile(leader, a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64,
+                         &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], u);
+        TR(w, u, 6);
       }
       bulk_wait0();
     }
   } else if (warp >= kCtlWarp) {
     // ---------------- issuer lane: the main UMMAs, as soon as a tile's inputs and an accumulator are there ----------------
-    if (lane == 0) {
+    {
+      const uint32_t leader = elect_one();
       const int w = warp - kCtlWarp;
       uint64_t* b = bars + w * LB_PER;
       uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
       const uint32_t tmem = tmem_s + 256u * w;
       const uint32_t aG = smem_u32(smem + L.G), aW = smem_u32(smem + L.Ws);
+      const uint64_t dG = chunk_desc(aG, 128, 0), dW = chunk_desc(aW, 32, 0);
       const int first = blockIdx.x * 2 + w;
       mbar_wait(bar_const, 0);
       const uint32_t idesc = idesc_bf16(128, 32);
       const uint32_t g_lo = 128u * (uint32_t)g.KZ * 2u, z_lo = (uint32_t)g.KZ * 64u;
       uint32_t u = 0;
       for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
-        const int s = u & 1;
-        mbar_wait(&b[LB_XFULL + s], full_par(u));
-        mbar_wait(&b[LB_DEMPTY + s], empty_par(u));
+        const int s = u % kLayerSlots, db = u & 1;
+        mbar_wait(&b[LB_XFULL + s], (u / kLayerSlots) & 1u);
+        TR(w, u, 1);
+        mbar_wait(&b[LB_DEMPTY + db], empty_par(u));
+        TR(w, u, 2);
         tc_fence_after();
-        const uint32_t aX = smem_u32(ws + L.X + s * kTileBytes), aZ = smem_u32(ws + L.Z + s * z_bytes);
-        const uint32_t d = tmem + 32u * s;
+        const uint64_t dX = chunk_desc(smem_u32(ws + L.X + s * kTileBytes), 128, 0),
+                       dZ = chunk_desc(smem_u32(ws + L.Z + s * z_bytes), 32, 0);
+        const uint32_t d = tmem + 32u * db;
         uint32_t acc = 0;
 #pragma unroll
         for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
           const uint32_t ga = term == 1 ? g_lo : 0u, zb = term == 2 ? z_lo : 0u;
           const uint32_t xa = term == 1 ? (uint32_t)kImg : 0u, wb = term == 2 ? 2048u : 0u;
-          for (int k0 = 0; k0 < g.KZ; k0 += 16) {
-            umma_bf16(d, chunk_desc(aG + ga, 128, k0), chunk_desc(aZ + zb, 32, k0), idesc, acc);
+#pragma unroll 4
+          for (int k0 = 0; k0 < g.KZ; k0 += 16) {     // operand chunks: 128 (32) rows x 16 bytes per 8 K
+            umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (k0 >> 3) * 512), idesc, acc);
             acc = 1;
           }
 #pragma unroll
           for (int k0 = 0; k0 < 32; k0 += 16)
-            umma_bf16(d, chunk_desc(aX + xa, 128, k0), chunk_desc(aW + wb, 32, k0), idesc, 1);
+            umma_bf16_p(leader, d, desc_off(dX, xa + (k0 >> 3) * 2048), desc_off(dW, wb + (k0 >> 3) * 512), idesc, 1);
         }
-        umma_commit(&b[LB_DFULL + s]);
+        umma_commit_p(leader, &b[LB_DFULL + db]);
+        umma_commit_p(leader, &b[LB_XFREE + s]);
+        __syncwarp();
       }
     }
   } else {
@@ -331,6 +359,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       mbar_wait(&b[LB_DFULL + s], full_par(u));
+      if ((tid & 255) == 0) TR(w, u, 3);
       tc_fence_after();
       float2 v[8];
       {
@@ -412,6 +441,7 @@ struct MlpIssuer {
   int hid, P;
   uint32_t nc;         // chunks issued so far
   uint32_t aOnes, aW1x;   // optional bias term of the first GEMM: Ones[128,16] * W1x[hid,16]^T (0 = none)
+  uint32_t leader;        // elect_one() of the (converged) control warp
 
   template <int K1>
   __device__ __forceinline__ void mma1(uint32_t u, int p, uint32_t gp) {
@@ -420,23 +450,26 @@ struct MlpIssuer {
     if (p == 0) mbar_wait(&b[MB_A1FULL + ub], full_par(u));
     tc_fence_after();
     const uint32_t idesc = idesc_bf16(128, 64);
-    const uint32_t a_hi = aA1 + ub * a1_stride, a_lo = a_hi + 128 * K1 * 2, w_lo = aW1 + (uint32_t)hid * K1 * 2;
+    const uint32_t a_lo = 128 * K1 * 2, w_lo = (uint32_t)hid * K1 * 2;
+    const uint64_t dA = chunk_desc(aA1 + ub * a1_stride, 128, 0),
+                   dW = smem_desc(aW1 + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128);
     uint32_t acc = 0;
 #pragma unroll
     for (int term = 0; term < 3; ++term) {
-      const uint32_t aa = term == 1 ? a_lo : a_hi, ww = term == 2 ? w_lo : aW1;
+      const uint32_t ao = term == 1 ? a_lo : 0u, wo = term == 2 ? w_lo : 0u;
 #pragma unroll
       for (int k0 = 0; k0 < K1; k0 += 16) {
-        umma_bf16(tmem + 64u * db, chunk_desc(aa, 128, k0),
-                  smem_desc(ww + (uint32_t)(k0 >> 3) * hid * 16 + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128), idesc, acc);
+        umma_bf16_p(leader, tmem + 64u * db, desc_off(dA, ao + (k0 >> 3) * 2048), desc_off(dW, wo + (uint32_t)(k0 >> 3) * hid * 16),
+                    idesc, acc);
         acc = 1;
       }
     }
     if (aW1x != 0)
-      umma_bf16(tmem + 64u * db, chunk_desc(aOnes, 128, 0), smem_desc(aW1x + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128),
-                idesc, 1);
-    umma_commit(&b[MB_D1FULL + db]);
-    if (p == P - 1) umma_commit(&b[MB_A1EMPTY + ub]);
+      umma_bf16_p(leader, tmem + 64u * db, chunk_desc(aOnes, 128, 0),
+                  smem_desc(aW1x + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128), idesc, 1);
+    umma_commit_p(leader, &b[MB_D1FULL + db]);
+    if (p == P - 1) umma_commit_p(leader, &b[MB_A1EMPTY + ub]);
+    __syncwarp();
   }
 
   template <int N2>
@@ -450,18 +483,20 @@ struct MlpIssuer {
       mbar_wait(&b[MB_A2FULL + ab], full_par(nc));
       if (p == 0 && j == 0) mbar_wait(&b[MB_D2EMPTY + (u & 1)], empty_par(u));
       tc_fence_after();
-      const uint32_t a2 = aA2 + ab * kTileBytes;
       const int hcol0 = p * 64 + 32 * j;
+      const uint64_t dA = chunk_desc(aA2 + ab * kTileBytes, 128, 0), dW = chunk_desc(aW2, N2, hcol0);
 #pragma unroll
       for (int term = 0; term < 3; ++term) {
-        const uint32_t aa = term == 1 ? a2 + kImg : a2, ww = term == 2 ? w_lo : aW2;
+        const uint32_t ao = term == 1 ? (uint32_t)kImg : 0u, wo = term == 2 ? w_lo - aW2 : 0u;
 #pragma unroll
         for (int kk = 0; kk < 32; kk += 16)
-          umma_bf16(d2, chunk_desc(aa, 128, kk), chunk_desc(ww, N2, hcol0 + kk), idesc, (p | j | term | kk) != 0);
+          umma_bf16_p(leader, d2, desc_off(dA, ao + (kk >> 3) * 2048), desc_off(dW, wo + (kk >> 3) * N2 * 16), idesc,
+                      (p | j | term | kk) != 0);
       }
-      umma_commit(&b[MB_A2EMPTY + ab]);
+      umma_commit_p(leader, &b[MB_A2EMPTY + ab]);
+      __syncwarp();
     }
-    if (p == P - 1) umma_commit(&b[MB_D2FULL + (u & 1)]);
+    if (p == P - 1) umma_commit_p(leader, &b[MB_D2FULL + (u & 1)]);
   }
 };
 
@@ -554,20 +589,21 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   const int stride = gridDim.x * 2;
 
   if (warp >= kCtlWarp) {
-    if (lane == 0) {
+    {
+      const uint32_t leader = elect_one();
       const int w = warp - kCtlWarp;
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + ProjSmem::Worker + w * ProjSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + ProjSmem::X), (uint32_t)kTileBytes, smem_u32(smem + ProjSmem::W1),
                    smem_u32(smem + ProjSmem::W2), smem_u32(ws + ProjSmem::A2), tmem_s + 256u * w, hid, P, 0u,
-                   smem_u32(smem + ProjSmem::Ones), smem_u32(smem + ProjSmem::W1x)};
+                   smem_u32(smem + ProjSmem::Ones), smem_u32(smem + ProjSmem::W1x), leader};
       const int first = blockIdx.x * 2 + w;
       mbar_wait(bar_const, 0);
       auto load_x = [&](int tile, uint32_t u) {
         const int s = u & 1;
         mbar_wait(&b[MB_A1EMPTY + s], empty_par(u));
-        mbar_arrive_expect_tx(&b[MB_A1FULL + s], kTileBytes);
-        bulk_g2s(ws + ProjSmem::X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[MB_A1FULL + s]);
+        mbar_arrive_expect_tx_p(leader, &b[MB_A1FULL + s], kTileBytes);
+        bulk_g2s_p(leader, ws + ProjSmem::X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[MB_A1FULL + s]);
       };
       if (first < g.ntiles) {
         load_x(first, 0);
@@ -694,17 +730,18 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   const int stride = gridDim.x * 2;
 
   if (warp >= kCtlWarp) {
-    if (lane == 0) {
+    {
+      const uint32_t leader = elect_one();
       const int w = warp - kCtlWarp;
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
-                   smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u};
+                   smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader};
       const uint32_t aF = smem_u32(smem + LiftSmem::F), d3 = tmem_s + 256u * w + 192u;
       const int first = blockIdx.x * 2 + w;
       const bool dft = a.Aout != nullptr;
       auto finish = [&](int tile, uint32_t n) {
-        ctrl_finish_tile(dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
+        ctrl_finish_tile(leader, dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
                          &b[MB_YFREE], n);
       };
       mbar_wait(bar_const, 0);
@@ -877,3 +914,9 @@ void tc_pack_stacked_f64(const double* m, int rows, int cols, int ld, int R, int
 }
 
 }  // namespace dlwp
+
+#ifdef DLWP_TRACE
+extern "C" int dlwp_debug_set_trace(unsigned long long* p) {
+  return cudaMemcpyToSymbol(dlwp::g_trace, &p, sizeof(p)) == cudaSuccess ? 0 : -2;
+}
+#endif

@@ -16,12 +16,12 @@
 //            (bulk-copied, double buffered), Fh is read as warp-broadcast 16-byte loads
 //   phase 2  warp r: lane = output channel; X is read as warp-broadcast 16-byte loads
 //   phase 3  item = (sample, 8 grid rows h): lane = output channel; split to bf16 hi / lo and
-//            stored as 16-byte chunks, 512 contiguous bytes per warp store
+//            stored into the operand image
 //
-// Z operand image of one 128-pixel tile (RT grid rows), K index k = kx * 8 + h2 * 2 + (re | im):
-//   byte offset = part * (KZ * 64) + kx * 512 + c * 16 + (h2 * 2 + reim) * 2,   part 0 = hi, 1 = lo
-// i.e. the chunk-major [32 rows = channels] x [KZ] K-major UMMA operand of tc_common.cuh; every
-// retained column owns one 8-wide K chunk (slots >= 2 * RT stay zero).
+// Z operand image of one 128-pixel tile (RT grid rows), K index k = (kx * RT + h2) * 2 + (re | im):
+//   byte offset = part * (KZ * 64) + (k / 8) * 512 + c * 16 + (k % 8) * 2,   part 0 = hi, 1 = lo
+// i.e. the chunk-major [32 rows = channels] x [KZ] K-major UMMA operand of tc_common.cuh; a CTA
+// writes the 4 RT bytes of its column into every (tile, channel) chunk row.
 #include "tc_common.cuh"
 #include "tc_fno.cuh"
 
@@ -158,24 +158,24 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
       uint32_t hi[8], lo[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) split2(z[j].x, z[j].y, hi[j], lo[j]);
+      // K slots of this column: k = kx * 2 RT + h2 * 2 + (re|im)  ->  4 RT bytes per tile and channel
       const size_t tile0 = ((size_t)b * H + hg * 8) / RT;
       const size_t part = (size_t)a.KZ * 64;
-      uint8_t* dst = a.Zimg + tile0 * (2 * part) + (size_t)kx * 512 + lane * 16;
+      const int k0 = kx * 2 * RT;
+      uint8_t* dst = a.Zimg + tile0 * (2 * part) + (size_t)(k0 >> 3) * 512 + lane * 16 + (k0 & 7) * 2;
 #pragma unroll
       for (int t = 0; t < 8 / RT; ++t) {
-        uint4 ch, cl;
+        uint8_t* d = dst + (size_t)t * (2 * part);
         if (RT == 1) {
-          ch = make_uint4(hi[t], 0u, 0u, 0u);
-          cl = make_uint4(lo[t], 0u, 0u, 0u);
+          *reinterpret_cast<uint32_t*>(d) = hi[t];
+          *reinterpret_cast<uint32_t*>(d + part) = lo[t];
         } else if (RT == 2) {
-          ch = make_uint4(hi[2 * t], hi[2 * t + 1], 0u, 0u);
-          cl = make_uint4(lo[2 * t], lo[2 * t + 1], 0u, 0u);
+          *reinterpret_cast<uint2*>(d) = make_uint2(hi[2 * t], hi[2 * t + 1]);
+          *reinterpret_cast<uint2*>(d + part) = make_uint2(lo[2 * t], lo[2 * t + 1]);
         } else {
-          ch = make_uint4(hi[4 * t], hi[4 * t + 1], hi[4 * t + 2], hi[4 * t + 3]);
-          cl = make_uint4(lo[4 * t], lo[4 * t + 1], lo[4 * t + 2], lo[4 * t + 3]);
+          *reinterpret_cast<uint4*>(d) = make_uint4(hi[4 * t], hi[4 * t + 1], hi[4 * t + 2], hi[4 * t + 3]);
+          *reinterpret_cast<uint4*>(d + part) = make_uint4(lo[4 * t], lo[4 * t + 1], lo[4 * t + 2], lo[4 * t + 3]);
         }
-        *reinterpret_cast<uint4*>(dst + (size_t)t * (2 * part)) = ch;
-        *reinterpret_cast<uint4*>(dst + (size_t)t * (2 * part) + part) = cl;
       }
     }
     // no barrier here: the next pass writes sX only after every warp left phase 2 (second

@@ -25,9 +25,9 @@ int plan_tc_build(dlwp_plan* p) {
     return DLWP_OK;
   if (p->Cin < 1 || p->Cin > 15 || d.prognostic_channels > 16) return DLWP_OK;
   // fno_mid_kernel: one warp per retained row, 8 grid rows per output item; the layer kernel's
-  // inverse W-DFT operands (8 K slots per retained column) must fit beside its tile buffers
-  const int KZ = (8 * Kc + 15) & ~15;
-  if (d.n_rows > 16 || H % 8 != 0 || KZ > 64 || tc_mid_smem_bytes(H, d.n_rows) > 220 * 1024) return DLWP_OK;
+  // inverse W-DFT operands (2 K slots per retained column and grid row of the tile) must fit beside its tile buffers
+  const int KZ = (2 * RT * Kc + 15) & ~15;
+  if (d.n_rows > 16 || H % 8 != 0 || KZ > 48 || tc_mid_smem_bytes(H, d.n_rows) > 220 * 1024) return DLWP_OK;
 
   p->tcg = TcGeom{0, H * W, H, W, RT, KXP, Kc, KZ};
   double s = 1.0, t = 1.0;
@@ -38,7 +38,7 @@ int plan_tc_build(dlwp_plan* p) {
 
   // inverse W-DFT operand G'[(h2, w), (kx, h2', re|im)]: y[w] = sum_kx Re(Gw[w, kx] * Z[kx]) with
   // Gw = t * c_kx * exp(+2 pi i kx w / W) (c = 1 for the self-conjugate columns, else 2), K index
-  // kx * 8 + h2' * 2 + (re|im) as fno_mid_kernel lays Z' out;
+  // (kx * RT + h2') * 2 + (re|im) as fno_mid_kernel lays Z' out;
   // forward operand F''[(h2, kx'), (h2', w)] with Fw = s * exp(-2 pi i kx w / W)
   std::vector<double> G((size_t)128 * KZ, 0.0), F((size_t)32 * 128, 0.0);
   for (int h2 = 0; h2 < RT; ++h2)
@@ -48,7 +48,7 @@ int plan_tc_build(dlwp_plan* p) {
         const double ang = 2.0 * M_PI * (double)r / (double)W;
         const bool self_conj = (kx == 0) || (W % 2 == 0 && kx == W / 2);
         const double ck = t * (self_conj ? 1.0 : 2.0);
-        const int m = h2 * W + w, k = h2 * KXP + 2 * kx, kz = kx * 8 + h2 * 2;
+        const int m = h2 * W + w, k = h2 * KXP + 2 * kx, kz = kx * 2 * RT + h2 * 2;
         G[(size_t)m * KZ + kz] = ck * std::cos(ang);
         G[(size_t)m * KZ + kz + 1] = -ck * std::sin(ang);
         F[(size_t)k * 128 + m] = s * std::cos(ang);
@@ -65,8 +65,8 @@ int plan_tc_build(dlwp_plan* p) {
   const size_t img = (size_t)d.max_batch * H * W * kTcC * 4;
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_img[0], img));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_img[1], img));
-  // Z' operand images: fno_mid_kernel writes whole 16-byte chunks of the retained columns; the
-  // chunks that pad K to a multiple of 16 stay zero from here on
+  // Z' operand images: fno_mid_kernel writes the K slots of the retained columns; the slots that
+  // pad K to a multiple of 16 stay zero from here on
   const size_t zimg = (size_t)d.max_batch * H * W / kTcTile * KZ * 128;
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_Z, zimg));
   DLWP_CUDA(cudaMemset(p->tc_Z, 0, zimg));
