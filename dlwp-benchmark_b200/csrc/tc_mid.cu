@@ -47,7 +47,9 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
   const int H = a.H, R = a.R, Rp = (R + 3) & ~3, Kc = a.Kc, B = a.B;
   const int kx = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
-  const int nquads = (B + kNB - 1) / kNB;
+  // this CTA's contiguous share of the samples (balanced to within one), in passes of up to kNB
+  const int per = B / nchunks, rem = B % nchunks;
+  const int b_lo = chunk * per + (chunk < rem ? chunk : rem), b_hi = b_lo + per + (chunk < rem ? 1 : 0);
 
   float* sA = reinterpret_cast<float*>(smem);              // [2][kNB][H][re|im][32]
   float2* sX = reinterpret_cast<float2*>(smem) + 2 * kNB * H * 32;   // [kNB][Rp][32]
@@ -61,16 +63,15 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     fence_mbar_init();
   }
   __syncthreads();
-  auto issue_load = [&](int q, int s) {   // warp 0: the (sample, kx) slabs of quad q -> stage s
-    const int b0 = q * kNB;
-    const int nb = B - b0 < kNB ? B - b0 : kNB;
+  auto issue_load = [&](int b0, int s) {   // warp 0: the (sample, kx) slabs of samples b0.. -> stage s
+    const int nb = b_hi - b0 < kNB ? b_hi - b0 : kNB;
     if (lane == 0) mbar_arrive_expect_tx(&bars[s], (uint32_t)(nb * H * 256));
     __syncwarp();
     if (lane < nb)
       bulk_g2s(sA + (size_t)(s * kNB + lane) * H * 64, a.A + ((size_t)(b0 + lane) * Kc + kx) * H * 64, (uint32_t)(H * 256),
                &bars[s]);
   };
-  if (warp == 0 && chunk < nquads) issue_load(chunk, 0);
+  if (warp == 0 && b_lo < b_hi) issue_load(b_lo, 0);
 
   for (int i = tid; i < H * Rp; i += blockDim.x) {
     const int h = i / Rp, r = i - h * Rp;
@@ -90,14 +91,15 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   __syncthreads();
 
   uint32_t p = 0;
-  for (int q = chunk; q < nquads; q += nchunks, ++p) {
+  for (int b0 = b_lo; b0 < b_hi; b0 += kNB, ++p) {
     const int s = p & 1;
-    if (warp == 0 && q + nchunks < nquads) issue_load(q + nchunks, s ^ 1);
+    const int nb = b_hi - b0 < kNB ? b_hi - b0 : kNB;
+    if (warp == 0 && b0 + kNB < b_hi) issue_load(b0 + kNB, s ^ 1);
     mbar_wait(&bars[s], (p >> 1) & 1u);
 
     // ---- phase 1: forward H-DFT, 4 retained rows per item ----
     const int ngrp = Rp >> 2;
-    for (int item = warp; item < kNB * ngrp; item += nw) {
+    for (int item = warp; item < nb * ngrp; item += nw) {
       const int bl = item / ngrp, rg = item - bl * ngrp;
       const float* Ab = sA + (size_t)(s * kNB + bl) * H * 64 + lane;
       const float4* F4 = reinterpret_cast<const float4*>(sF) + rg * 2;
@@ -122,6 +124,7 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     if (warp < R) {
 #pragma unroll
       for (int bl = 0; bl < kNB; ++bl) {
+        if (bl >= nb) break;
         const float4* X4 = reinterpret_cast<const float4*>(sX + (bl * Rp + warp) * 32);
         float2 y = make_float2(0.f, 0.f);
 #pragma unroll
@@ -137,10 +140,9 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
 
     // ---- phase 3: inverse H-DFT, 8 grid rows per item, split-bf16 operand image out ----
     const int nhg = H >> 3;
-    for (int item = warp; item < kNB * nhg; item += nw) {
+    for (int item = warp; item < nb * nhg; item += nw) {
       const int bl = item / nhg, hg = item - bl * nhg;
-      const int b = q * kNB + bl;
-      if (b >= B) continue;
+      const int b = b0 + bl;
       const float2* Yb = sY + bl * R * 32 + lane;
       float2 z[8];
 #pragma unroll
@@ -201,13 +203,10 @@ int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.R >= 1 && a.R <= 16 && a.H % 8 == 0 && a.Kc >= 1, "fno_mid_kernel: unsupported geometry R=%d H=%d", a.R, a.H);
   const size_t smem = tc_mid_smem_bytes(a.H, a.R);
   DLWP_REQUIRE(smem <= 220 * 1024, "fno_mid_kernel: %zu bytes of shared memory needed", smem);
-  const int nquads = (a.B + kNB - 1) / kNB;
+  // one CTA per SM at most; every CTA takes a contiguous, balanced share of the samples
   int nchunks = sms / a.Kc;
   if (nchunks < 1) nchunks = 1;
-  if (nchunks > nquads) nchunks = nquads;
-  // every CTA runs ceil(nquads / nchunks) passes at most: do not use more CTAs than that needs
-  const int passes = (nquads + nchunks - 1) / nchunks;
-  nchunks = (nquads + passes - 1) / passes;
+  if (nchunks > a.B) nchunks = a.B;
   const dim3 grid((unsigned)a.Kc, (unsigned)nchunks);
   const int threads = 32 * (a.R < 4 ? 4 : a.R);
   const int slot = a.RT == 1 ? 0 : (a.RT == 2 ? 1 : 2);

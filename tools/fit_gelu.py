@@ -53,7 +53,8 @@ def check(coef):
 
 
 if __name__ == "__main__":
-    for deg in (6, 7, 8, 9, 10):
+    # the kernels use degree 5: positive leading coefficient, so no clamp of the argument is needed
+    for deg in (5, 6, 7, 8):
         coef = fit(deg)
         e, at = check(coef)
         print(f"deg {deg}: max |gelu err| = {e:.3e} at x = {at:.3f}")
