@@ -149,6 +149,14 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
+// ---- programmatic dependent launch ------------------------------------------------------------
+// The kernels of one model evaluation form a chain on one stream.  Each one lets its successor
+// start launching at once (its CTAs become resident as SMs free up and run their prologue:
+// barrier init, TMEM allocation, constant operands) and itself waits for its predecessor's
+// memory before it touches anything that predecessor wrote -- or writes anything it read.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- warp-uniform control code ---------------------------------------------------------------
 // The control warps run converged: every lane computes the same addresses and descriptors (so
 // they live in uniform registers) and waits on the same barriers; the instructions that must be
@@ -215,4 +223,20 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
 }
 
 }  // namespace tc
+
+// host: launch `kern` with programmatic stream serialization (see pdl_wait above)
+template <class Args>
+inline cudaError_t launch_pdl(void (*kern)(Args), dim3 grid, dim3 block, size_t smem, cudaStream_t st, const Args& args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, args);
+}
 }  // namespace dlwp

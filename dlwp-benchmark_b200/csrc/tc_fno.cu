@@ -224,6 +224,7 @@ enum { LB_XFULL = 0, LB_XFREE = 3, LB_DFULL = 6, LB_DEMPTY = 8, LB_XTFULL = 10, 
 
 __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
   __shared__ uint64_t bars[2 * LB_PER + 1];
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -258,6 +259,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const uint32_t g_bytes = 2u * 128u * (uint32_t)g.KZ * 2u, z_bytes = (uint32_t)g.KZ * 128u;
   if (tid == 0) {
     mbar_arrive_expect_tx(bar_const, g_bytes + kFBytes + 4096);
@@ -397,7 +399,7 @@ int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
-  fno_layer_kernel<<<grid, kCtaLayer, L.Total, st>>>(a);
+  DLWP_CUDA(launch_pdl(fno_layer_kernel, dim3(grid), dim3(kCtaLayer), (size_t)L.Total, st, a));
   DLWP_LAUNCHED("fno_layer_kernel");
   return DLWP_OK;
 }
@@ -551,6 +553,7 @@ struct ProjSmem {   // sized for hid = 256
 
 __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
   __shared__ uint64_t bars[2 * MB_PER + 1];
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -578,6 +581,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const uint32_t w1_bytes = (uint32_t)hid * 32 * 4, w2_bytes = 16u * hid * 4, w1x_bytes = (uint32_t)hid * 16 * 2;
   if (tid == 0) {
     mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + w1x_bytes);
@@ -666,7 +670,7 @@ int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.hid == 128 || a.hid == 256, "tensor-core projection needs width 128 or 256, got %d", a.hid);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
-  fno_proj_kernel<<<grid, kCta, ProjSmem::Total, st>>>(a);
+  DLWP_CUDA(launch_pdl(fno_proj_kernel, dim3(grid), dim3(kCta), (size_t)ProjSmem::Total, st, a));
   DLWP_LAUNCHED("fno_proj_kernel");
   return DLWP_OK;
 }
@@ -685,6 +689,7 @@ struct LiftSmem {   // sized for hid = 256
 
 __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
   __shared__ uint64_t bars[2 * MB_PER + 1];
   __shared__ uint32_t tmem_s;
   __shared__ const float* kptr[16];     // per input channel: plane base and batch stride
@@ -719,6 +724,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const uint32_t w1_bytes = (uint32_t)hid * 16 * 4, w2_bytes = 32u * hid * 4;
   if (tid == 0) {
     mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + kFBytes);
@@ -838,7 +844,7 @@ int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 15 && a.ngrp >= 1, "tensor-core lifting needs 1..15 input channels, got %d", a.Cin);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
-  fno_lift_kernel<<<grid, kCta, LiftSmem::Total, st>>>(a);
+  DLWP_CUDA(launch_pdl(fno_lift_kernel, dim3(grid), dim3(kCta), (size_t)LiftSmem::Total, st, a));
   DLWP_LAUNCHED("fno_lift_kernel");
   return DLWP_OK;
 }

@@ -44,6 +44,7 @@ template <int RT>
 __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bars[2];
+  pdl_launch_dependents();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
   const int H = a.H, R = a.R, Rp = (R + 3) & ~3, Kc = a.Kc, B = a.B;
   const int kx = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
@@ -62,7 +63,6 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     mbar_init(&bars[1], 1);
     fence_mbar_init();
   }
-  __syncthreads();
   auto issue_load = [&](int b0, int s) {   // warp 0: the (sample, kx) slabs of samples b0.. -> stage s
     const int nb = b_hi - b0 < kNB ? b_hi - b0 : kNB;
     if (lane == 0) mbar_arrive_expect_tx(&bars[s], (uint32_t)(nb * H * 256));
@@ -71,8 +71,6 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
       bulk_g2s(sA + (size_t)(s * kNB + lane) * H * 64, a.A + ((size_t)(b0 + lane) * Kc + kx) * H * 64, (uint32_t)(H * 256),
                &bars[s]);
   };
-  if (warp == 0 && b_lo < b_hi) issue_load(b_lo, 0);
-
   for (int i = tid; i < H * Rp; i += blockDim.x) {
     const int h = i / Rp, r = i - h * Rp;
     sF[i] = r < R ? a.Fh[r * H + h] : make_float2(0.f, 0.f);
@@ -89,6 +87,8 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     for (int i = 0; i < 32; ++i) w[i] = wp[i * 32];
   }
   __syncthreads();
+  pdl_wait();   // the spectrum below comes from the previous kernel; Zimg is read by it
+  if (warp == 0 && b_lo < b_hi) issue_load(b_lo, 0);
 
   uint32_t p = 0;
   for (int b0 = b_lo; b0 < b_hi; b0 += kNB, ++p) {
@@ -218,15 +218,15 @@ int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
   switch (a.RT) {
     case 1:
       DLWP_CUDA(set_smem(fno_mid_kernel<1>));
-      fno_mid_kernel<1><<<grid, threads, smem, st>>>(a);
+      DLWP_CUDA(launch_pdl(fno_mid_kernel<1>, grid, dim3(threads), smem, st, a));
       break;
     case 2:
       DLWP_CUDA(set_smem(fno_mid_kernel<2>));
-      fno_mid_kernel<2><<<grid, threads, smem, st>>>(a);
+      DLWP_CUDA(launch_pdl(fno_mid_kernel<2>, grid, dim3(threads), smem, st, a));
       break;
     case 4:
       DLWP_CUDA(set_smem(fno_mid_kernel<4>));
-      fno_mid_kernel<4><<<grid, threads, smem, st>>>(a);
+      DLWP_CUDA(launch_pdl(fno_mid_kernel<4>, grid, dim3(threads), smem, st, a));
       break;
     default:
       return fail(DLWP_ERR_INVALID, "fno_mid_kernel: %d grid rows per tile", a.RT);
