@@ -332,6 +332,8 @@ def run_ours(args, wl):
     clim = (0.3 * torch.randn(Cg, H, W, generator=torch.Generator().manual_seed(7))).to(dev)
     const, presc, prog = (None if t is None else t.to(dev) for t in (const_h, presc_h, prog_h))
     in_bytes = sum(t.numel() * 4 for t in (const_h, presc_h, prog_h) if t is not None)
+    # what dlwp_rollout_host copies: constants, prescribed, and the first ctx frames of prognostic
+    h2d_bytes = sum(t.numel() * 4 for t in (const_h, presc_h) if t is not None) + members * ctx * Cg * H * W * 4
     out_bytes = members * lead * Cg * H * W * 4
     flush = None if in_bytes > 126e6 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream(dev)
@@ -415,9 +417,11 @@ def run_ours(args, wl):
                       "bf16": "bf16"}[args.precision],
             "data": "synthetic N(0,1) fields, random-init weights (seed 1234)",
             "config": config_block(args, wl, members),
-            "e2e": {"value": units / e2e_s, "unit": "samples*steps/s", "h2d_bytes_per_step": in_bytes,
+            "e2e": {"value": units / e2e_s, "unit": "samples*steps/s", "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": out_bytes, "ms_per_step": e2e_s / args.steps * 1e3,
-                    "api": "dlwp_rollout_host (pinned host buffers; whole forecast copied back)"},
+                    "api": "dlwp_rollout_host (pinned host buffers in the reference's [B,T,C,H,W] layout; copies in "
+                           "constants, prescribed and the ctx prognostic frames the loop reads, copies the whole "
+                           "forecast back frame by frame under the following steps' compute)"},
             "gpu_launches": launches,
             "roofline": roof,
             "step_roofline": {"algorithmic_bytes_per_rollout": sb * lead, "achieved_gbs": sb * lead / (ms_step * 1e-3) / 1e9,

@@ -32,6 +32,8 @@ void free_plan(dlwp_plan* p) {
   for (auto& kv : p->tensors) cudaFree(kv.second.data);
   for (int i = 0; i < 4; ++i)
     if (p->stage[i]) cudaFree(p->stage[i]);
+  for (cudaEvent_t e : p->step_done) cudaEventDestroy(e);
+  if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
   delete p;
 }
 
@@ -181,21 +183,52 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
   const dlwp_model_desc& d = plan->d;
   DLWP_REQUIRE(batch > 0 && batch <= d.max_batch, "batch %d outside [1, max_batch=%d]", batch, d.max_batch);
   DLWP_REQUIRE(T > d.context_size, "sequence length %d must exceed context_size %d", T, d.context_size);
+  DLWP_REQUIRE((d.constant_channels == 0) == (constants == nullptr),
+               "constants pointer does not match constant_channels=%d", d.constant_channels);
+  DLWP_REQUIRE((d.prescribed_channels == 0) == (prescribed == nullptr),
+               "prescribed pointer does not match prescribed_channels=%d", d.prescribed_channels);
   DLWP_CUDA(cudaSetDevice(plan->device));
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t HW = (size_t)d.height * d.width, B = (size_t)batch;
-  const size_t nb[4] = {constants ? B * d.constant_channels * HW * sizeof(float) : 0,
-                        prescribed ? B * T * d.prescribed_channels * HW * sizeof(float) : 0,
-                        B * T * d.prognostic_channels * HW * sizeof(float),
-                        B * (T - d.context_size) * d.prognostic_channels * HW * sizeof(float)};
-  const void* src[3] = {constants, prescribed, prognostic};
+  const size_t HW = (size_t)d.height * d.width, B = (size_t)batch, frame = HW * sizeof(float);
+  const int ctx = d.context_size, steps = T - ctx;
+  const size_t nb[4] = {constants ? B * d.constant_channels * frame : 0,
+                        prescribed ? B * T * d.prescribed_channels * frame : 0,
+                        B * T * d.prognostic_channels * frame,
+                        B * steps * d.prognostic_channels * frame};
   for (int i = 0; i < 4; ++i) DLWP_TRY(grow(plan, i, nb[i]));
-  for (int i = 0; i < 3; ++i)
-    if (nb[i]) DLWP_CUDA(cudaMemcpyAsync(plan->stage[i], src[i], nb[i], cudaMemcpyHostToDevice, st));
-  DLWP_TRY(dlwp_rollout(plan, constants ? (const float*)plan->stage[0] : nullptr,
-                        prescribed ? (const float*)plan->stage[1] : nullptr, (const float*)plan->stage[2], batch, T,
-                        (float*)plan->stage[3], stream));
-  DLWP_CUDA(cudaMemcpyAsync(outs, plan->stage[3], nb[3], cudaMemcpyDeviceToHost, st));
+  if (!plan->copy_stream) DLWP_CUDA(cudaStreamCreateWithFlags(&plan->copy_stream, cudaStreamNonBlocking));
+  while ((int)plan->step_done.size() < steps + 1) {
+    cudaEvent_t e = nullptr;
+    DLWP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    plan->step_done.push_back(e);
+  }
+  // host -> device: only what the loop reads.  Of `prognostic` that is the first `ctx` frames of
+  // every sample (fno.py:83,91-95 never look at later ground-truth frames), kept at their place
+  // in the [B, T, Cg, H, W] staging layout so the frame bookkeeping is the device entry's.
+  if (nb[0]) DLWP_CUDA(cudaMemcpyAsync(plan->stage[0], constants, nb[0], cudaMemcpyHostToDevice, st));
+  if (nb[1]) DLWP_CUDA(cudaMemcpyAsync(plan->stage[1], prescribed, nb[1], cudaMemcpyHostToDevice, st));
+  const size_t prog_pitch = (size_t)T * d.prognostic_channels * frame;
+  DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[2], prog_pitch, prognostic, prog_pitch, (size_t)ctx * d.prognostic_channels * frame, B,
+                              cudaMemcpyHostToDevice, st));
+  // the loop of dlwp_rollout; every lead time's frame starts its way back to the host on a second
+  // stream as soon as its projection kernel is done, under the following steps' compute
+  float* dev_outs = (float*)plan->stage[3];
+  const size_t out_pitch = (size_t)steps * d.prognostic_channels * frame, out_row = (size_t)d.prognostic_channels * frame;
+  for (int t = ctx; t < T; ++t) {
+    StepIO io;
+    rollout_io(plan, constants ? (const float*)plan->stage[0] : nullptr, prescribed ? (const float*)plan->stage[1] : nullptr,
+               (const float*)plan->stage[2], dev_outs, T, t, &io);
+    DLWP_TRY(plan_backbone(plan, io, batch, st));
+    cudaEvent_t ev = plan->step_done[t - ctx];
+    DLWP_CUDA(cudaEventRecord(ev, st));
+    DLWP_CUDA(cudaStreamWaitEvent(plan->copy_stream, ev, 0));
+    const size_t off = (size_t)(t - ctx) * d.prognostic_channels * HW;
+    DLWP_CUDA(cudaMemcpy2DAsync(outs + off, out_pitch, dev_outs + off, out_pitch, out_row, B, cudaMemcpyDeviceToHost,
+                                plan->copy_stream));
+  }
+  cudaEvent_t fin = plan->step_done[steps];
+  DLWP_CUDA(cudaEventRecord(fin, plan->copy_stream));
+  DLWP_CUDA(cudaStreamWaitEvent(st, fin, 0));
   DLWP_CUDA(cudaStreamSynchronize(st));
   return DLWP_OK;
 }

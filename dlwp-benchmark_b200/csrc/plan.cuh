@@ -67,6 +67,8 @@ struct dlwp_plan {
   // host-entry staging (dlwp_rollout_host)
   void* stage[4] = {nullptr, nullptr, nullptr, nullptr};
   size_t stage_bytes[4] = {0, 0, 0, 0};
+  cudaStream_t copy_stream = nullptr;        // device -> host frames, under the following steps' compute
+  std::vector<cudaEvent_t> step_done;        // one per lead time + one for the end of the copies
 };
 
 namespace dlwp {

@@ -126,9 +126,12 @@ int dlwp_step(dlwp_plan* plan, const float* x, float* y, int batch, void* stream
 int dlwp_rollout(dlwp_plan* plan, const float* constants, const float* prescribed,
                  const float* prognostic, int batch, int T, float* outs, void* stream);
 
-/* Same call with HOST buffers (pinned or pageable): copies inputs to plan-owned staging,
- * runs the rollout, copies outs back and synchronises `stream`.  This is the entry the
- * end-to-end benchmark times.  May grow the staging buffers on first use. */
+/* Same call with HOST buffers (pinned or pageable; what scripts/evaluate.py:214-217,235-243 does
+ * around the model): copies to plan-owned staging what the loop reads -- constants, prescribed and
+ * the first `ctx` frames of prognostic (later ground-truth frames are never read, fno.py:83,91-95)
+ * --, runs the rollout, copies every lead time's frame back on a second stream while the next
+ * steps compute, and synchronises `stream`.  This is the entry the end-to-end benchmark times.
+ * May grow the staging buffers on first use. */
 int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* prescribed,
                       const float* prognostic, int batch, int T, float* outs, void* stream);
 
