@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
   pdl_launch_dependents();
   __shared__ uint64_t bars[2 * LB_PER + 1];
   __shared__ uint32_t tmem_s;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform
   const TcGeom g = a.g;
   const LayerSmem L(g.KZ);
   float* sBias = reinterpret_cast<float*>(smem + L.Bias);
@@ -556,7 +556,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   pdl_launch_dependents();
   __shared__ uint64_t bars[2 * MB_PER + 1];
   __shared__ uint32_t tmem_s;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform
   const TcGeom g = a.g;
   const int hid = a.hid, P = hid / 64;
   float* sB2 = reinterpret_cast<float*>(smem + ProjSmem::B2);
@@ -694,7 +694,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   __shared__ uint32_t tmem_s;
   __shared__ const float* kptr[16];     // per input channel: plane base and batch stride
   __shared__ long long kbs[16];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform
   const TcGeom g = a.g;
   const int hid = a.hid, P = hid / 64;
   float* sB2 = reinterpret_cast<float*>(smem + LiftSmem::B2);
