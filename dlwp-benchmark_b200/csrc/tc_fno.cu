@@ -44,6 +44,33 @@ __device__ __forceinline__ float2 gelu2(float2 x) {
   return __ffma2_rn(a, t, hx);
 }
 
+// The same on eight pairs in lock step (eight independent dependency chains in flight), returning
+// TWICE the GELU: 2 gelu(x) = x + |x| (1 - 2 * 2^(-h)); the consumer GEMM's weights carry the 1/2
+// (exact), which saves the x/2 multiply.
+__device__ __forceinline__ void gelu2x_8(const uint32_t (&r)[16], float2 (&g)[8]) {
+  float2 x[8], p[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) x[e] = make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]));
+#pragma unroll
+  for (int e = 0; e < 8; ++e)
+    p[e] = __ffma2_rn(make_float2(-4.732980128e-04f, -4.732980128e-04f), make_float2(fabsf(x[e].x), fabsf(x[e].y)),
+                      make_float2(7.084488528e-03f, 7.084488528e-03f));
+  const float c[4] = {-5.182723514e-02f, -4.599925752e-01f, -1.150787801e+00f, -1.000037628e+00f};
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) p[e] = __ffma2_rn(p[e], make_float2(fabsf(x[e].x), fabsf(x[e].y)), make_float2(c[k], c[k]));
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p[e].x) : "f"(p[e].x));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p[e].y) : "f"(p[e].y));
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) p[e] = __ffma2_rn(p[e], make_float2(-2.0f, -2.0f), make_float2(1.0f, 1.0f));
+#pragma unroll
+  for (int e = 0; e < 8; ++e) g[e] = __ffma2_rn(make_float2(fabsf(x[e].x), fabsf(x[e].y)), p[e], x[e]);
+}
+
 // v = hi + lo for a pair, residual through one packed FMA
 __device__ __forceinline__ void split2p(float2 v, uint32_t& hi, uint32_t& lo) {
   __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
@@ -520,9 +547,12 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
         mbar_arrive(&b[MB_D1EMPTY + db]);
       }
       uint32_t h[8], l[8];
+      {
+        float2 g2[8];             // 2 * gelu: W2's operand image is packed with the factor 1/2
+        gelu2x_8(r, g2);
 #pragma unroll
-      for (int e = 0; e < 8; ++e)
-        split2p(gelu2(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]))), h[e], l[e]);
+        for (int e = 0; e < 8; ++e) split2p(g2[e], h[e], l[e]);
+      }
       const int ab = nc & 1;
       mbar_wait(&b[MB_A2EMPTY + ab], empty_par(nc));
       uint8_t* dst = sA2 + ab * kTileBytes + id.row * 16 + id.half * 4096;

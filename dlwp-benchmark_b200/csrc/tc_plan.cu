@@ -114,7 +114,9 @@ int plan_tc_commit(dlwp_plan* p, cudaStream_t st) {
     tc_pack_images(m.data(), L, 16, 16, L, 16, img.data());
     DLWP_TRY(upload(p->tc_liftW1, img));
   }
+  // the MLP epilogues hand 2 * gelu(hidden) to the second GEMM (tc_fno.cu: gelu2x_8): its weights carry the 1/2
   DLWP_TRY(fetch(p, "lifting.fcs.1.weight", (int64_t)kTcC * L, &w));
+  for (float& v : w) v *= 0.5f;
   img.assign((size_t)32 * L * 4, 0);
   tc_pack_images(w.data(), kTcC, L, L, 32, L, img.data());
   DLWP_TRY(upload(p->tc_liftW2, img));
@@ -133,6 +135,7 @@ int plan_tc_commit(dlwp_plan* p, cudaStream_t st) {
   tc_pack_bias_image(b.data(), Pj, Pj, img.data());
   DLWP_TRY(upload(p->tc_projW1x, img));
   DLWP_TRY(fetch(p, "projection.fcs.1.weight", (int64_t)Cg * Pj, &w));
+  for (float& v : w) v *= 0.5f;
   img.assign((size_t)16 * Pj * 4, 0);
   tc_pack_images(w.data(), Cg, Pj, Pj, 16, Pj, img.data());
   DLWP_TRY(upload(p->tc_projW2, img));
