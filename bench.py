@@ -143,7 +143,8 @@ def step_flops(cls, kw, B, H, W):
         dfth = 8 * B * C * m2 * H * m1
         mix = 8 * B * C * C * m1 * m2
         spectral = 2 * dftw + 2 * dfth + mix
-        return {"step": lift + proj + N * (spectral + 2 * B * S * C * C), "spectral_block": spectral}
+        return {"step": lift + proj + N * (spectral + 2 * B * S * C * C), "spectral_block": spectral,
+                "spectral_mid": 2 * dfth + mix}
     p1, p2 = kw["patch_size"]
     h, w = H // p1, W // p2
     E, nb = kw["embed_dim"], kw["num_blocks"]
@@ -288,6 +289,26 @@ def config_block(args, wl, members):
 # ----------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` summary (profiles/), or None."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "r01_ncu_full_tc_v2.csv")
+    try:
+        with open(path) as f:
+            rows = list(csv.reader(f))
+        hdr = rows[0]
+        kn, rd, wr = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot, n = 0.0, 0
+        for r in rows[2:]:
+            if kernel in r[kn]:
+                tot += float(r[rd]) * unit[rows[1][rd]] + float(r[wr]) * unit[rows[1][wr]]
+                n += 1
+        return tot / n if n else None
+    except (OSError, ValueError, KeyError, IndexError):
+        return None
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -404,10 +425,17 @@ def run_ours(args, wl):
             roof["achieved"] = per_launch / (kms / kn * 1e-3) / 1e9
             roof["frac"] = roof["achieved"] / hbm_peak
             roof["algorithmic_bytes_per_launch"] = per_launch
+        if args.workload == "c4" and members == members_default:
+            roof["traffic"] = ncu_traffic(name)
+            roof["traffic_source"] = "profiles/r01_ncu_full_tc_v2.csv (ncu --set full of this command, mean over the kernel's launches)"
         fl = step_flops(cls, kw, members, H, W)
         sb = step_bytes(cls, kw, members, H, W)
         spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel")]
         spec_ms = sum(entries[n][0] for n in spec_names)
+        # on the tensor-core path the W-DFTs of the spectral block run inside the lift / layer kernels; the
+        # separately timed part is the mid kernel (H-DFT, mode mixing, inverse H-DFT): count only its flops
+        fused_w = "fno_mid_kernel" in entries
+        spec_flops = fl["spectral_mid"] if fused_w and "spectral_mid" in fl else fl["spectral_block"]
         layers = kw.get("n_layers", kw.get("depth"))
         line = {
             "metric": "rollout samples*steps/s", "value": units / (ms_total * 1e-3), "unit": "samples*steps/s",
@@ -427,8 +455,11 @@ def run_ours(args, wl):
             "step_roofline": {"algorithmic_bytes_per_rollout": sb * lead, "achieved_gbs": sb * lead / (ms_step * 1e-3) / 1e9,
                               "frac_of_hbm_peak": sb * lead / (ms_step * 1e-3) / 1e9 / hbm_peak,
                               "tflops": fl["step"] * lead / (ms_step * 1e-3) / 1e12},
-            "spectral_block": {"kernels": spec_names, "tflops": (fl["spectral_block"] * layers * lead / (spec_ms * 1e-3) / 1e12)
+            "spectral_block": {"kernels": spec_names, "tflops": (spec_flops * layers * lead / (spec_ms * 1e-3) / 1e12)
                                if spec_ms > 0 else None, "peak_tflops": tc_peak,
+                               "flops_counted": ("H-DFT + mode mixing + inverse H-DFT (fp32 FMA in fno_mid_kernel); the W-DFT "
+                                                 "GEMMs of the block run on tcgen05 inside fno_lift / fno_layer_kernel"
+                                                 if fused_w else "whole spectral block (truncated-DFT-GEMM count)"),
                                "note": "profiled pass; includes the events' launch gaps"},
             "kernel_ms_per_rollout": {n: round(v[0], 4) for n, v in sorted(entries.items(), key=lambda kv: -kv[1][0])},
             "clocks": clk.summary(),

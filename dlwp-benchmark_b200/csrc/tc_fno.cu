@@ -10,7 +10,7 @@ namespace dlwp {
 using namespace tc;
 
 #ifdef DLWP_TRACE
-__device__ unsigned long long* g_trace = nullptr;
+__device__ unsigned long long* g_trace = nullptr;   // also used by tc_mid.cu
 #define TR(w, u, ev) do { if (g_trace && blockIdx.x == 0 && (u) < 16) g_trace[((w) * 16 + (u)) * 8 + (ev)] = clock64(); } while (0)
 #else
 #define TR(w, u, ev) do {} while (0)

@@ -29,6 +29,13 @@ namespace dlwp {
 
 using namespace tc;
 
+#ifdef DLWP_TRACE
+__device__ unsigned long long* g_trace_mid = nullptr;
+#define TRM(p, ev) do { if (g_trace_mid && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 32 && (p) < 8) g_trace_mid[(p) * 8 + (ev)] = clock64(); } while (0)
+#else
+#define TRM(p, ev) do {} while (0)
+#endif
+
 namespace {
 
 constexpr int kNB = kTcMidSamples;   // samples per pass
@@ -45,6 +52,7 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bars[2];
   pdl_launch_dependents();
+  TRM(0, 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
   const int H = a.H, R = a.R, Rp = (R + 3) & ~3, Kc = a.Kc, B = a.B;
   const int kx = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
@@ -87,7 +95,9 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     for (int i = 0; i < 32; ++i) w[i] = wp[i * 32];
   }
   __syncthreads();
+  TRM(0, 1);
   pdl_wait();   // the spectrum below comes from the previous kernel; Zimg is read by it
+  TRM(0, 2);
   if (warp == 0 && b_lo < b_hi) issue_load(b_lo, 0);
 
   uint32_t p = 0;
@@ -95,7 +105,9 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     const int s = p & 1;
     const int nb = b_hi - b0 < kNB ? b_hi - b0 : kNB;
     if (warp == 0 && b0 + kNB < b_hi) issue_load(b0 + kNB, s ^ 1);
+    TRM(p + 1, 0);
     mbar_wait(&bars[s], (p >> 1) & 1u);
+    TRM(p + 1, 1);
 
     // ---- phase 1: forward H-DFT, 4 retained rows per item ----
     const int ngrp = Rp >> 2;
@@ -119,6 +131,7 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
       for (int j = 0; j < 4; ++j) sX[(bl * Rp + rg * 4 + j) * 32 + lane] = acc[j];
     }
     __syncthreads();
+    TRM(p + 1, 2);
 
     // ---- phase 2: per-mode channel mixing with the register-resident weights ----
     if (warp < R) {
@@ -137,6 +150,7 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
       }
     }
     __syncthreads();
+    TRM(p + 1, 3);
 
     // ---- phase 3: inverse H-DFT, 8 grid rows per item, split-bf16 operand image out ----
     const int nhg = H >> 3;
@@ -147,6 +161,7 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
       float2 z[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) z[j] = make_float2(0.f, 0.f);
+#pragma unroll 4
       for (int r = 0; r < R; ++r) {
         const float2 y = Yb[r * 32];
         const float4* G4 = reinterpret_cast<const float4*>(sG + r * H + hg * 8);
@@ -180,6 +195,7 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
         }
       }
     }
+    TRM(p + 1, 4);
     // no barrier here: the next pass writes sX only after every warp left phase 2 (second
     // __syncthreads above) and sY only after the next pass's first __syncthreads
   }
@@ -208,7 +224,7 @@ int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
   if (nchunks < 1) nchunks = 1;
   if (nchunks > a.B) nchunks = a.B;
   const dim3 grid((unsigned)a.Kc, (unsigned)nchunks);
-  const int threads = 32 * (a.R < 4 ? 4 : a.R);
+  const int threads = 512;   // 16 warps: warp r < R owns mode row r in phase 2, all 16 share phases 1 and 3
   const int slot = a.RT == 1 ? 0 : (a.RT == 2 ? 1 : 2);
   auto set_smem = [&](auto kern) -> cudaError_t {
     if (smem_set[slot] >= smem) return cudaSuccess;
@@ -236,3 +252,9 @@ int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
 }
 
 }  // namespace dlwp
+
+#ifdef DLWP_TRACE
+extern "C" int dlwp_debug_set_trace_mid(unsigned long long* p) {
+  return cudaMemcpyToSymbol(dlwp::g_trace_mid, &p, sizeof(p)) == cudaSuccess ? 0 : -2;
+}
+#endif
