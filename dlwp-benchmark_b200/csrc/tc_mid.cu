@@ -9,12 +9,14 @@
 // column) is 0.26 GFMA per layer at the reference sizes -- far below the cost of staging these
 // skinny products for the tensor cores.
 //
-// Work split: CTA = one retained column kx x a strided set of sample quads; warp r of the CTA
-// keeps W[:, :, r, kx] (32 x 32 complex, this lane's output channel) in REGISTERS for the
-// whole launch, so the per-mode weights are read from L2 exactly once per CTA.  Per quad:
+// Work split: CTA = one retained column kx x a contiguous share of the samples; the mode
+// weights W[:, :, :, kx] (R x 32 x 32 complex, 96 KB at R = 12) are bulk-copied into SHARED
+// memory once per CTA, so they are read from L2 exactly once per CTA and the threads keep their
+// registers for deep load prefetch in the DFT phases.  Per pass of up to 4 samples:
 //   phase 1  item = (sample, 4 rows r): lane = input channel; A rows stream from shared memory
 //            (bulk-copied, double buffered), Fh is read as warp-broadcast 16-byte loads
-//   phase 2  warp r: lane = output channel; X is read as warp-broadcast 16-byte loads
+//   phase 2  warp r: lane = output channel, all samples of the pass at once (one weight load
+//            serves 4 samples); X is read as warp-broadcast 16-byte loads
 //   phase 3  item = (sample, 8 grid rows h): lane = output channel; split to bf16 hi / lo and
 //            stored into the operand image
 //
@@ -38,7 +40,6 @@ __device__ unsigned long long* g_trace_mid = nullptr;
 
 namespace {
 
-constexpr int kNB = kTcMidSamples;   // samples per pass
 
 __device__ __forceinline__ void cmac(float2& acc, float gx, float gy, float2 v) {
   acc.x = fmaf(gx, v.x, acc.x);
@@ -47,10 +48,11 @@ __device__ __forceinline__ void cmac(float2& acc, float gx, float gy, float2 v) 
   acc.y = fmaf(gy, v.x, acc.y);
 }
 
-template <int RT>
+// RT = grid rows per 128-pixel tile, kNB = samples per pass (4, or 2 when the slabs are large)
+template <int RT, int kNB>
 __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ uint64_t bars[2];
+  __shared__ uint64_t bars[3];
   pdl_launch_dependents();
   TRM(0, 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
@@ -65,11 +67,19 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   float2* sY = sX + kNB * Rp * 32;                          // [kNB][R][32]
   float2* sF = sY + kNB * R * 32;                           // [H][Rp]   Fh transposed, pad rows zero
   float2* sG = sF + H * Rp;                                 // [R][H]    Gh transposed
+  float2* sW = sG + R * H;                                  // [R][32 i][32 o] mode weights of this column
 
   if (tid == 0) {
     mbar_init(&bars[0], 1);
     mbar_init(&bars[1], 1);
+    mbar_init(&bars[2], 1);
     fence_mbar_init();
+  }
+  __syncthreads();
+  if (warp == 0) {   // weights of this column: one 8 KB bulk copy per retained row
+    if (lane == 0) mbar_arrive_expect_tx(&bars[2], (uint32_t)(R * 8192));
+    __syncwarp();
+    if (lane < R) bulk_g2s(sW + lane * 1024, a.Wm + (size_t)(lane * Kc + kx) * 1024, 8192, &bars[2]);
   }
   auto issue_load = [&](int b0, int s) {   // warp 0: the (sample, kx) slabs of samples b0.. -> stage s
     const int nb = b_hi - b0 < kNB ? b_hi - b0 : kNB;
@@ -86,13 +96,6 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
   for (int i = tid; i < R * H; i += blockDim.x) {
     const int r = i / H, h = i - r * H;
     sG[i] = a.Gh[h * R + r];
-  }
-  // this thread's slice of the mode weights: W[r = warp, kx, i, o = lane]
-  float2 w[32];
-  if (warp < R) {
-    const float2* wp = a.Wm + ((size_t)(warp * Kc + kx) * 32) * 32 + lane;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) w[i] = wp[i * 32];
   }
   __syncthreads();
   TRM(0, 1);
@@ -118,7 +121,7 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
       float2 acc[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[j] = make_float2(0.f, 0.f);
-#pragma unroll 4
+#pragma unroll 8
       for (int h = 0; h < H; ++h) {
         const float2 v = make_float2(Ab[h * 64], Ab[h * 64 + 32]);
         const float4 f01 = F4[h * (Rp >> 1)], f23 = F4[h * (Rp >> 1) + 1];
@@ -133,21 +136,26 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
     __syncthreads();
     TRM(p + 1, 2);
 
-    // ---- phase 2: per-mode channel mixing with the register-resident weights ----
-    if (warp < R) {
+    // ---- phase 2: per-mode channel mixing; warp r serves every sample of the pass ----
+    if (p == 0) mbar_wait(&bars[2], 0);
+    for (int r = warp; r < R; r += nw) {
+      const float2* Wr = sW + r * 1024 + lane;
+      float2 y[kNB];
 #pragma unroll
-      for (int bl = 0; bl < kNB; ++bl) {
-        if (bl >= nb) break;
-        const float4* X4 = reinterpret_cast<const float4*>(sX + (bl * Rp + warp) * 32);
-        float2 y = make_float2(0.f, 0.f);
+      for (int bl = 0; bl < kNB; ++bl) y[bl] = make_float2(0.f, 0.f);
+#pragma unroll 4
+      for (int i2 = 0; i2 < 16; ++i2) {
+        const float2 w0 = Wr[(2 * i2) * 32], w1 = Wr[(2 * i2 + 1) * 32];
 #pragma unroll
-        for (int i2 = 0; i2 < 16; ++i2) {
-          const float4 x = X4[i2];
-          cmac(y, x.x, x.y, w[2 * i2]);
-          cmac(y, x.z, x.w, w[2 * i2 + 1]);
+        for (int bl = 0; bl < kNB; ++bl) {
+          const float4 x = reinterpret_cast<const float4*>(sX + (bl * Rp + r) * 32)[i2];
+          cmac(y[bl], x.x, x.y, w0);
+          cmac(y[bl], x.z, x.w, w1);
         }
-        sY[(bl * R + warp) * 32 + lane] = y;
       }
+#pragma unroll
+      for (int bl = 0; bl < kNB; ++bl)
+        if (bl < nb) sY[(bl * R + r) * 32 + lane] = y[bl];
     }
     __syncthreads();
     TRM(p + 1, 3);
@@ -203,21 +211,24 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
 
 }  // namespace
 
-size_t tc_mid_smem_bytes(int H, int R) {
+static size_t mid_smem(int H, int R, int nb) {
   const int Rp = (R + 3) & ~3;
-  return (size_t)(2 * kNB * H * 32 + kNB * Rp * 32 + kNB * R * 32 + H * Rp + R * H) * sizeof(float2);
+  return (size_t)(2 * nb * H * 32 + nb * Rp * 32 + nb * R * 32 + H * Rp + R * H + R * 1024) * sizeof(float2);
 }
+static int mid_samples(int H, int R) { return mid_smem(H, R, kTcMidSamples) <= 220 * 1024 ? kTcMidSamples : 2; }
+size_t tc_mid_smem_bytes(int H, int R) { return mid_smem(H, R, mid_samples(H, R)); }
 
 int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
   static int sms = 0;
-  static size_t smem_set[3] = {0, 0, 0};
+  static size_t smem_set[6] = {0, 0, 0, 0, 0, 0};
   if (!sms) {
     int dev = 0;
     DLWP_CUDA(cudaGetDevice(&dev));
     DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   }
   DLWP_REQUIRE(a.R >= 1 && a.R <= 16 && a.H % 8 == 0 && a.Kc >= 1, "fno_mid_kernel: unsupported geometry R=%d H=%d", a.R, a.H);
-  const size_t smem = tc_mid_smem_bytes(a.H, a.R);
+  const int nbs = mid_samples(a.H, a.R);
+  const size_t smem = mid_smem(a.H, a.R, nbs);
   DLWP_REQUIRE(smem <= 220 * 1024, "fno_mid_kernel: %zu bytes of shared memory needed", smem);
   // one CTA per SM at most; every CTA takes a contiguous, balanced share of the samples
   int nchunks = sms / a.Kc;
@@ -225,28 +236,22 @@ int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
   if (nchunks > a.B) nchunks = a.B;
   const dim3 grid((unsigned)a.Kc, (unsigned)nchunks);
   const int threads = 512;   // 16 warps: warp r < R owns mode row r in phase 2, all 16 share phases 1 and 3
-  const int slot = a.RT == 1 ? 0 : (a.RT == 2 ? 1 : 2);
-  auto set_smem = [&](auto kern) -> cudaError_t {
-    if (smem_set[slot] >= smem) return cudaSuccess;
-    smem_set[slot] = smem;
-    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  };
-  switch (a.RT) {
-    case 1:
-      DLWP_CUDA(set_smem(fno_mid_kernel<1>));
-      DLWP_CUDA(launch_pdl(fno_mid_kernel<1>, grid, dim3(threads), smem, st, a));
-      break;
-    case 2:
-      DLWP_CUDA(set_smem(fno_mid_kernel<2>));
-      DLWP_CUDA(launch_pdl(fno_mid_kernel<2>, grid, dim3(threads), smem, st, a));
-      break;
-    case 4:
-      DLWP_CUDA(set_smem(fno_mid_kernel<4>));
-      DLWP_CUDA(launch_pdl(fno_mid_kernel<4>, grid, dim3(threads), smem, st, a));
-      break;
-    default:
-      return fail(DLWP_ERR_INVALID, "fno_mid_kernel: %d grid rows per tile", a.RT);
+  void (*kern)(TcMidArgs) = nullptr;
+  int slot = 0;
+#define DLWP_MID_PICK(rt, nb, idx) \
+  if (a.RT == rt && nbs == nb) {   \
+    kern = fno_mid_kernel<rt, nb>; \
+    slot = idx;                    \
   }
+  DLWP_MID_PICK(1, 4, 0) DLWP_MID_PICK(2, 4, 1) DLWP_MID_PICK(4, 4, 2) DLWP_MID_PICK(1, 2, 3) DLWP_MID_PICK(2, 2, 4)
+  DLWP_MID_PICK(4, 2, 5)
+#undef DLWP_MID_PICK
+  if (!kern) return fail(DLWP_ERR_INVALID, "fno_mid_kernel: %d grid rows per tile", a.RT);
+  if (smem_set[slot] < smem) {
+    DLWP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set[slot] = smem;
+  }
+  DLWP_CUDA(launch_pdl(kern, grid, dim3(threads), smem, st, a));
   DLWP_LAUNCHED("fno_mid_kernel");
   return DLWP_OK;
 }
