@@ -115,7 +115,25 @@ int dlwp_plan_workspace_bytes(const dlwp_plan* plan, size_t* bytes) {
 
 int dlwp_plan_uses_tensor_cores(const dlwp_plan* plan, int* out) {
   if (!plan || !out) return fail(DLWP_ERR_INVALID, "dlwp_plan_uses_tensor_cores: null argument");
-  *out = plan->tc ? 1 : 0;
+  *out = (plan->tc || plan->tcw) ? 1 : 0;
+  return DLWP_OK;
+}
+
+int dlwp_plan_debug_read(const dlwp_plan* plan, const char* name, void* dst, size_t max_bytes, void* stream) {
+  if (!plan || !name || !dst) return fail(DLWP_ERR_INVALID, "dlwp_plan_debug_read: null argument");
+  const std::string n(name);
+  const void* src = nullptr;
+  if (n == "tcw_in") src = plan->tcw_in;
+  else if (n == "tcw_hid") src = plan->tcw_hid;
+  else if (n == "tcw_x0") src = plan->tcw_x[0];
+  else if (n == "tcw_x1") src = plan->tcw_x[1];
+  else if (n == "tcw_z") src = plan->tcw_z;
+  else if (n == "specA") src = plan->specA;
+  else if (n == "specZ") src = plan->specZ;
+  else if (n == "tc_img0") src = plan->tc_img[0];
+  else if (n == "tc_img1") src = plan->tc_img[1];
+  if (!src) return fail(DLWP_ERR_INVALID, "dlwp_plan_debug_read: no buffer '%s' in this plan", name);
+  DLWP_CUDA(cudaMemcpyAsync(dst, src, max_bytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
   return DLWP_OK;
 }
 

@@ -74,8 +74,8 @@ static int build_bases(dlwp_plan* p) {
 int plan_build(dlwp_plan* p) {
   const dlwp_model_desc& d = p->d;
   DLWP_REQUIRE(d.kind == DLWP_MODEL_FNO || d.kind == DLWP_MODEL_AFNO, "unknown model kind %d", d.kind);
-  DLWP_REQUIRE(d.precision == DLWP_PREC_FP32 || d.precision == DLWP_PREC_FP32_TC,
-               "precision mode %d is not built into this library yet", d.precision);
+  DLWP_REQUIRE(d.precision == DLWP_PREC_FP32 || d.precision == DLWP_PREC_FP32_TC || d.precision == DLWP_PREC_BF16,
+               "unknown precision mode %d", d.precision);
   DLWP_REQUIRE(d.max_batch > 0 && d.height > 0 && d.width > 0, "max_batch/height/width must be positive");
   DLWP_REQUIRE(d.constant_channels >= 0 && d.prescribed_channels >= 0 && d.prognostic_channels > 0 &&
                    d.context_size > 0,
@@ -121,17 +121,20 @@ int plan_build(dlwp_plan* p) {
                     ? (size_t)d.mlp_hidden
                     : (size_t)(d.lifting_channels > d.projection_channels ? d.lifting_channels
                                                                           : d.projection_channels);
-  DLWP_TRY(dev_alloc(p, (void**)&p->act0, P * C * sizeof(float)));
-  DLWP_TRY(dev_alloc(p, (void**)&p->act1, P * C * sizeof(float)));
-  DLWP_TRY(dev_alloc(p, (void**)&p->act2, P * C * sizeof(float)));
-  DLWP_TRY(dev_alloc(p, (void**)&p->act3, P * C * sizeof(float)));
-  DLWP_TRY(dev_alloc(p, (void**)&p->hid, P * hidw * sizeof(float)));
+  if (d.precision != DLWP_PREC_BF16) {   // the bf16 kernel set keeps its activations as tile images (tc_wide.cuh)
+    DLWP_TRY(dev_alloc(p, (void**)&p->act0, P * C * sizeof(float)));
+    DLWP_TRY(dev_alloc(p, (void**)&p->act1, P * C * sizeof(float)));
+    DLWP_TRY(dev_alloc(p, (void**)&p->act2, P * C * sizeof(float)));
+    DLWP_TRY(dev_alloc(p, (void**)&p->act3, P * C * sizeof(float)));
+    DLWP_TRY(dev_alloc(p, (void**)&p->hid, P * hidw * sizeof(float)));
+  }
   const size_t R = (size_t)d.n_rows, Kc = (size_t)d.n_cols;
   DLWP_TRY(dev_alloc(p, (void**)&p->specA, B * p->gh * Kc * C * sizeof(float2)));
   DLWP_TRY(dev_alloc(p, (void**)&p->specZ, B * p->gh * Kc * C * sizeof(float2)));
   DLWP_TRY(dev_alloc(p, (void**)&p->specX, R * Kc * B * C * sizeof(float2)));
   DLWP_TRY(dev_alloc(p, (void**)&p->specY, R * Kc * B * C * sizeof(float2)));
   if (d.precision == DLWP_PREC_FP32_TC) DLWP_TRY(plan_tc_build(p));
+  if (d.precision == DLWP_PREC_BF16) DLWP_TRY(plan_tcw_build(p));
   return DLWP_OK;
 }
 
@@ -266,6 +269,7 @@ int plan_commit(dlwp_plan* p, cudaStream_t st) {
   if (p->d.kind == DLWP_MODEL_FNO) DLWP_TRY(commit_fno(p, st));
   else DLWP_TRY(commit_afno(p, st));
   if (p->tc) DLWP_TRY(plan_tc_commit(p, st));
+  if (p->tcw) DLWP_TRY(plan_tcw_commit(p, st));
   p->committed = true;
   return DLWP_OK;
 }
@@ -273,6 +277,26 @@ int plan_commit(dlwp_plan* p, cudaStream_t st) {
 }  // namespace dlwp
 
 namespace dlwp {
+
+// ---- the retained-column part of an FNO spectral layer: specA [B, gh, Kc, C] -> specZ (same shape) ----
+//   H-DFT on the retained columns, dense per-mode channel mixing, inverse H-DFT
+int spectral_mid_fno(dlwp_plan* p, const float2* wm, int B, cudaStream_t st) {
+  const int H = p->gh, C = p->C, R = p->d.n_rows, Kc = p->d.n_cols;
+  TdftArgs a{};
+  a.in = p->specA; a.out = p->specX; a.T = p->Fh; a.N = H; a.K = R; a.C = C; a.nb0 = B; a.nb1 = Kc;
+  a.in_sn = (long long)Kc * C; a.in_sb0 = (long long)H * Kc * C; a.in_sb1 = C;
+  a.out_sk = (long long)Kc * B * C; a.out_sb0 = C; a.out_sb1 = (long long)B * C;
+  a.in_complex = true; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  DLWP_TRY(launch_mix_dense(p->specX, wm, p->specY, R * Kc, B, C, C, st));
+  a = TdftArgs{};
+  a.in = p->specY; a.out = p->specZ; a.T = p->Gh; a.N = R; a.K = H; a.C = C; a.nb0 = B; a.nb1 = Kc;
+  a.in_sn = (long long)Kc * B * C; a.in_sb0 = C; a.in_sb1 = (long long)B * C;
+  a.out_sk = (long long)Kc * C; a.out_sb0 = (long long)H * Kc * C; a.out_sb1 = C;
+  a.in_complex = true; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  return DLWP_OK;
+}
 
 // ---- one spectral layer on channels-last activations -----------------------------------
 //   y = act( Re irfft2( mix( rfft2(x)[rows_in, :Kc] ) -> [rows_out, :Kc] ) + add1 + add2 + bias )
@@ -443,6 +467,7 @@ int plan_backbone(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   if (!p->committed) return fail(DLWP_ERR_STATE, "dlwp_plan_commit_weights has not been called");
   DLWP_REQUIRE(B > 0 && B <= p->d.max_batch, "batch %d outside [1, max_batch=%d]", B, p->d.max_batch);
   if (p->tc) return backbone_fno_tc(p, io, B, st);
+  if (p->tcw) return backbone_fno_tcw(p, io, B, st);
   return p->d.kind == DLWP_MODEL_FNO ? backbone_fno(p, io, B, st) : backbone_afno(p, io, B, st);
 }
 

@@ -7,6 +7,7 @@
 
 #include "kernels.cuh"
 #include "tc_fno.cuh"
+#include "tc_wide.cuh"
 
 namespace dlwp {
 
@@ -64,6 +65,16 @@ struct dlwp_plan {
           *tc_projW1x = nullptr;
   std::vector<uint8_t*> tc_skip;                        // per layer skip-conv images
 
+  // bf16 tensor-core path at hidden width 128 (tc_wide.cuh): precision == DLWP_PREC_BF16
+  bool tcw = false;
+  int tcw_TW = 0, tcw_KZ = 0;                           // tiles per grid row; K extent of the inverse W-DFT operands
+  uint8_t *tcw_in = nullptr, *tcw_hid = nullptr, *tcw_z = nullptr;
+  uint8_t* tcw_x[2] = {nullptr, nullptr};               // activation tile images (ping-pong)
+  uint8_t *tcw_G = nullptr, *tcw_F = nullptr;           // inverse / forward W-DFT tiles
+  uint8_t *tcw_W1 = nullptr, *tcw_W2 = nullptr, *tcw_b2 = nullptr, *tcw_P1 = nullptr, *tcw_pb1 = nullptr,
+          *tcw_P2 = nullptr, *tcw_pb2 = nullptr;
+  std::vector<uint8_t*> tcw_skip, tcw_cbias;            // per layer skip-conv and bias images
+
   // host-entry staging (dlwp_rollout_host)
   void* stage[4] = {nullptr, nullptr, nullptr, nullptr};
   size_t stage_bytes[4] = {0, 0, 0, 0};
@@ -78,6 +89,10 @@ int plan_backbone(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
 int plan_tc_build(dlwp_plan* p);                               // tc_plan.cu: eligibility + DFT operand images
 int plan_tc_commit(dlwp_plan* p, cudaStream_t st);             // tc_plan.cu: weight images
 int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
+int plan_tcw_build(dlwp_plan* p);                              // tc_wide_plan.cu
+int plan_tcw_commit(dlwp_plan* p, cudaStream_t st);
+int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
+int spectral_mid_fno(dlwp_plan* p, const float2* wm, int B, cudaStream_t st);
 int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);
 int plan_need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out);
 int spectral_layer(dlwp_plan* p, const float* x, float* y, const float2* wm_or_null, int layer,

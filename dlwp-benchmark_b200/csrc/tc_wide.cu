@@ -1,0 +1,459 @@
+// tcgen05 kernels of the FNO step at hidden width 128 in bf16 (see tc_wide.cuh).
+//
+// One persistent, warp-specialised kernel body, instantiated per GEMM of the step:
+//   warps 0-7 : epilogue group (TMEM -> registers -> GELU / convert -> shared-memory tile image
+//               -> one bulk store; or straight to HBM for the spectrum and the NCHW output)
+//   warp 8    : loader  -- bulk async copies of the streamed operands into a ring of stages
+//   warp 9    : issuer  -- tcgen05.mma into one of two TMEM accumulators (256 columns each)
+// The three sides meet only on mbarriers (full / empty per stage, acc_full / acc_empty per
+// accumulator).  An item is one 128-slot tile (one grid row for TCW_FWD) and consists of one or
+// more K blocks, each one stage of the ring.  Weights stay resident in shared memory; biases are
+// added by one extra K = 16 MMA of a ones operand with a [N x 16] bias image (hi, lo columns).
+#include "tc_wide.cuh"
+
+#include <cstring>
+#include <vector>
+
+#include <cuda_bf16.h>
+
+#include "tc_common.cuh"
+#include "tc_gelu.cuh"
+
+namespace dlwp {
+
+using namespace tc;
+
+namespace {
+
+constexpr int kWEpi = 256;                 // epilogue threads
+constexpr int kWLoader = kWEpi / 32;       // warp 8
+constexpr int kWIssuer = kWLoader + 1;     // warp 9
+constexpr int kWCta = kWEpi + 64;          // 320
+constexpr int kXTile = 128 * kWideC * 2;   // [128 x 128] bf16 image: 32 KB
+constexpr int kHidTile = 128 * kWideHid * 2;   // [128 x 256]: 64 KB
+constexpr int kInTile = 128 * 32 * 2;      // [128 x 32]: 8 KB
+constexpr int kOnes = 128 * 16 * 2;        // ones operand [128 x 16]
+constexpr int kMaxStages = 4;
+
+// per-GEMM constants
+template <int MODE> struct WT;
+template <> struct WT<TCW_LIFT1> {
+  static constexpr int N = 256, NS = 4, RES = 256 * 32 * 2, BIAS = 0, OUT = kHidTile, NOUT = 2;
+  __host__ __device__ static int stage(int) { return kInTile; }
+};
+template <> struct WT<TCW_LIFT2> {
+  static constexpr int N = 128, NS = 3, RES = 128 * 256 * 2, BIAS = 128 * 32, OUT = kXTile, NOUT = 1;
+  __host__ __device__ static int stage(int) { return kXTile; }   // one K half of a hidden tile
+};
+template <> struct WT<TCW_FWD> {
+  static constexpr int N = 128, NS = 3, RES = 0, BIAS = 0, OUT = 0, NOUT = 1;
+  __host__ __device__ static int stage(int) { return 2 * kXTile; }   // forward DFT tile + activation tile
+};
+template <> struct WT<TCW_LAYER> {
+  static constexpr int N = 128, NS = 2, RES = 128 * 128 * 2, BIAS = 128 * 32, OUT = kXTile, NOUT = 1;
+  __host__ __device__ static int stage(int KZ) { return kXTile + 2 * KZ * 256; }   // x, G tile, Z row image
+};
+template <> struct WT<TCW_PROJ1> {
+  static constexpr int N = 256, NS = 2, RES = 256 * 128 * 2, BIAS = 256 * 32, OUT = kHidTile, NOUT = 1;
+  __host__ __device__ static int stage(int) { return kXTile; }
+};
+template <> struct WT<TCW_PROJ2> {
+  static constexpr int N = 16, NS = 4, RES = 16 * 256 * 2, BIAS = 16 * 32, OUT = 0, NOUT = 1;
+  __host__ __device__ static int stage(int) { return kXTile; }   // one K half of a hidden tile
+};
+
+template <int MODE>
+__host__ __device__ inline int tcw_smem_bytes(int KZ) {
+  using T = WT<MODE>;
+  return T::RES + T::BIAS + (T::BIAS ? kOnes : 0) + T::NS * T::stage(KZ) + T::NOUT * T::OUT;
+}
+
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// 16 accumulator columns -> two 16-byte chunk rows of the bf16 tile image
+template <bool GELU>
+__device__ __forceinline__ void cols16_to_image(const uint32_t (&r)[16], uint8_t* img, int row, int c0) {
+  uint32_t o[8];
+  if (GELU) {
+    float2 g[8];
+    gelu2x_8(r, g);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o[e] = pack_bf16(g[e].x, g[e].y);
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o[e] = pack_bf16(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]));
+  }
+  uint8_t* d = img + (c0 >> 3) * 2048 + row * 16;
+  *reinterpret_cast<uint4*>(d) = make_uint4(o[0], o[1], o[2], o[3]);
+  *reinterpret_cast<uint4*>(d + 2048) = make_uint4(o[4], o[5], o[6], o[7]);
+}
+
+}  // namespace
+
+namespace {
+
+template <int MODE>
+__global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
+  using T = WT<MODE>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bars[2 * kMaxStages + 5];
+  __shared__ uint32_t tmem_slot;
+  pdl_launch_dependents();
+  uint64_t* full = bars;
+  uint64_t* empty = bars + kMaxStages;
+  uint64_t* acc_full = bars + 2 * kMaxStages;
+  uint64_t* acc_empty = acc_full + 2;
+  uint64_t* res_bar = acc_empty + 2;
+
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int stage_bytes = T::stage(a.KZ);
+  const int nblk = (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) ? 2 : (MODE == TCW_FWD ? a.TW : 1);
+  uint8_t* sRes = smem;
+  uint8_t* sBias = sRes + T::RES;
+  uint8_t* sOnes = sBias + T::BIAS;
+  uint8_t* sStage = sOnes + (T::BIAS ? kOnes : 0);
+  uint8_t* sOut = sStage + T::NS * stage_bytes;
+
+  if (tid == 0) {
+    for (int s = 0; s < T::NS; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], kWEpi);
+    }
+    mbar_init(res_bar, 1);
+    fence_mbar_init();
+  }
+  if (T::BIAS && tid < 128) {   // ones operand: columns 0 and 1 (hi and lo parts of the bias) are 1.0
+    *reinterpret_cast<uint4*>(sOnes + tid * 16) = make_uint4(0x3F803F80u, 0u, 0u, 0u);
+    *reinterpret_cast<uint4*>(sOnes + 2048 + tid * 16) = make_uint4(0u, 0u, 0u, 0u);
+    fence_async_smem();
+  }
+  if (warp == kWIssuer) {
+    tmem_alloc(&tmem_slot, 512);
+    tmem_relinquish();
+    tc_fence_before();
+  }
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp == kWLoader) {
+    // ------------------------------ loader ------------------------------
+    const uint32_t leader = elect_one();
+    if (T::RES + T::BIAS > 0) {   // constants: may be fetched before the previous kernel has finished
+      mbar_arrive_expect_tx_p(leader, res_bar, (uint32_t)(T::RES + T::BIAS));
+      if (T::RES) bulk_g2s_p(leader, sRes, a.b_res, T::RES, res_bar);
+      if (T::BIAS) bulk_g2s_p(leader, sBias, a.bias_img, T::BIAS, res_bar);
+    }
+    pdl_wait();
+    uint32_t u = 0;
+    for (int item = blockIdx.x; item < a.nitems; item += gridDim.x) {
+      for (int blk = 0; blk < nblk; ++blk, ++u) {
+        const uint32_t s = u % T::NS;
+        uint8_t* st = sStage + s * stage_bytes;
+        mbar_wait(&empty[s], ((u / T::NS) & 1u) ^ 1u);
+        mbar_arrive_expect_tx_p(leader, &full[s], (uint32_t)stage_bytes);
+        if (MODE == TCW_LIFT1) {
+          bulk_g2s_p(leader, st, a.a_img + (size_t)item * kInTile, kInTile, &full[s]);
+        } else if (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) {
+          bulk_g2s_p(leader, st, a.a_img + (size_t)item * kHidTile + (size_t)blk * kXTile, kXTile, &full[s]);
+        } else if (MODE == TCW_FWD) {
+          bulk_g2s_p(leader, st, a.g_img + (size_t)blk * kXTile, kXTile, &full[s]);
+          bulk_g2s_p(leader, st + kXTile, a.a_img + ((size_t)item * a.TW + blk) * kXTile, kXTile, &full[s]);
+        } else if (MODE == TCW_LAYER) {
+          const uint32_t zb = (uint32_t)a.KZ * 256u;
+          bulk_g2s_p(leader, st, a.a_img + (size_t)item * kXTile, kXTile, &full[s]);
+          bulk_g2s_p(leader, st + kXTile, a.g_img + (size_t)(item % a.TW) * zb, zb, &full[s]);
+          bulk_g2s_p(leader, st + kXTile + zb, a.z_img + (size_t)(item / a.TW) * zb, zb, &full[s]);
+        } else {   // TCW_PROJ1
+          bulk_g2s_p(leader, st, a.a_img + (size_t)item * kXTile, kXTile, &full[s]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == kWIssuer) {
+    // ------------------------------ issuer ------------------------------
+    const uint32_t leader = elect_one();
+    pdl_wait();
+    if (T::RES + T::BIAS > 0) mbar_wait(res_bar, 0);
+    const uint32_t idesc = idesc_bf16(128, T::N) | (MODE == TCW_FWD ? kIdescBMnMajor : 0u);
+    const uint64_t dRes = chunk_desc(smem_u32(sRes), T::N, 0);
+    const uint32_t bstep = 2u * T::N * 16u;   // resident operand: bytes per K = 16 step
+    uint32_t u = 0, it = 0;
+    for (int item = blockIdx.x; item < a.nitems; item += gridDim.x, ++it) {
+      const uint32_t acc = it & 1u;
+      mbar_wait(&acc_empty[acc], ((it >> 1) & 1u) ^ 1u);
+      tc_fence_after();
+      const uint32_t d = tmem + acc * 256u;
+      for (int blk = 0; blk < nblk; ++blk, ++u) {
+        const uint32_t s = u % T::NS;
+        const uint32_t st = smem_u32(sStage + s * stage_bytes);
+        mbar_wait(&full[s], (u / T::NS) & 1u);
+        tc_fence_after();
+        const uint64_t dA = chunk_desc(st, 128, 0);
+        if (MODE == TCW_LIFT1) {
+#pragma unroll
+          for (int j = 0; j < 2; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
+        } else if (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) {
+          const uint64_t dB = desc_off(dRes, (uint32_t)blk * 8u * bstep);   // K half of the resident weights
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dB, j * bstep), idesc, (blk | j) != 0);
+        } else if (MODE == TCW_FWD) {
+          // B: the activation image read in place as an MN-major operand (pixels = K, 8 x 8 core
+          // matrices 128 B apart along pixels, 2048 B along channels)
+          const uint64_t dX = smem_desc(st + kXTile, 128, 2048);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dX, j * 256), idesc, (blk | j) != 0);
+        } else if (MODE == TCW_LAYER) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
+          const uint32_t zb = (uint32_t)a.KZ * 256u;
+          const uint64_t dG = chunk_desc(st + kXTile, 128, 0), dZ = chunk_desc(st + kXTile + zb, 128, 0);
+          for (int j = 0; j < (a.KZ >> 4); ++j)
+            umma_bf16_p(leader, d, desc_off(dG, j * 4096), desc_off(dZ, j * 4096), idesc, 1u);
+        } else {   // TCW_PROJ1
+#pragma unroll
+          for (int j = 0; j < 8; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
+        }
+        umma_commit_p(leader, &empty[s]);
+      }
+      if (T::BIAS)
+        umma_bf16_p(leader, d, chunk_desc(smem_u32(sOnes), 128, 0), chunk_desc(smem_u32(sBias), T::N, 0), idesc, 1u);
+      umma_commit_p(leader, &acc_full[acc]);
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------ epilogue group ------------------------------
+    pdl_wait();
+    const int q4 = warp & 3, half = warp >> 2;
+    const int row = q4 * 32 + lane;                  // accumulator row = TMEM lane
+    const uint32_t trow = tmem + ((uint32_t)(q4 * 32) << 16);
+    uint32_t it = 0;
+    for (int item = blockIdx.x; item < a.nitems; item += gridDim.x, ++it) {
+      const uint32_t acc = it & 1u;
+      const uint32_t d = trow + acc * 256u;
+      uint8_t* ob = sOut + (T::NOUT > 1 ? (it & 1u) * T::OUT : 0u);
+      if (T::OUT) {   // the bulk store that last read this buffer must have drained it
+        if (tid == 0) {
+          if (T::NOUT > 1) bulk_wait_read1();
+          else bulk_wait_read0();
+        }
+        bar_sync(1, kWEpi);
+      }
+      mbar_wait(&acc_full[acc], (it >> 1) & 1u);
+      tc_fence_after();
+      if (MODE == TCW_LIFT1 || MODE == TCW_LIFT2 || MODE == TCW_LAYER || MODE == TCW_PROJ1) {
+        const bool gelu = MODE == TCW_LIFT1 || MODE == TCW_PROJ1 || (MODE == TCW_LAYER && a.gelu);
+#pragma unroll 1
+        for (int i = 0; i < T::N / 32; ++i) {
+          const int c0 = i * 32 + half * 16;
+          uint32_t r[16];
+          tmem_ld16(d + (uint32_t)c0, r);
+          tmem_ld_wait();
+          if (gelu) cols16_to_image<true>(r, ob, row, c0);
+          else cols16_to_image<false>(r, ob, row, c0);
+        }
+        tc_fence_before();
+        mbar_arrive(&acc_empty[acc]);
+        fence_async_smem();
+        bar_sync(2, kWEpi);
+        if (tid == 0) {
+          bulk_s2g(a.out_img + (size_t)item * T::OUT, ob, T::OUT);
+          bulk_commit();
+        }
+      } else if (MODE == TCW_FWD) {
+        // accumulator row k = 2 kx + (re | im), columns = channels.  Lane pairs swap halves of each
+        // 16-column block so that every lane stores whole complex values: the even lane (re) keeps
+        // channels c0..c0+7, the odd lane (im) channels c0+8..c0+15.
+        if (q4 * 32 < 2 * a.Kc) {
+          const int kx = row >> 1, odd = lane & 1;
+          const bool valid = row < 2 * a.Kc;
+          float2* dst = a.spec + ((size_t)item * a.Kc + kx) * kWideC;
+#pragma unroll 1
+          for (int i = 0; i < 4; ++i) {
+            const int c0 = half * 64 + i * 16;
+            uint32_t r[16];
+            tmem_ld16(d + (uint32_t)c0, r);
+            tmem_ld_wait();
+            float2 o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float mine = __uint_as_float(odd ? r[8 + j] : r[j]) * a.scale;
+              const float send = __uint_as_float(odd ? r[j] : r[8 + j]) * a.scale;
+              const float got = __shfl_xor_sync(0xffffffffu, send, 1);
+              o[j] = odd ? make_float2(got, mine) : make_float2(mine, got);
+            }
+            if (valid) {
+              float4* p = reinterpret_cast<float4*>(dst + c0 + odd * 8);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) p[j] = make_float4(o[2 * j].x, o[2 * j].y, o[2 * j + 1].x, o[2 * j + 1].y);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&acc_empty[acc]);
+      } else {   // TCW_PROJ2: accumulator columns = output channels, rows = pixel slots
+        if (half * 8 < a.Cg) {
+          uint32_t r[8];
+          tmem_ld8(d + (uint32_t)(half * 8), r);
+          tmem_ld_wait();
+          const int w = (item % a.TW) * 128 + row, rid = item / a.TW;
+          const int b = rid / a.H, h = rid - b * a.H;
+          if (w < a.W) {
+            const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int co = half * 8 + j;
+              if (co < a.Cg) {
+                float v = __uint_as_float(r[j]);
+                if (a.last) v += a.last[(size_t)b * a.last_bstride + co * plane + px];
+                a.out[(size_t)b * a.out_bstride + co * plane + px] = v;
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&acc_empty[acc]);
+      }
+    }
+    if (T::OUT && tid == 0) bulk_wait0();
+  }
+  __syncthreads();
+  if (warp == kWIssuer) tmem_dealloc(tmem, 512);
+}
+
+// ---- layout kernels ---------------------------------------------------------------------------
+// x_t from the NCHW sources -> [128 slots x 32] bf16 input images: columns 0..Cin-1 hi parts,
+// columns Cin and 15 ones (they meet the hi and lo parts of the first bias in the weight image),
+// columns 16..16+Cin-1 lo parts.
+__global__ void __launch_bounds__(128) wide_gather_kernel(const WideGatherArgs a) {
+  pdl_launch_dependents();
+  const int tile = blockIdx.x, s = threadIdx.x;
+  const int w = (tile % a.TW) * 128 + s, rid = tile / a.TW;
+  const int b = rid / a.H, h = rid - b * a.H;
+  const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
+  __nv_bfloat16 v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __float2bfloat16(0.f);
+  pdl_wait();
+  if (w < a.W) {
+    int c = 0;
+    for (int g = 0; g < a.ngrp; ++g)
+      for (int ch = 0; ch < a.grp[g].nch; ++ch, ++c) {
+        const float x = a.grp[g].base[(size_t)b * a.grp[g].bstride + ch * plane + px];
+        const __nv_bfloat16 hi = __float2bfloat16(x);
+#pragma unroll
+        for (int i = 0; i < 14; ++i)
+          if (i == c) {
+            v[i] = hi;
+            v[16 + i] = __float2bfloat16(x - __bfloat162float(hi));
+          }
+      }
+  }
+#pragma unroll
+  for (int i = 0; i < 16; ++i)
+    if (i == a.Cin || i == 15) v[i] = __float2bfloat16(1.f);
+  uint8_t* img = a.in_img + (size_t)tile * kInTile + s * 16;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(img + j * 2048) = *reinterpret_cast<const uint4*>(&v[8 * j]);
+}
+
+// Z [rows, Kc, 128] complex -> per-row [128 channels x KZ] operand image, k = 2 kx + (re | im)
+__global__ void __launch_bounds__(128) wide_zimg_kernel(const float2* __restrict__ Z, uint8_t* __restrict__ img, int Kc,
+                                                        int KZ) {
+  const int rowi = blockIdx.x, j = blockIdx.y, c = threadIdx.x;   // j = chunk of 8 k = 4 retained columns
+  const float2* z = Z + (size_t)rowi * Kc * kWideC + c;
+  uint32_t o[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int kx = 4 * j + q;
+    const float2 v = kx < Kc ? z[(size_t)kx * kWideC] : make_float2(0.f, 0.f);
+    o[q] = pack_bf16(v.x, v.y);
+  }
+  *reinterpret_cast<uint4*>(img + (size_t)rowi * KZ * 256 + j * 2048 + c * 16) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+}  // namespace
+
+// ---- launchers ---------------------------------------------------------------------------------
+template <int MODE>
+static int launch_tcw_mode(const TcwArgs& a, cudaStream_t st, const char* name) {
+  static int sms = 0;
+  static int smem_set = 0;
+  if (!sms) {
+    int dev = 0;
+    DLWP_CUDA(cudaGetDevice(&dev));
+    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int smem = tcw_smem_bytes<MODE>(a.KZ);
+  DLWP_REQUIRE(smem <= 226 * 1024, "%s: %d bytes of shared memory needed", name, smem);
+  if (smem_set < smem) {
+    DLWP_CUDA(cudaFuncSetAttribute(tcw_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    smem_set = smem;
+  }
+  const int grid = a.nitems < sms ? a.nitems : sms;
+  void (*kern)(TcwArgs) = tcw_kernel<MODE>;
+  DLWP_CUDA(launch_pdl(kern, dim3((unsigned)grid), dim3(kWCta), (size_t)smem, st, a));
+  DLWP_LAUNCHED(name);
+  return DLWP_OK;
+}
+
+int launch_tcw(int mode, const TcwArgs& a, cudaStream_t st) {
+  DLWP_REQUIRE(a.nitems > 0 && a.TW > 0 && a.H > 0 && a.W > 0, "tcw: empty problem");
+  DLWP_REQUIRE(a.KZ % 16 == 0 && a.KZ >= 16 && a.KZ <= 96 && 2 * a.Kc <= a.KZ, "tcw: %d retained columns do not fit", a.Kc);
+  switch (mode) {
+    case TCW_LIFT1: return launch_tcw_mode<TCW_LIFT1>(a, st, "tcw_lift1");
+    case TCW_LIFT2: return launch_tcw_mode<TCW_LIFT2>(a, st, "tcw_lift2");
+    case TCW_FWD: return launch_tcw_mode<TCW_FWD>(a, st, "tcw_fwd_wdft");
+    case TCW_LAYER: return launch_tcw_mode<TCW_LAYER>(a, st, "tcw_layer");
+    case TCW_PROJ1: return launch_tcw_mode<TCW_PROJ1>(a, st, "tcw_proj1");
+    case TCW_PROJ2: return launch_tcw_mode<TCW_PROJ2>(a, st, "tcw_proj2");
+  }
+  return fail(DLWP_ERR_INVALID, "tcw: unknown mode %d", mode);
+}
+
+int launch_wide_gather(const WideGatherArgs& a, cudaStream_t st) {
+  DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 14 && a.ngrp >= 1 && a.ngrp <= 4, "wide_gather: %d input channels", a.Cin);
+  void (*kern)(WideGatherArgs) = wide_gather_kernel;
+  DLWP_CUDA(launch_pdl(kern, dim3((unsigned)a.ntiles), dim3(128), 0, st, a));
+  DLWP_LAUNCHED("wide_gather_kernel");
+  return DLWP_OK;
+}
+
+int launch_wide_zimg(const float2* Z, uint8_t* z_img, int rows, int Kc, int KZ, cudaStream_t st) {
+  // chunks past 2 Kc stay zero from the plan's memset
+  const int nchunk = (2 * Kc + 7) / 8;
+  wide_zimg_kernel<<<dim3((unsigned)rows, (unsigned)nchunk), 128, 0, st>>>(Z, z_img, Kc, KZ);
+  DLWP_LAUNCHED("wide_zimg_kernel");
+  return DLWP_OK;
+}
+
+// ---- host packing --------------------------------------------------------------------------------
+template <class S>
+static void pack_image_t(const S* m, int rows, int cols, int ld, int R, int K, uint8_t* out) {
+  std::memset(out, 0, (size_t)R * K * 2);
+  for (int r = 0; r < rows; ++r)
+    for (int k = 0; k < cols; ++k) {
+      const __nv_bfloat16 v = __float2bfloat16((float)m[(size_t)r * ld + k]);
+      std::memcpy(out + (size_t)(k >> 3) * R * 16 + (size_t)r * 16 + (k & 7) * 2, &v, 2);
+    }
+}
+void tcw_pack_image(const float* m, int rows, int cols, int ld, int R, int K, uint8_t* out) {
+  pack_image_t(m, rows, cols, ld, R, K, out);
+}
+void tcw_pack_image_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out) {
+  pack_image_t(m, rows, cols, ld, R, K, out);
+}
+
+}  // namespace dlwp

@@ -1,0 +1,70 @@
+// Tensor-core (tcgen05) kernel set for the FNO step at hidden width 128 in bf16
+// (precision mode DLWP_PREC_BF16; BASELINE config 5: 721 x 1440 grid, 128 channels, 64 x 33 modes).
+//
+// Every grid row of W pixels is cut into TW = ceil(W / 128) tiles of 128 pixel slots (slots past
+// W are padding: they hold finite values that no result depends on).  Activations live in HBM
+// as bf16 "tile images": [128 slots] x [K channels] in the chunk-major UMMA operand layout of
+// tc_common.cuh, so a consumer brings a tile in with one bulk async copy and hands it to
+// tcgen05.mma untouched -- as the K-major A operand of the pointwise GEMMs, and as the MN-major
+// B operand of the forward W-DFT (which contracts over pixels).
+//
+// One model evaluation (reference: neuralop FNO.forward behind fno.py:103):
+//   wide_gather_kernel   x_t from the NCHW sources (fno.py:49-62) -> [128 x 32] input images
+//                        (hi parts, a ones column for the bias, lo parts)
+//   tcw LIFT1            hidden = gelu(W1 x + b1)                  -> [128 x 256] images
+//   tcw LIFT2            x0 = W2 hidden + b2                       -> [128 x 128] images
+//   per layer:
+//     tcw FWD            A[h, kx, c] = sum_w F[kx, w] x[h, w, c]   (fp32 spectrum, one item per grid row)
+//     tdft / mix / tdft  H-DFT, per-mode channel mixing, inverse H-DFT (fp32 FMA, kernels_fp32.cu)
+//     wide_zimg_kernel   Z[h, kx, c] -> [128 channels x KZ] bf16 operand image per grid row
+//     tcw LAYER          x' = act(G Z + Wskip x + bias)            -> [128 x 128] images
+//   tcw PROJ1            hidden = gelu(P1 x + b1)                  -> [128 x 256] images
+//   tcw PROJ2            out = P2 hidden + b2 + last frame         -> NCHW fp32
+// GELU epilogues store 2 * gelu (tc_gelu.cuh); the consumers' weights carry the 1/2.
+#pragma once
+#include "kernels.cuh"
+
+namespace dlwp {
+
+constexpr int kWideC = 128;     // hidden channels
+constexpr int kWideHid = 256;   // lifting / projection width
+
+enum TcwMode { TCW_LIFT1 = 0, TCW_LIFT2 = 1, TCW_FWD = 2, TCW_LAYER = 3, TCW_PROJ1 = 4, TCW_PROJ2 = 5 };
+
+struct TcwArgs {
+  int nitems;             // tiles (B * H * TW); grid rows (B * H) for TCW_FWD
+  int TW, H, W;           // tiles per grid row, grid rows per sample, grid width
+  int Kc, KZ;             // retained columns; K extent of the inverse W-DFT operands (2 Kc padded to 16)
+  const uint8_t* a_img;   // streamed tile images: input [128 x 32] / hidden [128 x 256] / activation [128 x 128]
+  const uint8_t* b_res;   // resident weight image [N rows x K]
+  const uint8_t* bias_img;// [N rows x 16]: columns 0 / 1 = hi / lo of the bias (times a ones operand), or null
+  const uint8_t* g_img;   // TCW_LAYER: TW inverse W-DFT tiles [128 x KZ]; TCW_FWD: TW forward tiles [128 x 128]
+  const uint8_t* z_img;   // TCW_LAYER: per grid row [128 x KZ]
+  uint8_t* out_img;       // tile images out
+  float2* spec;           // TCW_FWD: [B, H, Kc, 128] complex
+  float scale;            // TCW_FWD: factor on the spectrum (1/2 when the input image holds 2 * gelu)
+  int gelu;               // TCW_LAYER: apply GELU
+  float* out;             // TCW_PROJ2: NCHW frame(s) out[b * out_bstride + (c, y, x)]
+  long long out_bstride;
+  const float* last;      // residual frame or null
+  long long last_bstride;
+  int Cg;
+};
+int launch_tcw(int mode, const TcwArgs& a, cudaStream_t st);
+
+struct WideGatherArgs {
+  SrcGroup grp[4];
+  int ngrp, Cin;          // Cin <= 14
+  int ntiles, TW, H, W;
+  uint8_t* in_img;        // [ntiles] x [128 x 32]
+};
+int launch_wide_gather(const WideGatherArgs& a, cudaStream_t st);
+
+// Z [rows, Kc, 128] complex fp32 -> per-row operand image [128 channels x KZ], k = 2 kx + (re | im)
+int launch_wide_zimg(const float2* Z, uint8_t* z_img, int rows, int Kc, int KZ, cudaStream_t st);
+
+// host: chunk-major bf16 image of a row-major matrix `m` [rows, cols] padded to R x K with zeros
+void tcw_pack_image(const float* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
+void tcw_pack_image_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
+
+}  // namespace dlwp

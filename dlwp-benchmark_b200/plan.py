@@ -83,6 +83,14 @@ class NativePlan:
         native.check(self._lib.dlwp_plan_uses_tensor_cores(self._h, C.byref(n)))
         return bool(n.value)
 
+    def debug_read(self, name: str, nbytes: int) -> torch.Tensor:
+        """First `nbytes` bytes of a named internal workspace buffer (diagnostics; see dlwp_plan_debug_read)."""
+        out = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        native.check(self._lib.dlwp_plan_debug_read(self._h, name.encode(), C.c_void_p(out.data_ptr()), nbytes,
+                                                    self._stream()), "debug_read")
+        torch.cuda.current_stream(self.device).synchronize()
+        return out
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
