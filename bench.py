@@ -182,7 +182,7 @@ def step_bytes(cls, kw, B, H, W, b=4):
     return act + wts
 
 
-def kernel_bytes(cls, kw, B, H, W, name):
+def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
     """Algorithmic bytes ONE model evaluation moves through the kernel called `name` (sum over
     its launches in the step), or None when bench.py has no model for that kernel."""
     S, b = H * W, 4
@@ -199,6 +199,25 @@ def kernel_bytes(cls, kw, B, H, W, name):
         return None
     cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
     px = B * S
+    if name.startswith("tcw_") or name.startswith("wide_") or tcw:
+        # bf16 tile-image path (tc_wide.cuh): 128-slot tiles, rows padded to a whole number of tiles
+        pxp = B * H * ((W + 127) // 128) * 128
+        half = B * H * m2 * C * 2               # complex fp32 [B, H, Kc, C], in floats
+        modes = B * m1 * m2 * C * 2
+        kz = (2 * m2 + 15) // 16 * 16
+        table = {
+            "wide_gather_kernel": 4 * px * cin + 2 * pxp * 32,
+            "tcw_lift1": 2 * pxp * (32 + L),
+            "tcw_lift2": 2 * pxp * (L + C),
+            "tcw_fwd_wdft": N * (2 * pxp * C + 4 * half),
+            "tdft_kernel": 4 * N * ((half + modes) + (modes + half)),
+            "mix_dense_kernel": 4 * N * (2 * modes + m1 * m2 * C * C * 2),
+            "wide_zimg_kernel": N * (4 * half + 2 * B * H * kz * C),
+            "tcw_layer": N * (2 * 2 * pxp * C + 2 * B * H * kz * C),
+            "tcw_proj1": 2 * pxp * (C + P),
+            "tcw_proj2": 2 * pxp * P + 4 * 2 * px * Cg,
+        }
+        return table.get(name)
     if name == "pw_linear_kernel":      # lifting 1+2, N skips, projection 1+2 (unfused fp32 path)
         return b * px * ((cin + L) + (L + C) + N * 2 * C + (C + P) + (P + 2 * Cg))
     if name == "tdft_kernel":           # 4 truncated-DFT passes per layer
@@ -414,7 +433,8 @@ def run_ours(args, wl):
         ms_step = ms_total / args.steps
         entries = prof.entries
         name, (kms, kn) = max(entries.items(), key=lambda kv: kv[1][0])
-        kb = kernel_bytes(cls, kw, members, H, W, name)
+        tcw = "tcw_layer" in entries
+        kb = kernel_bytes(cls, kw, members, H, W, name, tcw)
         total_prof = sum(v[0] for v in entries.values())
         roof = {"bound": "hbm", "kernel": name, "achieved": None, "peak": hbm_peak, "unit": "GB/s", "frac": None,
                 "traffic": None, "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
@@ -430,8 +450,14 @@ def run_ours(args, wl):
             roof["traffic_source"] = "profiles/r01_ncu_full_tc_v3.csv (ncu --set full of this command, mean over the kernel's launches)"
         fl = step_flops(cls, kw, members, H, W)
         sb = step_bytes(cls, kw, members, H, W)
-        spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel")]
+        spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel",
+                                                  "tcw_fwd_wdft", "wide_zimg_kernel")]
         spec_ms = sum(entries[n][0] for n in spec_names)
+        if tcw:   # the inverse W-DFT runs inside tcw_layer next to the skip conv: its share of that kernel's K extent
+            m2c = fno_dims(kw, H, W)[7]
+            kzc = (2 * m2c + 15) // 16 * 16
+            spec_ms += entries["tcw_layer"][0] * kzc / (kzc + kw["hidden_channels"])
+            spec_names.append("tcw_layer (inverse W-DFT share of its K extent)")
         # on the tensor-core path the W-DFTs of the spectral block run inside the lift / layer kernels; the
         # separately timed part is the mid kernel (H-DFT, mode mixing, inverse H-DFT): count only its flops
         fused_w = "fno_mid_kernel" in entries
@@ -459,7 +485,8 @@ def run_ours(args, wl):
                                if spec_ms > 0 else None, "peak_tflops": tc_peak,
                                "flops_counted": ("H-DFT + mode mixing + inverse H-DFT (fp32 FMA in fno_mid_kernel); the W-DFT "
                                                  "GEMMs of the block run on tcgen05 inside fno_lift / fno_layer_kernel"
-                                                 if fused_w else "whole spectral block (truncated-DFT-GEMM count)"),
+                                                 if fused_w else "whole spectral block (truncated-DFT-GEMM count)"
+                                                 + (": W-DFTs on tcgen05 in bf16, H-DFTs and mode mixing in fp32 FMA" if tcw else "")),
                                "note": "profiled pass; includes the events' launch gaps"},
             "kernel_ms_per_rollout": {n: round(v[0], 4) for n, v in sorted(entries.items(), key=lambda kv: -kv[1][0])},
             "clocks": clk.summary(),

@@ -128,6 +128,9 @@ int dlwp_plan_debug_read(const dlwp_plan* plan, const char* name, void* dst, siz
   else if (n == "tcw_x0") src = plan->tcw_x[0];
   else if (n == "tcw_x1") src = plan->tcw_x[1];
   else if (n == "tcw_z") src = plan->tcw_z;
+  else if (n == "tcw_sa") src = plan->tcw_sa;
+  else if (n == "tcw_ys") src = plan->tcw_ys;
+  else if (n == "specX") src = plan->specX;
   else if (n == "specA") src = plan->specA;
   else if (n == "specZ") src = plan->specZ;
   else if (n == "tc_img0") src = plan->tc_img[0];

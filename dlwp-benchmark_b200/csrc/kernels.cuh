@@ -65,8 +65,14 @@ int launch_layernorm(const float* in, float* out, const float* gamma, const floa
 
 // ---- per-mode channel mixing ----------------------------------------------------------
 // X, Y: [modes, B, C] complex;  Wm: [modes, Ci, Co] complex
+// `im.img` set: Y is not written; the result goes out as bf16 tile images per (sample, retained column)
+// for the tensor-core inverse H-DFT (tc_wide.cuh), modes = rows * im.Kc
+struct MixImageOut {
+  uint8_t* img = nullptr;
+  int Kc = 0;
+};
 int launch_mix_dense(const float2* X, const float2* Wm, float2* Y, int modes, int B, int Ci, int Co,
-                     cudaStream_t st);
+                     cudaStream_t st, MixImageOut im = MixImageOut{});
 // AFNO block-diagonal 2-layer complex MLP with ReLU (re, im separately) and softshrink.
 // w1 [2, nb, bs, bs*f], b1 [2, nb, bs*f], w2 [2, nb, bs*f, bs], b2 [2, nb, bs]
 int launch_mix_afno(const float2* X, float2* Y, const float* w1, const float* b1, const float* w2,

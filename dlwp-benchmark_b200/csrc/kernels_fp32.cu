@@ -7,6 +7,8 @@
 // host, plan.cu), W axis first then H, and back H then W.
 #include "kernels.cuh"
 
+#include <cuda_bf16.h>
+
 namespace dlwp {
 
 // =====================================================================================
@@ -108,6 +110,9 @@ template <bool IC, bool OC>
 static int tdft_pick(const TdftArgs& a, cudaStream_t st) {
   int kpt = ceil_div(a.K, 8);
   if (kpt > 8) kpt = 8;
+  // few (batch, channel) blocks: split the outputs over more blocks so that the grid covers the machine
+  const long long bc = (long long)a.nb0 * a.nb1 * ceil_div(a.C, 32);
+  while (kpt > 2 && bc * ceil_div(a.K, 8 * kpt) < 296) kpt = (kpt + 1) / 2;
   dim3 grid((unsigned)(a.nb0 * a.nb1), (unsigned)ceil_div(a.C, 32), (unsigned)ceil_div(a.K, 8 * kpt));
   switch (kpt) {
     case 1: return tdft_go<IC, OC, 1>(a, grid, st);
@@ -295,6 +300,15 @@ int launch_layernorm(const float* in, float* out, const float* gamma, const floa
   return DLWP_OK;
 }
 
+// bf16 image output for the tensor-core inverse H-DFT (tc_wide.cuh): per (sample, retained column)
+// a [128 rows = (retained row, re | im)] x [128 channels] chunk-major tile; mode m = row * Kc + column
+__device__ __forceinline__ void mix_store_image(const MixImageOut& im, int m, int b, int o, float2 v) {
+  const int r = m / im.Kc, kx = m - r * im.Kc;
+  uint8_t* p = im.img + ((size_t)b * im.Kc + kx) * 32768 + (size_t)(o >> 3) * 2048 + (size_t)(2 * r) * 16 + (o & 7) * 2;
+  *reinterpret_cast<__nv_bfloat16*>(p) = __float2bfloat16(v.x);
+  *reinterpret_cast<__nv_bfloat16*>(p + 16) = __float2bfloat16(v.y);
+}
+
 // =====================================================================================
 // mix_dense_kernel: Y[m, b, o] = sum_i X[m, b, i] * Wm[m, i, o]   (complex)
 //   = einsum("bixy,ioxy->boxy") of unet.py:15-17 / neuralop's dense contraction, one
@@ -302,7 +316,8 @@ int launch_layernorm(const float* in, float* out, const float* gamma, const floa
 // =====================================================================================
 __global__ void __launch_bounds__(256) mix_dense_kernel(const float2* __restrict__ X,
                                                         const float2* __restrict__ Wm,
-                                                        float2* __restrict__ Y, int B, int Ci, int Co) {
+                                                        float2* __restrict__ Y, int B, int Ci, int Co,
+                                                        MixImageOut im) {
   extern __shared__ float2 s_x[];  // [8][Ci]
   const int m = blockIdx.x;
   const int b0 = blockIdx.y * 8;
@@ -327,18 +342,85 @@ __global__ void __launch_bounds__(256) mix_dense_kernel(const float2* __restrict
       ai = fmaf(xv.x, wv.y, ai);
       ai = fmaf(xv.y, wv.x, ai);
     }
-    Y[((long long)m * B + b) * Co + o] = make_float2(ar, ai);
+    if (im.img) mix_store_image(im, m, b, o, make_float2(ar, ai));
+    else Y[((long long)m * B + b) * Co + o] = make_float2(ar, ai);
+  }
+}
+
+// Few samples (B <= 4, e.g. one 721 x 1440 field per GPU): the launch is bound by reading every
+// mode's Ci x Co weights once.  Eight warps per mode each take an eighth of the input channels
+// with 16-byte weight loads (two outputs per lane), then the partial sums meet in shared memory.
+__global__ void __launch_bounds__(256) mix_dense_fewb_kernel(const float2* __restrict__ X,
+                                                             const float2* __restrict__ Wm,
+                                                             float2* __restrict__ Y, int B, int Ci, int Co,
+                                                             MixImageOut im) {
+  extern __shared__ float2 s_mix[];   // x [4][Ci], then partial sums [8][4][Co]
+  float2* s_x = s_mix;
+  float2* s_p = s_mix + 4 * Ci;
+  const int m = blockIdx.x, lane = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + lane;
+  for (int idx = tid; idx < 4 * Ci; idx += 256) {
+    const int bb = idx / Ci, i = idx - bb * Ci;
+    s_x[idx] = bb < B ? X[((long long)m * B + bb) * Ci + i] : make_float2(0.f, 0.f);
+  }
+  __syncthreads();
+  const int half = Co >> 1;
+  const float4* __restrict__ w4 = reinterpret_cast<const float4*>(Wm + (long long)m * Ci * Co);
+  const int i0 = ty * Ci / 8, i1 = (ty + 1) * Ci / 8;
+  for (int op = lane; op < half; op += 32) {
+    float2 a[4][2];
+#pragma unroll
+    for (int bb = 0; bb < 4; ++bb) a[bb][0] = a[bb][1] = make_float2(0.f, 0.f);
+#pragma unroll 4
+    for (int i = i0; i < i1; ++i) {
+      const float4 wv = w4[(long long)i * half + op];
+#pragma unroll
+      for (int bb = 0; bb < 4; ++bb) {
+        const float2 xv = s_x[bb * Ci + i];
+        a[bb][0].x = fmaf(xv.x, wv.x, a[bb][0].x);
+        a[bb][0].x = fmaf(-xv.y, wv.y, a[bb][0].x);
+        a[bb][0].y = fmaf(xv.x, wv.y, a[bb][0].y);
+        a[bb][0].y = fmaf(xv.y, wv.x, a[bb][0].y);
+        a[bb][1].x = fmaf(xv.x, wv.z, a[bb][1].x);
+        a[bb][1].x = fmaf(-xv.y, wv.w, a[bb][1].x);
+        a[bb][1].y = fmaf(xv.x, wv.w, a[bb][1].y);
+        a[bb][1].y = fmaf(xv.y, wv.z, a[bb][1].y);
+      }
+    }
+#pragma unroll
+    for (int bb = 0; bb < 4; ++bb)
+      *reinterpret_cast<float4*>(&s_p[(ty * 4 + bb) * Co + 2 * op]) = make_float4(a[bb][0].x, a[bb][0].y, a[bb][1].x, a[bb][1].y);
+  }
+  __syncthreads();
+  for (int idx = tid; idx < B * Co; idx += 256) {
+    const int bb = idx / Co, o = idx - bb * Co;
+    float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      const float2 v = s_p[(w * 4 + bb) * Co + o];
+      acc.x += v.x;
+      acc.y += v.y;
+    }
+    if (im.img) mix_store_image(im, m, bb, o, acc);
+    else Y[((long long)m * B + bb) * Co + o] = acc;
   }
 }
 
 int launch_mix_dense(const float2* X, const float2* Wm, float2* Y, int modes, int B, int Ci, int Co,
-                     cudaStream_t st) {
+                     cudaStream_t st, MixImageOut im) {
   DLWP_REQUIRE(modes > 0 && B > 0 && Ci > 0 && Co > 0, "mix_dense: empty problem");
+  DLWP_REQUIRE(!im.img || (Co == 128 && im.Kc > 0 && modes % im.Kc == 0 && modes / im.Kc <= 64),
+               "mix_dense: the image output is laid out for 128 channels and at most 64 retained rows");
+  const size_t smem_few = (size_t)(4 * Ci + 32 * Co) * sizeof(float2);
+  if (B <= 4 && Co % 2 == 0 && Ci >= 8 && smem_few <= 48 * 1024) {
+    mix_dense_fewb_kernel<<<dim3((unsigned)modes), dim3(32, 8), smem_few, st>>>(X, Wm, Y, B, Ci, Co, im);
+    DLWP_LAUNCHED("mix_dense_kernel");
+    return DLWP_OK;
+  }
   const size_t smem = (size_t)8 * Ci * sizeof(float2);
   DLWP_REQUIRE(smem <= 48 * 1024, "mix_dense: Ci=%d too large for the fp32 path", Ci);
   DLWP_REQUIRE(ceil_div(B, 8) < 65536, "mix_dense: batch too large");
   dim3 grid((unsigned)modes, (unsigned)ceil_div(B, 8));
-  mix_dense_kernel<<<grid, dim3(32, 8), smem, st>>>(X, Wm, Y, B, Ci, Co);
+  mix_dense_kernel<<<grid, dim3(32, 8), smem, st>>>(X, Wm, Y, B, Ci, Co, im);
   DLWP_LAUNCHED("mix_dense_kernel");
   return DLWP_OK;
 }
@@ -557,7 +639,7 @@ int launch_nhwc_to_nchw(const float* in, float* out, int B, int C, int HW, cudaS
 
 // =====================================================================================
 // Latitude-weighted error sums, scripts/evaluate.py:790-820.  One block per (t, c, chunk of
-// samples); fp64 accumulation; one atomicAdd per block and statistic.
+// samples, slice of the plane); fp64 accumulation; one atomicAdd per block and statistic.
 // =====================================================================================
 __global__ void __launch_bounds__(256) metrics_kernel(const float* __restrict__ o, const float* __restrict__ t,
                                                       const float* __restrict__ clim,
@@ -566,10 +648,12 @@ __global__ void __launch_bounds__(256) metrics_kernel(const float* __restrict__ 
   const int tc = blockIdx.x;  // t * C + c
   const int ti = tc / C, c = tc - ti * C;
   const int HW = H * W;
+  const int slice = (HW + gridDim.z - 1) / gridDim.z;
+  const int p_lo = blockIdx.z * slice, p_hi = p_lo + slice < HW ? p_lo + slice : HW;
   double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
   for (int b = blockIdx.y; b < B; b += gridDim.y) {
     const long long base = (((long long)b * T + ti) * C + c) * HW;
-    for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+    for (int p = p_lo + threadIdx.x; p < p_hi; p += blockDim.x) {
       const float w = latw[p / W];
       const float ov = o[base + p], tv = t[base + p];
       const float cv = clim ? clim[(long long)c * HW + p] : 0.f;
@@ -601,7 +685,13 @@ int launch_metrics(const float* o, const float* t, const float* clim, const floa
   DLWP_REQUIRE(B > 0 && T > 0 && C > 0 && H > 0 && W > 0, "metrics: empty problem");
   DLWP_REQUIRE((long long)T * C < (1ll << 31), "metrics: too many (lead time, variable) pairs");
   int by = B < 64 ? B : 64;
-  dim3 grid((unsigned)(T * C), (unsigned)by);
+  // large planes with few samples: slice the plane so that the grid still covers the machine
+  long long bz = (1184 + (long long)T * C * by - 1) / ((long long)T * C * by);
+  const long long bz_max = ((long long)H * W + 4095) / 4096;
+  if (bz > bz_max) bz = bz_max;
+  if (bz < 1) bz = 1;
+  if (bz > 65535) bz = 65535;
+  dim3 grid((unsigned)(T * C), (unsigned)by, (unsigned)bz);
   metrics_kernel<<<grid, 256, 0, st>>>(o, t, clim, latw, B, T, C, H, W, sums);
   DLWP_LAUNCHED("metrics_kernel");
   return DLWP_OK;

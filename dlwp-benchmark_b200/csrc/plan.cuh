@@ -67,10 +67,12 @@ struct dlwp_plan {
 
   // bf16 tensor-core path at hidden width 128 (tc_wide.cuh): precision == DLWP_PREC_BF16
   bool tcw = false;
-  int tcw_TW = 0, tcw_KZ = 0;                           // tiles per grid row; K extent of the inverse W-DFT operands
+  int tcw_TW = 0, tcw_KZ = 0, tcw_HB = 0;               // tiles per grid row; K extent of the inverse W-DFT operands; blocks of 64 grid rows
   uint8_t *tcw_in = nullptr, *tcw_hid = nullptr, *tcw_z = nullptr;
   uint8_t* tcw_x[2] = {nullptr, nullptr};               // activation tile images (ping-pong)
   uint8_t *tcw_G = nullptr, *tcw_F = nullptr;           // inverse / forward W-DFT tiles
+  uint8_t *tcw_Gs = nullptr, *tcw_Fs = nullptr;         // inverse / forward H-DFT tiles ((re | im)-stacked)
+  uint8_t *tcw_sa = nullptr, *tcw_ys = nullptr;         // spectrum images after the W-DFT / after the mode mixing
   uint8_t *tcw_W1 = nullptr, *tcw_W2 = nullptr, *tcw_b2 = nullptr, *tcw_P1 = nullptr, *tcw_pb1 = nullptr,
           *tcw_P2 = nullptr, *tcw_pb2 = nullptr;
   std::vector<uint8_t*> tcw_skip, tcw_cbias;            // per layer skip-conv and bias images

@@ -6,8 +6,9 @@
 //   warp 8    : loader  -- bulk async copies of the streamed operands into a ring of stages
 //   warp 9    : issuer  -- tcgen05.mma into one of two TMEM accumulators (256 columns each)
 // The three sides meet only on mbarriers (full / empty per stage, acc_full / acc_empty per
-// accumulator).  An item is one 128-slot tile (one grid row for TCW_FWD) and consists of one or
-// more K blocks, each one stage of the ring.  Weights stay resident in shared memory; biases are
+// accumulator).  An item is one 128-slot tile (one grid row for TCW_FWD, one (sample, retained
+// column) for TCW_HFWD, one (sample, retained column, block of 64 grid rows) for TCW_HINV) and
+// consists of one or more K blocks, each one stage of the ring.  Weights stay resident in shared memory; biases are
 // added by one extra K = 16 MMA of a ones operand with a [N x 16] bias image (hi, lo columns).
 #include "tc_wide.cuh"
 
@@ -49,6 +50,8 @@ template <> struct WT<TCW_FWD> {
   static constexpr int N = 128, NS = 3, RES = 0, BIAS = 0, OUT = 0, NOUT = 1;
   __host__ __device__ static int stage(int) { return 2 * kXTile; }   // forward DFT tile + activation tile
 };
+template <> struct WT<TCW_HFWD> : WT<TCW_FWD> {};   // forward H-DFT: DFT tile + spectrum image per 64 grid rows
+template <> struct WT<TCW_HINV> : WT<TCW_FWD> {};   // inverse H-DFT: DFT tile + mixed-spectrum image
 template <> struct WT<TCW_LAYER> {
   static constexpr int N = 128, NS = 2, RES = 128 * 128 * 2, BIAS = 128 * 32, OUT = kXTile, NOUT = 1;
   __host__ __device__ static int stage(int KZ) { return kXTile + 2 * KZ * 256; }   // x, G tile, Z row image
@@ -100,6 +103,8 @@ namespace {
 template <int MODE>
 __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
   using T = WT<MODE>;
+  // the three DFT GEMMs contract over the rows of a tile image read in place as an MN-major B operand
+  constexpr bool kDft = MODE == TCW_FWD || MODE == TCW_HFWD || MODE == TCW_HINV;
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bars[2 * kMaxStages + 5];
   __shared__ uint32_t tmem_slot;
@@ -113,7 +118,7 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int stage_bytes = T::stage(a.KZ);
-  const int nblk = (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) ? 2 : (MODE == TCW_FWD ? a.TW : 1);
+  const int nblk = (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) ? 2 : (MODE == TCW_FWD ? a.TW : (MODE == TCW_HFWD ? a.HB : 1));
   uint8_t* sRes = smem;
   uint8_t* sBias = sRes + T::RES;
   uint8_t* sOnes = sBias + T::BIAS;
@@ -166,9 +171,12 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
           bulk_g2s_p(leader, st, a.a_img + (size_t)item * kInTile, kInTile, &full[s]);
         } else if (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) {
           bulk_g2s_p(leader, st, a.a_img + (size_t)item * kHidTile + (size_t)blk * kXTile, kXTile, &full[s]);
-        } else if (MODE == TCW_FWD) {
-          bulk_g2s_p(leader, st, a.g_img + (size_t)blk * kXTile, kXTile, &full[s]);
-          bulk_g2s_p(leader, st + kXTile, a.a_img + ((size_t)item * a.TW + blk) * kXTile, kXTile, &full[s]);
+        } else if (kDft) {
+          // DFT tile: one per tile of the grid row / per block of 64 grid rows; image: this item's block
+          const size_t gi = MODE == TCW_HINV ? (size_t)(item % a.HB) : (size_t)blk;
+          const size_t ai = MODE == TCW_HINV ? (size_t)(item / a.HB) : (size_t)item * nblk + blk;
+          bulk_g2s_p(leader, st, a.g_img + gi * kXTile, kXTile, &full[s]);
+          bulk_g2s_p(leader, st + kXTile, a.a_img + ai * kXTile, kXTile, &full[s]);
         } else if (MODE == TCW_LAYER) {
           const uint32_t zb = (uint32_t)a.KZ * 256u;
           bulk_g2s_p(leader, st, a.a_img + (size_t)item * kXTile, kXTile, &full[s]);
@@ -185,7 +193,7 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
     const uint32_t leader = elect_one();
     pdl_wait();
     if (T::RES + T::BIAS > 0) mbar_wait(res_bar, 0);
-    const uint32_t idesc = idesc_bf16(128, T::N) | (MODE == TCW_FWD ? kIdescBMnMajor : 0u);
+    const uint32_t idesc = idesc_bf16(128, T::N) | (kDft ? kIdescBMnMajor : 0u);
     const uint64_t dRes = chunk_desc(smem_u32(sRes), T::N, 0);
     const uint32_t bstep = 2u * T::N * 16u;   // resident operand: bytes per K = 16 step
     uint32_t u = 0, it = 0;
@@ -208,7 +216,7 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dB, j * bstep), idesc, (blk | j) != 0);
-        } else if (MODE == TCW_FWD) {
+        } else if (kDft) {
           // B: the activation image read in place as an MN-major operand (pixels = K, 8 x 8 core
           // matrices 128 B apart along pixels, 2048 B along channels)
           const uint64_t dX = smem_desc(st + kXTile, 128, 2048);
@@ -219,9 +227,11 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
           const uint32_t zb = (uint32_t)a.KZ * 256u;
-          const uint64_t dG = chunk_desc(st + kXTile, 128, 0), dZ = chunk_desc(st + kXTile + zb, 128, 0);
+          // Z of this grid row: [KZ rows = (retained column, re | im)] x [128 channels], MN-major (as
+          // the inverse H-DFT epilogue stores it): core matrices 128 B apart along K, KZ * 16 B along channels
+          const uint64_t dG = chunk_desc(st + kXTile, 128, 0), dZ = smem_desc(st + kXTile + zb, 128, (uint32_t)a.KZ * 16u);
           for (int j = 0; j < (a.KZ >> 4); ++j)
-            umma_bf16_p(leader, d, desc_off(dG, j * 4096), desc_off(dZ, j * 4096), idesc, 1u);
+            umma_bf16_p(leader, d, desc_off(dG, j * 4096), desc_off(dZ, j * 256), idesc | kIdescBMnMajor, 1u);
         } else {   // TCW_PROJ1
 #pragma unroll
           for (int j = 0; j < 8; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
@@ -251,6 +261,22 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
         }
         bar_sync(1, kWEpi);
       }
+      // TCW_PROJ2: fetch the residual frame before waiting for the accumulator, so that its latency is
+      // not part of the accumulator's round trip
+      float lastv[8];
+      size_t oidx = 0;
+      bool pvalid = false;
+      if (MODE == TCW_PROJ2) {
+        const int w = (item % a.TW) * 128 + row, rid = item / a.TW;
+        const int b = rid / a.H, h = rid - b * a.H;
+        pvalid = w < a.W && half * 8 < a.Cg;
+        const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
+        oidx = (size_t)b * a.out_bstride + (size_t)(half * 8) * plane + px;
+        const size_t lidx = (size_t)b * a.last_bstride + (size_t)(half * 8) * plane + px;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          lastv[j] = (pvalid && a.last && half * 8 + j < a.Cg) ? a.last[lidx + j * plane] : 0.f;
+      }
       mbar_wait(&acc_full[acc], (it >> 1) & 1u);
       tc_fence_after();
       if (MODE == TCW_LIFT1 || MODE == TCW_LIFT2 || MODE == TCW_LAYER || MODE == TCW_PROJ1) {
@@ -272,14 +298,57 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
           bulk_s2g(a.out_img + (size_t)item * T::OUT, ob, T::OUT);
           bulk_commit();
         }
-      } else if (MODE == TCW_FWD) {
-        // accumulator row k = 2 kx + (re | im), columns = channels.  Lane pairs swap halves of each
-        // 16-column block so that every lane stores whole complex values: the even lane (re) keeps
-        // channels c0..c0+7, the odd lane (im) channels c0+8..c0+15.
-        if (q4 * 32 < 2 * a.Kc) {
-          const int kx = row >> 1, odd = lane & 1;
-          const bool valid = row < 2 * a.Kc;
-          float2* dst = a.spec + ((size_t)item * a.Kc + kx) * kWideC;
+      } else if (MODE == TCW_FWD || MODE == TCW_HINV) {
+        // bf16 operand images for the next DFT GEMM.  Accumulator row = (index, re | im), columns =
+        // channels; every lane stores 16-byte chunk rows (8 channels), re / im lanes side by side.
+        //   TCW_FWD : row k = 2 kx + (re | im) of grid row `item`  -> spectrum image (sample, kx, h / 64),
+        //             image row 2 (h % 64) + (re | im)
+        //   TCW_HINV: row 2 (h % 64) + (re | im) of (sample, kx, h / 64) -> Z image of grid row h,
+        //             image row k = 2 kx + (re | im)   (MN-major operand of TCW_LAYER, KZ rows)
+        bool valid;
+        uint8_t* dst;
+        uint32_t cstride;   // bytes between 8-channel chunks
+        if (MODE == TCW_FWD) {
+          const int b = item / a.H, h = item - b * a.H, kx = row >> 1;
+          valid = row < 2 * a.Kc;
+          dst = a.out_img + (((size_t)b * a.Kc + kx) * a.HB + (h >> 6)) * kXTile + (size_t)(((h & 63) << 1) | (row & 1)) * 16;
+          cstride = 2048;
+        } else {
+          const int hb = item % a.HB, bk = item / a.HB;
+          const int b = bk / a.Kc, kx = bk - b * a.Kc, h = hb * 64 + (row >> 1);
+          valid = h < a.H;
+          dst = a.out_img + ((size_t)b * a.H + h) * ((size_t)a.KZ * 256) + (size_t)((kx << 1) | (row & 1)) * 16;
+          cstride = (uint32_t)a.KZ * 16u;
+        }
+        if (MODE == TCW_HINV || q4 * 32 < 2 * a.Kc) {
+#pragma unroll 1
+          for (int i = 0; i < 4; ++i) {
+            const int c0 = half * 64 + i * 16;
+            uint32_t r[16];
+            tmem_ld16(d + (uint32_t)c0, r);
+            tmem_ld_wait();
+            if (valid) {
+              uint32_t o[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                o[e] = pack_bf16(__uint_as_float(r[2 * e]) * a.scale, __uint_as_float(r[2 * e + 1]) * a.scale);
+              uint8_t* p = dst + (size_t)(c0 >> 3) * cstride;
+              *reinterpret_cast<uint4*>(p) = make_uint4(o[0], o[1], o[2], o[3]);
+              *reinterpret_cast<uint4*>(p + cstride) = make_uint4(o[4], o[5], o[6], o[7]);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&acc_empty[acc]);
+      } else if (MODE == TCW_HFWD) {
+        // accumulator row 2 r + (re | im) of (sample, kx), columns = channels -> X [R, Kc, B, 128] complex fp32
+        // (what mix_dense reads).  Lane pairs swap halves of each 16-column block so that every lane
+        // stores whole complex values: the even lane keeps channels c0..c0+7, the odd lane c0+8..c0+15.
+        if (q4 * 32 < 2 * a.R) {
+          const int b = item / a.Kc, kx = item - b * a.Kc;
+          const int rr = row >> 1, odd = lane & 1;
+          const bool valid = row < 2 * a.R;
+          float2* dst = a.spec + (((size_t)rr * a.Kc + kx) * a.B + b) * kWideC;
 #pragma unroll 1
           for (int i = 0; i < 4; ++i) {
             const int c0 = half * 64 + i * 16;
@@ -289,8 +358,8 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
             float2 o[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float mine = __uint_as_float(odd ? r[8 + j] : r[j]) * a.scale;
-              const float send = __uint_as_float(odd ? r[j] : r[8 + j]) * a.scale;
+              const float mine = __uint_as_float(odd ? r[8 + j] : r[j]);
+              const float send = __uint_as_float(odd ? r[j] : r[8 + j]);
               const float got = __shfl_xor_sync(0xffffffffu, send, 1);
               o[j] = odd ? make_float2(got, mine) : make_float2(mine, got);
             }
@@ -304,27 +373,19 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
         tc_fence_before();
         mbar_arrive(&acc_empty[acc]);
       } else {   // TCW_PROJ2: accumulator columns = output channels, rows = pixel slots
+        uint32_t r[8];
         if (half * 8 < a.Cg) {
-          uint32_t r[8];
           tmem_ld8(d + (uint32_t)(half * 8), r);
           tmem_ld_wait();
-          const int w = (item % a.TW) * 128 + row, rid = item / a.TW;
-          const int b = rid / a.H, h = rid - b * a.H;
-          if (w < a.W) {
-            const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int co = half * 8 + j;
-              if (co < a.Cg) {
-                float v = __uint_as_float(r[j]);
-                if (a.last) v += a.last[(size_t)b * a.last_bstride + co * plane + px];
-                a.out[(size_t)b * a.out_bstride + co * plane + px] = v;
-              }
-            }
-          }
         }
         tc_fence_before();
         mbar_arrive(&acc_empty[acc]);
+        if (pvalid) {
+          const size_t plane = (size_t)a.H * a.W;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (half * 8 + j < a.Cg) a.out[oidx + j * plane] = __uint_as_float(r[j]) + lastv[j];
+        }
       }
     }
     if (T::OUT && tid == 0) bulk_wait0();
@@ -343,45 +404,31 @@ __global__ void __launch_bounds__(128) wide_gather_kernel(const WideGatherArgs a
   const int w = (tile % a.TW) * 128 + s, rid = tile / a.TW;
   const int b = rid / a.H, h = rid - b * a.H;
   const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
-  __nv_bfloat16 v[32];
-#pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __float2bfloat16(0.f);
+  float x[14];
   pdl_wait();
-  if (w < a.W) {
-    int c = 0;
-    for (int g = 0; g < a.ngrp; ++g)
-      for (int ch = 0; ch < a.grp[g].nch; ++ch, ++c) {
-        const float x = a.grp[g].base[(size_t)b * a.grp[g].bstride + ch * plane + px];
-        const __nv_bfloat16 hi = __float2bfloat16(x);
 #pragma unroll
-        for (int i = 0; i < 14; ++i)
-          if (i == c) {
-            v[i] = hi;
-            v[16 + i] = __float2bfloat16(x - __bfloat162float(hi));
-          }
-      }
+  for (int c = 0; c < 14; ++c) {
+    x[c] = 0.f;
+    if (c < a.Cin && w < a.W) {
+      int g = 0, ch = c;
+      while (ch >= a.grp[g].nch) ch -= a.grp[g++].nch;   // uniform: which source group holds channel c
+      x[c] = a.grp[g].base[(size_t)b * a.grp[g].bstride + ch * plane + px];
+    }
   }
+  uint32_t v[16];   // bf16 pairs: columns (2 i, 2 i + 1)
 #pragma unroll
-  for (int i = 0; i < 16; ++i)
-    if (i == a.Cin || i == 15) v[i] = __float2bfloat16(1.f);
+  for (int i = 0; i < 8; ++i) {
+    const float x0 = 2 * i < 14 ? x[2 * i < 14 ? 2 * i : 0] : 0.f, x1 = 2 * i + 1 < 14 ? x[2 * i + 1 < 14 ? 2 * i + 1 : 0] : 0.f;
+    const float h0 = (2 * i == a.Cin || 2 * i == 15) ? 1.f : x0, h1 = (2 * i + 1 == a.Cin || 2 * i + 1 == 15) ? 1.f : x1;
+    const __nv_bfloat162 hi = __floats2bfloat162_rn(h0, h1);
+    const float2 hf = __bfloat1622float2(hi);
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(2 * i < a.Cin ? x0 - hf.x : 0.f, 2 * i + 1 < a.Cin ? x1 - hf.y : 0.f);
+    v[i] = *reinterpret_cast<const uint32_t*>(&hi);
+    v[8 + i] = *reinterpret_cast<const uint32_t*>(&lo);
+  }
   uint8_t* img = a.in_img + (size_t)tile * kInTile + s * 16;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(img + j * 2048) = *reinterpret_cast<const uint4*>(&v[8 * j]);
-}
-
-// Z [rows, Kc, 128] complex -> per-row [128 channels x KZ] operand image, k = 2 kx + (re | im)
-__global__ void __launch_bounds__(128) wide_zimg_kernel(const float2* __restrict__ Z, uint8_t* __restrict__ img, int Kc,
-                                                        int KZ) {
-  const int rowi = blockIdx.x, j = blockIdx.y, c = threadIdx.x;   // j = chunk of 8 k = 4 retained columns
-  const float2* z = Z + (size_t)rowi * Kc * kWideC + c;
-  uint32_t o[4];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int kx = 4 * j + q;
-    const float2 v = kx < Kc ? z[(size_t)kx * kWideC] : make_float2(0.f, 0.f);
-    o[q] = pack_bf16(v.x, v.y);
-  }
-  *reinterpret_cast<uint4*>(img + (size_t)rowi * KZ * 256 + j * 2048 + c * 16) = make_uint4(o[0], o[1], o[2], o[3]);
+  for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(img + j * 2048) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
 }
 
 }  // namespace
@@ -416,6 +463,8 @@ int launch_tcw(int mode, const TcwArgs& a, cudaStream_t st) {
     case TCW_LIFT1: return launch_tcw_mode<TCW_LIFT1>(a, st, "tcw_lift1");
     case TCW_LIFT2: return launch_tcw_mode<TCW_LIFT2>(a, st, "tcw_lift2");
     case TCW_FWD: return launch_tcw_mode<TCW_FWD>(a, st, "tcw_fwd_wdft");
+    case TCW_HFWD: return launch_tcw_mode<TCW_HFWD>(a, st, "tcw_fwd_hdft");
+    case TCW_HINV: return launch_tcw_mode<TCW_HINV>(a, st, "tcw_inv_hdft");
     case TCW_LAYER: return launch_tcw_mode<TCW_LAYER>(a, st, "tcw_layer");
     case TCW_PROJ1: return launch_tcw_mode<TCW_PROJ1>(a, st, "tcw_proj1");
     case TCW_PROJ2: return launch_tcw_mode<TCW_PROJ2>(a, st, "tcw_proj2");
@@ -428,14 +477,6 @@ int launch_wide_gather(const WideGatherArgs& a, cudaStream_t st) {
   void (*kern)(WideGatherArgs) = wide_gather_kernel;
   DLWP_CUDA(launch_pdl(kern, dim3((unsigned)a.ntiles), dim3(128), 0, st, a));
   DLWP_LAUNCHED("wide_gather_kernel");
-  return DLWP_OK;
-}
-
-int launch_wide_zimg(const float2* Z, uint8_t* z_img, int rows, int Kc, int KZ, cudaStream_t st) {
-  // chunks past 2 Kc stay zero from the plan's memset
-  const int nchunk = (2 * Kc + 7) / 8;
-  wide_zimg_kernel<<<dim3((unsigned)rows, (unsigned)nchunk), 128, 0, st>>>(Z, z_img, Kc, KZ);
-  DLWP_LAUNCHED("wide_zimg_kernel");
   return DLWP_OK;
 }
 

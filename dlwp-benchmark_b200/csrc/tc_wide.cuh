@@ -14,9 +14,14 @@
 //   tcw LIFT1            hidden = gelu(W1 x + b1)                  -> [128 x 256] images
 //   tcw LIFT2            x0 = W2 hidden + b2                       -> [128 x 128] images
 //   per layer:
-//     tcw FWD            A[h, kx, c] = sum_w F[kx, w] x[h, w, c]   (fp32 spectrum, one item per grid row)
-//     tdft / mix / tdft  H-DFT, per-mode channel mixing, inverse H-DFT (fp32 FMA, kernels_fp32.cu)
-//     wide_zimg_kernel   Z[h, kx, c] -> [128 channels x KZ] bf16 operand image per grid row
+//     tcw FWD            A[h, kx, c] = sum_w F[kx, w] x[h, w, c]   one item per grid row -> bf16 spectrum images
+//                        per (sample, kx, block of 64 grid rows): rows (h, re | im), columns = channels
+//     tcw HFWD           X[r, kx, c] = sum_h Fh[r, h] A[h, kx, c]  complex product as one real GEMM with
+//                        (re | im)-stacked rows, contracting over the image rows -> fp32 [R, Kc, B, 128]
+//     mix_dense          per-mode channel mixing (fp32 FMA, kernels_fp32.cu) -> bf16 images per (sample, kx):
+//                        rows (r, re | im), columns = channels
+//     tcw HINV           Z[h, kx, c] = sum_r Gh[h, r] Y[r, kx, c]  -> per grid row [KZ rows (kx, re | im)] x
+//                        [128 channels] bf16 (the MN-major B operand of the inverse W-DFT)
 //     tcw LAYER          x' = act(G Z + Wskip x + bias)            -> [128 x 128] images
 //   tcw PROJ1            hidden = gelu(P1 x + b1)                  -> [128 x 256] images
 //   tcw PROJ2            out = P2 hidden + b2 + last frame         -> NCHW fp32
@@ -29,20 +34,21 @@ namespace dlwp {
 constexpr int kWideC = 128;     // hidden channels
 constexpr int kWideHid = 256;   // lifting / projection width
 
-enum TcwMode { TCW_LIFT1 = 0, TCW_LIFT2 = 1, TCW_FWD = 2, TCW_LAYER = 3, TCW_PROJ1 = 4, TCW_PROJ2 = 5 };
+enum TcwMode { TCW_LIFT1 = 0, TCW_LIFT2 = 1, TCW_FWD = 2, TCW_LAYER = 3, TCW_PROJ1 = 4, TCW_PROJ2 = 5, TCW_HFWD = 6, TCW_HINV = 7 };
 
 struct TcwArgs {
-  int nitems;             // tiles (B * H * TW); grid rows (B * H) for TCW_FWD
+  int nitems;             // tiles (B * H * TW); grid rows (B * H) for TCW_FWD; B * Kc (* HB) for TCW_HFWD (TCW_HINV)
   int TW, H, W;           // tiles per grid row, grid rows per sample, grid width
+  int B, R, HB;           // samples, retained rows (2 R <= 128), blocks of 64 grid rows per sample
   int Kc, KZ;             // retained columns; K extent of the inverse W-DFT operands (2 Kc padded to 16)
   const uint8_t* a_img;   // streamed tile images: input [128 x 32] / hidden [128 x 256] / activation [128 x 128]
   const uint8_t* b_res;   // resident weight image [N rows x K]
   const uint8_t* bias_img;// [N rows x 16]: columns 0 / 1 = hi / lo of the bias (times a ones operand), or null
-  const uint8_t* g_img;   // TCW_LAYER: TW inverse W-DFT tiles [128 x KZ]; TCW_FWD: TW forward tiles [128 x 128]
-  const uint8_t* z_img;   // TCW_LAYER: per grid row [128 x KZ]
-  uint8_t* out_img;       // tile images out
-  float2* spec;           // TCW_FWD: [B, H, Kc, 128] complex
-  float scale;            // TCW_FWD: factor on the spectrum (1/2 when the input image holds 2 * gelu)
+  const uint8_t* g_img;   // TCW_LAYER: TW inverse W-DFT tiles [128 x KZ]; DFT modes: the [128 x 128] DFT tiles
+  const uint8_t* z_img;   // TCW_LAYER: per grid row [KZ x 128 channels] (MN-major)
+  uint8_t* out_img;       // tile images out (TCW_FWD: spectrum images; TCW_HINV: Z images)
+  float2* spec;           // TCW_HFWD: X [R, Kc, B, 128] complex
+  float scale;            // TCW_FWD / TCW_HINV: factor on the result (1/2 when the input image holds 2 * gelu)
   int gelu;               // TCW_LAYER: apply GELU
   float* out;             // TCW_PROJ2: NCHW frame(s) out[b * out_bstride + (c, y, x)]
   long long out_bstride;
@@ -59,9 +65,6 @@ struct WideGatherArgs {
   uint8_t* in_img;        // [ntiles] x [128 x 32]
 };
 int launch_wide_gather(const WideGatherArgs& a, cudaStream_t st);
-
-// Z [rows, Kc, 128] complex fp32 -> per-row operand image [128 channels x KZ], k = 2 kx + (re | im)
-int launch_wide_zimg(const float2* Z, uint8_t* z_img, int rows, int Kc, int KZ, cudaStream_t st);
 
 // host: chunk-major bf16 image of a row-major matrix `m` [rows, cols] padded to R x K with zeros
 void tcw_pack_image(const float* m, int rows, int cols, int ld, int R, int K, uint8_t* out);

@@ -21,7 +21,8 @@ int plan_tcw_build(dlwp_plan* p) {
                "DLWP_PREC_BF16: %d input / %d output channels exceed 14 / 16", p->Cin, d.prognostic_channels);
   const int H = d.height, W = d.width, Kc = d.n_cols;
   const int KZ = (2 * Kc + 15) & ~15;
-  DLWP_REQUIRE(Kc >= 1 && KZ <= 80 && d.n_rows >= 1, "DLWP_PREC_BF16: %d retained columns (at most 40)", Kc);
+  DLWP_REQUIRE(Kc >= 1 && KZ <= 80 && d.n_rows >= 1 && d.n_rows <= 64,
+               "DLWP_PREC_BF16: %d x %d retained modes (at most 64 rows, 40 columns)", d.n_rows, Kc);
   const int TW = (W + 127) / 128;
   p->tcw_TW = TW;
   p->tcw_KZ = KZ;
@@ -62,12 +63,49 @@ int plan_tcw_build(dlwp_plan* p) {
   DLWP_CUDA(cudaMemcpy(p->tcw_G, gi.data(), gi.size(), cudaMemcpyHostToDevice));
   DLWP_CUDA(cudaMemcpy(p->tcw_F, fi.data(), fi.size(), cudaMemcpyHostToDevice));
 
+  // H-DFT tiles, one per block of 64 grid rows; complex products as real GEMMs on (re | im)-stacked indices:
+  //   Fs[(r, re|im), (h, re|im)] : X = Fh A,  Fh[r, h] = exp(-2 pi i rows_in[r] h / H)
+  //   Gs[(h, re|im), (r, re|im)] : Z = Gh Y,  Gh[h, r] = exp(+2 pi i rows_out[r] h / H)
+  const int HB = (H + 63) / 64, R = d.n_rows;
+  p->tcw_HB = HB;
+  std::vector<uint8_t> fsi((size_t)HB * fbytes), gsi((size_t)HB * fbytes);
+  std::vector<double> Fs((size_t)128 * 128), Gs((size_t)128 * 128);
+  for (int hb = 0; hb < HB; ++hb) {
+    std::fill(Fs.begin(), Fs.end(), 0.0);
+    std::fill(Gs.begin(), Gs.end(), 0.0);
+    for (int hh = 0; hh < 64; ++hh) {
+      const int h = hb * 64 + hh;
+      if (h >= H) continue;
+      for (int r = 0; r < R; ++r) {
+        const double af = -2.0 * M_PI * (double)(((long long)p->rows_in[r] * h) % H) / (double)H;
+        const double ag = 2.0 * M_PI * (double)(((long long)p->rows_out[r] * h) % H) / (double)H;
+        const double fr = std::cos(af), fi2 = std::sin(af), gr = std::cos(ag), gi2 = std::sin(ag);
+        Fs[(size_t)(2 * r) * 128 + 2 * hh] = fr;       Fs[(size_t)(2 * r) * 128 + 2 * hh + 1] = -fi2;
+        Fs[(size_t)(2 * r + 1) * 128 + 2 * hh] = fi2;  Fs[(size_t)(2 * r + 1) * 128 + 2 * hh + 1] = fr;
+        Gs[(size_t)(2 * hh) * 128 + 2 * r] = gr;       Gs[(size_t)(2 * hh) * 128 + 2 * r + 1] = -gi2;
+        Gs[(size_t)(2 * hh + 1) * 128 + 2 * r] = gi2;  Gs[(size_t)(2 * hh + 1) * 128 + 2 * r + 1] = gr;
+      }
+    }
+    tcw_pack_image_f64(Fs.data(), 128, 128, 128, 128, 128, fsi.data() + hb * fbytes);
+    tcw_pack_image_f64(Gs.data(), 128, 128, 128, 128, 128, gsi.data() + hb * fbytes);
+  }
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_Fs, fsi.size()));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_Gs, gsi.size()));
+  DLWP_CUDA(cudaMemcpy(p->tcw_Fs, fsi.data(), fsi.size(), cudaMemcpyHostToDevice));
+  DLWP_CUDA(cudaMemcpy(p->tcw_Gs, gsi.data(), gsi.size(), cudaMemcpyHostToDevice));
+  // spectrum images between the W- and H-DFTs (rows past H stay zero) and after the mode mixing (rows past 2 R stay zero)
+  const size_t sab = (size_t)d.max_batch * Kc * HB * fbytes, ysb = (size_t)d.max_batch * Kc * fbytes;
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_sa, sab));
+  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_ys, ysb));
+  DLWP_CUDA(cudaMemset(p->tcw_sa, 0, sab));
+  DLWP_CUDA(cudaMemset(p->tcw_ys, 0, ysb));
+
   const size_t nt = (size_t)d.max_batch * H * TW;
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_in, nt * 128 * 32 * 2));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_hid, nt * 128 * kWideHid * 2));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_x[0], nt * 128 * kWideC * 2));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_x[1], nt * 128 * kWideC * 2));
-  // per grid row [128 channels x KZ]; the K slots past 2 Kc stay zero from here on
+  // per grid row [KZ rows (kx, re | im)] x [128 channels]; the rows past 2 Kc stay zero from here on
   const size_t zb = (size_t)d.max_batch * H * KZ * 256;
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_z, zb));
   DLWP_CUDA(cudaMemset(p->tcw_z, 0, zb));
@@ -181,6 +219,7 @@ int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   TcwArgs base{};
   base.nitems = B * H * TW;
   base.TW = TW; base.H = H; base.W = W; base.Kc = d.n_cols; base.KZ = p->tcw_KZ;
+  base.B = B; base.R = d.n_rows; base.HB = p->tcw_HB;
   base.scale = 1.f;
 
   WideGatherArgs ga{};
@@ -198,12 +237,21 @@ int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
 
   int cur = 0;
   for (int l = 0; l < N; ++l) {
+    // forward W-DFT -> spectrum images; forward H-DFT -> X; mode mixing -> Y images; inverse H-DFT -> Z images
     a = base;
     a.nitems = B * H;
-    a.a_img = p->tcw_x[cur]; a.g_img = p->tcw_F; a.spec = p->specA; a.scale = l >= 1 ? 0.5f : 1.f;
+    a.a_img = p->tcw_x[cur]; a.g_img = p->tcw_F; a.out_img = p->tcw_sa; a.scale = l >= 1 ? 0.5f : 1.f;
     DLWP_TRY(launch_tcw(TCW_FWD, a, st));
-    DLWP_TRY(spectral_mid_fno(p, p->wm[l], B, st));
-    DLWP_TRY(launch_wide_zimg(p->specZ, p->tcw_z, B * H, d.n_cols, p->tcw_KZ, st));
+    a = base;
+    a.nitems = B * d.n_cols;
+    a.a_img = p->tcw_sa; a.g_img = p->tcw_Fs; a.spec = p->specX;
+    DLWP_TRY(launch_tcw(TCW_HFWD, a, st));
+    DLWP_TRY(launch_mix_dense(p->specX, p->wm[l], p->specY, d.n_rows * d.n_cols, B, kWideC, kWideC, st,
+                              MixImageOut{p->tcw_ys, d.n_cols}));
+    a = base;
+    a.nitems = B * d.n_cols * p->tcw_HB;
+    a.a_img = p->tcw_ys; a.g_img = p->tcw_Gs; a.out_img = p->tcw_z;
+    DLWP_TRY(launch_tcw(TCW_HINV, a, st));
     a = base;
     a.a_img = p->tcw_x[cur]; a.b_res = p->tcw_skip[l]; a.bias_img = p->tcw_cbias[l]; a.g_img = p->tcw_G;
     a.z_img = p->tcw_z; a.out_img = p->tcw_x[cur ^ 1]; a.gelu = l < N - 1 ? 1 : 0;

@@ -57,9 +57,20 @@ with torch.no_grad():
     print("lift (x0):", rel(to_grid(image("tcw_x0", 128)), x0))
     xf = torch.fft.rfft(x0, dim=-1, norm="forward")[..., :kw["n_modes"][1] // 2 + 1] / H   # [B, C, H, Kc]
     Kc = xf.shape[-1]
-    specA = plan.debug_read("specA", B * H * Kc * 128 * 8).view(torch.float32).view(B, H, Kc, 128, 2).cpu()
-    specA = torch.view_as_complex(specA.contiguous()).permute(0, 3, 1, 2)
-    print("fwd W-DFT (specA):", rel(torch.view_as_real(specA), torch.view_as_real(xf)))
+    HB = (H + 63) // 64
+    sa = plan.debug_read("tcw_sa", B * Kc * HB * 32768).view(torch.bfloat16).view(B, Kc, HB, 16, 128, 8)
+    sa = sa.permute(0, 1, 2, 4, 3, 5).reshape(B, Kc, HB * 64, 2, 128).float().cpu()[:, :, :H]      # [B, Kc, H, re|im, C]
+    specA = torch.complex(sa[..., 0, :], sa[..., 1, :]).permute(0, 3, 2, 1)                       # [B, C, H, Kc]
+    print("fwd W-DFT (spectrum images):", rel(torch.view_as_real(specA), torch.view_as_real(xf)))
+    from oracle.neuralop_fno import neuralop_row_bins
+    rin, rout = neuralop_row_bins(H, kw["n_modes"][0])
+    hh = torch.arange(H, dtype=torch.float64)
+    Fh = torch.exp(-2j * torch.pi * torch.tensor(rin, dtype=torch.float64)[:, None] * hh[None, :] / H)   # [R, H]
+    X = torch.einsum("rh,bchk->bcrk", Fh, xf.to(torch.complex128))
+    R = len(rin)
+    specX = plan.debug_read("specX", R * Kc * B * 128 * 8).view(torch.float32).view(R, Kc, B, 128, 2).cpu()
+    specX = torch.view_as_complex(specX.contiguous()).permute(2, 3, 0, 1)
+    print("fwd H-DFT (specX):", rel(torch.view_as_real(specX), torch.view_as_real(X.to(torch.complex64))))
     y_spec = fno.fno_blocks.convs(x0, 0)
     x1 = y_spec + fno.fno_blocks.fno_skips[0](x0)
     print("layer (x1):", rel(to_grid(image("tcw_x1", 128)), x1), " [spectral part scale", float(y_spec.abs().max()), "]")
