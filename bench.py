@@ -209,10 +209,10 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
             "wide_gather_kernel": 4 * px * cin + 2 * pxp * 32,
             "tcw_lift1": 2 * pxp * (32 + L),
             "tcw_lift2": 2 * pxp * (L + C),
-            "tcw_fwd_wdft": N * (2 * pxp * C + 4 * half),
-            "tdft_kernel": 4 * N * ((half + modes) + (modes + half)),
-            "mix_dense_kernel": 4 * N * (2 * modes + m1 * m2 * C * C * 2),
-            "wide_zimg_kernel": N * (4 * half + 2 * B * H * kz * C),
+            "tcw_fwd_wdft": N * (2 * pxp * C + 2 * B * m2 * ((H + 63) // 64) * 128 * C),
+            "tcw_fwd_hdft": N * (2 * B * m2 * ((H + 63) // 64) * 128 * C + 4 * modes),
+            "mix_dense_kernel": N * (4 * modes + 2 * B * m2 * 128 * C + 4 * m1 * m2 * C * C * 2),
+            "tcw_inv_hdft": N * (2 * B * m2 * 128 * C + 2 * B * H * kz * C),
             "tcw_layer": N * (2 * 2 * pxp * C + 2 * B * H * kz * C),
             "tcw_proj1": 2 * pxp * (C + P),
             "tcw_proj2": 2 * pxp * P + 4 * 2 * px * Cg,
@@ -451,7 +451,7 @@ def run_ours(args, wl):
         fl = step_flops(cls, kw, members, H, W)
         sb = step_bytes(cls, kw, members, H, W)
         spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel",
-                                                  "tcw_fwd_wdft", "wide_zimg_kernel")]
+                                                  "tcw_fwd_wdft", "tcw_fwd_hdft", "tcw_inv_hdft")]
         spec_ms = sum(entries[n][0] for n in spec_names)
         if tcw:   # the inverse W-DFT runs inside tcw_layer next to the skip conv: its share of that kernel's K extent
             m2c = fno_dims(kw, H, W)[7]
@@ -486,7 +486,7 @@ def run_ours(args, wl):
                                "flops_counted": ("H-DFT + mode mixing + inverse H-DFT (fp32 FMA in fno_mid_kernel); the W-DFT "
                                                  "GEMMs of the block run on tcgen05 inside fno_lift / fno_layer_kernel"
                                                  if fused_w else "whole spectral block (truncated-DFT-GEMM count)"
-                                                 + (": W-DFTs on tcgen05 in bf16, H-DFTs and mode mixing in fp32 FMA" if tcw else "")),
+                                                 + (": W- and H-DFT GEMMs on tcgen05 in bf16, mode mixing in fp32 FMA" if tcw else "")),
                                "note": "profiled pass; includes the events' launch gaps"},
             "kernel_ms_per_rollout": {n: round(v[0], 4) for n, v in sorted(entries.items(), key=lambda kv: -kv[1][0])},
             "clocks": clk.summary(),
