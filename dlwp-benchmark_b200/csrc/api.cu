@@ -124,7 +124,6 @@ int dlwp_plan_debug_read(const dlwp_plan* plan, const char* name, void* dst, siz
   const std::string n(name);
   const void* src = nullptr;
   if (n == "tcw_in") src = plan->tcw_in;
-  else if (n == "tcw_hid") src = plan->tcw_hid;
   else if (n == "tcw_x0") src = plan->tcw_x[0];
   else if (n == "tcw_x1") src = plan->tcw_x[1];
   else if (n == "tcw_z") src = plan->tcw_z;

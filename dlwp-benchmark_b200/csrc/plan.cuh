@@ -68,7 +68,7 @@ struct dlwp_plan {
   // bf16 tensor-core path at hidden width 128 (tc_wide.cuh): precision == DLWP_PREC_BF16
   bool tcw = false;
   int tcw_TW = 0, tcw_KZ = 0, tcw_HB = 0;               // tiles per grid row; K extent of the inverse W-DFT operands; blocks of 64 grid rows
-  uint8_t *tcw_in = nullptr, *tcw_hid = nullptr, *tcw_z = nullptr;
+  uint8_t *tcw_in = nullptr, *tcw_z = nullptr;
   uint8_t* tcw_x[2] = {nullptr, nullptr};               // activation tile images (ping-pong)
   uint8_t *tcw_G = nullptr, *tcw_F = nullptr;           // inverse / forward W-DFT tiles
   uint8_t *tcw_Gs = nullptr, *tcw_Fs = nullptr;         // inverse / forward H-DFT tiles ((re | im)-stacked)

@@ -394,6 +394,238 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
   if (warp == kWIssuer) tmem_dealloc(tmem, 512);
 }
 
+// ---- fused pointwise MLP: out = W2 gelu(W1 x + b1) + b2 with the 256-wide hidden kept on chip ------
+//   KIND 0 (lifting):    x = [128 x 32] input images,       out = [128 x 128] activation images
+//   KIND 1 (projection): x = [128 x 128] activation images, out = NCHW fp32 frame (+ residual frame)
+// Roles: warps 0-7 first epilogue (accumulator 1 -> 2 gelu -> bf16 hidden tile in shared memory, handed
+// to the issuer in four 64-column chunks so that the second GEMM runs under the GELU of the later
+// chunks), warps 8-11 second epilogue (accumulator 2 -> output), warp 12 loader, warp 13 issuer.
+// Accumulator 2 lives in the first columns of accumulator 1's buffer: those columns have been read
+// by the time the chunks that cover them were handed over.  Two buffers, so that the first GEMM of
+// the next tile runs while this tile is in the epilogues.
+constexpr int kMlpCta = 14 * 32;
+constexpr int kMlpLoader = 12, kMlpIssuer = 13;
+constexpr int kMlpEpi2 = 128;
+
+template <int KIND> struct MT;
+template <> struct MT<0> {
+  static constexpr int K1 = 32, N2 = 128, NS = 4, W1B = 256 * 32 * 2, B1B = 0, W2B = 128 * 256 * 2, B2B = 128 * 32, OUT = kXTile;
+};
+template <> struct MT<1> {
+  static constexpr int K1 = 128, N2 = 16, NS = 2, W1B = 256 * 128 * 2, B1B = 256 * 32, W2B = 16 * 256 * 2, B2B = 16 * 32, OUT = 0;
+};
+template <int KIND>
+constexpr int mlp_smem_bytes() {
+  using T = MT<KIND>;
+  return T::W1B + T::B1B + T::W2B + T::B2B + kOnes + T::NS * 128 * T::K1 * 2 + kHidTile + T::OUT;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kMlpCta, 1) tcw_mlp_kernel(const TcwArgs a) {
+  using T = MT<KIND>;
+  constexpr int kStage = 128 * T::K1 * 2;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bars[2 * kMaxStages + 2 + 2 + 4 + 4 + 2 + 1];
+  __shared__ uint32_t tmem_slot;
+  pdl_launch_dependents();
+  uint64_t* full = bars;
+  uint64_t* empty = full + kMaxStages;
+  uint64_t* d1_full = empty + kMaxStages;
+  uint64_t* acc_empty = d1_full + 2;
+  uint64_t* h_full = acc_empty + 2;
+  uint64_t* h_empty = h_full + 4;
+  uint64_t* d2_full = h_empty + 4;
+  uint64_t* res_bar = d2_full + 2;
+
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  uint8_t* sW1 = smem;
+  uint8_t* sB1 = sW1 + T::W1B;
+  uint8_t* sW2 = sB1 + T::B1B;
+  uint8_t* sB2 = sW2 + T::W2B;
+  uint8_t* sOnes = sB2 + T::B2B;
+  uint8_t* sStage = sOnes + kOnes;
+  uint8_t* sH = sStage + T::NS * kStage;
+  uint8_t* sOut = sH + kHidTile;
+
+  if (tid == 0) {
+    for (int s = 0; s < T::NS; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&d1_full[i], 1);
+      mbar_init(&acc_empty[i], kMlpEpi2);
+      mbar_init(&d2_full[i], 1);
+    }
+    for (int q = 0; q < 4; ++q) {
+      mbar_init(&h_full[q], kWEpi);
+      mbar_init(&h_empty[q], 1);
+    }
+    mbar_init(res_bar, 1);
+    fence_mbar_init();
+  }
+  if (tid < 128) {
+    *reinterpret_cast<uint4*>(sOnes + tid * 16) = make_uint4(0x3F803F80u, 0u, 0u, 0u);
+    *reinterpret_cast<uint4*>(sOnes + 2048 + tid * 16) = make_uint4(0u, 0u, 0u, 0u);
+    fence_async_smem();
+  }
+  if (warp == kMlpIssuer) {
+    tmem_alloc(&tmem_slot, 512);
+    tmem_relinquish();
+    tc_fence_before();
+  }
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp == kMlpLoader) {
+    const uint32_t leader = elect_one();
+    mbar_arrive_expect_tx_p(leader, res_bar, (uint32_t)(T::W1B + T::B1B + T::W2B + T::B2B));
+    bulk_g2s_p(leader, sW1, a.b_res, T::W1B, res_bar);
+    if (T::B1B) bulk_g2s_p(leader, sB1, a.bias_img, T::B1B, res_bar);
+    bulk_g2s_p(leader, sW2, a.w2_img, T::W2B, res_bar);
+    bulk_g2s_p(leader, sB2, a.bias2_img, T::B2B, res_bar);
+    pdl_wait();
+    uint32_t u = 0;
+    for (int item = blockIdx.x; item < a.nitems; item += gridDim.x, ++u) {
+      const uint32_t s = u % T::NS;
+      mbar_wait(&empty[s], ((u / T::NS) & 1u) ^ 1u);
+      mbar_arrive_expect_tx_p(leader, &full[s], (uint32_t)kStage);
+      bulk_g2s_p(leader, sStage + s * kStage, a.a_img + (size_t)item * kStage, kStage, &full[s]);
+      __syncwarp();
+    }
+  } else if (warp == kMlpIssuer) {
+    const uint32_t leader = elect_one();
+    pdl_wait();
+    mbar_wait(res_bar, 0);
+    const uint32_t idesc1 = idesc_bf16(128, 256), idesc2 = idesc_bf16(128, T::N2);
+    const uint64_t dW1 = chunk_desc(smem_u32(sW1), 256, 0), dW2 = chunk_desc(smem_u32(sW2), T::N2, 0);
+    const uint64_t dH = chunk_desc(smem_u32(sH), 128, 0), dOnes = chunk_desc(smem_u32(sOnes), 128, 0);
+    const uint32_t w2step = 2u * T::N2 * 16u;
+    const int n_mine = a.nitems > (int)blockIdx.x ? (a.nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    // first GEMM of tile `it` (K1 / 16 MMAs of N = 256, + bias)
+    auto gemm1 = [&](uint32_t it) {
+      const uint32_t acc = it & 1u, s = it % T::NS;
+      mbar_wait(&acc_empty[acc], ((it >> 1) & 1u) ^ 1u);
+      mbar_wait(&full[s], (it / T::NS) & 1u);
+      tc_fence_after();
+      const uint64_t dA = chunk_desc(smem_u32(sStage + s * kStage), 128, 0);
+      const uint32_t d = tmem + acc * 256u;
+#pragma unroll
+      for (int j = 0; j < T::K1 / 16; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dW1, j * 8192), idesc1, j != 0);
+      if (T::B1B) umma_bf16_p(leader, d, dOnes, chunk_desc(smem_u32(sB1), 256, 0), idesc1, 1u);
+      umma_commit_p(leader, &empty[s]);
+      umma_commit_p(leader, &d1_full[acc]);
+    };
+    if (n_mine > 0) gemm1(0);
+    for (uint32_t it = 0; it < (uint32_t)n_mine; ++it) {
+      if (it + 1 < (uint32_t)n_mine) gemm1(it + 1);
+      // second GEMM of tile `it`, chunk by chunk as the hidden tile arrives; its accumulator covers
+      // columns [0, N2) of this tile's first accumulator, which chunks 0 .. ceil(N2 / 64) - 1 have drained
+      const uint32_t d = tmem + (it & 1u) * 256u, par = it & 1u;
+      constexpr int kFirst = T::N2 > 64 ? 2 : 1;
+#pragma unroll
+      for (int q = 0; q < kFirst; ++q) mbar_wait(&h_full[q], par);
+      tc_fence_after();
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (q >= kFirst) {
+          mbar_wait(&h_full[q], par);
+          tc_fence_after();
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          umma_bf16_p(leader, d, desc_off(dH, (q * 4 + j) * 4096), desc_off(dW2, (q * 4 + j) * w2step), idesc2, (q | j) != 0);
+        if (q == 3) umma_bf16_p(leader, d, dOnes, chunk_desc(smem_u32(sB2), T::N2, 0), idesc2, 1u);
+        umma_commit_p(leader, &h_empty[q]);
+      }
+      umma_commit_p(leader, &d2_full[it & 1u]);
+      __syncwarp();
+    }
+  } else if (warp < 8) {
+    // ---- first epilogue: 2 gelu(accumulator 1) -> hidden tile, 64 columns per hand-over ----
+    pdl_wait();
+    const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane;
+    const uint32_t trow = tmem + ((uint32_t)(q4 * 32) << 16);
+    uint32_t it = 0;
+    for (int item = blockIdx.x; item < a.nitems; item += gridDim.x, ++it) {
+      const uint32_t d = trow + (it & 1u) * 256u;
+      mbar_wait(&d1_full[it & 1u], (it >> 1) & 1u);
+      tc_fence_after();
+#pragma unroll 1
+      for (int q = 0; q < 4; ++q) {
+        mbar_wait(&h_empty[q], (it & 1u) ^ 1u);   // the second GEMM of the previous tile has read this chunk
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int c0 = q * 64 + i * 32 + half * 16;
+          uint32_t r[16];
+          tmem_ld16(d + (uint32_t)c0, r);
+          tmem_ld_wait();
+          cols16_to_image<true>(r, sH, row, c0);
+        }
+        tc_fence_before();
+        fence_async_smem();
+        mbar_arrive(&h_full[q]);
+      }
+    }
+  } else {
+    // ---- second epilogue (warps 8-11): accumulator 2 -> output ----
+    pdl_wait();
+    const int q4 = warp & 3, row = q4 * 32 + lane, t2 = tid - 256;
+    const uint32_t trow = tmem + ((uint32_t)(q4 * 32) << 16);
+    uint32_t it = 0;
+    for (int item = blockIdx.x; item < a.nitems; item += gridDim.x, ++it) {
+      const uint32_t acc = it & 1u, d = trow + acc * 256u;
+      if (KIND == 0) {
+        if (t2 == 0) bulk_wait_read0();
+        bar_sync(3, kMlpEpi2);
+        mbar_wait(&d2_full[acc], (it >> 1) & 1u);
+        tc_fence_after();
+#pragma unroll 1
+        for (int i = 0; i < 8; ++i) {
+          uint32_t r[16];
+          tmem_ld16(d + (uint32_t)(i * 16), r);
+          tmem_ld_wait();
+          cols16_to_image<false>(r, sOut, row, i * 16);
+        }
+        tc_fence_before();
+        mbar_arrive(&acc_empty[acc]);
+        fence_async_smem();
+        bar_sync(4, kMlpEpi2);
+        if (t2 == 0) {
+          bulk_s2g(a.out_img + (size_t)item * kXTile, sOut, kXTile);
+          bulk_commit();
+        }
+      } else {
+        const int w = (item % a.TW) * 128 + row, rid = item / a.TW;
+        const int b = rid / a.H, h = rid - b * a.H;
+        const bool pvalid = w < a.W;
+        const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
+        float lastv[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          lastv[j] = (pvalid && a.last && j < a.Cg) ? a.last[(size_t)b * a.last_bstride + j * plane + px] : 0.f;
+        mbar_wait(&d2_full[acc], (it >> 1) & 1u);
+        tc_fence_after();
+        uint32_t r[16];
+        tmem_ld16(d, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(&acc_empty[acc]);
+        if (pvalid) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (j < a.Cg) a.out[(size_t)b * a.out_bstride + j * plane + px] = __uint_as_float(r[j]) + lastv[j];
+        }
+      }
+    }
+    if (KIND == 0 && t2 == 0) bulk_wait0();
+  }
+  __syncthreads();
+  if (warp == kMlpIssuer) tmem_dealloc(tmem, 512);
+}
+
 // ---- layout kernels ---------------------------------------------------------------------------
 // x_t from the NCHW sources -> [128 slots x 32] bf16 input images: columns 0..Cin-1 hi parts,
 // columns Cin and 15 ones (they meet the hi and lo parts of the first bias in the weight image),
@@ -470,6 +702,35 @@ int launch_tcw(int mode, const TcwArgs& a, cudaStream_t st) {
     case TCW_PROJ2: return launch_tcw_mode<TCW_PROJ2>(a, st, "tcw_proj2");
   }
   return fail(DLWP_ERR_INVALID, "tcw: unknown mode %d", mode);
+}
+
+template <int KIND>
+static int launch_tcw_mlp_kind(const TcwArgs& a, cudaStream_t st, const char* name) {
+  static int sms = 0;
+  static bool attr_set = false;
+  if (!sms) {
+    int dev = 0;
+    DLWP_CUDA(cudaGetDevice(&dev));
+    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  constexpr int smem = mlp_smem_bytes<KIND>();
+  static_assert(smem <= 226 * 1024, "fused MLP kernel: shared memory");
+  if (!attr_set) {
+    DLWP_CUDA(cudaFuncSetAttribute(tcw_mlp_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  const int grid = a.nitems < sms ? a.nitems : sms;
+  void (*kern)(TcwArgs) = tcw_mlp_kernel<KIND>;
+  DLWP_CUDA(launch_pdl(kern, dim3((unsigned)grid), dim3(kMlpCta), (size_t)smem, st, a));
+  DLWP_LAUNCHED(name);
+  return DLWP_OK;
+}
+
+int launch_tcw_mlp(int kind, const TcwArgs& a, cudaStream_t st) {
+  DLWP_REQUIRE(a.nitems > 0 && a.TW > 0 && a.H > 0 && a.W > 0 && a.w2_img && a.bias2_img, "tcw_mlp: incomplete arguments");
+  if (kind == 0) return launch_tcw_mlp_kind<0>(a, st, "tcw_lift");
+  if (kind == 1) return launch_tcw_mlp_kind<1>(a, st, "tcw_proj");
+  return fail(DLWP_ERR_INVALID, "tcw_mlp: unknown kind %d", kind);
 }
 
 int launch_wide_gather(const WideGatherArgs& a, cudaStream_t st) {

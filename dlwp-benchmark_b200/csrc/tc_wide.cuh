@@ -44,6 +44,8 @@ struct TcwArgs {
   const uint8_t* a_img;   // streamed tile images: input [128 x 32] / hidden [128 x 256] / activation [128 x 128]
   const uint8_t* b_res;   // resident weight image [N rows x K]
   const uint8_t* bias_img;// [N rows x 16]: columns 0 / 1 = hi / lo of the bias (times a ones operand), or null
+  const uint8_t* w2_img;  // fused MLP kernels: second weight image [N2 rows x 256] and its bias image
+  const uint8_t* bias2_img;
   const uint8_t* g_img;   // TCW_LAYER: TW inverse W-DFT tiles [128 x KZ]; DFT modes: the [128 x 128] DFT tiles
   const uint8_t* z_img;   // TCW_LAYER: per grid row [KZ x 128 channels] (MN-major)
   uint8_t* out_img;       // tile images out (TCW_FWD: spectrum images; TCW_HINV: Z images)
@@ -57,6 +59,9 @@ struct TcwArgs {
   int Cg;
 };
 int launch_tcw(int mode, const TcwArgs& a, cudaStream_t st);
+// fused pointwise MLP with the 256-wide hidden on chip: kind 0 = lifting (input images -> activation
+// images), kind 1 = projection (activation images -> NCHW frame + residual)
+int launch_tcw_mlp(int kind, const TcwArgs& a, cudaStream_t st);
 
 struct WideGatherArgs {
   SrcGroup grp[4];

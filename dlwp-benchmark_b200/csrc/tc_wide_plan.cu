@@ -102,7 +102,6 @@ int plan_tcw_build(dlwp_plan* p) {
 
   const size_t nt = (size_t)d.max_batch * H * TW;
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_in, nt * 128 * 32 * 2));
-  DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_hid, nt * 128 * kWideHid * 2));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_x[0], nt * 128 * kWideC * 2));
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_x[1], nt * 128 * kWideC * 2));
   // per grid row [KZ rows (kx, re | im)] x [128 channels]; the rows past 2 Kc stay zero from here on
@@ -229,11 +228,8 @@ int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   DLWP_TRY(launch_wide_gather(ga, st));
 
   TcwArgs a = base;
-  a.a_img = p->tcw_in; a.b_res = p->tcw_W1; a.out_img = p->tcw_hid;
-  DLWP_TRY(launch_tcw(TCW_LIFT1, a, st));
-  a = base;
-  a.a_img = p->tcw_hid; a.b_res = p->tcw_W2; a.bias_img = p->tcw_b2; a.out_img = p->tcw_x[0];
-  DLWP_TRY(launch_tcw(TCW_LIFT2, a, st));
+  a.a_img = p->tcw_in; a.b_res = p->tcw_W1; a.w2_img = p->tcw_W2; a.bias2_img = p->tcw_b2; a.out_img = p->tcw_x[0];
+  DLWP_TRY(launch_tcw_mlp(0, a, st));
 
   int cur = 0;
   for (int l = 0; l < N; ++l) {
@@ -260,13 +256,10 @@ int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   }
 
   a = base;
-  a.a_img = p->tcw_x[cur]; a.b_res = p->tcw_P1; a.bias_img = p->tcw_pb1; a.out_img = p->tcw_hid;
-  DLWP_TRY(launch_tcw(TCW_PROJ1, a, st));
-  a = base;
-  a.a_img = p->tcw_hid; a.b_res = p->tcw_P2; a.bias_img = p->tcw_pb2;
+  a.a_img = p->tcw_x[cur]; a.b_res = p->tcw_P1; a.bias_img = p->tcw_pb1; a.w2_img = p->tcw_P2; a.bias2_img = p->tcw_pb2;
   a.out = io.out; a.out_bstride = io.out_bstride; a.last = io.last; a.last_bstride = io.last_bstride;
   a.Cg = d.prognostic_channels;
-  DLWP_TRY(launch_tcw(TCW_PROJ2, a, st));
+  DLWP_TRY(launch_tcw_mlp(1, a, st));
   return DLWP_OK;
 }
 

@@ -102,7 +102,7 @@ int dlwp_plan_workspace_bytes(const dlwp_plan* plan, size_t* bytes);
  * it covers), 0 when it runs the fp32 FMA kernel set. */
 int dlwp_plan_uses_tensor_cores(const dlwp_plan* plan, int* out);
 /* Diagnostics: copy the first `max_bytes` bytes of a named internal workspace buffer ("specA", "specZ",
- * "tcw_in", "tcw_hid", "tcw_x0", "tcw_x1", "tcw_z", "tc_img0", "tc_img1") to the device buffer `dst`.
+ * "specX", "tcw_in", "tcw_x0", "tcw_x1", "tcw_sa", "tcw_ys", "tcw_z", "tc_img0", "tc_img1") to the device buffer `dst`.
  * The caller must know the buffer's size; used by the stage-by-stage tests.  No reference counterpart. */
 int dlwp_plan_debug_read(const dlwp_plan* plan, const char* name, void* dst, size_t max_bytes, void* stream);
 

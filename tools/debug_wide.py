@@ -74,7 +74,5 @@ with torch.no_grad():
     y_spec = fno.fno_blocks.convs(x0, 0)
     x1 = y_spec + fno.fno_blocks.fno_skips[0](x0)
     print("layer (x1):", rel(to_grid(image("tcw_x1", 128)), x1), " [spectral part scale", float(y_spec.abs().max()), "]")
-    hid = F.gelu(fno.projection.fcs[0](x1))
-    print("proj hidden (2*gelu):", rel(to_grid(image("tcw_hid", 256)), 2 * hid))
     incr = (want[:, 0] - prog[:, 0]).abs().max()
     print("output:", float((got[:, 0] - want[:, 0]).abs().max() / incr), "of increment", float(incr))
