@@ -47,8 +47,8 @@ WORKLOADS = {
     "c2": ("TFNO2DModule", TFNO_C2, 32, 64, 20, 8, "BASELINE configs[1]: TFNO2D 32x64, batch 8, 20 lead steps"),
     "c1": ("FNO2DModule", FNO_C1, 64, 64, 50, 8, "BASELINE configs[0]: FNO2D 64x64, batch 8, 50 lead steps"),
     "c3": ("FourCastNet", AFNO_C3, 32, 64, 5, 8, "BASELINE configs[2]: FourCastNet AFNO 32x64, batch 8, 5 lead steps"),
-    "c5": ("FNO2DModule", FNO_C5, 721, 1440, 8, 1,
-           "BASELINE configs[4]: FNO2D 721x1440, 128 channels, 64x64 modes, 8 lead steps"),
+    "c5": ("FNO2DModule", FNO_C5, 721, 1440, 8, 2,
+           "BASELINE configs[4]: FNO2D 721x1440, 128 channels, 64x64 modes, 8 lead steps, 2 samples per GPU"),
 }
 
 
@@ -207,15 +207,13 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
         kz = (2 * m2 + 15) // 16 * 16
         table = {
             "wide_gather_kernel": 4 * px * cin + 2 * pxp * 32,
-            "tcw_lift1": 2 * pxp * (32 + L),
-            "tcw_lift2": 2 * pxp * (L + C),
+            "tcw_lift": 2 * pxp * (32 + C),
             "tcw_fwd_wdft": N * (2 * pxp * C + 2 * B * m2 * ((H + 63) // 64) * 128 * C),
             "tcw_fwd_hdft": N * (2 * B * m2 * ((H + 63) // 64) * 128 * C + 4 * modes),
             "mix_dense_kernel": N * (4 * modes + 2 * B * m2 * 128 * C + 4 * m1 * m2 * C * C * 2),
             "tcw_inv_hdft": N * (2 * B * m2 * 128 * C + 2 * B * H * kz * C),
             "tcw_layer": N * (2 * 2 * pxp * C + 2 * B * H * kz * C),
-            "tcw_proj1": 2 * pxp * (C + P),
-            "tcw_proj2": 2 * pxp * P + 4 * 2 * px * Cg,
+            "tcw_proj": 2 * pxp * C + 4 * 2 * px * Cg,
         }
         return table.get(name)
     if name == "pw_linear_kernel":      # lifting 1+2, N skips, projection 1+2 (unfused fp32 path)

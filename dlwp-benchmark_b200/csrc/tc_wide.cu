@@ -1,8 +1,9 @@
 // tcgen05 kernels of the FNO step at hidden width 128 in bf16 (see tc_wide.cuh).
 //
-// One persistent, warp-specialised kernel body, instantiated per GEMM of the step:
+// tcw_kernel: one persistent, warp-specialised kernel body, instantiated for the DFT GEMMs and the
+// layer GEMM of the step (the fused lifting / projection MLPs are tcw_mlp_kernel below):
 //   warps 0-7 : epilogue group (TMEM -> registers -> GELU / convert -> shared-memory tile image
-//               -> one bulk store; or straight to HBM for the spectrum and the NCHW output)
+//               -> one bulk store; or 16-byte chunk rows straight into the next GEMM's operand images)
 //   warp 8    : loader  -- bulk async copies of the streamed operands into a ring of stages
 //   warp 9    : issuer  -- tcgen05.mma into one of two TMEM accumulators (256 columns each)
 // The three sides meet only on mbarriers (full / empty per stage, acc_full / acc_empty per
@@ -32,20 +33,11 @@ constexpr int kWIssuer = kWLoader + 1;     // warp 9
 constexpr int kWCta = kWEpi + 64;          // 320
 constexpr int kXTile = 128 * kWideC * 2;   // [128 x 128] bf16 image: 32 KB
 constexpr int kHidTile = 128 * kWideHid * 2;   // [128 x 256]: 64 KB
-constexpr int kInTile = 128 * 32 * 2;      // [128 x 32]: 8 KB
 constexpr int kOnes = 128 * 16 * 2;        // ones operand [128 x 16]
 constexpr int kMaxStages = 4;
 
 // per-GEMM constants
 template <int MODE> struct WT;
-template <> struct WT<TCW_LIFT1> {
-  static constexpr int N = 256, NS = 4, RES = 256 * 32 * 2, BIAS = 0, OUT = kHidTile, NOUT = 2;
-  __host__ __device__ static int stage(int) { return kInTile; }
-};
-template <> struct WT<TCW_LIFT2> {
-  static constexpr int N = 128, NS = 3, RES = 128 * 256 * 2, BIAS = 128 * 32, OUT = kXTile, NOUT = 1;
-  __host__ __device__ static int stage(int) { return kXTile; }   // one K half of a hidden tile
-};
 template <> struct WT<TCW_FWD> {
   static constexpr int N = 128, NS = 3, RES = 0, BIAS = 0, OUT = 0, NOUT = 1;
   __host__ __device__ static int stage(int) { return 2 * kXTile; }   // forward DFT tile + activation tile
@@ -56,15 +48,6 @@ template <> struct WT<TCW_LAYER> {
   static constexpr int N = 128, NS = 2, RES = 128 * 128 * 2, BIAS = 128 * 32, OUT = kXTile, NOUT = 1;
   __host__ __device__ static int stage(int KZ) { return kXTile + 2 * KZ * 256; }   // x, G tile, Z row image
 };
-template <> struct WT<TCW_PROJ1> {
-  static constexpr int N = 256, NS = 2, RES = 256 * 128 * 2, BIAS = 256 * 32, OUT = kHidTile, NOUT = 1;
-  __host__ __device__ static int stage(int) { return kXTile; }
-};
-template <> struct WT<TCW_PROJ2> {
-  static constexpr int N = 16, NS = 4, RES = 16 * 256 * 2, BIAS = 16 * 32, OUT = 0, NOUT = 1;
-  __host__ __device__ static int stage(int) { return kXTile; }   // one K half of a hidden tile
-};
-
 template <int MODE>
 __host__ __device__ inline int tcw_smem_bytes(int KZ) {
   using T = WT<MODE>;
@@ -118,7 +101,7 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int stage_bytes = T::stage(a.KZ);
-  const int nblk = (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) ? 2 : (MODE == TCW_FWD ? a.TW : (MODE == TCW_HFWD ? a.HB : 1));
+  const int nblk = MODE == TCW_FWD ? a.TW : (MODE == TCW_HFWD ? a.HB : 1);
   uint8_t* sRes = smem;
   uint8_t* sBias = sRes + T::RES;
   uint8_t* sOnes = sBias + T::BIAS;
@@ -167,23 +150,17 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
         uint8_t* st = sStage + s * stage_bytes;
         mbar_wait(&empty[s], ((u / T::NS) & 1u) ^ 1u);
         mbar_arrive_expect_tx_p(leader, &full[s], (uint32_t)stage_bytes);
-        if (MODE == TCW_LIFT1) {
-          bulk_g2s_p(leader, st, a.a_img + (size_t)item * kInTile, kInTile, &full[s]);
-        } else if (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) {
-          bulk_g2s_p(leader, st, a.a_img + (size_t)item * kHidTile + (size_t)blk * kXTile, kXTile, &full[s]);
-        } else if (kDft) {
+        if (kDft) {
           // DFT tile: one per tile of the grid row / per block of 64 grid rows; image: this item's block
           const size_t gi = MODE == TCW_HINV ? (size_t)(item % a.HB) : (size_t)blk;
           const size_t ai = MODE == TCW_HINV ? (size_t)(item / a.HB) : (size_t)item * nblk + blk;
           bulk_g2s_p(leader, st, a.g_img + gi * kXTile, kXTile, &full[s]);
           bulk_g2s_p(leader, st + kXTile, a.a_img + ai * kXTile, kXTile, &full[s]);
-        } else if (MODE == TCW_LAYER) {
+        } else {   // TCW_LAYER
           const uint32_t zb = (uint32_t)a.KZ * 256u;
           bulk_g2s_p(leader, st, a.a_img + (size_t)item * kXTile, kXTile, &full[s]);
           bulk_g2s_p(leader, st + kXTile, a.g_img + (size_t)(item % a.TW) * zb, zb, &full[s]);
           bulk_g2s_p(leader, st + kXTile + zb, a.z_img + (size_t)(item / a.TW) * zb, zb, &full[s]);
-        } else {   // TCW_PROJ1
-          bulk_g2s_p(leader, st, a.a_img + (size_t)item * kXTile, kXTile, &full[s]);
         }
         __syncwarp();
       }
@@ -208,22 +185,14 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
         mbar_wait(&full[s], (u / T::NS) & 1u);
         tc_fence_after();
         const uint64_t dA = chunk_desc(st, 128, 0);
-        if (MODE == TCW_LIFT1) {
-#pragma unroll
-          for (int j = 0; j < 2; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
-        } else if (MODE == TCW_LIFT2 || MODE == TCW_PROJ2) {
-          const uint64_t dB = desc_off(dRes, (uint32_t)blk * 8u * bstep);   // K half of the resident weights
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dB, j * bstep), idesc, (blk | j) != 0);
-        } else if (kDft) {
+        if (kDft) {
           // B: the activation image read in place as an MN-major operand (pixels = K, 8 x 8 core
           // matrices 128 B apart along pixels, 2048 B along channels)
           const uint64_t dX = smem_desc(st + kXTile, 128, 2048);
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dX, j * 256), idesc, (blk | j) != 0);
-        } else if (MODE == TCW_LAYER) {
+        } else {   // TCW_LAYER: skip conv, then the inverse W-DFT, into one accumulator
 #pragma unroll
           for (int j = 0; j < 8; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
           const uint32_t zb = (uint32_t)a.KZ * 256u;
@@ -232,9 +201,6 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
           const uint64_t dG = chunk_desc(st + kXTile, 128, 0), dZ = smem_desc(st + kXTile + zb, 128, (uint32_t)a.KZ * 16u);
           for (int j = 0; j < (a.KZ >> 4); ++j)
             umma_bf16_p(leader, d, desc_off(dG, j * 4096), desc_off(dZ, j * 256), idesc | kIdescBMnMajor, 1u);
-        } else {   // TCW_PROJ1
-#pragma unroll
-          for (int j = 0; j < 8; ++j) umma_bf16_p(leader, d, desc_off(dA, j * 4096), desc_off(dRes, j * bstep), idesc, j != 0);
         }
         umma_commit_p(leader, &empty[s]);
       }
@@ -261,26 +227,10 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
         }
         bar_sync(1, kWEpi);
       }
-      // TCW_PROJ2: fetch the residual frame before waiting for the accumulator, so that its latency is
-      // not part of the accumulator's round trip
-      float lastv[8];
-      size_t oidx = 0;
-      bool pvalid = false;
-      if (MODE == TCW_PROJ2) {
-        const int w = (item % a.TW) * 128 + row, rid = item / a.TW;
-        const int b = rid / a.H, h = rid - b * a.H;
-        pvalid = w < a.W && half * 8 < a.Cg;
-        const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
-        oidx = (size_t)b * a.out_bstride + (size_t)(half * 8) * plane + px;
-        const size_t lidx = (size_t)b * a.last_bstride + (size_t)(half * 8) * plane + px;
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          lastv[j] = (pvalid && a.last && half * 8 + j < a.Cg) ? a.last[lidx + j * plane] : 0.f;
-      }
       mbar_wait(&acc_full[acc], (it >> 1) & 1u);
       tc_fence_after();
-      if (MODE == TCW_LIFT1 || MODE == TCW_LIFT2 || MODE == TCW_LAYER || MODE == TCW_PROJ1) {
-        const bool gelu = MODE == TCW_LIFT1 || MODE == TCW_PROJ1 || (MODE == TCW_LAYER && a.gelu);
+      if (MODE == TCW_LAYER) {
+        const bool gelu = a.gelu != 0;
 #pragma unroll 1
         for (int i = 0; i < T::N / 32; ++i) {
           const int c0 = i * 32 + half * 16;
@@ -372,20 +322,6 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
         }
         tc_fence_before();
         mbar_arrive(&acc_empty[acc]);
-      } else {   // TCW_PROJ2: accumulator columns = output channels, rows = pixel slots
-        uint32_t r[8];
-        if (half * 8 < a.Cg) {
-          tmem_ld8(d + (uint32_t)(half * 8), r);
-          tmem_ld_wait();
-        }
-        tc_fence_before();
-        mbar_arrive(&acc_empty[acc]);
-        if (pvalid) {
-          const size_t plane = (size_t)a.H * a.W;
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (half * 8 + j < a.Cg) a.out[oidx + j * plane] = __uint_as_float(r[j]) + lastv[j];
-        }
       }
     }
     if (T::OUT && tid == 0) bulk_wait0();
@@ -397,15 +333,17 @@ __global__ void __launch_bounds__(kWCta, 1) tcw_kernel(const TcwArgs a) {
 // ---- fused pointwise MLP: out = W2 gelu(W1 x + b1) + b2 with the 256-wide hidden kept on chip ------
 //   KIND 0 (lifting):    x = [128 x 32] input images,       out = [128 x 128] activation images
 //   KIND 1 (projection): x = [128 x 128] activation images, out = NCHW fp32 frame (+ residual frame)
-// Roles: warps 0-7 first epilogue (accumulator 1 -> 2 gelu -> bf16 hidden tile in shared memory, handed
+// Roles: warps 0-15 first epilogue (accumulator 1 -> 2 gelu -> bf16 hidden tile in shared memory, handed
 // to the issuer in four 64-column chunks so that the second GEMM runs under the GELU of the later
-// chunks), warps 8-11 second epilogue (accumulator 2 -> output), warp 12 loader, warp 13 issuer.
+// chunks), warps 16-19 second epilogue (accumulator 2 -> output), warp 20 loader, warp 21 issuer.
 // Accumulator 2 lives in the first columns of accumulator 1's buffer: those columns have been read
 // by the time the chunks that cover them were handed over.  Two buffers, so that the first GEMM of
 // the next tile runs while this tile is in the epilogues.
-constexpr int kMlpCta = 14 * 32;
-constexpr int kMlpLoader = 12, kMlpIssuer = 13;
+constexpr int kMlpEpi1Warps = 16;                       // four warps per TMEM lane quarter, 16 of every 64 columns each
+constexpr int kMlpEpi1 = kMlpEpi1Warps * 32;
 constexpr int kMlpEpi2 = 128;
+constexpr int kMlpLoader = kMlpEpi1Warps + 4, kMlpIssuer = kMlpLoader + 1;
+constexpr int kMlpCta = (kMlpIssuer + 1) * 32;
 
 template <int KIND> struct MT;
 template <> struct MT<0> {
@@ -459,7 +397,7 @@ __global__ void __launch_bounds__(kMlpCta, 1) tcw_mlp_kernel(const TcwArgs a) {
       mbar_init(&d2_full[i], 1);
     }
     for (int q = 0; q < 4; ++q) {
-      mbar_init(&h_full[q], kWEpi);
+      mbar_init(&h_full[q], kMlpEpi1);
       mbar_init(&h_empty[q], 1);
     }
     mbar_init(res_bar, 1);
@@ -543,36 +481,33 @@ __global__ void __launch_bounds__(kMlpCta, 1) tcw_mlp_kernel(const TcwArgs a) {
       umma_commit_p(leader, &d2_full[it & 1u]);
       __syncwarp();
     }
-  } else if (warp < 8) {
+  } else if (warp < kMlpEpi1Warps) {
     // ---- first epilogue: 2 gelu(accumulator 1) -> hidden tile, 64 columns per hand-over ----
     pdl_wait();
-    const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane;
+    const int q4 = warp & 3, part = warp >> 2, row = q4 * 32 + lane;
     const uint32_t trow = tmem + ((uint32_t)(q4 * 32) << 16);
     uint32_t it = 0;
     for (int item = blockIdx.x; item < a.nitems; item += gridDim.x, ++it) {
       const uint32_t d = trow + (it & 1u) * 256u;
       mbar_wait(&d1_full[it & 1u], (it >> 1) & 1u);
       tc_fence_after();
-#pragma unroll 1
-      for (int q = 0; q < 4; ++q) {
-        mbar_wait(&h_empty[q], (it & 1u) ^ 1u);   // the second GEMM of the previous tile has read this chunk
+      uint32_t r[2][16];
+      tmem_ld16(d + (uint32_t)(part * 16), r[0]);
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int c0 = q * 64 + i * 32 + half * 16;
-          uint32_t r[16];
-          tmem_ld16(d + (uint32_t)c0, r);
-          tmem_ld_wait();
-          cols16_to_image<true>(r, sH, row, c0);
-        }
+      for (int q = 0; q < 4; ++q) {
+        tmem_ld_wait();
+        if (q < 3) tmem_ld16(d + (uint32_t)((q + 1) * 64 + part * 16), r[(q + 1) & 1]);   // next chunk's columns, under this chunk's GELU
+        mbar_wait(&h_empty[q], (it & 1u) ^ 1u);   // the second GEMM of the previous tile has read this chunk
+        cols16_to_image<true>(r[q & 1], sH, row, q * 64 + part * 16);
         tc_fence_before();
         fence_async_smem();
         mbar_arrive(&h_full[q]);
       }
     }
   } else {
-    // ---- second epilogue (warps 8-11): accumulator 2 -> output ----
+    // ---- second epilogue: accumulator 2 -> output ----
     pdl_wait();
-    const int q4 = warp & 3, row = q4 * 32 + lane, t2 = tid - 256;
+    const int q4 = warp & 3, row = q4 * 32 + lane, t2 = tid - kMlpEpi1;
     const uint32_t trow = tmem + ((uint32_t)(q4 * 32) << 16);
     uint32_t it = 0;
     for (int item = blockIdx.x; item < a.nitems; item += gridDim.x, ++it) {
@@ -658,7 +593,7 @@ __global__ void __launch_bounds__(128) wide_gather_kernel(const WideGatherArgs a
     v[i] = *reinterpret_cast<const uint32_t*>(&hi);
     v[8 + i] = *reinterpret_cast<const uint32_t*>(&lo);
   }
-  uint8_t* img = a.in_img + (size_t)tile * kInTile + s * 16;
+  uint8_t* img = a.in_img + (size_t)tile * 8192 + s * 16;   // [128 x 32] bf16 image
 #pragma unroll
   for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(img + j * 2048) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
 }
@@ -692,14 +627,10 @@ int launch_tcw(int mode, const TcwArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.nitems > 0 && a.TW > 0 && a.H > 0 && a.W > 0, "tcw: empty problem");
   DLWP_REQUIRE(a.KZ % 16 == 0 && a.KZ >= 16 && a.KZ <= 96 && 2 * a.Kc <= a.KZ, "tcw: %d retained columns do not fit", a.Kc);
   switch (mode) {
-    case TCW_LIFT1: return launch_tcw_mode<TCW_LIFT1>(a, st, "tcw_lift1");
-    case TCW_LIFT2: return launch_tcw_mode<TCW_LIFT2>(a, st, "tcw_lift2");
     case TCW_FWD: return launch_tcw_mode<TCW_FWD>(a, st, "tcw_fwd_wdft");
     case TCW_HFWD: return launch_tcw_mode<TCW_HFWD>(a, st, "tcw_fwd_hdft");
     case TCW_HINV: return launch_tcw_mode<TCW_HINV>(a, st, "tcw_inv_hdft");
     case TCW_LAYER: return launch_tcw_mode<TCW_LAYER>(a, st, "tcw_layer");
-    case TCW_PROJ1: return launch_tcw_mode<TCW_PROJ1>(a, st, "tcw_proj1");
-    case TCW_PROJ2: return launch_tcw_mode<TCW_PROJ2>(a, st, "tcw_proj2");
   }
   return fail(DLWP_ERR_INVALID, "tcw: unknown mode %d", mode);
 }

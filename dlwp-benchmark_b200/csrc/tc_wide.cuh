@@ -11,8 +11,7 @@
 // One model evaluation (reference: neuralop FNO.forward behind fno.py:103):
 //   wide_gather_kernel   x_t from the NCHW sources (fno.py:49-62) -> [128 x 32] input images
 //                        (hi parts, a ones column for the bias, lo parts)
-//   tcw LIFT1            hidden = gelu(W1 x + b1)                  -> [128 x 256] images
-//   tcw LIFT2            x0 = W2 hidden + b2                       -> [128 x 128] images
+//   tcw_lift             x0 = W2 gelu(W1 x + b1) + b2, hidden on chip  -> [128 x 128] activation images
 //   per layer:
 //     tcw FWD            A[h, kx, c] = sum_w F[kx, w] x[h, w, c]   one item per grid row -> bf16 spectrum images
 //                        per (sample, kx, block of 64 grid rows): rows (h, re | im), columns = channels
@@ -23,8 +22,7 @@
 //     tcw HINV           Z[h, kx, c] = sum_r Gh[h, r] Y[r, kx, c]  -> per grid row [KZ rows (kx, re | im)] x
 //                        [128 channels] bf16 (the MN-major B operand of the inverse W-DFT)
 //     tcw LAYER          x' = act(G Z + Wskip x + bias)            -> [128 x 128] images
-//   tcw PROJ1            hidden = gelu(P1 x + b1)                  -> [128 x 256] images
-//   tcw PROJ2            out = P2 hidden + b2 + last frame         -> NCHW fp32
+//   tcw_proj             out = P2 gelu(P1 x + b1) + b2 + last frame, hidden on chip -> NCHW fp32
 // GELU epilogues store 2 * gelu (tc_gelu.cuh); the consumers' weights carry the 1/2.
 #pragma once
 #include "kernels.cuh"
@@ -34,7 +32,7 @@ namespace dlwp {
 constexpr int kWideC = 128;     // hidden channels
 constexpr int kWideHid = 256;   // lifting / projection width
 
-enum TcwMode { TCW_LIFT1 = 0, TCW_LIFT2 = 1, TCW_FWD = 2, TCW_LAYER = 3, TCW_PROJ1 = 4, TCW_PROJ2 = 5, TCW_HFWD = 6, TCW_HINV = 7 };
+enum TcwMode { TCW_FWD = 0, TCW_HFWD = 1, TCW_HINV = 2, TCW_LAYER = 3 };
 
 struct TcwArgs {
   int nitems;             // tiles (B * H * TW); grid rows (B * H) for TCW_FWD; B * Kc (* HB) for TCW_HFWD (TCW_HINV)
@@ -52,7 +50,7 @@ struct TcwArgs {
   float2* spec;           // TCW_HFWD: X [R, Kc, B, 128] complex
   float scale;            // TCW_FWD / TCW_HINV: factor on the result (1/2 when the input image holds 2 * gelu)
   int gelu;               // TCW_LAYER: apply GELU
-  float* out;             // TCW_PROJ2: NCHW frame(s) out[b * out_bstride + (c, y, x)]
+  float* out;             // projection: NCHW frame(s) out[b * out_bstride + (c, y, x)]
   long long out_bstride;
   const float* last;      // residual frame or null
   long long last_bstride;
