@@ -26,6 +26,12 @@ CASES = {
     "c5like": (dict(n_modes=[16, 64], constant_channels=4, prescribed_channels=1, prognostic_channels=8,
                     hidden_channels=128, lifting_channels=256, projection_channels=256, n_layers=4, context_size=1),
                (2, 21, 320)),
+    # the limits: 14 input = 14 output channels and no constants / prescribed fields, grid rows that fill
+    # their tiles exactly, two blocks of 64 grid rows with the second one partly empty, 3 retained columns,
+    # a single (last, GELU-free) layer, odd batch
+    "limits": (dict(n_modes=[4, 4], constant_channels=0, prescribed_channels=0, prognostic_channels=14,
+                    hidden_channels=128, lifting_channels=256, projection_channels=256, n_layers=1, context_size=1),
+               (3, 70, 256)),
 }
 
 
