@@ -370,8 +370,9 @@ def run_ours(args, wl):
     clim = (0.3 * torch.randn(Cg, H, W, generator=torch.Generator().manual_seed(7))).to(dev)
     const, presc, prog = (None if t is None else t.to(dev) for t in (const_h, presc_h, prog_h))
     in_bytes = sum(t.numel() * 4 for t in (const_h, presc_h, prog_h) if t is not None)
-    # what dlwp_rollout_host copies: constants, prescribed, and the first ctx frames of prognostic
-    h2d_bytes = sum(t.numel() * 4 for t in (const_h, presc_h) if t is not None) + members * ctx * Cg * H * W * 4
+    # what dlwp_rollout_host copies: constants, prescribed frames [0, T-1), and the first ctx frames of prognostic
+    h2d_bytes = (const_h.numel() * 4 if const_h is not None else 0) + members * ctx * Cg * H * W * 4 + \
+        (members * (T - 1) * kw["prescribed_channels"] * H * W * 4 if presc_h is not None else 0)
     out_bytes = members * lead * Cg * H * W * 4
     flush = None if in_bytes > 126e6 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream(dev)
@@ -472,8 +473,8 @@ def run_ours(args, wl):
             "e2e": {"value": units / e2e_s, "unit": "samples*steps/s", "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": out_bytes, "ms_per_step": e2e_s / args.steps * 1e3,
                     "api": "dlwp_rollout_host (pinned host buffers in the reference's [B,T,C,H,W] layout; copies in "
-                           "constants, prescribed and the ctx prognostic frames the loop reads, copies the whole "
-                           "forecast back frame by frame under the following steps' compute)"},
+                           "constants and the ctx prescribed / prognostic frames ahead of the first step, streams the "
+                           "later prescribed frames in and the whole forecast back frame by frame under the steps' compute)"},
             "gpu_launches": launches,
             "roofline": roof,
             "step_roofline": {"algorithmic_bytes_per_rollout": sb * lead, "achieved_gbs": sb * lead / (ms_step * 1e-3) / 1e9,

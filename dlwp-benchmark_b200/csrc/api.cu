@@ -34,6 +34,8 @@ void free_plan(dlwp_plan* p) {
     if (p->stage[i]) cudaFree(p->stage[i]);
   for (cudaEvent_t e : p->step_done) cudaEventDestroy(e);
   if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
+  for (cudaEvent_t e : p->frame_ready) cudaEventDestroy(e);
+  if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
   delete p;
 }
 
@@ -226,7 +228,26 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
   // every sample (fno.py:83,91-95 never look at later ground-truth frames), kept at their place
   // in the [B, T, Cg, H, W] staging layout so the frame bookkeeping is the device entry's.
   if (nb[0]) DLWP_CUDA(cudaMemcpyAsync(plan->stage[0], constants, nb[0], cudaMemcpyHostToDevice, st));
-  if (nb[1]) DLWP_CUDA(cudaMemcpyAsync(plan->stage[1], prescribed, nb[1], cudaMemcpyHostToDevice, st));
+  // prescribed: step t reads frames [t - ctx, t) (fno.py:86,98).  The first ctx frames go ahead of the first
+  // step; frame f >= ctx is first needed by step f + 1 and arrives on a second copy stream under the
+  // compute of the earlier steps (the last frame is never read).
+  const size_t presc_pitch = (size_t)T * d.prescribed_channels * frame, presc_row = (size_t)d.prescribed_channels * frame;
+  if (nb[1]) {
+    DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[1], presc_pitch, prescribed, presc_pitch, (size_t)ctx * presc_row, B,
+                                cudaMemcpyHostToDevice, st));
+    if (!plan->h2d_stream) DLWP_CUDA(cudaStreamCreateWithFlags(&plan->h2d_stream, cudaStreamNonBlocking));
+    while ((int)plan->frame_ready.size() < T) {
+      cudaEvent_t e = nullptr;
+      DLWP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      plan->frame_ready.push_back(e);
+    }
+    for (int f = ctx; f < T - 1; ++f) {
+      const size_t off = (size_t)f * presc_row;
+      DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[1] + off, presc_pitch, (const char*)prescribed + off, presc_pitch, presc_row,
+                                  B, cudaMemcpyHostToDevice, plan->h2d_stream));
+      DLWP_CUDA(cudaEventRecord(plan->frame_ready[f], plan->h2d_stream));
+    }
+  }
   const size_t prog_pitch = (size_t)T * d.prognostic_channels * frame;
   DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[2], prog_pitch, prognostic, prog_pitch, (size_t)ctx * d.prognostic_channels * frame, B,
                               cudaMemcpyHostToDevice, st));
@@ -238,6 +259,7 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
     StepIO io;
     rollout_io(plan, constants ? (const float*)plan->stage[0] : nullptr, prescribed ? (const float*)plan->stage[1] : nullptr,
                (const float*)plan->stage[2], dev_outs, T, t, &io);
+    if (nb[1] && t - 1 >= ctx) DLWP_CUDA(cudaStreamWaitEvent(st, plan->frame_ready[t - 1], 0));
     DLWP_TRY(plan_backbone(plan, io, batch, st));
     cudaEvent_t ev = plan->step_done[t - ctx];
     DLWP_CUDA(cudaEventRecord(ev, st));

@@ -82,6 +82,8 @@ struct dlwp_plan {
   size_t stage_bytes[4] = {0, 0, 0, 0};
   cudaStream_t copy_stream = nullptr;        // device -> host frames, under the following steps' compute
   std::vector<cudaEvent_t> step_done;        // one per lead time + one for the end of the copies
+  cudaStream_t h2d_stream = nullptr;         // host -> device prescribed frames of later steps, under the earlier steps' compute
+  std::vector<cudaEvent_t> frame_ready;      // one per prescribed frame
 };
 
 namespace dlwp {

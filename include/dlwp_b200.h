@@ -131,10 +131,11 @@ int dlwp_rollout(dlwp_plan* plan, const float* constants, const float* prescribe
                  const float* prognostic, int batch, int T, float* outs, void* stream);
 
 /* Same call with HOST buffers (pinned or pageable; what scripts/evaluate.py:214-217,235-243 does
- * around the model): copies to plan-owned staging what the loop reads -- constants, prescribed and
- * the first `ctx` frames of prognostic (later ground-truth frames are never read, fno.py:83,91-95)
- * --, runs the rollout, copies every lead time's frame back on a second stream while the next
- * steps compute, and synchronises `stream`.  This is the entry the end-to-end benchmark times.
+ * around the model): copies to plan-owned staging what the loop reads -- constants, the first `ctx`
+ * frames of prescribed and of prognostic (later ground-truth prognostic frames are never read,
+ * fno.py:83,91-95) --, runs the rollout while the later prescribed frames arrive on a second
+ * stream just ahead of the step that first reads them and every lead time's frame goes back on a
+ * third stream under the following steps, and synchronises `stream`.  This is the entry the end-to-end benchmark times.
  * May grow the staging buffers on first use. */
 int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* prescribed,
                       const float* prognostic, int batch, int T, float* outs, void* stream);

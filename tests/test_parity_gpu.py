@@ -231,15 +231,23 @@ def test_afno_paper_size_matches_oracle(pkg):
 # ---------------------------------------------------------------------------------------
 # host entry, metrics kernel, weight reload
 # ---------------------------------------------------------------------------------------
-def test_rollout_host_equals_device_rollout(pkg):
-    _, mod, kw, (B, H, W) = _fno_pair(pkg, "C2")
-    const, presc, prog = synthetic(B, 4, 4, 1, 8, H, W)
+@pytest.mark.parametrize("ctx,T", [(1, 4), (2, 7)])
+def test_rollout_host_equals_device_rollout(pkg, ctx, T):
+    # the host entry streams the later prescribed frames in under the earlier steps: same bits as the device entry
+    cls, kw, (B, H, W) = FNO_CASES["C2"]
+    kw = dict(kw, context_size=ctx)
+    torch.manual_seed(1234)
+    mod = getattr(pkg, cls)(**kw).cuda().eval()
+    const, presc, prog = synthetic(B, T, 4, 1, 8, H, W)
     with torch.no_grad():
         dev = mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog)).cpu()
         host = mod.forward_host(constants=const.pin_memory(), prescribed=presc.pin_memory(),
                                 prognostic=prog.pin_memory())
-    assert host.device.type == "cpu"
+        again = mod.forward_host(constants=const.pin_memory(), prescribed=(presc + 1.0).pin_memory(),
+                                 prognostic=prog.pin_memory())
+    assert host.device.type == "cpu" and host.shape == (B, T - ctx, 8, H, W)
     assert torch.equal(dev, host)
+    assert not torch.equal(again, host)      # a second call with other prescribed frames is not served stale ones
 
 
 def test_metrics_kernel_matches_oracle(pkg):
