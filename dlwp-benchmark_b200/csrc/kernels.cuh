@@ -65,14 +65,18 @@ int launch_layernorm(const float* in, float* out, const float* gamma, const floa
 
 // ---- per-mode channel mixing ----------------------------------------------------------
 // X, Y: [modes, B, C] complex;  Wm: [modes, Ci, Co] complex
-// `im.img` set: Y is not written; the result goes out as bf16 tile images per (sample, retained column)
-// for the tensor-core inverse H-DFT (tc_wide.cuh), modes = rows * im.Kc
-struct MixImageOut {
+// Options of the bf16 kernel set (tc_wide.cuh).  `img` set: Y is not written; the result goes out as
+// bf16 tile images per (sample, retained column) for the tensor-core inverse H-DFT, modes = rows * Kc.
+// `w16` set (few-sample kernel only): the mode weights are read from this bf16 (re, im)-pair copy of Wm.
+struct MixWideOpts {
   uint8_t* img = nullptr;
   int Kc = 0;
+  const uint32_t* w16 = nullptr;
 };
+// complex fp32 -> bf16 (re, im) pairs
+int launch_narrow_bf16(const float2* in, uint32_t* out, long long n, cudaStream_t st);
 int launch_mix_dense(const float2* X, const float2* Wm, float2* Y, int modes, int B, int Ci, int Co,
-                     cudaStream_t st, MixImageOut im = MixImageOut{});
+                     cudaStream_t st, MixWideOpts im = MixWideOpts{});
 // AFNO block-diagonal 2-layer complex MLP with ReLU (re, im separately) and softshrink.
 // w1 [2, nb, bs, bs*f], b1 [2, nb, bs*f], w2 [2, nb, bs*f, bs], b2 [2, nb, bs]
 int launch_mix_afno(const float2* X, float2* Y, const float* w1, const float* b1, const float* w2,

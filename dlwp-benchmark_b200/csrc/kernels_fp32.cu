@@ -302,7 +302,7 @@ int launch_layernorm(const float* in, float* out, const float* gamma, const floa
 
 // bf16 image output for the tensor-core inverse H-DFT (tc_wide.cuh): per (sample, retained column)
 // a [128 rows = (retained row, re | im)] x [128 channels] chunk-major tile; mode m = row * Kc + column
-__device__ __forceinline__ void mix_store_image(const MixImageOut& im, int m, int b, int o, float2 v) {
+__device__ __forceinline__ void mix_store_image(const MixWideOpts& im, int m, int b, int o, float2 v) {
   const int r = m / im.Kc, kx = m - r * im.Kc;
   uint8_t* p = im.img + ((size_t)b * im.Kc + kx) * 32768 + (size_t)(o >> 3) * 2048 + (size_t)(2 * r) * 16 + (o & 7) * 2;
   *reinterpret_cast<__nv_bfloat16*>(p) = __float2bfloat16(v.x);
@@ -317,7 +317,7 @@ __device__ __forceinline__ void mix_store_image(const MixImageOut& im, int m, in
 __global__ void __launch_bounds__(256) mix_dense_kernel(const float2* __restrict__ X,
                                                         const float2* __restrict__ Wm,
                                                         float2* __restrict__ Y, int B, int Ci, int Co,
-                                                        MixImageOut im) {
+                                                        MixWideOpts im) {
   extern __shared__ float2 s_x[];  // [8][Ci]
   const int m = blockIdx.x;
   const int b0 = blockIdx.y * 8;
@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(256) mix_dense_kernel(const float2* __restrict
 __global__ void __launch_bounds__(256) mix_dense_fewb_kernel(const float2* __restrict__ X,
                                                              const float2* __restrict__ Wm,
                                                              float2* __restrict__ Y, int B, int Ci, int Co,
-                                                             MixImageOut im) {
+                                                             MixWideOpts im) {
   extern __shared__ float2 s_mix[];   // x [4][Ci], then partial sums [8][4][Co]
   float2* s_x = s_mix;
   float2* s_p = s_mix + 4 * Ci;
@@ -405,14 +405,89 @@ __global__ void __launch_bounds__(256) mix_dense_fewb_kernel(const float2* __res
   }
 }
 
+// The same with the mode weights stored as bf16 (re, im) pairs (the bf16 kernel set): half the bytes.
+// A lane takes four outputs per 16-byte load, so that a warp keeps as many bytes in flight as above.
+__global__ void __launch_bounds__(256) mix_dense_fewb16_kernel(const float2* __restrict__ X, float2* __restrict__ Y, int B,
+                                                               int Ci, int Co, MixWideOpts im) {
+  extern __shared__ float2 s_mix[];   // x [4][Ci], then partial sums [8][4][Co]
+  float2* s_x = s_mix;
+  float2* s_p = s_mix + 4 * Ci;
+  const int m = blockIdx.x, lane = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + lane;
+  for (int idx = tid; idx < 4 * Ci; idx += 256) {
+    const int bb = idx / Ci, i = idx - bb * Ci;
+    s_x[idx] = bb < B ? X[((long long)m * B + bb) * Ci + i] : make_float2(0.f, 0.f);
+  }
+  __syncthreads();
+  const int quarter = Co >> 2;
+  const uint4* __restrict__ w4 = reinterpret_cast<const uint4*>(im.w16 + (long long)m * Ci * Co);
+  const int i0 = ty * Ci / 8, i1 = (ty + 1) * Ci / 8;
+  for (int oq = lane; oq < quarter; oq += 32) {
+    float2 a[4][4];
+#pragma unroll
+    for (int bb = 0; bb < 4; ++bb)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) a[bb][j] = make_float2(0.f, 0.f);
+#pragma unroll 8
+    for (int i = i0; i < i1; ++i) {
+      const uint4 u = w4[(long long)i * quarter + oq];
+      const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float wr = __uint_as_float(uw[j] << 16), wi = __uint_as_float(uw[j] & 0xffff0000u);
+#pragma unroll
+        for (int bb = 0; bb < 4; ++bb) {
+          const float2 xv = s_x[bb * Ci + i];
+          a[bb][j].x = fmaf(xv.x, wr, a[bb][j].x);
+          a[bb][j].x = fmaf(-xv.y, wi, a[bb][j].x);
+          a[bb][j].y = fmaf(xv.x, wi, a[bb][j].y);
+          a[bb][j].y = fmaf(xv.y, wr, a[bb][j].y);
+        }
+      }
+    }
+#pragma unroll
+    for (int bb = 0; bb < 4; ++bb)
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+        *reinterpret_cast<float4*>(&s_p[(ty * 4 + bb) * Co + 4 * oq + 2 * j]) =
+            make_float4(a[bb][2 * j].x, a[bb][2 * j].y, a[bb][2 * j + 1].x, a[bb][2 * j + 1].y);
+  }
+  __syncthreads();
+  for (int idx = tid; idx < B * Co; idx += 256) {
+    const int bb = idx / Co, o = idx - bb * Co;
+    float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      const float2 v = s_p[(w * 4 + bb) * Co + o];
+      acc.x += v.x;
+      acc.y += v.y;
+    }
+    if (im.img) mix_store_image(im, m, bb, o, acc);
+    else Y[((long long)m * B + bb) * Co + o] = acc;
+  }
+}
+
+__global__ void narrow_bf16_kernel(const float2* __restrict__ in, uint32_t* __restrict__ out, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(in[i].x, in[i].y);
+    out[i] = *reinterpret_cast<const uint32_t*>(&v);
+  }
+}
+int launch_narrow_bf16(const float2* in, uint32_t* out, long long n, cudaStream_t st) {
+  narrow_bf16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, out, n);
+  DLWP_LAUNCHED("narrow_bf16_kernel");
+  return DLWP_OK;
+}
+
 int launch_mix_dense(const float2* X, const float2* Wm, float2* Y, int modes, int B, int Ci, int Co,
-                     cudaStream_t st, MixImageOut im) {
+                     cudaStream_t st, MixWideOpts im) {
   DLWP_REQUIRE(modes > 0 && B > 0 && Ci > 0 && Co > 0, "mix_dense: empty problem");
   DLWP_REQUIRE(!im.img || (Co == 128 && im.Kc > 0 && modes % im.Kc == 0 && modes / im.Kc <= 64),
                "mix_dense: the image output is laid out for 128 channels and at most 64 retained rows");
   const size_t smem_few = (size_t)(4 * Ci + 32 * Co) * sizeof(float2);
   if (B <= 4 && Co % 2 == 0 && Ci >= 8 && smem_few <= 48 * 1024) {
-    mix_dense_fewb_kernel<<<dim3((unsigned)modes), dim3(32, 8), smem_few, st>>>(X, Wm, Y, B, Ci, Co, im);
+    if (im.w16 && Co % 4 == 0) mix_dense_fewb16_kernel<<<dim3((unsigned)modes), dim3(32, 8), smem_few, st>>>(X, Y, B, Ci, Co, im);
+    else mix_dense_fewb_kernel<<<dim3((unsigned)modes), dim3(32, 8), smem_few, st>>>(X, Wm, Y, B, Ci, Co, im);
     DLWP_LAUNCHED("mix_dense_kernel");
     return DLWP_OK;
   }

@@ -76,6 +76,7 @@ struct dlwp_plan {
   uint8_t *tcw_W1 = nullptr, *tcw_W2 = nullptr, *tcw_b2 = nullptr, *tcw_P1 = nullptr, *tcw_pb1 = nullptr,
           *tcw_P2 = nullptr, *tcw_pb2 = nullptr;
   std::vector<uint8_t*> tcw_skip, tcw_cbias;            // per layer skip-conv and bias images
+  std::vector<uint32_t*> tcw_wm16;                      // per layer bf16 copy of the mode-major spectral weights
 
   // host-entry staging (dlwp_rollout_host)
   void* stage[4] = {nullptr, nullptr, nullptr, nullptr};

@@ -199,6 +199,17 @@ int plan_tcw_commit(dlwp_plan* p, cudaStream_t st) {
     std::vector<float> bl(b.begin() + (size_t)l * C, b.begin() + (size_t)(l + 1) * C);
     DLWP_TRY(put_bias(p->tcw_cbias[l], bl, C, C));
   }
+  // bf16 copy of the mode-major spectral weights (plan.cu: commit_fno packed them before this runs):
+  // with a few samples per GPU the mode mixing is bound by reading them
+  {
+    const long long n = (long long)d.n_rows * d.n_cols * C * C;
+    if (p->tcw_wm16.empty()) {
+      p->tcw_wm16.assign(N, nullptr);
+      for (int l = 0; l < N; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_wm16[l], (size_t)n * 4));
+    }
+    for (int l = 0; l < N; ++l) DLWP_TRY(launch_narrow_bf16(p->wm[l], p->tcw_wm16[l], n, st));
+    DLWP_CUDA(cudaStreamSynchronize(st));
+  }
   // the last block applies no GELU, so the projection reads a plain image
   DLWP_TRY(fetch(p, "projection.fcs.0.weight", (int64_t)L * C, &w));
   DLWP_TRY(put_weight(p->tcw_P1, w, 1.f, L, C, L, C));
@@ -243,7 +254,7 @@ int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
     a.a_img = p->tcw_sa; a.g_img = p->tcw_Fs; a.spec = p->specX;
     DLWP_TRY(launch_tcw(TCW_HFWD, a, st));
     DLWP_TRY(launch_mix_dense(p->specX, p->wm[l], p->specY, d.n_rows * d.n_cols, B, kWideC, kWideC, st,
-                              MixImageOut{p->tcw_ys, d.n_cols}));
+                              MixWideOpts{p->tcw_ys, d.n_cols, B <= 4 ? p->tcw_wm16[l] : nullptr}));
     a = base;
     a.nitems = B * d.n_cols * p->tcw_HB;
     a.a_img = p->tcw_ys; a.g_img = p->tcw_Gs; a.out_img = p->tcw_z;
