@@ -355,7 +355,8 @@ def run_ours(args, wl):
     if world > 1:
         dist.barrier()
     import dlwp_benchmark_b200 as pkg
-    from dlwp_benchmark_b200 import metrics as M, native
+    from dlwp_benchmark_b200 import ensemble, metrics as M, native
+    numa_bound = ensemble.bind_to_device_cpus(local) if world > 1 else False   # before any pinned allocation
 
     members = args.members or members_default
     ctx = kw["context_size"]
@@ -476,6 +477,7 @@ def run_ours(args, wl):
                            "constants and the ctx prescribed / prognostic frames ahead of the first step, streams the "
                            "later prescribed frames in and the whole forecast back frame by frame under the steps' compute)"},
             "gpu_launches": launches,
+            "host_affinity": "ranks pinned to their GPU's NUMA-local cores (NVML)" if numa_bound else "default",
             "roofline": roof,
             "step_roofline": {"algorithmic_bytes_per_rollout": sb * lead, "achieved_gbs": sb * lead / (ms_step * 1e-3) / 1e9,
                               "frac_of_hbm_peak": sb * lead / (ms_step * 1e-3) / 1e9 / hbm_peak,
