@@ -134,6 +134,7 @@ int plan_build(dlwp_plan* p) {
   DLWP_TRY(dev_alloc(p, (void**)&p->specX, R * Kc * B * C * sizeof(float2)));
   DLWP_TRY(dev_alloc(p, (void**)&p->specY, R * Kc * B * C * sizeof(float2)));
   if (d.precision == DLWP_PREC_FP32_TC) DLWP_TRY(plan_tc_build(p));
+  if (d.precision == DLWP_PREC_FP32_TC) DLWP_TRY(plan_atc_build(p));
   if (d.precision == DLWP_PREC_BF16) DLWP_TRY(plan_tcw_build(p));
   return DLWP_OK;
 }
@@ -270,6 +271,7 @@ int plan_commit(dlwp_plan* p, cudaStream_t st) {
   else DLWP_TRY(commit_afno(p, st));
   if (p->tc) DLWP_TRY(plan_tc_commit(p, st));
   if (p->tcw) DLWP_TRY(plan_tcw_commit(p, st));
+  if (p->atc) DLWP_TRY(plan_atc_commit(p, st));
   p->committed = true;
   return DLWP_OK;
 }
@@ -445,6 +447,10 @@ static int backbone_afno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st)
     DLWP_TRY(launch_layernorm(t, u, g1, be1, P, E, d.layernorm_eps, st));
     DLWP_TRY(spectral_layer(p, u, t2, nullptr, i, u, t, nullptr, 0, B, st));
     // x = mlp(norm2(x)) + x
+    if (p->atc) {
+      DLWP_TRY(atc_block_mlp(p, i, t2, t, P, st));
+      continue;
+    }
     DLWP_TRY(launch_layernorm(t2, u, g2, be2, P, E, d.layernorm_eps, st));
     DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.weight"), (int64_t)Hd * E, &w));
     DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.bias"), Hd, &b));

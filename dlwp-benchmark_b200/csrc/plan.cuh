@@ -7,6 +7,7 @@
 
 #include "kernels.cuh"
 #include "tc_fno.cuh"
+#include "tc_afno.cuh"
 #include "tc_wide.cuh"
 
 namespace dlwp {
@@ -78,6 +79,11 @@ struct dlwp_plan {
   std::vector<uint8_t*> tcw_skip, tcw_cbias;            // per layer skip-conv and bias images
   std::vector<uint32_t*> tcw_wm16;                      // per layer bf16 copy of the mode-major spectral weights
 
+  // tensor-core AFNO kernels (tc_afno.cuh): precision == DLWP_PREC_FP32_TC, embed_dim 64, mlp hidden 256
+  bool atc = false;
+  std::vector<uint8_t*> atc_W1, atc_W2;                 // per block: fc1 * diag(norm2.weight), fc2 / 2 operand images
+  std::vector<float*> atc_b1;                           // per block: fc1.bias + fc1 * norm2.bias
+
   // host-entry staging (dlwp_rollout_host)
   void* stage[4] = {nullptr, nullptr, nullptr, nullptr};
   size_t stage_bytes[4] = {0, 0, 0, 0};
@@ -97,6 +103,9 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
 int plan_tcw_build(dlwp_plan* p);                              // tc_wide_plan.cu
 int plan_tcw_commit(dlwp_plan* p, cudaStream_t st);
 int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
+int plan_atc_build(dlwp_plan* p);                              // tc_afno_plan.cu
+int plan_atc_commit(dlwp_plan* p, cudaStream_t st);
+int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st);
 int spectral_mid_fno(dlwp_plan* p, const float2* wm, int B, cudaStream_t st);
 int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);
 int plan_need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out);

@@ -1,0 +1,85 @@
+// Plan-side glue of the tensor-core AFNO kernels: eligibility, weight operand images
+// (reference: Block.forward / Mlp.forward, fourcastnet.py:41-57,176-193).
+#include <vector>
+
+#include "plan.cuh"
+
+namespace dlwp {
+
+static std::string bname(int i, const char* tail) { return "blocks." + std::to_string(i) + tail; }
+
+// The kernels are written for the reference configuration (configs/model/fourcastnet.yaml:
+// embed_dim 64, mlp_ratio 4) on token counts that fill 128-token tiles.  Anything else keeps the
+// fp32 kernel set of kernels_fp32.cu.
+int plan_atc_build(dlwp_plan* p) {
+  const dlwp_model_desc& d = p->d;
+  p->atc = false;
+  if (d.kind != DLWP_MODEL_AFNO || d.embed_dim != kAfnoE || d.mlp_hidden != kAfnoHid) return DLWP_OK;
+  if ((p->gh * p->gw) % kTcTile != 0) return DLWP_OK;
+  p->atc_W1.assign(d.depth, nullptr);
+  p->atc_W2.assign(d.depth, nullptr);
+  p->atc_b1.assign(d.depth, nullptr);
+  for (int i = 0; i < d.depth; ++i) {
+    DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_W1[i], (size_t)kAfnoHid * kAfnoE * 4));
+    DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_W2[i], (size_t)kAfnoE * kAfnoHid * 4));
+    DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_b1[i], (size_t)kAfnoHid * sizeof(float)));
+  }
+  p->atc = true;
+  return DLWP_OK;
+}
+
+static int fetch(const dlwp_plan* p, const std::string& name, int64_t numel, std::vector<float>* out) {
+  const float* dev;
+  DLWP_TRY(plan_need(p, name, numel, &dev));
+  out->resize((size_t)numel);
+  DLWP_CUDA(cudaMemcpy(out->data(), dev, (size_t)numel * sizeof(float), cudaMemcpyDeviceToHost));
+  return DLWP_OK;
+}
+
+int plan_atc_commit(dlwp_plan* p, cudaStream_t st) {
+  const dlwp_model_desc& d = p->d;
+  DLWP_CUDA(cudaStreamSynchronize(st));
+  std::vector<float> w, b, g, be;
+  std::vector<uint8_t> img((size_t)kAfnoHid * kAfnoE * 4);
+  for (int i = 0; i < d.depth; ++i) {
+    // LayerNorm(x) W1^T + b1 = xhat (W1 diag(gamma))^T + (b1 + W1 beta): the kernel only normalises
+    DLWP_TRY(fetch(p, bname(i, ".norm2.weight"), kAfnoE, &g));
+    DLWP_TRY(fetch(p, bname(i, ".norm2.bias"), kAfnoE, &be));
+    DLWP_TRY(fetch(p, bname(i, ".mlp.fc1.weight"), (int64_t)kAfnoHid * kAfnoE, &w));
+    DLWP_TRY(fetch(p, bname(i, ".mlp.fc1.bias"), kAfnoHid, &b));
+    std::vector<float> b1(kAfnoHid);
+    for (int h = 0; h < kAfnoHid; ++h) {
+      double acc = b[h];
+      for (int c = 0; c < kAfnoE; ++c) {
+        acc += (double)w[(size_t)h * kAfnoE + c] * (double)be[c];
+        w[(size_t)h * kAfnoE + c] = (float)((double)w[(size_t)h * kAfnoE + c] * (double)g[c]);
+      }
+      b1[h] = (float)acc;
+    }
+    tc_pack_images(w.data(), kAfnoHid, kAfnoE, kAfnoE, kAfnoHid, kAfnoE, img.data());
+    DLWP_CUDA(cudaMemcpy(p->atc_W1[i], img.data(), img.size(), cudaMemcpyHostToDevice));
+    DLWP_CUDA(cudaMemcpy(p->atc_b1[i], b1.data(), b1.size() * sizeof(float), cudaMemcpyHostToDevice));
+    // the GELU epilogue hands 2 * gelu(hidden) to the second GEMM: its weights carry the 1/2
+    DLWP_TRY(fetch(p, bname(i, ".mlp.fc2.weight"), (int64_t)kAfnoE * kAfnoHid, &w));
+    for (float& v : w) v *= 0.5f;
+    tc_pack_images(w.data(), kAfnoE, kAfnoHid, kAfnoHid, kAfnoE, kAfnoHid, img.data());
+    DLWP_CUDA(cudaMemcpy(p->atc_W2[i], img.data(), img.size(), cudaMemcpyHostToDevice));
+  }
+  return DLWP_OK;
+}
+
+// x = x + mlp(norm2(x))   (fourcastnet.py:189-192)
+int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st) {
+  AfnoMlpArgs a{};
+  a.ntiles = P / kTcTile;
+  a.x = x;
+  a.out = out;
+  a.W1img = p->atc_W1[block];
+  a.b1 = p->atc_b1[block];
+  a.W2img = p->atc_W2[block];
+  DLWP_TRY(plan_need(p, bname(block, ".mlp.fc2.bias"), kAfnoE, &a.b2));
+  a.eps = p->d.layernorm_eps;
+  return launch_afno_mlp(a, st);
+}
+
+}  // namespace dlwp

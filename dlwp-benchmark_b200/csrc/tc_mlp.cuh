@@ -1,0 +1,196 @@
+// Pieces shared by the tcgen05 MLP kernels (tc_fno.cu: lifting / projection; tc_afno.cu: the AFNO
+// block's LayerNorm + Mlp): CTA organisation, epilogue thread coordinates, the issuer of the two
+// chained GEMMs and the GELU epilogue that turns the first accumulator into the second operand.
+#pragma once
+#include "tc_common.cuh"
+#include "tc_fno.cuh"
+#include "tc_gelu.cuh"
+
+namespace dlwp {
+using namespace tc;
+
+namespace {
+
+constexpr int kImg = kTcImgBytes;            // 8192: one bf16 part of a [128 x 32] tile
+constexpr int kTileBytes = 2 * kImg;         // hi + lo
+constexpr int kFBytes = 2 * 32 * 128 * 2;     // forward W-DFT operand: [hi | lo] images of 32 rows x 128 pixels
+
+// v = hi + lo for a pair, residual through one packed FMA
+__device__ __forceinline__ void split2p(float2 v, uint32_t& hi, uint32_t& lo) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+  hi = *reinterpret_cast<uint32_t*>(&h);
+  const float2 hf = make_float2(__uint_as_float(hi << 16), __uint_as_float(hi & 0xffff0000u));
+  const float2 d = __ffma2_rn(hf, make_float2(-1.0f, -1.0f), v);
+  __nv_bfloat162 l = __floats2bfloat162_rn(d.x, d.y);
+  lo = *reinterpret_cast<uint32_t*>(&l);
+}
+
+}  // namespace
+
+namespace {
+
+constexpr int kEpi = 256;                    // epilogue threads per worker
+constexpr int kEpiWarps = kEpi / 32;
+constexpr int kCtlWarp = 2 * kEpiWarps;      // first control warp
+constexpr int kCta = 2 * kEpi + 2 * 32;      // 576
+constexpr int kCtaLayer = kCta + 2 * 32;     // the layer kernel splits control into an issuer and a loader / finisher warp
+
+// epilogue thread coordinates: tile row (= pixel = TMEM lane), column half, TMEM lane quarter
+struct EpiId {
+  int w, row, half, q4;
+  __device__ __forceinline__ explicit EpiId(int tid) {
+    const int warp = tid >> 5;
+    w = warp / kEpiWarps;
+    q4 = warp & 3;
+    half = (warp >> 2) & 1;
+    row = q4 * 32 + (tid & 31);
+  }
+};
+
+__device__ __forceinline__ uint32_t full_par(uint32_t u) { return (u >> 1) & 1u; }
+__device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1u) ^ 1u; }
+}  // namespace
+
+namespace {
+
+enum { MB_A1FULL = 0, MB_A1EMPTY = 2, MB_D1FULL = 4, MB_D1EMPTY = 6, MB_A2FULL = 8, MB_A2EMPTY = 10, MB_D2FULL = 12,
+       MB_D2EMPTY = 14, MB_XTFULL = 16, MB_D3FULL = 17, MB_YFREE = 18, MB_PER = 19 };
+
+__device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_count) {
+  for (int i = 0; i < 2; ++i) {
+    mbar_init(&b[MB_A1FULL + i], a1_full_count);
+    mbar_init(&b[MB_A1EMPTY + i], 1);
+    mbar_init(&b[MB_D1FULL + i], 1);
+    mbar_init(&b[MB_D1EMPTY + i], kEpi);
+    mbar_init(&b[MB_A2FULL + i], kEpi);
+    mbar_init(&b[MB_A2EMPTY + i], 1);
+    mbar_init(&b[MB_D2FULL + i], 1);
+    mbar_init(&b[MB_D2EMPTY + i], kEpi);
+  }
+  mbar_init(&b[MB_XTFULL], kEpi);
+  mbar_init(&b[MB_D3FULL], 1);
+  mbar_init(&b[MB_YFREE], 1);
+}
+
+struct MlpIssuer {
+  uint64_t* b;
+  uint32_t aA1;        // two A1 buffers, `a1_stride` bytes apart; lo image at +128*K1*2
+  uint32_t a1_stride;
+  uint32_t aW1, aW2, aA2, tmem;
+  int hid, P;
+  uint32_t nc;         // chunks issued so far
+  uint32_t aOnes, aW1x;   // optional bias term of the first GEMM: Ones[128,16] * W1x[hid,16]^T (0 = none)
+  uint32_t leader;        // elect_one() of the (converged) control warp
+
+  template <int K1>
+  __device__ __forceinline__ void mma1(uint32_t u, int p, uint32_t gp) {
+    const int db = gp & 1, ub = u & 1;
+    mbar_wait(&b[MB_D1EMPTY + db], empty_par(gp));
+    if (p == 0) mbar_wait(&b[MB_A1FULL + ub], full_par(u));
+    tc_fence_after();
+    const uint32_t idesc = idesc_bf16(128, 64);
+    const uint32_t a_lo = 128 * K1 * 2, w_lo = (uint32_t)hid * K1 * 2;
+    const uint64_t dA = chunk_desc(aA1 + ub * a1_stride, 128, 0),
+                   dW = smem_desc(aW1 + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128);
+    uint32_t acc = 0;
+#pragma unroll
+    for (int term = 0; term < 3; ++term) {
+      const uint32_t ao = term == 1 ? a_lo : 0u, wo = term == 2 ? w_lo : 0u;
+#pragma unroll
+      for (int k0 = 0; k0 < K1; k0 += 16) {
+        umma_bf16_p(leader, tmem + 64u * db, desc_off(dA, ao + (k0 >> 3) * 2048), desc_off(dW, wo + (uint32_t)(k0 >> 3) * hid * 16),
+                    idesc, acc);
+        acc = 1;
+      }
+    }
+    if (aW1x != 0)
+      umma_bf16_p(leader, tmem + 64u * db, chunk_desc(aOnes, 128, 0),
+                  smem_desc(aW1x + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128), idesc, 1);
+    umma_commit_p(leader, &b[MB_D1FULL + db]);
+    if (p == P - 1) umma_commit_p(leader, &b[MB_A1EMPTY + ub]);
+    __syncwarp();
+  }
+
+  template <int N2>
+  __device__ __forceinline__ void mma2(uint32_t u, int p) {
+    const uint32_t idesc = idesc_bf16(128, N2);
+    const uint32_t w_lo = aW2 + (uint32_t)N2 * hid * 2;
+    const uint32_t d2 = tmem + 128u + (N2 > 32 ? 64u : 32u) * (u & 1);
+#pragma unroll
+    for (int j = 0; j < 2; ++j, ++nc) {
+      const int ab = nc & 1;
+      mbar_wait(&b[MB_A2FULL + ab], full_par(nc));
+      if (p == 0 && j == 0) mbar_wait(&b[MB_D2EMPTY + (u & 1)], empty_par(u));
+      tc_fence_after();
+      const int hcol0 = p * 64 + 32 * j;
+      const uint64_t dA = chunk_desc(aA2 + ab * kTileBytes, 128, 0), dW = chunk_desc(aW2, N2, hcol0);
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t ao = term == 1 ? (uint32_t)kImg : 0u, wo = term == 2 ? w_lo - aW2 : 0u;
+#pragma unroll
+        for (int kk = 0; kk < 32; kk += 16)
+          umma_bf16_p(leader, d2, desc_off(dA, ao + (kk >> 3) * 2048), desc_off(dW, wo + (kk >> 3) * N2 * 16), idesc,
+                      (p | j | term | kk) != 0);
+      }
+      umma_commit_p(leader, &b[MB_A2EMPTY + ab]);
+      __syncwarp();
+    }
+    if (p == P - 1) umma_commit_p(leader, &b[MB_D2FULL + (u & 1)]);
+  }
+};
+
+// epilogue side of one tile's MLP; `after_pass0()` runs once after the first pass.  Each thread
+// turns 16 hidden columns of its pixel per 32-column chunk into split-bf16 operand bytes.
+// `sB1` (optional): the first layer's bias [hid] in shared memory, added here when the first GEMM
+// has no spare K column to carry it.
+template <class Hook>
+__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint32_t tmem_lane, int P, uint8_t* sA2,
+                                             uint32_t& gp, uint32_t& nc, Hook after_pass0, const float* sB1 = nullptr) {
+  for (int p = 0; p < P; ++p, ++gp) {
+    const int db = gp & 1;
+    mbar_wait(&b[MB_D1FULL + db], full_par(gp));
+    tc_fence_after();
+#pragma unroll
+    for (int j = 0; j < 2; ++j, ++nc) {
+      uint32_t r[16];
+      tmem_ld16(tmem_lane + 64u * db + 32u * j, r);
+      tmem_ld_wait();
+      if (j == 1) {
+        tc_fence_before();
+        mbar_arrive(&b[MB_D1EMPTY + db]);
+      }
+      uint32_t h[8], l[8];
+      {
+        if (sB1 != nullptr) {
+          const float4* bq = reinterpret_cast<const float4*>(sB1 + p * 64 + 32 * j + 16 * id.half);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float4 bv = bq[e];
+            r[4 * e] = __float_as_uint(__uint_as_float(r[4 * e]) + bv.x);
+            r[4 * e + 1] = __float_as_uint(__uint_as_float(r[4 * e + 1]) + bv.y);
+            r[4 * e + 2] = __float_as_uint(__uint_as_float(r[4 * e + 2]) + bv.z);
+            r[4 * e + 3] = __float_as_uint(__uint_as_float(r[4 * e + 3]) + bv.w);
+          }
+        }
+        float2 g2[8];             // 2 * gelu: W2's operand image is packed with the factor 1/2
+        gelu2x_8(r, g2);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) split2p(g2[e], h[e], l[e]);
+      }
+      const int ab = nc & 1;
+      mbar_wait(&b[MB_A2EMPTY + ab], empty_par(nc));
+      uint8_t* dst = sA2 + ab * kTileBytes + id.row * 16 + id.half * 4096;
+      *reinterpret_cast<uint4*>(dst) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(h[4], h[5], h[6], h[7]);
+      *reinterpret_cast<uint4*>(dst + kImg) = make_uint4(l[0], l[1], l[2], l[3]);
+      *reinterpret_cast<uint4*>(dst + kImg + 2048) = make_uint4(l[4], l[5], l[6], l[7]);
+      fence_async_smem();
+      mbar_arrive(&b[MB_A2FULL + ab]);
+    }
+    if (p == 0) after_pass0();
+  }
+}
+
+}  // namespace
+
+}  // namespace dlwp
