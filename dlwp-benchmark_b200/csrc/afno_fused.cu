@@ -1,0 +1,268 @@
+// Fused fp32 kernels of the AFNO2D token mixer at embed_dim 64 (fourcastnet.py:78-127,176-187):
+// three launches per block instead of LayerNorm + four transforms + the block MLP.
+//
+//   afno_fwd_kernel   y = LayerNorm(x) per token, then the truncated W-DFT of y           one CTA per grid row
+//                     A[b][kx][h][c] = sum_w Fw[kx, w] y[b, h, w, c]                      (:84-85, rfft2 W half)
+//   afno_mid_kernel   per (sample, retained column): H-DFT, the block-diagonal complex 2-layer MLP with
+//                     ReLU / softshrink on re and im separately, inverse H-DFT            (:85-124)
+//   afno_inv_kernel   t2 = Re(Gw Z) + y + x: C2R inverse W-DFT, AFNO2D's "+ bias" (its own input, :127)
+//                     and Block's double skip (:185-187); y is recomputed from x          one CTA per grid row
+// Layouts: A [B][Kc][H][64] and Z [B][H][Kc][64] complex, so that every producer writes and every
+// consumer reads 512-byte channel rows; the spectrum of one (sample, column) stays in shared memory
+// through the whole mid kernel.  All three start their successor early (programmatic dependent
+// launch) and load their constant operands before they wait for their predecessor.
+#include "tc_afno.cuh"
+#include "tc_common.cuh"
+
+namespace dlwp {
+
+namespace {
+constexpr int kC = kAfnoE;   // 64 channels: one thread per channel and quarter of the outputs
+
+// LayerNorm of the W tokens of one grid row (warp per token, two passes like torch), result (+ x when
+// `plus_x`) to shared memory [W][64]
+__device__ __forceinline__ void row_layernorm(const float* __restrict__ xrow, float* sy, int W, const float* __restrict__ gamma,
+                                              const float* __restrict__ beta, float eps, bool plus_x) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float2 g = reinterpret_cast<const float2*>(gamma)[lane], be = reinterpret_cast<const float2*>(beta)[lane];
+  for (int w = warp; w < W; w += 8) {
+    const float2 v = reinterpret_cast<const float2*>(xrow + (size_t)w * kC)[lane];
+    float s = v.x + v.y;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s * (1.0f / kC);
+    const float d0 = v.x - mean, d1 = v.y - mean;
+    float q = d0 * d0 + d1 * d1;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    const float rstd = rsqrtf(q * (1.0f / kC) + eps);
+    float2 y = make_float2(d0 * rstd * g.x + be.x, d1 * rstd * g.y + be.y);
+    if (plus_x) {
+      y.x += v.x;
+      y.y += v.y;
+    }
+    reinterpret_cast<float2*>(sy + (size_t)w * kC)[lane] = y;
+  }
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+template <int NK>   // retained columns per thread: kx = kg + 4 j
+__global__ void __launch_bounds__(256) afno_fwd_kernel(const AfnoFwdArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  tc::pdl_launch_dependents();
+  float* sy = reinterpret_cast<float*>(smem_raw);                       // [W][64]
+  float2* sF = reinterpret_cast<float2*>(smem_raw + (size_t)a.W * kC * 4);   // [4 * NK][W]
+  const int tid = threadIdx.x, c = tid & 63, kg = tid >> 6;
+  for (int i = tid; i < 4 * NK * a.W; i += 256) sF[i] = i < a.Kc * a.W ? a.Fw[i] : make_float2(0.f, 0.f);
+  tc::pdl_wait();
+  const int bh = blockIdx.x, b = bh / a.H, h = bh - b * a.H;
+  row_layernorm(a.x + (size_t)bh * a.W * kC, sy, a.W, a.gamma, a.beta, a.eps, false);
+  __syncthreads();
+  float2 acc[NK];
+#pragma unroll
+  for (int j = 0; j < NK; ++j) acc[j] = make_float2(0.f, 0.f);
+#pragma unroll 4
+  for (int w = 0; w < a.W; ++w) {
+    const float y = sy[w * kC + c];
+#pragma unroll
+    for (int j = 0; j < NK; ++j) {
+      const float2 f = sF[(kg + 4 * j) * a.W + w];
+      acc[j].x = fmaf(f.x, y, acc[j].x);
+      acc[j].y = fmaf(f.y, y, acc[j].y);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NK; ++j) {
+    const int kx = kg + 4 * j;
+    if (kx < a.Kc) a.A[(((size_t)b * a.Kc + kx) * a.H + h) * kC + c] = acc[j];
+  }
+}
+
+int launch_afno_fwd(const AfnoFwdArgs& a, cudaStream_t st) {
+  DLWP_REQUIRE(a.B > 0 && a.H > 0 && a.W > 0 && a.W <= 64 && a.Kc > 0 && a.Kc <= 36, "afno_fwd_kernel: unsupported shape");
+  const int nk = ceil_div(a.Kc, 4);
+  const dim3 grid((unsigned)(a.B * a.H)), block(256);
+  if (nk <= 3) {
+    DLWP_CUDA(launch_pdl(afno_fwd_kernel<3>, grid, block, (size_t)a.W * kC * 4 + (size_t)12 * a.W * 8, st, a));
+  } else if (nk <= 5) {
+    DLWP_CUDA(launch_pdl(afno_fwd_kernel<5>, grid, block, (size_t)a.W * kC * 4 + (size_t)20 * a.W * 8, st, a));
+  } else {
+    DLWP_CUDA(launch_pdl(afno_fwd_kernel<9>, grid, block, (size_t)a.W * kC * 4 + (size_t)36 * a.W * 8, st, a));
+  }
+  DLWP_LAUNCHED("afno_fwd_kernel");
+  return DLWP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+namespace {
+__device__ __forceinline__ void cfma(float2& acc, float2 f, float2 v) {   // acc += f * v (complex)
+  acc.x = fmaf(f.x, v.x, acc.x);
+  acc.x = fmaf(-f.y, v.y, acc.x);
+  acc.y = fmaf(f.x, v.y, acc.y);
+  acc.y = fmaf(f.y, v.x, acc.y);
+}
+
+// one layer of the block-diagonal complex MLP on the modes r = rg + 4 m of this CTA's column:
+// out[r][k * BS + j] = act(sum_i in[r][k * BS + i] * w[k][i][j] + b[k][j]); the thread's BS complex
+// weights live in registers.  w [2, nb, BS, BS], b [2, nb, BS] (planes: real, imaginary)
+template <int BS, bool RELU>
+__device__ __forceinline__ void block_layer(const float2* in, float2* out, const float* __restrict__ w, const float* __restrict__ bias,
+                                            int R, float lambda) {
+  constexpr int nb = kC / BS;
+  const int kj = threadIdx.x & 63, rg = threadIdx.x >> 6, k = kj / BS, j = kj - k * BS;
+  float2 wv[BS];
+#pragma unroll
+  for (int i = 0; i < BS; ++i)
+    wv[i] = make_float2(w[(k * BS + i) * BS + j], w[((nb + k) * BS + i) * BS + j]);
+  const float2 bv = make_float2(bias[k * BS + j], bias[(nb + k) * BS + j]);
+  float2 acc[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) acc[m] = bv;
+#pragma unroll
+  for (int i = 0; i < BS; ++i)
+#pragma unroll
+    for (int m = 0; m < 8; ++m) cfma(acc[m], wv[i], in[(rg + 4 * m) * kC + k * BS + i]);
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int r = rg + 4 * m;
+    if (r < R)
+      out[r * kC + kj] = RELU ? make_float2(fmaxf(acc[m].x, 0.f), fmaxf(acc[m].y, 0.f))
+                              : make_float2(softshrink(acc[m].x, lambda), softshrink(acc[m].y, lambda));
+  }
+}
+constexpr int kMidSmem = 2 * 32 * kC * 8 + 2 * 32 * 32 * 8;   // two [32][64] complex buffers + Fh + Gh
+}  // namespace
+
+template <int BS>
+__global__ void __launch_bounds__(256) afno_mid_kernel(const AfnoMidArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  tc::pdl_launch_dependents();
+  float2* bufA = reinterpret_cast<float2*>(smem_raw);     // [32][64]
+  float2* bufB = bufA + 32 * kC;
+  float2* sFh = bufB + 32 * kC;                           // [32][H] (rows >= R are zero)
+  float2* sGh = sFh + 32 * 32;                            // [32][R] (rows >= H are zero)
+  const int tid = threadIdx.x, c = tid & 63, g4 = tid >> 6;
+  const int H = a.H, R = a.R;
+  for (int i = tid; i < 32 * H; i += 256) sFh[i] = i < R * H ? a.Fh[i] : make_float2(0.f, 0.f);
+  for (int i = tid; i < 32 * R; i += 256) sGh[i] = i < H * R ? a.Gh[i] : make_float2(0.f, 0.f);
+  for (int i = tid; i < 32 * kC; i += 256) bufB[i] = make_float2(0.f, 0.f);   // modes >= R read as zero in the MLP
+  tc::pdl_wait();
+  const int bk = blockIdx.x, b = bk / a.Kc, kx = bk - b * a.Kc;
+  {   // the column's spectrum after the W-DFT: H x 64 complex, contiguous
+    const float4* src = reinterpret_cast<const float4*>(a.A + (size_t)bk * H * kC);
+    float4* dst = reinterpret_cast<float4*>(bufA);
+    for (int i = tid; i < H * kC / 2; i += 256) dst[i] = src[i];
+  }
+  __syncthreads();
+  {   // H-DFT: X[r][c] = sum_h Fh[r][h] A[h][c]
+    float2 acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = make_float2(0.f, 0.f);
+#pragma unroll 2
+    for (int h = 0; h < H; ++h) {
+      const float2 v = bufA[h * kC + c];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) cfma(acc[j], sFh[(g4 + 4 * j) * H + h], v);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (g4 + 4 * j < R) bufB[(g4 + 4 * j) * kC + c] = acc[j];
+  }
+  __syncthreads();
+  block_layer<BS, true>(bufB, bufA, a.w1, a.b1, R, 0.f);
+  __syncthreads();
+  block_layer<BS, false>(bufA, bufB, a.w2, a.b2, R, a.lambda);
+  __syncthreads();
+  {   // inverse H-DFT: Z[h][c] = sum_r Gh[h][r] Y[r][c]
+    float2 acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = make_float2(0.f, 0.f);
+#pragma unroll 2
+    for (int r = 0; r < R; ++r) {
+      const float2 v = bufB[r * kC + c];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) cfma(acc[j], sGh[(g4 + 4 * j) * R + r], v);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int h = g4 + 4 * j;
+      if (h < H) a.Z[(((size_t)b * H + h) * a.Kc + kx) * kC + c] = acc[j];
+    }
+  }
+}
+
+int launch_afno_mid(const AfnoMidArgs& a, cudaStream_t st) {
+  DLWP_REQUIRE(a.B > 0 && a.H > 0 && a.H <= 32 && a.R > 0 && a.R <= 32 && a.Kc > 0, "afno_mid_kernel: unsupported shape");
+  DLWP_REQUIRE(a.bs == 8 || a.bs == 16, "afno_mid_kernel: block size %d", a.bs);
+  static bool attr = false;
+  if (!attr) {
+    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMidSmem));
+    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMidSmem));
+    attr = true;
+  }
+  const dim3 grid((unsigned)(a.B * a.Kc)), block(256);
+  if (a.bs == 8) DLWP_CUDA(launch_pdl(afno_mid_kernel<8>, grid, block, (size_t)kMidSmem, st, a));
+  else DLWP_CUDA(launch_pdl(afno_mid_kernel<16>, grid, block, (size_t)kMidSmem, st, a));
+  DLWP_LAUNCHED("afno_mid_kernel");
+  return DLWP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int NW>   // pixels per thread: w = wg + 4 j
+__global__ void __launch_bounds__(256) afno_inv_kernel(const AfnoInvArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  tc::pdl_launch_dependents();
+  float* sy = reinterpret_cast<float*>(smem_raw);                            // [4 * NW][64]: LayerNorm(x) + x
+  float2* sG = reinterpret_cast<float2*>(smem_raw + (size_t)4 * NW * kC * 4);    // [4 * NW][Kc]
+  float2* sZ = sG + 4 * NW * a.Kc;                                            // [Kc][64]
+  const int tid = threadIdx.x, c = tid & 63, wg = tid >> 6;
+  for (int i = tid; i < 4 * NW * a.Kc; i += 256) sG[i] = i < a.W * a.Kc ? a.Gw[i] : make_float2(0.f, 0.f);
+  tc::pdl_wait();
+  const int bh = blockIdx.x;
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.Z + (size_t)bh * a.Kc * kC);
+    float4* dst = reinterpret_cast<float4*>(sZ);
+    for (int i = tid; i < a.Kc * kC / 2; i += 256) dst[i] = src[i];
+  }
+  row_layernorm(a.x + (size_t)bh * a.W * kC, sy, a.W, a.gamma, a.beta, a.eps, true);
+  __syncthreads();
+  float acc[NW];
+#pragma unroll
+  for (int j = 0; j < NW; ++j) acc[j] = 0.f;
+  for (int kx = 0; kx < a.Kc; ++kx) {
+    const float2 z = sZ[kx * kC + c];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      const float2 g = sG[(wg + 4 * j) * a.Kc + kx];
+      acc[j] = fmaf(g.x, z.x, acc[j]);
+      acc[j] = fmaf(-g.y, z.y, acc[j]);
+    }
+  }
+  float* orow = a.out + (size_t)bh * a.W * kC;
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const int w = wg + 4 * j;
+    if (w < a.W) orow[w * kC + c] = acc[j] + sy[w * kC + c];
+  }
+}
+
+int launch_afno_inv(const AfnoInvArgs& a, cudaStream_t st) {
+  DLWP_REQUIRE(a.B > 0 && a.H > 0 && a.W > 0 && a.W <= 64 && a.Kc > 0 && a.Kc <= 36, "afno_inv_kernel: unsupported shape");
+  const dim3 grid((unsigned)(a.B * a.H)), block(256);
+  const int nw = a.W <= 32 ? 8 : 16;
+  const size_t smem = (size_t)4 * nw * kC * 4 + (size_t)4 * nw * a.Kc * 8 + (size_t)a.Kc * kC * 8;
+  static bool attr = false;
+  if (!attr) {
+    DLWP_CUDA(cudaFuncSetAttribute(afno_inv_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    DLWP_CUDA(cudaFuncSetAttribute(afno_inv_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    attr = true;
+  }
+  DLWP_REQUIRE(smem <= 64 * 1024, "afno_inv_kernel: shared memory");
+  if (nw == 8) DLWP_CUDA(launch_pdl(afno_inv_kernel<8>, grid, block, smem, st, a));
+  else DLWP_CUDA(launch_pdl(afno_inv_kernel<16>, grid, block, smem, st, a));
+  DLWP_LAUNCHED("afno_inv_kernel");
+  return DLWP_OK;
+}
+
+}  // namespace dlwp

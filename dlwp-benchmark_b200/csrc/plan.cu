@@ -444,8 +444,12 @@ static int backbone_afno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st)
     DLWP_TRY(need(p, idx("blocks.", i, ".norm2.bias"), E, &be2));
     // x = filter(norm1(x)) + x : AFNO2D adds its own input back (:127) and Block adds the
     // pre-norm residual again (double_skip, :185-187)
-    DLWP_TRY(launch_layernorm(t, u, g1, be1, P, E, d.layernorm_eps, st));
-    DLWP_TRY(spectral_layer(p, u, t2, nullptr, i, u, t, nullptr, 0, B, st));
+    if (p->atc_spec) {
+      DLWP_TRY(atc_block_filter(p, i, t, t2, B, st));
+    } else {
+      DLWP_TRY(launch_layernorm(t, u, g1, be1, P, E, d.layernorm_eps, st));
+      DLWP_TRY(spectral_layer(p, u, t2, nullptr, i, u, t, nullptr, 0, B, st));
+    }
     // x = mlp(norm2(x)) + x
     if (p->atc) {
       DLWP_TRY(atc_block_mlp(p, i, t2, t, P, st));

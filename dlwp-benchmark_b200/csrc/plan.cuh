@@ -81,6 +81,7 @@ struct dlwp_plan {
 
   // tensor-core AFNO kernels (tc_afno.cuh): precision == DLWP_PREC_FP32_TC, embed_dim 64, mlp hidden 256
   bool atc = false;
+  bool atc_spec = false;                                // the fused token-mixer kernels (afno_fused.cu) cover the grid / modes too
   std::vector<uint8_t*> atc_W1, atc_W2;                 // per block: fc1 * diag(norm2.weight), fc2 / 2 operand images
   std::vector<float*> atc_b1;                           // per block: fc1.bias + fc1 * norm2.bias
 
@@ -105,6 +106,7 @@ int plan_tcw_commit(dlwp_plan* p, cudaStream_t st);
 int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
 int plan_atc_build(dlwp_plan* p);                              // tc_afno_plan.cu
 int plan_atc_commit(dlwp_plan* p, cudaStream_t st);
+int atc_block_filter(dlwp_plan* p, int block, const float* x, float* out, int B, cudaStream_t st);
 int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st);
 int spectral_mid_fno(dlwp_plan* p, const float2* wm, int B, cudaStream_t st);
 int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);

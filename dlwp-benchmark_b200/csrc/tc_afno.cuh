@@ -28,4 +28,34 @@ struct AfnoMlpArgs {
 };
 int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st);
 
+// ---- fused fp32 kernels of the AFNO2D token mixer (afno_fused.cu) -------------------------------
+struct AfnoFwdArgs {
+  const float* x;         // [B, H, W, 64] block input
+  float2* A;              // [B, Kc, H, 64] W-DFT of LayerNorm(x) on the retained columns
+  const float2* Fw;       // [Kc, W]
+  const float *gamma, *beta;
+  float eps;
+  int B, H, W, Kc;
+};
+struct AfnoMidArgs {
+  const float2* A;        // [B, Kc, H, 64]
+  float2* Z;              // [B, H, Kc, 64] after H-DFT, block MLP, inverse H-DFT
+  const float2 *Fh, *Gh;  // [R, H], [H, R]
+  const float *w1, *b1, *w2, *b2;   // filter weights, reference layout (fourcastnet.py:73-76), hidden_size_factor 1
+  float lambda;
+  int B, H, R, Kc, bs;
+};
+struct AfnoInvArgs {
+  const float2* Z;        // [B, H, Kc, 64]
+  const float* x;         // block input (the residual; LayerNorm(x) is recomputed)
+  float* out;             // [B, H, W, 64] = Re(Gw Z) + LayerNorm(x) + x
+  const float2* Gw;       // [W, Kc]
+  const float *gamma, *beta;
+  float eps;
+  int B, H, W, Kc;
+};
+int launch_afno_fwd(const AfnoFwdArgs& a, cudaStream_t st);
+int launch_afno_mid(const AfnoMidArgs& a, cudaStream_t st);
+int launch_afno_inv(const AfnoInvArgs& a, cudaStream_t st);
+
 }  // namespace dlwp

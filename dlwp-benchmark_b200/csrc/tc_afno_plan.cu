@@ -25,6 +25,9 @@ int plan_atc_build(dlwp_plan* p) {
     DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_b1[i], (size_t)kAfnoHid * sizeof(float)));
   }
   p->atc = true;
+  const int bs = d.embed_dim / d.num_blocks;
+  p->atc_spec = p->gw <= 64 && p->gh <= 32 && d.n_rows >= 1 && d.n_rows <= 32 && d.n_cols >= 1 && d.n_cols <= 36 &&
+                d.hidden_size_factor == 1 && (bs == 8 || bs == 16);
   return DLWP_OK;
 }
 
@@ -66,6 +69,28 @@ int plan_atc_commit(dlwp_plan* p, cudaStream_t st) {
     DLWP_CUDA(cudaMemcpy(p->atc_W2[i], img.data(), img.size(), cudaMemcpyHostToDevice));
   }
   return DLWP_OK;
+}
+
+// out = filter(norm1(x)) + norm1(x) + x   (fourcastnet.py:176-187 with AFNO2D.forward :78-127)
+int atc_block_filter(dlwp_plan* p, int block, const float* x, float* out, int B, cudaStream_t st) {
+  const dlwp_model_desc& d = p->d;
+  const int nb = d.num_blocks, bs = kAfnoE / nb;
+  const float *g, *be;
+  DLWP_TRY(plan_need(p, bname(block, ".norm1.weight"), kAfnoE, &g));
+  DLWP_TRY(plan_need(p, bname(block, ".norm1.bias"), kAfnoE, &be));
+  AfnoFwdArgs fa{x, p->specA, p->Fw, g, be, d.layernorm_eps, B, p->gh, p->gw, d.n_cols};
+  DLWP_TRY(launch_afno_fwd(fa, st));
+  AfnoMidArgs ma{};
+  ma.A = p->specA; ma.Z = p->specZ; ma.Fh = p->Fh; ma.Gh = p->Gh;
+  DLWP_TRY(plan_need(p, bname(block, ".filter.w1"), (int64_t)2 * nb * bs * bs, &ma.w1));
+  DLWP_TRY(plan_need(p, bname(block, ".filter.b1"), (int64_t)2 * nb * bs, &ma.b1));
+  DLWP_TRY(plan_need(p, bname(block, ".filter.w2"), (int64_t)2 * nb * bs * bs, &ma.w2));
+  DLWP_TRY(plan_need(p, bname(block, ".filter.b2"), (int64_t)2 * nb * bs, &ma.b2));
+  ma.lambda = d.sparsity_threshold;
+  ma.B = B; ma.H = p->gh; ma.R = d.n_rows; ma.Kc = d.n_cols; ma.bs = bs;
+  DLWP_TRY(launch_afno_mid(ma, st));
+  AfnoInvArgs ia{p->specZ, x, out, p->Gw, g, be, d.layernorm_eps, B, p->gh, p->gw, d.n_cols};
+  return launch_afno_inv(ia, st);
 }
 
 // x = x + mlp(norm2(x))   (fourcastnet.py:189-192)

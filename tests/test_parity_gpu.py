@@ -228,16 +228,16 @@ def test_afno_paper_size_matches_oracle(pkg):
     assert max_rel(got, want) < TOL_STEP
 
 
-@pytest.mark.parametrize("B", [3, 24])
-def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B):
+@pytest.mark.parametrize("B,nb,frac,H,W", [(3, 4, 1.0, 32, 64), (24, 4, 1.0, 32, 64), (5, 8, 0.5, 16, 32), (2, 4, 0.7, 24, 48)])
+def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B, nb, frac, H, W):
     """configs/model/fourcastnet.yaml shapes (embed_dim 64, mlp_ratio 4): the tcgen05 AFNO kernels of the
     default precision mode against the oracle and against the fp32 FMA kernel set; B = 24 gives every
     persistent CTA several 128-token tiles."""
     from oracle import afno as oafno
     native = pkg.native
-    kw = dict(img_height=32, img_width=64, patch_size=[1, 1], constant_channels=4, prescribed_channels=1,
-              prognostic_channels=3, embed_dim=64, depth=4, num_blocks=4, mlp_ratio=4.0, context_size=1,
-              use_pos_embed=True)
+    kw = dict(img_height=H, img_width=W, patch_size=[1, 1], constant_channels=4, prescribed_channels=1,
+              prognostic_channels=3, embed_dim=64, depth=4, num_blocks=nb, mlp_ratio=4.0, context_size=1,
+              use_pos_embed=True, hard_thresholding_fraction=frac)
     torch.manual_seed(11)
     ref = oafno.AFNONet(**kw).eval()
     with torch.no_grad():
@@ -246,7 +246,7 @@ def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B):
                 p.mul_(6.0)
             elif n.endswith("bias") or "norm" in n:
                 p.add_(0.3 * torch.randn_like(p))
-    const, presc, prog = synthetic(B, 4, 4, 1, 3, 32, 64, seed=77)
+    const, presc, prog = synthetic(B, 4, 4, 1, 3, H, W, seed=77)
     with torch.no_grad():
         want = ref(constants=const, prescribed=presc, prognostic=prog)
     outs = {}
