@@ -19,14 +19,13 @@ namespace dlwp {
 namespace {
 constexpr int kC = kAfnoE;   // 64 channels: one thread per channel and quarter of the outputs
 
-// LayerNorm of the W tokens of one grid row (warp per token, two passes like torch), result (+ x when
-// `plus_x`) to shared memory [W][64]
-__device__ __forceinline__ void row_layernorm(const float* __restrict__ xrow, float* sy, int W, const float* __restrict__ gamma,
-                                              const float* __restrict__ beta, float eps, bool plus_x) {
+// LayerNorm of the W tokens of one grid row held in shared memory [W][64], in place (warp per token, two
+// passes like torch); `plus_x` leaves LayerNorm(x) + x.  g / be: this lane's two channels of the affine.
+__device__ __forceinline__ void row_layernorm(float* sy, int W, float2 g, float2 be, float eps, bool plus_x) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const float2 g = reinterpret_cast<const float2*>(gamma)[lane], be = reinterpret_cast<const float2*>(beta)[lane];
   for (int w = warp; w < W; w += 8) {
-    const float2 v = reinterpret_cast<const float2*>(xrow + (size_t)w * kC)[lane];
+    float2* p = reinterpret_cast<float2*>(sy + (size_t)w * kC) + lane;
+    const float2 v = *p;
     float s = v.x + v.y;
 #pragma unroll
     for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -41,7 +40,18 @@ __device__ __forceinline__ void row_layernorm(const float* __restrict__ xrow, fl
       y.x += v.x;
       y.y += v.y;
     }
-    reinterpret_cast<float2*>(sy + (size_t)w * kC)[lane] = y;
+    *p = y;
+  }
+}
+
+// two mbarriers per CTA: [0] constant operands (requested before the predecessor kernel has finished),
+// [1] what the predecessor wrote.  Every operand arrives by bulk async copy: one request, no per-thread
+// load latency chains.
+__device__ __forceinline__ void init_bars(uint64_t* bar) {
+  if (threadIdx.x == 0) {
+    tc::mbar_init(&bar[0], 1);
+    tc::mbar_init(&bar[1], 1);
+    tc::fence_mbar_init();
   }
 }
 }  // namespace
@@ -49,15 +59,29 @@ __device__ __forceinline__ void row_layernorm(const float* __restrict__ xrow, fl
 // ---------------------------------------------------------------------------------------------
 template <int NK>   // retained columns per thread: kx = kg + 4 j
 __global__ void __launch_bounds__(256) afno_fwd_kernel(const AfnoFwdArgs a) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint64_t bar[2];
   tc::pdl_launch_dependents();
   float* sy = reinterpret_cast<float*>(smem_raw);                       // [W][64]
   float2* sF = reinterpret_cast<float2*>(smem_raw + (size_t)a.W * kC * 4);   // [4 * NK][W]
-  const int tid = threadIdx.x, c = tid & 63, kg = tid >> 6;
-  for (int i = tid; i < 4 * NK * a.W; i += 256) sF[i] = i < a.Kc * a.W ? a.Fw[i] : make_float2(0.f, 0.f);
-  tc::pdl_wait();
+  const int tid = threadIdx.x, c = tid & 63, kg = tid >> 6, lane = tid & 31;
+  init_bars(bar);
+  for (int i = a.Kc * a.W + tid; i < 4 * NK * a.W; i += 256) sF[i] = make_float2(0.f, 0.f);
+  const float2 g = reinterpret_cast<const float2*>(a.gamma)[lane], be = reinterpret_cast<const float2*>(a.beta)[lane];
+  __syncthreads();
   const int bh = blockIdx.x, b = bh / a.H, h = bh - b * a.H;
-  row_layernorm(a.x + (size_t)bh * a.W * kC, sy, a.W, a.gamma, a.beta, a.eps, false);
+  if (tid == 0) {
+    tc::mbar_arrive_expect_tx(&bar[0], (uint32_t)(a.Kc * a.W * 8));
+    tc::bulk_g2s(sF, a.Fw, (uint32_t)(a.Kc * a.W * 8), &bar[0]);
+  }
+  tc::pdl_wait();
+  if (tid == 0) {
+    tc::mbar_arrive_expect_tx(&bar[1], (uint32_t)(a.W * kC * 4));
+    tc::bulk_g2s(sy, a.x + (size_t)bh * a.W * kC, (uint32_t)(a.W * kC * 4), &bar[1]);
+  }
+  tc::mbar_wait(&bar[1], 0);
+  row_layernorm(sy, a.W, g, be, a.eps, false);
+  tc::mbar_wait(&bar[0], 0);
   __syncthreads();
   float2 acc[NK];
 #pragma unroll
@@ -105,9 +129,9 @@ __device__ __forceinline__ void cfma(float2& acc, float2 f, float2 v) {   // acc
 
 // one layer of the block-diagonal complex MLP on the modes r = rg + 4 m of this CTA's column:
 // out[r][k * BS + j] = act(sum_i in[r][k * BS + i] * w[k][i][j] + b[k][j]); the thread's BS complex
-// weights live in registers.  w [2, nb, BS, BS], b [2, nb, BS] (planes: real, imaginary)
+// weights move from shared memory to registers once.  w [2, nb, BS, BS], b [2, nb, BS] (planes: real, imaginary)
 template <int BS, bool RELU>
-__device__ __forceinline__ void block_layer(const float2* in, float2* out, const float* __restrict__ w, const float* __restrict__ bias,
+__device__ __forceinline__ void block_layer(const float2* in, float2* out, const float* w, const float* bias,
                                             int R, float lambda) {
   constexpr int nb = kC / BS;
   const int kj = threadIdx.x & 63, rg = threadIdx.x >> 6, k = kj / BS, j = kj - k * BS;
@@ -131,30 +155,47 @@ __device__ __forceinline__ void block_layer(const float2* in, float2* out, const
                               : make_float2(softshrink(acc[m].x, lambda), softshrink(acc[m].y, lambda));
   }
 }
-constexpr int kMidSmem = 2 * 32 * kC * 8 + 2 * 32 * 32 * 8;   // two [32][64] complex buffers + Fh + Gh
+// two [32][64] complex buffers + Fh + Gh + the filter weights and biases
+constexpr int mid_smem(int bs) { return 2 * 32 * kC * 8 + 2 * 32 * 32 * 8 + 2 * (2 * kC * bs * 4) + 2 * (2 * kC * 4); }
 }  // namespace
 
 template <int BS>
 __global__ void __launch_bounds__(256) afno_mid_kernel(const AfnoMidArgs a) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint64_t bar[2];
   tc::pdl_launch_dependents();
   float2* bufA = reinterpret_cast<float2*>(smem_raw);     // [32][64]
   float2* bufB = bufA + 32 * kC;
   float2* sFh = bufB + 32 * kC;                           // [32][H] (rows >= R are zero)
   float2* sGh = sFh + 32 * 32;                            // [32][R] (rows >= H are zero)
+  float* sW1 = reinterpret_cast<float*>(sGh + 32 * 32);   // [2, nb, BS, BS]
+  float* sW2 = sW1 + 2 * kC * BS;
+  float* sB1 = sW2 + 2 * kC * BS;                         // [2, nb, BS]
+  float* sB2 = sB1 + 2 * kC;
   const int tid = threadIdx.x, c = tid & 63, g4 = tid >> 6;
   const int H = a.H, R = a.R;
-  for (int i = tid; i < 32 * H; i += 256) sFh[i] = i < R * H ? a.Fh[i] : make_float2(0.f, 0.f);
-  for (int i = tid; i < 32 * R; i += 256) sGh[i] = i < H * R ? a.Gh[i] : make_float2(0.f, 0.f);
-  for (int i = tid; i < 32 * kC; i += 256) bufB[i] = make_float2(0.f, 0.f);   // modes >= R read as zero in the MLP
-  tc::pdl_wait();
-  const int bk = blockIdx.x, b = bk / a.Kc, kx = bk - b * a.Kc;
-  {   // the column's spectrum after the W-DFT: H x 64 complex, contiguous
-    const float4* src = reinterpret_cast<const float4*>(a.A + (size_t)bk * H * kC);
-    float4* dst = reinterpret_cast<float4*>(bufA);
-    for (int i = tid; i < H * kC / 2; i += 256) dst[i] = src[i];
-  }
+  init_bars(bar);
+  for (int i = R * H + tid; i < 32 * H; i += 256) sFh[i] = make_float2(0.f, 0.f);
+  for (int i = H * R + tid; i < 32 * R; i += 256) sGh[i] = make_float2(0.f, 0.f);
   __syncthreads();
+  const int bk = blockIdx.x, b = bk / a.Kc, kx = bk - b * a.Kc;
+  if (tid == 0) {
+    const uint32_t fb = (uint32_t)(R * H * 8), wb = 2u * kC * BS * 4u, bb = 2u * kC * 4u;
+    tc::mbar_arrive_expect_tx(&bar[0], 2 * fb + 2 * wb + 2 * bb);
+    tc::bulk_g2s(sFh, a.Fh, fb, &bar[0]);
+    tc::bulk_g2s(sGh, a.Gh, fb, &bar[0]);
+    tc::bulk_g2s(sW1, a.w1, wb, &bar[0]);
+    tc::bulk_g2s(sW2, a.w2, wb, &bar[0]);
+    tc::bulk_g2s(sB1, a.b1, bb, &bar[0]);
+    tc::bulk_g2s(sB2, a.b2, bb, &bar[0]);
+  }
+  tc::pdl_wait();
+  if (tid == 0) {   // the column's spectrum after the W-DFT: H x 64 complex, contiguous
+    tc::mbar_arrive_expect_tx(&bar[1], (uint32_t)(H * kC * 8));
+    tc::bulk_g2s(bufA, a.A + (size_t)bk * H * kC, (uint32_t)(H * kC * 8), &bar[1]);
+  }
+  tc::mbar_wait(&bar[0], 0);
+  tc::mbar_wait(&bar[1], 0);
   {   // H-DFT: X[r][c] = sum_h Fh[r][h] A[h][c]
     float2 acc[8];
 #pragma unroll
@@ -170,9 +211,9 @@ __global__ void __launch_bounds__(256) afno_mid_kernel(const AfnoMidArgs a) {
       if (g4 + 4 * j < R) bufB[(g4 + 4 * j) * kC + c] = acc[j];
   }
   __syncthreads();
-  block_layer<BS, true>(bufB, bufA, a.w1, a.b1, R, 0.f);
+  block_layer<BS, true>(bufB, bufA, sW1, sB1, R, 0.f);
   __syncthreads();
-  block_layer<BS, false>(bufA, bufB, a.w2, a.b2, R, a.lambda);
+  block_layer<BS, false>(bufA, bufB, sW2, sB2, R, a.lambda);
   __syncthreads();
   {   // inverse H-DFT: Z[h][c] = sum_r Gh[h][r] Y[r][c]
     float2 acc[8];
@@ -197,13 +238,13 @@ int launch_afno_mid(const AfnoMidArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.bs == 8 || a.bs == 16, "afno_mid_kernel: block size %d", a.bs);
   static bool attr = false;
   if (!attr) {
-    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMidSmem));
-    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMidSmem));
+    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, mid_smem(8)));
+    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, mid_smem(16)));
     attr = true;
   }
   const dim3 grid((unsigned)(a.B * a.Kc)), block(256);
-  if (a.bs == 8) DLWP_CUDA(launch_pdl(afno_mid_kernel<8>, grid, block, (size_t)kMidSmem, st, a));
-  else DLWP_CUDA(launch_pdl(afno_mid_kernel<16>, grid, block, (size_t)kMidSmem, st, a));
+  if (a.bs == 8) DLWP_CUDA(launch_pdl(afno_mid_kernel<8>, grid, block, (size_t)mid_smem(8), st, a));
+  else DLWP_CUDA(launch_pdl(afno_mid_kernel<16>, grid, block, (size_t)mid_smem(16), st, a));
   DLWP_LAUNCHED("afno_mid_kernel");
   return DLWP_OK;
 }
@@ -211,21 +252,31 @@ int launch_afno_mid(const AfnoMidArgs& a, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------
 template <int NW>   // pixels per thread: w = wg + 4 j
 __global__ void __launch_bounds__(256) afno_inv_kernel(const AfnoInvArgs a) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint64_t bar[2];
   tc::pdl_launch_dependents();
   float* sy = reinterpret_cast<float*>(smem_raw);                            // [4 * NW][64]: LayerNorm(x) + x
   float2* sG = reinterpret_cast<float2*>(smem_raw + (size_t)4 * NW * kC * 4);    // [4 * NW][Kc]
   float2* sZ = sG + 4 * NW * a.Kc;                                            // [Kc][64]
-  const int tid = threadIdx.x, c = tid & 63, wg = tid >> 6;
-  for (int i = tid; i < 4 * NW * a.Kc; i += 256) sG[i] = i < a.W * a.Kc ? a.Gw[i] : make_float2(0.f, 0.f);
-  tc::pdl_wait();
+  const int tid = threadIdx.x, c = tid & 63, wg = tid >> 6, lane = tid & 31;
+  init_bars(bar);
+  for (int i = a.W * a.Kc + tid; i < 4 * NW * a.Kc; i += 256) sG[i] = make_float2(0.f, 0.f);
+  const float2 g = reinterpret_cast<const float2*>(a.gamma)[lane], be = reinterpret_cast<const float2*>(a.beta)[lane];
+  __syncthreads();
   const int bh = blockIdx.x;
-  {
-    const float4* src = reinterpret_cast<const float4*>(a.Z + (size_t)bh * a.Kc * kC);
-    float4* dst = reinterpret_cast<float4*>(sZ);
-    for (int i = tid; i < a.Kc * kC / 2; i += 256) dst[i] = src[i];
+  if (tid == 0) {
+    tc::mbar_arrive_expect_tx(&bar[0], (uint32_t)(a.W * a.Kc * 8));
+    tc::bulk_g2s(sG, a.Gw, (uint32_t)(a.W * a.Kc * 8), &bar[0]);
   }
-  row_layernorm(a.x + (size_t)bh * a.W * kC, sy, a.W, a.gamma, a.beta, a.eps, true);
+  tc::pdl_wait();
+  if (tid == 0) {
+    tc::mbar_arrive_expect_tx(&bar[1], (uint32_t)(a.Kc * kC * 8 + a.W * kC * 4));
+    tc::bulk_g2s(sZ, a.Z + (size_t)bh * a.Kc * kC, (uint32_t)(a.Kc * kC * 8), &bar[1]);
+    tc::bulk_g2s(sy, a.x + (size_t)bh * a.W * kC, (uint32_t)(a.W * kC * 4), &bar[1]);
+  }
+  tc::mbar_wait(&bar[1], 0);
+  row_layernorm(sy, a.W, g, be, a.eps, true);
+  tc::mbar_wait(&bar[0], 0);
   __syncthreads();
   float acc[NW];
 #pragma unroll

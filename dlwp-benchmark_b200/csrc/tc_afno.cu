@@ -11,17 +11,19 @@ using namespace tc;
 // afno_mlp_kernel: out = x + fc2(GELU(fc1(LN(x))))  on 128-token tiles, persistent, one CTA per SM
 //   warps 0-7 : epilogue group (two threads per token: channel halves)     warp 8 : control warp
 // Both 64 KB weight operands ([hi | lo] split-bf16 images) stay in shared memory for the whole
-// kernel, which leaves room for one worker per CTA: A1 (normalised tokens, 2 x 32 KB) and A2
-// (32-column hidden chunks, 2 x 16 KB) are double-buffered, the hidden accumulator D1 [128 x 64]
-// and the output accumulator D2 [128 x 64] are double-buffered in tensor memory.
+// kernel, which leaves room for one worker per CTA: one A1 buffer (normalised tokens, 32 KB; the
+// next tile's tokens are stored after the last first-layer MMA of this tile has read it, two passes
+// before they are needed) and a ring of four A2 buffers (32-column hidden chunks, 16 KB each), so the
+// epilogue group never waits for the second-layer MMAs of the chunks it has just handed over; the hidden
+// accumulator D1 [128 x 64] and the output accumulator D2 [128 x 64] are double-buffered in tensor memory.
 // LayerNorm: each thread holds half a token (32 channels), computes its mean and centred sum of
 // squares, and the two halves are combined with the pairwise update (exact like two passes).
 // =============================================================================================
 namespace {
 constexpr int kAmEpi = 256, kAmCta = kAmEpi + 32, kAmCtlWarp = kAmEpi / 32;
 struct AmSmem {
-  static constexpr int W1 = 0, W2 = W1 + kAfnoHid * kAfnoE * 4, A1 = W2 + kAfnoE * kAfnoHid * 4, A2 = A1 + 2 * 32768,
-                       Stats = A2 + 2 * kTileBytes, Total = Stats + 2 * 128 * 8;
+  static constexpr int W1 = 0, W2 = W1 + kAfnoHid * kAfnoE * 4, A1 = W2 + kAfnoE * kAfnoHid * 4, A2 = A1 + 32768,
+                       Stats = A2 + 4 * kTileBytes, Total = Stats + 2 * 128 * 8;
   static_assert(Total <= 226 * 1024, "afno_mlp_kernel shared memory");
 };
 }  // namespace
@@ -47,19 +49,19 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
-  if (tid == 0) {
+  if (tid == 0) {   // constant operands: on their way before the predecessor has finished
     mbar_arrive_expect_tx(bar_const, 2u * 65536u);
     bulk_g2s(smem + AmSmem::W1, a.W1img, 65536, bar_const);
     bulk_g2s(smem + AmSmem::W2, a.W2img, 65536, bar_const);
   }
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const int stride = gridDim.x, first = blockIdx.x;
   uint64_t* b = bars;
 
   if (warp == kAmCtlWarp) {
     const uint32_t leader = elect_one();
     MlpIssuer is{b, smem_u32(smem + AmSmem::A1), 32768u, smem_u32(smem + AmSmem::W1), smem_u32(smem + AmSmem::W2),
-                 smem_u32(smem + AmSmem::A2), tmem_s, hid, P, 0u, 0u, 0u, leader};
+                 smem_u32(smem + AmSmem::A2), tmem_s, hid, P, 0u, 0u, 0u, leader, 1u};
     mbar_wait(bar_const, 0);
     if (first < a.ntiles) is.mma1<kAfnoE>(0, 0, 0);
     uint32_t u = 0;
@@ -69,7 +71,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
         const uint32_t gp = u * P + p;
         if (p + 1 < P) is.mma1<kAfnoE>(u, p + 1, gp + 1);
         else if (has_next) is.mma1<kAfnoE>(u + 1, 0, gp + 1);
-        is.mma2<kAfnoE>(u, p);
+        is.mma2<kAfnoE, 4>(u, p);
       }
     }
   } else {
@@ -100,9 +102,8 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       const float mean = 0.5f * (mh + o.x), dm = mh - o.x;
       const float var = (q + o.y + 16.0f * dm * dm) * (1.0f / 64.0f);
       const float rstd = rsqrtf(var + a.eps);
-      const int s2 = u & 1;
-      mbar_wait(&b[MB_A1EMPTY + s2], empty_par(u));
-      uint8_t* d = smem + AmSmem::A1 + s2 * 32768 + (4 * id.half) * 2048 + id.row * 16;
+      mbar_wait(&b[MB_A1EMPTY], (u & 1u) ^ 1u);      // ring of depth 1
+      uint8_t* d = smem + AmSmem::A1 + (4 * id.half) * 2048 + id.row * 16;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {     // 8 channels = one 16-byte unit of the chunk-major image
         uint32_t h[4], l[4];
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
         *reinterpret_cast<uint4*>(d + 16384 + j * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
       }
       fence_async_smem();
-      mbar_arrive(&b[MB_A1FULL + s2]);
+      mbar_arrive(&b[MB_A1FULL]);
     };
 
     float4 nx[8];
@@ -126,10 +127,10 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
     uint32_t u = 0, gp = 0, nc = 0;
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const bool has_next = tile + stride < a.ntiles;
-      if (has_next) gather(tile + stride, nx);      // loads in flight while the first pass is processed
-      epi_mlp_tile(b, id, tmem_lane, P, smem + AmSmem::A2, gp, nc, [&] {
+      if (has_next) gather(tile + stride, nx);      // loads in flight while the first passes are processed
+      epi_mlp_tile<4>(b, id, tmem_lane, P, smem + AmSmem::A2, gp, nc, [&] {
         if (has_next) store_a1(u + 1, nx);
-      }, a.b1);
+      }, a.b1, P - 2);
       // out = x + D2 + b2 on this thread's 32 channels (x is re-read: an L2 hit)
       const size_t off = ((size_t)tile * kTcTile + id.row) * kAfnoE + c0;
       const float4* xr = reinterpret_cast<const float4*>(a.x + off);

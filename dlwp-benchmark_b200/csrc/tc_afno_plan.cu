@@ -27,7 +27,8 @@ int plan_atc_build(dlwp_plan* p) {
   p->atc = true;
   const int bs = d.embed_dim / d.num_blocks;
   p->atc_spec = p->gw <= 64 && p->gh <= 32 && d.n_rows >= 1 && d.n_rows <= 32 && d.n_cols >= 1 && d.n_cols <= 36 &&
-                d.hidden_size_factor == 1 && (bs == 8 || bs == 16);
+                d.hidden_size_factor == 1 && (bs == 8 || bs == 16) &&
+                p->gw % 2 == 0 && (d.n_rows * p->gh) % 2 == 0;   // bulk copies move multiples of 16 bytes
   return DLWP_OK;
 }
 

@@ -53,8 +53,9 @@ __device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1
 
 namespace {
 
-enum { MB_A1FULL = 0, MB_A1EMPTY = 2, MB_D1FULL = 4, MB_D1EMPTY = 6, MB_A2FULL = 8, MB_A2EMPTY = 10, MB_D2FULL = 12,
-       MB_D2EMPTY = 14, MB_XTFULL = 16, MB_D3FULL = 17, MB_YFREE = 18, MB_PER = 19 };
+// (the A2 ring has room for four slots; the FNO kernels use two)
+enum { MB_A1FULL = 0, MB_A1EMPTY = 2, MB_D1FULL = 4, MB_D1EMPTY = 6, MB_A2FULL = 8, MB_A2EMPTY = 12, MB_D2FULL = 16,
+       MB_D2EMPTY = 18, MB_XTFULL = 20, MB_D3FULL = 21, MB_YFREE = 22, MB_PER = 23 };
 
 __device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_count) {
   for (int i = 0; i < 2; ++i) {
@@ -64,6 +65,8 @@ __device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_
     mbar_init(&b[MB_D1EMPTY + i], kEpi);
     mbar_init(&b[MB_A2FULL + i], kEpi);
     mbar_init(&b[MB_A2EMPTY + i], 1);
+    mbar_init(&b[MB_A2FULL + 2 + i], kEpi);
+    mbar_init(&b[MB_A2EMPTY + 2 + i], 1);
     mbar_init(&b[MB_D2FULL + i], 1);
     mbar_init(&b[MB_D2EMPTY + i], kEpi);
   }
@@ -81,12 +84,13 @@ struct MlpIssuer {
   uint32_t nc;         // chunks issued so far
   uint32_t aOnes, aW1x;   // optional bias term of the first GEMM: Ones[128,16] * W1x[hid,16]^T (0 = none)
   uint32_t leader;        // elect_one() of the (converged) control warp
+  uint32_t a1_single;     // 1: one A1 buffer (ring of depth 1) instead of two
 
   template <int K1>
   __device__ __forceinline__ void mma1(uint32_t u, int p, uint32_t gp) {
-    const int db = gp & 1, ub = u & 1;
+    const int db = gp & 1, ub = a1_single ? 0 : (u & 1);
     mbar_wait(&b[MB_D1EMPTY + db], empty_par(gp));
-    if (p == 0) mbar_wait(&b[MB_A1FULL + ub], full_par(u));
+    if (p == 0) mbar_wait(&b[MB_A1FULL + ub], a1_single ? (u & 1u) : full_par(u));
     tc_fence_after();
     const uint32_t idesc = idesc_bf16(128, 64);
     const uint32_t a_lo = 128 * K1 * 2, w_lo = (uint32_t)hid * K1 * 2;
@@ -111,15 +115,15 @@ struct MlpIssuer {
     __syncwarp();
   }
 
-  template <int N2>
+  template <int N2, int NA2 = 2>     // NA2: depth of the A2 ring
   __device__ __forceinline__ void mma2(uint32_t u, int p) {
     const uint32_t idesc = idesc_bf16(128, N2);
     const uint32_t w_lo = aW2 + (uint32_t)N2 * hid * 2;
     const uint32_t d2 = tmem + 128u + (N2 > 32 ? 64u : 32u) * (u & 1);
 #pragma unroll
     for (int j = 0; j < 2; ++j, ++nc) {
-      const int ab = nc & 1;
-      mbar_wait(&b[MB_A2FULL + ab], full_par(nc));
+      const int ab = nc % NA2;
+      mbar_wait(&b[MB_A2FULL + ab], (nc / NA2) & 1u);
       if (p == 0 && j == 0) mbar_wait(&b[MB_D2EMPTY + (u & 1)], empty_par(u));
       tc_fence_after();
       const int hcol0 = p * 64 + 32 * j;
@@ -143,9 +147,11 @@ struct MlpIssuer {
 // turns 16 hidden columns of its pixel per 32-column chunk into split-bf16 operand bytes.
 // `sB1` (optional): the first layer's bias [hid] in shared memory, added here when the first GEMM
 // has no spare K column to carry it.
-template <class Hook>
+// `NA2`: depth of the A2 ring; `hook_pass`: the pass after which the hook runs.
+template <int NA2 = 2, class Hook>
 __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint32_t tmem_lane, int P, uint8_t* sA2,
-                                             uint32_t& gp, uint32_t& nc, Hook after_pass0, const float* sB1 = nullptr) {
+                                             uint32_t& gp, uint32_t& nc, Hook after_pass0, const float* sB1 = nullptr,
+                                             int hook_pass = 0) {
   for (int p = 0; p < P; ++p, ++gp) {
     const int db = gp & 1;
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
@@ -177,8 +183,8 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
 #pragma unroll
         for (int e = 0; e < 8; ++e) split2p(g2[e], h[e], l[e]);
       }
-      const int ab = nc & 1;
-      mbar_wait(&b[MB_A2EMPTY + ab], empty_par(nc));
+      const int ab = nc % NA2;
+      mbar_wait(&b[MB_A2EMPTY + ab], ((nc / NA2) & 1u) ^ 1u);
       uint8_t* dst = sA2 + ab * kTileBytes + id.row * 16 + id.half * 4096;
       *reinterpret_cast<uint4*>(dst) = make_uint4(h[0], h[1], h[2], h[3]);
       *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(h[4], h[5], h[6], h[7]);
@@ -187,7 +193,7 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
       fence_async_smem();
       mbar_arrive(&b[MB_A2FULL + ab]);
     }
-    if (p == 0) after_pass0();
+    if (p == hook_pass) after_pass0();
   }
 }
 
