@@ -85,7 +85,10 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
 #pragma unroll
       for (int j = 0; j < 8; ++j) x[j] = src[j];
     };
-    auto store_a1 = [&](uint32_t u, const float4 (&x)[8]) {
+    auto store_a1 = [&](uint32_t u, float4 (&x)[8]) {
+      // the statistics are computed here, not where the loads were issued (the loads' latency hides behind the passes in between)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) asm volatile("" : "+f"(x[j].x), "+f"(x[j].y), "+f"(x[j].z), "+f"(x[j].w));
       float s = 0.f;
 #pragma unroll
       for (int j = 0; j < 8; ++j) s += (x[j].x + x[j].y) + (x[j].z + x[j].w);
@@ -119,6 +122,9 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       mbar_arrive(&b[MB_A1FULL]);
     };
 
+    float4 b2v[8];      // this thread's 32 output biases
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b2v[j] = __ldg(reinterpret_cast<const float4*>(a.b2 + c0) + j);
     float4 nx[8];
     if (first < a.ntiles) {
       gather(first, nx);
@@ -134,7 +140,6 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       // out = x + D2 + b2 on this thread's 32 channels (x is re-read: an L2 hit)
       const size_t off = ((size_t)tile * kTcTile + id.row) * kAfnoE + c0;
       const float4* xr = reinterpret_cast<const float4*>(a.x + off);
-      const float4* b2 = reinterpret_cast<const float4*>(a.b2 + c0);
       float4 res[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) res[j] = xr[j];
@@ -148,7 +153,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       float4* o = reinterpret_cast<float4*>(a.out + off);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float4 bb = b2[j];
+        const float4 bb = b2v[j];
         o[j] = make_float4(__uint_as_float(r[4 * j]) + bb.x + res[j].x, __uint_as_float(r[4 * j + 1]) + bb.y + res[j].y,
                            __uint_as_float(r[4 * j + 2]) + bb.z + res[j].z, __uint_as_float(r[4 * j + 3]) + bb.w + res[j].w);
       }

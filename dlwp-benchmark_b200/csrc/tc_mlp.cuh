@@ -154,6 +154,13 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
                                              int hook_pass = 0) {
   for (int p = 0; p < P; ++p, ++gp) {
     const int db = gp & 1;
+    float4 bv[2][4];    // this pass's bias values: requested before the wait so that their latency hides behind it
+    if (sB1 != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) bv[j][e] = __ldg(reinterpret_cast<const float4*>(sB1 + p * 64 + 32 * j + 16 * id.half) + e);
+    }
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
     tc_fence_after();
 #pragma unroll
@@ -168,14 +175,12 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
       uint32_t h[8], l[8];
       {
         if (sB1 != nullptr) {
-          const float4* bq = reinterpret_cast<const float4*>(sB1 + p * 64 + 32 * j + 16 * id.half);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const float4 bv = bq[e];
-            r[4 * e] = __float_as_uint(__uint_as_float(r[4 * e]) + bv.x);
-            r[4 * e + 1] = __float_as_uint(__uint_as_float(r[4 * e + 1]) + bv.y);
-            r[4 * e + 2] = __float_as_uint(__uint_as_float(r[4 * e + 2]) + bv.z);
-            r[4 * e + 3] = __float_as_uint(__uint_as_float(r[4 * e + 3]) + bv.w);
+            r[4 * e] = __float_as_uint(__uint_as_float(r[4 * e]) + bv[j][e].x);
+            r[4 * e + 1] = __float_as_uint(__uint_as_float(r[4 * e + 1]) + bv[j][e].y);
+            r[4 * e + 2] = __float_as_uint(__uint_as_float(r[4 * e + 2]) + bv[j][e].z);
+            r[4 * e + 3] = __float_as_uint(__uint_as_float(r[4 * e + 3]) + bv[j][e].w);
           }
         }
         float2 g2[8];             // 2 * gelu: W2's operand image is packed with the factor 1/2
