@@ -57,29 +57,75 @@ __device__ __forceinline__ void init_bars(uint64_t* bar) {
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
-template <int NK>   // retained columns per thread: kx = kg + 4 j
+template <int NK, bool EMBED>   // NK retained columns per thread: kx = kg + 4 j
 __global__ void __launch_bounds__(256) afno_fwd_kernel(const AfnoFwdArgs a) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint64_t bar[2];
   tc::pdl_launch_dependents();
   float* sy = reinterpret_cast<float*>(smem_raw);                       // [W][64]
   float2* sF = reinterpret_cast<float2*>(smem_raw + (size_t)a.W * kC * 4);   // [4 * NK][W]
+  float* sIn = reinterpret_cast<float*>(sF + 4 * NK * a.W);              // EMBED: [Cin][W] input row, then [Cin][64] weights
+  float* sWe = sIn + 16 * 64;
   const int tid = threadIdx.x, c = tid & 63, kg = tid >> 6, lane = tid & 31;
   init_bars(bar);
   for (int i = a.Kc * a.W + tid; i < 4 * NK * a.W; i += 256) sF[i] = make_float2(0.f, 0.f);
   const float2 g = reinterpret_cast<const float2*>(a.gamma)[lane], be = reinterpret_cast<const float2*>(a.beta)[lane];
-  __syncthreads();
   const int bh = blockIdx.x, b = bh / a.H, h = bh - b * a.H;
+  float xe[16];     // EMBED: bias + position embedding of this thread's (token, channel) outputs, w = kg + 4 j
+  if constexpr (EMBED) {
+    for (int i = tid; i < a.Cin * kC; i += 256) {     // transposed: one channel row per input channel
+      const int k = i >> 6, cc = i & 63;
+      sWe[i] = a.We[cc * a.Cin + k];
+    }
+    const float bias = a.be[c];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int w = kg + 4 * j;
+      xe[j] = bias + ((a.pos != nullptr && w < a.W) ? a.pos[((size_t)h * a.W + w) * kC + c] : 0.f);
+    }
+  }
+  __syncthreads();
   if (tid == 0) {
     tc::mbar_arrive_expect_tx(&bar[0], (uint32_t)(a.Kc * a.W * 8));
     tc::bulk_g2s(sF, a.Fw, (uint32_t)(a.Kc * a.W * 8), &bar[0]);
   }
   tc::pdl_wait();
-  if (tid == 0) {
-    tc::mbar_arrive_expect_tx(&bar[1], (uint32_t)(a.W * kC * 4));
-    tc::bulk_g2s(sy, a.x + (size_t)bh * a.W * kC, (uint32_t)(a.W * kC * 4), &bar[1]);
+  if constexpr (EMBED) {
+    // gather the row of x_t from the NCHW sources (fourcastnet.py:294-307): coalesced along w
+    const int HWp = a.H * a.W;
+    for (int i = tid; i < a.Cin * a.W; i += 256) {
+      const int k = i / a.W, w = i - k * a.W;
+      int ch = k;
+      float v = 0.f;
+#pragma unroll
+      for (int gi = 0; gi < 4; ++gi) {
+        if (gi < a.ngrp) {
+          if (ch >= 0 && ch < a.grp[gi].nch) v = a.grp[gi].base[(size_t)b * a.grp[gi].bstride + (size_t)ch * HWp + (size_t)h * a.W + w];
+          ch -= a.grp[gi].nch;
+        }
+      }
+      sIn[k * 64 + w] = v;
+    }
+    __syncthreads();
+    float* xrow = a.xout + (size_t)bh * a.W * kC;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int w = kg + 4 * j;
+      if (w < a.W) {
+        float acc = xe[j];
+        for (int k = 0; k < a.Cin; ++k) acc = fmaf(sIn[k * 64 + w], sWe[k * kC + c], acc);
+        sy[w * kC + c] = acc;
+        xrow[w * kC + c] = acc;
+      }
+    }
+    __syncthreads();
+  } else {
+    if (tid == 0) {
+      tc::mbar_arrive_expect_tx(&bar[1], (uint32_t)(a.W * kC * 4));
+      tc::bulk_g2s(sy, a.x + (size_t)bh * a.W * kC, (uint32_t)(a.W * kC * 4), &bar[1]);
+    }
+    tc::mbar_wait(&bar[1], 0);
   }
-  tc::mbar_wait(&bar[1], 0);
   row_layernorm(sy, a.W, g, be, a.eps, false);
   tc::mbar_wait(&bar[0], 0);
   __syncthreads();
@@ -103,17 +149,22 @@ __global__ void __launch_bounds__(256) afno_fwd_kernel(const AfnoFwdArgs a) {
   }
 }
 
+template <int NK>
+static int fwd_go(const AfnoFwdArgs& a, cudaStream_t st) {
+  const dim3 grid((unsigned)(a.B * a.H)), block(256);
+  const size_t smem = (size_t)a.W * kC * 4 + (size_t)4 * NK * a.W * 8 + (a.ngrp > 0 ? (size_t)2 * 16 * 64 * 4 : 0);
+  if (a.ngrp > 0) DLWP_CUDA(launch_pdl(afno_fwd_kernel<NK, true>, grid, block, smem, st, a));
+  else DLWP_CUDA(launch_pdl(afno_fwd_kernel<NK, false>, grid, block, smem, st, a));
+  return DLWP_OK;
+}
+
 int launch_afno_fwd(const AfnoFwdArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.B > 0 && a.H > 0 && a.W > 0 && a.W <= 64 && a.Kc > 0 && a.Kc <= 36, "afno_fwd_kernel: unsupported shape");
+  DLWP_REQUIRE(a.ngrp == 0 || (a.Cin >= 1 && a.Cin <= 16 && a.We && a.be && a.xout), "afno_fwd_kernel: bad embedding arguments");
   const int nk = ceil_div(a.Kc, 4);
-  const dim3 grid((unsigned)(a.B * a.H)), block(256);
-  if (nk <= 3) {
-    DLWP_CUDA(launch_pdl(afno_fwd_kernel<3>, grid, block, (size_t)a.W * kC * 4 + (size_t)12 * a.W * 8, st, a));
-  } else if (nk <= 5) {
-    DLWP_CUDA(launch_pdl(afno_fwd_kernel<5>, grid, block, (size_t)a.W * kC * 4 + (size_t)20 * a.W * 8, st, a));
-  } else {
-    DLWP_CUDA(launch_pdl(afno_fwd_kernel<9>, grid, block, (size_t)a.W * kC * 4 + (size_t)36 * a.W * 8, st, a));
-  }
+  if (nk <= 3) DLWP_TRY(fwd_go<3>(a, st));
+  else if (nk <= 5) DLWP_TRY(fwd_go<5>(a, st));
+  else DLWP_TRY(fwd_go<9>(a, st));
   DLWP_LAUNCHED("afno_fwd_kernel");
   return DLWP_OK;
 }

@@ -48,6 +48,7 @@ struct PwArgs {
   int act;            // 0 none, 1 exact GELU
   const float* pos;   // [tokens, N] or null (added after act)
   const float* resid; // NHWC [P, N] or null
+  const float* resid2; // a second one (the FNO2D token mixer adds its input and the block residual)
   // output: NHWC `out[p * N + n]`, or (unpatch != 0) NCHW frame with n = (i, j, co):
   //   out[b * out_bstride + co*H*W + y*W + x] = v + last[b * last_bstride + same]
   float* out;

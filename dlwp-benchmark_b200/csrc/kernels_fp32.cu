@@ -233,6 +233,7 @@ __global__ void __launch_bounds__(256) pw_linear_kernel(PwArgs a) {
       if (a.act == 1) v = gelu_erf(v);
       if (a.pos) v += a.pos[(long long)(p % a.tokens) * a.N + n];
       if (a.resid) v += a.resid[(long long)p * a.N + n];
+      if (a.resid2) v += a.resid2[(long long)p * a.N + n];
       if (!a.unpatch) {
         a.out[(long long)p * a.N + n] = v;
       } else {

@@ -89,6 +89,11 @@ int plan_build(dlwp_plan* p) {
     DLWP_REQUIRE(d.embed_dim > 0 && d.depth > 0 && d.num_blocks > 0 && d.embed_dim % d.num_blocks == 0,
                  "hidden_size %d should be divisble by num_blocks %d", d.embed_dim, d.num_blocks);
     DLWP_REQUIRE(d.mlp_hidden > 0 && d.hidden_size_factor > 0, "mlp_hidden / hidden_size_factor must be positive");
+    DLWP_REQUIRE(d.afno_filter == DLWP_AFNO_FILTER_AFNO2D || d.afno_filter == DLWP_AFNO_FILTER_FNO2D, "unknown afno_filter %d",
+                 d.afno_filter);
+    // the FNO2D token mixer keeps two [P, E] buffers in the hidden workspace
+    DLWP_REQUIRE(d.afno_filter == DLWP_AFNO_FILTER_AFNO2D || d.mlp_hidden >= 2 * d.embed_dim,
+                 "the FNO2D filter needs mlp_hidden >= 2 * embed_dim");
     p->C = d.embed_dim;
     p->n_spec = d.depth;
   } else {
@@ -239,7 +244,7 @@ static int commit_fno(dlwp_plan* p, cudaStream_t st) {
   return DLWP_OK;
 }
 
-static int commit_afno(dlwp_plan* p, cudaStream_t) {
+static int commit_afno(dlwp_plan* p, cudaStream_t st) {
   const dlwp_model_desc& d = p->d;
   const int E = d.embed_dim, nb = d.num_blocks, bs = E / nb, f = d.hidden_size_factor;
   const int pp = d.patch_h * d.patch_w;
@@ -253,10 +258,30 @@ static int commit_afno(dlwp_plan* p, cudaStream_t) {
     DLWP_TRY(need(p, idx("blocks.", i, ".norm1.bias"), E, &dummy));
     DLWP_TRY(need(p, idx("blocks.", i, ".norm2.weight"), E, &dummy));
     DLWP_TRY(need(p, idx("blocks.", i, ".norm2.bias"), E, &dummy));
+    if (d.afno_filter == DLWP_AFNO_FILTER_FNO2D) {
+      // fourcastnet.py:134-143: FNO(in = hidden = lifting = projection = out = E, n_layers = 1), dense weights
+      const std::string f0 = idx("blocks.", i, ".filter.fno.");
+      for (const char* mlp : {"lifting", "projection"})
+        for (const char* fc : {".fcs.0", ".fcs.1"}) {
+          DLWP_TRY(need(p, f0 + mlp + fc + ".weight", (int64_t)E * E, &dummy));
+          DLWP_TRY(need(p, f0 + mlp + fc + ".bias", E, &dummy));
+        }
+      DLWP_TRY(need(p, f0 + "fno_blocks.fno_skips.0.weight", (int64_t)E * E, &dummy));
+      DLWP_TRY(need(p, f0 + "fno_blocks.convs.bias", E, &dummy));
+      const int64_t dense_n = (int64_t)E * E * d.n_rows * d.n_cols;
+      const float* src;
+      DLWP_TRY(need(p, f0 + "fno_blocks.convs.weight.0.tensor", dense_n * 2, &src));
+      if ((int)p->wm.size() != d.depth) {
+        p->wm.assign(d.depth, nullptr);
+        for (int l = 0; l < d.depth; ++l) DLWP_TRY(dev_alloc(p, (void**)&p->wm[l], (size_t)dense_n * sizeof(float2)));
+      }
+      DLWP_TRY(launch_pack_modes(reinterpret_cast<const float2*>(src), p->wm[i], E, E, d.n_rows, d.n_cols, st));
+    } else {
     DLWP_TRY(need(p, idx("blocks.", i, ".filter.w1"), (int64_t)2 * nb * bs * bs * f, &dummy));
     DLWP_TRY(need(p, idx("blocks.", i, ".filter.b1"), (int64_t)2 * nb * bs * f, &dummy));
     DLWP_TRY(need(p, idx("blocks.", i, ".filter.w2"), (int64_t)2 * nb * bs * f * bs, &dummy));
     DLWP_TRY(need(p, idx("blocks.", i, ".filter.b2"), (int64_t)2 * nb * bs, &dummy));
+    }
     DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.weight"), (int64_t)d.mlp_hidden * E, &dummy));
     DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc1.bias"), d.mlp_hidden, &dummy));
     DLWP_TRY(need(p, idx("blocks.", i, ".mlp.fc2.weight"), (int64_t)E * d.mlp_hidden, &dummy));
@@ -320,8 +345,8 @@ int spectral_layer(dlwp_plan* p, const float* x, float* y, const float2* wm, int
   a.out_sk = (long long)Kc * B * C; a.out_sb0 = C; a.out_sb1 = (long long)B * C;
   a.in_complex = true; a.out_complex = true;
   DLWP_TRY(launch_tdft(a, st));
-  // channel mixing per retained mode
-  if (p->d.kind == DLWP_MODEL_FNO) {
+  // channel mixing per retained mode (dense for FNO and for the FNO2D token mixer of AFNONet)
+  if (p->d.kind == DLWP_MODEL_FNO || wm != nullptr) {
     DLWP_TRY(launch_mix_dense(p->specX, wm, p->specY, R * Kc, B, C, C, st));
   } else {
     const float *w1, *b1, *w2, *b2;
@@ -428,10 +453,14 @@ static int backbone_afno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st)
   float* t = p->act0;   // residual stream
   float* u = p->act1;   // LayerNorm output
   float* t2 = p->act2;  // after the filter + skips
+  // with 1x1 patches the fused AFNO kernels take the patch embedding into the first block's forward kernel and
+  // the head into the last block's Mlp kernel
+  const bool fuse_embed = p->atc_spec && pp == 1 && p->Cin <= 16;
+  const bool fuse_head = p->atc && pp == 1 && Cg <= 4;
   // patch embedding (+ position embedding), fourcastnet.py:285-289,537-542
   DLWP_TRY(need(p, "patch_embed.proj.weight", (int64_t)E * p->Cin * pp, &w));
   DLWP_TRY(need(p, "patch_embed.proj.bias", E, &b));
-  {
+  if (!fuse_embed) {
     PwArgs a = pw_plain(nullptr, w, b, t, P, p->Cin * pp, E, tokens, 0);
     pw_set_gather(a, io, H, W, p1, p2);
     if (d.use_pos_embed) DLWP_TRY(need(p, "pos_embed", (int64_t)tokens * E, &a.pos));
@@ -444,15 +473,41 @@ static int backbone_afno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st)
     DLWP_TRY(need(p, idx("blocks.", i, ".norm2.bias"), E, &be2));
     // x = filter(norm1(x)) + x : AFNO2D adds its own input back (:127) and Block adds the
     // pre-norm residual again (double_skip, :185-187)
-    if (p->atc_spec) {
-      DLWP_TRY(atc_block_filter(p, i, t, t2, B, st));
+    if (d.afno_filter == DLWP_AFNO_FILTER_FNO2D) {
+      // x = fno(norm1(x)) + norm1(x) + x   (FNO2D.forward fourcastnet.py:145-153, Block.forward :176-187)
+      const std::string f0 = idx("blocks.", i, ".filter.fno.");
+      float *ha = p->hid, *hb = p->hid + (size_t)P * E, *x0 = p->act3;
+      const float *w2, *b2;
+      DLWP_TRY(launch_layernorm(t, u, g1, be1, P, E, d.layernorm_eps, st));
+      DLWP_TRY(need(p, f0 + "lifting.fcs.0.weight", (int64_t)E * E, &w));
+      DLWP_TRY(need(p, f0 + "lifting.fcs.0.bias", E, &b));
+      DLWP_TRY(launch_pw_linear(pw_plain(u, w, b, ha, P, E, E, tokens, 1), st));
+      DLWP_TRY(need(p, f0 + "lifting.fcs.1.weight", (int64_t)E * E, &w));
+      DLWP_TRY(need(p, f0 + "lifting.fcs.1.bias", E, &b));
+      DLWP_TRY(launch_pw_linear(pw_plain(ha, w, b, x0, P, E, E, tokens, 0), st));
+      // the single FNO block is the last one: spectral conv + bias + linear skip, no activation
+      DLWP_TRY(need(p, f0 + "fno_blocks.fno_skips.0.weight", (int64_t)E * E, &w));
+      DLWP_TRY(launch_pw_linear(pw_plain(x0, w, nullptr, ha, P, E, E, tokens, 0), st));
+      DLWP_TRY(need(p, f0 + "fno_blocks.convs.bias", E, &b));
+      DLWP_TRY(spectral_layer(p, x0, hb, p->wm[i], i, ha, nullptr, b, 0, B, st));
+      DLWP_TRY(need(p, f0 + "projection.fcs.0.weight", (int64_t)E * E, &w));
+      DLWP_TRY(need(p, f0 + "projection.fcs.0.bias", E, &b));
+      DLWP_TRY(launch_pw_linear(pw_plain(hb, w, b, ha, P, E, E, tokens, 1), st));
+      DLWP_TRY(need(p, f0 + "projection.fcs.1.weight", (int64_t)E * E, &w2));
+      DLWP_TRY(need(p, f0 + "projection.fcs.1.bias", E, &b2));
+      PwArgs fa = pw_plain(ha, w2, b2, t2, P, E, E, tokens, 0);
+      fa.resid = u;
+      fa.resid2 = t;
+      DLWP_TRY(launch_pw_linear(fa, st));
+    } else if (p->atc_spec) {
+      DLWP_TRY(atc_block_filter(p, i, t, t2, B, st, (i == 0 && fuse_embed) ? &io : nullptr));
     } else {
       DLWP_TRY(launch_layernorm(t, u, g1, be1, P, E, d.layernorm_eps, st));
       DLWP_TRY(spectral_layer(p, u, t2, nullptr, i, u, t, nullptr, 0, B, st));
     }
     // x = mlp(norm2(x)) + x
     if (p->atc) {
-      DLWP_TRY(atc_block_mlp(p, i, t2, t, P, st));
+      DLWP_TRY(atc_block_mlp(p, i, t2, t, P, st, (i == d.depth - 1 && fuse_head) ? &io : nullptr));
       continue;
     }
     DLWP_TRY(launch_layernorm(t2, u, g2, be2, P, E, d.layernorm_eps, st));
@@ -466,6 +521,7 @@ static int backbone_afno(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st)
     DLWP_TRY(launch_pw_linear(a, st));
   }
   // head (no bias, the final self.norm is not applied) + un-patchify + last-frame residual
+  if (fuse_head) return DLWP_OK;
   DLWP_TRY(need(p, "head.weight", (int64_t)Cg * pp * E, &w));
   PwArgs a = pw_plain(t, w, nullptr, nullptr, P, E, Cg * pp, tokens, 0);
   pw_set_unpatch(a, io, H, W, p1, p2, Cg);

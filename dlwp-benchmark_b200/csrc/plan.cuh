@@ -106,8 +106,8 @@ int plan_tcw_commit(dlwp_plan* p, cudaStream_t st);
 int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st);
 int plan_atc_build(dlwp_plan* p);                              // tc_afno_plan.cu
 int plan_atc_commit(dlwp_plan* p, cudaStream_t st);
-int atc_block_filter(dlwp_plan* p, int block, const float* x, float* out, int B, cudaStream_t st);
-int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st);
+int atc_block_filter(dlwp_plan* p, int block, float* x, float* out, int B, cudaStream_t st, const dlwp::StepIO* embed);
+int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st, const dlwp::StepIO* head);
 int spectral_mid_fno(dlwp_plan* p, const float2* wm, int B, cudaStream_t st);
 int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);
 int plan_need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out);

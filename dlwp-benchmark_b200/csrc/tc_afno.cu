@@ -150,12 +150,51 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
-      float4* o = reinterpret_cast<float4*>(a.out + off);
+      float4 v[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 bb = b2v[j];
-        o[j] = make_float4(__uint_as_float(r[4 * j]) + bb.x + res[j].x, __uint_as_float(r[4 * j + 1]) + bb.y + res[j].y,
+        v[j] = make_float4(__uint_as_float(r[4 * j]) + bb.x + res[j].x, __uint_as_float(r[4 * j + 1]) + bb.y + res[j].y,
                            __uint_as_float(r[4 * j + 2]) + bb.z + res[j].z, __uint_as_float(r[4 * j + 3]) + bb.w + res[j].w);
+      }
+      if (a.Wh == nullptr) {
+        float4* o = reinterpret_cast<float4*>(a.out + off);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = v[j];
+      } else {
+        // fused head (fourcastnet.py:349-358, 1x1 patches): each thread's half of the 64-channel dot products, the upper
+        // halves meet the lower ones in shared memory, the lower threads add the residual frame and write NCHW
+        float part[4];
+#pragma unroll
+        for (int co = 0; co < 4; ++co) {
+          part[co] = 0.f;
+          if (co < a.Cg) {
+            const float4* wq = reinterpret_cast<const float4*>(a.Wh + co * kAfnoE + c0);
+            float acc = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 w = __ldg(wq + j);
+              acc = fmaf(v[j].x, w.x, acc); acc = fmaf(v[j].y, w.y, acc); acc = fmaf(v[j].z, w.z, acc); acc = fmaf(v[j].w, w.w, acc);
+            }
+            part[co] = acc;
+          }
+        }
+        float* sc = reinterpret_cast<float*>(stats);     // [4][128]; the statistics of the next tile were consumed two passes ago
+        if (id.half == 1) {
+#pragma unroll
+          for (int co = 0; co < 4; ++co) sc[co * 128 + id.row] = part[co];
+        }
+        bar_sync(1, kAmEpi);
+        if (id.half == 0) {
+          const long long p = (long long)tile * kTcTile + id.row;
+          const long long bb = p / a.HW, pix = p - bb * a.HW;
+#pragma unroll
+          for (int co = 0; co < 4; ++co)
+            if (co < a.Cg) {
+              const float lastv = a.last != nullptr ? a.last[bb * a.last_bstride + (long long)co * a.HW + pix] : 0.f;
+              a.frame[bb * a.frame_bstride + (long long)co * a.HW + pix] = part[co] + sc[co * 128 + id.row] + lastv;
+            }
+        }
       }
     }
   }
@@ -173,6 +212,7 @@ int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
     DLWP_CUDA(cudaFuncSetAttribute(afno_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AmSmem::Total));
   }
   DLWP_REQUIRE(a.ntiles > 0, "afno_mlp_kernel: empty problem");
+  DLWP_REQUIRE(a.Wh == nullptr || (a.Cg >= 1 && a.Cg <= 4 && a.HW > 0 && a.frame != nullptr), "afno_mlp_kernel: bad head arguments");
   const int grid = a.ntiles < sms ? a.ntiles : sms;
   DLWP_CUDA(launch_pdl(afno_mlp_kernel, dim3(grid), dim3(kAmCta), (size_t)AmSmem::Total, st, a));
   DLWP_LAUNCHED("afno_mlp_kernel");

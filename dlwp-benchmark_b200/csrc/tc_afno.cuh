@@ -25,11 +25,29 @@ struct AfnoMlpArgs {
   const uint8_t* W2img;   // fc2 / 2 (the epilogue hands on 2 gelu): [hi | lo] images, R = 64 rows, K = 256
   const float* b2;        // [64]
   float eps;
+  // optional fused head of the network (last block, 1x1 patches; fourcastnet.py:349-358): instead of storing
+  // `out`, frame[b, co, pix] = last[b, co, pix] + sum_c out[token, c] * Wh[co, c]
+  const float* Wh;        // [Cg, 64] head.weight, or null
+  int Cg;                 // <= 4
+  int HW;                 // tokens (= pixels) per sample
+  float* frame;
+  long long frame_bstride;
+  const float* last;      // residual frame or null
+  long long last_bstride;
 };
 int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st);
 
 // ---- fused fp32 kernels of the AFNO2D token mixer (afno_fused.cu) -------------------------------
 struct AfnoFwdArgs {
+  // optional fused patch embedding of the network (first block, 1x1 patches; fourcastnet.py:285-289,537-542):
+  // x = conv1x1(gathered NCHW input) + bias + pos_embed is computed here and stored to `xout`
+  SrcGroup grp[4];
+  int ngrp;               // 0: no embedding, read x
+  int Cin;                // <= 16
+  const float* We;        // [64, Cin] patch_embed.proj.weight
+  const float* be;        // [64]
+  const float* pos;       // [H * W, 64] or null
+  float* xout;            // [B, H, W, 64]
   const float* x;         // [B, H, W, 64] block input
   float2* A;              // [B, Kc, H, 64] W-DFT of LayerNorm(x) on the retained columns
   const float2* Fw;       // [Kc, W]

@@ -26,7 +26,7 @@ int plan_atc_build(dlwp_plan* p) {
   }
   p->atc = true;
   const int bs = d.embed_dim / d.num_blocks;
-  p->atc_spec = p->gw <= 64 && p->gh <= 32 && d.n_rows >= 1 && d.n_rows <= 32 && d.n_cols >= 1 && d.n_cols <= 36 &&
+  p->atc_spec = d.afno_filter == DLWP_AFNO_FILTER_AFNO2D && p->gw <= 64 && p->gh <= 32 && d.n_rows >= 1 && d.n_rows <= 32 && d.n_cols >= 1 && d.n_cols <= 36 &&
                 d.hidden_size_factor == 1 && (bs == 8 || bs == 16) &&
                 p->gw % 2 == 0 && (d.n_rows * p->gh) % 2 == 0;   // bulk copies move multiples of 16 bytes
   return DLWP_OK;
@@ -73,13 +73,26 @@ int plan_atc_commit(dlwp_plan* p, cudaStream_t st) {
 }
 
 // out = filter(norm1(x)) + norm1(x) + x   (fourcastnet.py:176-187 with AFNO2D.forward :78-127)
-int atc_block_filter(dlwp_plan* p, int block, const float* x, float* out, int B, cudaStream_t st) {
+// `embed` (first block, 1x1 patches): x is not read but computed here from the NCHW sources of the step
+// (patch embedding + position embedding, fourcastnet.py:285-289) and stored for the residual uses.
+int atc_block_filter(dlwp_plan* p, int block, float* x, float* out, int B, cudaStream_t st, const StepIO* embed) {
   const dlwp_model_desc& d = p->d;
   const int nb = d.num_blocks, bs = kAfnoE / nb;
   const float *g, *be;
   DLWP_TRY(plan_need(p, bname(block, ".norm1.weight"), kAfnoE, &g));
   DLWP_TRY(plan_need(p, bname(block, ".norm1.bias"), kAfnoE, &be));
-  AfnoFwdArgs fa{x, p->specA, p->Fw, g, be, d.layernorm_eps, B, p->gh, p->gw, d.n_cols};
+  AfnoFwdArgs fa{};
+  fa.x = x; fa.A = p->specA; fa.Fw = p->Fw; fa.gamma = g; fa.beta = be; fa.eps = d.layernorm_eps;
+  fa.B = B; fa.H = p->gh; fa.W = p->gw; fa.Kc = d.n_cols;
+  if (embed != nullptr) {
+    fa.ngrp = embed->ngrp;
+    for (int i = 0; i < embed->ngrp; ++i) fa.grp[i] = embed->grp[i];
+    fa.Cin = p->Cin;
+    DLWP_TRY(plan_need(p, "patch_embed.proj.weight", (int64_t)kAfnoE * p->Cin, &fa.We));
+    DLWP_TRY(plan_need(p, "patch_embed.proj.bias", kAfnoE, &fa.be));
+    if (d.use_pos_embed) DLWP_TRY(plan_need(p, "pos_embed", (int64_t)p->gh * p->gw * kAfnoE, &fa.pos));
+    fa.xout = x;
+  }
   DLWP_TRY(launch_afno_fwd(fa, st));
   AfnoMidArgs ma{};
   ma.A = p->specA; ma.Z = p->specZ; ma.Fh = p->Fh; ma.Gh = p->Gh;
@@ -95,8 +108,17 @@ int atc_block_filter(dlwp_plan* p, int block, const float* x, float* out, int B,
 }
 
 // x = x + mlp(norm2(x))   (fourcastnet.py:189-192)
-int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st) {
+// `head` (last block, 1x1 patches): the network head + residual frame are applied in the epilogue and the NCHW
+// frame of the step is written instead of `out` (fourcastnet.py:349-358).
+int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st, const StepIO* head) {
   AfnoMlpArgs a{};
+  if (head != nullptr) {
+    a.Cg = p->d.prognostic_channels;
+    a.HW = p->gh * p->gw;
+    DLWP_TRY(plan_need(p, "head.weight", (int64_t)a.Cg * kAfnoE, &a.Wh));
+    a.frame = head->out; a.frame_bstride = head->out_bstride;
+    a.last = head->last; a.last_bstride = head->last_bstride;
+  }
   a.ntiles = P / kTcTile;
   a.x = x;
   a.out = out;

@@ -333,11 +333,22 @@ class _MlpParams(nn.Module):
         self.fc2 = nn.Linear(hidden, dim)
 
 
+class _FNO2DFilterParams(nn.Module):
+    """``fourcastnet.py:130-143``: the one-layer neuralop FNO behind ``filter: FNO2D`` (parameters under ``fno.``)."""
+
+    n_modes = (12, 12)
+
+    def __init__(self, hidden_size):
+        super().__init__()
+        stored = (self.n_modes[0], self.n_modes[1] // 2 + 1)
+        self.fno = _FNOParams(hidden_size, hidden_size, hidden_size, hidden_size, hidden_size, 1, stored, None, 1.0)
+
+
 class _BlockParams(nn.Module):
-    def __init__(self, dim, mlp_hidden, num_blocks):
+    def __init__(self, dim, mlp_hidden, num_blocks, filter="AFNO2D"):
         super().__init__()
         self.norm1 = nn.LayerNorm(dim, eps=1e-6)
-        self.filter = _AFNO2DParams(dim, num_blocks)
+        self.filter = _AFNO2DParams(dim, num_blocks) if filter == "AFNO2D" else _FNO2DFilterParams(dim)
         self.norm2 = nn.LayerNorm(dim, eps=1e-6)
         self.mlp = _MlpParams(dim, mlp_hidden)
 
@@ -349,7 +360,8 @@ class _PatchEmbedParams(nn.Module):
 
 
 class AFNONet(_NativeRollout):
-    """``models/fourcastnet/fourcastnet.py:214-361`` with the ``AFNO2D`` filter."""
+    """``models/fourcastnet/fourcastnet.py:214-361`` with the ``AFNO2D`` filter (``:60-127``) or the ``FNO2D`` filter
+    (``:130-153``: a one-layer neuralop FNO as the token mixer)."""
 
     def __init__(self, img_height: int = 720, img_width: int = 1440, patch_size: tuple = (16, 16),
                  constant_channels: int = 4, prescribed_channels: int = 0, prognostic_channels: int = 1,
@@ -359,9 +371,10 @@ class AFNONet(_NativeRollout):
                  use_pos_embed: bool = True, **kwargs):
         super().__init__()
         self._init_native()
-        if filter != "AFNO2D":
-            raise NotImplementedError(f"filter={filter!r}: only the AFNO2D filter of configs/model/fourcastnet.yaml "
-                                      "is implemented natively")
+        if filter not in ("AFNO2D", "FNO2D"):
+            raise NotImplementedError(f"filter={filter!r}: the AFNO2D and FNO2D filters of fourcastnet.py are implemented "
+                                      "natively (SFNO needs torch_harmonics)")
+        self.filter_kind = filter
         if drop_rate or drop_path_rate:
             raise NotImplementedError("forward-only implementation: drop_rate / drop_path_rate must be 0")
         self.img_size = (int(img_height), int(img_width))
@@ -387,7 +400,7 @@ class AFNONet(_NativeRollout):
         if self.use_pos_embed:
             self.pos_embed = nn.Parameter(torch.zeros(1, self.h * self.w, self.embed_dim))
             nn.init.trunc_normal_(self.pos_embed, std=0.02)
-        self.blocks = nn.ModuleList(_BlockParams(self.embed_dim, self.mlp_hidden, self.num_blocks)
+        self.blocks = nn.ModuleList(_BlockParams(self.embed_dim, self.mlp_hidden, self.num_blocks, filter)
                                     for _ in range(self.depth))
         self.norm = nn.LayerNorm(self.embed_dim, eps=1e-6)   # held for state_dict parity; never applied (:263)
         self.head = nn.Linear(self.embed_dim, self.out_chans * self.patch_size[0] * self.patch_size[1], bias=False)
@@ -403,22 +416,35 @@ class AFNONet(_NativeRollout):
     def _desc(self, H, W):
         if (H, W) != self.img_size:
             raise AssertionError(f"Input image size ({H}*{W}) doesn't match model ({self.img_size[0]}*{self.img_size[1]}).")
-        rows, cols = afno_kept_region(self.h, self.w // 2 + 1, self.hard_thresholding_fraction)
-        if not rows or cols <= 0:
-            raise NotImplementedError("hard_thresholding_fraction keeps no Fourier mode")
-        fields = dict(kind=native.MODEL_AFNO, constant_channels=self.constant_channels,
+        if self.filter_kind == "FNO2D":
+            m1, cols = self._fno2d_modes()
+            rows, rows_out = neuralop_row_bins(self.h, m1)
+            norm, filt = native.FFT_NORM_FORWARD, native.AFNO_FILTER_FNO2D
+        else:
+            rows, cols = afno_kept_region(self.h, self.w // 2 + 1, self.hard_thresholding_fraction)
+            if not rows or cols <= 0:
+                raise NotImplementedError("hard_thresholding_fraction keeps no Fourier mode")
+            rows_out, norm, filt = rows, native.FFT_NORM_ORTHO, native.AFNO_FILTER_AFNO2D
+        fields = dict(kind=native.MODEL_AFNO, afno_filter=filt, constant_channels=self.constant_channels,
                       prescribed_channels=self.prescribed_channels, prognostic_channels=self.prognostic_channels,
-                      context_size=self.context_size, fft_norm=native.FFT_NORM_ORTHO, n_cols=cols,
+                      context_size=self.context_size, fft_norm=norm, n_cols=cols,
                       embed_dim=self.embed_dim, depth=self.depth, num_blocks=self.num_blocks,
                       mlp_hidden=self.mlp_hidden, patch_h=self.patch_size[0], patch_w=self.patch_size[1],
                       use_pos_embed=int(self.use_pos_embed), hidden_size_factor=1,
                       sparsity_threshold=self.sparsity_threshold, layernorm_eps=1e-6)
-        return fields, rows, rows
+        return fields, rows, rows_out
+
+    def _fno2d_modes(self):
+        n1, n2 = _FNO2DFilterParams.n_modes
+        return min(n1, self.h), min(n2 // 2 + 1, self.w // 2 + 1)
 
     def _native_weights(self, H, W):
         for name, p in self.named_parameters():
             if name.startswith("norm."):
                 continue
+            if name.endswith(".convs.weight.0.tensor"):      # FNO2D filter: the modes the token grid can hold
+                m1, m2 = self._fno2d_modes()
+                p = p[:, :, centre_crop(_FNO2DFilterParams.n_modes[0], m1), :m2]
             yield name, p
 
 

@@ -13,8 +13,9 @@ import threading
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libdlwp_b200.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 MODEL_FNO, MODEL_AFNO = 0, 1
+AFNO_FILTER_AFNO2D, AFNO_FILTER_FNO2D = 0, 1
 PREC_FP32, PREC_FP32_TC, PREC_BF16 = 0, 1, 2
 FFT_NORM_BACKWARD, FFT_NORM_FORWARD, FFT_NORM_ORTHO = 0, 1, 2
 
@@ -34,6 +35,7 @@ class ModelDesc(C.Structure):
         ("mlp_hidden", C.c_int32), ("patch_h", C.c_int32), ("patch_w", C.c_int32),
         ("use_pos_embed", C.c_int32), ("hidden_size_factor", C.c_int32),
         ("sparsity_threshold", C.c_float), ("layernorm_eps", C.c_float),
+        ("afno_filter", C.c_int32),
     ]
 
 

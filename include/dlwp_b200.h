@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define DLWP_ABI_VERSION 1
+#define DLWP_ABI_VERSION 2
 
 typedef enum {
   DLWP_OK = 0,
@@ -43,8 +43,15 @@ typedef enum {
 
 typedef enum {
   DLWP_MODEL_FNO = 0,         /* neuralop FNO (dense) and TFNO (Tucker, densified at load) */
-  DLWP_MODEL_AFNO = 1         /* FourCastNet AFNONet with the AFNO2D filter                */
+  DLWP_MODEL_AFNO = 1         /* FourCastNet AFNONet (token mixer: see dlwp_afno_filter below)       */
 } dlwp_model_kind;
+
+typedef enum {
+  DLWP_AFNO_FILTER_AFNO2D = 0, /* block-diagonal spectral MLP (fourcastnet.py:60-127)       */
+  DLWP_AFNO_FILTER_FNO2D = 1   /* one-layer neuralop FNO as token mixer (fourcastnet.py:130-153):
+                                  hidden = lifting = projection = embed_dim; the spectral fields
+                                  (fft_norm, rows, n_cols) then describe that FNO's modes    */
+} dlwp_afno_filter;
 
 typedef enum {
   DLWP_PREC_FP32 = 0,         /* fp32 storage, fp32 FMA arithmetic (parity mode, <=1e-4)   */
@@ -86,6 +93,7 @@ typedef struct {
   int32_t hidden_size_factor;   /* AFNO2D hidden_size_factor (1 in the reference) */
   float sparsity_threshold;     /* softshrink lambda */
   float layernorm_eps;          /* 1e-6 (fourcastnet.py:245) */
+  int32_t afno_filter;          /* dlwp_afno_filter: the filter key of fourcastnet.yaml, eval'd at fourcastnet.py:259 */
 } dlwp_model_desc;
 
 typedef struct dlwp_plan dlwp_plan;

@@ -74,6 +74,26 @@ class AFNO2D(nn.Module):
         return y.to(in_dtype) + resid
 
 
+class FNO2D(nn.Module):
+    """``fourcastnet.py:130-153``: a one-layer neuralop ``FNO`` (hidden = lifting = projection = embed_dim,
+    ``n_modes=(12, 12)``) as the token mixer, selected by ``filter: FNO2D`` (``eval`` at ``:259``).  ``Block`` passes
+    ``(dim, num_blocks, sparsity_threshold, hard_thresholding_fraction)`` positionally (``:173``); only ``dim`` is
+    used.  The FNO itself is the restatement of ``oracle/neuralop_fno.py`` (parity unpinned, see there)."""
+
+    def __init__(self, hidden_size, num_blocks=8, sparsity_threshold=0.01, hard_thresholding_fraction=1,
+                 hidden_size_factor=1, n_modes=(12, 12), max_n_modes=None, n_layers=1):
+        super().__init__()
+        from .neuralop_fno import FNO
+        self.fno = FNO(n_modes=n_modes, max_n_modes=max_n_modes, in_channels=hidden_size, hidden_channels=hidden_size,
+                       lifting_channels=hidden_size, projection_channels=hidden_size, out_channels=hidden_size,
+                       n_layers=n_layers)
+
+    def forward(self, x):                                   # [B, h, w, C]
+        bias = x
+        y = self.fno(x.float().permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
+        return y + bias
+
+
 class Mlp(nn.Module):
     def __init__(self, in_features, hidden_features):
         super().__init__()
@@ -85,10 +105,11 @@ class Mlp(nn.Module):
 
 
 class Block(nn.Module):
-    def __init__(self, dim, mlp_ratio, num_blocks, sparsity_threshold, hard_thresholding_fraction):
+    def __init__(self, dim, mlp_ratio, num_blocks, sparsity_threshold, hard_thresholding_fraction, filter="AFNO2D"):
         super().__init__()
         self.norm1 = nn.LayerNorm(dim, eps=1e-6)
-        self.filter = AFNO2D(dim, num_blocks, sparsity_threshold, hard_thresholding_fraction)
+        self.filter = {"AFNO2D": AFNO2D, "FNO2D": FNO2D}[filter](dim, num_blocks, sparsity_threshold,
+                                                                 hard_thresholding_fraction)
         self.norm2 = nn.LayerNorm(dim, eps=1e-6)
         self.mlp = Mlp(dim, int(dim * mlp_ratio))
 
@@ -119,8 +140,8 @@ class AFNONet(nn.Module):
                  mlp_ratio=4.0, drop_rate=0.0, drop_path_rate=0.0, num_blocks=16, sparsity_threshold=0.01,
                  hard_thresholding_fraction=1.0, context_size=1, use_pos_embed=True, **kwargs):
         super().__init__()
-        if filter != "AFNO2D":
-            raise NotImplementedError("oracle restates the AFNO2D filter only")
+        if filter not in ("AFNO2D", "FNO2D"):
+            raise NotImplementedError("oracle restates the AFNO2D and FNO2D filters")
         if drop_rate or drop_path_rate:
             raise NotImplementedError("forward-only oracle: dropout / drop-path must be 0")
         self.img_size = (img_height, img_width)
@@ -135,11 +156,11 @@ class AFNONet(nn.Module):
         self.h = img_height // self.patch_size[0]
         self.w = img_width // self.patch_size[1]
         self.blocks = nn.ModuleList(
-            Block(embed_dim, mlp_ratio, num_blocks, sparsity_threshold, hard_thresholding_fraction)
+            Block(embed_dim, mlp_ratio, num_blocks, sparsity_threshold, hard_thresholding_fraction, filter)
             for _ in range(depth))
         self.norm = nn.LayerNorm(embed_dim, eps=1e-6)       # defined, never applied (:263 vs :283-293)
         self.head = nn.Linear(embed_dim, self.out_chans * self.patch_size[0] * self.patch_size[1], bias=False)
-        for m in self.modules():
+        for m in self.modules():                             # _init_weights (:270-277): nn.Linear and LayerNorm only
             if isinstance(m, nn.Linear):
                 nn.init.trunc_normal_(m.weight, std=0.02)
                 if m.bias is not None:

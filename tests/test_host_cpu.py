@@ -99,6 +99,31 @@ def test_afno_state_dict_layout_matches_oracle_and_yaml_kwargs():
         pkg.FourCastNet(embed_dim=30, num_blocks=4)
 
 
+def test_fourcastnet_fno2d_filter_layout_and_oracle_semantics():
+    """``filter: FNO2D`` (fourcastnet.py:130-153, eval'd at :259): parameter names / shapes match the oracle's,
+    and the oracle block is ``fno(norm1(x)) + norm1(x) + x`` followed by the Mlp branch."""
+    kw = dict(img_height=16, img_width=32, patch_size=[1, 1], constant_channels=2, prescribed_channels=1,
+              prognostic_channels=2, embed_dim=32, filter="FNO2D", depth=2, num_blocks=4, context_size=1)
+    ours, ref = pkg.FourCastNet(**kw), oafno.AFNONet(**kw).eval()
+    a = {k: tuple(v.shape) for k, v in ours.state_dict().items()}
+    b = {k: tuple(v.shape) for k, v in ref.state_dict().items()}
+    assert a == b
+    assert "blocks.0.filter.fno.fno_blocks.convs.weight.0.tensor" in a
+    assert a["blocks.0.filter.fno.fno_blocks.convs.weight.0.tensor"] == (32, 32, 12, 7, 2)
+    fields, rows_in, rows_out = ours._desc(16, 32)
+    assert fields["afno_filter"] == native.AFNO_FILTER_FNO2D and fields["fft_norm"] == native.FFT_NORM_FORWARD
+    assert fields["n_cols"] == 7 and len(rows_in) == 12
+    blk = ref.blocks[0]
+    x = torch.randn(2, 16, 32, 32)
+    with torch.no_grad():
+        y = blk.norm1(x)
+        t2 = blk.filter.fno(y.permute(0, 3, 1, 2)).permute(0, 2, 3, 1) + y + x
+        want = blk.mlp(blk.norm2(t2)) + t2
+        assert torch.allclose(blk(x), want, atol=1e-6)
+    with pytest.raises(NotImplementedError):
+        pkg.FourCastNet(filter="SFNO")
+
+
 def test_forward_guards():
     m = pkg.TFNO2DModule(context_size=1, type="TFNO2DModule", name="test")
     prog = torch.randn(1, 2, 8, 8, 16)

@@ -228,16 +228,17 @@ def test_afno_paper_size_matches_oracle(pkg):
     assert max_rel(got, want) < TOL_STEP
 
 
-@pytest.mark.parametrize("B,nb,frac,H,W", [(3, 4, 1.0, 32, 64), (24, 4, 1.0, 32, 64), (5, 8, 0.5, 16, 32), (2, 4, 0.7, 24, 48)])
-def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B, nb, frac, H, W):
+@pytest.mark.parametrize("B,nb,frac,H,W,Cg", [(3, 4, 1.0, 32, 64, 3), (24, 4, 1.0, 32, 64, 3), (5, 8, 0.5, 16, 32, 4),
+                                               (2, 4, 0.7, 24, 48, 6)])
+def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B, nb, frac, H, W, Cg):
     """configs/model/fourcastnet.yaml shapes (embed_dim 64, mlp_ratio 4): the tcgen05 AFNO kernels of the
     default precision mode against the oracle and against the fp32 FMA kernel set; B = 24 gives every
-    persistent CTA several 128-token tiles."""
+    persistent CTA several 128-token tiles; more than 4 prognostic channels keep the head a separate launch."""
     from oracle import afno as oafno
     native = pkg.native
     kw = dict(img_height=H, img_width=W, patch_size=[1, 1], constant_channels=4, prescribed_channels=1,
-              prognostic_channels=3, embed_dim=64, depth=4, num_blocks=nb, mlp_ratio=4.0, context_size=1,
-              use_pos_embed=True, hard_thresholding_fraction=frac)
+              prognostic_channels=Cg, embed_dim=64, depth=4, num_blocks=nb, mlp_ratio=4.0, context_size=1,
+              use_pos_embed=(Cg != 4), hard_thresholding_fraction=frac)
     torch.manual_seed(11)
     ref = oafno.AFNONet(**kw).eval()
     with torch.no_grad():
@@ -246,7 +247,7 @@ def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B, nb, f
                 p.mul_(6.0)
             elif n.endswith("bias") or "norm" in n:
                 p.add_(0.3 * torch.randn_like(p))
-    const, presc, prog = synthetic(B, 4, 4, 1, 3, H, W, seed=77)
+    const, presc, prog = synthetic(B, 4, 4, 1, Cg, H, W, seed=77)
     with torch.no_grad():
         want = ref(constants=const, prescribed=presc, prognostic=prog)
     outs = {}
@@ -258,6 +259,29 @@ def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B, nb, f
             outs[prec] = mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog)).cpu()
         assert max_rel(outs[prec], want) < 2 * TOL_STEP
     assert max_rel(outs[native.PREC_FP32_TC], outs[native.PREC_FP32]) < 2 * TOL_STEP
+
+
+@pytest.mark.parametrize("H,W,E", [(32, 64, 64), (8, 20, 48)])
+def test_fourcastnet_fno2d_filter_matches_oracle(pkg, H, W, E):
+    """``filter: FNO2D`` (fourcastnet.py:130-153): a one-layer neuralop FNO as the token mixer; the second case
+    has a token grid smaller than the 12 x 7 stored modes."""
+    from oracle import afno as oafno
+    kw = dict(img_height=H, img_width=W, patch_size=[1, 1], constant_channels=4, prescribed_channels=1,
+              prognostic_channels=3, embed_dim=E, depth=2, num_blocks=4, mlp_ratio=4.0, context_size=1,
+              use_pos_embed=True, filter="FNO2D")
+    torch.manual_seed(3)
+    ref = oafno.AFNONet(**kw).eval()
+    with torch.no_grad():
+        for n, p in ref.named_parameters():
+            if n.endswith("bias") or "norm" in n:
+                p.add_(0.2 * torch.randn_like(p))
+    mod = pkg.FourCastNet(**kw).cuda().eval()
+    mod.load_state_dict(ref.state_dict(), strict=True)
+    const, presc, prog = synthetic(3, 4, 4, 1, 3, H, W, seed=5)
+    with torch.no_grad():
+        want = ref(constants=const, prescribed=presc, prognostic=prog)
+        got = mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog)).cpu()
+    assert max_rel(got, want) < 2 * TOL_STEP
 
 
 # ---------------------------------------------------------------------------------------
