@@ -196,7 +196,21 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
                         + tok * E + 2 * B * S * Cg)
         if name == "layernorm_kernel":
             return b * D * 2 * 2 * tok * E
-        return None
+        # fused AFNO kernels (afno_fused.cu, tc_afno.cu; 1x1 patches): retained half spectrum [B, h, Kc, E] complex
+        h, w = H // p1, W // p2
+        frac = kw.get("hard_thresholding_fraction", 1.0)
+        kc = int((h // 2 + 1) * frac)
+        rows = min(2 * kc, h)
+        spec = B * h * kc * E * 2
+        table = {
+            # block 0 reads the NCHW step input and writes x instead of reading it
+            "afno_fwd_kernel": b * ((B * S * cin + tok * E) + (D - 1) * tok * E + D * spec),
+            "afno_mid_kernel": b * D * (2 * spec + 4 * 2 * E * (E // kw["num_blocks"])),
+            "afno_inv_kernel": b * D * (spec + 2 * tok * E),
+            # the last block writes the NCHW frame (+ reads the residual frame) instead of the token stream
+            "afno_mlp_kernel": b * ((D - 1) * 2 * tok * E + tok * E + 2 * B * S * Cg) + D * 2 * 2 * 2 * E * hid,
+        }
+        return table.get(name)
     cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
     px = B * S
     if name.startswith("tcw_") or name.startswith("wide_") or tcw:
@@ -451,7 +465,8 @@ def run_ours(args, wl):
         fl = step_flops(cls, kw, members, H, W)
         sb = step_bytes(cls, kw, members, H, W)
         spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel",
-                                                  "tcw_fwd_wdft", "tcw_fwd_hdft", "tcw_inv_hdft")]
+                                                  "tcw_fwd_wdft", "tcw_fwd_hdft", "tcw_inv_hdft",
+                                                  "afno_fwd_kernel", "afno_mid_kernel", "afno_inv_kernel")]
         spec_ms = sum(entries[n][0] for n in spec_names)
         if tcw:   # the inverse W-DFT runs inside tcw_layer next to the skip conv: its share of that kernel's K extent
             m2c = fno_dims(kw, H, W)[7]
