@@ -252,8 +252,9 @@ __global__ void __launch_bounds__(256) afno_mid_kernel(const AfnoMidArgs a) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = make_float2(0.f, 0.f);
 #pragma unroll 2
+    const float* pl = reinterpret_cast<const float*>(bufA);
     for (int h = 0; h < H; ++h) {
-      const float2 v = bufA[h * kC + c];
+      const float2 v = a.planarA ? make_float2(pl[(2 * h) * kC + c], pl[(2 * h + 1) * kC + c]) : bufA[h * kC + c];
 #pragma unroll
       for (int j = 0; j < 8; ++j) cfma(acc[j], sFh[(g4 + 4 * j) * H + h], v);
     }

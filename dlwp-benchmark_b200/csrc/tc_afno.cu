@@ -219,4 +219,406 @@ int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
   return DLWP_OK;
 }
 
+// =============================================================================================
+// The truncated W-DFTs of the AFNO token mixer on tcgen05 (fourcastnet.py:84-85,124-127), 128-token tiles
+// (= RT grid rows), persistent, one CTA per SM: 8 worker warps + 1 control warp.
+//
+// afno_fwd_tc_kernel:  A[(h2, kx, re | im), c] = sum_px F''[(h2, kx, re | im), px] * LayerNorm(x)[px, c]
+//   The fp32 token tile arrives by one bulk copy; the workers normalise it (a warp takes four tokens per
+//   step: eight lanes per token, eight channels per lane, statistics by shuffles) and write it as a
+//   split-bf16 image that the tensor core reads in place as an MN-major B operand (tokens = K rows);
+//   the accumulator rows (one retained column of one grid row, Re or Im) go from TMEM lanes to their
+//   256-byte rows of the planar spectrum one tile late, under the next tile's LayerNorm.
+// =============================================================================================
+namespace {
+constexpr int kWtWork = 256, kWtCta = kWtWork + 32, kWtCtlWarp = kWtWork / 32;
+enum { WB_XFULL = 0, WB_XEMPTY = 2, WB_YFULL = 4, WB_YEMPTY = 6, WB_DFULL = 8, WB_DEMPTY = 10, WB_CONST = 12, WB_N = 13 };
+struct FwdSmem {
+  static constexpr int F = 0, X = F + 2 * 128 * 128 * 2, Y = X + 2 * 32768, Total = Y + 2 * 32768;
+};
+
+__device__ __forceinline__ void wt_init_barriers(uint64_t* b) {
+  for (int i = 0; i < 2; ++i) {
+    mbar_init(&b[WB_XFULL + i], 1);
+    mbar_init(&b[WB_XEMPTY + i], kWtWork);
+    mbar_init(&b[WB_YFULL + i], kWtWork);
+    mbar_init(&b[WB_YEMPTY + i], 1);
+    mbar_init(&b[WB_DFULL + i], 1);
+    mbar_init(&b[WB_DEMPTY + i], kWtWork);
+  }
+  mbar_init(&b[WB_CONST], 1);
+  fence_mbar_init();
+}
+
+// LayerNorm of one token spread over eight lanes (eight channels each); returns xhat * gamma + beta
+__device__ __forceinline__ void ln8(float4& v0, float4& v1, const float4& g0, const float4& g1, const float4& b0, const float4& b1,
+                                    float eps) {
+  float s = (v0.x + v0.y) + (v0.z + v0.w) + (v1.x + v1.y) + (v1.z + v1.w);
+#pragma unroll
+  for (int o = 1; o < 8; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s * (1.0f / 64.0f);
+  v0.x -= mean; v0.y -= mean; v0.z -= mean; v0.w -= mean; v1.x -= mean; v1.y -= mean; v1.z -= mean; v1.w -= mean;
+  float q = v0.x * v0.x;
+  q = fmaf(v0.y, v0.y, q); q = fmaf(v0.z, v0.z, q); q = fmaf(v0.w, v0.w, q);
+  q = fmaf(v1.x, v1.x, q); q = fmaf(v1.y, v1.y, q); q = fmaf(v1.z, v1.z, q); q = fmaf(v1.w, v1.w, q);
+#pragma unroll
+  for (int o = 1; o < 8; o <<= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q * (1.0f / 64.0f) + eps);
+  v0.x = fmaf(v0.x * rstd, g0.x, b0.x); v0.y = fmaf(v0.y * rstd, g0.y, b0.y);
+  v0.z = fmaf(v0.z * rstd, g0.z, b0.z); v0.w = fmaf(v0.w * rstd, g0.w, b0.w);
+  v1.x = fmaf(v1.x * rstd, g1.x, b1.x); v1.y = fmaf(v1.y * rstd, g1.y, b1.y);
+  v1.z = fmaf(v1.z * rstd, g1.z, b1.z); v1.w = fmaf(v1.w * rstd, g1.w, b1.w);
+}
+}  // namespace
+
+__global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
+  __shared__ uint64_t bars[WB_N];
+  __shared__ uint32_t tmem_s;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+  if (tid == 0) wt_init_barriers(bars);
+  if (warp == kWtCtlWarp) {
+    tmem_alloc(&tmem_s, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint64_t* b = bars;
+  const int stride = gridDim.x, first = blockIdx.x;
+
+  if (warp == kWtCtlWarp) {
+    const uint32_t leader = elect_one();
+    mbar_arrive_expect_tx_p(leader, &b[WB_CONST], 65536u);
+    bulk_g2s_p(leader, smem + FwdSmem::F, a.Fimg, 65536u, &b[WB_CONST]);
+    pdl_wait();   // x is what the previous kernel wrote
+    auto load_x = [&](int tile, int s) {
+      mbar_arrive_expect_tx_p(leader, &b[WB_XFULL + s], 32768u);
+      bulk_g2s_p(leader, smem + FwdSmem::X + s * 32768, a.x + (size_t)tile * kTcTile * kAfnoE, 32768u, &b[WB_XFULL + s]);
+    };
+    for (int i = 0; i < 2; ++i)
+      if (first + i * stride < a.ntiles) load_x(first + i * stride, i);
+    mbar_wait(&b[WB_CONST], 0);
+    const uint32_t idesc = idesc_bf16(128, 64) | kIdescBMnMajor;
+    const uint64_t dF = chunk_desc(smem_u32(smem + FwdSmem::F), 128, 0);
+    uint32_t u = 0;
+    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
+      const int s = u & 1;
+      const uint32_t ph = (u >> 1) & 1u;
+      mbar_wait(&b[WB_YFULL + s], ph);
+      mbar_wait(&b[WB_DEMPTY + s], ph ^ 1u);
+      tc_fence_after();
+      // B: 8 x 8 core matrices 128 B apart along tokens (K), 2048 B along channels (N)
+      const uint64_t dY = smem_desc(smem_u32(smem + FwdSmem::Y + s * 32768), 128, 2048);
+      const uint32_t d = tmem_s + 64u * s;
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
+        const uint32_t fa = term == 1 ? 32768u : 0u, yp = term == 2 ? 16384u : 0u;
+#pragma unroll
+        for (int k0 = 0; k0 < 128; k0 += 16)
+          umma_bf16_p(leader, d, desc_off(dF, fa + (k0 >> 3) * 2048), desc_off(dY, yp + k0 * 16), idesc, (term | k0) != 0);
+      }
+      umma_commit_p(leader, &b[WB_DFULL + s]);
+      umma_commit_p(leader, &b[WB_YEMPTY + s]);
+      if (tile + 2 * stride < a.ntiles) {
+        mbar_wait(&b[WB_XEMPTY + s], ph);
+        load_x(tile + 2 * stride, s);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int t4 = lane >> 3, o = lane & 7;      // LayerNorm: token of the step, channel octet
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o), g1 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o + 1);
+    const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o), e1 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o + 1);
+    const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane;     // drain: accumulator row, column half
+    const int rows_used = a.RT * 2 * a.Kc;
+    auto drain = [&](int tile, uint32_t u) {
+      const int s = u & 1;
+      mbar_wait(&b[WB_DFULL + s], (u >> 1) & 1u);
+      tc_fence_after();
+      uint32_t r[32];
+      tmem_ld32(tmem_s + ((uint32_t)(q4 * 32) << 16) + 64u * s + 32u * half, r);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&b[WB_DEMPTY + s]);
+      if (row < rows_used) {
+        const int h2 = row / (2 * a.Kc), rem = row - h2 * 2 * a.Kc, kx = rem >> 1, reim = rem & 1;
+        const int grow = tile * a.RT + h2, bb = grow / a.H, h = grow - bb * a.H;
+        float4* dst = reinterpret_cast<float4*>(a.A + ((((size_t)bb * a.Kc + kx) * a.H + h) * 2 + reim) * kAfnoE + 32 * half);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                               __uint_as_float(r[4 * j + 3]));
+      }
+    };
+    uint32_t u = 0;
+    int prev = -1;
+    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
+      const int s = u & 1;
+      const uint32_t ph = (u >> 1) & 1u;
+      mbar_wait(&b[WB_XFULL + s], ph);
+      float4 v[4][2];
+      const float* xs = reinterpret_cast<const float*>(smem + FwdSmem::X + s * 32768);
+#pragma unroll
+      for (int st = 0; st < 4; ++st) {
+        const int px = warp * 16 + st * 4 + t4;
+        v[st][0] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8);
+        v[st][1] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8 + 4);
+      }
+      mbar_arrive(&b[WB_XEMPTY + s]);
+      mbar_wait(&b[WB_YEMPTY + s], ph ^ 1u);
+      uint8_t* ys = smem + FwdSmem::Y + s * 32768;
+#pragma unroll
+      for (int st = 0; st < 4; ++st) {
+        const int px = warp * 16 + st * 4 + t4;
+        ln8(v[st][0], v[st][1], g0, g1, e0, e1, a.eps);
+        uint32_t h[4], l[4];
+        split2p(make_float2(v[st][0].x, v[st][0].y), h[0], l[0]);
+        split2p(make_float2(v[st][0].z, v[st][0].w), h[1], l[1]);
+        split2p(make_float2(v[st][1].x, v[st][1].y), h[2], l[2]);
+        split2p(make_float2(v[st][1].z, v[st][1].w), h[3], l[3]);
+        *reinterpret_cast<uint4*>(ys + o * 2048 + px * 16) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(ys + 16384 + o * 2048 + px * 16) = make_uint4(l[0], l[1], l[2], l[3]);
+      }
+      fence_async_smem();
+      mbar_arrive(&b[WB_YFULL + s]);
+      if (prev >= 0) drain(prev, u - 1);
+      prev = tile;
+    }
+    if (prev >= 0) drain(prev, u - 1);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWtCtlWarp) tmem_dealloc(tmem_s, 128);
+}
+
+int launch_afno_fwd_tc(const AfnoWTcArgs& a, cudaStream_t st) {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    DLWP_CUDA(cudaGetDevice(&dev));
+    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    DLWP_CUDA(cudaFuncSetAttribute(afno_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::Total));
+  }
+  DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= 128, "afno_fwd_tc_kernel: unsupported shape");
+  const int grid = a.ntiles < sms ? a.ntiles : sms;
+  DLWP_CUDA(launch_pdl(afno_fwd_tc_kernel, dim3(grid), dim3(kWtCta), (size_t)FwdSmem::Total, st, a));
+  DLWP_LAUNCHED("afno_fwd_tc_kernel");
+  return DLWP_OK;
+}
+
+// =============================================================================================
+// afno_inv_tc_kernel:  out[px, c] = sum_k G'[px, k] * Z'[c, k] + LayerNorm(x)[px, c] + x[px, c],  k = (h2, kx, re | im)
+//   The tile's rows of Z (complex fp32, after the inverse H-DFT) arrive by one bulk copy and are split into
+//   the K-major bf16 operand image Z' by the workers; the accumulator is staged row-padded in shared memory
+//   so that the second phase can work token-major (four tokens per warp step as in the forward kernel):
+//   LayerNorm(x) is recomputed from the token tile (bulk-copied, never stored normalised), the sum is
+//   written with fully coalesced 1 KB warp stores.  A tile is finished one iteration late, under the
+//   tensor-core work of the next one.
+// =============================================================================================
+namespace {
+enum { IB_ZRFULL = 0, IB_ZREMPTY = 2, IB_ZIFULL = 4, IB_ZIEMPTY = 6, IB_XFULL = 8, IB_XEMPTY = 10, IB_DFULL = 12, IB_DEMPTY = 14,
+       IB_CONST = 16, IB_N = 17 };
+constexpr int kDstRow = 68;      // floats per staged accumulator row (64 + 4: conflict-free 16-byte accesses)
+struct InvSmem {
+  int G, X, Zraw, Zimg, Dst, zraw_bytes, zimg_bytes, Total;
+  __host__ __device__ InvSmem(int RT, int Kc, int KZ) {
+    zraw_bytes = RT * Kc * kAfnoE * 8;
+    zimg_bytes = 2 * kAfnoE * KZ * 2;
+    G = 0;
+    X = G + 2 * 128 * KZ * 2;
+    Zraw = X + 2 * 32768;
+    Zimg = Zraw + 2 * zraw_bytes;
+    Dst = Zimg + 2 * zimg_bytes;
+    Total = Dst + 128 * kDstRow * 4;
+  }
+};
+}  // namespace
+
+__global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
+  __shared__ uint64_t bars[IB_N];
+  __shared__ uint32_t tmem_s;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+  const InvSmem L(a.RT, a.Kc, a.KZ);
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars[IB_ZRFULL + i], 1);
+      mbar_init(&bars[IB_ZREMPTY + i], kWtWork);
+      mbar_init(&bars[IB_ZIFULL + i], kWtWork);
+      mbar_init(&bars[IB_ZIEMPTY + i], 1);
+      mbar_init(&bars[IB_XFULL + i], 1);
+      mbar_init(&bars[IB_XEMPTY + i], kWtWork);
+      mbar_init(&bars[IB_DFULL + i], 1);
+      mbar_init(&bars[IB_DEMPTY + i], kWtWork);
+    }
+    mbar_init(&bars[IB_CONST], 1);
+    fence_mbar_init();
+  }
+  if (warp == kWtCtlWarp) {
+    tmem_alloc(&tmem_s, 128);
+    tmem_relinquish();
+  }
+  // the K slots that pad the operand to a multiple of 16 stay zero in both Z' buffers
+  for (int i = tid; i < 2 * L.zimg_bytes / 16; i += kWtCta) reinterpret_cast<uint4*>(smem + L.Zimg)[i] = make_uint4(0, 0, 0, 0);
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint64_t* b = bars;
+  const int stride = gridDim.x, first = blockIdx.x;
+  const uint32_t g_bytes = 2u * 128u * (uint32_t)a.KZ * 2u;
+
+  if (warp == kWtCtlWarp) {
+    const uint32_t leader = elect_one();
+    mbar_arrive_expect_tx_p(leader, &b[IB_CONST], g_bytes);
+    bulk_g2s_p(leader, smem + L.G, a.Gimg, g_bytes, &b[IB_CONST]);
+    pdl_wait();   // Z and x are what the previous kernels wrote
+    auto load_z = [&](int tile, int s) {
+      mbar_arrive_expect_tx_p(leader, &b[IB_ZRFULL + s], (uint32_t)L.zraw_bytes);
+      bulk_g2s_p(leader, smem + L.Zraw + s * L.zraw_bytes, a.Z + (size_t)tile * a.RT * a.Kc * kAfnoE, (uint32_t)L.zraw_bytes,
+                 &b[IB_ZRFULL + s]);
+    };
+    auto load_x = [&](int tile, int s) {
+      mbar_arrive_expect_tx_p(leader, &b[IB_XFULL + s], 32768u);
+      bulk_g2s_p(leader, smem + L.X + s * 32768, a.x + (size_t)tile * kTcTile * kAfnoE, 32768u, &b[IB_XFULL + s]);
+    };
+    for (int i = 0; i < 2; ++i)
+      if (first + i * stride < a.ntiles) {
+        load_z(first + i * stride, i);
+        load_x(first + i * stride, i);
+      }
+    mbar_wait(&b[IB_CONST], 0);
+    const uint32_t idesc = idesc_bf16(128, 64);
+    const uint64_t dG = chunk_desc(smem_u32(smem + L.G), 128, 0);
+    const uint32_t g_lo = 128u * (uint32_t)a.KZ * 2u, z_lo = (uint32_t)kAfnoE * (uint32_t)a.KZ * 2u;
+    uint32_t u = 0;
+    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
+      const int s = u & 1;
+      const uint32_t ph = (u >> 1) & 1u;
+      mbar_wait(&b[IB_ZIFULL + s], ph);
+      mbar_wait(&b[IB_DEMPTY + s], ph ^ 1u);
+      tc_fence_after();
+      const uint64_t dZ = chunk_desc(smem_u32(smem + L.Zimg + s * L.zimg_bytes), kAfnoE, 0);
+      const uint32_t d = tmem_s + 64u * s;
+      uint32_t acc = 0;
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
+        const uint32_t ga = term == 1 ? g_lo : 0u, zb = term == 2 ? z_lo : 0u;
+#pragma unroll 4
+        for (int k0 = 0; k0 < a.KZ; k0 += 16) {
+          umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (k0 >> 3) * 1024), idesc, acc);
+          acc = 1;
+        }
+      }
+      umma_commit_p(leader, &b[IB_DFULL + s]);
+      umma_commit_p(leader, &b[IB_ZIEMPTY + s]);
+      if (tile + 2 * stride < a.ntiles) {      // the raw Z buffer was released when the workers had converted it
+        mbar_wait(&b[IB_ZREMPTY + s], ph);
+        load_z(tile + 2 * stride, s);
+      }
+      if (u >= 1 && tile + stride < a.ntiles) {   // the token buffer of tile u - 1 is released when that tile has been finished
+        mbar_wait(&b[IB_XEMPTY + (s ^ 1)], ((u - 1) >> 1) & 1u);
+        load_x(tile + stride, s ^ 1);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int t4 = lane >> 3, o = lane & 7;      // phase B: token of the step, channel octet
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o), g1 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o + 1);
+    const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o), e1 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o + 1);
+    const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane;     // phase A: accumulator row, column half
+    float* dstg = reinterpret_cast<float*>(smem + L.Dst);
+    const int n_el = a.RT * a.Kc * kAfnoE;
+
+    auto finish = [&](int tile, uint32_t u) {
+      const int s = u & 1;
+      const uint32_t ph = (u >> 1) & 1u;
+      mbar_wait(&b[IB_DFULL + s], ph);
+      tc_fence_after();
+      {
+        uint32_t r[32];
+        tmem_ld32(tmem_s + ((uint32_t)(q4 * 32) << 16) + 64u * s + 32u * half, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(&b[IB_DEMPTY + s]);
+        float4* drow = reinterpret_cast<float4*>(dstg + row * kDstRow + 32 * half);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          drow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                __uint_as_float(r[4 * j + 3]));
+      }
+      bar_sync(1, kWtWork);
+      mbar_wait(&b[IB_XFULL + s], ph);
+      const float* xs = reinterpret_cast<const float*>(smem + L.X + s * 32768);
+      float* orow = a.out + (size_t)tile * kTcTile * kAfnoE;
+#pragma unroll
+      for (int st = 0; st < 4; ++st) {
+        const int px = warp * 16 + st * 4 + t4;
+        const float4 x0 = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8),
+                     x1 = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8 + 4);
+        const float4 d0 = *reinterpret_cast<const float4*>(dstg + px * kDstRow + o * 8),
+                     d1 = *reinterpret_cast<const float4*>(dstg + px * kDstRow + o * 8 + 4);
+        float4 y0 = x0, y1 = x1;
+        ln8(y0, y1, g0, g1, e0, e1, a.eps);
+        float4* op = reinterpret_cast<float4*>(orow + px * kAfnoE + o * 8);
+        op[0] = make_float4(d0.x + y0.x + x0.x, d0.y + y0.y + x0.y, d0.z + y0.z + x0.z, d0.w + y0.w + x0.w);
+        op[1] = make_float4(d1.x + y1.x + x1.x, d1.y + y1.y + x1.y, d1.z + y1.z + x1.z, d1.w + y1.w + x1.w);
+      }
+      mbar_arrive(&b[IB_XEMPTY + s]);
+      bar_sync(1, kWtWork);      // the staging rows are rewritten by the next tile's first phase
+    };
+
+    uint32_t u = 0;
+    int prev = -1;
+    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
+      const int s = u & 1;
+      const uint32_t ph = (u >> 1) & 1u;
+      mbar_wait(&b[IB_ZRFULL + s], ph);
+      mbar_wait(&b[IB_ZIEMPTY + s], ph ^ 1u);
+      const float2* zr = reinterpret_cast<const float2*>(smem + L.Zraw + s * L.zraw_bytes);
+      uint8_t* zi = smem + L.Zimg + s * L.zimg_bytes;
+      const uint32_t lo_off = (uint32_t)kAfnoE * (uint32_t)a.KZ * 2u;
+      for (int i = tid; i < n_el; i += kWtWork) {      // (grid row of the tile, column) x channel -> K slots (re, im) of that channel's row
+        const int hk = i >> 6, c = i & 63, k = 2 * hk;
+        uint32_t hi, lo;
+        split2p(zr[i], hi, lo);
+        uint8_t* dst = zi + (k >> 3) * (kAfnoE * 16) + c * 16 + (k & 7) * 2;
+        *reinterpret_cast<uint32_t*>(dst) = hi;
+        *reinterpret_cast<uint32_t*>(dst + lo_off) = lo;
+      }
+      mbar_arrive(&b[IB_ZREMPTY + s]);
+      fence_async_smem();
+      mbar_arrive(&b[IB_ZIFULL + s]);
+      if (prev >= 0) finish(prev, u - 1);
+      prev = tile;
+    }
+    if (prev >= 0) finish(prev, u - 1);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWtCtlWarp) tmem_dealloc(tmem_s, 128);
+}
+
+int afno_inv_tc_smem_bytes(int RT, int Kc, int KZ) { return InvSmem(RT, Kc, KZ).Total; }
+
+int launch_afno_inv_tc(const AfnoWTcArgs& a, cudaStream_t st) {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    DLWP_CUDA(cudaGetDevice(&dev));
+    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    DLWP_CUDA(cudaFuncSetAttribute(afno_inv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  }
+  const InvSmem L(a.RT, a.Kc, a.KZ);
+  DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= a.KZ && a.KZ % 16 == 0 && L.Total <= 226 * 1024,
+               "afno_inv_tc_kernel: unsupported shape");
+  const int grid = a.ntiles < sms ? a.ntiles : sms;
+  DLWP_CUDA(launch_pdl(afno_inv_tc_kernel, dim3(grid), dim3(kWtCta), (size_t)L.Total, st, a));
+  DLWP_LAUNCHED("afno_inv_tc_kernel");
+  return DLWP_OK;
+}
+
 }  // namespace dlwp

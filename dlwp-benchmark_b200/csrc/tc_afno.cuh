@@ -62,6 +62,7 @@ struct AfnoMidArgs {
   const float *w1, *b1, *w2, *b2;   // filter weights, reference layout (fourcastnet.py:73-76), hidden_size_factor 1
   float lambda;
   int B, H, R, Kc, bs;
+  int planarA;            // A is [B, Kc, H, (re | im), 64] (what afno_fwd_tc_kernel writes) instead of interleaved complex
 };
 struct AfnoInvArgs {
   const float2* Z;        // [B, H, Kc, 64]
@@ -73,6 +74,26 @@ struct AfnoInvArgs {
   int B, H, W, Kc;
 };
 int launch_afno_fwd(const AfnoFwdArgs& a, cudaStream_t st);
+
+// ---- the W-DFTs of the token mixer on tcgen05 (tc_afno.cu) -------------------------------------------
+// Tiles of 128 tokens = RT grid rows (W = 128 / RT in {32, 64, 128}); retained columns RT * Kc * 2 <= 128.
+struct AfnoWTcArgs {
+  int ntiles, H, W, RT, Kc;
+  const float* x;         // [tokens, 64] block input
+  const float *gamma, *beta;   // norm1
+  float eps;
+  // forward: A [B, Kc, H, (re | im), 64] = W-DFT of LayerNorm(x)
+  const uint8_t* Fimg;    // [hi | lo] images of F''[(h2, kx, re | im), (h2', w)], R = 128 rows, K = 128
+  float* A;
+  // inverse: out = Re(Gw Z) + LayerNorm(x) + x
+  const uint8_t* Gimg;    // [hi | lo] images of G'[(h2, w), (h2', kx, re | im)], R = 128 rows, K = KZ
+  int KZ;                 // RT * Kc * 2 rounded up to a multiple of 16
+  const float2* Z;        // [B, H, Kc, 64]
+  float* out;             // [tokens, 64]
+};
+int launch_afno_fwd_tc(const AfnoWTcArgs& a, cudaStream_t st);
+int launch_afno_inv_tc(const AfnoWTcArgs& a, cudaStream_t st);
+int afno_inv_tc_smem_bytes(int RT, int Kc, int KZ);
 int launch_afno_mid(const AfnoMidArgs& a, cudaStream_t st);
 int launch_afno_inv(const AfnoInvArgs& a, cudaStream_t st);
 

@@ -1,5 +1,6 @@
 // Plan-side glue of the tensor-core AFNO kernels: eligibility, weight operand images
 // (reference: Block.forward / Mlp.forward, fourcastnet.py:41-57,176-193).
+#include <cmath>
 #include <vector>
 
 #include "plan.cuh"
@@ -29,6 +30,42 @@ int plan_atc_build(dlwp_plan* p) {
   p->atc_spec = d.afno_filter == DLWP_AFNO_FILTER_AFNO2D && p->gw <= 64 && p->gh <= 32 && d.n_rows >= 1 && d.n_rows <= 32 && d.n_cols >= 1 && d.n_cols <= 36 &&
                 d.hidden_size_factor == 1 && (bs == 8 || bs == 16) &&
                 p->gw % 2 == 0 && (d.n_rows * p->gh) % 2 == 0;   // bulk copies move multiples of 16 bytes
+  // W-DFTs on tcgen05: whole grid rows per 128-token tile, all retained (column, re | im) pairs of a tile in one M = 128 UMMA
+  const int W = p->gw, Kc = d.n_cols;
+  if (p->atc_spec && W <= kTcTile && kTcTile % W == 0 && (kTcTile / W) * 2 * Kc <= 128 && p->gh % (kTcTile / W) == 0) {
+    const int RT = kTcTile / W, KZ = (RT * 2 * Kc + 15) & ~15;
+    double sc = 1.0, tc = 1.0;
+    const double hw = (double)p->gh * (double)W;
+    if (d.fft_norm == DLWP_FFT_NORM_BACKWARD) tc = 1.0 / hw;
+    else if (d.fft_norm == DLWP_FFT_NORM_FORWARD) sc = 1.0 / hw;
+    else sc = tc = 1.0 / std::sqrt(hw);
+    // F''[(h2, kx, re | im), (h2', w)] = [h2 == h2'] s exp(-2 pi i kx w / W);  G'[(h2, w), (h2', kx, re | im)]: y[w] =
+    // sum_kx Re(Gw[w, kx] Z[kx]), Gw = t c_kx exp(+2 pi i kx w / W), c = 1 for the self-conjugate columns, else 2
+    std::vector<double> F((size_t)128 * 128, 0.0), G((size_t)128 * KZ, 0.0);
+    for (int h2 = 0; h2 < RT; ++h2)
+      for (int w = 0; w < W; ++w)
+        for (int kx = 0; kx < Kc; ++kx) {
+          const long long r = ((long long)kx * w) % W;
+          const double ang = 2.0 * M_PI * (double)r / (double)W;
+          const bool self_conj = (kx == 0) || (W % 2 == 0 && kx == W / 2);
+          const double ck = tc * (self_conj ? 1.0 : 2.0);
+          const int row = (h2 * Kc + kx) * 2, px = h2 * W + w;
+          F[(size_t)row * 128 + px] = sc * std::cos(ang);
+          F[(size_t)(row + 1) * 128 + px] = -sc * std::sin(ang);
+          G[(size_t)px * KZ + row] = ck * std::cos(ang);
+          G[(size_t)px * KZ + row + 1] = -ck * std::sin(ang);
+        }
+    std::vector<uint8_t> fi((size_t)2 * 128 * 128 * 2), gi((size_t)2 * 128 * KZ * 2);
+    tc_pack_images_f64(F.data(), 128, 128, 128, 128, 128, fi.data());
+    tc_pack_images_f64(G.data(), 128, KZ, KZ, 128, KZ, gi.data());
+    DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_F, fi.size()));
+    DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_G, gi.size()));
+    DLWP_CUDA(cudaMemcpy(p->atc_F, fi.data(), fi.size(), cudaMemcpyHostToDevice));
+    DLWP_CUDA(cudaMemcpy(p->atc_G, gi.data(), gi.size(), cudaMemcpyHostToDevice));
+    p->atc_RT = RT;
+    p->atc_KZ = KZ;
+    p->atc_wtc = true;
+  }
   return DLWP_OK;
 }
 
@@ -93,8 +130,16 @@ int atc_block_filter(dlwp_plan* p, int block, float* x, float* out, int B, cudaS
     if (d.use_pos_embed) DLWP_TRY(plan_need(p, "pos_embed", (int64_t)p->gh * p->gw * kAfnoE, &fa.pos));
     fa.xout = x;
   }
-  DLWP_TRY(launch_afno_fwd(fa, st));
+  AfnoWTcArgs wa{};
+  wa.ntiles = B * p->gh * p->gw / kTcTile; wa.H = p->gh; wa.W = p->gw; wa.RT = p->atc_RT; wa.Kc = d.n_cols;
+  wa.x = x; wa.gamma = g; wa.beta = be; wa.eps = d.layernorm_eps;
+  wa.Fimg = p->atc_F; wa.A = reinterpret_cast<float*>(p->specA);
+  wa.Gimg = p->atc_G; wa.KZ = p->atc_KZ; wa.Z = p->specZ; wa.out = out;
+  const bool fwd_tc = p->atc_wtc && embed == nullptr;
+  if (fwd_tc) DLWP_TRY(launch_afno_fwd_tc(wa, st));
+  else DLWP_TRY(launch_afno_fwd(fa, st));
   AfnoMidArgs ma{};
+  ma.planarA = fwd_tc ? 1 : 0;
   ma.A = p->specA; ma.Z = p->specZ; ma.Fh = p->Fh; ma.Gh = p->Gh;
   DLWP_TRY(plan_need(p, bname(block, ".filter.w1"), (int64_t)2 * nb * bs * bs, &ma.w1));
   DLWP_TRY(plan_need(p, bname(block, ".filter.b1"), (int64_t)2 * nb * bs, &ma.b1));
@@ -103,6 +148,7 @@ int atc_block_filter(dlwp_plan* p, int block, float* x, float* out, int B, cudaS
   ma.lambda = d.sparsity_threshold;
   ma.B = B; ma.H = p->gh; ma.R = d.n_rows; ma.Kc = d.n_cols; ma.bs = bs;
   DLWP_TRY(launch_afno_mid(ma, st));
+  if (p->atc_wtc && afno_inv_tc_smem_bytes(p->atc_RT, d.n_cols, p->atc_KZ) <= 226 * 1024) return launch_afno_inv_tc(wa, st);
   AfnoInvArgs ia{p->specZ, x, out, p->Gw, g, be, d.layernorm_eps, B, p->gh, p->gw, d.n_cols};
   return launch_afno_inv(ia, st);
 }
