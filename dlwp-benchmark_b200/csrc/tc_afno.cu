@@ -232,15 +232,18 @@ int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
 // =============================================================================================
 namespace {
 constexpr int kWtWork = 256, kWtCta = kWtWork + 32, kWtCtlWarp = kWtWork / 32;
-enum { WB_XFULL = 0, WB_XEMPTY = 2, WB_YFULL = 4, WB_YEMPTY = 6, WB_DFULL = 8, WB_DEMPTY = 10, WB_CONST = 12, WB_N = 13 };
+enum { WB_XFULL = 0, WB_XEMPTY = 3, WB_YFULL = 6, WB_YEMPTY = 8, WB_DFULL = 10, WB_DEMPTY = 12, WB_CONST = 14, WB_N = 15 };
+constexpr int kXStages = 3;      // token tiles in flight ahead of the LayerNorm (HBM latency against ~1 us per tile)
 struct FwdSmem {
-  static constexpr int F = 0, X = F + 2 * 128 * 128 * 2, Y = X + 2 * 32768, Total = Y + 2 * 32768;
+  static constexpr int F = 0, X = F + 2 * 128 * 128 * 2, Y = X + kXStages * 32768, Total = Y + 2 * 32768;
 };
 
 __device__ __forceinline__ void wt_init_barriers(uint64_t* b) {
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < kXStages; ++i) {
     mbar_init(&b[WB_XFULL + i], 1);
     mbar_init(&b[WB_XEMPTY + i], kWtWork);
+  }
+  for (int i = 0; i < 2; ++i) {
     mbar_init(&b[WB_YFULL + i], kWtWork);
     mbar_init(&b[WB_YEMPTY + i], 1);
     mbar_init(&b[WB_DFULL + i], 1);
@@ -297,8 +300,9 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
       mbar_arrive_expect_tx_p(leader, &b[WB_XFULL + s], 32768u);
       bulk_g2s_p(leader, smem + FwdSmem::X + s * 32768, a.x + (size_t)tile * kTcTile * kAfnoE, 32768u, &b[WB_XFULL + s]);
     };
-    for (int i = 0; i < 2; ++i)
-      if (first + i * stride < a.ntiles) load_x(first + i * stride, i);
+    const bool embed = a.ngrp > 0;      // the workers compute the tokens themselves
+    for (int i = 0; i < kXStages; ++i)
+      if (!embed && first + i * stride < a.ntiles) load_x(first + i * stride, i);
     mbar_wait(&b[WB_CONST], 0);
     const uint32_t idesc = idesc_bf16(128, 64) | kIdescBMnMajor;
     const uint64_t dF = chunk_desc(smem_u32(smem + FwdSmem::F), 128, 0);
@@ -306,6 +310,11 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       const uint32_t ph = (u >> 1) & 1u;
+      if (!embed && u >= 1 && tile + (kXStages - 1) * stride < a.ntiles) {   // the stage tile u - 1 was read from is free
+        const int xs = (u - 1) % kXStages;
+        mbar_wait(&b[WB_XEMPTY + xs], ((u - 1) / kXStages) & 1u);
+        load_x(tile + (kXStages - 1) * stride, xs);
+      }
       mbar_wait(&b[WB_YFULL + s], ph);
       mbar_wait(&b[WB_DEMPTY + s], ph ^ 1u);
       tc_fence_after();
@@ -321,10 +330,6 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
       }
       umma_commit_p(leader, &b[WB_DFULL + s]);
       umma_commit_p(leader, &b[WB_YEMPTY + s]);
-      if (tile + 2 * stride < a.ntiles) {
-        mbar_wait(&b[WB_XEMPTY + s], ph);
-        load_x(tile + 2 * stride, s);
-      }
       __syncwarp();
     }
   } else {
@@ -352,21 +357,92 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
                                __uint_as_float(r[4 * j + 3]));
       }
     };
+    // patch embedding (first block): weights transposed to [Cin][64] and the tile's input rows [Cin][128] live in the
+    // (otherwise unused) token staging area
+    const bool embed = a.ngrp > 0;
+    float* sWe = reinterpret_cast<float*>(smem + FwdSmem::X);
+    float* sIn = sWe + 16 * kAfnoE;
+    float4 eb0 = make_float4(0.f, 0.f, 0.f, 0.f), eb1 = eb0;
+    if (embed) {
+      for (int i = tid; i < a.Cin * kAfnoE; i += kWtWork) sWe[i] = a.We[(i & 63) * a.Cin + (i >> 6)];
+      eb0 = __ldg(reinterpret_cast<const float4*>(a.be) + 2 * o);
+      eb1 = __ldg(reinterpret_cast<const float4*>(a.be) + 2 * o + 1);
+    }
+    pdl_wait();   // the step input (embedding) is what earlier kernels wrote
+    const int HW = a.H * a.W;
     uint32_t u = 0;
     int prev = -1;
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       const uint32_t ph = (u >> 1) & 1u;
-      mbar_wait(&b[WB_XFULL + s], ph);
       float4 v[4][2];
-      const float* xs = reinterpret_cast<const float*>(smem + FwdSmem::X + s * 32768);
+      if (embed) {
+        const long long p0 = (long long)tile * kTcTile;
+        const long long bb = p0 / HW, pix0 = p0 - bb * HW;      // a tile never straddles samples
+        // gather x_t from the NCHW sources (fourcastnet.py:294-307): every global load of the tile is issued before
+        // the first one is used
+        float gv[8];
 #pragma unroll
-      for (int st = 0; st < 4; ++st) {
-        const int px = warp * 16 + st * 4 + t4;
-        v[st][0] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8);
-        v[st][1] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8 + 4);
+        for (int j = 0; j < 8; ++j) {
+          const int i = tid + j * kWtWork;
+          const int k = i >> 7, px = i & 127;
+          int ch = k;
+          float val = 0.f;
+          if (i < a.Cin * kTcTile) {
+#pragma unroll
+            for (int gi = 0; gi < 4; ++gi)
+              if (gi < a.ngrp) {
+                if (ch >= 0 && ch < a.grp[gi].nch) val = a.grp[gi].base[bb * a.grp[gi].bstride + (long long)ch * HW + pix0 + px];
+                ch -= a.grp[gi].nch;
+              }
+          }
+          gv[j] = val;
+        }
+        float4 pq[4][2];
+#pragma unroll
+        for (int st = 0; st < 4; ++st) {
+          const int px = warp * 16 + st * 4 + t4;
+          pq[st][0] = pq[st][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (a.pos != nullptr) {
+            pq[st][0] = __ldg(reinterpret_cast<const float4*>(a.pos + (pix0 + px) * kAfnoE + o * 8));
+            pq[st][1] = __ldg(reinterpret_cast<const float4*>(a.pos + (pix0 + px) * kAfnoE + o * 8 + 4));
+          }
+        }
+        bar_sync(1, kWtWork);      // the previous tile's input rows have been consumed
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (tid + j * kWtWork < a.Cin * kTcTile) sIn[tid + j * kWtWork] = gv[j];
+        bar_sync(1, kWtWork);
+        float* xo = a.xout + (size_t)tile * kTcTile * kAfnoE;
+#pragma unroll
+        for (int st = 0; st < 4; ++st) {
+          const int px = warp * 16 + st * 4 + t4;
+          float4 a0 = make_float4(eb0.x + pq[st][0].x, eb0.y + pq[st][0].y, eb0.z + pq[st][0].z, eb0.w + pq[st][0].w);
+          float4 a1 = make_float4(eb1.x + pq[st][1].x, eb1.y + pq[st][1].y, eb1.z + pq[st][1].z, eb1.w + pq[st][1].w);
+          for (int k = 0; k < a.Cin; ++k) {
+            const float xin = sIn[k * kTcTile + px];
+            const float4 w0 = *reinterpret_cast<const float4*>(sWe + k * kAfnoE + o * 8),
+                         w1 = *reinterpret_cast<const float4*>(sWe + k * kAfnoE + o * 8 + 4);
+            a0.x = fmaf(xin, w0.x, a0.x); a0.y = fmaf(xin, w0.y, a0.y); a0.z = fmaf(xin, w0.z, a0.z); a0.w = fmaf(xin, w0.w, a0.w);
+            a1.x = fmaf(xin, w1.x, a1.x); a1.y = fmaf(xin, w1.y, a1.y); a1.z = fmaf(xin, w1.z, a1.z); a1.w = fmaf(xin, w1.w, a1.w);
+          }
+          *reinterpret_cast<float4*>(xo + px * kAfnoE + o * 8) = a0;
+          *reinterpret_cast<float4*>(xo + px * kAfnoE + o * 8 + 4) = a1;
+          v[st][0] = a0;
+          v[st][1] = a1;
+        }
+      } else {
+        const int xst = u % kXStages;
+        mbar_wait(&b[WB_XFULL + xst], (u / kXStages) & 1u);
+        const float* xs = reinterpret_cast<const float*>(smem + FwdSmem::X + xst * 32768);
+#pragma unroll
+        for (int st = 0; st < 4; ++st) {
+          const int px = warp * 16 + st * 4 + t4;
+          v[st][0] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8);
+          v[st][1] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8 + 4);
+        }
+        mbar_arrive(&b[WB_XEMPTY + xst]);
       }
-      mbar_arrive(&b[WB_XEMPTY + s]);
       mbar_wait(&b[WB_YEMPTY + s], ph ^ 1u);
       uint8_t* ys = smem + FwdSmem::Y + s * 32768;
 #pragma unroll
@@ -402,6 +478,7 @@ int launch_afno_fwd_tc(const AfnoWTcArgs& a, cudaStream_t st) {
     DLWP_CUDA(cudaFuncSetAttribute(afno_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::Total));
   }
   DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= 128, "afno_fwd_tc_kernel: unsupported shape");
+  DLWP_REQUIRE(a.ngrp == 0 || (a.Cin >= 1 && a.Cin <= 16 && a.We && a.be && a.xout), "afno_fwd_tc_kernel: bad embedding arguments");
   const int grid = a.ntiles < sms ? a.ntiles : sms;
   DLWP_CUDA(launch_pdl(afno_fwd_tc_kernel, dim3(grid), dim3(kWtCta), (size_t)FwdSmem::Total, st, a));
   DLWP_LAUNCHED("afno_fwd_tc_kernel");

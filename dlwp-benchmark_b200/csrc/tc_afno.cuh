@@ -85,6 +85,15 @@ struct AfnoWTcArgs {
   // forward: A [B, Kc, H, (re | im), 64] = W-DFT of LayerNorm(x)
   const uint8_t* Fimg;    // [hi | lo] images of F''[(h2, kx, re | im), (h2', w)], R = 128 rows, K = 128
   float* A;
+  // forward, first block with 1x1 patches: x is not read but computed from the NCHW sources of the step (patch embedding +
+  // position embedding, fourcastnet.py:285-289,537-542) and stored to `xout`
+  SrcGroup grp[4];
+  int ngrp;               // 0: read x
+  int Cin;                // <= 16
+  const float* We;        // [64, Cin] patch_embed.proj.weight
+  const float* be;        // [64]
+  const float* pos;       // [H * W, 64] or null
+  float* xout;
   // inverse: out = Re(Gw Z) + LayerNorm(x) + x
   const uint8_t* Gimg;    // [hi | lo] images of G'[(h2, w), (h2', kx, re | im)], R = 128 rows, K = KZ
   int KZ;                 // RT * Kc * 2 rounded up to a multiple of 16
