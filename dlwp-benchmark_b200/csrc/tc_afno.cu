@@ -7,6 +7,13 @@ namespace dlwp {
 
 using namespace tc;
 
+#ifdef DLWP_TRACE
+__device__ unsigned long long* g_trace_afno = nullptr;   // [16 tiles][8 events] clock64 stamps of CTA 0 (tools/trace_afno.py)
+#define TRA(u, ev) do { if (g_trace_afno && blockIdx.x == 0 && (u) < 16) g_trace_afno[(u) * 8 + (ev)] = clock64(); } while (0)
+#else
+#define TRA(u, ev) do {} while (0)
+#endif
+
 // =============================================================================================
 // afno_mlp_kernel: out = x + fc2(GELU(fc1(LN(x))))  on 128-token tiles, persistent, one CTA per SM
 //   warps 0-7 : epilogue group (two threads per token: channel halves)     warp 8 : control warp
@@ -224,25 +231,22 @@ int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
 // (= RT grid rows), persistent, one CTA per SM: 8 worker warps + 1 control warp.
 //
 // afno_fwd_tc_kernel:  A[(h2, kx, re | im), c] = sum_px F''[(h2, kx, re | im), px] * LayerNorm(x)[px, c]
-//   The fp32 token tile arrives by one bulk copy; the workers normalise it (a warp takes four tokens per
-//   step: eight lanes per token, eight channels per lane, statistics by shuffles) and write it as a
-//   split-bf16 image that the tensor core reads in place as an MN-major B operand (tokens = K rows);
+//   Two worker threads per token load its channels (32 each, the next tile's loads in flight under this
+//   tile's work), normalise them (pairwise-combined statistics) and write the tile as a split-bf16 image
+//   that the tensor core reads in place as an MN-major B operand (tokens = K rows; a warp's lanes are 32
+//   consecutive tokens, so every operand store is 512 contiguous bytes);
 //   the accumulator rows (one retained column of one grid row, Re or Im) go from TMEM lanes to their
 //   256-byte rows of the planar spectrum one tile late, under the next tile's LayerNorm.
 // =============================================================================================
 namespace {
 constexpr int kWtWork = 256, kWtCta = kWtWork + 32, kWtCtlWarp = kWtWork / 32;
-enum { WB_XFULL = 0, WB_XEMPTY = 3, WB_YFULL = 6, WB_YEMPTY = 8, WB_DFULL = 10, WB_DEMPTY = 12, WB_CONST = 14, WB_N = 15 };
-constexpr int kXStages = 3;      // token tiles in flight ahead of the LayerNorm (HBM latency against ~1 us per tile)
+enum { WB_YFULL = 0, WB_YEMPTY = 2, WB_DFULL = 4, WB_DEMPTY = 6, WB_CONST = 8, WB_N = 9 };
 struct FwdSmem {
-  static constexpr int F = 0, X = F + 2 * 128 * 128 * 2, Y = X + kXStages * 32768, Total = Y + 2 * 32768;
+  static constexpr int F = 0, Y = F + 2 * 128 * 128 * 2, Stats = Y + 2 * 32768, GB = Stats + 2 * 2 * 128 * 8, Emb = GB + 2 * kAfnoE * 4,
+                       Total = Emb + (16 * kAfnoE + 16 * kTcTile + kAfnoE) * 4;
 };
 
 __device__ __forceinline__ void wt_init_barriers(uint64_t* b) {
-  for (int i = 0; i < kXStages; ++i) {
-    mbar_init(&b[WB_XFULL + i], 1);
-    mbar_init(&b[WB_XEMPTY + i], kWtWork);
-  }
   for (int i = 0; i < 2; ++i) {
     mbar_init(&b[WB_YFULL + i], kWtWork);
     mbar_init(&b[WB_YEMPTY + i], 1);
@@ -285,6 +289,19 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
     tmem_alloc(&tmem_s, 128);
     tmem_relinquish();
   }
+  float* sGB = reinterpret_cast<float*>(smem + FwdSmem::GB);      // norm1 weight [64], bias [64]
+  if (tid < kAfnoE) {
+    sGB[tid] = a.gamma[tid];
+    sGB[kAfnoE + tid] = a.beta[tid];
+  }
+  const bool embed = a.ngrp > 0;      // first block: the tokens are computed from the step input, not read
+  float* sWe = reinterpret_cast<float*>(smem + FwdSmem::Emb);     // [Cin][64] embedding weights, transposed
+  float* sIn = sWe + 16 * kAfnoE;                                 // [Cin][128] input rows of the tile
+  float* sBe = sIn + 16 * kTcTile;                                // [64] embedding bias
+  if (embed) {
+    for (int i = tid; i < a.Cin * kAfnoE; i += kWtCta) sWe[i] = a.We[(i & 63) * a.Cin + (i >> 6)];
+    if (tid < kAfnoE) sBe[tid] = a.be[tid];
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -295,14 +312,6 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
     const uint32_t leader = elect_one();
     mbar_arrive_expect_tx_p(leader, &b[WB_CONST], 65536u);
     bulk_g2s_p(leader, smem + FwdSmem::F, a.Fimg, 65536u, &b[WB_CONST]);
-    pdl_wait();   // x is what the previous kernel wrote
-    auto load_x = [&](int tile, int s) {
-      mbar_arrive_expect_tx_p(leader, &b[WB_XFULL + s], 32768u);
-      bulk_g2s_p(leader, smem + FwdSmem::X + s * 32768, a.x + (size_t)tile * kTcTile * kAfnoE, 32768u, &b[WB_XFULL + s]);
-    };
-    const bool embed = a.ngrp > 0;      // the workers compute the tokens themselves
-    for (int i = 0; i < kXStages; ++i)
-      if (!embed && first + i * stride < a.ntiles) load_x(first + i * stride, i);
     mbar_wait(&b[WB_CONST], 0);
     const uint32_t idesc = idesc_bf16(128, 64) | kIdescBMnMajor;
     const uint64_t dF = chunk_desc(smem_u32(smem + FwdSmem::F), 128, 0);
@@ -310,13 +319,9 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       const uint32_t ph = (u >> 1) & 1u;
-      if (!embed && u >= 1 && tile + (kXStages - 1) * stride < a.ntiles) {   // the stage tile u - 1 was read from is free
-        const int xs = (u - 1) % kXStages;
-        mbar_wait(&b[WB_XEMPTY + xs], ((u - 1) / kXStages) & 1u);
-        load_x(tile + (kXStages - 1) * stride, xs);
-      }
       mbar_wait(&b[WB_YFULL + s], ph);
       mbar_wait(&b[WB_DEMPTY + s], ph ^ 1u);
+      if (lane == 0) TRA(u, 6);
       tc_fence_after();
       // B: 8 x 8 core matrices 128 B apart along tokens (K), 2048 B along channels (N)
       const uint64_t dY = smem_desc(smem_u32(smem + FwdSmem::Y + s * 32768), 128, 2048);
@@ -330,17 +335,21 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
       }
       umma_commit_p(leader, &b[WB_DFULL + s]);
       umma_commit_p(leader, &b[WB_YEMPTY + s]);
+      if (lane == 0) TRA(u, 7);
       __syncwarp();
     }
   } else {
-    const int t4 = lane >> 3, o = lane & 7;      // LayerNorm: token of the step, channel octet
-    const float4 g0 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o), g1 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o + 1);
-    const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o), e1 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o + 1);
-    const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane;     // drain: accumulator row, column half
+    // two threads per token (32 channels each): LayerNorm without a transposition, and the operand image is
+    // written with 512 contiguous bytes per warp store (a warp's lanes are 32 consecutive tokens)
+    const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane, c0 = 32 * half;
+    float2* stats = reinterpret_cast<float2*>(smem + FwdSmem::Stats);   // [tile parity][half][row] = (mean, centred sum of squares)
     const int rows_used = a.RT * 2 * a.Kc;
+    const int HW = a.H * a.W;
+
     auto drain = [&](int tile, uint32_t u) {
       const int s = u & 1;
       mbar_wait(&b[WB_DFULL + s], (u >> 1) & 1u);
+      if (tid == 0) TRA(u + 1, 4);
       tc_fence_after();
       uint32_t r[32];
       tmem_ld32(tmem_s + ((uint32_t)(q4 * 32) << 16) + 64u * s + 32u * half, r);
@@ -350,116 +359,121 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
       if (row < rows_used) {
         const int h2 = row / (2 * a.Kc), rem = row - h2 * 2 * a.Kc, kx = rem >> 1, reim = rem & 1;
         const int grow = tile * a.RT + h2, bb = grow / a.H, h = grow - bb * a.H;
-        float4* dst = reinterpret_cast<float4*>(a.A + ((((size_t)bb * a.Kc + kx) * a.H + h) * 2 + reim) * kAfnoE + 32 * half);
+        float4* dst = reinterpret_cast<float4*>(a.A + ((((size_t)bb * a.Kc + kx) * a.H + h) * 2 + reim) * kAfnoE + c0);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
                                __uint_as_float(r[4 * j + 3]));
       }
     };
-    // patch embedding (first block): weights transposed to [Cin][64] and the tile's input rows [Cin][128] live in the
-    // (otherwise unused) token staging area
-    const bool embed = a.ngrp > 0;
-    float* sWe = reinterpret_cast<float*>(smem + FwdSmem::X);
-    float* sIn = sWe + 16 * kAfnoE;
-    float4 eb0 = make_float4(0.f, 0.f, 0.f, 0.f), eb1 = eb0;
-    if (embed) {
-      for (int i = tid; i < a.Cin * kAfnoE; i += kWtWork) sWe[i] = a.We[(i & 63) * a.Cin + (i >> 6)];
-      eb0 = __ldg(reinterpret_cast<const float4*>(a.be) + 2 * o);
-      eb1 = __ldg(reinterpret_cast<const float4*>(a.be) + 2 * o + 1);
-    }
-    pdl_wait();   // the step input (embedding) is what earlier kernels wrote
-    const int HW = a.H * a.W;
+    auto load_x = [&](int tile, float4 (&x)[8]) {
+      const float4* src = reinterpret_cast<const float4*>(a.x + ((size_t)tile * kTcTile + row) * kAfnoE + c0);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] = src[j];
+    };
+    // first block: x = patch embedding + position embedding of the step input (fourcastnet.py:285-289,294-307), stored to xout
+    auto embed_x = [&](int tile, float4 (&x)[8]) {
+      const long long p0 = (long long)tile * kTcTile;
+      const long long bb = p0 / HW, pix0 = p0 - bb * HW;      // a tile never straddles samples
+      float gv[8];      // every global load of the tile is issued before the first one is used
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i = tid + j * kWtWork;
+        const int k = i >> 7, px = i & 127;
+        int ch = k;
+        float val = 0.f;
+        if (i < a.Cin * kTcTile) {
+#pragma unroll
+          for (int gi = 0; gi < 4; ++gi)
+            if (gi < a.ngrp) {
+              if (ch >= 0 && ch < a.grp[gi].nch) val = a.grp[gi].base[bb * a.grp[gi].bstride + (long long)ch * HW + pix0 + px];
+              ch -= a.grp[gi].nch;
+            }
+        }
+        gv[j] = val;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 bq = *reinterpret_cast<const float4*>(sBe + c0 + 4 * j);
+        x[j] = bq;
+        if (a.pos != nullptr) {
+          const float4 pq = __ldg(reinterpret_cast<const float4*>(a.pos + (pix0 + row) * kAfnoE + c0) + j);
+          x[j] = make_float4(bq.x + pq.x, bq.y + pq.y, bq.z + pq.z, bq.w + pq.w);
+        }
+      }
+      bar_sync(1, kWtWork);      // the previous tile's input rows have been consumed
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (tid + j * kWtWork < a.Cin * kTcTile) sIn[tid + j * kWtWork] = gv[j];
+      bar_sync(1, kWtWork);
+      for (int k = 0; k < a.Cin; ++k) {
+        const float xin = sIn[k * kTcTile + row];
+        const float4* wq = reinterpret_cast<const float4*>(sWe + k * kAfnoE + c0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 w = wq[j];
+          x[j].x = fmaf(xin, w.x, x[j].x); x[j].y = fmaf(xin, w.y, x[j].y);
+          x[j].z = fmaf(xin, w.z, x[j].z); x[j].w = fmaf(xin, w.w, x[j].w);
+        }
+      }
+      float4* xo = reinterpret_cast<float4*>(a.xout + ((size_t)tile * kTcTile + row) * kAfnoE + c0);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) xo[j] = x[j];
+    };
+
+    pdl_wait();   // x / the step input are what earlier kernels wrote
+    float4 x[8];
+    if (first < a.ntiles && !embed) load_x(first, x);
     uint32_t u = 0;
     int prev = -1;
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       const uint32_t ph = (u >> 1) & 1u;
-      float4 v[4][2];
-      if (embed) {
-        const long long p0 = (long long)tile * kTcTile;
-        const long long bb = p0 / HW, pix0 = p0 - bb * HW;      // a tile never straddles samples
-        // gather x_t from the NCHW sources (fourcastnet.py:294-307): every global load of the tile is issued before
-        // the first one is used
-        float gv[8];
+      if (tid == 0) TRA(u, 0);
+      if (embed) embed_x(tile, x);
+      // the statistics are computed here, not where the loads were issued
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int i = tid + j * kWtWork;
-          const int k = i >> 7, px = i & 127;
-          int ch = k;
-          float val = 0.f;
-          if (i < a.Cin * kTcTile) {
+      for (int j = 0; j < 8; ++j) asm volatile("" : "+f"(x[j].x), "+f"(x[j].y), "+f"(x[j].z), "+f"(x[j].w));
+      if (tid == 0) TRA(u, 1);
+      float sum = 0.f;
 #pragma unroll
-            for (int gi = 0; gi < 4; ++gi)
-              if (gi < a.ngrp) {
-                if (ch >= 0 && ch < a.grp[gi].nch) val = a.grp[gi].base[bb * a.grp[gi].bstride + (long long)ch * HW + pix0 + px];
-                ch -= a.grp[gi].nch;
-              }
-          }
-          gv[j] = val;
-        }
-        float4 pq[4][2];
+      for (int j = 0; j < 8; ++j) sum += (x[j].x + x[j].y) + (x[j].z + x[j].w);
+      const float mh = sum * (1.0f / 32.0f);
+      float q = 0.f;
 #pragma unroll
-        for (int st = 0; st < 4; ++st) {
-          const int px = warp * 16 + st * 4 + t4;
-          pq[st][0] = pq[st][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (a.pos != nullptr) {
-            pq[st][0] = __ldg(reinterpret_cast<const float4*>(a.pos + (pix0 + px) * kAfnoE + o * 8));
-            pq[st][1] = __ldg(reinterpret_cast<const float4*>(a.pos + (pix0 + px) * kAfnoE + o * 8 + 4));
-          }
-        }
-        bar_sync(1, kWtWork);      // the previous tile's input rows have been consumed
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (tid + j * kWtWork < a.Cin * kTcTile) sIn[tid + j * kWtWork] = gv[j];
-        bar_sync(1, kWtWork);
-        float* xo = a.xout + (size_t)tile * kTcTile * kAfnoE;
-#pragma unroll
-        for (int st = 0; st < 4; ++st) {
-          const int px = warp * 16 + st * 4 + t4;
-          float4 a0 = make_float4(eb0.x + pq[st][0].x, eb0.y + pq[st][0].y, eb0.z + pq[st][0].z, eb0.w + pq[st][0].w);
-          float4 a1 = make_float4(eb1.x + pq[st][1].x, eb1.y + pq[st][1].y, eb1.z + pq[st][1].z, eb1.w + pq[st][1].w);
-          for (int k = 0; k < a.Cin; ++k) {
-            const float xin = sIn[k * kTcTile + px];
-            const float4 w0 = *reinterpret_cast<const float4*>(sWe + k * kAfnoE + o * 8),
-                         w1 = *reinterpret_cast<const float4*>(sWe + k * kAfnoE + o * 8 + 4);
-            a0.x = fmaf(xin, w0.x, a0.x); a0.y = fmaf(xin, w0.y, a0.y); a0.z = fmaf(xin, w0.z, a0.z); a0.w = fmaf(xin, w0.w, a0.w);
-            a1.x = fmaf(xin, w1.x, a1.x); a1.y = fmaf(xin, w1.y, a1.y); a1.z = fmaf(xin, w1.z, a1.z); a1.w = fmaf(xin, w1.w, a1.w);
-          }
-          *reinterpret_cast<float4*>(xo + px * kAfnoE + o * 8) = a0;
-          *reinterpret_cast<float4*>(xo + px * kAfnoE + o * 8 + 4) = a1;
-          v[st][0] = a0;
-          v[st][1] = a1;
-        }
-      } else {
-        const int xst = u % kXStages;
-        mbar_wait(&b[WB_XFULL + xst], (u / kXStages) & 1u);
-        const float* xs = reinterpret_cast<const float*>(smem + FwdSmem::X + xst * 32768);
-#pragma unroll
-        for (int st = 0; st < 4; ++st) {
-          const int px = warp * 16 + st * 4 + t4;
-          v[st][0] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8);
-          v[st][1] = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8 + 4);
-        }
-        mbar_arrive(&b[WB_XEMPTY + xst]);
+      for (int j = 0; j < 8; ++j) {
+        const float d0 = x[j].x - mh, d1 = x[j].y - mh, d2 = x[j].z - mh, d3 = x[j].w - mh;
+        q = fmaf(d0, d0, q); q = fmaf(d1, d1, q); q = fmaf(d2, d2, q); q = fmaf(d3, d3, q);
       }
+      float2* st = stats + s * 256;
+      st[half * 128 + row] = make_float2(mh, q);
+      bar_sync(2, kWtWork);
+      const float2 o = st[(half ^ 1) * 128 + row];
+      const float mean = 0.5f * (mh + o.x), dm = mh - o.x;
+      const float rstd = rsqrtf((q + o.y + 16.0f * dm * dm) * (1.0f / 64.0f) + a.eps);
       mbar_wait(&b[WB_YEMPTY + s], ph ^ 1u);
-      uint8_t* ys = smem + FwdSmem::Y + s * 32768;
+      if (tid == 0) TRA(u, 2);
+      uint8_t* yd = smem + FwdSmem::Y + s * 32768 + (4 * half) * 2048 + row * 16;
 #pragma unroll
-      for (int st = 0; st < 4; ++st) {
-        const int px = warp * 16 + st * 4 + t4;
-        ln8(v[st][0], v[st][1], g0, g1, e0, e1, a.eps);
+      for (int j = 0; j < 4; ++j) {     // 8 channels = one 16-byte unit of the chunk-major image
+        const float4 ga = *reinterpret_cast<const float4*>(sGB + c0 + 8 * j), gb = *reinterpret_cast<const float4*>(sGB + c0 + 8 * j + 4);
+        const float4 ba = *reinterpret_cast<const float4*>(sGB + kAfnoE + c0 + 8 * j),
+                     bb = *reinterpret_cast<const float4*>(sGB + kAfnoE + c0 + 8 * j + 4);
+        const float4 v0 = x[2 * j], v1 = x[2 * j + 1];
         uint32_t h[4], l[4];
-        split2p(make_float2(v[st][0].x, v[st][0].y), h[0], l[0]);
-        split2p(make_float2(v[st][0].z, v[st][0].w), h[1], l[1]);
-        split2p(make_float2(v[st][1].x, v[st][1].y), h[2], l[2]);
-        split2p(make_float2(v[st][1].z, v[st][1].w), h[3], l[3]);
-        *reinterpret_cast<uint4*>(ys + o * 2048 + px * 16) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4*>(ys + 16384 + o * 2048 + px * 16) = make_uint4(l[0], l[1], l[2], l[3]);
+        split2p(make_float2(fmaf((v0.x - mean) * rstd, ga.x, ba.x), fmaf((v0.y - mean) * rstd, ga.y, ba.y)), h[0], l[0]);
+        split2p(make_float2(fmaf((v0.z - mean) * rstd, ga.z, ba.z), fmaf((v0.w - mean) * rstd, ga.w, ba.w)), h[1], l[1]);
+        split2p(make_float2(fmaf((v1.x - mean) * rstd, gb.x, bb.x), fmaf((v1.y - mean) * rstd, gb.y, bb.y)), h[2], l[2]);
+        split2p(make_float2(fmaf((v1.z - mean) * rstd, gb.z, bb.z), fmaf((v1.w - mean) * rstd, gb.w, bb.w)), h[3], l[3]);
+        *reinterpret_cast<uint4*>(yd + j * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(yd + 16384 + j * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
       }
+      if (!embed && tile + stride < a.ntiles) load_x(tile + stride, x);   // in flight under the fence, the drain and the MMAs
       fence_async_smem();
       mbar_arrive(&b[WB_YFULL + s]);
+      if (tid == 0) TRA(u, 3);
       if (prev >= 0) drain(prev, u - 1);
+      if (tid == 0) TRA(u, 5);
       prev = tile;
     }
     if (prev >= 0) drain(prev, u - 1);
@@ -699,3 +713,9 @@ int launch_afno_inv_tc(const AfnoWTcArgs& a, cudaStream_t st) {
 }
 
 }  // namespace dlwp
+
+#ifdef DLWP_TRACE
+extern "C" int dlwp_debug_set_trace_afno(unsigned long long* p) {
+  return cudaMemcpyToSymbol(dlwp::g_trace_afno, &p, sizeof(p)) == cudaSuccess ? 0 : -2;
+}
+#endif
