@@ -228,34 +228,27 @@ int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
 
 // =============================================================================================
 // The truncated W-DFTs of the AFNO token mixer on tcgen05 (fourcastnet.py:84-85,124-127), 128-token tiles
-// (= RT grid rows), persistent, one CTA per SM: 8 worker warps + 1 control warp.
+// (= RT grid rows), persistent, one CTA per SM.
 //
 // afno_fwd_tc_kernel:  A[(h2, kx, re | im), c] = sum_px F''[(h2, kx, re | im), px] * LayerNorm(x)[px, c]
-//   Two worker threads per token load its channels (32 each, the next tile's loads in flight under this
-//   tile's work), normalise them (pairwise-combined statistics) and write the tile as a split-bf16 image
-//   that the tensor core reads in place as an MN-major B operand (tokens = K rows; a warp's lanes are 32
-//   consecutive tokens, so every operand store is 512 contiguous bytes);
-//   the accumulator rows (one retained column of one grid row, Re or Im) go from TMEM lanes to their
-//   256-byte rows of the planar spectrum one tile late, under the next tile's LayerNorm.
+//   Three independent worker groups of 128 threads take the CTA's tiles in turn, one thread per token: the
+//   token's 64 channels come straight from global memory into registers (the next tile's loads are issued
+//   before this tile's accumulator is drained), LayerNorm is thread-local, and the normalised token goes
+//   into the group's split-bf16 image, which the tensor core reads in place as an MN-major B operand
+//   (tokens = K rows; a warp's lanes are 32 consecutive tokens, so every operand store is 512 contiguous
+//   bytes).  A proxy fence waits for the global accesses its thread has in flight, so a group stalls for
+//   about a memory latency per tile: the other two groups work meanwhile.  The control warp issues the
+//   UMMAs of the tiles in order; a group drains its accumulator rows (one retained column of one grid
+//   row, Re or Im) from TMEM lanes to their 256-byte rows of the planar spectrum.
 // =============================================================================================
 namespace {
-constexpr int kWtWork = 256, kWtCta = kWtWork + 32, kWtCtlWarp = kWtWork / 32;
-enum { WB_YFULL = 0, WB_YEMPTY = 2, WB_DFULL = 4, WB_DEMPTY = 6, WB_CONST = 8, WB_N = 9 };
+constexpr int kFwGroups = 3, kFwGrp = 128, kFwWork = kFwGroups * kFwGrp, kFwCta = kFwWork + 32, kFwCtlWarp = kFwWork / 32;
+enum { WB_YFULL = 0, WB_DFULL = kFwGroups, WB_CONST = 2 * kFwGroups, WB_N = 2 * kFwGroups + 1 };
 struct FwdSmem {
-  static constexpr int F = 0, Y = F + 2 * 128 * 128 * 2, Stats = Y + 2 * 32768, GB = Stats + 2 * 2 * 128 * 8, Emb = GB + 2 * kAfnoE * 4,
-                       Total = Emb + (16 * kAfnoE + 16 * kTcTile + kAfnoE) * 4;
+  static constexpr int F = 0, Y = F + 2 * 128 * 128 * 2, GB = Y + kFwGroups * 32768, Emb = GB + 2 * kAfnoE * 4,
+                       Total = Emb + (16 * kAfnoE + kAfnoE) * 4;
 };
-
-__device__ __forceinline__ void wt_init_barriers(uint64_t* b) {
-  for (int i = 0; i < 2; ++i) {
-    mbar_init(&b[WB_YFULL + i], kWtWork);
-    mbar_init(&b[WB_YEMPTY + i], 1);
-    mbar_init(&b[WB_DFULL + i], 1);
-    mbar_init(&b[WB_DEMPTY + i], kWtWork);
-  }
-  mbar_init(&b[WB_CONST], 1);
-  fence_mbar_init();
-}
+constexpr int kWtWork = 256, kWtCta = kWtWork + 32, kWtCtlWarp = kWtWork / 32;     // afno_inv_tc_kernel
 
 // LayerNorm of one token spread over eight lanes (eight channels each); returns xhat * gamma + beta
 __device__ __forceinline__ void ln8(float4& v0, float4& v1, const float4& g0, const float4& g1, const float4& b0, const float4& b1,
@@ -278,15 +271,22 @@ __device__ __forceinline__ void ln8(float4& v0, float4& v1, const float4& g0, co
 }
 }  // namespace
 
-__global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArgs a) {
+__global__ void __launch_bounds__(kFwCta, 1) afno_fwd_tc_kernel(const AfnoWTcArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_launch_dependents();
   __shared__ uint64_t bars[WB_N];
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
-  if (tid == 0) wt_init_barriers(bars);
-  if (warp == kWtCtlWarp) {
-    tmem_alloc(&tmem_s, 128);
+  if (tid == 0) {
+    for (int g = 0; g < kFwGroups; ++g) {
+      mbar_init(&bars[WB_YFULL + g], kFwGrp);
+      mbar_init(&bars[WB_DFULL + g], 1);
+    }
+    mbar_init(&bars[WB_CONST], 1);
+    fence_mbar_init();
+  }
+  if (warp == kFwCtlWarp) {
+    tmem_alloc(&tmem_s, 256);
     tmem_relinquish();
   }
   float* sGB = reinterpret_cast<float*>(smem + FwdSmem::GB);      // norm1 weight [64], bias [64]
@@ -296,10 +296,9 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
   }
   const bool embed = a.ngrp > 0;      // first block: the tokens are computed from the step input, not read
   float* sWe = reinterpret_cast<float*>(smem + FwdSmem::Emb);     // [Cin][64] embedding weights, transposed
-  float* sIn = sWe + 16 * kAfnoE;                                 // [Cin][128] input rows of the tile
-  float* sBe = sIn + 16 * kTcTile;                                // [64] embedding bias
+  float* sBe = sWe + 16 * kAfnoE;                                 // [64] embedding bias
   if (embed) {
-    for (int i = tid; i < a.Cin * kAfnoE; i += kWtCta) sWe[i] = a.We[(i & 63) * a.Cin + (i >> 6)];
+    for (int i = tid; i < a.Cin * kAfnoE; i += kFwCta) sWe[i] = a.We[(i & 63) * a.Cin + (i >> 6)];
     if (tid < kAfnoE) sBe[tid] = a.be[tid];
   }
   tc_fence_before();
@@ -308,24 +307,22 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
   uint64_t* b = bars;
   const int stride = gridDim.x, first = blockIdx.x;
 
-  if (warp == kWtCtlWarp) {
+  if (warp == kFwCtlWarp) {
     const uint32_t leader = elect_one();
     mbar_arrive_expect_tx_p(leader, &b[WB_CONST], 65536u);
     bulk_g2s_p(leader, smem + FwdSmem::F, a.Fimg, 65536u, &b[WB_CONST]);
     mbar_wait(&b[WB_CONST], 0);
     const uint32_t idesc = idesc_bf16(128, 64) | kIdescBMnMajor;
     const uint64_t dF = chunk_desc(smem_u32(smem + FwdSmem::F), 128, 0);
-    uint32_t u = 0;
-    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
-      const int s = u & 1;
-      const uint32_t ph = (u >> 1) & 1u;
-      mbar_wait(&b[WB_YFULL + s], ph);
-      mbar_wait(&b[WB_DEMPTY + s], ph ^ 1u);
-      if (lane == 0) TRA(u, 6);
+    uint32_t t = 0;      // tiles of this CTA in order: tile t belongs to group t % kFwGroups
+    for (int tile = first; tile < a.ntiles; tile += stride, ++t) {
+      const int g = t % kFwGroups;
+      mbar_wait(&b[WB_YFULL + g], (t / kFwGroups) & 1u);      // the group has drained its previous accumulator before it arrives here
+      if (lane == 0) TRA(t, 6);
       tc_fence_after();
       // B: 8 x 8 core matrices 128 B apart along tokens (K), 2048 B along channels (N)
-      const uint64_t dY = smem_desc(smem_u32(smem + FwdSmem::Y + s * 32768), 128, 2048);
-      const uint32_t d = tmem_s + 64u * s;
+      const uint64_t dY = smem_desc(smem_u32(smem + FwdSmem::Y + g * 32768), 128, 2048);
+      const uint32_t d = tmem_s + 64u * g;
 #pragma unroll
       for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
         const uint32_t fa = term == 1 ? 32768u : 0u, yp = term == 2 ? 16384u : 0u;
@@ -333,154 +330,144 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
         for (int k0 = 0; k0 < 128; k0 += 16)
           umma_bf16_p(leader, d, desc_off(dF, fa + (k0 >> 3) * 2048), desc_off(dY, yp + k0 * 16), idesc, (term | k0) != 0);
       }
-      umma_commit_p(leader, &b[WB_DFULL + s]);
-      umma_commit_p(leader, &b[WB_YEMPTY + s]);
-      if (lane == 0) TRA(u, 7);
+      umma_commit_p(leader, &b[WB_DFULL + g]);
+      if (lane == 0) TRA(t, 7);
       __syncwarp();
     }
   } else {
-    // two threads per token (32 channels each): LayerNorm without a transposition, and the operand image is
-    // written with 512 contiguous bytes per warp store (a warp's lanes are 32 consecutive tokens)
-    const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane, c0 = 32 * half;
-    float2* stats = reinterpret_cast<float2*>(smem + FwdSmem::Stats);   // [tile parity][half][row] = (mean, centred sum of squares)
+    const int g = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;      // group, TMEM lane quarter, token of the tile = accumulator row
     const int rows_used = a.RT * 2 * a.Kc;
     const int HW = a.H * a.W;
+    uint8_t* ybase = smem + FwdSmem::Y + g * 32768 + row * 16;
 
-    auto drain = [&](int tile, uint32_t u) {
-      const int s = u & 1;
-      mbar_wait(&b[WB_DFULL + s], (u >> 1) & 1u);
-      if (tid == 0) TRA(u + 1, 4);
-      tc_fence_after();
-      uint32_t r[32];
-      tmem_ld32(tmem_s + ((uint32_t)(q4 * 32) << 16) + 64u * s + 32u * half, r);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&b[WB_DEMPTY + s]);
-      if (row < rows_used) {
-        const int h2 = row / (2 * a.Kc), rem = row - h2 * 2 * a.Kc, kx = rem >> 1, reim = rem & 1;
-        const int grow = tile * a.RT + h2, bb = grow / a.H, h = grow - bb * a.H;
-        float4* dst = reinterpret_cast<float4*>(a.A + ((((size_t)bb * a.Kc + kx) * a.H + h) * 2 + reim) * kAfnoE + c0);
+    auto load_x = [&](int tile, float4 (&x)[16]) {
+      if (!embed) {
+        const float4* src = reinterpret_cast<const float4*>(a.x + ((size_t)tile * kTcTile + row) * kAfnoE);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
-                               __uint_as_float(r[4 * j + 3]));
+        for (int j = 0; j < 16; ++j) x[j] = src[j];
+      } else {
+        // first block: x = patch embedding + position embedding of the step input (fourcastnet.py:285-289,294-307);
+        // here only the loads: position embedding row into x, the token's input channels into xin
+        const long long p0 = (long long)tile * kTcTile + row;
+        const long long bb = p0 / HW, pix = p0 - bb * HW;
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          x[j] = a.pos != nullptr ? __ldg(reinterpret_cast<const float4*>(a.pos + pix * kAfnoE) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     };
-    auto load_x = [&](int tile, float4 (&x)[8]) {
-      const float4* src = reinterpret_cast<const float4*>(a.x + ((size_t)tile * kTcTile + row) * kAfnoE + c0);
+    auto load_in = [&](int tile, float (&xin)[8]) {
+      const long long p0 = (long long)tile * kTcTile + row;
+      const long long bb = p0 / HW, pix = p0 - bb * HW;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) x[j] = src[j];
-    };
-    // first block: x = patch embedding + position embedding of the step input (fourcastnet.py:285-289,294-307), stored to xout
-    auto embed_x = [&](int tile, float4 (&x)[8]) {
-      const long long p0 = (long long)tile * kTcTile;
-      const long long bb = p0 / HW, pix0 = p0 - bb * HW;      // a tile never straddles samples
-      float gv[8];      // every global load of the tile is issued before the first one is used
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int i = tid + j * kWtWork;
-        const int k = i >> 7, px = i & 127;
+      for (int k = 0; k < 8; ++k) {
         int ch = k;
         float val = 0.f;
-        if (i < a.Cin * kTcTile) {
+        if (k < a.Cin) {
 #pragma unroll
           for (int gi = 0; gi < 4; ++gi)
             if (gi < a.ngrp) {
-              if (ch >= 0 && ch < a.grp[gi].nch) val = a.grp[gi].base[bb * a.grp[gi].bstride + (long long)ch * HW + pix0 + px];
+              if (ch >= 0 && ch < a.grp[gi].nch) val = a.grp[gi].base[bb * a.grp[gi].bstride + (long long)ch * HW + pix];
               ch -= a.grp[gi].nch;
             }
         }
-        gv[j] = val;
+        xin[k] = val;
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float4 bq = *reinterpret_cast<const float4*>(sBe + c0 + 4 * j);
-        x[j] = bq;
-        if (a.pos != nullptr) {
-          const float4 pq = __ldg(reinterpret_cast<const float4*>(a.pos + (pix0 + row) * kAfnoE + c0) + j);
-          x[j] = make_float4(bq.x + pq.x, bq.y + pq.y, bq.z + pq.z, bq.w + pq.w);
-        }
-      }
-      bar_sync(1, kWtWork);      // the previous tile's input rows have been consumed
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (tid + j * kWtWork < a.Cin * kTcTile) sIn[tid + j * kWtWork] = gv[j];
-      bar_sync(1, kWtWork);
-      for (int k = 0; k < a.Cin; ++k) {
-        const float xin = sIn[k * kTcTile + row];
-        const float4* wq = reinterpret_cast<const float4*>(sWe + k * kAfnoE + c0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 w = wq[j];
-          x[j].x = fmaf(xin, w.x, x[j].x); x[j].y = fmaf(xin, w.y, x[j].y);
-          x[j].z = fmaf(xin, w.z, x[j].z); x[j].w = fmaf(xin, w.w, x[j].w);
-        }
-      }
-      float4* xo = reinterpret_cast<float4*>(a.xout + ((size_t)tile * kTcTile + row) * kAfnoE + c0);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) xo[j] = x[j];
     };
 
     pdl_wait();   // x / the step input are what earlier kernels wrote
-    float4 x[8];
-    if (first < a.ntiles && !embed) load_x(first, x);
-    uint32_t u = 0;
-    int prev = -1;
-    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
-      const int s = u & 1;
-      const uint32_t ph = (u >> 1) & 1u;
+    float4 x[16];
+    float xin[8];      // the fused embedding takes up to 8 input channels
+    const int tile0 = first + g * stride;
+    if (tile0 < a.ntiles) {
+      load_x(tile0, x);
+      if (embed) load_in(tile0, xin);
+    }
+    uint32_t u = 0;      // this group's tiles
+    for (int tile = tile0; tile < a.ntiles; tile += kFwGroups * stride, ++u) {
       if (tid == 0) TRA(u, 0);
-      if (embed) embed_x(tile, x);
-      // the statistics are computed here, not where the loads were issued
+      if (embed) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) asm volatile("" : "+f"(x[j].x), "+f"(x[j].y), "+f"(x[j].z), "+f"(x[j].w));
-      if (tid == 0) TRA(u, 1);
+        for (int k = 0; k < 8; ++k)
+          if (k < a.Cin) {
+            const float4* wq = reinterpret_cast<const float4*>(sWe + k * kAfnoE);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float4 w = wq[j];
+              x[j].x = fmaf(xin[k], w.x, x[j].x); x[j].y = fmaf(xin[k], w.y, x[j].y);
+              x[j].z = fmaf(xin[k], w.z, x[j].z); x[j].w = fmaf(xin[k], w.w, x[j].w);
+            }
+          }
+        float4* xo = reinterpret_cast<float4*>(a.xout + ((size_t)tile * kTcTile + row) * kAfnoE);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float4 bq = *reinterpret_cast<const float4*>(sBe + 4 * j);
+          x[j] = make_float4(x[j].x + bq.x, x[j].y + bq.y, x[j].z + bq.z, x[j].w + bq.w);
+          xo[j] = x[j];
+        }
+      }
+      // LayerNorm of the token, two passes, thread-local
       float sum = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) sum += (x[j].x + x[j].y) + (x[j].z + x[j].w);
-      const float mh = sum * (1.0f / 32.0f);
+      for (int j = 0; j < 16; ++j) sum += (x[j].x + x[j].y) + (x[j].z + x[j].w);
+      if (tid == 0) TRA(u, 1);
+      const float mean = sum * (1.0f / 64.0f);
       float q = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float d0 = x[j].x - mh, d1 = x[j].y - mh, d2 = x[j].z - mh, d3 = x[j].w - mh;
+      for (int j = 0; j < 16; ++j) {
+        const float d0 = x[j].x - mean, d1 = x[j].y - mean, d2 = x[j].z - mean, d3 = x[j].w - mean;
         q = fmaf(d0, d0, q); q = fmaf(d1, d1, q); q = fmaf(d2, d2, q); q = fmaf(d3, d3, q);
       }
-      float2* st = stats + s * 256;
-      st[half * 128 + row] = make_float2(mh, q);
-      bar_sync(2, kWtWork);
-      const float2 o = st[(half ^ 1) * 128 + row];
-      const float mean = 0.5f * (mh + o.x), dm = mh - o.x;
-      const float rstd = rsqrtf((q + o.y + 16.0f * dm * dm) * (1.0f / 64.0f) + a.eps);
-      mbar_wait(&b[WB_YEMPTY + s], ph ^ 1u);
-      if (tid == 0) TRA(u, 2);
-      uint8_t* yd = smem + FwdSmem::Y + s * 32768 + (4 * half) * 2048 + row * 16;
+      const float rstd = rsqrtf(q * (1.0f / 64.0f) + a.eps);
+      // the group's image is free: its previous tile's accumulator has been drained, so those MMAs are complete
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {     // 8 channels = one 16-byte unit of the chunk-major image
-        const float4 ga = *reinterpret_cast<const float4*>(sGB + c0 + 8 * j), gb = *reinterpret_cast<const float4*>(sGB + c0 + 8 * j + 4);
-        const float4 ba = *reinterpret_cast<const float4*>(sGB + kAfnoE + c0 + 8 * j),
-                     bb = *reinterpret_cast<const float4*>(sGB + kAfnoE + c0 + 8 * j + 4);
+      for (int j = 0; j < 8; ++j) {     // 8 channels = one 16-byte unit of the chunk-major image
+        const float4 ga = *reinterpret_cast<const float4*>(sGB + 8 * j), gb = *reinterpret_cast<const float4*>(sGB + 8 * j + 4);
+        const float4 ba = *reinterpret_cast<const float4*>(sGB + kAfnoE + 8 * j), bb = *reinterpret_cast<const float4*>(sGB + kAfnoE + 8 * j + 4);
         const float4 v0 = x[2 * j], v1 = x[2 * j + 1];
         uint32_t h[4], l[4];
         split2p(make_float2(fmaf((v0.x - mean) * rstd, ga.x, ba.x), fmaf((v0.y - mean) * rstd, ga.y, ba.y)), h[0], l[0]);
         split2p(make_float2(fmaf((v0.z - mean) * rstd, ga.z, ba.z), fmaf((v0.w - mean) * rstd, ga.w, ba.w)), h[1], l[1]);
         split2p(make_float2(fmaf((v1.x - mean) * rstd, gb.x, bb.x), fmaf((v1.y - mean) * rstd, gb.y, bb.y)), h[2], l[2]);
         split2p(make_float2(fmaf((v1.z - mean) * rstd, gb.z, bb.z), fmaf((v1.w - mean) * rstd, gb.w, bb.w)), h[3], l[3]);
-        *reinterpret_cast<uint4*>(yd + j * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4*>(yd + 16384 + j * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
+        *reinterpret_cast<uint4*>(ybase + j * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(ybase + 16384 + j * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
       }
-      if (!embed && tile + stride < a.ntiles) load_x(tile + stride, x);   // in flight under the fence, the drain and the MMAs
       fence_async_smem();
-      mbar_arrive(&b[WB_YFULL + s]);
+      mbar_arrive(&b[WB_YFULL + g]);
       if (tid == 0) TRA(u, 3);
-      if (prev >= 0) drain(prev, u - 1);
+      // the next tile's loads are in flight while this tile's MMAs run and its accumulator is drained
+      const int next = tile + kFwGroups * stride;
+      if (next < a.ntiles) {
+        load_x(next, x);
+        if (embed) load_in(next, xin);
+      }
+      mbar_wait(&b[WB_DFULL + g], u & 1u);
+      if (tid == 0) TRA(u, 4);
+      tc_fence_after();
+      {
+        const int h2 = row / (2 * a.Kc), rem = row - h2 * 2 * a.Kc, kx = rem >> 1, reim = rem & 1;
+        const int grow = tile * a.RT + h2, bb = grow / a.H, h = grow - bb * a.H;
+        float4* dst = reinterpret_cast<float4*>(a.A + ((((size_t)bb * a.Kc + kx) * a.H + h) * 2 + reim) * kAfnoE);
+#pragma unroll
+        for (int qc = 0; qc < 4; ++qc) {      // 16 columns at a time: the next tile's tokens are live in registers
+          uint32_t r[16];
+          tmem_ld16(tmem_s + ((uint32_t)(q4 * 32) << 16) + 64u * g + 16u * qc, r);
+          tmem_ld_wait();
+          if (row < rows_used) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              dst[4 * qc + j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                            __uint_as_float(r[4 * j + 3]));
+          }
+        }
+      }
+      tc_fence_before();
       if (tid == 0) TRA(u, 5);
-      prev = tile;
     }
-    if (prev >= 0) drain(prev, u - 1);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kWtCtlWarp) tmem_dealloc(tmem_s, 128);
+  if (warp == kFwCtlWarp) tmem_dealloc(tmem_s, 256);
 }
 
 int launch_afno_fwd_tc(const AfnoWTcArgs& a, cudaStream_t st) {
@@ -492,9 +479,9 @@ int launch_afno_fwd_tc(const AfnoWTcArgs& a, cudaStream_t st) {
     DLWP_CUDA(cudaFuncSetAttribute(afno_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::Total));
   }
   DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= 128, "afno_fwd_tc_kernel: unsupported shape");
-  DLWP_REQUIRE(a.ngrp == 0 || (a.Cin >= 1 && a.Cin <= 16 && a.We && a.be && a.xout), "afno_fwd_tc_kernel: bad embedding arguments");
+  DLWP_REQUIRE(a.ngrp == 0 || (a.Cin >= 1 && a.Cin <= 8 && a.We && a.be && a.xout), "afno_fwd_tc_kernel: bad embedding arguments");
   const int grid = a.ntiles < sms ? a.ntiles : sms;
-  DLWP_CUDA(launch_pdl(afno_fwd_tc_kernel, dim3(grid), dim3(kWtCta), (size_t)FwdSmem::Total, st, a));
+  DLWP_CUDA(launch_pdl(afno_fwd_tc_kernel, dim3(grid), dim3(kFwCta), (size_t)FwdSmem::Total, st, a));
   DLWP_LAUNCHED("afno_fwd_tc_kernel");
   return DLWP_OK;
 }

@@ -135,7 +135,7 @@ int atc_block_filter(dlwp_plan* p, int block, float* x, float* out, int B, cudaS
   wa.x = x; wa.gamma = g; wa.beta = be; wa.eps = d.layernorm_eps;
   wa.Fimg = p->atc_F; wa.A = reinterpret_cast<float*>(p->specA);
   wa.Gimg = p->atc_G; wa.KZ = p->atc_KZ; wa.Z = p->specZ; wa.out = out;
-  const bool fwd_tc = p->atc_wtc;
+  const bool fwd_tc = p->atc_wtc && (embed == nullptr || p->Cin <= 8);
   if (embed != nullptr) {
     wa.ngrp = fa.ngrp;
     for (int i = 0; i < fa.ngrp; ++i) wa.grp[i] = fa.grp[i];
