@@ -210,6 +210,9 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
             # the last block writes the NCHW frame (+ reads the residual frame) instead of the token stream
             "afno_mlp_kernel": b * ((D - 1) * 2 * tok * E + tok * E + 2 * B * S * Cg) + D * 2 * 2 * 2 * E * hid,
         }
+        # the tcgen05 forms of the W-DFT kernels move the same tensors
+        table["afno_fwd_tc_kernel"] = table["afno_fwd_kernel"]
+        table["afno_inv_tc_kernel"] = table["afno_inv_kernel"]
         return table.get(name)
     cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
     px = B * S
@@ -466,7 +469,8 @@ def run_ours(args, wl):
         sb = step_bytes(cls, kw, members, H, W)
         spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel",
                                                   "tcw_fwd_wdft", "tcw_fwd_hdft", "tcw_inv_hdft",
-                                                  "afno_fwd_kernel", "afno_mid_kernel", "afno_inv_kernel")]
+                                                  "afno_fwd_kernel", "afno_mid_kernel", "afno_inv_kernel",
+                                                  "afno_fwd_tc_kernel", "afno_inv_tc_kernel")]
         spec_ms = sum(entries[n][0] for n in spec_names)
         if tcw:   # the inverse W-DFT runs inside tcw_layer next to the skip conv: its share of that kernel's K extent
             m2c = fno_dims(kw, H, W)[7]
