@@ -8,6 +8,7 @@
 #include "kernels.cuh"
 
 #include <cuda_bf16.h>
+#include <cstdint>
 
 namespace dlwp {
 
@@ -717,6 +718,9 @@ int launch_nhwc_to_nchw(const float* in, float* out, int B, int C, int HW, cudaS
 // Latitude-weighted error sums, scripts/evaluate.py:790-820.  One block per (t, c, chunk of
 // samples, slice of the plane); fp64 accumulation; one atomicAdd per block and statistic.
 // =====================================================================================
+// VEC = 4: W % 4 == 0 and 16-byte aligned planes, one float4 per thread and plane position, the loads of four
+// samples in flight together; VEC = 1: any shape.
+template <int VEC>
 __global__ void __launch_bounds__(256) metrics_kernel(const float* __restrict__ o, const float* __restrict__ t,
                                                       const float* __restrict__ clim,
                                                       const float* __restrict__ latw, int B, int T, int C, int H,
@@ -724,20 +728,53 @@ __global__ void __launch_bounds__(256) metrics_kernel(const float* __restrict__ 
   const int tc = blockIdx.x;  // t * C + c
   const int ti = tc / C, c = tc - ti * C;
   const int HW = H * W;
-  const int slice = (HW + gridDim.z - 1) / gridDim.z;
+  int slice = (HW + gridDim.z - 1) / gridDim.z;
+  slice = (slice + VEC - 1) / VEC * VEC;
   const int p_lo = blockIdx.z * slice, p_hi = p_lo + slice < HW ? p_lo + slice : HW;
+  const long long bstride = (long long)T * C * HW;
+  const long long plane = ((long long)ti * C + c) * HW;
   double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-  for (int b = blockIdx.y; b < B; b += gridDim.y) {
-    const long long base = (((long long)b * T + ti) * C + c) * HW;
-    for (int p = p_lo + threadIdx.x; p < p_hi; p += blockDim.x) {
+  auto acc = [&](float w, float ov, float tv, float cv) {
+    const double d = (double)ov - (double)tv, oa = (double)ov - (double)cv, ta = (double)tv - (double)cv;
+    s0 += (double)w * d * d;
+    s1 += (double)w * oa * ta;
+    s2 += (double)w * oa * oa;
+    s3 += (double)w * ta * ta;
+  };
+  if constexpr (VEC == 4) {
+    constexpr int U = 4;
+    for (int p = p_lo + threadIdx.x * 4; p < p_hi; p += blockDim.x * 4) {
       const float w = latw[p / W];
-      const float ov = o[base + p], tv = t[base + p];
-      const float cv = clim ? clim[(long long)c * HW + p] : 0.f;
-      const double d = (double)ov - (double)tv, oa = (double)ov - (double)cv, ta = (double)tv - (double)cv;
-      s0 += (double)w * d * d;
-      s1 += (double)w * oa * ta;
-      s2 += (double)w * oa * oa;
-      s3 += (double)w * ta * ta;
+      float4 cv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (clim) cv = *reinterpret_cast<const float4*>(clim + (long long)c * HW + p);
+      for (int b = blockIdx.y; b < B; b += gridDim.y * U) {
+        float4 ov[U], tv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int bb = b + u * gridDim.y;
+          if (bb < B) {
+            ov[u] = __ldcs(reinterpret_cast<const float4*>(o + bb * bstride + plane + p));
+            tv[u] = __ldcs(reinterpret_cast<const float4*>(t + bb * bstride + plane + p));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (b + u * gridDim.y < B) {
+            acc(w, ov[u].x, tv[u].x, cv.x);
+            acc(w, ov[u].y, tv[u].y, cv.y);
+            acc(w, ov[u].z, tv[u].z, cv.z);
+            acc(w, ov[u].w, tv[u].w, cv.w);
+          }
+        }
+      }
+    }
+  } else {
+    for (int b = blockIdx.y; b < B; b += gridDim.y) {
+      const long long base = b * bstride + plane;
+      for (int p = p_lo + threadIdx.x; p < p_hi; p += blockDim.x) {
+        const float cv = clim ? clim[(long long)c * HW + p] : 0.f;
+        acc(latw[p / W], o[base + p], t[base + p], cv);
+      }
     }
   }
   __shared__ double red[4][8];
@@ -750,9 +787,9 @@ __global__ void __launch_bounds__(256) metrics_kernel(const float* __restrict__ 
   }
   __syncthreads();
   if (threadIdx.x < 4) {
-    double acc = 0.0;
-    for (int wdx = 0; wdx < 8; ++wdx) acc += red[threadIdx.x][wdx];
-    atomicAdd(&sums[(long long)tc * 4 + threadIdx.x], acc);
+    double a = 0.0;
+    for (int wdx = 0; wdx < 8; ++wdx) a += red[threadIdx.x][wdx];
+    atomicAdd(&sums[(long long)tc * 4 + threadIdx.x], a);
   }
 }
 
@@ -768,7 +805,11 @@ int launch_metrics(const float* o, const float* t, const float* clim, const floa
   if (bz < 1) bz = 1;
   if (bz > 65535) bz = 65535;
   dim3 grid((unsigned)(T * C), (unsigned)by, (unsigned)bz);
-  metrics_kernel<<<grid, 256, 0, st>>>(o, t, clim, latw, B, T, C, H, W, sums);
+  const bool vec = W % 4 == 0 && (((uintptr_t)o | (uintptr_t)t | (uintptr_t)clim) & 15) == 0;
+  if (vec)
+    metrics_kernel<4><<<grid, 256, 0, st>>>(o, t, clim, latw, B, T, C, H, W, sums);
+  else
+    metrics_kernel<1><<<grid, 256, 0, st>>>(o, t, clim, latw, B, T, C, H, W, sums);
   DLWP_LAUNCHED("metrics_kernel");
   return DLWP_OK;
 }

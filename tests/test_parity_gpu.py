@@ -306,10 +306,11 @@ def test_rollout_host_equals_device_rollout(pkg, ctx, T):
     assert not torch.equal(again, host)      # a second call with other prescribed frames is not served stale ones
 
 
-def test_metrics_kernel_matches_oracle(pkg):
+@pytest.mark.parametrize("B,T,Cn,H,W", [(5, 3, 4, 32, 64), (70, 2, 3, 32, 64), (3, 2, 2, 9, 15), (2, 1, 1, 181, 360)])
+def test_metrics_kernel_matches_oracle(pkg, B, T, Cn, H, W):
+    # float4 form (W % 4 == 0), more samples than one pass of a CTA covers, ragged planes (scalar form), sliced planes
     from oracle import metrics as om
     torch.manual_seed(2)
-    B, T, Cn, H, W = 5, 3, 4, 32, 64
     o, t, c = torch.randn(B, T, Cn, H, W), torch.randn(B, T, Cn, H, W), 0.3 * torch.randn(Cn, H, W)
     rmse, acc = pkg.rollout_metrics(o.cuda(), t.cuda(), c.cuda())
     wr, wa = om.rmse_acc(o.double(), t.double(), c.double())
