@@ -448,26 +448,40 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
     const uint32_t tmem_lane = tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 16u * id.half;
     const int c0 = 8 * id.half;      // this thread's 8 output channels
     uint32_t u = 0, gp = 0, nc = 0;
-    for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
-      // residual frame values: requested now, consumed after the MLP passes
-      const long long p = (long long)tile * kTcTile + id.row;
-      const long long bb = p / g.HW, pix = p - bb * g.HW;
-      float lastv[8];
-#pragma unroll
-      for (int c = 0; c < 8; ++c)
-        lastv[c] = (a.last != nullptr && c0 + c < a.Cg) ? a.last[bb * a.last_bstride + (long long)(c0 + c) * g.HW + pix] : 0.f;
-      epi_mlp_tile(b, id, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [] {});
-      mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
+    // A tile is finished one tile late, after the first pass of the next one: its second GEMM completes under
+    // that pass instead of being waited for (D2 is double buffered in TMEM).
+    float lastv[8];
+    long long obase = 0;
+    auto finish = [&](uint32_t v) {
+      mbar_wait(&b[MB_D2FULL + (v & 1)], full_par(v));
       tc_fence_after();
       uint32_t r[8];
-      tmem_ld8(tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 128u + 32u * (u & 1) + (uint32_t)c0, r);
+      tmem_ld8(tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 128u + 32u * (v & 1) + (uint32_t)c0, r);
       tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
-      float* o = a.out + bb * a.out_bstride + pix;
+      mbar_arrive(&b[MB_D2EMPTY + (v & 1)]);
+      float* o = a.out + obase;
 #pragma unroll
       for (int c = 0; c < 8; ++c)
         if (c0 + c < a.Cg) o[(long long)(c0 + c) * g.HW] = __uint_as_float(r[c]) + sB2[c0 + c] + lastv[c];
+    };
+    auto load_last = [&](int tile) {      // residual frame values of a tile: requested a pass before they are consumed
+      const long long p = (long long)tile * kTcTile + id.row;
+      const long long bb = p / g.HW, pix = p - bb * g.HW;
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        lastv[c] = (a.last != nullptr && c0 + c < a.Cg) ? a.last[bb * a.last_bstride + (long long)(c0 + c) * g.HW + pix] : 0.f;
+      obase = bb * a.out_bstride + pix;
+    };
+    int prev = -1;
+    for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
+      if (prev >= 0) load_last(prev);
+      epi_mlp_tile(b, id, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [&] { if (prev >= 0) finish(u - 1); });
+      prev = tile;
+    }
+    if (prev >= 0) {
+      load_last(prev);
+      finish(u - 1);
     }
   }
   tc_fence_before();
