@@ -141,9 +141,9 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const bool has_next = tile + stride < a.ntiles;
       if (has_next) gather(tile + stride, nx);      // loads in flight while the first passes are processed
-      epi_mlp_tile<4>(b, id, tmem_lane, P, smem + AmSmem::A2, gp, nc, [&] {
-        if (has_next) store_a1(u + 1, nx);
-      }, a.b1, P - 2);
+      epi_mlp_tile<4>(b, id, tmem_lane, P, smem + AmSmem::A2, gp, nc, [&](int pass) {
+        if (pass == P - 2 && has_next) store_a1(u + 1, nx);
+      }, a.b1);
       // out = x + D2 + b2 on this thread's 32 channels (x is re-read: an L2 hit)
       const size_t off = ((size_t)tile * kTcTile + id.row) * kAfnoE + c0;
       const float4* xr = reinterpret_cast<const float4*>(a.x + off);

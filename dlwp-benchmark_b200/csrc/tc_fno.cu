@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
     int prev = -1;
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
       if (prev >= 0) load_last(prev);
-      epi_mlp_tile(b, id, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [&] { if (prev >= 0) finish(u - 1); });
+      epi_mlp_tile(b, id, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [&](int pass) { if (pass == 0 && prev >= 0) finish(u - 1); });
       prev = tile;
     }
     if (prev >= 0) {
@@ -588,7 +588,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
           const uint32_t gp = u * P + p;
           if (p + 1 < P) is.mma1<16>(u, p + 1, gp + 1);
           else if (has_next) is.mma1<16>(u + 1, 0, gp + 1);
-          if (p == 0 && u > 0) finish(tile - stride, u - 1);
+          if (p == 1 && u > 0) finish(tile - stride, u - 1);      // handed over after the epilogue's first pass of this tile
           is.mma2<32>(u, p);
         }
       }
@@ -630,21 +630,17 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
     }
     uint32_t u = 0, gp = 0, nc = 0, n3 = 0;
     int prev_tile = 0;
-    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
-      const bool has_next = tile + stride < g.ntiles;
-      if (has_next) gather(tile + stride, nx);      // loads in flight while the first pass is processed
-      epi_mlp_tile(b, id, tmem_lane, P, ws + LiftSmem::A2, gp, nc, [&] {
-        if (has_next) store_a1(u + 1, nx);
-      });
-      mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
+    // tile v's second GEMM completes under the first pass of tile v + 1: its output is taken over after that pass
+    auto finish_ep = [&](int tile_f, uint32_t v_) {
+      mbar_wait(&b[MB_D2FULL + (v_ & 1)], full_par(v_));
       tc_fence_after();
       float2 v[8];
       {
         uint32_t r[16];
-        tmem_ld16(tmem_lane + 128u + 32u * (u & 1), r);
+        tmem_ld16(tmem_lane + 128u + 32u * (v_ & 1), r);
         tmem_ld_wait();
         tc_fence_before();
-        mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
+        mbar_arrive(&b[MB_D2EMPTY + (v_ & 1)]);
         const float2* bias2 = reinterpret_cast<const float2*>(sB2 + 16 * id.half);
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
@@ -652,9 +648,19 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
           v[c] = make_float2(__uint_as_float(r[2 * c]) + bb.x, __uint_as_float(r[2 * c + 1]) + bb.y);
         }
       }
-      finish_tile(v, id, tile, g, a.Aout, ws + LiftSmem::Y, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], &b[MB_YFREE], n3,
+      finish_tile(v, id, tile_f, g, a.Aout, ws + LiftSmem::Y, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], &b[MB_YFREE], n3,
                   prev_tile);
+    };
+    const int a1_pass = P >= 3 ? P - 2 : 0;      // the next tile's gathered inputs are consumed as late as the issuer allows
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+      const bool has_next = tile + stride < g.ntiles;
+      if (has_next) gather(tile + stride, nx);      // loads in flight while the first passes are processed
+      epi_mlp_tile(b, id, tmem_lane, P, ws + LiftSmem::A2, gp, nc, [&](int pass) {
+        if (pass == 0 && u > 0) finish_ep(tile - stride, u - 1);
+        if (pass == a1_pass && has_next) store_a1(u + 1, nx);
+      });
     }
+    if (u > 0) finish_ep(first + (int)(u - 1) * stride, u - 1);
     if (n3 > 0 && a.Aout != nullptr) drain_d3(id, prev_tile, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3 - 1);
   }
   tc_fence_before();

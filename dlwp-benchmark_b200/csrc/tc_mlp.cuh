@@ -143,15 +143,14 @@ struct MlpIssuer {
   }
 };
 
-// epilogue side of one tile's MLP; `after_pass0()` runs once after the first pass.  Each thread
+// epilogue side of one tile's MLP; `after_pass(p)` runs after every pass p.  Each thread
 // turns 16 hidden columns of its pixel per 32-column chunk into split-bf16 operand bytes.
 // `sB1` (optional): the first layer's bias [hid] in shared memory, added here when the first GEMM
 // has no spare K column to carry it.
-// `NA2`: depth of the A2 ring; `hook_pass`: the pass after which the hook runs.
+// `NA2`: depth of the A2 ring.
 template <int NA2 = 2, class Hook>
 __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint32_t tmem_lane, int P, uint8_t* sA2,
-                                             uint32_t& gp, uint32_t& nc, Hook after_pass0, const float* sB1 = nullptr,
-                                             int hook_pass = 0) {
+                                             uint32_t& gp, uint32_t& nc, Hook after_pass, const float* sB1 = nullptr) {
   for (int p = 0; p < P; ++p, ++gp) {
     const int db = gp & 1;
     float4 bv[2][4];    // this pass's bias values: requested before the wait so that their latency hides behind it
@@ -198,7 +197,7 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
       fence_async_smem();
       mbar_arrive(&b[MB_A2FULL + ab]);
     }
-    if (p == hook_pass) after_pass0();
+    after_pass(p);
   }
 }
 
