@@ -11,7 +11,7 @@ using namespace tc;
 
 #ifdef DLWP_TRACE
 __device__ unsigned long long* g_trace = nullptr;   // also used by tc_mid.cu
-#define TR(w, u, ev) do { if (g_trace && blockIdx.x == 0 && (u) < 16) g_trace[((w) * 16 + (u)) * 8 + (ev)] = clock64(); } while (0)
+#define TR(w, u, ev) do { if (g_trace && tr_on && blockIdx.x == 0 && (u) < 16) g_trace[((w) * 16 + (u)) * 8 + (ev)] = clock64(); } while (0)
 #else
 #define TR(w, u, ev) do {} while (0)
 #endif
@@ -75,20 +75,36 @@ __device__ __forceinline__ void drain_d3(const EpiId& id, int tile, const TcGeom
   tc_fence_before();
 }
 
-// n3 counts the tiles this worker has handed over; prev_tile is the last one.
-// v[8] = this thread's 16 output channels (16 * half ..) of its pixel, as pairs
+// n3 counts the tiles this worker has handed over.  v[8] = this thread's 16 output channels (16 * half ..) of its
+// pixel, as pairs.  The tiles take `ny` image buffers (each with its xt_full / y_free barrier) and `nd` W-DFT
+// accumulators (32 TMEM columns apart, each with its d3_full barrier) in turn:
+//   nd = 1          the previous tile's accumulator is drained before this tile is handed over;
+//   nd = 2 or 3     the accumulator of tile n - (nd - 1), which tile n + 1 overwrites, is drained AFTER tile n is
+//                   handed over: the proxy fence of the hand-over waits for the thread's global stores in
+//                   flight, so those of the drain must not be issued just ahead of it, and the chain of small
+//                   W-DFT UMMAs of a tile (~3 k cycles) has nd - 1 tile periods to complete.
+//   ny = 2          the epilogue of a tile does not wait for the bulk store of the tile before it either.
+// (layer kernel: ny = 2, nd = 3 when the shared memory is there; lift kernel: ny = 1, nd = 2)
+// prev_tile: nd = 3 keeps tile n in prev_tile[n & 1]; otherwise prev_tile[0] is the last tile.
+struct TailCfg {
+  int ny, nd;
+};
+__device__ __forceinline__ uint32_t d3_slot(uint32_t n, int nd) { return nd == 3 ? n % 3u : nd == 2 ? (n & 1u) : 0u; }
+__device__ __forceinline__ uint32_t d3_use(uint32_t n, int nd) { return nd == 3 ? n / 3u : nd == 2 ? (n >> 1) : n; }
+
 __device__ __forceinline__ void finish_tile(const float2 (&v)[8], const EpiId& id, int tile, const TcGeom& g, float* Aout,
                                             uint8_t* sY, uint32_t tmem_d3, uint64_t* xt_full, uint64_t* d3_full,
-                                            uint64_t* y_free, uint32_t& n3, int& prev_tile) {
+                                            uint64_t* y_free, uint32_t& n3, int (&prev_tile)[2], const TailCfg cfg,
+                                            bool tr_on = false) {
+  const int ny = cfg.ny, nd = cfg.nd;
   uint32_t hi[8], lo[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) split2p(v[j], hi[j], lo[j]);
-  if (n3 > 0) {   // the previous tile must have left the image buffer (bulk store, UMMAs) and the accumulator
-    mbar_wait(y_free, (n3 - 1) & 1u);
-    if ((threadIdx.x & 255) == 0) TR(id.w, n3, 7);
-    if (Aout != nullptr) drain_d3(id, prev_tile, g, Aout, tmem_d3, d3_full, n3 - 1);
-  }
-  uint8_t* dst = sY + id.row * 16 + id.half * 4096;
+  const uint32_t yb = ny == 2 ? (n3 & 1u) : 0u, use = ny == 2 ? (n3 >> 1) : n3;
+  if (use > 0) mbar_wait(&y_free[yb], (use - 1) & 1u);   // the tile that used this image buffer last has left it (bulk store, UMMAs)
+  if (nd == 1 && n3 > 0 && Aout != nullptr) drain_d3(id, prev_tile[0], g, Aout, tmem_d3, d3_full, n3 - 1);
+  if ((threadIdx.x & 255) == 0) TR(id.w, n3, 7);
+  uint8_t* dst = sY + yb * kTileBytes + id.row * 16 + id.half * 4096;
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     *reinterpret_cast<uint4*>(dst + q * 2048) = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
@@ -96,18 +112,41 @@ __device__ __forceinline__ void finish_tile(const float2 (&v)[8], const EpiId& i
   }
   fence_async_smem();
   tc_fence_before();
-  mbar_arrive(xt_full);
+  mbar_arrive(&xt_full[yb]);
   if ((threadIdx.x & 255) == 0) TR(id.w, n3, 4);
+  const uint32_t back = (uint32_t)nd - 1u;
+  if (nd > 1 && n3 >= back && Aout != nullptr) {
+    const uint32_t k = n3 - back;
+    const int kt = nd == 3 ? ((k & 1u) ? prev_tile[1] : prev_tile[0]) : prev_tile[0];
+    drain_d3(id, kt, g, Aout, tmem_d3 + 32u * d3_slot(k, nd), &d3_full[d3_slot(k, nd)], d3_use(k, nd));
+  }
+  if (nd == 3 && (n3 & 1u)) prev_tile[1] = tile;
+  else prev_tile[0] = tile;
   ++n3;
-  prev_tile = tile;
+}
+
+// after a worker's last tile: the accumulators that are still to be drained
+__device__ __forceinline__ void drain_tail(const EpiId& id, const TcGeom& g, float* Aout, uint32_t tmem_d3, uint64_t* d3_full,
+                                           uint32_t n3, const int (&prev_tile)[2], const TailCfg cfg) {
+  if (Aout == nullptr) return;
+  const int nd = cfg.nd;
+  const uint32_t left = nd == 3 ? 2u : 1u;
+  for (uint32_t k = n3 > left ? n3 - left : 0u; k < n3; ++k) {
+    const int kt = nd == 3 ? ((k & 1u) ? prev_tile[1] : prev_tile[0]) : prev_tile[0];
+    drain_d3(id, kt, g, Aout, tmem_d3 + 32u * d3_slot(k, nd), &d3_full[d3_slot(k, nd)], d3_use(k, nd));
+  }
 }
 
 // control warp: n-th tile handed over by the epilogue group -> forward W-DFT UMMAs (hi*hi, lo*hi,
 // hi*lo; when `dft`), bulk store of the image, release of the buffer
 __device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint32_t aF, uint8_t* sY, uint8_t* y_dst,
                                                  uint32_t tmem_d3, uint64_t* xt_full, uint64_t* d3_full, uint64_t* y_free,
-                                                 uint32_t n) {
-  mbar_wait(xt_full, n & 1u);
+                                                 uint32_t n, const TailCfg cfg, bool tr_on = false, int tw = 0) {
+  const int ny = cfg.ny, nd = cfg.nd;
+  const uint32_t yb = ny == 2 ? (n & 1u) : 0u, use = ny == 2 ? (n >> 1) : n;
+  sY += yb * kTileBytes;
+  mbar_wait(&xt_full[yb], use & 1u);
+  TR(tw, n, 5);
   tc_fence_after();
   if (dft) {
     const uint32_t idesc = idesc_bf16(64, 32) | kIdescBMnMajor;
@@ -119,15 +158,16 @@ __device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint
       const uint32_t fa = term == 1 ? 32u * 128u * 2u : 0u, yp = term == 2 ? (uint32_t)kImg : 0u;
 #pragma unroll
       for (int k0 = 0; k0 < 128; k0 += 16)
-        umma_bf16_p(leader, tmem_d3, desc_off(dF, fa + (k0 >> 3) * 512), desc_off(dY, yp + k0 * 16), idesc, (term | k0) != 0);
+        umma_bf16_p(leader, tmem_d3 + 32u * d3_slot(n, nd), desc_off(dF, fa + (k0 >> 3) * 512), desc_off(dY, yp + k0 * 16), idesc,
+                    (term | k0) != 0);
     }
-    umma_commit_p(leader, d3_full);
+    umma_commit_p(leader, &d3_full[d3_slot(n, nd)]);
   }
   bulk_s2g_p(leader, y_dst, sY, kTileBytes);
   bulk_commit();
   bulk_wait_read0();
-  if (dft) umma_commit_p(leader, y_free);   // arrives when the UMMAs above have read the image too
-  else mbar_arrive_p(leader, y_free);
+  if (dft) umma_commit_p(leader, &y_free[yb]);   // arrives when the UMMAs above have read the image too
+  else mbar_arrive_p(leader, &y_free[yb]);
   __syncwarp();
 }
 
@@ -146,7 +186,7 @@ namespace {
 constexpr int kLayerSlots = 3;
 struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
   int G, F, Ws, Bias, Worker, X, Z, Y, WorkerBytes, Total;
-  __host__ __device__ explicit LayerSmem(int KZ) {
+  __host__ __device__ explicit LayerSmem(int KZ, int ny) {
     G = 0;
     F = G + 2 * 128 * KZ * 2;
     Ws = F + kFBytes;
@@ -155,12 +195,12 @@ struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
     X = 0;
     Z = X + kLayerSlots * kTileBytes;
     Y = Z + kLayerSlots * KZ * 128;
-    WorkerBytes = Y + kTileBytes;
+    WorkerBytes = Y + ny * kTileBytes;
     Total = Worker + 2 * WorkerBytes;
   }
 };
 constexpr int kLayerSmemMax = 226 * 1024;   // 227 KB per CTA minus the kernel's static shared memory
-enum { LB_XFULL = 0, LB_XFREE = 3, LB_DFULL = 6, LB_DEMPTY = 8, LB_XTFULL = 10, LB_D3FULL = 11, LB_YFREE = 12, LB_PER = 13 };
+enum { LB_XFULL = 0, LB_XFREE = 3, LB_DFULL = 6, LB_DEMPTY = 8, LB_XTFULL = 10, LB_D3FULL = 12, LB_YFREE = 15, LB_PER = 17 };
 }  // namespace
 
 __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerArgs a) {
@@ -170,7 +210,9 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform
   const TcGeom g = a.g;
-  const LayerSmem L(g.KZ);
+  const LayerSmem L(g.KZ, a.ny);
+  const TailCfg tail{a.ny, a.ny == 2 ? 3 : 1};
+  [[maybe_unused]] const bool tr_on = a.gelu && a.Aout != nullptr;      // trace builds: a layer with GELU and forward W-DFT
   float* sBias = reinterpret_cast<float*>(smem + L.Bias);
   uint64_t* bar_const = &bars[2 * LB_PER];
 
@@ -186,8 +228,12 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
       mbar_init(&b[LB_DEMPTY], kEpi);
       mbar_init(&b[LB_DEMPTY + 1], kEpi);
       mbar_init(&b[LB_XTFULL], kEpi);
+      mbar_init(&b[LB_XTFULL + 1], kEpi);
       mbar_init(&b[LB_D3FULL], 1);
+      mbar_init(&b[LB_D3FULL + 1], 1);
+      mbar_init(&b[LB_D3FULL + 2], 1);
       mbar_init(&b[LB_YFREE], 1);
+      mbar_init(&b[LB_YFREE + 1], 1);
     }
     mbar_init(bar_const, 1);
     fence_mbar_init();
@@ -237,10 +283,8 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
       uint32_t u = 0;
       for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
         if (tile + kLayerSlots * stride < g.ntiles) load_inputs(tile + kLayerSlots * stride, u + kLayerSlots);
-        mbar_wait(&b[LB_XTFULL], u & 1u);
-        TR(w, u, 5);
         ctrl_finish_tile(leader, a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64,
-                         &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], u);
+                         &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], u, tail, tr_on, w);
         TR(w, u, 6);
       }
       bulk_wait0();
@@ -297,7 +341,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
     uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
     const uint32_t tmem = tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 16u * id.half;
     uint32_t u = 0, n3 = 0;
-    int prev_tile = 0;
+    int prev_tile[2] = {0, 0};
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       mbar_wait(&b[LB_DFULL + s], full_par(u));
@@ -319,16 +363,18 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
         }
       }
       finish_tile(v, id, tile, g, a.Aout, ws + L.Y, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], n3,
-                  prev_tile);
+                  prev_tile, tail, tr_on);
     }
-    if (n3 > 0 && a.Aout != nullptr) drain_d3(id, prev_tile, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3 - 1);
+    drain_tail(id, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3, prev_tile, tail);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == kCtlWarp) tmem_dealloc(tmem_s, 512);
 }
 
-int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
+int launch_tc_layer(const TcLayerArgs& a_in, cudaStream_t st) {
+  TcLayerArgs a = a_in;
+  a.ny = LayerSmem(a.g.KZ, 2).Total <= kLayerSmemMax ? 2 : 1;      // two output image buffers per worker when they fit
   static int sms = 0;
   if (!sms) {
     int dev = 0;
@@ -336,7 +382,7 @@ int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
     DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     DLWP_CUDA(cudaFuncSetAttribute(fno_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLayerSmemMax));
   }
-  const LayerSmem L(a.g.KZ);
+  const LayerSmem L(a.g.KZ, a.ny);
   DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
@@ -352,7 +398,7 @@ int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st) {
 //   D2[128, N2] += A2 * W2[:, chunk]^T             double-buffered across tiles
 // The hidden activations never leave the SM.  The control lane runs one pass ahead of the
 // epilogue group, so the group only ever waits for data that had a full pass of time to arrive.
-// Worker TMEM columns: D1 at +0 / +64, D2 at +128 / +160, D3 (lift only) at +192.
+// Worker TMEM columns: D1 at +0 / +64, D2 at +128 / +160, D3 (lift only) at +192 / +224.
 // =============================================================================================
 
 // =============================================================================================
@@ -577,7 +623,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       const bool dft = a.Aout != nullptr;
       auto finish = [&](int tile, uint32_t n) {
         ctrl_finish_tile(leader, dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
-                         &b[MB_YFREE], n);
+                         &b[MB_YFREE], n, TailCfg{1, 2});
       };
       mbar_wait(bar_const, 0);
       if (first < g.ntiles) is.mma1<16>(0, 0, 0);
@@ -629,7 +675,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       store_a1(0, nx);
     }
     uint32_t u = 0, gp = 0, nc = 0, n3 = 0;
-    int prev_tile = 0;
+    int prev_tile[2] = {0, 0};
     // tile v's second GEMM completes under the first pass of tile v + 1: its output is taken over after that pass
     auto finish_ep = [&](int tile_f, uint32_t v_) {
       mbar_wait(&b[MB_D2FULL + (v_ & 1)], full_par(v_));
@@ -649,7 +695,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
         }
       }
       finish_tile(v, id, tile_f, g, a.Aout, ws + LiftSmem::Y, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], &b[MB_YFREE], n3,
-                  prev_tile);
+                  prev_tile, TailCfg{1, 2});
     };
     const int a1_pass = P >= 3 ? P - 2 : 0;      // the next tile's gathered inputs are consumed as late as the issuer allows
     for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
@@ -661,7 +707,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       });
     }
     if (u > 0) finish_ep(first + (int)(u - 1) * stride, u - 1);
-    if (n3 > 0 && a.Aout != nullptr) drain_d3(id, prev_tile, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3 - 1);
+    drain_tail(id, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3, prev_tile, TailCfg{1, 2});
   }
   tc_fence_before();
   __syncthreads();

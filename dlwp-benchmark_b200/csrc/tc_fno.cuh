@@ -63,6 +63,7 @@ struct TcLayerArgs {
   const uint8_t* Wsimg;   // skip conv [hi | lo] images, R = 32, K = 32
   const float* bias;      // [32] spectral-conv bias of this layer
   int gelu;
+  int ny;                 // output image buffers per worker (set by the launcher)
 };
 
 struct TcProjArgs {

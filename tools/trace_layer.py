@@ -17,7 +17,7 @@ with torch.no_grad():
     mod(constants=const, prescribed=presc, prognostic=prog)
     torch.cuda.synchronize()
 t = tr.cpu().view(2,16,8)
-names = ['load_issue','XFULL_seen','DEMPTY_seen','DFULL_epi','xt_arrive','xt_seen_fin','fin_done','yfree_epi(prev)']
+names = ['load_issue','XFULL_seen','DEMPTY_seen','DFULL_epi','xt_arrive','xt_seen_fin','fin_done','d3_drained(prev)']
 for w in range(2):
     t0 = int(t[w][t[w]>0].min())
     print('worker', w)
