@@ -408,8 +408,8 @@ namespace {
 struct ProjSmem {   // sized for hid = 256
   static constexpr int W1 = 0, W2 = W1 + 256 * 32 * 4, W1x = W2 + 16 * 256 * 4, Ones = W1x + 256 * 16 * 2, B2 = Ones + 4096,
                        Worker = B2 + 64;
-  static constexpr int X = 0, A2 = X + 2 * kTileBytes, WorkerBytes = A2 + 2 * kTileBytes;
-  static constexpr int Total = Worker + 2 * WorkerBytes;
+  static constexpr int X = 0, A2 = X + 2 * kTileBytes, Last = A2 + 2 * kTileBytes, WorkerBytes = Last + 2 * 16 * 512;
+  static constexpr int Total = Worker + 2 * WorkerBytes;      // Last: two slots of [16 channels][128 pixels] fp32
 };
 }  // namespace
 
@@ -470,6 +470,19 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
         mbar_arrive_expect_tx_p(leader, &b[MB_A1FULL + s], kTileBytes);
         bulk_g2s_p(leader, ws + ProjSmem::X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[MB_A1FULL + s]);
       };
+      // the tile's rows of the residual frame (128 consecutive pixels per channel) for the epilogue: bulk copies,
+      // because a generic global load in flight in an epilogue thread would be waited for by its next proxy fence
+      auto load_last = [&](int tile, uint32_t u) {
+        const int s = u & 1;
+        const long long p0 = (long long)tile * kTcTile;
+        const long long bb = p0 / g.HW, pix = p0 - bb * g.HW;
+        mbar_wait(&b[MB_INEMPTY + s], empty_par(u));
+        mbar_arrive_expect_tx_p(leader, &b[MB_INFULL + s], (uint32_t)a.Cg * 512u);
+        for (int c = 0; c < a.Cg; ++c)
+          bulk_g2s_p(leader, ws + ProjSmem::Last + s * 8192 + c * 512, a.last + bb * a.last_bstride + (long long)c * g.HW + pix, 512u,
+                     &b[MB_INFULL + s]);
+      };
+      const bool bulk_last = a.last != nullptr && a.last_bulk;
       if (first < g.ntiles) {
         load_x(first, 0);
         is.mma1<32>(0, 0, 0);
@@ -478,6 +491,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
         const bool has_next = tile + stride < g.ntiles;
         if (has_next) load_x(tile + stride, u + 1);
+        if (bulk_last) load_last(tile, u);
         for (int p = 0; p < P; ++p) {
           const uint32_t gp = u * P + p;
           if (p + 1 < P) is.mma1<32>(u, p + 1, gp + 1);
@@ -498,7 +512,15 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
     // that pass instead of being waited for (D2 is double buffered in TMEM).
     float lastv[8];
     long long obase = 0;
+    const bool bulk_last = a.last != nullptr && a.last_bulk;
+    const float* sLast = reinterpret_cast<const float*>(ws + ProjSmem::Last);
     auto finish = [&](uint32_t v) {
+      if (bulk_last) {
+        mbar_wait(&b[MB_INFULL + (v & 1)], full_par(v));
+#pragma unroll
+        for (int c = 0; c < 8; ++c) lastv[c] = c0 + c < a.Cg ? sLast[(v & 1) * 2048 + (c0 + c) * 128 + id.row] : 0.f;
+        mbar_arrive(&b[MB_INEMPTY + (v & 1)]);
+      }
       mbar_wait(&b[MB_D2FULL + (v & 1)], full_par(v));
       tc_fence_after();
       uint32_t r[8];
@@ -511,12 +533,14 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       for (int c = 0; c < 8; ++c)
         if (c0 + c < a.Cg) o[(long long)(c0 + c) * g.HW] = __uint_as_float(r[c]) + sB2[c0 + c] + lastv[c];
     };
-    auto load_last = [&](int tile) {      // residual frame values of a tile: requested a pass before they are consumed
+    auto load_last = [&](int tile) {      // output position; without bulk copies also the residual frame values
       const long long p = (long long)tile * kTcTile + id.row;
       const long long bb = p / g.HW, pix = p - bb * g.HW;
+      if (!bulk_last) {
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
-        lastv[c] = (a.last != nullptr && c0 + c < a.Cg) ? a.last[bb * a.last_bstride + (long long)(c0 + c) * g.HW + pix] : 0.f;
+        for (int c = 0; c < 8; ++c)
+          lastv[c] = (a.last != nullptr && c0 + c < a.Cg) ? a.last[bb * a.last_bstride + (long long)(c0 + c) * g.HW + pix] : 0.f;
+      }
       obase = bb * a.out_bstride + pix;
     };
     int prev = -1;
@@ -535,7 +559,9 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   if (warp == kCtlWarp) tmem_dealloc(tmem_s, 512);
 }
 
-int launch_tc_proj(const TcProjArgs& a, cudaStream_t st) {
+int launch_tc_proj(const TcProjArgs& a_in, cudaStream_t st) {
+  TcProjArgs a = a_in;
+  a.last_bulk = a.last != nullptr && (reinterpret_cast<uintptr_t>(a.last) & 15) == 0 && a.last_bstride % 4 == 0 && a.g.HW % 4 == 0;
   static int sms = 0;
   if (!sms) {
     int dev = 0;

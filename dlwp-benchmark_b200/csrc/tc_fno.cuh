@@ -79,6 +79,7 @@ struct TcProjArgs {
   long long out_bstride;
   const float* last;      // residual frame or null
   long long last_bstride;
+  int last_bulk;          // set by the launcher: the residual rows are 16-byte aligned (bulk copies)
 };
 
 // H-DFT, per-mode channel mixing and inverse H-DFT on the retained columns (tc_mid.cu)

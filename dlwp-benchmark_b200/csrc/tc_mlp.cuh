@@ -55,7 +55,8 @@ namespace {
 
 // (the A2 ring has room for four slots; the FNO kernels use two)
 enum { MB_A1FULL = 0, MB_A1EMPTY = 2, MB_D1FULL = 4, MB_D1EMPTY = 6, MB_A2FULL = 8, MB_A2EMPTY = 12, MB_D2FULL = 16,
-       MB_D2EMPTY = 18, MB_XTFULL = 20, MB_D3FULL = 21 /* two */, MB_YFREE = 23, MB_PER = 24 };
+       MB_D2EMPTY = 18, MB_XTFULL = 20, MB_D3FULL = 21 /* two */, MB_YFREE = 23,
+       MB_INFULL = 24 /* two */, MB_INEMPTY = 26 /* two */, MB_PER = 28 };      // IN: fp32 rows bulk-copied for the epilogue
 
 __device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_count) {
   for (int i = 0; i < 2; ++i) {
@@ -74,6 +75,10 @@ __device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_
   mbar_init(&b[MB_D3FULL], 1);
   mbar_init(&b[MB_D3FULL + 1], 1);
   mbar_init(&b[MB_YFREE], 1);
+  for (int i = 0; i < 2; ++i) {
+    mbar_init(&b[MB_INFULL + i], 1);
+    mbar_init(&b[MB_INEMPTY + i], kEpi);
+  }
 }
 
 struct MlpIssuer {
