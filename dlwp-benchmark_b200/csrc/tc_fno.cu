@@ -88,6 +88,7 @@ __device__ __forceinline__ void drain_d3(const EpiId& id, int tile, const TcGeom
 // prev_tile: nd = 3 keeps tile n in prev_tile[n & 1]; otherwise prev_tile[0] is the last tile.
 struct TailCfg {
   int ny, nd;
+  bool ext;      // the accumulators are drained by dedicated warps (layer kernel), not by the epilogue group
 };
 __device__ __forceinline__ uint32_t d3_slot(uint32_t n, int nd) { return nd == 3 ? n % 3u : nd == 2 ? (n & 1u) : 0u; }
 __device__ __forceinline__ uint32_t d3_use(uint32_t n, int nd) { return nd == 3 ? n / 3u : nd == 2 ? (n >> 1) : n; }
@@ -102,7 +103,7 @@ __device__ __forceinline__ void finish_tile(const float2 (&v)[8], const EpiId& i
   for (int j = 0; j < 8; ++j) split2p(v[j], hi[j], lo[j]);
   const uint32_t yb = ny == 2 ? (n3 & 1u) : 0u, use = ny == 2 ? (n3 >> 1) : n3;
   if (use > 0) mbar_wait(&y_free[yb], (use - 1) & 1u);   // the tile that used this image buffer last has left it (bulk store, UMMAs)
-  if (nd == 1 && n3 > 0 && Aout != nullptr) drain_d3(id, prev_tile[0], g, Aout, tmem_d3, d3_full, n3 - 1);
+  if (!cfg.ext && nd == 1 && n3 > 0 && Aout != nullptr) drain_d3(id, prev_tile[0], g, Aout, tmem_d3, d3_full, n3 - 1);
   if ((threadIdx.x & 255) == 0) TR(id.w, n3, 7);
   uint8_t* dst = sY + yb * kTileBytes + id.row * 16 + id.half * 4096;
 #pragma unroll
@@ -115,7 +116,7 @@ __device__ __forceinline__ void finish_tile(const float2 (&v)[8], const EpiId& i
   mbar_arrive(&xt_full[yb]);
   if ((threadIdx.x & 255) == 0) TR(id.w, n3, 4);
   const uint32_t back = (uint32_t)nd - 1u;
-  if (nd > 1 && n3 >= back && Aout != nullptr) {
+  if (!cfg.ext && nd > 1 && n3 >= back && Aout != nullptr) {
     const uint32_t k = n3 - back;
     const int kt = nd == 3 ? ((k & 1u) ? prev_tile[1] : prev_tile[0]) : prev_tile[0];
     drain_d3(id, kt, g, Aout, tmem_d3 + 32u * d3_slot(k, nd), &d3_full[d3_slot(k, nd)], d3_use(k, nd));
@@ -141,12 +142,14 @@ __device__ __forceinline__ void drain_tail(const EpiId& id, const TcGeom& g, flo
 // hi*lo; when `dft`), bulk store of the image, release of the buffer
 __device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint32_t aF, uint8_t* sY, uint8_t* y_dst,
                                                  uint32_t tmem_d3, uint64_t* xt_full, uint64_t* d3_full, uint64_t* y_free,
-                                                 uint32_t n, const TailCfg cfg, bool tr_on = false, int tw = 0) {
+                                                 uint32_t n, const TailCfg cfg, bool tr_on = false, int tw = 0,
+                                                 uint64_t* d3_empty = nullptr) {
   const int ny = cfg.ny, nd = cfg.nd;
   const uint32_t yb = ny == 2 ? (n & 1u) : 0u, use = ny == 2 ? (n >> 1) : n;
   sY += yb * kTileBytes;
   mbar_wait(&xt_full[yb], use & 1u);
   TR(tw, n, 5);
+  if (dft && cfg.ext && d3_use(n, nd) > 0) mbar_wait(&d3_empty[d3_slot(n, nd)], (d3_use(n, nd) - 1) & 1u);   // drained by the drain warps
   tc_fence_after();
   if (dft) {
     const uint32_t idesc = idesc_bf16(64, 32) | kIdescBMnMajor;
@@ -165,9 +168,23 @@ __device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint
   }
   bulk_s2g_p(leader, y_dst, sY, kTileBytes);
   bulk_commit();
-  bulk_wait_read0();
-  if (dft) umma_commit_p(leader, &y_free[yb]);   // arrives when the UMMAs above have read the image too
-  else mbar_arrive_p(leader, &y_free[yb]);
+  if (cfg.ext) {
+    // y_free takes two arrivals per use: the UMMAs above have read the image / the bulk store has.  With two image
+    // buffers the control warp does not sit out the store's read: it confirms the store of tile n - 1 here.
+    if (dft) umma_commit_p(leader, &y_free[yb]);
+    else mbar_arrive_p(leader, &y_free[yb]);
+    if (ny == 2) {
+      bulk_wait_read1();
+      if (n > 0) mbar_arrive_p(leader, &y_free[yb ^ 1u]);
+    } else {
+      bulk_wait_read0();
+      mbar_arrive_p(leader, &y_free[yb]);
+    }
+  } else {
+    bulk_wait_read0();
+    if (dft) umma_commit_p(leader, &y_free[yb]);   // arrives when the UMMAs above have read the image too
+    else mbar_arrive_p(leader, &y_free[yb]);
+  }
   __syncwarp();
 }
 
@@ -200,10 +217,11 @@ struct LayerSmem {   // byte offsets; the inverse W-DFT operands scale with KZ
   }
 };
 constexpr int kLayerSmemMax = 226 * 1024;   // 227 KB per CTA minus the kernel's static shared memory
-enum { LB_XFULL = 0, LB_XFREE = 3, LB_DFULL = 6, LB_DEMPTY = 8, LB_XTFULL = 10, LB_D3FULL = 12, LB_YFREE = 15, LB_PER = 17 };
+enum { LB_XFULL = 0, LB_XFREE = 3, LB_DFULL = 6, LB_DEMPTY = 8, LB_XTFULL = 10, LB_D3FULL = 12, LB_YFREE = 15, LB_D3EMPTY = 17, LB_PER = 20 };
+constexpr int kCtaLayerAll = kCtaLayer + 2 * 32;      // + two drain warps (TMEM lane quarters 0 and 1)
 }  // namespace
 
-__global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerArgs a) {
+__global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLayerArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_launch_dependents();
   __shared__ uint64_t bars[2 * LB_PER + 1];
@@ -211,7 +229,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform
   const TcGeom g = a.g;
   const LayerSmem L(g.KZ, a.ny);
-  const TailCfg tail{a.ny, a.ny == 2 ? 3 : 1};
+  const TailCfg tail{a.ny, a.ny == 2 ? 3 : 1, true};
   [[maybe_unused]] const bool tr_on = a.gelu && a.Aout != nullptr;      // trace builds: a layer with GELU and forward W-DFT
   float* sBias = reinterpret_cast<float*>(smem + L.Bias);
   uint64_t* bar_const = &bars[2 * LB_PER];
@@ -232,8 +250,9 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
       mbar_init(&b[LB_D3FULL], 1);
       mbar_init(&b[LB_D3FULL + 1], 1);
       mbar_init(&b[LB_D3FULL + 2], 1);
-      mbar_init(&b[LB_YFREE], 1);
-      mbar_init(&b[LB_YFREE + 1], 1);
+      mbar_init(&b[LB_YFREE], 2);
+      mbar_init(&b[LB_YFREE + 1], 2);
+      for (int i = 0; i < 3; ++i) mbar_init(&b[LB_D3EMPTY + i], 2);
     }
     mbar_init(bar_const, 1);
     fence_mbar_init();
@@ -256,7 +275,48 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
   }
   const int stride = gridDim.x * 2;
 
-  if (warp >= kCtlWarp + 2) {
+  if (warp >= kCtlWarp + 4) {
+    // ---------------- drain warps: the forward W-DFT accumulators of both workers -> planar spectrum ----------------
+    // (an M = 64 accumulator keeps row r in TMEM lane 32 * (r / 16) + r % 16: warp q of the two reads rows 16 q .. 16 q + 15,
+    //  one 128-byte row of Aout[b][kx][h][re|im][32] per lane.  In the epilogue group this drain sat on the
+    //  critical path of every tile: a TMEM round trip, the address arithmetic and the stores, ~1.3 k cycles.)
+    if (a.Aout != nullptr) {
+      const int q = warp - kCtlWarp - 4, lane = tid & 31;
+      const int row = q * 16 + lane;
+      const int h2 = row / g.KXP, rem = row - h2 * g.KXP, kx = rem >> 1, reim = rem & 1;
+      const bool live = lane < 16 && h2 < g.RT && kx < g.Kc;
+      const int nd = tail.nd;
+      for (uint32_t u = 0;; ++u) {
+        const int t0 = blockIdx.x * 2 + (int)u * stride;
+        if (t0 >= g.ntiles) break;
+        for (int w = 0; w < 2; ++w) {
+          const int tile = t0 + w;
+          if (tile >= g.ntiles) break;
+          uint64_t* b = bars + w * LB_PER;
+          const uint32_t sl = d3_slot(u, nd);
+          mbar_wait(&b[LB_D3FULL + sl], d3_use(u, nd) & 1u);
+          tc_fence_after();
+          uint32_t r[32];
+          const uint32_t ta = tmem_s + 256u * w + 64u + 32u * sl + ((uint32_t)(q * 32) << 16);
+          tmem_ld16(ta, r);
+          tmem_ld16(ta + 16u, r + 16);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&b[LB_D3EMPTY + sl]);
+          if (live) {
+            const int grow = tile * g.RT + h2;
+            const int bb = grow / g.H, h = grow - bb * g.H;
+            float4* dst = reinterpret_cast<float4*>(a.Aout + ((((size_t)bb * g.Kc + kx) * g.H + h) * 2 + reim) * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                   __uint_as_float(r[4 * j + 3]));
+          }
+        }
+      }
+    }
+  } else if (warp >= kCtlWarp + 2) {
     // ---------------- loader / finisher lane: input bulk copies, forward W-DFT, image store ----------------
     // (its own warp so that a late input never delays handing a finished tile on, and vice versa)
     {
@@ -284,7 +344,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
       for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
         if (tile + kLayerSlots * stride < g.ntiles) load_inputs(tile + kLayerSlots * stride, u + kLayerSlots);
         ctrl_finish_tile(leader, a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64,
-                         &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], u, tail, tr_on, w);
+                         &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], u, tail, tr_on, w, &b[LB_D3EMPTY]);
         TR(w, u, 6);
       }
       bulk_wait0();
@@ -365,7 +425,6 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_layer_kernel(const TcLayerAr
       finish_tile(v, id, tile, g, a.Aout, ws + L.Y, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], n3,
                   prev_tile, tail, tr_on);
     }
-    drain_tail(id, g, a.Aout, tmem_s + 256u * w + 64, &b[LB_D3FULL], n3, prev_tile, tail);
   }
   tc_fence_before();
   __syncthreads();
@@ -386,7 +445,7 @@ int launch_tc_layer(const TcLayerArgs& a_in, cudaStream_t st) {
   DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
-  DLWP_CUDA(launch_pdl(fno_layer_kernel, dim3(grid), dim3(kCtaLayer), (size_t)L.Total, st, a));
+  DLWP_CUDA(launch_pdl(fno_layer_kernel, dim3(grid), dim3(kCtaLayerAll), (size_t)L.Total, st, a));
   DLWP_LAUNCHED("fno_layer_kernel");
   return DLWP_OK;
 }
@@ -649,7 +708,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       const bool dft = a.Aout != nullptr;
       auto finish = [&](int tile, uint32_t n) {
         ctrl_finish_tile(leader, dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
-                         &b[MB_YFREE], n, TailCfg{1, 2});
+                         &b[MB_YFREE], n, TailCfg{1, 2, false});
       };
       mbar_wait(bar_const, 0);
       if (first < g.ntiles) is.mma1<16>(0, 0, 0);
@@ -721,7 +780,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
         }
       }
       finish_tile(v, id, tile_f, g, a.Aout, ws + LiftSmem::Y, tmem_w + 192u, &b[MB_XTFULL], &b[MB_D3FULL], &b[MB_YFREE], n3,
-                  prev_tile, TailCfg{1, 2});
+                  prev_tile, TailCfg{1, 2, false});
     };
     const int a1_pass = P >= 3 ? P - 2 : 0;      // the next tile's gathered inputs are consumed as late as the issuer allows
     for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
@@ -733,7 +792,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       });
     }
     if (u > 0) finish_ep(first + (int)(u - 1) * stride, u - 1);
-    drain_tail(id, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3, prev_tile, TailCfg{1, 2});
+    drain_tail(id, g, a.Aout, tmem_w + 192u, &b[MB_D3FULL], n3, prev_tile, TailCfg{1, 2, false});
   }
   tc_fence_before();
   __syncthreads();
