@@ -88,7 +88,9 @@ __device__ __forceinline__ void drain_d3(const EpiId& id, int tile, const TcGeom
 // prev_tile: nd = 3 keeps tile n in prev_tile[n & 1]; otherwise prev_tile[0] is the last tile.
 struct TailCfg {
   int ny, nd;
-  bool ext;      // the accumulators are drained by dedicated warps (layer kernel), not by the epilogue group
+  bool ext;      // the accumulators are drained by dedicated warps (layer kernel), not by the epilogue group;
+                 // the W-DFT then runs as F_hi x [Y_hi | Y_lo] (N = 64) + F_lo x Y_hi (N = 32): 16 UMMAs instead of 24
+                 // (shared-memory operand traffic bounds this kernel), accumulators 64 TMEM columns apart
 };
 __device__ __forceinline__ uint32_t d3_slot(uint32_t n, int nd) { return nd == 3 ? n % 3u : nd == 2 ? (n & 1u) : 0u; }
 __device__ __forceinline__ uint32_t d3_use(uint32_t n, int nd) { return nd == 3 ? n / 3u : nd == 2 ? (n >> 1) : n; }
@@ -156,13 +158,24 @@ __device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint
     // A: the 32-row image read as M = 64 (rows 32..63 alias the next K chunk: their accumulator
     // rows are never looked at); B: 8x8 core matrices 128 B apart along pixels, 2048 B along channels
     const uint64_t dF = chunk_desc(aF, 32, 0), dY = smem_desc(smem_u32(sY), 128, 2048);
-#pragma unroll
-    for (int term = 0; term < 3; ++term) {
-      const uint32_t fa = term == 1 ? 32u * 128u * 2u : 0u, yp = term == 2 ? (uint32_t)kImg : 0u;
+    if (cfg.ext) {
+      // the lo image follows the hi image 4 channel groups (4 x 2048 B) on: one N = 64 operand [Y_hi | Y_lo]
+      const uint32_t idesc64 = idesc_bf16(64, 64) | kIdescBMnMajor, d = tmem_d3 + 64u * d3_slot(n, nd);
 #pragma unroll
       for (int k0 = 0; k0 < 128; k0 += 16)
-        umma_bf16_p(leader, tmem_d3 + 32u * d3_slot(n, nd), desc_off(dF, fa + (k0 >> 3) * 512), desc_off(dY, yp + k0 * 16), idesc,
-                    (term | k0) != 0);
+        umma_bf16_p(leader, d, desc_off(dF, (k0 >> 3) * 512), desc_off(dY, k0 * 16), idesc64, k0 != 0);
+#pragma unroll
+      for (int k0 = 0; k0 < 128; k0 += 16)
+        umma_bf16_p(leader, d, desc_off(dF, 32u * 128u * 2u + (k0 >> 3) * 512), desc_off(dY, k0 * 16), idesc, 1);
+    } else {
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t fa = term == 1 ? 32u * 128u * 2u : 0u, yp = term == 2 ? (uint32_t)kImg : 0u;
+#pragma unroll
+        for (int k0 = 0; k0 < 128; k0 += 16)
+          umma_bf16_p(leader, tmem_d3 + 32u * d3_slot(n, nd), desc_off(dF, fa + (k0 >> 3) * 512), desc_off(dY, yp + k0 * 16), idesc,
+                      (term | k0) != 0);
+      }
     }
     umma_commit_p(leader, &d3_full[d3_slot(n, nd)]);
   }
@@ -296,10 +309,12 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
           const uint32_t sl = d3_slot(u, nd);
           mbar_wait(&b[LB_D3FULL + sl], d3_use(u, nd) & 1u);
           tc_fence_after();
-          uint32_t r[32];
-          const uint32_t ta = tmem_s + 256u * w + 64u + 32u * sl + ((uint32_t)(q * 32) << 16);
+          uint32_t r[32], r2[32];      // columns 0..31: F_hi Y_hi + F_lo Y_hi, 32..63: F_hi Y_lo
+          const uint32_t ta = tmem_s + 256u * w + 64u + 64u * sl + ((uint32_t)(q * 32) << 16);
           tmem_ld16(ta, r);
           tmem_ld16(ta + 16u, r + 16);
+          tmem_ld16(ta + 32u, r2);
+          tmem_ld16(ta + 48u, r2 + 16);
           tmem_ld_wait();
           tc_fence_before();
           __syncwarp();
@@ -310,8 +325,10 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
             float4* dst = reinterpret_cast<float4*>(a.Aout + ((((size_t)bb * g.Kc + kx) * g.H + h) * 2 + reim) * 32);
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-              dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
-                                   __uint_as_float(r[4 * j + 3]));
+              dst[j] = make_float4(__uint_as_float(r[4 * j]) + __uint_as_float(r2[4 * j]),
+                                   __uint_as_float(r[4 * j + 1]) + __uint_as_float(r2[4 * j + 1]),
+                                   __uint_as_float(r[4 * j + 2]) + __uint_as_float(r2[4 * j + 2]),
+                                   __uint_as_float(r[4 * j + 3]) + __uint_as_float(r2[4 * j + 3]));
           }
         }
       }
