@@ -326,7 +326,7 @@ def config_block(args, wl, members):
 def ncu_traffic(kernel):
     """DRAM bytes per launch of `kernel` from the committed `ncu --set full` summary (profiles/), or None."""
     import csv
-    path = os.path.join(ROOT, "profiles", "r01_ncu_full_tc_v3.csv")
+    path = os.path.join(ROOT, "profiles", "r01_ncu_full_tc_v5.csv")
     try:
         with open(path) as f:
             rows = list(csv.reader(f))
@@ -464,7 +464,7 @@ def run_ours(args, wl):
             roof["algorithmic_bytes_per_launch"] = per_launch
         if args.workload == "c4" and members == members_default:
             roof["traffic"] = ncu_traffic(name)
-            roof["traffic_source"] = "profiles/r01_ncu_full_tc_v3.csv (ncu --set full of this command, mean over the kernel's launches)"
+            roof["traffic_source"] = "profiles/r01_ncu_full_tc_v5.csv (ncu --set full of this command, mean over the kernel's launches)"
         fl = step_flops(cls, kw, members, H, W)
         sb = step_bytes(cls, kw, members, H, W)
         spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel",
