@@ -67,15 +67,55 @@ def synthetic_inputs(kw, members, T, H, W, seed, pin):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
+    """SM clock / throttle reasons sampled while the timed region runs: NVML in-process every 10 ms (the timed
+    region of the default run is a few tens of ms), `nvidia-smi -lms 100` when NVML is not importable."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    # NVML clocks-event-reason bits
+    BITS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.samples = index, None, [], []
+        self.stop, self.thread, self.nvml = threading.Event(), None, None
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = self.index
+        if vis:
+            try:
+                idx = int(vis.split(",")[self.index])
+            except (ValueError, IndexError):
+                pass
+        return pynvml, pynvml.nvmlDeviceGetHandleByIndex(idx)
+
+    def _poll(self, pynvml, h):
+        mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+        while True:
+            try:
+                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                try:
+                    bits = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except AttributeError:
+                    bits = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((float(sm), float(mx), int(bits)))
+            except Exception:
+                pass
+            if self.stop.is_set():
+                break
+            self.stop.wait(0.01)
 
     def __enter__(self):
+        try:
+            pynvml, h = self._nvml_handle()
+            self.nvml = pynvml
+            self.thread = threading.Thread(target=self._poll, args=(pynvml, h), daemon=True)
+            self.thread.start()
+            return self
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -91,7 +131,10 @@ class ClockSampler:
             self.lines.append(line.strip())
 
     def __exit__(self, *exc):
-        if self.proc is not None:
+        if self.nvml is not None:
+            self.stop.set()
+            self.thread.join(timeout=2)      # (the poll loop takes its last sample after the stop request)
+        elif self.proc is not None:
             time.sleep(0.15)
             self.proc.terminate()
             try:
@@ -103,6 +146,12 @@ class ClockSampler:
     def summary(self):
         sm, mx, reasons = [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for s_, m_, bits in self.samples:
+            sm.append(s_)
+            mx.append(m_)
+            for n, bit in self.BITS:
+                if bits & bit:
+                    reasons.add(n)
         for line in self.lines:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) < 6:
@@ -118,7 +167,8 @@ class ClockSampler:
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvml" if self.samples else "nvidia-smi"}
 
 
 # ----------------------------------------------------------------------------------------
