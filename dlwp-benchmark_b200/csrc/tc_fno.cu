@@ -278,7 +278,8 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
+  // constant operands (packed at weight-commit time, which ends with a stream synchronisation): requested before the
+  // programmatic-dependent-launch wait, so that on a partly filled machine they arrive under the previous kernel
   const uint32_t g_bytes = 2u * 128u * (uint32_t)g.KZ * 2u, z_bytes = (uint32_t)g.KZ * 128u;
   if (tid == 0) {
     mbar_arrive_expect_tx(bar_const, g_bytes + kFBytes + 4096);
@@ -286,6 +287,7 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
     bulk_g2s(smem + L.F, a.Fimg, kFBytes, bar_const);
     bulk_g2s(smem + L.Ws, a.Wsimg, 4096, bar_const);
   }
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const int stride = gridDim.x * 2;
 
   if (warp >= kCtlWarp + 4) {
@@ -519,14 +521,14 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const uint32_t w1_bytes = (uint32_t)hid * 32 * 4, w2_bytes = 16u * hid * 4, w1x_bytes = (uint32_t)hid * 16 * 2;
-  if (tid == 0) {
+  if (tid == 0) {   // constant operands: requested before the programmatic-dependent-launch wait
     mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + w1x_bytes);
     bulk_g2s(smem + ProjSmem::W1, a.W1img, w1_bytes, bar_const);
     bulk_g2s(smem + ProjSmem::W2, a.W2img, w2_bytes, bar_const);
     bulk_g2s(smem + ProjSmem::W1x, a.W1ximg, w1x_bytes, bar_const);
   }
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const int stride = gridDim.x * 2;
 
   if (warp >= kCtlWarp) {
@@ -702,14 +704,14 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const uint32_t w1_bytes = (uint32_t)hid * 16 * 4, w2_bytes = 32u * hid * 4;
-  if (tid == 0) {
+  if (tid == 0) {   // constant operands: requested before the programmatic-dependent-launch wait
     mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + kFBytes);
     bulk_g2s(smem + LiftSmem::W1, a.W1img, w1_bytes, bar_const);
     bulk_g2s(smem + LiftSmem::W2, a.W2img, w2_bytes, bar_const);
     bulk_g2s(smem + LiftSmem::F, a.Fimg, kFBytes, bar_const);
   }
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const int stride = gridDim.x * 2;
 
   if (warp >= kCtlWarp) {
