@@ -36,6 +36,8 @@ void free_plan(dlwp_plan* p) {
   if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
   for (cudaEvent_t e : p->frame_ready) cudaEventDestroy(e);
   if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
+  if (p->half_ready) cudaEventDestroy(p->half_ready);
+  if (p->half_done) cudaEventDestroy(p->half_done);
   delete p;
 }
 
@@ -227,19 +229,40 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
   // host -> device: only what the loop reads.  Of `prognostic` that is the first `ctx` frames of
   // every sample (fno.py:83,91-95 never look at later ground-truth frames), kept at their place
   // in the [B, T, Cg, H, W] staging layout so the frame bookkeeping is the device entry's.
-  if (nb[0]) DLWP_CUDA(cudaMemcpyAsync(plan->stage[0], constants, nb[0], cudaMemcpyHostToDevice, st));
+  // Large batches: the first and the last step run as two half batches, so that the second half's initial frames
+  // arrive under the first half's first step and the first half's last frame leaves under the second half's last step
+  // (the other steps run on the whole batch: every kernel launch has a fixed cost).
+  const bool split = batch >= 64 && batch % 2 == 0 && steps >= 2;
+  const size_t Ba = split ? B / 2 : B, Bb = B - Ba;      // members of the two halves
+  if (!plan->h2d_stream) DLWP_CUDA(cudaStreamCreateWithFlags(&plan->h2d_stream, cudaStreamNonBlocking));
+  if (split && !plan->half_ready) DLWP_CUDA(cudaEventCreateWithFlags(&plan->half_ready, cudaEventDisableTiming));
+  const size_t const_row = (size_t)d.constant_channels * frame;
+  if (nb[0]) {
+    DLWP_CUDA(cudaMemcpyAsync(plan->stage[0], constants, Ba * const_row, cudaMemcpyHostToDevice, st));
+    if (split)
+      DLWP_CUDA(cudaMemcpyAsync((char*)plan->stage[0] + Ba * const_row, (const char*)constants + Ba * const_row, Bb * const_row,
+                                cudaMemcpyHostToDevice, plan->h2d_stream));
+  }
   // prescribed: step t reads frames [t - ctx, t) (fno.py:86,98).  The first ctx frames go ahead of the first
   // step; frame f >= ctx is first needed by step f + 1 and arrives on a second copy stream under the
   // compute of the earlier steps (the last frame is never read).
   const size_t presc_pitch = (size_t)T * d.prescribed_channels * frame, presc_row = (size_t)d.prescribed_channels * frame;
   if (nb[1]) {
-    DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[1], presc_pitch, prescribed, presc_pitch, (size_t)ctx * presc_row, B,
+    DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[1], presc_pitch, prescribed, presc_pitch, (size_t)ctx * presc_row, Ba,
                                 cudaMemcpyHostToDevice, st));
-    if (!plan->h2d_stream) DLWP_CUDA(cudaStreamCreateWithFlags(&plan->h2d_stream, cudaStreamNonBlocking));
+    if (split)
+      DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[1] + Ba * presc_pitch, presc_pitch, (const char*)prescribed + Ba * presc_pitch,
+                                  presc_pitch, (size_t)ctx * presc_row, Bb, cudaMemcpyHostToDevice, plan->h2d_stream));
     while ((int)plan->frame_ready.size() < T) {
       cudaEvent_t e = nullptr;
       DLWP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
       plan->frame_ready.push_back(e);
+    }
+    if (split) {   // the second half's context frames of `prognostic` go ahead of the later prescribed frames
+      const size_t pp = (size_t)T * d.prognostic_channels * frame;
+      DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[2] + Ba * pp, pp, (const char*)prognostic + Ba * pp, pp,
+                                  (size_t)ctx * d.prognostic_channels * frame, Bb, cudaMemcpyHostToDevice, plan->h2d_stream));
+      DLWP_CUDA(cudaEventRecord(plan->half_ready, plan->h2d_stream));
     }
     for (int f = ctx; f < T - 1; ++f) {
       const size_t off = (size_t)f * presc_row;
@@ -249,24 +272,49 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
     }
   }
   const size_t prog_pitch = (size_t)T * d.prognostic_channels * frame;
-  DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[2], prog_pitch, prognostic, prog_pitch, (size_t)ctx * d.prognostic_channels * frame, B,
+  DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[2], prog_pitch, prognostic, prog_pitch, (size_t)ctx * d.prognostic_channels * frame, Ba,
                               cudaMemcpyHostToDevice, st));
+  if (split && !nb[1]) {
+    DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[2] + Ba * prog_pitch, prog_pitch, (const char*)prognostic + Ba * prog_pitch, prog_pitch,
+                                (size_t)ctx * d.prognostic_channels * frame, Bb, cudaMemcpyHostToDevice, plan->h2d_stream));
+    DLWP_CUDA(cudaEventRecord(plan->half_ready, plan->h2d_stream));
+  }
   // the loop of dlwp_rollout; every lead time's frame starts its way back to the host on a second
   // stream as soon as its projection kernel is done, under the following steps' compute
   float* dev_outs = (float*)plan->stage[3];
   const size_t out_pitch = (size_t)steps * d.prognostic_channels * frame, out_row = (size_t)d.prognostic_channels * frame;
-  for (int t = ctx; t < T; ++t) {
+  const float* dc = constants ? (const float*)plan->stage[0] : nullptr;
+  const float* dp = prescribed ? (const float*)plan->stage[1] : nullptr;
+  const float* dg = (const float*)plan->stage[2];
+  const size_t cs = (size_t)d.constant_channels * HW, ps = (size_t)T * d.prescribed_channels * HW,
+               gs = (size_t)T * d.prognostic_channels * HW, os = (size_t)steps * d.prognostic_channels * HW;      // floats per member
+  auto run = [&](int t, size_t b0, size_t nbm) -> int {      // step t on members [b0, b0 + nbm)
     StepIO io;
-    rollout_io(plan, constants ? (const float*)plan->stage[0] : nullptr, prescribed ? (const float*)plan->stage[1] : nullptr,
-               (const float*)plan->stage[2], dev_outs, T, t, &io);
-    if (nb[1] && t - 1 >= ctx) DLWP_CUDA(cudaStreamWaitEvent(st, plan->frame_ready[t - 1], 0));
-    DLWP_TRY(plan_backbone(plan, io, batch, st));
-    cudaEvent_t ev = plan->step_done[t - ctx];
+    rollout_io(plan, dc ? dc + b0 * cs : nullptr, dp ? dp + b0 * ps : nullptr, dg + b0 * gs, dev_outs + b0 * os, T, t, &io);
+    return plan_backbone(plan, io, (int)nbm, st);
+  };
+  auto send_back = [&](int t, size_t b0, size_t nbm, cudaEvent_t ev) -> int {      // lead time t's frames of these members -> host
     DLWP_CUDA(cudaEventRecord(ev, st));
     DLWP_CUDA(cudaStreamWaitEvent(plan->copy_stream, ev, 0));
-    const size_t off = (size_t)(t - ctx) * d.prognostic_channels * HW;
-    DLWP_CUDA(cudaMemcpy2DAsync(outs + off, out_pitch, dev_outs + off, out_pitch, out_row, B, cudaMemcpyDeviceToHost,
+    const size_t off = b0 * os + (size_t)(t - ctx) * d.prognostic_channels * HW;
+    DLWP_CUDA(cudaMemcpy2DAsync(outs + off, out_pitch, dev_outs + off, out_pitch, out_row, nbm, cudaMemcpyDeviceToHost,
                                 plan->copy_stream));
+    return DLWP_OK;
+  };
+  if (split && !plan->half_done) DLWP_CUDA(cudaEventCreateWithFlags(&plan->half_done, cudaEventDisableTiming));
+  for (int t = ctx; t < T; ++t) {
+    if (nb[1] && t - 1 >= ctx) DLWP_CUDA(cudaStreamWaitEvent(st, plan->frame_ready[t - 1], 0));
+    const bool halves = split && (t == ctx || t == T - 1);
+    if (!halves) {
+      DLWP_TRY(run(t, 0, B));
+      DLWP_TRY(send_back(t, 0, B, plan->step_done[t - ctx]));
+    } else {
+      DLWP_TRY(run(t, 0, Ba));
+      DLWP_TRY(send_back(t, 0, Ba, plan->half_done));
+      if (t == ctx) DLWP_CUDA(cudaStreamWaitEvent(st, plan->half_ready, 0));
+      DLWP_TRY(run(t, Ba, Bb));
+      DLWP_TRY(send_back(t, Ba, Bb, plan->step_done[t - ctx]));
+    }
   }
   cudaEvent_t fin = plan->step_done[steps];
   DLWP_CUDA(cudaEventRecord(fin, plan->copy_stream));

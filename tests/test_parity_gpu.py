@@ -287,10 +287,12 @@ def test_fourcastnet_fno2d_filter_matches_oracle(pkg, H, W, E):
 # ---------------------------------------------------------------------------------------
 # host entry, metrics kernel, weight reload
 # ---------------------------------------------------------------------------------------
-@pytest.mark.parametrize("ctx,T", [(1, 4), (2, 7)])
-def test_rollout_host_equals_device_rollout(pkg, ctx, T):
+@pytest.mark.parametrize("ctx,T,members", [(1, 4, None), (2, 7, None), (1, 4, 64), (2, 5, 66), (1, 2, 64)])
+def test_rollout_host_equals_device_rollout(pkg, ctx, T, members):
     # the host entry streams the later prescribed frames in under the earlier steps: same bits as the device entry
+    # (64 members or more: the host entry runs the first and the last step as two half batches)
     cls, kw, (B, H, W) = FNO_CASES["C2"]
+    B = members or B
     kw = dict(kw, context_size=ctx)
     torch.manual_seed(1234)
     mod = getattr(pkg, cls)(**kw).cuda().eval()
