@@ -36,8 +36,7 @@ void free_plan(dlwp_plan* p) {
   if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
   for (cudaEvent_t e : p->frame_ready) cudaEventDestroy(e);
   if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
-  if (p->half_ready) cudaEventDestroy(p->half_ready);
-  if (p->half_done) cudaEventDestroy(p->half_done);
+  for (cudaEvent_t e : p->part_ev) cudaEventDestroy(e);
   delete p;
 }
 
@@ -226,43 +225,44 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
     DLWP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     plan->step_done.push_back(e);
   }
-  // host -> device: only what the loop reads.  Of `prognostic` that is the first `ctx` frames of
-  // every sample (fno.py:83,91-95 never look at later ground-truth frames), kept at their place
-  // in the [B, T, Cg, H, W] staging layout so the frame bookkeeping is the device entry's.
-  // Large batches: the first and the last step run as two half batches, so that the second half's initial frames
-  // arrive under the first half's first step and the first half's last frame leaves under the second half's last step
-  // (the other steps run on the whole batch: every kernel launch has a fixed cost).
-  const bool split = batch >= 64 && batch % 2 == 0 && steps >= 2;
-  const size_t Ba = split ? B / 2 : B, Bb = B - Ba;      // members of the two halves
+  // Large batches: the first and the last step run in K parts of the members, so that the later parts' initial frames
+  // arrive under the first part's first step and the earlier parts' last frames leave under the later parts' last
+  // step (the other steps run on the whole batch: every kernel launch has a fixed cost).
+  const int K = (steps >= 2 && batch >= 64 && batch % 2 == 0) ? 2 : 1;      // (four parts at 256 members measured no better than two)
+  const size_t Bp = B / K;      // members per part
   if (!plan->h2d_stream) DLWP_CUDA(cudaStreamCreateWithFlags(&plan->h2d_stream, cudaStreamNonBlocking));
-  if (split && !plan->half_ready) DLWP_CUDA(cudaEventCreateWithFlags(&plan->half_ready, cudaEventDisableTiming));
-  const size_t const_row = (size_t)d.constant_channels * frame;
-  if (nb[0]) {
-    DLWP_CUDA(cudaMemcpyAsync(plan->stage[0], constants, Ba * const_row, cudaMemcpyHostToDevice, st));
-    if (split)
-      DLWP_CUDA(cudaMemcpyAsync((char*)plan->stage[0] + Ba * const_row, (const char*)constants + Ba * const_row, Bb * const_row,
-                                cudaMemcpyHostToDevice, plan->h2d_stream));
+  while ((int)plan->part_ev.size() < 2 * K) {      // [k]: part k's initial frames are on the device; [K + k]: part k's step is done
+    cudaEvent_t e = nullptr;
+    DLWP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    plan->part_ev.push_back(e);
   }
-  // prescribed: step t reads frames [t - ctx, t) (fno.py:86,98).  The first ctx frames go ahead of the first
-  // step; frame f >= ctx is first needed by step f + 1 and arrives on a second copy stream under the
-  // compute of the earlier steps (the last frame is never read).
+  const size_t const_row = (size_t)d.constant_channels * frame;
   const size_t presc_pitch = (size_t)T * d.prescribed_channels * frame, presc_row = (size_t)d.prescribed_channels * frame;
+  const size_t prog_pitch = (size_t)T * d.prognostic_channels * frame;
+  // host -> device: only what the loop reads.  Of `prognostic` that is the first `ctx` frames of every sample
+  // (fno.py:83,91-95 never look at later ground-truth frames), kept at their place in the [B, T, Cg, H, W] staging
+  // layout so the frame bookkeeping is the device entry's.  Part 0 goes on the caller's stream, the others on the
+  // copy-in stream ahead of the later prescribed frames.
+  for (int k = 0; k < K; ++k) {
+    cudaStream_t cs_ = k == 0 ? st : plan->h2d_stream;
+    const size_t b0 = (size_t)k * Bp;
+    if (nb[0])
+      DLWP_CUDA(cudaMemcpyAsync((char*)plan->stage[0] + b0 * const_row, (const char*)constants + b0 * const_row, Bp * const_row,
+                                cudaMemcpyHostToDevice, cs_));
+    if (nb[1])
+      DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[1] + b0 * presc_pitch, presc_pitch, (const char*)prescribed + b0 * presc_pitch,
+                                  presc_pitch, (size_t)ctx * presc_row, Bp, cudaMemcpyHostToDevice, cs_));
+    DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[2] + b0 * prog_pitch, prog_pitch, (const char*)prognostic + b0 * prog_pitch, prog_pitch,
+                                (size_t)ctx * d.prognostic_channels * frame, Bp, cudaMemcpyHostToDevice, cs_));
+    if (k > 0) DLWP_CUDA(cudaEventRecord(plan->part_ev[k], plan->h2d_stream));
+  }
+  // prescribed: step t reads frames [t - ctx, t) (fno.py:86,98).  Frame f >= ctx is first needed by step f + 1 and
+  // arrives on the copy-in stream under the compute of the earlier steps (the last frame is never read).
   if (nb[1]) {
-    DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[1], presc_pitch, prescribed, presc_pitch, (size_t)ctx * presc_row, Ba,
-                                cudaMemcpyHostToDevice, st));
-    if (split)
-      DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[1] + Ba * presc_pitch, presc_pitch, (const char*)prescribed + Ba * presc_pitch,
-                                  presc_pitch, (size_t)ctx * presc_row, Bb, cudaMemcpyHostToDevice, plan->h2d_stream));
     while ((int)plan->frame_ready.size() < T) {
       cudaEvent_t e = nullptr;
       DLWP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
       plan->frame_ready.push_back(e);
-    }
-    if (split) {   // the second half's context frames of `prognostic` go ahead of the later prescribed frames
-      const size_t pp = (size_t)T * d.prognostic_channels * frame;
-      DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[2] + Ba * pp, pp, (const char*)prognostic + Ba * pp, pp,
-                                  (size_t)ctx * d.prognostic_channels * frame, Bb, cudaMemcpyHostToDevice, plan->h2d_stream));
-      DLWP_CUDA(cudaEventRecord(plan->half_ready, plan->h2d_stream));
     }
     for (int f = ctx; f < T - 1; ++f) {
       const size_t off = (size_t)f * presc_row;
@@ -270,14 +270,6 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
                                   B, cudaMemcpyHostToDevice, plan->h2d_stream));
       DLWP_CUDA(cudaEventRecord(plan->frame_ready[f], plan->h2d_stream));
     }
-  }
-  const size_t prog_pitch = (size_t)T * d.prognostic_channels * frame;
-  DLWP_CUDA(cudaMemcpy2DAsync(plan->stage[2], prog_pitch, prognostic, prog_pitch, (size_t)ctx * d.prognostic_channels * frame, Ba,
-                              cudaMemcpyHostToDevice, st));
-  if (split && !nb[1]) {
-    DLWP_CUDA(cudaMemcpy2DAsync((char*)plan->stage[2] + Ba * prog_pitch, prog_pitch, (const char*)prognostic + Ba * prog_pitch, prog_pitch,
-                                (size_t)ctx * d.prognostic_channels * frame, Bb, cudaMemcpyHostToDevice, plan->h2d_stream));
-    DLWP_CUDA(cudaEventRecord(plan->half_ready, plan->h2d_stream));
   }
   // the loop of dlwp_rollout; every lead time's frame starts its way back to the host on a second
   // stream as soon as its projection kernel is done, under the following steps' compute
@@ -301,19 +293,17 @@ int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* pres
                                 plan->copy_stream));
     return DLWP_OK;
   };
-  if (split && !plan->half_done) DLWP_CUDA(cudaEventCreateWithFlags(&plan->half_done, cudaEventDisableTiming));
   for (int t = ctx; t < T; ++t) {
     if (nb[1] && t - 1 >= ctx) DLWP_CUDA(cudaStreamWaitEvent(st, plan->frame_ready[t - 1], 0));
-    const bool halves = split && (t == ctx || t == T - 1);
-    if (!halves) {
+    if (K == 1 || (t != ctx && t != T - 1)) {
       DLWP_TRY(run(t, 0, B));
       DLWP_TRY(send_back(t, 0, B, plan->step_done[t - ctx]));
     } else {
-      DLWP_TRY(run(t, 0, Ba));
-      DLWP_TRY(send_back(t, 0, Ba, plan->half_done));
-      if (t == ctx) DLWP_CUDA(cudaStreamWaitEvent(st, plan->half_ready, 0));
-      DLWP_TRY(run(t, Ba, Bb));
-      DLWP_TRY(send_back(t, Ba, Bb, plan->step_done[t - ctx]));
+      for (int k = 0; k < K; ++k) {
+        if (t == ctx && k > 0) DLWP_CUDA(cudaStreamWaitEvent(st, plan->part_ev[k], 0));
+        DLWP_TRY(run(t, (size_t)k * Bp, Bp));
+        DLWP_TRY(send_back(t, (size_t)k * Bp, Bp, k + 1 < K ? plan->part_ev[K + k] : plan->step_done[t - ctx]));
+      }
     }
   }
   cudaEvent_t fin = plan->step_done[steps];

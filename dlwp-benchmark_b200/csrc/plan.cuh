@@ -94,7 +94,7 @@ struct dlwp_plan {
   cudaStream_t copy_stream = nullptr;        // device -> host frames, under the following steps' compute
   std::vector<cudaEvent_t> step_done;        // one per lead time + one for the end of the copies
   cudaStream_t h2d_stream = nullptr;         // host -> device prescribed frames of later steps, under the earlier steps' compute
-  cudaEvent_t half_ready = nullptr, half_done = nullptr;   // dlwp_rollout_host: second half's initial frames there / first half's step done
+  std::vector<cudaEvent_t> part_ev;          // dlwp_rollout_host: per part of the members, initial frames there / step done
   std::vector<cudaEvent_t> frame_ready;      // one per prescribed frame
 };
 

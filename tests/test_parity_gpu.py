@@ -287,10 +287,10 @@ def test_fourcastnet_fno2d_filter_matches_oracle(pkg, H, W, E):
 # ---------------------------------------------------------------------------------------
 # host entry, metrics kernel, weight reload
 # ---------------------------------------------------------------------------------------
-@pytest.mark.parametrize("ctx,T,members", [(1, 4, None), (2, 7, None), (1, 4, 64), (2, 5, 66), (1, 2, 64)])
+@pytest.mark.parametrize("ctx,T,members", [(1, 4, None), (2, 7, None), (1, 4, 64), (2, 5, 66), (1, 2, 64), (1, 3, 256)])
 def test_rollout_host_equals_device_rollout(pkg, ctx, T, members):
     # the host entry streams the later prescribed frames in under the earlier steps: same bits as the device entry
-    # (64 members or more: the host entry runs the first and the last step as two half batches)
+    # (64 members or more: the host entry runs the first and the last step in two parts of the members, 256 or more: in four)
     cls, kw, (B, H, W) = FNO_CASES["C2"]
     B = members or B
     kw = dict(kw, context_size=ctx)
