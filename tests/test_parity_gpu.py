@@ -308,6 +308,27 @@ def test_rollout_host_equals_device_rollout(pkg, ctx, T, members):
     assert not torch.equal(again, host)      # a second call with other prescribed frames is not served stale ones
 
 
+@pytest.mark.parametrize("members,no_forcings", [(64, False), (70, False), (64, True)])
+def test_fourcastnet_rollout_host_equals_device_rollout(pkg, members, no_forcings):
+    # the host entry's two half batches on the AFNO path (fused first / last kernels), with and without the
+    # constants / prescribed groups (fourcastnet.py:294-307 skips absent groups)
+    kw = dict(img_height=32, img_width=64, patch_size=[1, 1], constant_channels=0 if no_forcings else 4,
+              prescribed_channels=0 if no_forcings else 1, prognostic_channels=3, embed_dim=64, filter="AFNO2D", depth=2,
+              mlp_ratio=4.0, num_blocks=4, sparsity_threshold=0.01, hard_thresholding_fraction=1.0, context_size=1,
+              use_pos_embed=True)
+    torch.manual_seed(7)
+    mod = pkg.FourCastNet(**kw).cuda().eval()
+    const, presc, prog = synthetic(members, 4, 4, 1, 3, 32, 64)
+    if no_forcings:
+        const = presc = None
+    pin = lambda x: None if x is None else x.pin_memory()
+    with torch.no_grad():
+        dev = mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog)).cpu()
+        host = mod.forward_host(constants=pin(const), prescribed=pin(presc), prognostic=pin(prog))
+    assert host.shape == (members, 3, 3, 32, 64)
+    assert torch.equal(dev, host)
+
+
 @pytest.mark.parametrize("B,T,Cn,H,W", [(5, 3, 4, 32, 64), (70, 2, 3, 32, 64), (3, 2, 2, 9, 15), (2, 1, 1, 181, 360)])
 def test_metrics_kernel_matches_oracle(pkg, B, T, Cn, H, W):
     # float4 form (W % 4 == 0), more samples than one pass of a CTA covers, ragged planes (scalar form), sliced planes
