@@ -719,8 +719,9 @@ int launch_nhwc_to_nchw(const float* in, float* out, int B, int C, int HW, cudaS
 // samples, slice of the plane); fp64 accumulation; one atomicAdd per block and statistic.
 // =====================================================================================
 // VEC = 4: W % 4 == 0 and 16-byte aligned planes, one float4 per thread and plane position, the loads of four
-// samples in flight together; VEC = 1: any shape.
-template <int VEC>
+// samples in flight together (PU = false) or, with few samples per CTA, of four plane positions (PU = true);
+// VEC = 1: any shape.
+template <int VEC, bool PU = false>
 __global__ void __launch_bounds__(256) metrics_kernel(const float* __restrict__ o, const float* __restrict__ t,
                                                       const float* __restrict__ clim,
                                                       const float* __restrict__ latw, int B, int T, int C, int H,
@@ -741,7 +742,37 @@ __global__ void __launch_bounds__(256) metrics_kernel(const float* __restrict__ 
     s2 += (double)w * oa * oa;
     s3 += (double)w * ta * ta;
   };
-  if constexpr (VEC == 4) {
+  if constexpr (VEC == 4 && PU) {
+    constexpr int U = 4;
+    const int pstep = blockDim.x * 4;
+    for (int b = blockIdx.y; b < B; b += gridDim.y) {
+      const long long base = b * bstride + plane;
+      for (int p = p_lo + threadIdx.x * 4; p < p_hi; p += pstep * U) {
+        float4 ov[U], tv[U], cv[U];
+        float w[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int pp = p + u * pstep;
+          cv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (pp < p_hi) {
+            ov[u] = __ldcs(reinterpret_cast<const float4*>(o + base + pp));
+            tv[u] = __ldcs(reinterpret_cast<const float4*>(t + base + pp));
+            if (clim) cv[u] = *reinterpret_cast<const float4*>(clim + (long long)c * HW + pp);
+            w[u] = latw[pp / W];
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (p + u * pstep < p_hi) {
+            acc(w[u], ov[u].x, tv[u].x, cv[u].x);
+            acc(w[u], ov[u].y, tv[u].y, cv[u].y);
+            acc(w[u], ov[u].z, tv[u].z, cv[u].z);
+            acc(w[u], ov[u].w, tv[u].w, cv[u].w);
+          }
+        }
+      }
+    }
+  } else if constexpr (VEC == 4) {
     constexpr int U = 4;
     for (int p = p_lo + threadIdx.x * 4; p < p_hi; p += blockDim.x * 4) {
       const float w = latw[p / W];
@@ -806,7 +837,9 @@ int launch_metrics(const float* o, const float* t, const float* clim, const floa
   if (bz > 65535) bz = 65535;
   dim3 grid((unsigned)(T * C), (unsigned)by, (unsigned)bz);
   const bool vec = W % 4 == 0 && (((uintptr_t)o | (uintptr_t)t | (uintptr_t)clim) & 15) == 0;
-  if (vec)
+  if (vec && B < 4 * by)      // fewer than four samples per CTA: keep four plane positions in flight instead
+    metrics_kernel<4, true><<<grid, 256, 0, st>>>(o, t, clim, latw, B, T, C, H, W, sums);
+  else if (vec)
     metrics_kernel<4><<<grid, 256, 0, st>>>(o, t, clim, latw, B, T, C, H, W, sums);
   else
     metrics_kernel<1><<<grid, 256, 0, st>>>(o, t, clim, latw, B, T, C, H, W, sums);
