@@ -73,6 +73,33 @@ def test_bf16_single_step_matches_oracle(pkg, case):
     assert float(err) < TOL_BF16
 
 
+def test_bf16_config5_real_grid_single_step_matches_oracle(pkg):
+    """BASELINE config 5 itself: 721 x 1440 grid (odd row count; 12 tiles per grid row, the last one with 96
+    padding slots), 128 channels, 64 x 33 retained modes, one sample, one step (the CPU oracle takes a few seconds)."""
+    from oracle import wrappers as owrap
+    kw = dict(n_modes=[64, 64], constant_channels=4, prescribed_channels=1, prognostic_channels=8, hidden_channels=128,
+              lifting_channels=256, projection_channels=256, n_layers=4, context_size=1)
+    torch.manual_seed(1234)
+    ref = owrap.FNO2DModule(**kw).eval()
+    mod = pkg.FNO2DModule(**kw).cuda().eval()
+    mod.load_state_dict(ref.state_dict(), strict=True)
+    mod.precision = pkg.native.PREC_BF16
+    const, presc, prog = synthetic(1, 2, 4, 1, 8, 721, 1440)
+    with torch.no_grad():
+        want = ref(constants=const, prescribed=presc, prognostic=prog)
+        got = mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog)).cpu()
+    assert all(p.uses_tensor_cores() for p in mod._plans.values())
+    assert torch.isfinite(got).all()
+    incr = (want[:, 0] - prog[:, 0]).abs().max()
+    err = (got[:, 0] - want[:, 0]).abs().max() / incr
+    rms = ((got - want).pow(2).mean().sqrt() / (want[:, 0] - prog[:, 0]).pow(2).mean().sqrt())
+    print(f"config 5 (721 x 1440): bf16 single-step max error {float(err):.3e} of the increment scale {float(incr):.3e}, "
+          f"rms error {float(rms):.3e} of the rms increment")
+    assert float(err) < TOL_BF16
+    del mod
+    torch.cuda.empty_cache()
+
+
 def test_bf16_rollout_tracks_oracle_rmse_curve(pkg):
     from oracle import metrics as om
     ref, mod, kw, (B, H, W) = _pair(pkg, "small")
