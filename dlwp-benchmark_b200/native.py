@@ -18,6 +18,7 @@ MODEL_FNO, MODEL_AFNO = 0, 1
 AFNO_FILTER_AFNO2D, AFNO_FILTER_FNO2D = 0, 1
 PREC_FP32, PREC_FP32_TC, PREC_BF16 = 0, 1, 2
 FFT_NORM_BACKWARD, FFT_NORM_FORWARD, FFT_NORM_ORTHO = 0, 1, 2
+STATIC_SCRATCH_BYTES, STATIC_MAX_ROWS = 16 << 20, 64      # DLWP_STATIC_SCRATCH_BYTES / DLWP_STATIC_MAX_ROWS
 
 
 class ModelDesc(C.Structure):
@@ -57,6 +58,8 @@ SYMBOLS = {
     "dlwp_metrics_accumulate": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "dlwp_spectral_conv2d": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
+    "dlwp_spectral_conv2d_static": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                              C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
     "dlwp_launch_count": (C.c_int64, []),
     "dlwp_selftest_umma": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_selftest_umma_bmn": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),

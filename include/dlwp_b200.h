@@ -164,6 +164,21 @@ int dlwp_spectral_conv2d(const float* x, const float* weight, const float* bias,
                          const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
                          void* stream);
 
+/* The same layer for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments
+ * and results as dlwp_spectral_conv2d (Ci != Co is accepted), but every intermediate lives in one file-scope device array
+ * of DLWP_STATIC_SCRATCH_BYTES that each GPU loading the library holds until exit: the call does no cudaMalloc / cudaFree,
+ * calls no allocating library routine and does not synchronise (it only enqueues kernels on `stream`).  Problems that
+ * need more scratch, or more than DLWP_STATIC_MAX_ROWS retained rows, are rejected with DLWP_ERR_INVALID and a message
+ * that states both sizes.  All calls share the array: calls that overlap on the GPU (other streams, other host threads)
+ * race on it -- serialise them.  x, weight, bias, y must belong to the current device. */
+#define DLWP_STATIC_SCRATCH_BYTES (16u << 20)
+#define DLWP_STATIC_MAX_ROWS 64
+int dlwp_spectral_conv2d_static(const float* x, const float* weight, const float* bias, float* y,
+                                int batch, int Ci, int Co, int H, int W, int n_rows, int n_cols,
+                                const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
+                                void* stream);
+
 /* Number of kernels this library has launched in this process (for bench "gpu_launches"). */
 int64_t dlwp_launch_count(void);
 
