@@ -288,12 +288,8 @@ __global__ void __launch_bounds__(256) afno_mid_kernel(const AfnoMidArgs a) {
 int launch_afno_mid(const AfnoMidArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.B > 0 && a.H > 0 && a.H <= 32 && a.R > 0 && a.R <= 32 && a.Kc > 0, "afno_mid_kernel: unsupported shape");
   DLWP_REQUIRE(a.bs == 8 || a.bs == 16, "afno_mid_kernel: block size %d", a.bs);
-  static bool attr = false;
-  if (!attr) {
-    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, mid_smem(8)));
-    DLWP_CUDA(cudaFuncSetAttribute(afno_mid_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, mid_smem(16)));
-    attr = true;
-  }
+  DLWP_TRY(ensure_dynamic_smem((const void*)afno_mid_kernel<8>, mid_smem(8)));
+  DLWP_TRY(ensure_dynamic_smem((const void*)afno_mid_kernel<16>, mid_smem(16)));
   const dim3 grid((unsigned)(a.B * a.Kc)), block(256);
   if (a.bs == 8) DLWP_CUDA(launch_pdl(afno_mid_kernel<8>, grid, block, (size_t)mid_smem(8), st, a));
   else DLWP_CUDA(launch_pdl(afno_mid_kernel<16>, grid, block, (size_t)mid_smem(16), st, a));
@@ -355,12 +351,8 @@ int launch_afno_inv(const AfnoInvArgs& a, cudaStream_t st) {
   const dim3 grid((unsigned)(a.B * a.H)), block(256);
   const int nw = a.W <= 32 ? 8 : 16;
   const size_t smem = (size_t)4 * nw * kC * 4 + (size_t)4 * nw * a.Kc * 8 + (size_t)a.Kc * kC * 8;
-  static bool attr = false;
-  if (!attr) {
-    DLWP_CUDA(cudaFuncSetAttribute(afno_inv_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    DLWP_CUDA(cudaFuncSetAttribute(afno_inv_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    attr = true;
-  }
+  DLWP_TRY(ensure_dynamic_smem((const void*)afno_inv_kernel<8>, 64 * 1024));
+  DLWP_TRY(ensure_dynamic_smem((const void*)afno_inv_kernel<16>, 64 * 1024));
   DLWP_REQUIRE(smem <= 64 * 1024, "afno_inv_kernel: shared memory");
   if (nw == 8) DLWP_CUDA(launch_pdl(afno_inv_kernel<8>, grid, block, smem, st, a));
   else DLWP_CUDA(launch_pdl(afno_inv_kernel<16>, grid, block, smem, st, a));

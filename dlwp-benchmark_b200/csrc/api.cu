@@ -122,6 +122,14 @@ int dlwp_plan_uses_tensor_cores(const dlwp_plan* plan, int* out) {
   return DLWP_OK;
 }
 
+int dlwp_plan_check_guards(const dlwp_plan* plan, void* stream) {
+  if (!plan) return fail(DLWP_ERR_INVALID, "dlwp_plan_check_guards: null plan");
+  DLWP_CUDA(cudaSetDevice(plan->device));
+  DLWP_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  int bad = -1;
+  return plan_check_guards(plan, &bad);
+}
+
 int dlwp_plan_debug_read(const dlwp_plan* plan, const char* name, void* dst, size_t max_bytes, void* stream) {
   if (!plan || !name || !dst) return fail(DLWP_ERR_INVALID, "dlwp_plan_debug_read: null argument");
   const std::string n(name);
@@ -174,6 +182,7 @@ int dlwp_plan_commit_weights(dlwp_plan* plan, void* stream) {
 
 int dlwp_step(dlwp_plan* plan, const float* x, float* y, int batch, void* stream) {
   if (!plan || !x || !y) return fail(DLWP_ERR_INVALID, "dlwp_step: null argument");
+  DLWP_CUDA(cudaSetDevice(plan->device));
   const long long HW = (long long)plan->d.height * plan->d.width;
   StepIO io;
   io.grp[0] = SrcGroup{x, plan->Cin * HW, plan->Cin};
@@ -186,6 +195,7 @@ int dlwp_step(dlwp_plan* plan, const float* x, float* y, int batch, void* stream
 int dlwp_rollout(dlwp_plan* plan, const float* constants, const float* prescribed, const float* prognostic,
                  int batch, int T, float* outs, void* stream) {
   if (!plan || !prognostic || !outs) return fail(DLWP_ERR_INVALID, "dlwp_rollout: null prognostic / outs");
+  DLWP_CUDA(cudaSetDevice(plan->device));
   const dlwp_model_desc& d = plan->d;
   DLWP_REQUIRE(T > d.context_size, "sequence length %d must exceed context_size %d", T, d.context_size);
   DLWP_REQUIRE((d.constant_channels == 0) == (constants == nullptr),

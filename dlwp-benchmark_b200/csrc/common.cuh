@@ -60,6 +60,13 @@ inline int fail(int code, const char* fmt, ...) {
       return ::dlwp::fail(DLWP_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(_e)); \
   } while (0)
 
+// Per-device launch state (plan.cu).  Function attributes and SM counts belong to a device, and the launchers may be
+// reached from several host threads: both are cached per (device, kernel) behind a mutex instead of in function-local
+// statics.  `current_sms`: SM count of the current device.  `ensure_dynamic_smem`: raises the kernel's
+// MaxDynamicSharedMemorySize on the current device to at least `bytes` (once per device and size).
+int current_sms(int* sms);
+int ensure_dynamic_smem(const void* kernel, int bytes);
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

@@ -8,19 +8,75 @@
 
 #include <cmath>
 #include <cstring>
+#include <mutex>
+#include <utility>
 
 namespace dlwp {
 
 thread_local std::string g_last_error;
 std::atomic<int64_t> g_launches{0};
 
+// ---- per-device launch state (common.cuh) ---------------------------------------------------
+namespace {
+std::mutex g_dev_mutex;
+int g_dev_sms[64] = {};
+std::map<std::pair<const void*, int>, int> g_dyn_smem;      // (kernel, device) -> bytes granted
+}  // namespace
+
+int current_sms(int* sms) {
+  int dev = 0;
+  DLWP_CUDA(cudaGetDevice(&dev));
+  DLWP_REQUIRE(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_dev_mutex);
+  if (!g_dev_sms[dev]) DLWP_CUDA(cudaDeviceGetAttribute(&g_dev_sms[dev], cudaDevAttrMultiProcessorCount, dev));
+  *sms = g_dev_sms[dev];
+  return DLWP_OK;
+}
+
+int ensure_dynamic_smem(const void* kernel, int bytes) {
+  int dev = 0;
+  DLWP_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(g_dev_mutex);
+  int& have = g_dyn_smem[std::make_pair(kernel, dev)];
+  if (have < bytes) {
+    DLWP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    have = bytes;
+  }
+  return DLWP_OK;
+}
+
 int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);
 static int dev_alloc(dlwp_plan* p, void** out, size_t bytes) { return plan_dev_alloc(p, out, bytes); }
+// Every plan-owned buffer sits between two guard zones of kGuardBytes filled with kGuardByte; dlwp_plan_check_guards
+// reads them back.  (compute-sanitizer is closed on the GPU pool this library is developed on: the guard zones, the
+// oracle comparisons at multi-tile sizes and the repeat-run bit-equality tests stand in for memcheck / racecheck.)
 int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes) {
   if (bytes == 0) bytes = 16;
-  DLWP_CUDA(cudaMalloc(out, bytes));
-  p->owned.push_back(*out);
+  uint8_t* base = nullptr;
+  DLWP_CUDA(cudaMalloc((void**)&base, bytes + 2 * kGuardBytes));
+  p->owned.push_back(base);
+  DLWP_CUDA(cudaMemset(base, kGuardByte, kGuardBytes));
+  DLWP_CUDA(cudaMemset(base + kGuardBytes + bytes, kGuardByte, kGuardBytes));
+  *out = base + kGuardBytes;
+  p->guarded.push_back({base + kGuardBytes, bytes});
   p->workspace_bytes += bytes;
+  return DLWP_OK;
+}
+
+int plan_check_guards(const dlwp_plan* p, int* bad_index) {
+  std::vector<uint8_t> h(2 * kGuardBytes);
+  *bad_index = -1;
+  for (size_t i = 0; i < p->guarded.size(); ++i) {
+    const uint8_t* u = p->guarded[i].first;
+    DLWP_CUDA(cudaMemcpy(h.data(), u - kGuardBytes, kGuardBytes, cudaMemcpyDeviceToHost));
+    DLWP_CUDA(cudaMemcpy(h.data() + kGuardBytes, u + p->guarded[i].second, kGuardBytes, cudaMemcpyDeviceToHost));
+    for (size_t j = 0; j < h.size(); ++j)
+      if (h[j] != kGuardByte) {
+        *bad_index = (int)i;
+        return fail(DLWP_ERR_STATE, "guard zone %s plan buffer %zu (%zu bytes) was overwritten at offset %zu",
+                    j < kGuardBytes ? "in front of" : "behind", i, p->guarded[i].second, j % kGuardBytes);
+      }
+  }
   return DLWP_OK;
 }
 

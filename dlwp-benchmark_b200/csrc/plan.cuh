@@ -3,6 +3,7 @@
 #pragma once
 #include <map>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "kernels.cuh"
@@ -42,6 +43,7 @@ struct dlwp_plan {
 
   std::map<std::string, dlwp::NamedTensor> tensors;
   std::vector<void*> owned;   // every cudaMalloc of this plan except `tensors` and staging
+  std::vector<std::pair<uint8_t*, size_t>> guarded;   // (buffer, bytes) of every plan_dev_alloc: guard zones on both sides
   size_t workspace_bytes = 0;
 
   // truncated-DFT bases (float2, built in fp64)
@@ -114,6 +116,9 @@ int atc_block_filter(dlwp_plan* p, int block, float* x, float* out, int B, cudaS
 int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cudaStream_t st, const dlwp::StepIO* head);
 int spectral_mid_fno(dlwp_plan* p, const float2* wm, int B, cudaStream_t st);
 int plan_dev_alloc(dlwp_plan* p, void** out, size_t bytes);
+int plan_check_guards(const dlwp_plan* p, int* bad_index);
+constexpr size_t kGuardBytes = 256;      // keeps the 256-byte alignment of cudaMalloc
+constexpr int kGuardByte = 0xA5;
 int plan_need(const dlwp_plan* p, const std::string& name, int64_t numel, const float** out);
 int spectral_layer(dlwp_plan* p, const float* x, float* y, const float2* wm_or_null, int layer,
                    const float* add1, const float* add2, const float* bias, int act, int B, cudaStream_t st);

@@ -211,13 +211,9 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
 }
 
 int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DLWP_CUDA(cudaFuncSetAttribute(afno_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AmSmem::Total));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
+  DLWP_TRY(ensure_dynamic_smem((const void*)afno_mlp_kernel, AmSmem::Total));
   DLWP_REQUIRE(a.ntiles > 0, "afno_mlp_kernel: empty problem");
   DLWP_REQUIRE(a.Wh == nullptr || (a.Cg >= 1 && a.Cg <= 4 && a.HW > 0 && a.frame != nullptr), "afno_mlp_kernel: bad head arguments");
   const int grid = a.ntiles < sms ? a.ntiles : sms;
@@ -471,13 +467,9 @@ __global__ void __launch_bounds__(kFwCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
 }
 
 int launch_afno_fwd_tc(const AfnoWTcArgs& a, cudaStream_t st) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DLWP_CUDA(cudaFuncSetAttribute(afno_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::Total));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
+  DLWP_TRY(ensure_dynamic_smem((const void*)afno_fwd_tc_kernel, FwdSmem::Total));
   DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= 128, "afno_fwd_tc_kernel: unsupported shape");
   DLWP_REQUIRE(a.ngrp == 0 || (a.Cin >= 1 && a.Cin <= 8 && a.We && a.be && a.xout), "afno_fwd_tc_kernel: bad embedding arguments");
   const int grid = a.ntiles < sms ? a.ntiles : sms;
@@ -683,13 +675,9 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArg
 int afno_inv_tc_smem_bytes(int RT, int Kc, int KZ) { return InvSmem(RT, Kc, KZ).Total; }
 
 int launch_afno_inv_tc(const AfnoWTcArgs& a, cudaStream_t st) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DLWP_CUDA(cudaFuncSetAttribute(afno_inv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
+  DLWP_TRY(ensure_dynamic_smem((const void*)afno_inv_tc_kernel, 226 * 1024));
   const InvSmem L(a.RT, a.Kc, a.KZ);
   DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= a.KZ && a.KZ % 16 == 0 && L.Total <= 226 * 1024,
                "afno_inv_tc_kernel: unsupported shape");

@@ -453,13 +453,9 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
 int launch_tc_layer(const TcLayerArgs& a_in, cudaStream_t st) {
   TcLayerArgs a = a_in;
   a.ny = LayerSmem(a.g.KZ, 2).Total <= kLayerSmemMax ? 2 : 1;      // two output image buffers per worker when they fit
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DLWP_CUDA(cudaFuncSetAttribute(fno_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLayerSmemMax));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
+  DLWP_TRY(ensure_dynamic_smem((const void*)fno_layer_kernel, kLayerSmemMax));
   const LayerSmem L(a.g.KZ, a.ny);
   DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
   const int want = (a.g.ntiles + 1) / 2;
@@ -640,13 +636,9 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
 int launch_tc_proj(const TcProjArgs& a_in, cudaStream_t st) {
   TcProjArgs a = a_in;
   a.last_bulk = a.last != nullptr && (reinterpret_cast<uintptr_t>(a.last) & 15) == 0 && a.last_bstride % 4 == 0 && a.g.HW % 4 == 0;
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DLWP_CUDA(cudaFuncSetAttribute(fno_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ProjSmem::Total));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
+  DLWP_TRY(ensure_dynamic_smem((const void*)fno_proj_kernel, ProjSmem::Total));
   DLWP_REQUIRE(a.hid == 128 || a.hid == 256, "tensor-core projection needs width 128 or 256, got %d", a.hid);
   const int want = (a.g.ntiles + 1) / 2;
   const int grid = want < sms ? want : sms;
@@ -819,13 +811,9 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
 }
 
 int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DLWP_CUDA(cudaFuncSetAttribute(fno_lift_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LiftSmem::Total));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
+  DLWP_TRY(ensure_dynamic_smem((const void*)fno_lift_kernel, LiftSmem::Total));
   DLWP_REQUIRE(a.hid == 128 || a.hid == 256, "tensor-core lifting needs width 128 or 256, got %d", a.hid);
   DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 15 && a.ngrp >= 1, "tensor-core lifting needs 1..15 input channels, got %d", a.Cin);
   const int want = (a.g.ntiles + 1) / 2;

@@ -219,13 +219,8 @@ static int mid_samples(int H, int R) { return mid_smem(H, R, kTcMidSamples) <= 2
 size_t tc_mid_smem_bytes(int H, int R) { return mid_smem(H, R, mid_samples(H, R)); }
 
 int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
-  static int sms = 0;
-  static size_t smem_set[6] = {0, 0, 0, 0, 0, 0};
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
   DLWP_REQUIRE(a.R >= 1 && a.R <= 16 && a.H % 8 == 0 && a.Kc >= 1, "fno_mid_kernel: unsupported geometry R=%d H=%d", a.R, a.H);
   const int nbs = mid_samples(a.H, a.R);
   const size_t smem = mid_smem(a.H, a.R, nbs);
@@ -247,10 +242,8 @@ int launch_tc_mid(const TcMidArgs& a, cudaStream_t st) {
   DLWP_MID_PICK(4, 2, 5)
 #undef DLWP_MID_PICK
   if (!kern) return fail(DLWP_ERR_INVALID, "fno_mid_kernel: %d grid rows per tile", a.RT);
-  if (smem_set[slot] < smem) {
-    DLWP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set[slot] = smem;
-  }
+  (void)slot;
+  DLWP_TRY(ensure_dynamic_smem((const void*)kern, (int)smem));
   DLWP_CUDA(launch_pdl(kern, grid, dim3(threads), smem, st, a));
   DLWP_LAUNCHED("fno_mid_kernel");
   return DLWP_OK;

@@ -603,19 +603,11 @@ __global__ void __launch_bounds__(128) wide_gather_kernel(const WideGatherArgs a
 // ---- launchers ---------------------------------------------------------------------------------
 template <int MODE>
 static int launch_tcw_mode(const TcwArgs& a, cudaStream_t st, const char* name) {
-  static int sms = 0;
-  static int smem_set = 0;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
   const int smem = tcw_smem_bytes<MODE>(a.KZ);
   DLWP_REQUIRE(smem <= 226 * 1024, "%s: %d bytes of shared memory needed", name, smem);
-  if (smem_set < smem) {
-    DLWP_CUDA(cudaFuncSetAttribute(tcw_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    smem_set = smem;
-  }
+  DLWP_TRY(ensure_dynamic_smem((const void*)tcw_kernel<MODE>, smem));
   const int grid = a.nitems < sms ? a.nitems : sms;
   void (*kern)(TcwArgs) = tcw_kernel<MODE>;
   DLWP_CUDA(launch_pdl(kern, dim3((unsigned)grid), dim3(kWCta), (size_t)smem, st, a));
@@ -637,19 +629,11 @@ int launch_tcw(int mode, const TcwArgs& a, cudaStream_t st) {
 
 template <int KIND>
 static int launch_tcw_mlp_kind(const TcwArgs& a, cudaStream_t st, const char* name) {
-  static int sms = 0;
-  static bool attr_set = false;
-  if (!sms) {
-    int dev = 0;
-    DLWP_CUDA(cudaGetDevice(&dev));
-    DLWP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
   constexpr int smem = mlp_smem_bytes<KIND>();
   static_assert(smem <= 226 * 1024, "fused MLP kernel: shared memory");
-  if (!attr_set) {
-    DLWP_CUDA(cudaFuncSetAttribute(tcw_mlp_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
-  }
+  DLWP_TRY(ensure_dynamic_smem((const void*)tcw_mlp_kernel<KIND>, smem));
   const int grid = a.nitems < sms ? a.nitems : sms;
   void (*kern)(TcwArgs) = tcw_mlp_kernel<KIND>;
   DLWP_CUDA(launch_pdl(kern, dim3((unsigned)grid), dim3(kMlpCta), (size_t)smem, st, a));

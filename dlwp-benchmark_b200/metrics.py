@@ -24,9 +24,10 @@ def lat_weights(H: int, device=None) -> torch.Tensor:
     return (c / c.mean()).to(torch.float32).to(device)
 
 
-def partial_sums(outputs, targets, climatology=None, weights=None) -> torch.Tensor:
+def partial_sums(outputs, targets, climatology=None, weights=None, out=None) -> torch.Tensor:
     """``[T, C, 4]`` fp64 sums over (sample, lat, lon) of ``w (o-t)^2, w (o-c)(t-c), w (o-c)^2,
-    w (t-c)^2`` for device tensors ``[B, T, C, H, W]``."""
+    w (t-c)^2`` for device tensors ``[B, T, C, H, W]``.  ``out``: a zeroed ``[T, C, 4]`` fp64 device
+    tensor to accumulate into (a view of a larger reduction buffer, see ``rollout_metrics``)."""
     if outputs.device.type != "cuda":
         raise native.NativeError("metrics run on CUDA tensors only (no CPU fallback)")
     B, T, Cn, H, W = outputs.shape
@@ -34,7 +35,8 @@ def partial_sums(outputs, targets, climatology=None, weights=None) -> torch.Tens
     t = targets.to(device=o.device, dtype=torch.float32).contiguous()
     w = (lat_weights(H, o.device) if weights is None else weights.to(device=o.device, dtype=torch.float32)).contiguous()
     c = None if climatology is None else climatology.to(device=o.device, dtype=torch.float32).contiguous()
-    sums = torch.zeros(T, Cn, 4, dtype=torch.float64, device=o.device)
+    sums = torch.zeros(T, Cn, 4, dtype=torch.float64, device=o.device) if out is None else out
+    assert sums.shape == (T, Cn, 4) and sums.dtype == torch.float64 and sums.is_contiguous()
     with torch.cuda.device(o.device):
         st = C.c_void_p(torch.cuda.current_stream(o.device).cuda_stream)
         native.check(native.lib().dlwp_metrics_accumulate(
@@ -43,27 +45,35 @@ def partial_sums(outputs, targets, climatology=None, weights=None) -> torch.Tens
     return sums
 
 
-def finalize(sums: torch.Tensor, count: float):
-    """Reduced sums ``[T, C, 4]`` and the number of (sample, lat, lon) points -> (rmse, acc)."""
-    mean = sums / float(count)
+def finalize(sums: torch.Tensor, count):
+    """Reduced sums ``[T, C, 4]`` and the number of (sample, lat, lon) points (a number, or a 0-d tensor
+    on the sums' device) -> (rmse, acc)."""
+    mean = sums / count
     rmse = torch.sqrt(mean[..., 0])
     acc = mean[..., 1] / torch.sqrt(mean[..., 2] * mean[..., 3])
     return rmse, acc
 
 
-def reduce_sums(sums: torch.Tensor, count: float, group=None):
-    """Sum the per-rank partials over the process group (the rollout's only collective)."""
+def reduce_sums(sums: torch.Tensor, group=None) -> torch.Tensor:
+    """Sum the per-rank partials over the process group IN PLACE: the rollout's only collective (one
+    all-reduce of a few KB; nothing is copied from or to the host and nothing synchronises)."""
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        packed = torch.cat([sums.reshape(-1), torch.tensor([float(count)], dtype=torch.float64, device=sums.device)])
-        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
-        return packed[:-1].reshape(sums.shape), float(packed[-1].item())
-    return sums, float(count)
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    return sums
 
 
-def rollout_metrics(outputs, targets, climatology=None, weights=None, group=None):
-    """(rmse ``[T, C]``, acc ``[T, C]``) over the whole (possibly sharded) ensemble."""
+def rollout_metrics(outputs, targets, climatology=None, weights=None, group=None, total_samples=None):
+    """(rmse ``[T, C]``, acc ``[T, C]``) over the whole (possibly sharded) ensemble.  ``total_samples``: the
+    number of members over all ranks when the caller knows it (an even split does); otherwise the per-rank
+    counts ride in the same all-reduce as one extra element."""
     B, T, Cn, H, W = outputs.shape
-    sums = partial_sums(outputs, targets, climatology, weights)
-    sums, count = reduce_sums(sums, B * H * W, group)
-    return finalize(sums, count)
+    buf = torch.zeros(T * Cn * 4 + 1, dtype=torch.float64, device=outputs.device)
+    sums = buf[:-1].view(T, Cn, 4)
+    partial_sums(outputs, targets, climatology, weights, out=sums)
+    if total_samples is not None:
+        reduce_sums(sums, group)
+        return finalize(sums, float(total_samples) * H * W)
+    buf[-1:].fill_(float(B * H * W))
+    reduce_sums(buf, group)
+    return finalize(sums, buf[-1])

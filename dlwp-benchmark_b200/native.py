@@ -49,6 +49,7 @@ SYMBOLS = {
     "dlwp_plan_destroy": (C.c_int, [_P]),
     "dlwp_plan_workspace_bytes": (C.c_int, [_P, C.POINTER(C.c_size_t)]),
     "dlwp_plan_uses_tensor_cores": (C.c_int, [_P, C.POINTER(C.c_int)]),
+    "dlwp_plan_check_guards": (C.c_int, [_P, _P]),
     "dlwp_plan_debug_read": (C.c_int, [_P, C.c_char_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "dlwp_plan_set_tensor": (C.c_int, [_P, C.c_char_p, _P, C.c_int, C.POINTER(C.c_int64), _P]),
     "dlwp_plan_commit_weights": (C.c_int, [_P, _P]),

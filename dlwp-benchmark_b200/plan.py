@@ -83,6 +83,10 @@ class NativePlan:
         native.check(self._lib.dlwp_plan_uses_tensor_cores(self._h, C.byref(n)))
         return bool(n.value)
 
+    def check_guards(self):
+        """Raise when a kernel wrote outside a plan-owned buffer (guard zones around every allocation)."""
+        native.check(self._lib.dlwp_plan_check_guards(self._h, self._stream()), "dlwp_plan_check_guards")
+
     def debug_read(self, name: str, nbytes: int) -> torch.Tensor:
         """First `nbytes` bytes of a named internal workspace buffer (diagnostics; see dlwp_plan_debug_read)."""
         out = torch.empty(nbytes, dtype=torch.uint8, device=self.device)

@@ -109,6 +109,10 @@ int dlwp_plan_workspace_bytes(const dlwp_plan* plan, size_t* bytes);
 /* *out = 1 when the plan runs the tcgen05 tensor-core kernel set (DLWP_PREC_FP32_TC on a shape
  * it covers), 0 when it runs the fp32 FMA kernel set. */
 int dlwp_plan_uses_tensor_cores(const dlwp_plan* plan, int* out);
+/* Diagnostics (no reference counterpart): every plan-owned buffer (workspace, operand images, packed weights) is allocated
+ * between two 256-byte guard zones; this synchronises `stream`, reads the zones back and fails with DLWP_ERR_STATE when a
+ * kernel wrote outside its buffer.  Used by the GPU tests after rollouts at the multi-tile sizes. */
+int dlwp_plan_check_guards(const dlwp_plan* plan, void* stream);
 /* Diagnostics: copy the first `max_bytes` bytes of a named internal workspace buffer ("specA", "specZ",
  * "specX", "tcw_in", "tcw_x0", "tcw_x1", "tcw_sa", "tcw_ys", "tcw_z", "tc_img0", "tc_img1") to the device buffer `dst`.
  * The caller must know the buffer's size; used by the stage-by-stage tests.  No reference counterpart. */

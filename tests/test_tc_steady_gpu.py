@@ -122,3 +122,56 @@ def test_tc_rollout_trajectory_tracks_oracle_per_lead_time(pkg, cls, kw, B, H, W
           ", ".join(f"{t}: {float(e[t - 1]):.3e}" for t in leads))
     for t in range(1, steps + 1):
         assert float(e[t - 1]) < TOL_TRAJ * (1 + t / 10), (t, float(e[t - 1]))
+
+
+# compute-sanitizer is closed on the GPU pool (profiles/r02_compute_sanitizer_closed.txt): its place is taken by
+#   * guard zones around every plan-owned buffer, read back after rollouts at multi-tile sizes (out-of-bounds writes),
+#   * canaries around the caller's output buffer,
+#   * bit-equality of repeated runs (a race between the warp-specialised roles would show as run-to-run differences),
+#   * the oracle comparisons above (a phase / hand-over bug reads stale or half-written data).
+def _models_for_guards(pkg):
+    afno = dict(img_height=32, img_width=64, patch_size=[1, 1], constant_channels=4, prescribed_channels=1,
+                prognostic_channels=3, embed_dim=64, depth=4, num_blocks=4, mlp_ratio=4.0, context_size=1, use_pos_embed=True)
+    wide = dict(n_modes=[4, 4], constant_channels=0, prescribed_channels=0, prognostic_channels=14, hidden_channels=128,
+                lifting_channels=256, projection_channels=256, n_layers=1, context_size=1)
+    return {
+        "c4-B256": ("TFNO2DModule", C2, pkg.native.PREC_FP32_TC, (256, 32, 64)),
+        "c1-B33": ("FNO2DModule", C1, pkg.native.PREC_FP32_TC, (33, 64, 64)),
+        "afno-B24": ("FourCastNet", afno, pkg.native.PREC_FP32_TC, (24, 32, 64)),
+        "wide-limits": ("FNO2DModule", wide, pkg.native.PREC_BF16, (3, 70, 256)),
+        "fp32-odd": ("FNO2DModule", dict(n_modes=[6, 10], constant_channels=1, prescribed_channels=0, prognostic_channels=2,
+                                         hidden_channels=12, lifting_channels=24, projection_channels=20, n_layers=2,
+                                         context_size=2), pkg.native.PREC_FP32, (5, 17, 30)),
+    }
+
+
+@pytest.mark.parametrize("case", ["c4-B256", "c1-B33", "afno-B24", "wide-limits", "fp32-odd"])
+def test_repeated_rollouts_are_bit_identical_and_stay_inside_their_buffers(pkg, case):
+    cls, kw, prec, (B, H, W) = _models_for_guards(pkg)[case]
+    torch.manual_seed(3)
+    mod = getattr(pkg, cls)(**kw).cuda().eval()
+    mod.precision = prec
+    ctx, steps = kw["context_size"], 3
+    const, presc, prog = synthetic(B, ctx + steps, kw["constant_channels"], kw["prescribed_channels"],
+                                   kw["prognostic_channels"], H, W, seed=11)
+    dev = lambda t: None if t is None else t.cuda()
+    const, presc, prog = dev(const), dev(presc), dev(prog)
+    runs = []
+    with torch.no_grad():
+        for _ in range(4):
+            runs.append(mod(constants=const, prescribed=presc, prognostic=prog))
+    torch.cuda.synchronize()
+    assert torch.isfinite(runs[0]).all()
+    for r in runs[1:]:
+        assert torch.equal(r, runs[0]), "two runs of the same rollout differ"
+    for p in mod._plans.values():
+        p.check_guards()
+    # the caller's output buffer between canaries: the rollout writes [B, steps, Cg, H, W] and nothing around it
+    n = runs[0].numel()
+    buf = torch.full((n + 2048,), 12345.0, device="cuda")
+    plan = next(iter(mod._plans.values()))
+    with torch.no_grad():
+        plan.rollout(const, presc, prog, buf[1024:1024 + n])
+    torch.cuda.synchronize()
+    assert torch.equal(buf[1024:1024 + n].view_as(runs[0]), runs[0])
+    assert bool((buf[:1024] == 12345.0).all()) and bool((buf[1024 + n:] == 12345.0).all())
