@@ -6,8 +6,10 @@
 One bench "step" = one full autoregressive rollout (all lead times) of this rank's shard of
 ensemble members, inputs resident in HBM, followed by the on-device RMSE/ACC partial sums and
 (N > 1) the single all-reduce of those partials.  ``value`` = members * lead_steps * K / time
-summed over all ranks (weak scaling: every GPU rolls out ``--members`` members).  ``e2e`` is
-the same rollout through ``dlwp_rollout_host`` with pinned HOST buffers: H2D of the inputs
+summed over all ranks.  ``--scaling strong`` (the default of workload c4 = BASELINE configs[3]: "256-member
+ensemble sharded across 1/2/4/8 B200"): the ensemble has ``--members`` members in TOTAL and rank r rolls out
+``ensemble.shard_range(members, r, N)``; ``--scaling weak``: every GPU rolls out ``--members`` members.
+``e2e`` is the same rollout through ``dlwp_rollout_host`` with pinned HOST buffers: H2D of the inputs
 and D2H of the whole forecast inside the timed region.
 
 ``--impl reference`` times the reference's CPU path for the same model (the oracle: the
@@ -43,7 +45,7 @@ FNO_C5 = dict(n_modes=[64, 64], constant_channels=4, prescribed_channels=1, prog
 WORKLOADS = {
     "c4": ("TFNO2DModule", TFNO_C2, 32, 64, 20, 256,
            "BASELINE configs[3]: TFNO2D (configs/model/fno.yaml, rank 0.8) 32x64, 20 lead steps (5 days, 6-hourly), "
-           "256 ensemble members per GPU"),
+           "256 ensemble members sharded over the GPUs"),
     "c2": ("TFNO2DModule", TFNO_C2, 32, 64, 20, 8, "BASELINE configs[1]: TFNO2D 32x64, batch 8, 20 lead steps"),
     "c1": ("FNO2DModule", FNO_C1, 64, 64, 50, 8, "BASELINE configs[0]: FNO2D 64x64, batch 8, 50 lead steps"),
     "c3": ("FourCastNet", AFNO_C3, 32, 64, 5, 8, "BASELINE configs[2]: FourCastNet AFNO 32x64, batch 8, 5 lead steps"),
@@ -214,11 +216,13 @@ def step_flops(cls, kw, B, H, W):
 
 def step_bytes(cls, kw, B, H, W, b=4):
     """Algorithmic HBM bytes of one model evaluation with per-layer fusion: every layer reads its
-    input once and writes its output once, MLP hiddens stay on chip, weights are read once."""
+    input once and writes its output once, MLP hiddens stay on chip, weights are read once.
+    `b` = bytes per ACTIVATION element between kernels (2 in the bf16 mode); the model's inputs and outputs
+    (NCHW frames of the reference) stay fp32."""
     S = H * W
     if cls != "FourCastNet":
         cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
-        act = B * S * b * (cin + C + 2 * N * C + C + Cg)
+        act = B * S * (4 * cin + b * (C + 2 * N * C + C) + 4 * Cg)
         wts = N * (2 * C * C * m1 * m2 + C * C + C) * b + (cin * L + L + L * C + C + C * P + P + P * Cg + Cg) * b
         return act + wts
     p1, p2 = kw["patch_size"]
@@ -314,24 +318,56 @@ def oracle_module(cls, kw):
     return getattr(owrap, cls)(**kw).eval()
 
 
-def cpu_rollout_rate(cls, kw, H, W, lead, sample_members, repeats, warmup):
-    """samples*steps/s of the CPU oracle on `sample_members` members x `lead` lead steps."""
+def cpu_rollout_rate(cls, kw, H, W, lead, sample_members, repeats, warmup, state_dict=None, inputs=None):
+    """samples*steps/s of the CPU oracle on `sample_members` members x `lead` lead steps; also returns the last
+    rollout (the GPU arm checks its own output against it: `parity` on the bench line).  `state_dict` / `inputs`:
+    the timed module's weights and the first members of its inputs instead of fresh random ones."""
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     model = oracle_module(cls, kw)
+    if state_dict is not None:
+        model.load_state_dict(state_dict, strict=True)
     ctx = kw["context_size"]
-    const, presc, prog = synthetic_inputs(kw, sample_members, ctx + lead, H, W, 1234, pin=False)
-    times = []
+    if inputs is None:
+        inputs = synthetic_inputs(kw, sample_members, ctx + lead, H, W, 1234, pin=False)
+    const, presc, prog = (None if t is None else t[:sample_members, :(1 if i == 0 else ctx + lead)]
+                          for i, t in enumerate(inputs))
+    times, out = [], None
     with torch.no_grad():
         for i in range(warmup + repeats):
             t0 = time.perf_counter()
-            model(constants=const, prescribed=presc, prognostic=prog)
+            out = model(constants=const, prescribed=presc, prognostic=prog)
             dt = time.perf_counter() - t0
             if i >= warmup:
                 times.append(dt)
     total = sum(times)
-    return sample_members * lead * len(times) / total, total / len(times), cores
+    return sample_members * lead * len(times) / total, total / len(times), cores, out
+
+
+def gpu_eager_rate(cls, kw, lead, state_dict, inputs, dev, repeats=3):
+    """The oracle modules moved to the GPU (`.cuda()`): stock PyTorch eager (cuFFT, cuBLAS / cuDNN, torch defaults for
+    TF32) on the same inputs and weights -- the number BASELINE.md calls the meaningful one to beat, since the reference
+    ships no GPU kernels of its own.  Timed with CUDA events, outside the bench's timed region."""
+    import torch
+    model = oracle_module(cls, kw)
+    model.load_state_dict(state_dict, strict=True)
+    model = model.to(dev)
+    const, presc, prog = inputs
+    members = prog.shape[0]
+    with torch.no_grad():
+        model(constants=const, prescribed=presc, prognostic=prog)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(repeats):
+            model(constants=const, prescribed=presc, prognostic=prog)
+        e1.record()
+        torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / repeats
+    del model
+    torch.cuda.empty_cache()
+    return members * lead / (ms * 1e-3), ms
 
 
 def run_reference(args, wl):
@@ -339,16 +375,17 @@ def run_reference(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    members = min(args.cpu_members, args.members or members_default)
+    total, per_gpu, _, _ = member_split(args, members_default, 0)
+    members = min(args.cpu_members, per_gpu)
     if args.workload == "c5":
         lead = 1
-    rate, sec, cores = cpu_rollout_rate(cls, kw, H, W, lead, members, max(args.steps, 1), min(args.warmup, 1))
+    rate, sec, cores, _ = cpu_rollout_rate(cls, kw, H, W, lead, members, max(args.steps, 1), min(args.warmup, 1))
     sample = f"{members} members x {lead} lead steps per bench step (bounded sample of the workload), fp32, torch CPU"
     line = {
         "impl": "reference", "metric": "rollout samples*steps/s", "value": rate, "unit": "samples*steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config_block(args, wl, args.members or members_default),
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_block(args, wl, per_gpu, total),
         "cpu_baseline": {"value": rate, "unit": "samples*steps/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": "samples*steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -359,12 +396,29 @@ def run_reference(args, wl):
     print(json.dumps(line), flush=True)
 
 
-def config_block(args, wl, members):
+def member_split(args, members_default, rank):
+    """(members in total, members on the largest rank, this rank's first member, this rank's member count)."""
+    m = args.members or members_default
+    if args.scaling == "strong":
+        if args.impl == "ours":
+            from dlwp_benchmark_b200.ensemble import shard_range
+        else:      # the reference arm imports nothing of the product: same contiguous balanced split
+            def shard_range(total, r, world):
+                base, extra = divmod(total, world)
+                start = r * base + min(r, extra)
+                return start, start + base + (1 if r < extra else 0)
+        a, b = shard_range(m, rank, args.gpus)
+        a0, b0 = shard_range(m, 0, args.gpus)
+        return m, b0 - a0, a, b - a
+    return m * args.gpus, m, rank * m, m
+
+
+def config_block(args, wl, members, total):
     cls, kw, H, W, lead, _, desc = wl
     return {"workload": f"{args.workload}: {desc}", "model_class": cls, "grid": [H, W], "lead_steps": lead,
-            "members_per_gpu": members, "members_total": members * args.gpus,
-            "parallelism": f"ensemble-sharded x{args.gpus}, no data-path collective; one all-reduce of [T,C,4] fp64 "
-                           "metric partials per rollout",
+            "members_per_gpu": members, "members_total": total,
+            "parallelism": f"ensemble-sharded x{args.gpus} ({args.scaling} scaling), no data-path collective; one in-place "
+                           "all-reduce of [T,C,4] fp64 metric partials per rollout",
             "l2": "inputs larger than L2" if members * (lead + 1) * kw["prognostic_channels"] * H * W * 4 > 126e6
                   else "L2 flushed between timed rollouts (256 MiB write)",
             "precision_mode": args.precision}
@@ -373,10 +427,13 @@ def config_block(args, wl, members):
 # ----------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------
+NCU_FULL_CSV = "r02_ncu_full_c4.csv"      # `ncu --set full` summary of this command on the current kernels (tools/ncu_summary_csv.py)
+
+
 def ncu_traffic(kernel):
     """DRAM bytes per launch of `kernel` from the committed `ncu --set full` summary (profiles/), or None."""
     import csv
-    path = os.path.join(ROOT, "profiles", "r01_ncu_full_tc_v5.csv")
+    path = os.path.join(ROOT, "profiles", NCU_FULL_CSV)
     try:
         with open(path) as f:
             rows = list(csv.reader(f))
@@ -425,7 +482,7 @@ def run_ours(args, wl):
     from dlwp_benchmark_b200 import ensemble, metrics as M, native
     numa_bound = ensemble.bind_to_device_cpus(local) if world > 1 else False   # before any pinned allocation
 
-    members = args.members or members_default
+    members_total, members_max, _, members = member_split(args, members_default, rank)
     ctx = kw["context_size"]
     T = ctx + lead
     torch.manual_seed(1234)                                   # identical random-init weights on every rank
@@ -439,17 +496,21 @@ def run_ours(args, wl):
     const, presc, prog = (None if t is None else t.to(dev) for t in (const_h, presc_h, prog_h))
     in_bytes = sum(t.numel() * 4 for t in (const_h, presc_h, prog_h) if t is not None)
     # what dlwp_rollout_host copies: constants, prescribed frames [0, T-1), and the first ctx frames of prognostic
-    h2d_bytes = (const_h.numel() * 4 if const_h is not None else 0) + members * ctx * Cg * H * W * 4 + \
-        (members * (T - 1) * kw["prescribed_channels"] * H * W * 4 if presc_h is not None else 0)
-    out_bytes = members * lead * Cg * H * W * 4
+    # whole job (all ranks): constants, the first ctx prognostic frames, prescribed frames [0, T-1) in; the forecast out
+    h2d_bytes = members_total * H * W * 4 * (kw["constant_channels"] + ctx * Cg + (T - 1) * kw["prescribed_channels"])
+    out_bytes = members_total * lead * Cg * H * W * 4
     flush = None if in_bytes > 126e6 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream(dev)
 
+    count = members_total * H * W      # (sample, lat, lon) points over all ranks: known without communication
+    sums_buf = torch.zeros(lead, Cg, 4, dtype=torch.float64, device=dev)
+
     def step():
         out = mod(constants=const, prescribed=presc, prognostic=prog)
-        sums = M.partial_sums(out, target, clim)
-        sums, count = M.reduce_sums(sums, members * H * W)
-        return out, sums, count
+        sums_buf.zero_()
+        M.partial_sums(out, target, clim, out=sums_buf)
+        M.reduce_sums(sums_buf)      # in place; NCCL when world > 1
+        return out, sums_buf
 
     def barrier():
         if world > 1:
@@ -458,7 +519,7 @@ def run_ours(args, wl):
 
     with torch.no_grad():
         for _ in range(max(args.warmup, 3)):
-            out, sums, count = step()
+            out, sums = step()
         barrier()
         n0 = native.launch_count()
         pairs = []
@@ -468,7 +529,7 @@ def run_ours(args, wl):
                     flush.fill_(1)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(stream)
-                out, sums, count = step()
+                out, sums = step()
                 e1.record(stream)
                 pairs.append((e0, e1))
             barrier()
@@ -496,7 +557,7 @@ def run_ours(args, wl):
     ms_total, e2e_s = float(t[0]), float(t[1])
     if rank == 0:
         hbm_peak, tc_peak, which = measured_peaks()
-        units = members * lead * args.steps * world
+        units = members_total * lead * args.steps
         ms_step = ms_total / args.steps
         entries = prof.entries
         name, (kms, kn) = max(entries.items(), key=lambda kv: kv[1][0])
@@ -512,11 +573,14 @@ def run_ours(args, wl):
             roof["achieved"] = per_launch / (kms / kn * 1e-3) / 1e9
             roof["frac"] = roof["achieved"] / hbm_peak
             roof["algorithmic_bytes_per_launch"] = per_launch
-        if args.workload == "c4" and members == members_default:
+        if args.workload == "c4" and members == members_default and world == 1:
             roof["traffic"] = ncu_traffic(name)
-            roof["traffic_source"] = "profiles/r01_ncu_full_tc_v5.csv (ncu --set full of this command, mean over the kernel's launches)"
+            roof["traffic_source"] = (f"profiles/{NCU_FULL_CSV} (ncu --set full of this command on this kernel set, mean over "
+                                      "the kernel's launches; null when the summary does not hold the kernel)")
+        roof["note"] = ("achieved = ALGORITHMIC bytes per launch / measured time per launch (a fraction of speed of light, "
+                        "not measured DRAM traffic: that is `traffic`)")
         fl = step_flops(cls, kw, members, H, W)
-        sb = step_bytes(cls, kw, members, H, W)
+        sb = step_bytes(cls, kw, members, H, W, b=2 if args.precision == "bf16" else 4)
         spec_names = [n for n in entries if n in ("tdft_kernel", "mix_dense_kernel", "mix_afno_kernel", "fno_mid_kernel",
                                                   "tcw_fwd_wdft", "tcw_fwd_hdft", "tcw_inv_hdft",
                                                   "afno_fwd_kernel", "afno_mid_kernel", "afno_inv_kernel",
@@ -535,13 +599,14 @@ def run_ours(args, wl):
         line = {
             "metric": "rollout samples*steps/s", "value": units / (ms_total * 1e-3), "unit": "samples*steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": {"fp32": "f32", "fp32_tc": "f32 (split-bf16 tensor-core products, fp32 accumulate)",
                       "bf16": "bf16"}[args.precision],
             "data": "synthetic N(0,1) fields, random-init weights (seed 1234)",
-            "config": config_block(args, wl, members),
+            "config": config_block(args, wl, members_max, members_total),
             "e2e": {"value": units / e2e_s, "unit": "samples*steps/s", "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": out_bytes, "ms_per_step": e2e_s / args.steps * 1e3,
+                    "bytes_are": "whole job (sum over ranks)",
                     "api": "dlwp_rollout_host (pinned host buffers in the reference's [B,T,C,H,W] layout; copies in "
                            "constants and the ctx prescribed / prognostic frames ahead of the first step, streams the "
                            "later prescribed frames in and the whole forecast back frame by frame under the steps' compute)"},
@@ -563,12 +628,37 @@ def run_ours(args, wl):
             "rmse_lead1_lastlead": [float(rmse[0].mean()), float(rmse[-1].mean())],
         }
         if world == 1 and not args.no_cpu_baseline:
+            # the CPU oracle on the first `cm` members of the TIMED inputs with the timed module's weights: its time is
+            # the cpu_baseline, its output checks the timed rollout (`parity`; outside the timed region)
             cm = min(args.cpu_members, members)
             cl = 1 if args.workload == "c5" else lead
-            rate, sec, cores = cpu_rollout_rate(cls, kw, H, W, cl, cm, 1, 0)
+            sd = {k: v.detach().cpu() for k, v in mod.state_dict().items()}
+            rate, sec, cores, want = cpu_rollout_rate(cls, kw, H, W, cl, cm, 1, 0, state_dict=sd,
+                                                      inputs=(const_h, presc_h, prog_h))
             line["cpu_baseline"] = {"value": rate, "unit": "samples*steps/s", "cores": cores, "kind": "port",
                                     "sample": f"{cm} members x {cl} lead steps, one rollout ({sec:.1f} s), "
                                               "oracle/ in torch fp32 on all host threads"}
+            got = out[:cm, :cl].float().cpu().double()
+            want = want.double()
+            x0 = prog_h[:cm, ctx - 1].double()
+            incr = (want[:, 0] - x0).abs().max()
+            disp = (want - x0.unsqueeze(1)).pow(2).mean(dim=(0, 2, 3, 4)).sqrt()
+            traj = (got - want).pow(2).mean(dim=(0, 2, 3, 4)).sqrt() / disp
+            line["parity"] = {
+                "max_rel_increment": float((got[:, 0] - want[:, 0]).abs().max() / incr),
+                "max_rel_output_step1": float((got[:, 0] - want[:, 0]).abs().max() / want[:, 0].abs().max()),
+                "traj_err_over_displacement": {"lead_1": float(traj[0]), f"lead_{cl}": float(traj[-1]), "max": float(traj.max())},
+                "members_checked": cm, "lead_steps_checked": cl,
+                "what": "the timed rollout's first members against the CPU oracle (oracle/, torch fp32) on the same inputs "
+                        "with the timed module's state_dict; increment = out_1 - x_0; FNO/TFNO oracle = restatement of the "
+                        "un-vendored neuralop (parity unpinned), FourCastNet oracle pinned to the reference source"}
+            if not args.no_eager:
+                erate, ems = gpu_eager_rate(cls, kw, lead, sd, (const, presc, prog), dev)
+                line["gpu_eager_baseline"] = {
+                    "value": erate, "unit": "samples*steps/s", "ms_per_step": ems, "members": members,
+                    "what": "oracle/ modules .cuda(): stock PyTorch eager on this B200 (cuFFT rfft2 / irfft2, einsum, cuDNN 1x1 "
+                            "convolutions; torch defaults, i.e. TF32 allowed in cuDNN), same inputs and weights, CUDA events, "
+                            "3 rollouts after one warm-up"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -582,11 +672,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c4")
-    ap.add_argument("--members", type=int, default=0, help="ensemble members per GPU (0 = the workload's default)")
+    ap.add_argument("--members", type=int, default=0,
+                    help="ensemble members: in total with --scaling strong, per GPU with --scaling weak (0 = the workload's default)")
+    ap.add_argument("--scaling", choices=["strong", "weak"], default=None,
+                    help="strong: --members in total, sharded over the GPUs (default for c4); weak: --members per GPU")
+    ap.add_argument("--no-eager", action="store_true", help="skip the PyTorch-eager-on-GPU baseline leg")
     ap.add_argument("--precision", choices=["fp32", "fp32_tc", "bf16"], default="fp32_tc")
     ap.add_argument("--cpu-members", type=int, default=64, help="members in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.scaling is None:
+        args.scaling = "strong" if args.workload == "c4" else "weak"
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, wl)
