@@ -67,6 +67,9 @@ struct dlwp_plan {
   uint8_t *tc_liftW1 = nullptr, *tc_liftW2 = nullptr, *tc_projW1 = nullptr, *tc_projW2 = nullptr,
           *tc_projW1x = nullptr;
   std::vector<uint8_t*> tc_skip;                        // per layer skip-conv images
+  bool tc_mid2 = false;                                 // the retained-column products run on tcgen05 (fno_mid_tc_kernel, tc_mid2.cu)
+  uint8_t *tc_midF = nullptr, *tc_midG = nullptr;       // (re|im)-stacked forward / inverse H-DFT operand images
+  std::vector<uint8_t*> tc_midW;                        // per layer mode-weight operand images [Kc][R][8 KB]
 
   // bf16 tensor-core path at hidden width 128 (tc_wide.cuh): precision == DLWP_PREC_BF16
   bool tcw = false;

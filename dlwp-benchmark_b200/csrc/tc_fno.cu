@@ -65,11 +65,26 @@ __device__ __forceinline__ void drain_d3(const EpiId& id, int tile, const TcGeom
     if (lane < 16 && h2 < g.RT && kx < g.Kc) {
       const int grow = tile * g.RT + h2;
       const int b = grow / g.H, h = grow - b * g.H;
+      if (g.abf) {
+        // split-bf16 operand tiles of fno_mid_tc_kernel: [kx][hi | lo][b][channel group][k = 2h + (re|im)][8 channels]
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) split2p(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), hi[e], lo[e]);
+        const size_t tile_b = (size_t)g.H * 128;
+        uint8_t* d = reinterpret_cast<uint8_t*>(Aout) + ((size_t)(kx * 2) * g.Bn + b) * tile_b + (size_t)(2 * id.half) * (g.H * 32) +
+                     (size_t)(2 * h + reim) * 16;
+#pragma unroll
+        for (int gq = 0; gq < 2; ++gq) {
+          *reinterpret_cast<uint4*>(d + gq * (g.H * 32)) = make_uint4(hi[4 * gq], hi[4 * gq + 1], hi[4 * gq + 2], hi[4 * gq + 3]);
+          *reinterpret_cast<uint4*>(d + (size_t)g.Bn * tile_b + gq * (g.H * 32)) = make_uint4(lo[4 * gq], lo[4 * gq + 1], lo[4 * gq + 2], lo[4 * gq + 3]);
+        }
+      } else {
       float4* dst = reinterpret_cast<float4*>(Aout + ((((size_t)b * g.Kc + kx) * g.H + h) * 2 + reim) * 32 + 16 * id.half);
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         dst[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
                              __uint_as_float(r[4 * j + 3]));
+      }
     }
   }
   tc_fence_before();
@@ -324,6 +339,22 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
           if (live) {
             const int grow = tile * g.RT + h2;
             const int bb = grow / g.H, h = grow - bb * g.H;
+            if (g.abf) {
+              // split-bf16 operand tiles of fno_mid_tc_kernel: [kx][hi | lo][b][channel group][k = 2h + (re|im)][8 channels]
+              uint32_t hi[16], lo[16];
+#pragma unroll
+              for (int e = 0; e < 16; ++e)
+                split2p(make_float2(__uint_as_float(r[2 * e]) + __uint_as_float(r2[2 * e]), __uint_as_float(r[2 * e + 1]) + __uint_as_float(r2[2 * e + 1])),
+                        hi[e], lo[e]);
+              const size_t tile_b = (size_t)g.H * 128;
+              uint8_t* d = reinterpret_cast<uint8_t*>(a.Aout) + ((size_t)(kx * 2) * g.Bn + bb) * tile_b + (size_t)(2 * h + reim) * 16;
+#pragma unroll
+              for (int gq = 0; gq < 4; ++gq) {
+                *reinterpret_cast<uint4*>(d + gq * (g.H * 32)) = make_uint4(hi[4 * gq], hi[4 * gq + 1], hi[4 * gq + 2], hi[4 * gq + 3]);
+                *reinterpret_cast<uint4*>(d + (size_t)g.Bn * tile_b + gq * (g.H * 32)) =
+                    make_uint4(lo[4 * gq], lo[4 * gq + 1], lo[4 * gq + 2], lo[4 * gq + 3]);
+              }
+            } else {
             float4* dst = reinterpret_cast<float4*>(a.Aout + ((((size_t)bb * g.Kc + kx) * g.H + h) * 2 + reim) * 32);
 #pragma unroll
             for (int j = 0; j < 8; ++j)
@@ -331,6 +362,7 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
                                    __uint_as_float(r[4 * j + 1]) + __uint_as_float(r2[4 * j + 1]),
                                    __uint_as_float(r[4 * j + 2]) + __uint_as_float(r2[4 * j + 2]),
                                    __uint_as_float(r[4 * j + 3]) + __uint_as_float(r2[4 * j + 3]));
+            }
           }
         }
       }

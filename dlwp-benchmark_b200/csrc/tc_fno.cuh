@@ -36,6 +36,8 @@ struct TcGeom {
   int KXP;             // padded real columns per grid row = 32 / RT  (2 * Kc <= KXP)
   int Kc;              // retained half-spectrum columns
   int KZ;              // K extent of the inverse W-DFT operands: 8 per retained column, padded to 16
+  int abf;             // the forward W-DFT leaves as split-bf16 operand tiles for fno_mid_tc_kernel (tc_mid2.cu) instead of planar fp32
+  int Bn;              // samples of this launch (ntiles * 128 / HW)
 };
 
 struct TcLiftArgs {
@@ -94,6 +96,27 @@ struct TcMidArgs {
 };
 size_t tc_mid_smem_bytes(int H, int R);
 int launch_tc_mid(const TcMidArgs& a, cudaStream_t st);
+
+// The same three products on tcgen05 (tc_mid2.cu): the forward W-DFT of the lift / layer kernels arrives as
+// split-bf16 operand tiles, one per (retained column kx, part hi | lo, sample b):
+//   A[kx][part][b] : [4 channel groups g][2H rows k = 2 h + (re|im)][8 channels] bf16 = H * 128 bytes,
+// i.e. the MN-major B operand of   X[(re|im, r), (b, i)] = Fs[(re|im, r), k] * A[k, (b, i)]   for NB samples at once.
+struct TcMid2Args {
+  const uint8_t* A;       // [Kc][2][B][H * 128 bytes]
+  const uint8_t* Wimg;    // this layer's mode weights as operand images [Kc][R][hi 4 KB | lo 4 KB]: rows o, K = (Wr^T | Wi^T)
+  const uint8_t* Fimg;    // forward H-DFT, (re|im)-stacked: [hi | lo] images of 32 rows x 2H
+  const uint8_t* Gimg;    // inverse H-DFT, (re|im)-stacked: [hi | lo] images of 2H rows x 32
+  uint8_t* Zimg;          // as TcMidArgs
+  int B, H, R, Kc, RT, KZ;
+};
+// samples per work item (0 = this geometry is not covered: the fp32 FMA kernel runs instead)
+int tc_mid2_samples(int H, int R);
+int launch_tc_mid2(const TcMid2Args& a, cudaStream_t st);
+// mode-major fp32 weights [R][Kc][32][32] complex -> operand images (device kernel)
+int launch_tc_mid2_pack(const float2* wm, uint8_t* Wimg, int R, int Kc, cudaStream_t st);
+// host: the stacked DFT operand images; Fh [R][H], Gh [H][R] complex as in plan.cu:build_bases (fp64)
+void tc_mid2_pack_bases(const double* Fh_re, const double* Fh_im, const double* Gh_re, const double* Gh_im, int H, int R,
+                        uint8_t* Fimg, uint8_t* Gimg);
 
 int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st);
 int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st);

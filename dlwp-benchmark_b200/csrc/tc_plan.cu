@@ -1,6 +1,7 @@
 // Plan-side glue of the tensor-core FNO path: eligibility, constant operand images, weight
 // images, and the per-step kernel sequence (reference: neuralop FNO.forward behind fno.py:103).
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "plan.cuh"
@@ -29,7 +30,7 @@ int plan_tc_build(dlwp_plan* p) {
   const int KZ = (2 * RT * Kc + 15) & ~15;
   if (d.n_rows > 16 || H % 8 != 0 || KZ > 48 || tc_mid_smem_bytes(H, d.n_rows) > 220 * 1024) return DLWP_OK;
 
-  p->tcg = TcGeom{0, H * W, H, W, RT, KXP, Kc, KZ};
+  p->tcg = TcGeom{0, H * W, H, W, RT, KXP, Kc, KZ, 0, 0};
   double s = 1.0, t = 1.0;
   const double hw = (double)H * (double)W;
   if (d.fft_norm == DLWP_FFT_NORM_BACKWARD) t = 1.0 / hw;
@@ -78,6 +79,29 @@ int plan_tc_build(dlwp_plan* p) {
   DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_projW1x, (size_t)Pj * 16 * 2));
   p->tc_skip.assign(d.n_layers, nullptr);
   for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_skip[l], 4096));
+  // H-DFT, mode mixing and inverse H-DFT on tcgen05 where the geometry allows it (DLWP_MID_FMA=1 keeps the fp32 FMA kernel: A/B runs)
+  p->tc_mid2 = tc_mid2_samples(H, d.n_rows) != 0 && std::getenv("DLWP_MID_FMA") == nullptr;
+  if (p->tc_mid2) {
+    const int R = d.n_rows;
+    std::vector<double> fr((size_t)R * H), fi((size_t)R * H), gr((size_t)H * R), gi2((size_t)H * R);
+    for (int j = 0; j < R; ++j)
+      for (int h = 0; h < H; ++h) {
+        long long a = ((long long)p->rows_in[j] * h) % H, b = ((long long)p->rows_out[j] * h) % H;
+        const double af = -2.0 * M_PI * (double)a / (double)H, ag = 2.0 * M_PI * (double)b / (double)H;
+        fr[(size_t)j * H + h] = std::cos(af);
+        fi[(size_t)j * H + h] = std::sin(af);
+        gr[(size_t)h * R + j] = std::cos(ag);
+        gi2[(size_t)h * R + j] = std::sin(ag);
+      }
+    std::vector<uint8_t> fimg((size_t)2 * 32 * 2 * H * 2), gimg((size_t)2 * 2 * H * 32 * 2);
+    tc_mid2_pack_bases(fr.data(), fi.data(), gr.data(), gi2.data(), H, R, fimg.data(), gimg.data());
+    DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_midF, fimg.size()));
+    DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_midG, gimg.size()));
+    DLWP_CUDA(cudaMemcpy(p->tc_midF, fimg.data(), fimg.size(), cudaMemcpyHostToDevice));
+    DLWP_CUDA(cudaMemcpy(p->tc_midG, gimg.data(), gimg.size(), cudaMemcpyHostToDevice));
+    p->tc_midW.assign(d.n_layers, nullptr);
+    for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_midW[l], (size_t)Kc * R * 8192));
+  }
   p->tc = true;
   return DLWP_OK;
 }
@@ -139,6 +163,8 @@ int plan_tc_commit(dlwp_plan* p, cudaStream_t st) {
   img.assign((size_t)16 * Pj * 4, 0);
   tc_pack_images(w.data(), Cg, Pj, Pj, 16, Pj, img.data());
   DLWP_TRY(upload(p->tc_projW2, img));
+  if (p->tc_mid2)      // the mode-major fp32 weights (packed by commit_fno on `st`) as tcgen05 operand images
+    for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(launch_tc_mid2_pack(p->wm[l], p->tc_midW[l], d.n_rows, d.n_cols, st));
   return DLWP_OK;
 }
 
@@ -148,6 +174,8 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   const int H = d.height, C = kTcC, R = d.n_rows, Kc = d.n_cols, N = d.n_layers;
   TcGeom g = p->tcg;
   g.ntiles = (int)((long long)B * g.HW / kTcTile);
+  g.abf = p->tc_mid2 ? 1 : 0;
+  g.Bn = B;
   const float *b2, *cbias, *pb2;
   DLWP_TRY(plan_need(p, "lifting.fcs.1.bias", C, &b2));
   DLWP_TRY(plan_need(p, "fno_blocks.convs.bias", (int64_t)N * C, &cbias));
@@ -170,10 +198,17 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   int cur = 0;
   for (int l = 0; l < N; ++l) {
     // H-DFT on the retained columns, per-mode channel mixing, inverse H-DFT -> Z' operand images
+    if (p->tc_mid2) {
+      TcMid2Args ma{};
+      ma.A = reinterpret_cast<const uint8_t*>(p->specA); ma.Wimg = p->tc_midW[l]; ma.Fimg = p->tc_midF; ma.Gimg = p->tc_midG;
+      ma.Zimg = p->tc_Z; ma.B = B; ma.H = H; ma.R = R; ma.Kc = Kc; ma.RT = g.RT; ma.KZ = g.KZ;
+      DLWP_TRY(launch_tc_mid2(ma, st));
+    } else {
     TcMidArgs ma{};
     ma.A = reinterpret_cast<const float*>(p->specA); ma.Wm = p->wm[l]; ma.Fh = p->Fh; ma.Gh = p->Gh; ma.Zimg = p->tc_Z;
     ma.B = B; ma.H = H; ma.R = R; ma.Kc = Kc; ma.RT = g.RT; ma.KZ = g.KZ;
     DLWP_TRY(launch_tc_mid(ma, st));
+    }
 
     TcLayerArgs ya{};
     ya.g = g;

@@ -119,7 +119,7 @@ extern "C" int dlwp_selftest_umma_bmn(const float* A, const float* Bkn, float* D
 static int selftest(const float* A, const float* B, float* Draw, int M, int N, int K, int bmn, void* stream) {
   if (!A || !B || !Draw) return fail(DLWP_ERR_INVALID, "dlwp_selftest_umma: null argument");
   DLWP_REQUIRE(M == 64 || M == 128, "M must be 64 or 128");
-  DLWP_REQUIRE(N >= 16 && N <= 256 && N % 16 == 0, "N must be a multiple of 16 in [16, 256]");
+  DLWP_REQUIRE(N >= 8 && N <= 256 && N % 8 == 0 && (M == 64 || N % 16 == 0), "N must be a multiple of 8 (M = 64) or 16 (M = 128) in [8, 256]");
   DLWP_REQUIRE(K >= 16 && K <= 128 && K % 16 == 0, "K must be a multiple of 16 in [16, 128]");
   cudaStream_t st = (cudaStream_t)stream;
   const size_t smem = (size_t)(M + N) * K * 2;
