@@ -422,8 +422,9 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
         mbar_wait(&b[LB_DEMPTY + db], empty_par(u));
         TR(w, u, 2);
         tc_fence_after();
+        // Z': MN-major B operand (K rows of 16 bytes = 8 channels; 8-row core matrices 128 B apart along K, KZ * 16 B along the channels)
         const uint64_t dX = chunk_desc(smem_u32(ws + L.X + s * kTileBytes), 128, 0),
-                       dZ = chunk_desc(smem_u32(ws + L.Z + s * z_bytes), 32, 0);
+                       dZ = smem_desc(smem_u32(ws + L.Z + s * z_bytes), 128, (uint32_t)g.KZ * 16u);
         const uint32_t d = tmem + 32u * db;
         uint32_t acc = 0;
 #pragma unroll
@@ -432,7 +433,7 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
           const uint32_t xa = term == 1 ? (uint32_t)kImg : 0u, wb = term == 2 ? 2048u : 0u;
 #pragma unroll 4
           for (int k0 = 0; k0 < g.KZ; k0 += 16) {     // operand chunks: 128 (32) rows x 16 bytes per 8 K
-            umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (k0 >> 3) * 512), idesc, acc);
+            umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (uint32_t)k0 * 16u), idesc | kIdescBMnMajor, acc);
             acc = 1;
           }
 #pragma unroll

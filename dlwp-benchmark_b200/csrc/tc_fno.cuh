@@ -58,7 +58,7 @@ struct TcLayerArgs {
   TcGeom g;
   const uint8_t* x_img;
   uint8_t* y_img;
-  const uint8_t* Zimg;    // per tile: split-bf16 operand image of the spectrum after the inverse H-DFT (tc_mid.cu)
+  const uint8_t* Zimg;    // per tile: split-bf16 MN-major operand image of the spectrum after the inverse H-DFT (layout: tc_mid.cu)
   float* Aout;            // forward W-DFT of the output (planar, as above), or null (last layer)
   const uint8_t* Gimg;    // inverse W-DFT operand [hi | lo] images, R = 128, K = KZ
   const uint8_t* Fimg;
@@ -103,9 +103,9 @@ int launch_tc_mid(const TcMidArgs& a, cudaStream_t st);
 // i.e. the MN-major B operand of   X[(re|im, r), (b, i)] = Fs[(re|im, r), k] * A[k, (b, i)]   for NB samples at once.
 struct TcMid2Args {
   const uint8_t* A;       // [Kc][2][B][H * 128 bytes]
-  const uint8_t* Wimg;    // this layer's mode weights as operand images [Kc][R][hi 4 KB | lo 4 KB]: rows o, K = (Wr^T | Wi^T)
-  const uint8_t* Fimg;    // forward H-DFT, (re|im)-stacked: [hi | lo] images of 32 rows x 2H
-  const uint8_t* Gimg;    // inverse H-DFT, (re|im)-stacked: [hi | lo] images of 2H rows x 32
+  const uint8_t* Wimg;    // this layer's mode weights as operand images [Kc][groups of 4 modes][hi 16 KB | lo 16 KB]: rows (mode, o), K = (Wr^T | Wi^T)
+  const uint8_t* Fimg;    // forward H-DFT, (re|im)-stacked: [hi | lo] images of 64 rows (Re X, Im X, -Im X, Re X) x 2H
+  const uint8_t* Gimg;    // inverse H-DFT, (re|im)-stacked: [hi | lo] images of max(2H, 64) rows x 32
   uint8_t* Zimg;          // as TcMidArgs
   int B, H, R, Kc, RT, KZ;
 };

@@ -21,9 +21,10 @@
 //            stored into the operand image
 //
 // Z operand image of one 128-pixel tile (RT grid rows), K index k = (kx * RT + h2) * 2 + (re | im):
-//   byte offset = part * (KZ * 64) + (k / 8) * 512 + c * 16 + (k % 8) * 2,   part 0 = hi, 1 = lo
-// i.e. the chunk-major [32 rows = channels] x [KZ] K-major UMMA operand of tc_common.cuh; a CTA
-// writes the 4 RT bytes of its column into every (tile, channel) chunk row.
+//   byte offset = part * (KZ * 64) + (c / 8) * (KZ * 16) + k * 16 + (c % 8) * 2,   part 0 = hi, 1 = lo
+// i.e. an MN-major UMMA operand (K rows of 8 channels = 16 bytes, four channel groups): the 2 RT rows of one retained
+// column are 32 RT contiguous bytes per channel group, so every store of a (tile, column) is made of whole 32-byte
+// sectors (the K-major form interleaved the columns' bytes inside every 16-byte row: four partial writes per sector).
 #include "tc_common.cuh"
 #include "tc_fno.cuh"
 
@@ -183,24 +184,17 @@ __global__ void __launch_bounds__(512, 1) fno_mid_kernel(const TcMidArgs a) {
       uint32_t hi[8], lo[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) split2(z[j].x, z[j].y, hi[j], lo[j]);
-      // K slots of this column: k = kx * 2 RT + h2 * 2 + (re|im)  ->  4 RT bytes per tile and channel
+      // K rows of this column: k = kx * 2 RT + h2 * 2 + (re|im); lane = channel: 2 bytes per K row (8 lanes fill a 16-byte row)
       const size_t tile0 = ((size_t)b * H + hg * 8) / RT;
       const size_t part = (size_t)a.KZ * 64;
-      const int k0 = kx * 2 * RT;
-      uint8_t* dst = a.Zimg + tile0 * (2 * part) + (size_t)(k0 >> 3) * 512 + lane * 16 + (k0 & 7) * 2;
+      uint8_t* dst = a.Zimg + tile0 * (2 * part) + (size_t)(lane >> 3) * (a.KZ * 16) + (size_t)(kx * 2 * RT) * 16 + (lane & 7) * 2;
 #pragma unroll
-      for (int t = 0; t < 8 / RT; ++t) {
-        uint8_t* d = dst + (size_t)t * (2 * part);
-        if (RT == 1) {
-          *reinterpret_cast<uint32_t*>(d) = hi[t];
-          *reinterpret_cast<uint32_t*>(d + part) = lo[t];
-        } else if (RT == 2) {
-          *reinterpret_cast<uint2*>(d) = make_uint2(hi[2 * t], hi[2 * t + 1]);
-          *reinterpret_cast<uint2*>(d + part) = make_uint2(lo[2 * t], lo[2 * t + 1]);
-        } else {
-          *reinterpret_cast<uint4*>(d) = make_uint4(hi[4 * t], hi[4 * t + 1], hi[4 * t + 2], hi[4 * t + 3]);
-          *reinterpret_cast<uint4*>(d + part) = make_uint4(lo[4 * t], lo[4 * t + 1], lo[4 * t + 2], lo[4 * t + 3]);
-        }
+      for (int j = 0; j < 8; ++j) {      // grid row hg * 8 + j: tile j / RT, row j % RT of it
+        uint8_t* d = dst + (size_t)(j / RT) * (2 * part) + (size_t)((j % RT) * 2) * 16;
+        *reinterpret_cast<uint16_t*>(d) = (uint16_t)(hi[j] & 0xffffu);
+        *reinterpret_cast<uint16_t*>(d + 16) = (uint16_t)(hi[j] >> 16);
+        *reinterpret_cast<uint16_t*>(d + part) = (uint16_t)(lo[j] & 0xffffu);
+        *reinterpret_cast<uint16_t*>(d + part + 16) = (uint16_t)(lo[j] >> 16);
       }
     }
     TRM(p + 1, 4);

@@ -93,14 +93,18 @@ int plan_tc_build(dlwp_plan* p) {
         gr[(size_t)h * R + j] = std::cos(ag);
         gi2[(size_t)h * R + j] = std::sin(ag);
       }
-    std::vector<uint8_t> fimg((size_t)2 * 32 * 2 * H * 2), gimg((size_t)2 * 2 * H * 32 * 2);
+    std::vector<uint8_t> fimg((size_t)2 * 64 * 2 * H * 2), gimg((size_t)2 * (2 * H < 64 ? 64 : 2 * H) * 32 * 2);
     tc_mid2_pack_bases(fr.data(), fi.data(), gr.data(), gi2.data(), H, R, fimg.data(), gimg.data());
     DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_midF, fimg.size()));
     DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_midG, gimg.size()));
     DLWP_CUDA(cudaMemcpy(p->tc_midF, fimg.data(), fimg.size(), cudaMemcpyHostToDevice));
     DLWP_CUDA(cudaMemcpy(p->tc_midG, gimg.data(), gimg.size(), cudaMemcpyHostToDevice));
     p->tc_midW.assign(d.n_layers, nullptr);
-    for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_midW[l], (size_t)Kc * R * 8192));
+    for (int l = 0; l < d.n_layers; ++l) {      // [Kc][groups of 4 modes][hi 16 KB | lo 16 KB]; the modes that pad the last group stay zero
+      const size_t wb = (size_t)Kc * ((R + 3) / 4) * 32768;
+      DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_midW[l], wb));
+      DLWP_CUDA(cudaMemset(p->tc_midW[l], 0, wb));
+    }
   }
   p->tc = true;
   return DLWP_OK;

@@ -21,7 +21,7 @@ t = tr.cpu().view(4, 24)
 t0 = int(t[0, 0])
 names = {1: 'before_pdl_wait', 2: 'after_pdl_wait', 3: 'consts_in', 4: 'A_in', 5: 'G1_issued', 6: 'X_full', 7: 'G2_issued', 8: 'G2_done',
          9: 'Y_full', 10: 'G3_issued', 11: 'E3_done', 12: 'e:D1_full', 13: 'e:E1_done', 14: 'e:D2_full', 15: 'e:E2_done', 16: 'e:D3_full',
-         17: 'e:E3_done'}
+         17: 'e:E3_done', 18: 'e:E1_ld', 19: 'e:E3_ld', 20: 'e:E3_stored', 21: 'e:E1_stored', 22: 'e:E1_fenced'}
 print(f'B={B} (last layer launch of the evaluation; cycles from kernel start)')
 for it in range(4):
     ev = sorted((int(t[it, k]) - t0, names[k]) for k in names if t[it, k] > 0)
