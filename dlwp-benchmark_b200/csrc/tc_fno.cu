@@ -928,6 +928,9 @@ void tc_pack_stacked_f64(const double* m, int rows, int cols, int ld, int R, int
 }  // namespace dlwp
 
 #ifdef DLWP_TRACE
+extern "C" int dlwp_debug_set_trace_mlp(unsigned long long* p) {
+  return cudaMemcpyToSymbol(dlwp::g_trace_mlp, &p, sizeof(p)) == cudaSuccess ? 0 : -2;
+}
 extern "C" int dlwp_debug_set_trace(unsigned long long* p) {
   return cudaMemcpyToSymbol(dlwp::g_trace, &p, sizeof(p)) == cudaSuccess ? 0 : -2;
 }

@@ -51,6 +51,14 @@ __device__ __forceinline__ uint32_t full_par(uint32_t u) { return (u >> 1) & 1u;
 __device__ __forceinline__ uint32_t empty_par(uint32_t u) { return ((u >> 1) & 1u) ^ 1u; }
 }  // namespace
 
+#ifdef DLWP_TRACE
+// clock64 stamps of the MLP epilogue of block 0, worker 0, warp 0 (one copy per translation unit): [chunk step < 64][8]
+static __device__ unsigned long long* g_trace_mlp = nullptr;
+#define TRE(nc, ev) do { if (g_trace_mlp && blockIdx.x == 0 && threadIdx.x == 0 && (nc) < 64) g_trace_mlp[(nc) * 8 + (ev)] = clock64(); } while (0)
+#else
+#define TRE(nc, ev) do {} while (0)
+#endif
+
 namespace {
 
 // (the A2 ring has room for four slots; the FNO kernels use two)
@@ -166,13 +174,17 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
 #pragma unroll
         for (int e = 0; e < 4; ++e) bv[j][e] = __ldg(reinterpret_cast<const float4*>(sB1 + p * 64 + 32 * j + 16 * id.half) + e);
     }
+    TRE(nc, 0);
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
+    TRE(nc, 1);
     tc_fence_after();
 #pragma unroll
     for (int j = 0; j < 2; ++j, ++nc) {
       uint32_t r[16];
+      TRE(nc, 2);
       tmem_ld16(tmem_lane + 64u * db + 32u * j, r);
       tmem_ld_wait();
+      TRE(nc, 3);
       if (j == 1) {
         tc_fence_before();
         mbar_arrive(&b[MB_D1EMPTY + db]);
@@ -194,14 +206,18 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
         for (int e = 0; e < 8; ++e) split2p(g2[e], h[e], l[e]);
       }
       const int ab = nc % NA2;
+      TRE(nc, 4);
       mbar_wait(&b[MB_A2EMPTY + ab], ((nc / NA2) & 1u) ^ 1u);
+      TRE(nc, 5);
       uint8_t* dst = sA2 + ab * kTileBytes + id.row * 16 + id.half * 4096;
       *reinterpret_cast<uint4*>(dst) = make_uint4(h[0], h[1], h[2], h[3]);
       *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(h[4], h[5], h[6], h[7]);
       *reinterpret_cast<uint4*>(dst + kImg) = make_uint4(l[0], l[1], l[2], l[3]);
       *reinterpret_cast<uint4*>(dst + kImg + 2048) = make_uint4(l[4], l[5], l[6], l[7]);
+      TRE(nc, 6);
       fence_async_smem();
       mbar_arrive(&b[MB_A2FULL + ab]);
+      TRE(nc, 7);
     }
     after_pass(p);
   }
