@@ -57,7 +57,7 @@ class AFNO2D(nn.Module):
         cdt = torch.complex64 if x.dtype == torch.float32 else torch.complex128
         spec = torch.fft.rfft2(x, dim=(1, 2), norm="ortho").reshape(B, H, wh, self.num_blocks, self.block_size)
         rows, cols = afno_kept_region(H, wh, self.hard_thresholding_fraction)
-        out = torch.zeros(B, H, wh, self.num_blocks, self.block_size, dtype=cdt)
+        out = torch.zeros(B, H, wh, self.num_blocks, self.block_size, dtype=cdt, device=x.device)
         if rows and cols:
             r0, r1, c1 = rows[0], rows[-1] + 1, cols[-1] + 1
             w1 = torch.complex(self.w1[0], self.w1[1]).to(cdt)
