@@ -331,37 +331,4 @@ int dlwp_metrics_accumulate(const float* outputs, const float* targets, const fl
   return launch_metrics(outputs, targets, climatology, lat_weights, batch, T, C, H, W, sums, (cudaStream_t)stream);
 }
 
-int dlwp_spectral_conv2d(const float* x, const float* weight, const float* bias, float* y, int batch, int Ci,
-                         int Co, int H, int W, int n_rows, int n_cols, const int32_t* rows_in,
-                         const int32_t* rows_out, int fft_norm, void* stream) {
-  if (!x || !weight || !y || !rows_in || !rows_out)
-    return fail(DLWP_ERR_INVALID, "dlwp_spectral_conv2d: null argument");
-  DLWP_REQUIRE(Ci == Co, "dlwp_spectral_conv2d: Ci != Co is not supported by the stand-alone entry (%d vs %d)", Ci, Co);
-  // a throw-away FNO-kind plan supplies bases and workspace; this entry is a convenience for
-  // tests and single-layer users, not the graph-capturable hot path
-  dlwp_model_desc d{};
-  d.kind = DLWP_MODEL_FNO; d.precision = DLWP_PREC_FP32; d.max_batch = batch; d.height = H; d.width = W;
-  d.prognostic_channels = Co; d.context_size = 1; d.fft_norm = fft_norm; d.n_rows = n_rows; d.n_cols = n_cols;
-  d.rows_in = rows_in; d.rows_out = rows_out; d.hidden_channels = Ci; d.projection_channels = 1; d.n_layers = 1;
-  int dev = 0;
-  DLWP_CUDA(cudaGetDevice(&dev));
-  dlwp_plan* p = nullptr;
-  DLWP_TRY(dlwp_plan_create(&d, dev, &p));
-  cudaStream_t st = (cudaStream_t)stream;
-  float2* wm = nullptr;
-  int rc = DLWP_OK;
-  const size_t wn = (size_t)Ci * Co * n_rows * n_cols;
-  if (cudaMalloc((void**)&wm, wn * sizeof(float2)) != cudaSuccess) {
-    rc = fail(DLWP_ERR_CUDA, "cudaMalloc failed for the packed spectral weight");
-  }
-  if (rc == DLWP_OK) rc = launch_pack_modes(reinterpret_cast<const float2*>(weight), wm, Ci, Co, n_rows, n_cols, st);
-  if (rc == DLWP_OK) rc = launch_nchw_to_nhwc(x, p->act0, batch, Ci, H * W, st);
-  if (rc == DLWP_OK) rc = spectral_layer(p, p->act0, p->act1, wm, 0, nullptr, nullptr, bias, 0, batch, st);
-  if (rc == DLWP_OK) rc = launch_nhwc_to_nchw(p->act1, y, batch, Co, H * W, st);
-  cudaStreamSynchronize(st);
-  if (wm) cudaFree(wm);
-  free_plan(p);
-  return rc;
-}
-
 }  // extern "C"

@@ -13,7 +13,7 @@ import threading
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libdlwp_b200.so")
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 MODEL_FNO, MODEL_AFNO = 0, 1
 AFNO_FILTER_AFNO2D, AFNO_FILTER_FNO2D = 0, 1
 PREC_FP32, PREC_FP32_TC, PREC_BF16 = 0, 1, 2
@@ -40,6 +40,13 @@ class ModelDesc(C.Structure):
     ]
 
 
+class FrbWeights(C.Structure):
+    """Mirror of ``dlwp_frb_weights`` (FourierResidualBlock parameters, device pointers)."""
+    _fields_ = [(n, C.c_void_p) for n in (
+        "f1_w1", "f1_w2", "conv1_w", "conv1_b", "f2_w1", "f2_w2", "conv2_w", "conv2_b", "short_w", "short_b",
+        "norm1_w", "norm1_b", "norm2_w", "norm2_b")] + [("n_groups", C.c_int32), ("eps", C.c_float)]
+
+
 # name -> (restype, argtypes); every symbol the header declares
 _P = C.c_void_p
 SYMBOLS = {
@@ -61,6 +68,8 @@ SYMBOLS = {
                                        C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
     "dlwp_spectral_conv2d_static": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                               C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
+    "dlwp_fourier_residual_block_workspace": (C.c_int, [C.c_int] * 7 + [C.POINTER(C.c_size_t)]),
+    "dlwp_fourier_residual_block": (C.c_int, [_P, C.POINTER(FrbWeights), _P] + [C.c_int] * 7 + [_P, C.c_size_t, _P]),
     "dlwp_launch_count": (C.c_int64, []),
     "dlwp_selftest_umma": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_selftest_umma_bmn": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define DLWP_ABI_VERSION 2
+#define DLWP_ABI_VERSION 3
 
 typedef enum {
   DLWP_OK = 0,
@@ -161,8 +161,9 @@ int dlwp_metrics_accumulate(const float* outputs, const float* targets, const fl
                             double* sums, void* stream);
 
 /* Stand-alone dense Fourier layer y = irfft2(mix(rfft2(x)[bins])) for NCHW tensors:
- * unet.py:19-69 (SpectralConv2d) and the neuralop SpectralConv.  weight: device complex
- * (real view) [Ci, Co, n_rows, n_cols, 2]; bias: device [Co] or NULL. */
+ * unet.py:19-69 (SpectralConv2d; Ci != Co as unet.py:26-44 allows) and the neuralop SpectralConv.  weight: device complex
+ * (real view) [Ci, Co, n_rows, n_cols, 2]; bias: device [Co] or NULL.  A convenience entry: one cudaMalloc / cudaFree and a
+ * stream synchronisation per call (dlwp_spectral_conv2d_static allocates nothing; dlwp_fourier_residual_block takes a workspace). */
 int dlwp_spectral_conv2d(const float* x, const float* weight, const float* bias, float* y,
                          int batch, int Ci, int Co, int H, int W, int n_rows, int n_cols,
                          const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
@@ -182,6 +183,30 @@ int dlwp_spectral_conv2d_static(const float* x, const float* weight, const float
                                 int batch, int Ci, int Co, int H, int W, int n_rows, int n_cols,
                                 const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
                                 void* stream);
+
+/* FourierResidualBlock.forward (models/unet/unet.py:780-836), the in-repo statement of the fused spectral pattern:
+ *   h = act(norm1(x)); out = fourier1(h) + conv1(h); out = act(norm2(out)); y = fourier2(out) + conv2(out) + shortcut(x)
+ * with act = exact GELU (the constructor default, :804), SpectralConv2d corners rows [:modes1] and [-modes1:], columns
+ * [:modes2] (:60-65), 1x1 convolutions with bias, GroupNorm when the norm pointers are set (norm=True, :818-820) and the
+ * shortcut convolution when in_channels != out_channels (:813-816).  All pointers are device pointers; weights in the
+ * reference's state_dict shapes (complex weights as real views [.., 2]).  x [B, Ci, H, W] -> y [B, Co, H, W].
+ * The call allocates nothing and does not synchronise: every intermediate lives in `workspace` (device,
+ * dlwp_fourier_residual_block_workspace bytes, 256-byte aligned); the additions and the second GELU run in the epilogue of
+ * the inverse transforms. */
+typedef struct {
+  const float *f1_w1, *f1_w2;       /* fourier1.weights1 / .weights2  [Ci, Co, modes1, modes2, 2] */
+  const float *conv1_w, *conv1_b;   /* conv1.weight [Co, Ci, 1, 1], conv1.bias [Co] */
+  const float *f2_w1, *f2_w2;       /* fourier2.weights1 / .weights2  [Co, Co, modes1, modes2, 2] */
+  const float *conv2_w, *conv2_b;   /* conv2.weight [Co, Co, 1, 1], conv2.bias [Co] */
+  const float *short_w, *short_b;   /* shortcut.weight [Co, Ci, 1, 1], .bias [Co]; NULL = Identity (Ci == Co) */
+  const float *norm1_w, *norm1_b;   /* norm1.weight / .bias [Ci]; NULL = Identity (norm=False) */
+  const float *norm2_w, *norm2_b;   /* norm2.weight / .bias [Co]; NULL = Identity */
+  int32_t n_groups;                 /* GroupNorm groups (ignored without normalisation) */
+  float eps;                        /* GroupNorm eps (torch default 1e-5) */
+} dlwp_frb_weights;
+int dlwp_fourier_residual_block_workspace(int batch, int Ci, int Co, int H, int W, int modes1, int modes2, size_t* bytes);
+int dlwp_fourier_residual_block(const float* x, const dlwp_frb_weights* w, float* y, int batch, int Ci, int Co, int H, int W,
+                                int modes1, int modes2, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Number of kernels this library has launched in this process (for bench "gpu_launches"). */
 int64_t dlwp_launch_count(void);

@@ -37,17 +37,20 @@ class SpectralConv2d(nn.Module):
 
 
 class FourierResidualBlock(nn.Module):
-    """GELU -> (spectral + 1x1) -> GELU -> (spectral + 1x1) + shortcut; norm=False path only."""
+    """act(norm1) -> (spectral + 1x1) -> act(norm2) -> (spectral + 1x1) + shortcut (``unet.py:780-836``); act = exact
+    GELU (the constructor default), norm = GroupNorm(n_groups) or Identity."""
 
-    def __init__(self, in_channels, out_channels, modes1=16, modes2=16):
+    def __init__(self, in_channels, out_channels, modes1=16, modes2=16, norm=False, n_groups=1):
         super().__init__()
         self.fourier1 = SpectralConv2d(in_channels, out_channels, modes1, modes2)
         self.conv1 = nn.Conv2d(in_channels, out_channels, 1)
         self.fourier2 = SpectralConv2d(out_channels, out_channels, modes1, modes2)
         self.conv2 = nn.Conv2d(out_channels, out_channels, 1)
         self.shortcut = nn.Conv2d(in_channels, out_channels, 1) if in_channels != out_channels else nn.Identity()
+        self.norm1 = nn.GroupNorm(n_groups, in_channels) if norm else nn.Identity()
+        self.norm2 = nn.GroupNorm(n_groups, out_channels) if norm else nn.Identity()
 
     def forward(self, x):
-        h = F.gelu(x)
-        out = F.gelu(self.fourier1(h) + self.conv1(h))
+        h = F.gelu(self.norm1(x))
+        out = F.gelu(self.norm2(self.fourier1(h) + self.conv1(h)))
         return self.fourier2(out) + self.conv2(out) + self.shortcut(x)

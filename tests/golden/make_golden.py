@@ -82,6 +82,20 @@ def spectral_case(seed=7):
     out.update({"block/" + k: v.detach().numpy() for k, v in blk.state_dict().items()})
     np.savez_compressed(os.path.join(HERE, "spectral2d.npz"), **out)
     print("spectral2d", tuple(y_conv.shape), tuple(y_blk.shape))
+    # a second block with GroupNorm (norm=True, two groups) and the identity shortcut (in_channels == out_channels);
+    # its own fixture file, drawn after the first one so that spectral2d.npz keeps its bytes
+    nblk = u.FourierResidualBlock(12, 12, modes1=5, modes2=7, norm=True, n_groups=2)
+    with torch.no_grad():
+        for n_, p_ in nblk.named_parameters():
+            if n_.startswith("norm"):
+                p_.add_(0.3 * torch.randn_like(p_))
+    xn = torch.randn(3, 12, 24, 40)
+    with torch.no_grad():
+        yn = nblk(xn)
+    outn = {"x": xn.numpy(), "y_block": yn.numpy()}
+    outn.update({"block/" + k: v.detach().numpy() for k, v in nblk.state_dict().items()})
+    np.savez_compressed(os.path.join(HERE, "spectral2d_norm.npz"), **outn)
+    print("spectral2d_norm", tuple(yn.shape))
 
 
 if __name__ == "__main__":

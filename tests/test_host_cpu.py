@@ -136,3 +136,30 @@ def test_forward_guards():
             m(prognostic=prog[:, :1], constants=torch.randn(1, 1, 4, 8, 16), prescribed=torch.randn(1, 1, 1, 8, 16))
         with pytest.raises(native.NativeError):         # CPU tensors: no fallback
             m(prognostic=prog, constants=torch.randn(1, 1, 4, 8, 16), prescribed=torch.randn(1, 2, 1, 8, 16))
+
+
+REF_CFG = "/root/reference/src/dlwpbench/configs"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_CFG), reason="/root/reference is not on this machine")
+@pytest.mark.parametrize("fname", ["fno.yaml", "fourcastnet.yaml"])
+def test_modules_build_from_the_reference_model_yaml(fname):
+    """scripts/train.py:54 / evaluate.py:140 do ``eval(cfg.model.type)(**cfg.model)``: every key of the reference's OWN yaml
+    file (including ``type`` and ``name``) goes to the constructor.  The ${data.*} interpolations are resolved from
+    configs/data/initial_variables.yaml as Hydra would."""
+    import yaml
+    data = yaml.safe_load(open(os.path.join(REF_CFG, "data", "initial_variables.yaml")))
+    text = open(os.path.join(REF_CFG, "model", fname)).read()
+    text = text.replace("${data.height}", str(data["height"])).replace("${data.width}", str(data["width"]))
+    cfg = yaml.safe_load(text)
+    cls = getattr(pkg, cfg["type"])
+    mod = cls(**cfg)
+    ref_cls = {"TFNO2DModule": owrap.TFNO2DModule, "FourCastNet": oafno.AFNONet}[cfg["type"]]
+    torch.manual_seed(0)
+    ref = ref_cls(**cfg)
+    # same parameter names and shapes as the (oracle restatement of the) reference module built from the same file
+    want = {k: tuple(v.shape) for k, v in ref.state_dict().items()}
+    got = {k: tuple(v.shape) for k, v in mod.state_dict().items()}
+    assert got == want
+    mod.load_state_dict(ref.state_dict(), strict=True)
+    assert mod.context_size == cfg["context_size"] and mod.prognostic_channels == cfg["prognostic_channels"]

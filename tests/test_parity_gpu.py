@@ -57,6 +57,31 @@ def test_spectral_conv2d_matches_reference_golden(pkg):
     assert max_rel(_spectral(x.cuda(), weight.cuda(), H, W, m1, m2), torch.from_numpy(g["y_conv"])) < 2e-5
 
 
+def test_spectral_conv2d_module_and_residual_block_match_reference_golden(pkg):
+    """The drop-in modules (reference parameter names; in_channels != out_channels) against the fixtures the unmodified
+    reference produced: SpectralConv2d 8 -> 12, FourierResidualBlock 8 -> 12 with the shortcut convolution, and a
+    GroupNorm block (norm=True, two groups, identity shortcut)."""
+    g = load_golden("spectral2d")
+    x = torch.from_numpy(g["x"]).cuda()
+    conv = pkg.SpectralConv2d(8, 12, 6, 5).cuda()
+    conv.load_state_dict({k[5:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("conv/")}, strict=True)
+    blk = pkg.FourierResidualBlock(8, 12, modes1=6, modes2=5).cuda()
+    blk.load_state_dict({k[6:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("block/")}, strict=True)
+    with torch.no_grad():
+        assert max_rel(conv(x), torch.from_numpy(g["y_conv"])) < 2e-5
+        for _ in range(2):      # the second call reuses the module's workspace
+            assert max_rel(blk(x), torch.from_numpy(g["y_block"])) < 2e-5
+    g = load_golden("spectral2d_norm")
+    nblk = pkg.FourierResidualBlock(12, 12, modes1=5, modes2=7, norm=True, n_groups=2).cuda()
+    nblk.load_state_dict({k[6:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("block/")}, strict=True)
+    with torch.no_grad():
+        err = max_rel(nblk(torch.from_numpy(g["x"]).cuda()), torch.from_numpy(g["y_block"]))
+    print(f"FourierResidualBlock with GroupNorm vs reference fixture: max-rel {err:.3e}")
+    assert err < 2e-5
+    with pytest.raises(NotImplementedError):
+        blk(x)      # grad mode on: forward-only
+
+
 def _spectral(x, weight, H, W, m1, m2):
     from dlwp_benchmark_b200 import native
     rows = list(range(m1)) + list(range(H - m1, H))

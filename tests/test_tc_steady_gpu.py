@@ -175,3 +175,39 @@ def test_repeated_rollouts_are_bit_identical_and_stay_inside_their_buffers(pkg, 
     torch.cuda.synchronize()
     assert torch.equal(buf[1024:1024 + n].view_as(runs[0]), runs[0])
     assert bool((buf[:1024] == 12345.0).all()) and bool((buf[1024 + n:] == 12345.0).all())
+
+
+@pytest.mark.parametrize("case", ["c4-B256", "afno-B24"])
+def test_rollout_is_cuda_graph_capturable(pkg, case):
+    """include/dlwp_b200.h promises that dlwp_rollout never allocates, never synchronises and only uses the caller's
+    stream: the whole rollout (programmatic-dependent launches included) is captured in a CUDA graph, replayed on new input
+    values, and gives the bits of the direct launches."""
+    cls, kw, prec, (B, H, W) = _models_for_guards(pkg)[case]
+    B = min(B, 64)
+    torch.manual_seed(3)
+    mod = getattr(pkg, cls)(**kw).cuda().eval()
+    mod.precision = prec
+    steps = 3
+    const, presc, prog = (t.cuda() for t in synthetic(B, 1 + steps, kw["constant_channels"], kw["prescribed_channels"],
+                                                      kw["prognostic_channels"], H, W, seed=21))
+    with torch.no_grad():
+        want0 = mod(constants=const, prescribed=presc, prognostic=prog).clone()
+    plan = next(iter(mod._plans.values()))
+    out = torch.empty_like(want0)
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s), torch.cuda.graph(graph, stream=s):
+        plan.rollout(const, presc, prog, out)
+    torch.cuda.synchronize()
+    out.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, want0)
+    prog.mul_(0.5)      # same buffers, new values
+    with torch.no_grad():
+        want1 = mod(constants=const, prescribed=presc, prognostic=prog).clone()
+    torch.cuda.synchronize()
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, want1) and not torch.equal(want1, want0)
