@@ -1,6 +1,8 @@
 // extern "C" surface of libdlwp_b200.so (include/dlwp_b200.h).  Nothing here throws.
 #include <new>
 
+#include <nvtx3/nvToolsExt.h>      // header-only; the ranges cost a null-pointer test unless a profiler is attached
+
 #include "plan.cuh"
 
 using namespace dlwp;
@@ -189,7 +191,10 @@ int dlwp_step(dlwp_plan* plan, const float* x, float* y, int batch, void* stream
   io.ngrp = 1;
   io.out = y;
   io.out_bstride = plan->d.prognostic_channels * HW;
-  return plan_backbone(plan, io, batch, (cudaStream_t)stream);
+  nvtxRangePushA("dlwp_step");
+  const int rc = plan_backbone(plan, io, batch, (cudaStream_t)stream);
+  nvtxRangePop();
+  return rc;
 }
 
 int dlwp_rollout(dlwp_plan* plan, const float* constants, const float* prescribed, const float* prognostic,
@@ -202,12 +207,17 @@ int dlwp_rollout(dlwp_plan* plan, const float* constants, const float* prescribe
                "constants pointer does not match constant_channels=%d", d.constant_channels);
   DLWP_REQUIRE((d.prescribed_channels == 0) == (prescribed == nullptr),
                "prescribed pointer does not match prescribed_channels=%d", d.prescribed_channels);
-  for (int t = d.context_size; t < T; ++t) {
+  nvtxRangePushA("dlwp_rollout");
+  int rc = DLWP_OK;
+  for (int t = d.context_size; t < T && rc == DLWP_OK; ++t) {
+    nvtxRangePushA("dlwp_rollout: lead step");
     StepIO io;
     rollout_io(plan, constants, prescribed, prognostic, outs, T, t, &io);
-    DLWP_TRY(plan_backbone(plan, io, batch, (cudaStream_t)stream));
+    rc = plan_backbone(plan, io, batch, (cudaStream_t)stream);
+    nvtxRangePop();
   }
-  return DLWP_OK;
+  nvtxRangePop();
+  return rc;
 }
 
 int dlwp_rollout_host(dlwp_plan* plan, const float* constants, const float* prescribed, const float* prognostic,

@@ -64,6 +64,7 @@ SYMBOLS = {
     "dlwp_rollout": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
     "dlwp_rollout_host": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
     "dlwp_metrics_accumulate": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "dlwp_denormalize_split": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_spectral_conv2d": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
     "dlwp_spectral_conv2d_static": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

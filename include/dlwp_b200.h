@@ -160,6 +160,12 @@ int dlwp_metrics_accumulate(const float* outputs, const float* targets, const fl
                             const float* lat_weights, int batch, int T, int C, int H, int W,
                             double* sums, void* stream);
 
+/* Evaluation tail (scripts/evaluate.py:281-296 + the per-variable slicing of build_dataset, :366-383): undoes the
+ * normalisation, out[c][b][t][:] = x[b][t][c][:] * std[c] + mean[c], and leaves one contiguous [B, T, H, W] array per
+ * variable for the writer.  x: device [B, T, C, H, W]; mean / std: device [C] or NULL (0 / 1); out: device [C, B, T, H, W]. */
+int dlwp_denormalize_split(const float* x, const float* mean, const float* std, float* out, int B, int T, int C, int H, int W,
+                           void* stream);
+
 /* Stand-alone dense Fourier layer y = irfft2(mix(rfft2(x)[bins])) for NCHW tensors:
  * unet.py:19-69 (SpectralConv2d; Ci != Co as unet.py:26-44 allows) and the neuralop SpectralConv.  weight: device complex
  * (real view) [Ci, Co, n_rows, n_cols, 2]; bias: device [Co] or NULL.  A convenience entry: one cudaMalloc / cudaFree and a

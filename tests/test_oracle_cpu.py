@@ -135,6 +135,8 @@ def test_fno_oracle_matches_live_neuralop(factorized):
     parameter names), outputs compared.  Skipped on machines without the package (this image has none: FNO / TFNO
     parity stays unpinned until this test has run somewhere)."""
     neuralop_models = pytest.importorskip("neuralop.models")
+    if getattr(neuralop_models, "__graft_stub__", False):      # the import stub oracle/ref_loader.py installs for the AFNO file
+        pytest.skip("neuralop is not installed (only ref_loader's import stub is)")
     from oracle import neuralop_fno as ofno
     kw = dict(n_modes=[12, 12], max_n_modes=None, in_channels=13, hidden_channels=32, lifting_channels=256,
               projection_channels=256, out_channels=8, n_layers=4)

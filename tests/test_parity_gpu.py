@@ -366,6 +366,19 @@ def test_metrics_kernel_matches_oracle(pkg, B, T, Cn, H, W):
     assert float((acc.cpu() - wa).abs().max()) < 1e-6
 
 
+@pytest.mark.parametrize("B,T,Cn,H,W", [(5, 3, 8, 32, 64), (2, 2, 3, 9, 15)])
+def test_denormalize_split_matches_the_reference_loop(pkg, B, T, Cn, H, W):
+    # evaluate.py:281-296 (x * std + mean per variable) + the per-variable arrays build_dataset slices out (:366-383)
+    from dlwp_benchmark_b200 import evaluation as ev
+    torch.manual_seed(4)
+    x, mean, std = torch.randn(B, T, Cn, H, W), 10.0 * torch.randn(Cn), torch.rand(Cn) + 0.5
+    got = ev.denormalize_split(x.cuda(), mean, std).cpu()
+    want = (x * std.view(1, 1, Cn, 1, 1) + mean.view(1, 1, Cn, 1, 1)).permute(2, 0, 1, 3, 4)
+    assert got.shape == (Cn, B, T, H, W)
+    assert torch.allclose(got, want, rtol=1e-6, atol=1e-6)
+    assert torch.equal(ev.denormalize_split(x.cuda()).cpu(), x.permute(2, 0, 1, 3, 4))
+
+
 def test_weights_are_repacked_after_in_place_update(pkg):
     ref, mod, kw, (B, H, W) = _fno_pair(pkg, "C2")
     const, presc, prog = synthetic(B, 2, 4, 1, 8, H, W)
