@@ -49,6 +49,8 @@ struct PwArgs {
   const float* pos;   // [tokens, N] or null (added after act)
   const float* resid; // NHWC [P, N] or null
   const float* resid2; // a second one (the FNO2D token mixer adds its input and the block residual)
+  const float* pre;    // NHWC [P, N] or null: added BEFORE the activation (training path: spectral branch of an FNO block)
+  float* preact;       // NHWC [P, N] or null: the pre-activation value is stored here too (saved for the backward pass)
   // output: NHWC `out[p * N + n]`, or (unpatch != 0) NCHW frame with n = (i, j, co):
   //   out[b * out_bstride + co*H*W + y*W + x] = v + last[b * last_bstride + same]
   float* out;

@@ -231,6 +231,8 @@ __global__ void __launch_bounds__(256) pw_linear_kernel(PwArgs a) {
       const int p = p0 + tm * 4 + i;
       if (p >= a.P) continue;
       float v = acc[i][j] + bias;
+      if (a.pre) v += a.pre[(long long)p * a.N + n];
+      if (a.preact) a.preact[(long long)p * a.N + n] = v;
       if (a.act == 1) v = gelu_erf(v);
       if (a.pos) v += a.pos[(long long)(p % a.tokens) * a.N + n];
       if (a.resid) v += a.resid[(long long)p * a.N + n];

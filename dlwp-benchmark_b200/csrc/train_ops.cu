@@ -1,0 +1,304 @@
+// Training primitives (the backward pass that scripts/train.py:263-271 needs) on the fp32 kernel set:
+//   dlwp_linear_forward / _backward      1x1 convolution / Linear with bias, optional pre-activation addend and exact GELU
+//                                        (neuralop MLP lifting / projection, the FNO skip convolutions + block epilogue)
+//   dlwp_spectral_forward / _backward    the dense Fourier layer (unet.py:15-69 / neuralop SpectralConv) on channels-last tensors:
+//                                        forward = the truncated-DFT chain of spectral_chain.cuh; backward = its adjoint
+//                                        (the same kernels with conjugate-transposed bases and weights) + the per-mode
+//                                        outer-product weight gradient
+// The Python side (dlwp_benchmark_b200/training.py) wraps them in torch.autograd.Function objects; everything between them
+// in the training-mode forward (concatenation of the step input, residual frame) is torch glue, every FLOP is here.
+#include <cmath>
+
+#include "kernels.cuh"
+#include "spectral_chain.cuh"
+
+namespace dlwp {
+namespace {
+
+// d gelu(z) / dz for the exact-erf GELU: Phi(z) + z phi(z)
+__device__ __forceinline__ float gelu_erf_grad(float z) {
+  const float cdf = 0.5f * (1.0f + erff(z * 0.70710678118654752440f));
+  const float pdf = 0.39894228040143267794f * __expf(-0.5f * z * z);
+  return cdf + z * pdf;
+}
+
+// dz = dy * act'(z)   (act = 1: exact GELU; otherwise a copy)
+__global__ void act_backward_kernel(const float* __restrict__ dy, const float* __restrict__ z, float* __restrict__ dz, long long n, int act) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dz[i] = act == 1 ? dy[i] * gelu_erf_grad(z[i]) : dy[i];
+}
+
+// dW[n, k] += sum_p dz[p, n] x[p, k],  db[n] += sum_p dz[p, n]: 32 x 32 tiles of dW, the pixels split over blockIdx.z,
+// partial tiles added with atomics (dW / db are cleared by the launcher)
+constexpr int WG_T = 32, WG_P = 32;
+__global__ void __launch_bounds__(256) linear_wgrad_kernel(const float* __restrict__ dz, const float* __restrict__ x, float* __restrict__ dW,
+                                                           float* __restrict__ db, int P, int K, int N, int per) {
+  __shared__ float sZ[WG_P][WG_T + 1], sX[WG_P][WG_T + 1];
+  const int n0 = blockIdx.x * WG_T, k0 = blockIdx.y * WG_T;
+  const int p_lo = blockIdx.z * per, p_hi = min(P, p_lo + per);
+  const int tn = threadIdx.x >> 4, tk = threadIdx.x & 15;      // 16 x 16 threads, 2 x 2 outputs each
+  float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, bsum = 0.f;
+  for (int p0 = p_lo; p0 < p_hi; p0 += WG_P) {
+    for (int i = threadIdx.x; i < WG_P * WG_T; i += 256) {
+      const int pp = i / WG_T, c = i - pp * WG_T, p = p0 + pp;
+      sZ[pp][c] = (p < p_hi && n0 + c < N) ? dz[(long long)p * N + n0 + c] : 0.f;
+      sX[pp][c] = (p < p_hi && k0 + c < K) ? x[(long long)p * K + k0 + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int pp = 0; pp < WG_P; ++pp) {
+      const float z0 = sZ[pp][2 * tn], z1 = sZ[pp][2 * tn + 1], x0 = sX[pp][2 * tk], x1 = sX[pp][2 * tk + 1];
+      acc[0][0] = fmaf(z0, x0, acc[0][0]);
+      acc[0][1] = fmaf(z0, x1, acc[0][1]);
+      acc[1][0] = fmaf(z1, x0, acc[1][0]);
+      acc[1][1] = fmaf(z1, x1, acc[1][1]);
+    }
+    if (db != nullptr && blockIdx.y == 0 && threadIdx.x < WG_T)
+      for (int pp = 0; pp < WG_P; ++pp) bsum += sZ[pp][threadIdx.x];
+    __syncthreads();
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int n = n0 + 2 * tn + a, k = k0 + 2 * tk + b;
+      if (n < N && k < K) atomicAdd(&dW[(long long)n * K + k], acc[a][b]);
+    }
+  if (db != nullptr && blockIdx.y == 0 && threadIdx.x < WG_T && n0 + threadIdx.x < N) atomicAdd(&db[n0 + threadIdx.x], bsum);
+}
+
+// [rows, cols] -> [cols, rows] for the small weight matrices (dx = dz W needs W with the other index contiguous)
+__global__ void transpose_small_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int cols) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows * cols; i += gridDim.x * blockDim.x) {
+    const int r = i / cols, c = i - r * cols;
+    out[(long long)c * rows + r] = in[i];
+  }
+}
+
+// adjoint bases of spectral_chain.cuh: GwH [Kc, W] = conj(Gw)^T, GhH [R, H] = conj(Gh)^T, FhH [H, R] = conj(Fh)^T, FwH [W, Kc] = conj(Fw)^T
+__global__ void adjoint_bases_kernel(const float2* __restrict__ Fw, const float2* __restrict__ Fh, const float2* __restrict__ Gh,
+                                     const float2* __restrict__ Gw, float2* GwH, float2* GhH, float2* FhH, float2* FwH, int H, int W, int R, int Kc) {
+  const int n_w = Kc * W, n_h = R * H, total = 2 * n_w + 2 * n_h;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    float2 v;
+    if (i < n_w) {                       // GwH[k, w] = conj(Gw[w, k])
+      const int k = i / W, w = i - k * W;
+      v = Gw[w * Kc + k];
+      GwH[i] = make_float2(v.x, -v.y);
+    } else if (i < n_w + n_h) {          // GhH[r, h] = conj(Gh[h, r])
+      const int e = i - n_w, r = e / H, h = e - r * H;
+      v = Gh[h * R + r];
+      GhH[e] = make_float2(v.x, -v.y);
+    } else if (i < n_w + 2 * n_h) {      // FhH[h, r] = conj(Fh[r, h])
+      const int e = i - n_w - n_h, h = e / R, r = e - h * R;
+      v = Fh[r * H + h];
+      FhH[e] = make_float2(v.x, -v.y);
+    } else {                             // FwH[w, k] = conj(Fw[k, w])
+      const int e = i - n_w - 2 * n_h, w = e / Kc, k = e - w * Kc;
+      v = Fw[k * W + w];
+      FwH[e] = make_float2(v.x, -v.y);
+    }
+  }
+}
+
+// dense complex [Ci, Co, R, Kc] -> mode-major adjoint [R, Kc, Co, Ci] with conj: WmH[m][o][i] = conj(W[i][o][m])
+__global__ void pack_modes_adjoint_kernel(const float2* __restrict__ w, float2* __restrict__ wmh, int Ci, int Co, int R, int Kc) {
+  const long long total = (long long)Ci * Co * R * Kc;
+  for (long long d = blockIdx.x * (long long)blockDim.x + threadIdx.x; d < total; d += (long long)gridDim.x * blockDim.x) {
+    long long t = d;      // destination [r][k][o][i]
+    const int i = (int)(t % Ci); t /= Ci;
+    const int o = (int)(t % Co); t /= Co;
+    const int k = (int)(t % Kc); t /= Kc;
+    const int r = (int)t;
+    const float2 v = w[(((long long)i * Co + o) * R + r) * Kc + k];
+    wmh[d] = make_float2(v.x, -v.y);
+  }
+}
+
+// dW[i, o, r, k] = sum_b conj(X[m, b, i]) dY[m, b, o]   (m = r Kc + k), written in the reference's dense layout [Ci, Co, R, Kc] complex
+__global__ void __launch_bounds__(256) mix_wgrad_kernel(const float2* __restrict__ X, const float2* __restrict__ dY, float2* __restrict__ dW, int B,
+                                                        int Ci, int Co, int R, int Kc) {
+  const int m = blockIdx.x, r = m / Kc, k = m - r * Kc;
+  for (int e = threadIdx.x; e < Ci * Co; e += 256) {
+    const int i = e / Co, o = e - i * Co;
+    float2 acc = make_float2(0.f, 0.f);
+    for (int b = 0; b < B; ++b) {
+      const float2 x = X[((long long)m * B + b) * Ci + i], g = dY[((long long)m * B + b) * Co + o];
+      acc.x += x.x * g.x + x.y * g.y;      // conj(x) * g
+      acc.y += x.x * g.y - x.y * g.x;
+    }
+    dW[(((long long)i * Co + o) * R + r) * Kc + k] = acc;
+  }
+}
+
+}  // namespace
+}  // namespace dlwp
+
+using namespace dlwp;
+
+namespace dlwp {
+namespace {
+inline size_t up256t(size_t v) { return (v + 255) & ~(size_t)255; }
+
+struct SpecTrain {
+  SpecChain c;
+  float2 *GwH = nullptr, *GhH = nullptr, *FhH = nullptr, *FwH = nullptr, *WmH = nullptr;
+  size_t total = 0;
+  int layout(int batch, int Ci, int Co, int H, int W, int R, int Kc, const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
+             unsigned char* base, const char* who) {
+    c.B = batch; c.Ci = Ci; c.Co = Co; c.H = H; c.W = W; c.R = R; c.Kc = Kc;
+    DLWP_TRY(c.check(rows_in, rows_out, fft_norm, who));
+    size_t off = c.carve(base);
+    const size_t sizes[5] = {(size_t)Kc * W * 8, (size_t)R * H * 8, (size_t)H * R * 8, (size_t)W * Kc * 8, (size_t)Ci * Co * R * Kc * 8};
+    float2** dst[5] = {&GwH, &GhH, &FhH, &FwH, &WmH};
+    for (int i = 0; i < 5; ++i) {
+      *dst[i] = reinterpret_cast<float2*>(base ? base + off : nullptr);
+      off += up256t(sizes[i]);
+    }
+    total = off;
+    return DLWP_OK;
+  }
+};
+}  // namespace
+}  // namespace dlwp
+
+extern "C" int dlwp_linear_forward(const float* x, const float* W, const float* b, const float* pre, float* y, float* z, int P, int K,
+                                   int N, int act, void* stream) {
+  if (!x || !W || !y) return fail(DLWP_ERR_INVALID, "dlwp_linear_forward: null argument");
+  PwArgs a{};
+  a.in = x; a.Wt = W; a.bias = b; a.out = y; a.P = P; a.K = K; a.N = N; a.tokens = P; a.p1 = a.p2 = 1;
+  a.act = act; a.pre = pre; a.preact = z;
+  return launch_pw_linear(a, (cudaStream_t)stream);
+}
+
+extern "C" int dlwp_linear_backward(const float* dy, const float* z, const float* x, const float* W, float* dz, float* dx, float* dW,
+                                    float* db, float* wt_scratch, int P, int K, int N, int act, void* stream) {
+  if (!dy || !x || !W || !dz || !dW) return fail(DLWP_ERR_INVALID, "dlwp_linear_backward: null argument");
+  DLWP_REQUIRE(act == 0 || z != nullptr, "dlwp_linear_backward: the pre-activation values are needed for the GELU derivative");
+  DLWP_REQUIRE(dx == nullptr || wt_scratch != nullptr, "dlwp_linear_backward: dx needs the [K, N] weight scratch");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n = (long long)P * N;
+  act_backward_kernel<<<(unsigned)((n + 1023) / 1024 < 148 * 8 ? (n + 1023) / 1024 : 148 * 8), 256, 0, st>>>(dy, z, dz, n, act);
+  DLWP_LAUNCHED("act_backward_kernel");
+  if (dx != nullptr) {      // dx[p, k] = sum_n dz[p, n] W[n, k]
+    transpose_small_kernel<<<ceil_div(N * K, 256), 256, 0, st>>>(W, wt_scratch, N, K);
+    DLWP_LAUNCHED("transpose_small_kernel");
+    PwArgs a{};
+    a.in = dz; a.Wt = wt_scratch; a.out = dx; a.P = P; a.K = N; a.N = K; a.tokens = P; a.p1 = a.p2 = 1;
+    DLWP_TRY(launch_pw_linear(a, st));
+  }
+  DLWP_CUDA(cudaMemsetAsync(dW, 0, (size_t)N * K * sizeof(float), st));
+  if (db) DLWP_CUDA(cudaMemsetAsync(db, 0, (size_t)N * sizeof(float), st));
+  const int tiles = ceil_div(N, WG_T) * ceil_div(K, WG_T);
+  int nsplit = ceil_div(148 * 4, tiles);
+  const int max_split = ceil_div(P, 4 * WG_P);
+  if (nsplit > max_split) nsplit = max_split;
+  if (nsplit < 1) nsplit = 1;
+  int per = ceil_div(ceil_div(P, nsplit), WG_P) * WG_P;
+  nsplit = ceil_div(P, per);
+  linear_wgrad_kernel<<<dim3((unsigned)ceil_div(N, WG_T), (unsigned)ceil_div(K, WG_T), (unsigned)nsplit), 256, 0, st>>>(dz, x, dW, db, P, K, N, per);
+  DLWP_LAUNCHED("linear_wgrad_kernel");
+  return DLWP_OK;
+}
+
+extern "C" int dlwp_spectral_train_workspace(int batch, int Ci, int Co, int H, int W, int n_rows, int n_cols, size_t* bytes) {
+  if (!bytes) return fail(DLWP_ERR_INVALID, "dlwp_spectral_train_workspace: null argument");
+  SpecTrain t;
+  int32_t rows[kSpecMaxRows] = {0};
+  DLWP_REQUIRE(n_rows >= 1 && n_rows <= kSpecMaxRows, "dlwp_spectral_train_workspace: n_rows=%d outside [1, %d]", n_rows, kSpecMaxRows);
+  DLWP_TRY(t.layout(batch, Ci, Co, H, W, n_rows, n_cols, rows, rows, DLWP_FFT_NORM_FORWARD, nullptr, "dlwp_spectral_train_workspace"));
+  *bytes = t.total;
+  return DLWP_OK;
+}
+
+extern "C" int dlwp_spectral_forward(const float* x, const float* weight, float* y, int batch, int Ci, int Co, int H, int W, int n_rows,
+                                     int n_cols, const int32_t* rows_in, const int32_t* rows_out, int fft_norm, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+  if (!x || !weight || !y || !rows_in || !rows_out || !workspace) return fail(DLWP_ERR_INVALID, "dlwp_spectral_forward: null argument");
+  SpecTrain t;
+  DLWP_TRY(t.layout(batch, Ci, Co, H, W, n_rows, n_cols, rows_in, rows_out, fft_norm, static_cast<unsigned char*>(workspace), "dlwp_spectral_forward"));
+  DLWP_REQUIRE(workspace_bytes >= t.total, "dlwp_spectral_forward: workspace of %zu bytes, %zu needed", workspace_bytes, t.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  DLWP_TRY(t.c.bases(st));
+  DLWP_TRY(launch_pack_modes(reinterpret_cast<const float2*>(weight), t.c.wm, Ci, Co, n_rows, n_cols, st));
+  return t.c.run(x, y, nullptr, nullptr, nullptr, 0, st);
+}
+
+extern "C" int dlwp_spectral_backward(const float* x, const float* weight, const float* dy, float* dx, float* dweight, int batch, int Ci,
+                                      int Co, int H, int W, int n_rows, int n_cols, const int32_t* rows_in, const int32_t* rows_out,
+                                      int fft_norm, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!x || !weight || !dy || !dweight || !rows_in || !rows_out || !workspace)
+    return fail(DLWP_ERR_INVALID, "dlwp_spectral_backward: null argument");
+  SpecTrain t;
+  DLWP_TRY(t.layout(batch, Ci, Co, H, W, n_rows, n_cols, rows_in, rows_out, fft_norm, static_cast<unsigned char*>(workspace), "dlwp_spectral_backward"));
+  DLWP_REQUIRE(workspace_bytes >= t.total, "dlwp_spectral_backward: workspace of %zu bytes, %zu needed", workspace_bytes, t.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  SpecChain& c = t.c;
+  const int B = batch, R = n_rows, Kc = n_cols;
+  const long long HW = (long long)H * W, K = Kc;
+  DLWP_TRY(c.bases(st));
+  adjoint_bases_kernel<<<ceil_div(2 * Kc * W + 2 * R * H, 256), 256, 0, st>>>(c.Fw, c.Fh, c.Gh, c.Gw, t.GwH, t.GhH, t.FhH, t.FwH, H, W, R, Kc);
+  DLWP_LAUNCHED("adjoint_bases_kernel");
+  // forward spectrum of x on the retained modes (recomputed, not saved): A = Fw x, X = Fh A
+  TdftArgs a{};
+  a.in = x; a.out = c.A; a.T = c.Fw; a.N = W; a.K = Kc; a.C = Ci; a.nb0 = B; a.nb1 = H;
+  a.in_sn = Ci; a.in_sb0 = HW * Ci; a.in_sb1 = (long long)W * Ci;
+  a.out_sk = Ci; a.out_sb0 = (long long)H * K * Ci; a.out_sb1 = K * Ci;
+  a.in_complex = false; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  a = TdftArgs{};
+  a.in = c.A; a.out = c.X; a.T = c.Fh; a.N = H; a.K = R; a.C = Ci; a.nb0 = B; a.nb1 = Kc;
+  a.in_sn = K * Ci; a.in_sb0 = (long long)H * K * Ci; a.in_sb1 = Ci;
+  a.out_sk = K * B * Ci; a.out_sb0 = Ci; a.out_sb1 = (long long)B * Ci;
+  a.in_complex = true; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  // adjoint of y = Re(Gw Z):  dZ = Gw^H dy   (real -> complex along W)
+  a = TdftArgs{};
+  a.in = dy; a.out = c.Z; a.T = t.GwH; a.N = W; a.K = Kc; a.C = Co; a.nb0 = B; a.nb1 = H;
+  a.in_sn = Co; a.in_sb0 = HW * Co; a.in_sb1 = (long long)W * Co;
+  a.out_sk = Co; a.out_sb0 = (long long)H * K * Co; a.out_sb1 = K * Co;
+  a.in_complex = false; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  // adjoint of Z = Gh Y:  dY = Gh^H dZ
+  a = TdftArgs{};
+  a.in = c.Z; a.out = c.Y; a.T = t.GhH; a.N = H; a.K = R; a.C = Co; a.nb0 = B; a.nb1 = Kc;
+  a.in_sn = K * Co; a.in_sb0 = (long long)H * K * Co; a.in_sb1 = Co;
+  a.out_sk = K * B * Co; a.out_sb0 = Co; a.out_sb1 = (long long)B * Co;
+  a.in_complex = true; a.out_complex = true;
+  DLWP_TRY(launch_tdft(a, st));
+  // weight gradient: dW[i, o, mode] = sum_b conj(X[mode, b, i]) dY[mode, b, o]   (dense layout of the reference, real view)
+  mix_wgrad_kernel<<<R * Kc, 256, 0, st>>>(c.X, c.Y, reinterpret_cast<float2*>(dweight), B, Ci, Co, R, Kc);
+  DLWP_LAUNCHED("mix_wgrad_kernel");
+  if (dx != nullptr) {
+    // adjoint of the mode mixing: dX[b, i] = sum_o conj(W[i, o]) dY[b, o]
+    const long long total = (long long)Ci * Co * R * Kc;
+    pack_modes_adjoint_kernel<<<(unsigned)(ceil_div64(total, 256) < 148 * 16 ? ceil_div64(total, 256) : 148 * 16), 256, 0, st>>>(
+        reinterpret_cast<const float2*>(weight), t.WmH, Ci, Co, R, Kc);
+    DLWP_LAUNCHED("pack_modes_adjoint_kernel");
+    DLWP_TRY(launch_mix_dense(c.Y, t.WmH, c.X, R * Kc, B, Co, Ci, st));
+    // adjoint of X = Fh A:  dA = Fh^H dX
+    a = TdftArgs{};
+    a.in = c.X; a.out = c.A; a.T = t.FhH; a.N = R; a.K = H; a.C = Ci; a.nb0 = B; a.nb1 = Kc;
+    a.in_sn = K * B * Ci; a.in_sb0 = Ci; a.in_sb1 = (long long)B * Ci;
+    a.out_sk = K * Ci; a.out_sb0 = (long long)H * K * Ci; a.out_sb1 = Ci;
+    a.in_complex = true; a.out_complex = true;
+    DLWP_TRY(launch_tdft(a, st));
+    // adjoint of A = Fw x (x real):  dx = Re(Fw^H dA)
+    a = TdftArgs{};
+    a.in = c.A; a.out = dx; a.T = t.FwH; a.N = Kc; a.K = W; a.C = Ci; a.nb0 = B; a.nb1 = H;
+    a.in_sn = Ci; a.in_sb0 = (long long)H * K * Ci; a.in_sb1 = K * Ci;
+    a.out_sk = Ci; a.out_sb0 = HW * Ci; a.out_sb1 = (long long)W * Ci;
+    a.in_complex = true; a.out_complex = false;
+    DLWP_TRY(launch_tdft(a, st));
+  }
+  return DLWP_OK;
+}
+
+extern "C" int dlwp_nchw_to_nhwc(const float* in, float* out, int B, int C, int HW, void* stream) {
+  if (!in || !out) return fail(DLWP_ERR_INVALID, "dlwp_nchw_to_nhwc: null argument");
+  return launch_nchw_to_nhwc(in, out, B, C, HW, (cudaStream_t)stream);
+}
+extern "C" int dlwp_nhwc_to_nchw(const float* in, float* out, int B, int C, int HW, void* stream) {
+  if (!in || !out) return fail(DLWP_ERR_INVALID, "dlwp_nhwc_to_nchw: null argument");
+  return launch_nhwc_to_nchw(in, out, B, C, HW, (cudaStream_t)stream);
+}

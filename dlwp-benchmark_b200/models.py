@@ -65,10 +65,9 @@ class _NativeRollout(nn.Module):
     def _check(self, constants, prescribed, prognostic):
         if prognostic is None or prognostic.dim() != 5:
             raise ValueError("prognostic must be a [B, T, C, H, W] tensor")
-        if torch.is_grad_enabled() and (any(p.requires_grad for p in self.parameters()) or any(
-                t is not None and t.requires_grad for t in (constants, prescribed, prognostic))):
+        if self._needs_grad(constants, prescribed, prognostic) and not self._trainable:
             raise NotImplementedError(
-                "dlwp_benchmark_b200 implements the forward (rollout) pass only; call it under "
+                "this model family has a forward (rollout) pass only in dlwp_benchmark_b200; call it under "
                 "torch.no_grad() / torch.inference_mode() as scripts/evaluate.py:205 does")
         B, T, Cg, H, W = prognostic.shape
         if T <= self.context_size:
@@ -85,6 +84,13 @@ class _NativeRollout(nn.Module):
                 raise ValueError(f"{name} has shape {tuple(t.shape)}, expected {(B, frames, ch, H, W)}")
         return B, T, Cg, H, W
 
+    # training (scripts/train.py:263-271): FNO2DModule / TFNO2DModule route to training.py under grad mode
+    _trainable = False
+
+    def _needs_grad(self, *tensors):
+        return torch.is_grad_enabled() and (any(p.requires_grad for p in self.parameters()) or any(
+            t is not None and t.requires_grad for t in tensors))
+
     @staticmethod
     def _f32c(t):
         return None if t is None else t.to(torch.float32).contiguous()
@@ -96,6 +102,10 @@ class _NativeRollout(nn.Module):
             raise native.NativeError("inputs must live on a CUDA device (no CPU fallback); "
                                      "use forward_host() for host buffers")
         dev = prognostic.device
+        if self._needs_grad(constants, prescribed, prognostic):      # autograd path on the fp32 training primitives
+            from . import training
+            with torch.cuda.device(dev):
+                return training.fno_rollout(self, constants, prescribed, prognostic)
         with torch.cuda.device(dev):
             plan = self._plan_for(dev, B, H, W)
             c, p, g = self._f32c(constants), self._f32c(prescribed), self._f32c(prognostic)
@@ -109,6 +119,8 @@ class _NativeRollout(nn.Module):
         B, T, Cg, H, W = self._check(constants, prescribed, prognostic)
         if prognostic.device.type != "cpu":
             raise ValueError("forward_host takes host tensors")
+        if self._needs_grad(constants, prescribed, prognostic):
+            raise NotImplementedError("forward_host is the inference entry: call it under torch.no_grad()")
         dev = torch.device(device) if device is not None else next(self.parameters()).device
         if dev.type != "cuda":
             raise native.NativeError("move the module to a CUDA device first (no CPU fallback)")
@@ -123,8 +135,12 @@ class _NativeRollout(nn.Module):
 
     def backbone(self, x: torch.Tensor) -> torch.Tensor:
         """One model evaluation on a prepared input ``[B, Cin, H, W]`` (``self.fno(x_t)``)."""
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            raise NotImplementedError("forward-only: call under torch.no_grad()")
+        if self._needs_grad(x):
+            if not self._trainable:
+                raise NotImplementedError("forward-only: call under torch.no_grad()")
+            from . import training
+            with torch.cuda.device(x.device):
+                return training.fno_backbone(self, x)
         B, _, H, W = x.shape
         with torch.cuda.device(x.device):
             plan = self._plan_for(x.device, B, H, W)
@@ -235,6 +251,7 @@ class FNO2DModule(_NativeRollout):
     keys (``type``, ``name``) are absorbed by ``**kwargs`` exactly as there."""
 
     _factorization = None
+    _trainable = True
 
     def __init__(self, n_modes: list = [12, 12], constant_channels: int = 4, prescribed_channels: int = 1,
                  prognostic_channels: int = 8, hidden_channels: int = 32, lifting_channels: int = 256,

@@ -71,6 +71,13 @@ SYMBOLS = {
                                               C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, _P]),
     "dlwp_fourier_residual_block_workspace": (C.c_int, [C.c_int] * 7 + [C.POINTER(C.c_size_t)]),
     "dlwp_fourier_residual_block": (C.c_int, [_P, C.POINTER(FrbWeights), _P] + [C.c_int] * 7 + [_P, C.c_size_t, _P]),
+    "dlwp_linear_forward": (C.c_int, [_P] * 6 + [C.c_int] * 4 + [_P]),
+    "dlwp_linear_backward": (C.c_int, [_P] * 9 + [C.c_int] * 4 + [_P]),
+    "dlwp_spectral_train_workspace": (C.c_int, [C.c_int] * 7 + [C.POINTER(C.c_size_t)]),
+    "dlwp_spectral_forward": (C.c_int, [_P] * 3 + [C.c_int] * 7 + [C.POINTER(C.c_int32)] * 2 + [C.c_int, _P, C.c_size_t, _P]),
+    "dlwp_spectral_backward": (C.c_int, [_P] * 5 + [C.c_int] * 7 + [C.POINTER(C.c_int32)] * 2 + [C.c_int, _P, C.c_size_t, _P]),
+    "dlwp_nchw_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
+    "dlwp_nhwc_to_nchw": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_launch_count": (C.c_int64, []),
     "dlwp_selftest_umma": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_selftest_umma_bmn": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),

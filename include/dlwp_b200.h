@@ -214,6 +214,34 @@ int dlwp_fourier_residual_block_workspace(int batch, int Ci, int Co, int H, int 
 int dlwp_fourier_residual_block(const float* x, const dlwp_frb_weights* w, float* y, int batch, int Ci, int Co, int H, int W,
                                 int modes1, int modes2, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- training primitives (scripts/train.py:263-271 back-propagates through the model) ----------------------
+ * fp32 kernel set, channels-last activations [P = B*H*W, C]; dlwp_benchmark_b200/training.py wraps them in
+ * torch.autograd.Function objects.  None of them allocates or synchronises.
+ *
+ * y = act(x W^T + b + pre), act 0 = none, 1 = exact GELU (neuralop MLP 1x1 convolutions, the FNO skip convolution with the
+ * spectral branch as `pre`, fno_blocks epilogue).  x [P, K], W [N, K], b [N] | NULL, pre [P, N] | NULL, y [P, N];
+ * z [P, N] | NULL receives the pre-activation values (saved for the backward pass). */
+int dlwp_linear_forward(const float* x, const float* W, const float* b, const float* pre, float* y, float* z, int P, int K, int N,
+                        int act, void* stream);
+/* dz = dy * act'(z) (also the gradient of `pre`), dx = dz W (skipped when dx is NULL), dW = dz^T x, db = column sums of dz
+ * (NULL: no bias).  wt_scratch: [K, N] floats (needed for dx). */
+int dlwp_linear_backward(const float* dy, const float* z, const float* x, const float* W, float* dz, float* dx, float* dW, float* db,
+                         float* wt_scratch, int P, int K, int N, int act, void* stream);
+/* The dense Fourier layer y = irfft2(mix(rfft2(x)[bins])) (unet.py:15-69 / neuralop SpectralConv, no bias) on channels-last
+ * tensors x [B, H, W, Ci] -> y [B, H, W, Co]; weight: complex (real view) [Ci, Co, n_rows, n_cols, 2].  backward: the adjoint of
+ * the truncated-DFT chain gives dx (NULL: skipped), dweight[i, o, mode] = sum_b conj(X[mode, b, i]) dY[mode, b, o] in the
+ * weight's own layout.  workspace: dlwp_spectral_train_workspace bytes (device, 256-byte aligned). */
+int dlwp_spectral_train_workspace(int batch, int Ci, int Co, int H, int W, int n_rows, int n_cols, size_t* bytes);
+int dlwp_spectral_forward(const float* x, const float* weight, float* y, int batch, int Ci, int Co, int H, int W, int n_rows,
+                          int n_cols, const int32_t* rows_in, const int32_t* rows_out, int fft_norm, void* workspace,
+                          size_t workspace_bytes, void* stream);
+int dlwp_spectral_backward(const float* x, const float* weight, const float* dy, float* dx, float* dweight, int batch, int Ci, int Co,
+                           int H, int W, int n_rows, int n_cols, const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
+                           void* workspace, size_t workspace_bytes, void* stream);
+/* layout changes between the reference's NCHW tensors and the channels-last form above */
+int dlwp_nchw_to_nhwc(const float* in, float* out, int B, int C, int HW, void* stream);
+int dlwp_nhwc_to_nchw(const float* in, float* out, int B, int C, int HW, void* stream);
+
 /* Number of kernels this library has launched in this process (for bench "gpu_launches"). */
 int64_t dlwp_launch_count(void);
 
