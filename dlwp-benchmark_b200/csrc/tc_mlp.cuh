@@ -178,17 +178,18 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
     TRE(nc, 1);
     tc_fence_after();
+    // both 16-column chunks of the pass with one tensor-memory round trip; the accumulator is released at once
+    uint32_t rr[2][16];
+    TRE(nc, 2);
+    tmem_ld16(tmem_lane + 64u * db, rr[0]);
+    tmem_ld16(tmem_lane + 64u * db + 32u, rr[1]);
+    tmem_ld_wait();
+    TRE(nc, 3);
+    tc_fence_before();
+    mbar_arrive(&b[MB_D1EMPTY + db]);
 #pragma unroll
     for (int j = 0; j < 2; ++j, ++nc) {
-      uint32_t r[16];
-      TRE(nc, 2);
-      tmem_ld16(tmem_lane + 64u * db + 32u * j, r);
-      tmem_ld_wait();
-      TRE(nc, 3);
-      if (j == 1) {
-        tc_fence_before();
-        mbar_arrive(&b[MB_D1EMPTY + db]);
-      }
+      uint32_t (&r)[16] = rr[j];
       uint32_t h[8], l[8];
       {
         if (sB1 != nullptr) {

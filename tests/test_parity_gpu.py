@@ -175,8 +175,9 @@ def test_fno_rollout_tracks_oracle_rmse_curve(pkg, case, steps):
 
 
 # tensor-core mode (DLWP_PREC_FP32_TC): split-bf16 products on tcgen05, same 1e-4 bound
-@pytest.mark.parametrize("case,steps", [("C2", 1), ("C1", 1), ("C2", 20), ("C1", 50)])
+@pytest.mark.parametrize("case,steps", [("C2", 1), ("C1", 1), ("C2", 20), ("C1", 50), ("C1b", 12)])
 def test_fno_tensor_core_path_matches_oracle(pkg, case, steps):
+    # (C1b: context_size 10 -- ten input channels gathered from ground-truth frames and the model's own outputs, fno.py:89-100)
     from dlwp_benchmark_b200 import native
     ref, mod, kw, (B, H, W) = _fno_pair(pkg, case)
     mod.precision = native.PREC_FP32_TC
