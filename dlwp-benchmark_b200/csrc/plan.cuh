@@ -92,6 +92,11 @@ struct dlwp_plan {
   bool atc_wtc = false;                                 // the token mixer's W-DFTs run on tcgen05 (afno_fwd_tc / afno_inv_tc)
   int atc_RT = 0, atc_KZ = 0;                           // grid rows per 128-token tile; K extent of the inverse operand
   uint8_t *atc_F = nullptr, *atc_G = nullptr;           // forward / inverse W-DFT operand images
+  bool atc_mid2 = false;                                // H-DFT + block MLP + inverse H-DFT on tcgen05 (afno_mid_tc_kernel)
+  uint8_t *atc_midF = nullptr, *atc_midG = nullptr;     // its Fs / Gs operand images
+  std::vector<uint8_t*> atc_midW1, atc_midW2;           // per block: (re|im)-stacked filter weights, operand images per channel block
+  std::vector<float*> atc_midb;                         // per block: filter biases b1 | b2 in accumulator column order
+  uint8_t* atc_Zimg = nullptr;                          // Z' operand images per 128-token tile (the A images overlay specA)
 
   // host-entry staging (dlwp_rollout_host)
   void* stage[4] = {nullptr, nullptr, nullptr, nullptr};

@@ -444,12 +444,30 @@ __global__ void __launch_bounds__(kFwCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
         const int h2 = row / (2 * a.Kc), rem = row - h2 * 2 * a.Kc, kx = rem >> 1, reim = rem & 1;
         const int grow = tile * a.RT + h2, bb = grow / a.H, h = grow - bb * a.H;
         float4* dst = reinterpret_cast<float4*>(a.A + ((((size_t)bb * a.Kc + kx) * a.H + h) * 2 + reim) * kAfnoE);
+        // operand-image form (afno_mid_tc_kernel): K row k = 2h + (re|im) of the column's image, 16 bytes per channel octet;
+        // the (re, im) rows of a mode sit on adjacent lanes: whole 32-byte sectors per store
+        const uint32_t ostride = (uint32_t)a.H * 32u;      // 2H K rows x 16 bytes
+        uint8_t* idst = a.Aimg + ((size_t)bb * a.Kc + kx) * (8u * ostride) + (size_t)(2 * h + reim) * 16;
+        const size_t ilo = (size_t)a.ncols * (8u * ostride);
 #pragma unroll
         for (int qc = 0; qc < 4; ++qc) {      // 16 columns at a time: the next tile's tokens are live in registers
           uint32_t r[16];
           tmem_ld16(tmem_s + ((uint32_t)(q4 * 32) << 16) + 64u * g + 16u * qc, r);
           tmem_ld_wait();
-          if (row < rows_used) {
+          if (a.Aimg != nullptr) {
+            if (row < rows_used) {
+#pragma unroll
+              for (int o2 = 0; o2 < 2; ++o2) {
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                  split2p(make_float2(__uint_as_float(r[8 * o2 + 2 * e]), __uint_as_float(r[8 * o2 + 2 * e + 1])), hi[e], lo[e]);
+                uint8_t* d = idst + (size_t)(2 * qc + o2) * ostride;
+                *reinterpret_cast<uint4*>(d) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(d + ilo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+              }
+            }
+          } else if (row < rows_used) {
 #pragma unroll
             for (int j = 0; j < 4; ++j)
               dst[4 * qc + j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
@@ -555,23 +573,32 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArg
       mbar_arrive_expect_tx_p(leader, &b[IB_XFULL + s], 32768u);
       bulk_g2s_p(leader, smem + L.X + s * 32768, a.x + (size_t)tile * kTcTile * kAfnoE, 32768u, &b[IB_XFULL + s]);
     };
+    // ready operand images (afno_mid_tc_kernel): straight into the operand buffers, no conversion by the workers
+    const bool zimg = a.Zimg != nullptr;
+    auto load_zi = [&](int tile, int s) {
+      mbar_arrive_expect_tx_p(leader, &b[IB_ZRFULL + s], (uint32_t)L.zimg_bytes);
+      bulk_g2s_p(leader, smem + L.Zimg + s * L.zimg_bytes, a.Zimg + (size_t)tile * L.zimg_bytes, (uint32_t)L.zimg_bytes, &b[IB_ZRFULL + s]);
+    };
     for (int i = 0; i < 2; ++i)
       if (first + i * stride < a.ntiles) {
-        load_z(first + i * stride, i);
+        if (zimg) load_zi(first + i * stride, i);
+        else load_z(first + i * stride, i);
         load_x(first + i * stride, i);
       }
     mbar_wait(&b[IB_CONST], 0);
-    const uint32_t idesc = idesc_bf16(128, 64);
+    const uint32_t idesc = idesc_bf16(128, 64) | (zimg ? kIdescBMnMajor : 0u);
     const uint64_t dG = chunk_desc(smem_u32(smem + L.G), 128, 0);
     const uint32_t g_lo = 128u * (uint32_t)a.KZ * 2u, z_lo = (uint32_t)kAfnoE * (uint32_t)a.KZ * 2u;
+    const uint32_t zstep = zimg ? 256u : 2048u;      // bytes per K step of 16: MN-major K rows of 16 bytes / K-major chunks of 64 rows
     uint32_t u = 0;
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       const uint32_t ph = (u >> 1) & 1u;
-      mbar_wait(&b[IB_ZIFULL + s], ph);
+      mbar_wait(&b[(zimg ? IB_ZRFULL : IB_ZIFULL) + s], ph);
       mbar_wait(&b[IB_DEMPTY + s], ph ^ 1u);
       tc_fence_after();
-      const uint64_t dZ = chunk_desc(smem_u32(smem + L.Zimg + s * L.zimg_bytes), kAfnoE, 0);
+      const uint32_t zaddr = smem_u32(smem + L.Zimg + s * L.zimg_bytes);
+      const uint64_t dZ = zimg ? smem_desc(zaddr, 128, (uint32_t)a.KZ * 16u) : chunk_desc(zaddr, kAfnoE, 0);
       const uint32_t d = tmem_s + 64u * s;
       uint32_t acc = 0;
 #pragma unroll
@@ -579,13 +606,18 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArg
         const uint32_t ga = term == 1 ? g_lo : 0u, zb = term == 2 ? z_lo : 0u;
 #pragma unroll 4
         for (int k0 = 0; k0 < a.KZ; k0 += 16) {
-          umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (k0 >> 3) * 1024), idesc, acc);
+          umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (k0 >> 4) * zstep), idesc, acc);
           acc = 1;
         }
       }
       umma_commit_p(leader, &b[IB_DFULL + s]);
       umma_commit_p(leader, &b[IB_ZIEMPTY + s]);
-      if (tile + 2 * stride < a.ntiles) {      // the raw Z buffer was released when the workers had converted it
+      if (zimg) {      // the other operand buffer is free when the previous tile's MMAs have completed
+        if (u >= 1 && tile + stride < a.ntiles) {
+          mbar_wait(&b[IB_ZIEMPTY + (s ^ 1)], ((u - 1) >> 1) & 1u);
+          load_zi(tile + stride, s ^ 1);
+        }
+      } else if (tile + 2 * stride < a.ntiles) {      // the raw Z buffer was released when the workers had converted it
         mbar_wait(&b[IB_ZREMPTY + s], ph);
         load_z(tile + 2 * stride, s);
       }
@@ -646,22 +678,24 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArg
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       const uint32_t ph = (u >> 1) & 1u;
-      mbar_wait(&b[IB_ZRFULL + s], ph);
-      mbar_wait(&b[IB_ZIEMPTY + s], ph ^ 1u);
-      const float2* zr = reinterpret_cast<const float2*>(smem + L.Zraw + s * L.zraw_bytes);
-      uint8_t* zi = smem + L.Zimg + s * L.zimg_bytes;
-      const uint32_t lo_off = (uint32_t)kAfnoE * (uint32_t)a.KZ * 2u;
-      for (int i = tid; i < n_el; i += kWtWork) {      // (grid row of the tile, column) x channel -> K slots (re, im) of that channel's row
-        const int hk = i >> 6, c = i & 63, k = 2 * hk;
-        uint32_t hi, lo;
-        split2p(zr[i], hi, lo);
-        uint8_t* dst = zi + (k >> 3) * (kAfnoE * 16) + c * 16 + (k & 7) * 2;
-        *reinterpret_cast<uint32_t*>(dst) = hi;
-        *reinterpret_cast<uint32_t*>(dst + lo_off) = lo;
+      if (a.Zimg == nullptr) {
+        mbar_wait(&b[IB_ZRFULL + s], ph);
+        mbar_wait(&b[IB_ZIEMPTY + s], ph ^ 1u);
+        const float2* zr = reinterpret_cast<const float2*>(smem + L.Zraw + s * L.zraw_bytes);
+        uint8_t* zi = smem + L.Zimg + s * L.zimg_bytes;
+        const uint32_t lo_off = (uint32_t)kAfnoE * (uint32_t)a.KZ * 2u;
+        for (int i = tid; i < n_el; i += kWtWork) {      // (grid row of the tile, column) x channel -> K slots (re, im) of that channel's row
+          const int hk = i >> 6, c = i & 63, k = 2 * hk;
+          uint32_t hi, lo;
+          split2p(zr[i], hi, lo);
+          uint8_t* dst = zi + (k >> 3) * (kAfnoE * 16) + c * 16 + (k & 7) * 2;
+          *reinterpret_cast<uint32_t*>(dst) = hi;
+          *reinterpret_cast<uint32_t*>(dst + lo_off) = lo;
+        }
+        mbar_arrive(&b[IB_ZREMPTY + s]);
+        fence_async_smem();
+        mbar_arrive(&b[IB_ZIFULL + s]);
       }
-      mbar_arrive(&b[IB_ZREMPTY + s]);
-      fence_async_smem();
-      mbar_arrive(&b[IB_ZIFULL + s]);
       if (prev >= 0) finish(prev, u - 1);
       prev = tile;
     }

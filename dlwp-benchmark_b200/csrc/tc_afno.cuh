@@ -85,6 +85,8 @@ struct AfnoWTcArgs {
   // forward: A [B, Kc, H, (re | im), 64] = W-DFT of LayerNorm(x)
   const uint8_t* Fimg;    // [hi | lo] images of F''[(h2, kx, re | im), (h2', w)], R = 128 rows, K = 128
   float* A;
+  uint8_t* Aimg;          // when set: instead of A, the split-bf16 operand image afno_mid_tc_kernel reads (AfnoMid2Args::Aimg)
+  int ncols;              // B * Kc (part stride of Aimg)
   // forward, first block with 1x1 patches: x is not read but computed from the NCHW sources of the step (patch embedding +
   // position embedding, fourcastnet.py:285-289,537-542) and stored to `xout`
   SrcGroup grp[4];
@@ -98,8 +100,25 @@ struct AfnoWTcArgs {
   const uint8_t* Gimg;    // [hi | lo] images of G'[(h2, w), (h2', kx, re | im)], R = 128 rows, K = KZ
   int KZ;                 // RT * Kc * 2 rounded up to a multiple of 16
   const float2* Z;        // [B, H, Kc, 64]
+  const uint8_t* Zimg;    // when set: instead of Z, ready MN-major operand images per tile (AfnoMid2Args::Zimg)
   float* out;             // [tokens, 64]
 };
+// ---- H-DFT, block MLP, inverse H-DFT on tcgen05 (tc_afno_mid.cu) ----------------------------------------
+struct AfnoMid2Args {
+  const uint8_t* Aimg;    // [hi | lo][column = b Kc + kx][8 channel octets][2H K rows k = 2h + (re|im)][8 ch] bf16: afno_fwd_tc_kernel
+  uint8_t* Zimg;          // per 128-token tile [hi | lo][8 channel octets][KZ K rows (h2, kx, re|im)][8 ch]: afno_inv_tc_kernel's operand
+  const uint8_t *Fimg, *Gimg;      // Fs / Gs [hi | lo] images, 64 rows x K = 64 (afno_mid_tc_pack_bases)
+  const uint8_t *W1img, *W2img;    // per channel block [hi | lo] images of the (re|im)-stacked weights (afno_mid_tc_pack_layer)
+  const float *b1, *b2;   // [128], column order (block, re|im, o)
+  float lambda;           // softshrink threshold
+  int ncols;              // B * Kc
+  int H, R, Kc, bs, RT, KZ;
+};
+bool afno_mid_tc_covers(int H, int R, int bs);
+int launch_afno_mid_tc(const AfnoMid2Args& a, cudaStream_t st);
+void afno_mid_tc_pack_bases(const double* Fr, const double* Fi, const double* Gr, const double* Gi, int H, int R, uint8_t* Fimg, uint8_t* Gimg);
+void afno_mid_tc_pack_layer(const float* w, const float* b, int nb, int bs, uint8_t* Wimg, float* bias);
+
 int launch_afno_fwd_tc(const AfnoWTcArgs& a, cudaStream_t st);
 int launch_afno_inv_tc(const AfnoWTcArgs& a, cudaStream_t st);
 int afno_inv_tc_smem_bytes(int RT, int Kc, int KZ);

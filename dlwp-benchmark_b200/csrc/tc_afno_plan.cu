@@ -1,6 +1,7 @@
 // Plan-side glue of the tensor-core AFNO kernels: eligibility, weight operand images
 // (reference: Block.forward / Mlp.forward, fourcastnet.py:41-57,176-193).
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "plan.cuh"
@@ -65,6 +66,42 @@ int plan_atc_build(dlwp_plan* p) {
     p->atc_RT = RT;
     p->atc_KZ = KZ;
     p->atc_wtc = true;
+    // H-DFT, block MLP and inverse H-DFT on tcgen05 where the geometry allows it (DLWP_MID_FMA=1 keeps the fp32 FMA kernel: A/B runs)
+    if (afno_mid_tc_covers(p->gh, d.n_rows, bs) && std::getenv("DLWP_MID_FMA") == nullptr) {
+      const int H = p->gh, R = d.n_rows;
+      std::vector<double> fr((size_t)R * H), fi((size_t)R * H), gr((size_t)H * R), gi2((size_t)H * R);
+      for (int j = 0; j < R; ++j)
+        for (int h = 0; h < H; ++h) {
+          long long r1 = ((long long)p->rows_in[j] * h) % H, r2 = ((long long)p->rows_out[j] * h) % H;
+          if (r1 < 0) r1 += H;
+          if (r2 < 0) r2 += H;
+          const double a1 = -2.0 * M_PI * (double)r1 / (double)H, a2 = 2.0 * M_PI * (double)r2 / (double)H;
+          fr[(size_t)j * H + h] = std::cos(a1);
+          fi[(size_t)j * H + h] = std::sin(a1);
+          gr[(size_t)h * R + j] = std::cos(a2);
+          gi2[(size_t)h * R + j] = std::sin(a2);
+        }
+      std::vector<uint8_t> fimg(16384), gimg(16384);
+      afno_mid_tc_pack_bases(fr.data(), fi.data(), gr.data(), gi2.data(), H, R, fimg.data(), gimg.data());
+      DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_midF, fimg.size()));
+      DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_midG, gimg.size()));
+      DLWP_CUDA(cudaMemcpy(p->atc_midF, fimg.data(), fimg.size(), cudaMemcpyHostToDevice));
+      DLWP_CUDA(cudaMemcpy(p->atc_midG, gimg.data(), gimg.size(), cudaMemcpyHostToDevice));
+      p->atc_midW1.assign(d.depth, nullptr);
+      p->atc_midW2.assign(d.depth, nullptr);
+      p->atc_midb.assign(d.depth, nullptr);
+      const size_t wbytes = (size_t)d.num_blocks * 2 * (2 * bs) * (2 * bs) * 2;
+      for (int i = 0; i < d.depth; ++i) {
+        DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_midW1[i], wbytes));
+        DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_midW2[i], wbytes));
+        DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_midb[i], (size_t)4 * kAfnoE * sizeof(float)));
+      }
+      // the K rows that pad an image to a multiple of 16 are never written: they stay zero
+      const size_t zbytes = (size_t)d.max_batch * p->gh / RT * 2 * KZ * 128;
+      DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_Zimg, zbytes));
+      DLWP_CUDA(cudaMemset(p->atc_Zimg, 0, zbytes));
+      p->atc_mid2 = true;
+    }
   }
   return DLWP_OK;
 }
@@ -105,6 +142,20 @@ int plan_atc_commit(dlwp_plan* p, cudaStream_t st) {
     for (float& v : w) v *= 0.5f;
     tc_pack_images(w.data(), kAfnoE, kAfnoHid, kAfnoHid, kAfnoE, kAfnoHid, img.data());
     DLWP_CUDA(cudaMemcpy(p->atc_W2[i], img.data(), img.size(), cudaMemcpyHostToDevice));
+    if (p->atc_mid2) {      // the block MLP of the filter as (re|im)-stacked operand images (fourcastnet.py:73-76,96-119)
+      const int nb = d.num_blocks, bs = kAfnoE / nb;
+      std::vector<uint8_t> wimg((size_t)nb * 2 * (2 * bs) * (2 * bs) * 2);
+      std::vector<float> bias((size_t)4 * kAfnoE);
+      DLWP_TRY(fetch(p, bname(i, ".filter.w1"), (int64_t)2 * nb * bs * bs, &w));
+      DLWP_TRY(fetch(p, bname(i, ".filter.b1"), (int64_t)2 * nb * bs, &b));
+      afno_mid_tc_pack_layer(w.data(), b.data(), nb, bs, wimg.data(), bias.data());
+      DLWP_CUDA(cudaMemcpy(p->atc_midW1[i], wimg.data(), wimg.size(), cudaMemcpyHostToDevice));
+      DLWP_TRY(fetch(p, bname(i, ".filter.w2"), (int64_t)2 * nb * bs * bs, &w));
+      DLWP_TRY(fetch(p, bname(i, ".filter.b2"), (int64_t)2 * nb * bs, &b));
+      afno_mid_tc_pack_layer(w.data(), b.data(), nb, bs, wimg.data(), bias.data() + 2 * kAfnoE);
+      DLWP_CUDA(cudaMemcpy(p->atc_midW2[i], wimg.data(), wimg.size(), cudaMemcpyHostToDevice));
+      DLWP_CUDA(cudaMemcpy(p->atc_midb[i], bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
   }
   return DLWP_OK;
 }
@@ -140,6 +191,21 @@ int atc_block_filter(dlwp_plan* p, int block, float* x, float* out, int B, cudaS
     wa.ngrp = fa.ngrp;
     for (int i = 0; i < fa.ngrp; ++i) wa.grp[i] = fa.grp[i];
     wa.Cin = fa.Cin; wa.We = fa.We; wa.be = fa.be; wa.pos = fa.pos; wa.xout = fa.xout;
+  }
+  const bool mid2 = fwd_tc && p->atc_mid2 && afno_inv_tc_smem_bytes(p->atc_RT, d.n_cols, p->atc_KZ) <= 226 * 1024;
+  if (mid2) {      // operand images between the three kernels instead of the fp32 spectra
+    wa.Aimg = reinterpret_cast<uint8_t*>(p->specA);
+    wa.ncols = B * d.n_cols;
+    wa.Zimg = p->atc_Zimg;
+    DLWP_TRY(launch_afno_fwd_tc(wa, st));
+    AfnoMid2Args m2{};
+    m2.Aimg = wa.Aimg; m2.Zimg = p->atc_Zimg; m2.Fimg = p->atc_midF; m2.Gimg = p->atc_midG;
+    m2.W1img = p->atc_midW1[block]; m2.W2img = p->atc_midW2[block];
+    m2.b1 = p->atc_midb[block]; m2.b2 = p->atc_midb[block] + 2 * kAfnoE;
+    m2.lambda = d.sparsity_threshold;
+    m2.ncols = wa.ncols; m2.H = p->gh; m2.R = d.n_rows; m2.Kc = d.n_cols; m2.bs = bs; m2.RT = p->atc_RT; m2.KZ = p->atc_KZ;
+    DLWP_TRY(launch_afno_mid_tc(m2, st));
+    return launch_afno_inv_tc(wa, st);
   }
   if (fwd_tc) DLWP_TRY(launch_afno_fwd_tc(wa, st));
   else DLWP_TRY(launch_afno_fwd(fa, st));
