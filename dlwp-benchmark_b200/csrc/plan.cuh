@@ -88,7 +88,7 @@ struct dlwp_plan {
   bool atc = false;
   bool atc_spec = false;                                // the fused token-mixer kernels (afno_fused.cu) cover the grid / modes too
   std::vector<uint8_t*> atc_W1, atc_W2;                 // per block: fc1 * diag(norm2.weight), fc2 / 2 operand images
-  std::vector<float*> atc_b1;                           // per block: fc1.bias + fc1 * norm2.bias
+  std::vector<std::vector<float>> atc_b1h, atc_b2h;     // per block, host: fc1.bias + fc1 * norm2.bias; fc2.bias (kernel parameters)
   bool atc_wtc = false;                                 // the token mixer's W-DFTs run on tcgen05 (afno_fwd_tc / afno_inv_tc)
   int atc_RT = 0, atc_KZ = 0;                           // grid rows per 128-token tile; K extent of the inverse operand
   uint8_t *atc_F = nullptr, *atc_G = nullptr;           // forward / inverse W-DFT operand images

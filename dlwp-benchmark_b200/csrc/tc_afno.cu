@@ -16,41 +16,46 @@ __device__ unsigned long long* g_trace_afno = nullptr;   // [16 tiles][8 events]
 
 // =============================================================================================
 // afno_mlp_kernel: out = x + fc2(GELU(fc1(LN(x))))  on 128-token tiles, persistent, one CTA per SM
-//   warps 0-7 : epilogue group (two threads per token: channel halves)     warp 8 : control warp
-// Both 64 KB weight operands ([hi | lo] split-bf16 images) stay in shared memory for the whole
-// kernel, which leaves room for one worker per CTA: one A1 buffer (normalised tokens, 32 KB; the
-// next tile's tokens are stored after the last first-layer MMA of this tile has read it, two passes
-// before they are needed) and a ring of four A2 buffers (32-column hidden chunks, 16 KB each), so the
-// epilogue group never waits for the second-layer MMAs of the chunks it has just handed over; the hidden
-// accumulator D1 [128 x 64] and the output accumulator D2 [128 x 64] are double-buffered in tensor memory.
-// LayerNorm: each thread holds half a token (32 channels), computes its mean and centred sum of
-// squares, and the two halves are combined with the pairwise update (exact like two passes).
+//   warps 0-7 / 8-15 : the epilogue groups of two workers (two threads per token: channel halves)
+//   warps 16 / 17    : their control warps
+// Both 64 KB weight operands ([hi | lo] split-bf16 images) stay in shared memory for the whole kernel and are
+// shared by the two workers, which take the CTA's tiles alternately: the TMEM -> GELU -> shared memory -> MMA
+// chain of one tile's four passes is a latency chain, so a second, independent tile per SM is what fills the
+// pipes (one worker: 9.4 us per tile).  What is left of shared memory is one A1 buffer (normalised tokens,
+// 32 KB; the next tile's tokens are stored after the last first-layer MMA of this tile has read it, two passes
+// before they are needed) and ONE A2 buffer (a 32-column hidden chunk, 16 KB) per worker: a chunk's store
+// waits for the second-layer MMAs of the chunk before it, which have had the chunk's GELU time to complete.
+// The hidden accumulator D1 [128 x 64] and the output accumulator D2 [128 x 64] are double-buffered in tensor
+// memory (256 columns per worker); a tile's output is taken over after the first pass of the worker's next tile.
+// LayerNorm: the two halves of a token are lanes l and l + 16 of a warp for the gather: each computes the mean and centred
+// sum of squares of its 32 channels, a shuffle brings the other half's, pairwise update (exact like two passes).
 // =============================================================================================
 namespace {
-constexpr int kAmEpi = 256, kAmCta = kAmEpi + 32, kAmCtlWarp = kAmEpi / 32;
+constexpr int kAmCta = kCta;      // 2 x 256 epilogue threads + 2 control warps
 struct AmSmem {
-  static constexpr int W1 = 0, W2 = W1 + kAfnoHid * kAfnoE * 4, A1 = W2 + kAfnoE * kAfnoHid * 4, A2 = A1 + 32768,
-                       Stats = A2 + 4 * kTileBytes, Total = Stats + 2 * 128 * 8;
-  static_assert(Total <= 226 * 1024, "afno_mlp_kernel shared memory");
+  static constexpr int W1 = 0, W2 = W1 + kAfnoHid * kAfnoE * 4, Worker = W2 + kAfnoE * kAfnoHid * 4, A1 = 0, A2 = 32768,
+                       WorkerBytes = A2 + kTileBytes, Total = Worker + 2 * WorkerBytes;
+  static_assert(Total <= 224 * 1024, "afno_mlp_kernel shared memory");
 };
 }  // namespace
 
 __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_launch_dependents();
-  __shared__ uint64_t bars[MB_PER + 1];
+  __shared__ uint64_t bars[2 * MB_PER + 1];
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform
   constexpr int hid = kAfnoHid, P = kAfnoHid / 64;
-  uint64_t* bar_const = &bars[MB_PER];
+  uint64_t* bar_const = &bars[2 * MB_PER];
 
   if (tid == 0) {
-    mlp_init_barriers(bars, kAmEpi);
+    mlp_init_barriers(bars, kEpi);
+    mlp_init_barriers(bars + MB_PER, kEpi);
     mbar_init(bar_const, 1);
     fence_mbar_init();
   }
-  if (warp == kAmCtlWarp) {
-    tmem_alloc(&tmem_s, 256);
+  if (warp == kCtlWarp) {
+    tmem_alloc(&tmem_s, 512);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -62,13 +67,16 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
     bulk_g2s(smem + AmSmem::W2, a.W2img, 65536, bar_const);
   }
   pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
-  const int stride = gridDim.x, first = blockIdx.x;
-  uint64_t* b = bars;
+  const int stride = gridDim.x * 2;
 
-  if (warp == kAmCtlWarp) {
+  if (warp >= kCtlWarp) {
     const uint32_t leader = elect_one();
-    MlpIssuer is{b, smem_u32(smem + AmSmem::A1), 32768u, smem_u32(smem + AmSmem::W1), smem_u32(smem + AmSmem::W2),
-                 smem_u32(smem + AmSmem::A2), tmem_s, hid, P, 0u, 0u, 0u, leader, 1u};
+    const int w = warp - kCtlWarp;
+    uint64_t* b = bars + w * MB_PER;
+    uint8_t* ws = smem + AmSmem::Worker + w * AmSmem::WorkerBytes;
+    MlpIssuer is{b, smem_u32(ws + AmSmem::A1), 32768u, smem_u32(smem + AmSmem::W1), smem_u32(smem + AmSmem::W2),
+                 smem_u32(ws + AmSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader, 1u};
+    const int first = blockIdx.x + w * (int)gridDim.x;      // worker 1 starts on the CTA's second tile
     mbar_wait(bar_const, 0);
     if (first < a.ntiles) is.mma1<kAfnoE>(0, 0, 0);
     uint32_t u = 0;
@@ -78,136 +86,166 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
         const uint32_t gp = u * P + p;
         if (p + 1 < P) is.mma1<kAfnoE>(u, p + 1, gp + 1);
         else if (has_next) is.mma1<kAfnoE>(u + 1, 0, gp + 1);
-        is.mma2<kAfnoE, 4>(u, p);
+        is.mma2<kAfnoE, 1>(u, p);
       }
     }
   } else {
     const EpiId id(tid);
-    const uint32_t tmem_row = tmem_s + ((uint32_t)(id.q4 * 32) << 16), tmem_lane = tmem_row + 16u * id.half;
-    float2* stats = reinterpret_cast<float2*>(smem + AmSmem::Stats);   // [half][row] = (mean, centred sum of squares)
-    const int c0 = 32 * id.half;      // this thread's 32 channels of its token
+    const int w = id.w;
+    uint64_t* b = bars + w * MB_PER;
+    uint8_t* ws = smem + AmSmem::Worker + w * AmSmem::WorkerBytes;
+    const uint32_t tmem_w = tmem_s + 256u * w, tmem_row = tmem_w + ((uint32_t)(id.q4 * 32) << 16), tmem_lane = tmem_row + 16u * id.half;
+    // gather / LayerNorm coordinates: a warp takes 8 tokens per step, lane = token t + 8 g; the thread holds channel octets
+    // g and g + 4 of its token (a load instruction touches 8 lines of 128 bytes, not 32), statistics over the four lanes
+    // of a token by shuffles (two passes like torch)
+    const int lw = (tid >> 5) & (kEpiWarps - 1), ltid = tid & (kEpi - 1), gt = lw * 8 + (tid & 7), gg = (tid >> 3) & 3;
 
     auto gather = [&](int tile, float4 (&x)[8]) {
-      const float4* src = reinterpret_cast<const float4*>(a.x + ((size_t)tile * kTcTile + id.row) * kAfnoE + c0);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) x[j] = src[j];
+      for (int st = 0; st < 2; ++st) {
+        const float4* src = reinterpret_cast<const float4*>(a.x + ((size_t)tile * kTcTile + st * 64 + gt) * kAfnoE);
+        x[4 * st] = src[2 * gg];
+        x[4 * st + 1] = src[2 * gg + 1];
+        x[4 * st + 2] = src[8 + 2 * gg];
+        x[4 * st + 3] = src[8 + 2 * gg + 1];
+      }
     };
     auto store_a1 = [&](uint32_t u, float4 (&x)[8]) {
-      // the statistics are computed here, not where the loads were issued (the loads' latency hides behind the passes in between)
+      float mean[2], rstd[2];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) asm volatile("" : "+f"(x[j].x), "+f"(x[j].y), "+f"(x[j].z), "+f"(x[j].w));
-      float s = 0.f;
+      for (int st = 0; st < 2; ++st) {
+        float s = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) s += (x[j].x + x[j].y) + (x[j].z + x[j].w);
-      const float mh = s * (1.0f / 32.0f);
-      float q = 0.f;
+        for (int j = 0; j < 4; ++j) s += (x[4 * st + j].x + x[4 * st + j].y) + (x[4 * st + j].z + x[4 * st + j].w);
+        s += __shfl_xor_sync(0xffffffffu, s, 8);
+        s += __shfl_xor_sync(0xffffffffu, s, 16);
+        mean[st] = s * (1.0f / 64.0f);
+        float q = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float d0 = x[j].x - mh, d1 = x[j].y - mh, d2 = x[j].z - mh, d3 = x[j].w - mh;
-        q = fmaf(d0, d0, q); q = fmaf(d1, d1, q); q = fmaf(d2, d2, q); q = fmaf(d3, d3, q);
+        for (int j = 0; j < 4; ++j) {
+          const float d0 = x[4 * st + j].x - mean[st], d1 = x[4 * st + j].y - mean[st], d2 = x[4 * st + j].z - mean[st], d3 = x[4 * st + j].w - mean[st];
+          q = fmaf(d0, d0, q); q = fmaf(d1, d1, q); q = fmaf(d2, d2, q); q = fmaf(d3, d3, q);
+        }
+        q += __shfl_xor_sync(0xffffffffu, q, 8);
+        q += __shfl_xor_sync(0xffffffffu, q, 16);
+        rstd[st] = rsqrtf(q * (1.0f / 64.0f) + a.eps);
       }
-      stats[id.half * 128 + id.row] = make_float2(mh, q);
-      bar_sync(1, kAmEpi);
-      const float2 o = stats[(id.half ^ 1) * 128 + id.row];
-      const float mean = 0.5f * (mh + o.x), dm = mh - o.x;
-      const float var = (q + o.y + 16.0f * dm * dm) * (1.0f / 64.0f);
-      const float rstd = rsqrtf(var + a.eps);
       mbar_wait(&b[MB_A1EMPTY], (u & 1u) ^ 1u);      // ring of depth 1
-      uint8_t* d = smem + AmSmem::A1 + (4 * id.half) * 2048 + id.row * 16;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {     // 8 channels = one 16-byte unit of the chunk-major image
-        uint32_t h[4], l[4];
-        const float4 v0 = x[2 * j], v1 = x[2 * j + 1];
-        split2p(make_float2((v0.x - mean) * rstd, (v0.y - mean) * rstd), h[0], l[0]);
-        split2p(make_float2((v0.z - mean) * rstd, (v0.w - mean) * rstd), h[1], l[1]);
-        split2p(make_float2((v1.x - mean) * rstd, (v1.y - mean) * rstd), h[2], l[2]);
-        split2p(make_float2((v1.z - mean) * rstd, (v1.w - mean) * rstd), h[3], l[3]);
-        *reinterpret_cast<uint4*>(d + j * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4*>(d + 16384 + j * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
+      for (int st = 0; st < 2; ++st) {
+        uint8_t* d = ws + AmSmem::A1 + gg * 2048 + (st * 64 + gt) * 16;      // 8 channels = one 16-byte unit of the chunk-major image
+#pragma unroll
+        for (int o = 0; o < 2; ++o) {      // octets g and g + 4
+          uint32_t h[4], l[4];
+          const float4 v0 = x[4 * st + 2 * o], v1 = x[4 * st + 2 * o + 1];
+          const float m = mean[st], r = rstd[st];
+          split2p(make_float2((v0.x - m) * r, (v0.y - m) * r), h[0], l[0]);
+          split2p(make_float2((v0.z - m) * r, (v0.w - m) * r), h[1], l[1]);
+          split2p(make_float2((v1.x - m) * r, (v1.y - m) * r), h[2], l[2]);
+          split2p(make_float2((v1.z - m) * r, (v1.w - m) * r), h[3], l[3]);
+          *reinterpret_cast<uint4*>(d + o * 8192) = make_uint4(h[0], h[1], h[2], h[3]);
+          *reinterpret_cast<uint4*>(d + 16384 + o * 8192) = make_uint4(l[0], l[1], l[2], l[3]);
+        }
       }
       fence_async_smem();
       mbar_arrive(&b[MB_A1FULL]);
     };
 
-    float4 b2v[8];      // this thread's 32 output biases
-#pragma unroll
-    for (int j = 0; j < 8; ++j) b2v[j] = __ldg(reinterpret_cast<const float4*>(a.b2 + c0) + j);
-    float4 nx[8];
+    const int first = blockIdx.x + w * (int)gridDim.x;      // worker 1 starts on the CTA's second tile
     if (first < a.ntiles) {
+      float4 nx[8];
       gather(first, nx);
       store_a1(0, nx);
     }
-    uint32_t u = 0, gp = 0, nc = 0;
-    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
-      const bool has_next = tile + stride < a.ntiles;
-      if (has_next) gather(tile + stride, nx);      // loads in flight while the first passes are processed
-      epi_mlp_tile<4>(b, id, tmem_lane, P, smem + AmSmem::A2, gp, nc, [&](int pass) {
-        if (pass == P - 2 && has_next) store_a1(u + 1, nx);
-      }, a.b1);
-      // out = x + D2 + b2 on this thread's 32 channels (x is re-read: an L2 hit)
-      const size_t off = ((size_t)tile * kTcTile + id.row) * kAfnoE + c0;
-      const float4* xr = reinterpret_cast<const float4*>(a.x + off);
-      float4 res[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) res[j] = xr[j];
-      mbar_wait(&b[MB_D2FULL + (u & 1)], full_par(u));
+    // out = x + D2 + b2.  The accumulator rows pass through the worker's A2 buffer (free once D2 is complete), 32 channels
+    // at a time: thread (row, half) writes its 128 bytes (16-byte units XOR-swizzled by the row: conflict-free), then the
+    // 256 threads of the worker add x and the bias and store with a token's 8 units on consecutive lanes: 4 lines of 128
+    // bytes per load / store instruction instead of 32 (the L1 data pipe is what bounds this kernel).
+    // Fused head (last block, 1x1 patches; fourcastnet.py:349-358): instead of storing `out`, the 8 lanes of a token reduce
+    // their share of the 64-channel dot products by shuffles, over both rounds; lane 0 adds the residual frame and writes NCHW.
+    auto finish = [&](int tile, uint32_t v_) {
+      uint8_t* stage = ws + AmSmem::A2;
+      mbar_wait(&b[MB_D2FULL + (v_ & 1)], full_par(v_));
       tc_fence_after();
-      uint32_t r[32];
-      tmem_ld32(tmem_row + 128u + 64u * (u & 1) + (uint32_t)c0, r);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&b[MB_D2EMPTY + (u & 1)]);
-      float4 v[8];
+      float hp[4][4];      // head: [row of the thread][output channel]
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float4 bb = b2v[j];
-        v[j] = make_float4(__uint_as_float(r[4 * j]) + bb.x + res[j].x, __uint_as_float(r[4 * j + 1]) + bb.y + res[j].y,
-                           __uint_as_float(r[4 * j + 2]) + bb.z + res[j].z, __uint_as_float(r[4 * j + 3]) + bb.w + res[j].w);
-      }
-      if (a.Wh == nullptr) {
-        float4* o = reinterpret_cast<float4*>(a.out + off);
+      for (int it = 0; it < 4; ++it)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = v[j];
-      } else {
-        // fused head (fourcastnet.py:349-358, 1x1 patches): each thread's half of the 64-channel dot products, the upper
-        // halves meet the lower ones in shared memory, the lower threads add the residual frame and write NCHW
-        float part[4];
+        for (int co = 0; co < 4; ++co) hp[it][co] = 0.f;
 #pragma unroll
-        for (int co = 0; co < 4; ++co) {
-          part[co] = 0.f;
-          if (co < a.Cg) {
-            const float4* wq = reinterpret_cast<const float4*>(a.Wh + co * kAfnoE + c0);
-            float acc = 0.f;
+      for (int h = 0; h < 2; ++h) {
+        if (id.half == h) {
+          uint32_t r[32];
+          tmem_ld32(tmem_row + 128u + 64u * (v_ & 1) + 32u * h, r);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(&b[MB_D2EMPTY + (v_ & 1)]);
+          uint8_t* srow = stage + id.row * 128;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 w = __ldg(wq + j);
-              acc = fmaf(v[j].x, w.x, acc); acc = fmaf(v[j].y, w.y, acc); acc = fmaf(v[j].z, w.z, acc); acc = fmaf(v[j].w, w.w, acc);
-            }
-            part[co] = acc;
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(srow + ((j ^ (id.row & 7)) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        }
+        bar_sync(1 + w, kEpi);
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int row = it * 32 + (ltid >> 3), un = ltid & 7, c = 32 * h + 4 * un;
+          const float4 d = *reinterpret_cast<const float4*>(stage + row * 128 + ((un ^ (row & 7)) << 4));
+          const size_t off = ((size_t)tile * kTcTile + row) * kAfnoE + c;
+          const float4 xv = *reinterpret_cast<const float4*>(a.x + off);
+          const float4 v = make_float4(d.x + a.b2c[c] + xv.x, d.y + a.b2c[c + 1] + xv.y, d.z + a.b2c[c + 2] + xv.z, d.w + a.b2c[c + 3] + xv.w);
+          if (a.Wh == nullptr) {
+            *reinterpret_cast<float4*>(a.out + off) = v;
+          } else {
+#pragma unroll
+            for (int co = 0; co < 4; ++co)
+              if (co < a.Cg) {
+                const float4 wv = __ldg(reinterpret_cast<const float4*>(a.Wh + co * kAfnoE + c));
+                hp[it][co] = fmaf(v.x, wv.x, fmaf(v.y, wv.y, fmaf(v.z, wv.z, fmaf(v.w, wv.w, hp[it][co]))));
+              }
           }
         }
-        float* sc = reinterpret_cast<float*>(stats);     // [4][128]; the statistics of the next tile were consumed two passes ago
-        if (id.half == 1) {
+        bar_sync(1 + w, kEpi);      // the staging rows are rewritten by the next round / the next tile's first chunk
+      }
+      if (a.Wh != nullptr) {
 #pragma unroll
-          for (int co = 0; co < 4; ++co) sc[co * 128 + id.row] = part[co];
-        }
-        bar_sync(1, kAmEpi);
-        if (id.half == 0) {
-          const long long p = (long long)tile * kTcTile + id.row;
+        for (int it = 0; it < 4; ++it) {
+          const long long p = (long long)tile * kTcTile + it * 32 + (ltid >> 3);
           const long long bb = p / a.HW, pix = p - bb * a.HW;
 #pragma unroll
           for (int co = 0; co < 4; ++co)
             if (co < a.Cg) {
-              const float lastv = a.last != nullptr ? a.last[bb * a.last_bstride + (long long)co * a.HW + pix] : 0.f;
-              a.frame[bb * a.frame_bstride + (long long)co * a.HW + pix] = part[co] + sc[co * 128 + id.row] + lastv;
+              float s = hp[it][co];
+              s += __shfl_xor_sync(0xffffffffu, s, 1);
+              s += __shfl_xor_sync(0xffffffffu, s, 2);
+              s += __shfl_xor_sync(0xffffffffu, s, 4);
+              if ((ltid & 7) == 0) {
+                const float lastv = a.last != nullptr ? a.last[bb * a.last_bstride + (long long)co * a.HW + pix] : 0.f;
+                a.frame[bb * a.frame_bstride + (long long)co * a.HW + pix] = s + lastv;
+              }
             }
         }
       }
+    };
+    uint32_t u = 0, gp = 0, nc = 0;
+    for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
+      const bool has_next = tile + stride < a.ntiles;
+      epi_mlp_tile<1>(b, id, tmem_lane, P, ws + AmSmem::A2, gp, nc, [&](int pass) {
+        if (pass == P - 2 && has_next) {      // (not prefetched over the passes: registers; the other worker runs meanwhile)
+          float4 nx[8];
+          gather(tile + stride, nx);
+          store_a1(u + 1, nx);
+        }
+      }, [&](int p, int j, uint32_t (&r)[16]) {
+        const int c = p * 64 + 32 * j + 16 * id.half;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) + a.b1c[c + e]);
+      });
+      finish(tile, u);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kAmCtlWarp) tmem_dealloc(tmem_s, 256);
+  if (warp == kCtlWarp) tmem_dealloc(tmem_s, 512);
 }
 
 int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
@@ -216,7 +254,7 @@ int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
   DLWP_TRY(ensure_dynamic_smem((const void*)afno_mlp_kernel, AmSmem::Total));
   DLWP_REQUIRE(a.ntiles > 0, "afno_mlp_kernel: empty problem");
   DLWP_REQUIRE(a.Wh == nullptr || (a.Cg >= 1 && a.Cg <= 4 && a.HW > 0 && a.frame != nullptr), "afno_mlp_kernel: bad head arguments");
-  const int grid = a.ntiles < sms ? a.ntiles : sms;
+  const int grid = a.ntiles < sms ? a.ntiles : sms;      // two workers per CTA: the second one has work when there are more tiles than CTAs
   DLWP_CUDA(launch_pdl(afno_mlp_kernel, dim3(grid), dim3(kAmCta), (size_t)AmSmem::Total, st, a));
   DLWP_LAUNCHED("afno_mlp_kernel");
   return DLWP_OK;

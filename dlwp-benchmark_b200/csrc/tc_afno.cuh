@@ -21,9 +21,11 @@ struct AfnoMlpArgs {
   const float* x;         // [tokens, 64] block input (the residual), channels-last
   float* out;             // [tokens, 64]; may alias x (each thread reads the rows it writes first)
   const uint8_t* W1img;   // fc1 * diag(gamma): [hi | lo] images, R = 256 rows, K = 64
-  const float* b1;        // [256] fc1 bias + fc1 * beta
   const uint8_t* W2img;   // fc2 / 2 (the epilogue hands on 2 gelu): [hi | lo] images, R = 64 rows, K = 256
-  const float* b2;        // [64]
+  // the biases travel as kernel parameters: warp-uniform reads from the constant bank instead of 40 global loads
+  // per thread and tile through the L1 data pipe (which is what bounds this kernel)
+  float b1c[kAfnoHid];    // fc1 bias + fc1 * beta
+  float b2c[kAfnoE];      // fc2 bias
   float eps;
   // optional fused head of the network (last block, 1x1 patches; fourcastnet.py:349-358): instead of storing
   // `out`, frame[b, co, pix] = last[b, co, pix] + sum_c out[token, c] * Wh[co, c]

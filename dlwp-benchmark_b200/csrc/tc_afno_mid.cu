@@ -33,6 +33,13 @@ namespace dlwp {
 
 using namespace tc;
 
+#ifdef DLWP_TRACE
+__device__ unsigned long long* g_trace_amid = nullptr;      // [item < 4][24] clock64 stamps of block 0: control warp 0..11, epilogue warp 0 at 12..23
+#define TRM(it, ev) do { if (g_trace_amid && blockIdx.x == 0 && (threadIdx.x & 31) == 0 && (it) < 4) g_trace_amid[(it) * 24 + (ev)] = clock64(); } while (0)
+#else
+#define TRM(it, ev) do {} while (0)
+#endif
+
 namespace {
 
 constexpr int kEpiWarps = 16;
@@ -46,7 +53,7 @@ struct Smem {      // byte offsets
                        Total = Buf + 2 * kBuf;
 };
 
-enum { MB_CONST = 0, MB_AFULL, MB_D1FULL = MB_AFULL + 2, MB_XFULL, MB_D2AFULL, MB_HFULL, MB_D2BFULL, MB_YFULL, MB_D3FULL, MB_E3DONE, MB_N };
+enum { MB_CONST = 0, MB_AFULL, MB_D1FULL = MB_AFULL + 2, MB_XFULL, MB_D2AFULL, MB_HFULL, MB_D2BFULL, MB_YFULL, MB_D3FULL, MB_N };
 constexpr uint32_t kD2Col = 256;
 
 __device__ __forceinline__ void split2p(float2 v, uint32_t& hi, uint32_t& lo) {
@@ -91,7 +98,6 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
     mbar_init(&bars[MB_D2BFULL], 1);
     mbar_init(&bars[MB_YFULL], 512);
     mbar_init(&bars[MB_D3FULL], 1);
-    mbar_init(&bars[MB_E3DONE], 512);
     fence_mbar_init();
   }
   if (warp == kEpiWarps) {
@@ -116,7 +122,9 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
     bulk_g2s(smem + Smem::W1, a.W1img, wbytes, &bars[MB_CONST]);
     bulk_g2s(smem + Smem::W2, a.W2img, wbytes, &bars[MB_CONST]);
   }
+  if (warp == kEpiWarps) TRM(0, 0);
   pdl_wait();      // Aimg comes from the previous kernel; Zimg is read by the kernel before it
+  if (warp == kEpiWarps) TRM(0, 1);
   const uint32_t tmem = tmem_s;
 
   if (warp == kEpiWarps) {
@@ -136,28 +144,33 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
     const uint32_t wblk = (uint32_t)(2 * (2 * bs) * (2 * bs) * 2), wlo = wblk / 2;      // one block's [hi | lo] images; offset of lo
     const uint32_t wchunk = (uint32_t)(2 * bs * 16);                                      // K-chunk stride of a block image
     const uint64_t dF = chunk_desc(aF, 64, 0), dG = chunk_desc(aG, 64, 0);
+    auto gemm1 = [&](uint32_t n) {      // item n (its images are in buffer n & 1) -> D1
+      mbar_wait(&bars[MB_AFULL + (n & 1u)], (n >> 1) & 1u);
+      TRM(n, 2);
+      tc_fence_after();
+      const uint64_t dA = smem_desc(smem_u32(smem + Smem::Buf + (n & 1u) * kBuf), 128, 1024);
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
+        const uint32_t fo = term == 1 ? 8192u : 0u, ao = term == 2 ? (uint32_t)kPart : 0u;
+#pragma unroll
+        for (int k0 = 0; k0 < 64; k0 += 16)
+          umma_bf16_p(leader, tmem, desc_off(dF, fo + (uint32_t)(k0 >> 3) * 1024u), desc_off(dA, ao + (uint32_t)k0 * 16u), idesc13, (term | k0) != 0);
+      }
+      umma_commit_p(leader, &bars[MB_D1FULL]);
+      TRM(n, 3);
+    };
+    if (first < nitems) {
+      if (first + stride < nitems) load(first + stride, 1);
+      gemm1(0);
+    }
     uint32_t n = 0;
     for (int item = first; item < nitems; item += stride, ++n) {
       const uint32_t par = n & 1u, s = n & 1u;
       const uint32_t aB = smem_u32(smem + Smem::Buf + s * kBuf);
-      if (item + stride < nitems) load(item + stride, s ^ 1);      // that buffer's previous item has been finished (E3DONE)
-      // GEMM 1
-      mbar_wait(&bars[MB_AFULL + s], (n >> 1) & 1u);
-      tc_fence_after();
-      {
-        const uint64_t dA = smem_desc(aB, 128, 1024);
-#pragma unroll
-        for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
-          const uint32_t fo = term == 1 ? 8192u : 0u, ao = term == 2 ? (uint32_t)kPart : 0u;
-#pragma unroll
-          for (int k0 = 0; k0 < 64; k0 += 16)
-            umma_bf16_p(leader, tmem, desc_off(dF, fo + (uint32_t)(k0 >> 3) * 1024u), desc_off(dA, ao + (uint32_t)k0 * 16u), idesc13, (term | k0) != 0);
-        }
-        umma_commit_p(leader, &bars[MB_D1FULL]);
-      }
       // GEMM 2a / 2b: one small GEMM per channel block (K = N = 2 bs) on the token-major operand
       for (int layer = 0; layer < 2; ++layer) {
         mbar_wait(&bars[layer == 0 ? MB_XFULL : MB_HFULL], par);
+        TRM(n, 4 + 2 * layer);
         tc_fence_after();
         const uint32_t aW = layer == 0 ? aW1 : aW2;
         for (int blk = 0; blk < nblk; ++blk) {
@@ -171,9 +184,11 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
           }
         }
         umma_commit_p(leader, &bars[layer == 0 ? MB_D2AFULL : MB_D2BFULL]);
+        TRM(n, 5 + 2 * layer);
       }
-      // GEMM 3
+      // GEMM 3 (its accumulator takes the columns of D2, dead by now, and the 128 after them)
       mbar_wait(&bars[MB_YFULL], par);
+      TRM(n, 8);
       tc_fence_after();
       {
         const uint64_t dY = smem_desc(aB, 128, 1024);
@@ -182,11 +197,18 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
           const uint32_t go = term == 1 ? 8192u : 0u, yo = term == 2 ? (uint32_t)kPart : 0u;
 #pragma unroll
           for (int k0 = 0; k0 < 64; k0 += 16)
-            umma_bf16_p(leader, tmem, desc_off(dG, go + (uint32_t)(k0 >> 3) * 1024u), desc_off(dY, yo + (uint32_t)k0 * 16u), idesc13, (term | k0) != 0);
+            umma_bf16_p(leader, tmem + kD2Col, desc_off(dG, go + (uint32_t)(k0 >> 3) * 1024u), desc_off(dY, yo + (uint32_t)k0 * 16u), idesc13, (term | k0) != 0);
         }
         umma_commit_p(leader, &bars[MB_D3FULL]);
+        TRM(n, 9);
       }
-      mbar_wait(&bars[MB_E3DONE], par);      // D3 shares its columns with the next item's D1
+      // the next item's GEMM 1 runs under this item's last epilogue (D1 was read long ago; the next GEMM 2a, which shares
+      // columns with D3, is ordered behind E 3 by the epilogue warps' arrival on XFULL)
+      if (item + stride < nitems) gemm1(n + 1);
+      if (item + 2 * stride < nitems) {      // this item's buffer is free when GEMM 3 has read Y
+        mbar_wait(&bars[MB_D3FULL], par);
+        load(item + 2 * stride, (int)s);
+      }
       __syncwarp();
     }
   } else {
@@ -204,6 +226,7 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
       {
         // ---- E 1: D1 row (re|im, ky) (M = 64: lanes < 16 of quarter q hold rows 16 q + lane), column j of the item: its 64 channels ----
         mbar_wait(&bars[MB_D1FULL], par);
+        if (warp == 0) TRM(n, 12);
         tc_fence_after();
         const int row = 16 * q + lane, reim = row >> 5, ky = row & 31;
         uint8_t* dst = buf + (j * 32 + ky) * 16;
@@ -224,10 +247,12 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
         tc_fence_before();
         fence_async_smem();
         mbar_arrive(&bars[MB_XFULL]);
+        if (warp == 0) TRM(n, 13);
       }
       // ---- E 2a / E 2b: lane = token 32 q + lane, accumulator columns 32 j .. 32 j + 31 = k of the next operand ----
       {
         mbar_wait(&bars[MB_D2AFULL], par);
+        if (warp == 0) TRM(n, 14);
         tc_fence_after();
         uint32_t v[32];
         tmem_ld32(tq + kD2Col + (uint32_t)(j * 32), v);
@@ -240,9 +265,11 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
         tc_fence_before();
         fence_async_smem();
         mbar_arrive(&bars[MB_HFULL]);
+        if (warp == 0) TRM(n, 15);
       }
       {
         mbar_wait(&bars[MB_D2BFULL], par);
+        if (warp == 0) TRM(n, 16);
         tc_fence_after();
         uint32_t v[32];
         tmem_ld32(tq + kD2Col + (uint32_t)(j * 32), v);
@@ -260,10 +287,12 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
         tc_fence_before();
         fence_async_smem();
         mbar_arrive(&bars[MB_YFULL]);
+        if (warp == 0) TRM(n, 17);
       }
       {
         // ---- E 3: D3 row (h, re|im) = 16 q + lane (lanes < 16), column j of the item -> K row of the Z' image of its tile ----
         mbar_wait(&bars[MB_D3FULL], par);
+        if (warp == 0) TRM(n, 18);
         tc_fence_after();
         const int row = 16 * q + lane, h = row >> 1, reim = row & 1;
         const int col = item * kCols + j, b = col / a.Kc, kx = col - b * a.Kc;
@@ -274,7 +303,7 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
-          tmem_ld32(tq + (uint32_t)(j * 64 + half * 32), v);
+          tmem_ld32(tq + kD2Col + (uint32_t)(j * 64 + half * 32), v);
           tmem_ld_wait();
           if (live) {
 #pragma unroll
@@ -282,7 +311,7 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
           }
         }
         tc_fence_before();
-        mbar_arrive(&bars[MB_E3DONE]);
+        if (warp == 0) TRM(n, 19);
       }
     }
   }
@@ -351,3 +380,9 @@ void afno_mid_tc_pack_layer(const float* w, const float* b, int nb, int bs, uint
 }
 
 }  // namespace dlwp
+
+#ifdef DLWP_TRACE
+extern "C" int dlwp_debug_set_trace_afno_mid(unsigned long long* p) {
+  return cudaMemcpyToSymbol(dlwp::g_trace_amid, &p, sizeof(p)) == cudaSuccess ? 0 : -2;
+}
+#endif

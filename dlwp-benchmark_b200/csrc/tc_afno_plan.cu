@@ -2,6 +2,7 @@
 // (reference: Block.forward / Mlp.forward, fourcastnet.py:41-57,176-193).
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "plan.cuh"
@@ -20,11 +21,11 @@ int plan_atc_build(dlwp_plan* p) {
   if ((p->gh * p->gw) % kTcTile != 0) return DLWP_OK;
   p->atc_W1.assign(d.depth, nullptr);
   p->atc_W2.assign(d.depth, nullptr);
-  p->atc_b1.assign(d.depth, nullptr);
+  p->atc_b1h.assign(d.depth, std::vector<float>());
+  p->atc_b2h.assign(d.depth, std::vector<float>());
   for (int i = 0; i < d.depth; ++i) {
     DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_W1[i], (size_t)kAfnoHid * kAfnoE * 4));
     DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_W2[i], (size_t)kAfnoE * kAfnoHid * 4));
-    DLWP_TRY(plan_dev_alloc(p, (void**)&p->atc_b1[i], (size_t)kAfnoHid * sizeof(float)));
   }
   p->atc = true;
   const int bs = d.embed_dim / d.num_blocks;
@@ -136,7 +137,8 @@ int plan_atc_commit(dlwp_plan* p, cudaStream_t st) {
     }
     tc_pack_images(w.data(), kAfnoHid, kAfnoE, kAfnoE, kAfnoHid, kAfnoE, img.data());
     DLWP_CUDA(cudaMemcpy(p->atc_W1[i], img.data(), img.size(), cudaMemcpyHostToDevice));
-    DLWP_CUDA(cudaMemcpy(p->atc_b1[i], b1.data(), b1.size() * sizeof(float), cudaMemcpyHostToDevice));
+    p->atc_b1h[i] = b1;
+    DLWP_TRY(fetch(p, bname(i, ".mlp.fc2.bias"), kAfnoE, &p->atc_b2h[i]));
     // the GELU epilogue hands 2 * gelu(hidden) to the second GEMM: its weights carry the 1/2
     DLWP_TRY(fetch(p, bname(i, ".mlp.fc2.weight"), (int64_t)kAfnoE * kAfnoHid, &w));
     for (float& v : w) v *= 0.5f;
@@ -240,9 +242,10 @@ int atc_block_mlp(dlwp_plan* p, int block, const float* x, float* out, int P, cu
   a.x = x;
   a.out = out;
   a.W1img = p->atc_W1[block];
-  a.b1 = p->atc_b1[block];
+  DLWP_REQUIRE((int)p->atc_b1h[block].size() == kAfnoHid && (int)p->atc_b2h[block].size() == kAfnoE, "afno_mlp_kernel: weights not committed");
+  std::memcpy(a.b1c, p->atc_b1h[block].data(), sizeof(a.b1c));
+  std::memcpy(a.b2c, p->atc_b2h[block].data(), sizeof(a.b2c));
   a.W2img = p->atc_W2[block];
-  DLWP_TRY(plan_need(p, bname(block, ".mlp.fc2.bias"), kAfnoE, &a.b2));
   a.eps = p->d.layernorm_eps;
   return launch_afno_mlp(a, st);
 }

@@ -159,21 +159,17 @@ struct MlpIssuer {
 
 // epilogue side of one tile's MLP; `after_pass(p)` runs after every pass p.  Each thread
 // turns 16 hidden columns of its pixel per 32-column chunk into split-bf16 operand bytes.
-// `sB1` (optional): the first layer's bias [hid] in shared memory, added here when the first GEMM
-// has no spare K column to carry it.
+// `bias(p, j, r)` (optional) adds the first layer's bias to the 16 accumulator values of chunk j of pass p, when the
+// first GEMM has no spare K column to carry it.
 // `NA2`: depth of the A2 ring.
-template <int NA2 = 2, class Hook>
+struct NoBias {
+  __device__ __forceinline__ void operator()(int, int, uint32_t (&)[16]) const {}
+};
+template <int NA2 = 2, class Hook, class Bias = NoBias>
 __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint32_t tmem_lane, int P, uint8_t* sA2,
-                                             uint32_t& gp, uint32_t& nc, Hook after_pass, const float* sB1 = nullptr) {
+                                             uint32_t& gp, uint32_t& nc, Hook after_pass, Bias bias = Bias{}) {
   for (int p = 0; p < P; ++p, ++gp) {
     const int db = gp & 1;
-    float4 bv[2][4];    // this pass's bias values: requested before the wait so that their latency hides behind it
-    if (sB1 != nullptr) {
-#pragma unroll
-      for (int j = 0; j < 2; ++j)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) bv[j][e] = __ldg(reinterpret_cast<const float4*>(sB1 + p * 64 + 32 * j + 16 * id.half) + e);
-    }
     TRE(nc, 0);
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
     TRE(nc, 1);
@@ -192,15 +188,7 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
       uint32_t (&r)[16] = rr[j];
       uint32_t h[8], l[8];
       {
-        if (sB1 != nullptr) {
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            r[4 * e] = __float_as_uint(__uint_as_float(r[4 * e]) + bv[j][e].x);
-            r[4 * e + 1] = __float_as_uint(__uint_as_float(r[4 * e + 1]) + bv[j][e].y);
-            r[4 * e + 2] = __float_as_uint(__uint_as_float(r[4 * e + 2]) + bv[j][e].z);
-            r[4 * e + 3] = __float_as_uint(__uint_as_float(r[4 * e + 3]) + bv[j][e].w);
-          }
-        }
+        bias(p, j, r);
         float2 g2[8];             // 2 * gelu: W2's operand image is packed with the factor 1/2
         gelu2x_8(r, g2);
 #pragma unroll
