@@ -280,7 +280,8 @@ constexpr int kFwGroups = 3, kFwGrp = 128, kFwWork = kFwGroups * kFwGrp, kFwCta 
 enum { WB_YFULL = 0, WB_DFULL = kFwGroups, WB_CONST = 2 * kFwGroups, WB_N = 2 * kFwGroups + 1 };
 struct FwdSmem {
   static constexpr int F = 0, Y = F + 2 * 128 * 128 * 2, GB = Y + kFwGroups * 32768, Emb = GB + 2 * kAfnoE * 4,
-                       Total = Emb + (16 * kAfnoE + kAfnoE) * 4;
+                       In = Emb + (16 * kAfnoE + kAfnoE) * 4,      // first block: the step-input channels of a group's tile [8][128]
+                       Total = In + kFwGroups * 8 * 128 * 4;
 };
 constexpr int kWtWork = 256, kWtCta = kWtWork + 32, kWtCtlWarp = kWtWork / 32;     // afno_inv_tc_kernel
 
@@ -372,99 +373,133 @@ __global__ void __launch_bounds__(kFwCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
     const int g = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;      // group, TMEM lane quarter, token of the tile = accumulator row
     const int rows_used = a.RT * 2 * a.Kc;
     const int HW = a.H * a.W;
-    uint8_t* ybase = smem + FwdSmem::Y + g * 32768 + row * 16;
+    // Token loads and LayerNorm: a warp takes 8 tokens per step (4 steps per tile), lane = token t + 8 og; the thread holds
+    // channel octets og and og + 4 of its token, so a load instruction touches 8 lines of 128 bytes (one thread per token
+    // touched 32, and the L1 data pipe is what bounds this kernel); statistics over the four lanes of a token by shuffles.
+    const int lt = q4 * 8 + (lane & 7), og = lane >> 3;      // token of step 0, octet pair
+    uint8_t* ybase = smem + FwdSmem::Y + g * 32768 + og * 2048;
 
     auto load_x = [&](int tile, float4 (&x)[16]) {
-      if (!embed) {
-        const float4* src = reinterpret_cast<const float4*>(a.x + ((size_t)tile * kTcTile + row) * kAfnoE);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) x[j] = src[j];
-      } else {
-        // first block: x = patch embedding + position embedding of the step input (fourcastnet.py:285-289,294-307);
-        // here only the loads: position embedding row into x, the token's input channels into xin
-        const long long p0 = (long long)tile * kTcTile + row;
-        const long long bb = p0 / HW, pix = p0 - bb * HW;
-#pragma unroll
-        for (int j = 0; j < 16; ++j)
-          x[j] = a.pos != nullptr ? __ldg(reinterpret_cast<const float4*>(a.pos + pix * kAfnoE) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int st = 0; st < 4; ++st) {
+        const long long p0 = (long long)tile * kTcTile + st * 32 + lt;
+        const float4* src;
+        if (!embed) {
+          src = reinterpret_cast<const float4*>(a.x + (size_t)p0 * kAfnoE);
+        } else {
+          // first block: x = patch embedding + position embedding of the step input (fourcastnet.py:285-289,294-307);
+          // here only the position embedding row
+          const long long bb = p0 / HW, pix = p0 - bb * HW;
+          src = reinterpret_cast<const float4*>(a.pos + pix * kAfnoE);
+        }
+        if (!embed || a.pos != nullptr) {
+          x[4 * st] = src[2 * og];
+          x[4 * st + 1] = src[2 * og + 1];
+          x[4 * st + 2] = src[8 + 2 * og];
+          x[4 * st + 3] = src[8 + 2 * og + 1];
+        } else {
+          x[4 * st] = x[4 * st + 1] = x[4 * st + 2] = x[4 * st + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       }
     };
-    auto load_in = [&](int tile, float (&xin)[8]) {
-      const long long p0 = (long long)tile * kTcTile + row;
-      const long long bb = p0 / HW, pix = p0 - bb * HW;
+    // first block: the input channels of the group's next tile travel global -> shared memory asynchronously (no registers
+    // held over the drain); lane (t, og) copies channels og and og + 4 of its tokens, the four lanes of a token read all
+    float* sIn = reinterpret_cast<float*>(smem + FwdSmem::In) + g * 8 * 128;
+    auto issue_in = [&](int tile) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        int ch = k;
-        float val = 0.f;
-        if (k < a.Cin) {
+      for (int st = 0; st < 4; ++st) {
+        const long long p0 = (long long)tile * kTcTile + st * 32 + lt;
+        const long long bb = p0 / HW, pix = p0 - bb * HW;
 #pragma unroll
-          for (int gi = 0; gi < 4; ++gi)
-            if (gi < a.ngrp) {
-              if (ch >= 0 && ch < a.grp[gi].nch) val = a.grp[gi].base[bb * a.grp[gi].bstride + (long long)ch * HW + pix];
-              ch -= a.grp[gi].nch;
-            }
+        for (int i = 0; i < 2; ++i) {
+          const int k = og + 4 * i;
+          int ch = k;
+          const float* src = nullptr;
+          if (k < a.Cin) {
+#pragma unroll
+            for (int gi = 0; gi < 4; ++gi)
+              if (gi < a.ngrp) {
+                if (ch >= 0 && ch < a.grp[gi].nch) src = a.grp[gi].base + bb * a.grp[gi].bstride + (long long)ch * HW + pix;
+                ch -= a.grp[gi].nch;
+              }
+          }
+          if (src != nullptr)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(sIn + k * 128 + st * 32 + lt)), "l"(src) : "memory");
         }
-        xin[k] = val;
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
     pdl_wait();   // x / the step input are what earlier kernels wrote
     float4 x[16];
-    float xin[8];      // the fused embedding takes up to 8 input channels
     const int tile0 = first + g * stride;
     if (tile0 < a.ntiles) {
       load_x(tile0, x);
-      if (embed) load_in(tile0, xin);
+      if (embed) issue_in(tile0);
     }
     uint32_t u = 0;      // this group's tiles
     for (int tile = tile0; tile < a.ntiles; tile += kFwGroups * stride, ++u) {
       if (tid == 0) TRA(u, 0);
       if (embed) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          if (k < a.Cin) {
-            const float4* wq = reinterpret_cast<const float4*>(sWe + k * kAfnoE);
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const float4 w = wq[j];
-              x[j].x = fmaf(xin[k], w.x, x[j].x); x[j].y = fmaf(xin[k], w.y, x[j].y);
-              x[j].z = fmaf(xin[k], w.z, x[j].z); x[j].w = fmaf(xin[k], w.w, x[j].w);
-            }
-          }
-        float4* xo = reinterpret_cast<float4*>(a.xout + ((size_t)tile * kTcTile + row) * kAfnoE);
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float4 bq = *reinterpret_cast<const float4*>(sBe + 4 * j);
-          x[j] = make_float4(x[j].x + bq.x, x[j].y + bq.y, x[j].z + bq.z, x[j].w + bq.w);
-          xo[j] = x[j];
-        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
       }
-      // LayerNorm of the token, two passes, thread-local
-      float sum = 0.f;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) sum += (x[j].x + x[j].y) + (x[j].z + x[j].w);
-      if (tid == 0) TRA(u, 1);
-      const float mean = sum * (1.0f / 64.0f);
-      float q = 0.f;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const float d0 = x[j].x - mean, d1 = x[j].y - mean, d2 = x[j].z - mean, d3 = x[j].w - mean;
-        q = fmaf(d0, d0, q); q = fmaf(d1, d1, q); q = fmaf(d2, d2, q); q = fmaf(d3, d3, q);
-      }
-      const float rstd = rsqrtf(q * (1.0f / 64.0f) + a.eps);
       // the group's image is free: its previous tile's accumulator has been drained, so those MMAs are complete
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {     // 8 channels = one 16-byte unit of the chunk-major image
-        const float4 ga = *reinterpret_cast<const float4*>(sGB + 8 * j), gb = *reinterpret_cast<const float4*>(sGB + 8 * j + 4);
-        const float4 ba = *reinterpret_cast<const float4*>(sGB + kAfnoE + 8 * j), bb = *reinterpret_cast<const float4*>(sGB + kAfnoE + 8 * j + 4);
-        const float4 v0 = x[2 * j], v1 = x[2 * j + 1];
-        uint32_t h[4], l[4];
-        split2p(make_float2(fmaf((v0.x - mean) * rstd, ga.x, ba.x), fmaf((v0.y - mean) * rstd, ga.y, ba.y)), h[0], l[0]);
-        split2p(make_float2(fmaf((v0.z - mean) * rstd, ga.z, ba.z), fmaf((v0.w - mean) * rstd, ga.w, ba.w)), h[1], l[1]);
-        split2p(make_float2(fmaf((v1.x - mean) * rstd, gb.x, bb.x), fmaf((v1.y - mean) * rstd, gb.y, bb.y)), h[2], l[2]);
-        split2p(make_float2(fmaf((v1.z - mean) * rstd, gb.z, bb.z), fmaf((v1.w - mean) * rstd, gb.w, bb.w)), h[3], l[3]);
-        *reinterpret_cast<uint4*>(ybase + j * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4*>(ybase + 16384 + j * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
+      for (int st = 0; st < 4; ++st) {
+        float4* xs = x + 4 * st;
+        if (embed) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (k < a.Cin) {
+              const float xk = sIn[k * 128 + st * 32 + lt];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float4 w = *reinterpret_cast<const float4*>(sWe + k * kAfnoE + (j >> 1) * 32 + og * 8 + (j & 1) * 4);
+                xs[j].x = fmaf(xk, w.x, xs[j].x); xs[j].y = fmaf(xk, w.y, xs[j].y);
+                xs[j].z = fmaf(xk, w.z, xs[j].z); xs[j].w = fmaf(xk, w.w, xs[j].w);
+              }
+            }
+          float4* xo = reinterpret_cast<float4*>(a.xout + ((size_t)tile * kTcTile + st * 32 + lt) * kAfnoE);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c4 = (j >> 1) * 8 + og * 2 + (j & 1);      // float4 index within the token
+            const float4 bq = *reinterpret_cast<const float4*>(sBe + 4 * c4);
+            xs[j] = make_float4(xs[j].x + bq.x, xs[j].y + bq.y, xs[j].z + bq.z, xs[j].w + bq.w);
+            xo[c4] = xs[j];
+          }
+        }
+        // LayerNorm of the token, two passes
+        float sum = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) sum += (xs[j].x + xs[j].y) + (xs[j].z + xs[j].w);
+        sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+        sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+        const float mean = sum * (1.0f / 64.0f);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float d0 = xs[j].x - mean, d1 = xs[j].y - mean, d2 = xs[j].z - mean, d3 = xs[j].w - mean;
+          q = fmaf(d0, d0, q); q = fmaf(d1, d1, q); q = fmaf(d2, d2, q); q = fmaf(d3, d3, q);
+        }
+        q += __shfl_xor_sync(0xffffffffu, q, 8);
+        q += __shfl_xor_sync(0xffffffffu, q, 16);
+        const float rstd = rsqrtf(q * (1.0f / 64.0f) + a.eps);
+#pragma unroll
+        for (int o = 0; o < 2; ++o) {     // octets og and og + 4: 8 channels = one 16-byte unit of the chunk-major image
+          const int c = 32 * o + 8 * og;
+          const float4 ga = *reinterpret_cast<const float4*>(sGB + c), gb = *reinterpret_cast<const float4*>(sGB + c + 4);
+          const float4 ba = *reinterpret_cast<const float4*>(sGB + kAfnoE + c), bb = *reinterpret_cast<const float4*>(sGB + kAfnoE + c + 4);
+          const float4 v0 = xs[2 * o], v1 = xs[2 * o + 1];
+          uint32_t h[4], l[4];
+          split2p(make_float2(fmaf((v0.x - mean) * rstd, ga.x, ba.x), fmaf((v0.y - mean) * rstd, ga.y, ba.y)), h[0], l[0]);
+          split2p(make_float2(fmaf((v0.z - mean) * rstd, ga.z, ba.z), fmaf((v0.w - mean) * rstd, ga.w, ba.w)), h[1], l[1]);
+          split2p(make_float2(fmaf((v1.x - mean) * rstd, gb.x, bb.x), fmaf((v1.y - mean) * rstd, gb.y, bb.y)), h[2], l[2]);
+          split2p(make_float2(fmaf((v1.z - mean) * rstd, gb.z, bb.z), fmaf((v1.w - mean) * rstd, gb.w, bb.w)), h[3], l[3]);
+          uint8_t* yd = ybase + o * 8192 + (st * 32 + lt) * 16;
+          *reinterpret_cast<uint4*>(yd) = make_uint4(h[0], h[1], h[2], h[3]);
+          *reinterpret_cast<uint4*>(yd + 16384) = make_uint4(l[0], l[1], l[2], l[3]);
+        }
       }
       fence_async_smem();
       mbar_arrive(&b[WB_YFULL + g]);
@@ -473,7 +508,10 @@ __global__ void __launch_bounds__(kFwCta, 1) afno_fwd_tc_kernel(const AfnoWTcArg
       const int next = tile + kFwGroups * stride;
       if (next < a.ntiles) {
         load_x(next, x);
-        if (embed) load_in(next, xin);
+        if (embed) {
+          __syncwarp();      // every lane of the warp has read this tile's channels
+          issue_in(next);
+        }
       }
       mbar_wait(&b[WB_DFULL + g], u & 1u);
       if (tid == 0) TRA(u, 4);
@@ -666,9 +704,11 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArg
       __syncwarp();
     }
   } else {
-    const int t4 = lane >> 3, o = lane & 7;      // phase B: token of the step, channel octet
-    const float4 g0 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o), g1 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 2 * o + 1);
-    const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o), e1 = __ldg(reinterpret_cast<const float4*>(a.beta) + 2 * o + 1);
+    // phase B: token of the step; the lane's channels 4 o .. 4 o + 3 and 32 + 4 o .. 32 + 4 o + 3 (the 8 lanes of a token read
+    // 128 contiguous bytes per access: no bank conflicts, 4 lines per global store instruction)
+    const int t4 = lane >> 3, o = lane & 7;
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(a.gamma) + o), g1 = __ldg(reinterpret_cast<const float4*>(a.gamma) + 8 + o);
+    const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.beta) + o), e1 = __ldg(reinterpret_cast<const float4*>(a.beta) + 8 + o);
     const int q4 = warp & 3, half = warp >> 2, row = q4 * 32 + lane;     // phase A: accumulator row, column half
     float* dstg = reinterpret_cast<float*>(smem + L.Dst);
     const int n_el = a.RT * a.Kc * kAfnoE;
@@ -697,15 +737,15 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArg
 #pragma unroll
       for (int st = 0; st < 4; ++st) {
         const int px = warp * 16 + st * 4 + t4;
-        const float4 x0 = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8),
-                     x1 = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 8 + 4);
-        const float4 d0 = *reinterpret_cast<const float4*>(dstg + px * kDstRow + o * 8),
-                     d1 = *reinterpret_cast<const float4*>(dstg + px * kDstRow + o * 8 + 4);
+        const float4 x0 = *reinterpret_cast<const float4*>(xs + px * kAfnoE + o * 4),
+                     x1 = *reinterpret_cast<const float4*>(xs + px * kAfnoE + 32 + o * 4);
+        const float4 d0 = *reinterpret_cast<const float4*>(dstg + px * kDstRow + o * 4),
+                     d1 = *reinterpret_cast<const float4*>(dstg + px * kDstRow + 32 + o * 4);
         float4 y0 = x0, y1 = x1;
         ln8(y0, y1, g0, g1, e0, e1, a.eps);
-        float4* op = reinterpret_cast<float4*>(orow + px * kAfnoE + o * 8);
+        float4* op = reinterpret_cast<float4*>(orow + px * kAfnoE + o * 4);
         op[0] = make_float4(d0.x + y0.x + x0.x, d0.y + y0.y + x0.y, d0.z + y0.z + x0.z, d0.w + y0.w + x0.w);
-        op[1] = make_float4(d1.x + y1.x + x1.x, d1.y + y1.y + x1.y, d1.z + y1.z + x1.z, d1.w + y1.w + x1.w);
+        op[8] = make_float4(d1.x + y1.x + x1.x, d1.y + y1.y + x1.y, d1.z + y1.z + x1.z, d1.w + y1.w + x1.w);
       }
       mbar_arrive(&b[IB_XEMPTY + s]);
       bar_sync(1, kWtWork);      // the staging rows are rewritten by the next tile's first phase
