@@ -260,7 +260,9 @@ def test_afno_paper_size_matches_oracle(pkg):
 
 
 @pytest.mark.parametrize("B,nb,frac,H,W,Cg", [(3, 4, 1.0, 32, 64, 3), (24, 4, 1.0, 32, 64, 3), (5, 8, 0.5, 16, 32, 4),
-                                               (2, 4, 0.7, 24, 48, 6)])
+                                               (2, 4, 0.7, 24, 48, 6),
+                                               # afno_mid_tc_kernel: 8 channel blocks of 8; truncated modes (16 rows x 8 columns); one sample
+                                               (4, 8, 1.0, 32, 64, 3), (2, 4, 0.5, 32, 64, 3), (1, 4, 1.0, 32, 64, 3)])
 def test_afno_tensor_core_kernels_match_oracle_and_fp32_kernel_set(pkg, B, nb, frac, H, W, Cg):
     """configs/model/fourcastnet.yaml shapes (embed_dim 64, mlp_ratio 4): the tcgen05 AFNO kernels of the
     default precision mode against the oracle and against the fp32 FMA kernel set; B = 24 gives every
