@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
         const uint32_t gp = u * P + p;
         if (p + 1 < P) is.mma1<kAfnoE>(u, p + 1, gp + 1);
         else if (has_next) is.mma1<kAfnoE>(u + 1, 0, gp + 1);
-        is.mma2<kAfnoE, 1>(u, p);
+        is.mma2<kAfnoE>(u, p);
       }
     }
   } else {
@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
     uint32_t u = 0, gp = 0, nc = 0;
     for (int tile = first; tile < a.ntiles; tile += stride, ++u) {
       const bool has_next = tile + stride < a.ntiles;
-      epi_mlp_tile<1>(b, id, tmem_lane, P, ws + AmSmem::A2, gp, nc, [&](int pass) {
+      epi_mlp_tile(b, id, tmem_lane, P, gp, nc, [&](int pass) {
         if (pass == P - 2 && has_next) {      // (not prefetched over the passes: registers; the other worker runs meanwhile)
           float4 nx[8];
           gather(tile + stride, nx);

@@ -130,6 +130,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- registers -> TMEM ----------------------------------------------------------------------
+// lane i of the warp writes TMEM lane (taddr.lane + i), 8 consecutive 32-bit columns
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+               "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 // ---- bulk async copy global -> shared (1-D TMA, no tensor map) ----------------------------------
 // bytes: multiple of 16; both addresses 16-byte aligned; completion is signalled on `bar`
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
@@ -174,6 +183,17 @@ __device__ __forceinline__ void umma_bf16_p(uint32_t leader, uint32_t d_tmem, ui
       "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
       "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader)
+      : "memory");
+}
+// The same with the A operand in tensor memory: row i of A = TMEM lane i, 32-bit column c of the operand = the bf16 pair
+// (k = 2c low half, k = 2c + 1 high half), 8 columns per K = 16 instruction (checked by tools/ubench/umma_ts.cu).  No
+// shared-memory fetch for A: 19 cycles for a 128 x 32 x 16 instruction instead of 41 (tools/ubench/umma.cu).
+__device__ __forceinline__ void umma_ts_bf16_p(uint32_t leader, uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader)
       : "memory");
 }
 __device__ __forceinline__ void umma_commit_p(uint32_t leader, uint64_t* bar) {

@@ -653,7 +653,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
     int prev = -1;
     for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
       if (prev >= 0) load_last(prev);
-      epi_mlp_tile(b, id, tmem_lane, P, ws + ProjSmem::A2, gp, nc, [&](int pass) { if (pass == 0 && prev >= 0) finish(u - 1); });
+      epi_mlp_tile(b, id, tmem_lane, P, gp, nc, [&](int pass) { if (pass == 0 && prev >= 0) finish(u - 1); });
       prev = tile;
     }
     if (prev >= 0) {
@@ -830,7 +830,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
     for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
       const bool has_next = tile + stride < g.ntiles;
       if (has_next) gather(tile + stride, nx);      // loads in flight while the first passes are processed
-      epi_mlp_tile(b, id, tmem_lane, P, ws + LiftSmem::A2, gp, nc, [&](int pass) {
+      epi_mlp_tile(b, id, tmem_lane, P, gp, nc, [&](int pass) {
         if (pass == 0 && u > 0) finish_ep(tile - stride, u - 1);
         if (pass == a1_pass && has_next) store_a1(u + 1, nx);
       });

@@ -61,7 +61,10 @@ static __device__ unsigned long long* g_trace_mlp = nullptr;
 
 namespace {
 
-// (the A2 ring has room for four slots; the FNO kernels use two)
+// The hidden activations never touch shared memory: the epilogue writes GELU(hidden) back INTO the accumulator columns it
+// has just read (each thread owns 16 fp32 columns per 32-column chunk and writes 8 columns of bf16 hi pairs + 8 of lo pairs
+// in their place), and the second GEMM takes its A operand from tensor memory.  A2FULL[2 (pass & 1) + chunk] hands a chunk
+// to the issuer; the accumulator buffer returns to the first GEMM (D1EMPTY) when the second GEMM has consumed both chunks.
 enum { MB_A1FULL = 0, MB_A1EMPTY = 2, MB_D1FULL = 4, MB_D1EMPTY = 6, MB_A2FULL = 8, MB_A2EMPTY = 12, MB_D2FULL = 16,
        MB_D2EMPTY = 18, MB_XTFULL = 20, MB_D3FULL = 21 /* two */, MB_YFREE = 23,
        MB_INFULL = 24 /* two */, MB_INEMPTY = 26 /* two */, MB_PER = 28 };      // IN: fp32 rows bulk-copied for the epilogue
@@ -71,7 +74,7 @@ __device__ __forceinline__ void mlp_init_barriers(uint64_t* b, uint32_t a1_full_
     mbar_init(&b[MB_A1FULL + i], a1_full_count);
     mbar_init(&b[MB_A1EMPTY + i], 1);
     mbar_init(&b[MB_D1FULL + i], 1);
-    mbar_init(&b[MB_D1EMPTY + i], kEpi);
+    mbar_init(&b[MB_D1EMPTY + i], 1);
     mbar_init(&b[MB_A2FULL + i], kEpi);
     mbar_init(&b[MB_A2EMPTY + i], 1);
     mbar_init(&b[MB_A2FULL + 2 + i], kEpi);
@@ -129,60 +132,58 @@ struct MlpIssuer {
     __syncwarp();
   }
 
-  template <int N2, int NA2 = 2>     // NA2: depth of the A2 ring
+  template <int N2>
   __device__ __forceinline__ void mma2(uint32_t u, int p) {
     const uint32_t idesc = idesc_bf16(128, N2);
-    const uint32_t w_lo = aW2 + (uint32_t)N2 * hid * 2;
+    const uint32_t w_lo = (uint32_t)N2 * hid * 2;
     const uint32_t d2 = tmem + 128u + (N2 > 32 ? 64u : 32u) * (u & 1);
+    const uint32_t db = (u * (uint32_t)P + (uint32_t)p) & 1u;
 #pragma unroll
     for (int j = 0; j < 2; ++j, ++nc) {
-      const int ab = nc % NA2;
-      mbar_wait(&b[MB_A2FULL + ab], (nc / NA2) & 1u);
+      const int ab = nc & 3;
+      mbar_wait(&b[MB_A2FULL + ab], (nc >> 2) & 1u);
       if (p == 0 && j == 0) mbar_wait(&b[MB_D2EMPTY + (u & 1)], empty_par(u));
       tc_fence_after();
       const int hcol0 = p * 64 + 32 * j;
-      const uint64_t dA = chunk_desc(aA2 + ab * kTileBytes, 128, 0), dW = chunk_desc(aW2, N2, hcol0);
+      const uint64_t dW = chunk_desc(aW2, N2, hcol0);
+      const uint32_t a2 = tmem + 64u * db + 32u * j;      // [K step 0: hi 8 columns | lo 8][K step 1: hi | lo]
 #pragma unroll
-      for (int term = 0; term < 3; ++term) {
-        const uint32_t ao = term == 1 ? (uint32_t)kImg : 0u, wo = term == 2 ? w_lo - aW2 : 0u;
+      for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
+        const uint32_t ao = term == 1 ? 8u : 0u, wo = term == 2 ? w_lo : 0u;
 #pragma unroll
-        for (int kk = 0; kk < 32; kk += 16)
-          umma_bf16_p(leader, d2, desc_off(dA, ao + (kk >> 3) * 2048), desc_off(dW, wo + (kk >> 3) * N2 * 16), idesc,
-                      (p | j | term | kk) != 0);
+        for (int kk = 0; kk < 2; ++kk)
+          umma_ts_bf16_p(leader, d2, a2 + 16u * kk + ao, desc_off(dW, wo + (uint32_t)kk * 2 * N2 * 16), idesc, (p | j | term | kk) != 0);
       }
-      umma_commit_p(leader, &b[MB_A2EMPTY + ab]);
       __syncwarp();
     }
+    umma_commit_p(leader, &b[MB_D1EMPTY + db]);      // the accumulator buffer (now the consumed A operand) goes back to the first GEMM
     if (p == P - 1) umma_commit_p(leader, &b[MB_D2FULL + (u & 1)]);
   }
 };
 
-// epilogue side of one tile's MLP; `after_pass(p)` runs after every pass p.  Each thread
-// turns 16 hidden columns of its pixel per 32-column chunk into split-bf16 operand bytes.
+// epilogue side of one tile's MLP; `after_pass(p)` runs after every pass p.  Each thread turns its 16 hidden columns of its
+// pixel per 32-column chunk into split-bf16 operand pairs, in place in tensor memory.
 // `bias(p, j, r)` (optional) adds the first layer's bias to the 16 accumulator values of chunk j of pass p, when the
 // first GEMM has no spare K column to carry it.
-// `NA2`: depth of the A2 ring.
 struct NoBias {
   __device__ __forceinline__ void operator()(int, int, uint32_t (&)[16]) const {}
 };
-template <int NA2 = 2, class Hook, class Bias = NoBias>
-__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint32_t tmem_lane, int P, uint8_t* sA2,
-                                             uint32_t& gp, uint32_t& nc, Hook after_pass, Bias bias = Bias{}) {
+template <class Hook, class Bias = NoBias>
+__device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint32_t tmem_lane, int P, uint32_t& gp, uint32_t& nc,
+                                             Hook after_pass, Bias bias = Bias{}) {
   for (int p = 0; p < P; ++p, ++gp) {
     const int db = gp & 1;
     TRE(nc, 0);
     mbar_wait(&b[MB_D1FULL + db], full_par(gp));
     TRE(nc, 1);
     tc_fence_after();
-    // both 16-column chunks of the pass with one tensor-memory round trip; the accumulator is released at once
+    // both 16-column chunks of the pass with one tensor-memory round trip
     uint32_t rr[2][16];
     TRE(nc, 2);
     tmem_ld16(tmem_lane + 64u * db, rr[0]);
     tmem_ld16(tmem_lane + 64u * db + 32u, rr[1]);
     tmem_ld_wait();
     TRE(nc, 3);
-    tc_fence_before();
-    mbar_arrive(&b[MB_D1EMPTY + db]);
 #pragma unroll
     for (int j = 0; j < 2; ++j, ++nc) {
       uint32_t (&r)[16] = rr[j];
@@ -194,18 +195,13 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
 #pragma unroll
         for (int e = 0; e < 8; ++e) split2p(g2[e], h[e], l[e]);
       }
-      const int ab = nc % NA2;
       TRE(nc, 4);
-      mbar_wait(&b[MB_A2EMPTY + ab], ((nc / NA2) & 1u) ^ 1u);
-      TRE(nc, 5);
-      uint8_t* dst = sA2 + ab * kTileBytes + id.row * 16 + id.half * 4096;
-      *reinterpret_cast<uint4*>(dst) = make_uint4(h[0], h[1], h[2], h[3]);
-      *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(h[4], h[5], h[6], h[7]);
-      *reinterpret_cast<uint4*>(dst + kImg) = make_uint4(l[0], l[1], l[2], l[3]);
-      *reinterpret_cast<uint4*>(dst + kImg + 2048) = make_uint4(l[4], l[5], l[6], l[7]);
+      tmem_st8(tmem_lane + 64u * db + 32u * j, h);
+      tmem_st8(tmem_lane + 64u * db + 32u * j + 8u, l);
+      tmem_st_wait();
       TRE(nc, 6);
-      fence_async_smem();
-      mbar_arrive(&b[MB_A2FULL + ab]);
+      tc_fence_before();
+      mbar_arrive(&b[MB_A2FULL + (nc & 3)]);
       TRE(nc, 7);
     }
     after_pass(p);
