@@ -127,8 +127,12 @@ def test_fourcastnet_fno2d_filter_layout_and_oracle_semantics():
 def test_forward_guards():
     m = pkg.TFNO2DModule(context_size=1, type="TFNO2DModule", name="test")
     prog = torch.randn(1, 2, 8, 8, 16)
-    with pytest.raises(NotImplementedError):            # grad mode on: forward-only
+    with pytest.raises(native.NativeError):             # grad mode on: the training path runs on CUDA tensors only, like inference
         m(prognostic=prog, constants=torch.randn(1, 1, 4, 8, 16), prescribed=torch.randn(1, 2, 1, 8, 16))
+    fc = pkg.FourCastNet(img_height=8, img_width=16, patch_size=[1, 1], constant_channels=4, prescribed_channels=1, prognostic_channels=8,
+                         embed_dim=64, depth=1, num_blocks=4, context_size=1)
+    with pytest.raises((NotImplementedError, native.NativeError)):      # FourCastNet has no training path
+        fc(prognostic=prog, constants=torch.randn(1, 1, 4, 8, 16), prescribed=torch.randn(1, 2, 1, 8, 16))
     with torch.no_grad():
         with pytest.raises(ValueError):
             m(prognostic=prog, constants=None, prescribed=torch.randn(1, 2, 1, 8, 16))
