@@ -68,7 +68,9 @@ struct Mid2Smem {      // byte offsets
   }
 };
 
-enum { MB_CONST = 0, MB_AFULL, MB_D1FULL, MB_XFULL, MB_D2FULL, MB_YFULL, MB_D3FULL, MB_E3DONE, MB_N };
+// (D3FULL: one barrier per half of the item's samples when NB = 8: the last epilogue of samples 0..3 runs under the UMMAs of 4..7)
+// (D2FULL: one barrier per group of 4 modes: the epilogue of a group runs under the UMMAs of the next ones)
+enum { MB_CONST = 0, MB_AFULL, MB_D1FULL, MB_XFULL, MB_D2FULL, MB_YFULL = MB_D2FULL + 4, MB_D3FULL, MB_E3DONE = MB_D3FULL + 2, MB_N };
 constexpr uint32_t kD2Col = 256;
 
 // v = hi + lo for a pair (hi = bf16(v), lo = bf16(v - hi)), residual through one packed FMA
@@ -104,9 +106,10 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
     mbar_init(&bars[MB_AFULL], 1);
     mbar_init(&bars[MB_D1FULL], 1);
     mbar_init(&bars[MB_XFULL], 512);
-    mbar_init(&bars[MB_D2FULL], 1);
+    for (int g = 0; g < 4; ++g) mbar_init(&bars[MB_D2FULL + g], 1);
     mbar_init(&bars[MB_YFULL], 512);
     mbar_init(&bars[MB_D3FULL], 1);
+    mbar_init(&bars[MB_D3FULL + 1], 1);
     mbar_init(&bars[MB_E3DONE], 512);
     fence_mbar_init();
   }
@@ -153,8 +156,9 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
     const uint32_t aW = smem_u32(smem + L.W), aF = smem_u32(smem + L.F), aG = smem_u32(smem + L.G), aA = smem_u32(smem + L.A),
                    aY = smem_u32(smem + L.Y);
     const int M3 = 2 * H < 64 ? 64 : 2 * H;      // rows of Gs (H = 16: the upper 32 rows are zero)
+    constexpr int NHV = NB == 8 ? 2 : 1, NBH = NB / NHV;      // GEMM 3 in halves of the item's samples (NB = 8); samples per half
     const uint32_t idesc1 = idesc_bf16(64, NB * 32) | kIdescBMnMajor, idesc2 = idesc_bf16(128, 8 * NB),
-                   idesc3 = idesc_bf16((uint32_t)M3, NB * 32);
+                   idesc3 = idesc_bf16((uint32_t)M3, NBH * 32);
     uint32_t n = 0;
     for (int grp = chunk; grp < ngroups; grp += nchunks, ++n) {
       const uint32_t par = n & 1u;
@@ -190,11 +194,11 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
           for (int k0 = 0; k0 < 64; k0 += 16)
             umma_bf16_p(leader, d2, desc_off(dW, wo + (uint32_t)(k0 >> 3) * 2048u), desc_off(dX, xo + (uint32_t)(k0 >> 3) * CS), idesc2, (term | k0) != 0);
         }
+        umma_commit_p(leader, &bars[MB_D2FULL + g]);
       }
-      umma_commit_p(leader, &bars[MB_D2FULL]);
-      // X is dead once GEMM 2 has completed: the next item's tiles may overwrite it
+      // X is dead once GEMM 2 has completed (the last group's commit covers the earlier ones): the next item's tiles may overwrite it
       TR2(n, 7);
-      mbar_wait(&bars[MB_D2FULL], par);
+      mbar_wait(&bars[MB_D2FULL + L.NG - 1], par);
       TR2(n, 8);
       if (grp + nchunks < ngroups) load(grp + nchunks);
       // GEMM 3
@@ -202,17 +206,21 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
       TR2(n, 9);
       tc_fence_after();
       {
-        const uint64_t dG = chunk_desc(aG, (uint32_t)M3, 0), dY = smem_desc(aY, (uint32_t)(NB * 512), 128);
+        const uint64_t dG = chunk_desc(aG, (uint32_t)M3, 0);
 #pragma unroll
-        for (int term = 0; term < 3; ++term) {      // Gs_hi Y_hi, Gs_lo Y_hi, Gs_hi Y_lo
-          const uint32_t go = term == 1 ? (uint32_t)L.g_part : 0u, yo = term == 2 ? (uint32_t)L.y_part : 0u;
+        for (int hv = 0; hv < NHV; ++hv) {      // rows (b, o) of the operand: the second half of the samples starts NBH * 32 rows on
+          const uint64_t dY = smem_desc(aY + (uint32_t)(hv * NBH * 512), (uint32_t)(NB * 512), 128);
 #pragma unroll
-          for (int k0 = 0; k0 < 32; k0 += 16)
-            umma_bf16_p(leader, tmem, desc_off(dG, go + (uint32_t)(k0 >> 3) * (uint32_t)(M3 * 16)), desc_off(dY, yo + (uint32_t)(k0 >> 3) * (NB * 512)),
-                        idesc3, (term | k0) != 0);
+          for (int term = 0; term < 3; ++term) {      // Gs_hi Y_hi, Gs_lo Y_hi, Gs_hi Y_lo
+            const uint32_t go = term == 1 ? (uint32_t)L.g_part : 0u, yo = term == 2 ? (uint32_t)L.y_part : 0u;
+#pragma unroll
+            for (int k0 = 0; k0 < 32; k0 += 16)
+              umma_bf16_p(leader, tmem + (uint32_t)(hv * NBH * 32), desc_off(dG, go + (uint32_t)(k0 >> 3) * (uint32_t)(M3 * 16)),
+                          desc_off(dY, yo + (uint32_t)(k0 >> 3) * (NB * 512)), idesc3, (term | k0) != 0);
+          }
+          umma_commit_p(leader, &bars[MB_D3FULL + hv]);
         }
       }
-      umma_commit_p(leader, &bars[MB_D3FULL]);
       TR2(n, 10);
       mbar_wait(&bars[MB_E3DONE], par);      // D3 shares its columns with the next item's D1
       TR2(n, 11);
@@ -261,10 +269,10 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
         if (warp == 0) TR2(n, 13);
       }
       // ---- E 2: warp (q, j): mode r = 4 j + q, lane = o: its columns (P | Q, b, q) of group j -> (Yr, Yi) pairs of the GEMM 3 operand ----
-      mbar_wait(&bars[MB_D2FULL], par);
-      if (warp == 0) TR2(n, 14);
-      tc_fence_after();
       if (j < L.NG) {
+        mbar_wait(&bars[MB_D2FULL + j], par);
+        if (warp == 0) TR2(n, 14);
+        tc_fence_after();
         uint32_t c[8 * NB];
 #pragma unroll
         for (int t = 0; t < 8 * NB; t += 16) tmem_ld16(tq + kD2Col + (uint32_t)(j * 8 * NB + t), c + t);
@@ -285,30 +293,29 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
       mbar_arrive(&bars[MB_YFULL]);
       if (warp == 0) TR2(n, 15);
       // ---- E 3: D3 row = K row (h, re|im) of the Z' images; warp (q, j): rows of quarter q, NB / 4 samples: 32 channels each ----
-      mbar_wait(&bars[MB_D3FULL], par);
-      if (warp == 0) TR2(n, 16);
-      tc_fence_after();
       {
         constexpr int MB = NB > 4 ? 2 : 1;      // warp j: samples j and j + 4 of the item (those below NB)
         // M = 64: accumulator row 16 q + lane (lanes < 16);  M = 128: row 32 q + lane
         const int row = H == 64 ? 32 * q + lane : 16 * q + lane;
         const bool live = (H == 64 || lane < 16) && row < 2 * H;
         const int h = row >> 1, reim = row & 1;
-        uint32_t z[MB][32];
-#pragma unroll
-        for (int t = 0; t < MB; ++t) tmem_ld32(tq + (uint32_t)(((j + 4 * t) % NB) * 32), z[t]);
-        tmem_ld_wait();
-        if (warp == 0) TR2(n, 19);
         const size_t zpart = (size_t)a.KZ * 64;
         const int rts = a.RT == 4 ? 2 : a.RT == 2 ? 1 : 0;      // RT is 1, 2 or 4
         const int k = kx * 2 * a.RT + (h & (a.RT - 1)) * 2 + reim;
 #pragma unroll
-        for (int t = 0; t < MB; ++t) {
+        for (int t = 0; t < MB; ++t) {      // (NB = 8: round t = half t of GEMM 3: samples 0..3 are stored under the UMMAs of 4..7)
+          mbar_wait(&bars[MB_D3FULL + (NB == 8 ? t : 0)], par);
+          if (warp == 0 && t == 0) TR2(n, 16);
+          tc_fence_after();
+          uint32_t z[32];
+          tmem_ld32(tq + (uint32_t)(((j + 4 * t) % NB) * 32), z);
+          tmem_ld_wait();
+          if (warp == 0 && t == 0) TR2(n, 19);
           const int b = b0 + j + 4 * t;
           if (live && j < NB && b < a.B) {
             uint32_t hi[16], lo[16];
 #pragma unroll
-            for (int e = 0; e < 16; ++e) split2p(make_float2(__uint_as_float(z[t][2 * e]), __uint_as_float(z[t][2 * e + 1])), hi[e], lo[e]);
+            for (int e = 0; e < 16; ++e) split2p(make_float2(__uint_as_float(z[2 * e]), __uint_as_float(z[2 * e + 1])), hi[e], lo[e]);
             uint8_t* dst = a.Zimg + (size_t)((uint32_t)(b * H + h) >> rts) * (2 * zpart) + (size_t)k * 16;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {      // channel groups
