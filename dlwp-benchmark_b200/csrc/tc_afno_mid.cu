@@ -53,7 +53,10 @@ struct Smem {      // byte offsets
                        Total = Buf + 2 * kBuf;
 };
 
-enum { MB_CONST = 0, MB_AFULL, MB_D1FULL = MB_AFULL + 2, MB_XFULL, MB_D2AFULL, MB_HFULL, MB_D2BFULL, MB_YFULL, MB_D3FULL, MB_N };
+// (D2AFULL / HFULL: one barrier per group of 32 accumulator columns = the channel block(s) warp share j works on: the first
+//  layer's epilogue of a group and the second layer's UMMAs of that group run under the other groups' first-layer UMMAs)
+enum { MB_CONST = 0, MB_AFULL, MB_D1FULL = MB_AFULL + 2, MB_XFULL, MB_D2AFULL, MB_HFULL = MB_D2AFULL + 4, MB_D2BFULL = MB_HFULL + 4, MB_YFULL,
+       MB_D3FULL, MB_N };
 constexpr uint32_t kD2Col = 256;
 
 __device__ __forceinline__ void split2p(float2 v, uint32_t& hi, uint32_t& lo) {
@@ -93,8 +96,10 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
     mbar_init(&bars[MB_AFULL + 1], 1);
     mbar_init(&bars[MB_D1FULL], 1);
     mbar_init(&bars[MB_XFULL], 512);
-    mbar_init(&bars[MB_D2AFULL], 1);
-    mbar_init(&bars[MB_HFULL], 512);
+    for (int g = 0; g < 4; ++g) {
+      mbar_init(&bars[MB_D2AFULL + g], 1);
+      mbar_init(&bars[MB_HFULL + g], 128);
+    }
     mbar_init(&bars[MB_D2BFULL], 1);
     mbar_init(&bars[MB_YFULL], 512);
     mbar_init(&bars[MB_D3FULL], 1);
@@ -167,23 +172,34 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
     for (int item = first; item < nitems; item += stride, ++n) {
       const uint32_t par = n & 1u, s = n & 1u;
       const uint32_t aB = smem_u32(smem + Smem::Buf + s * kBuf);
-      // GEMM 2a / 2b: one small GEMM per channel block (K = N = 2 bs) on the token-major operand
+      // GEMM 2a / 2b: one small GEMM per channel block (K = N = 2 bs) on the token-major operand, in groups of 32 columns
+      const int bpg = nblk / 4;      // channel blocks per group: 1 (bs = 16) or 2 (bs = 8)
       for (int layer = 0; layer < 2; ++layer) {
-        mbar_wait(&bars[layer == 0 ? MB_XFULL : MB_HFULL], par);
-        TRM(n, 4 + 2 * layer);
-        tc_fence_after();
-        const uint32_t aW = layer == 0 ? aW1 : aW2;
-        for (int blk = 0; blk < nblk; ++blk) {
-          const uint64_t dX = chunk_desc(aB, 128, (uint32_t)(blk * 2 * bs)), dW = smem_desc(aW + (uint32_t)blk * wblk, wchunk, 128);
-          const uint32_t d2 = tmem + kD2Col + (uint32_t)(blk * 2 * bs);
-#pragma unroll
-          for (int term = 0; term < 3; ++term) {      // X_hi W_hi, X_lo W_hi, X_hi W_lo
-            const uint32_t xo = term == 1 ? (uint32_t)kPart : 0u, wo = term == 2 ? wlo : 0u;
-            for (int k0 = 0; k0 < 2 * bs; k0 += 16)
-              umma_bf16_p(leader, d2, desc_off(dX, xo + (uint32_t)(k0 >> 3) * 2048u), desc_off(dW, wo + (uint32_t)(k0 >> 3) * wchunk), idesc2, (term | k0) != 0);
-          }
+        if (layer == 0) {
+          mbar_wait(&bars[MB_XFULL], par);
+          TRM(n, 4);
+          tc_fence_after();
         }
-        umma_commit_p(leader, &bars[layer == 0 ? MB_D2AFULL : MB_D2BFULL]);
+        const uint32_t aW = layer == 0 ? aW1 : aW2;
+        for (int g = 0; g < 4; ++g) {
+          if (layer == 1) {      // the group's K chunks have been rewritten by its first-layer epilogue
+            mbar_wait(&bars[MB_HFULL + g], par);
+            if (g == 0) TRM(n, 6);
+            tc_fence_after();
+          }
+          for (int blk = g * bpg; blk < (g + 1) * bpg; ++blk) {
+            const uint64_t dX = chunk_desc(aB, 128, (uint32_t)(blk * 2 * bs)), dW = smem_desc(aW + (uint32_t)blk * wblk, wchunk, 128);
+            const uint32_t d2 = tmem + kD2Col + (uint32_t)(blk * 2 * bs);
+#pragma unroll
+            for (int term = 0; term < 3; ++term) {      // X_hi W_hi, X_lo W_hi, X_hi W_lo
+              const uint32_t xo = term == 1 ? (uint32_t)kPart : 0u, wo = term == 2 ? wlo : 0u;
+              for (int k0 = 0; k0 < 2 * bs; k0 += 16)
+                umma_bf16_p(leader, d2, desc_off(dX, xo + (uint32_t)(k0 >> 3) * 2048u), desc_off(dW, wo + (uint32_t)(k0 >> 3) * wchunk), idesc2, (term | k0) != 0);
+            }
+          }
+          if (layer == 0) umma_commit_p(leader, &bars[MB_D2AFULL + g]);
+        }
+        if (layer == 1) umma_commit_p(leader, &bars[MB_D2BFULL]);
         TRM(n, 5 + 2 * layer);
       }
       // GEMM 3 (its accumulator takes the columns of D2, dead by now, and the 128 after them)
@@ -251,7 +267,7 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
       }
       // ---- E 2a / E 2b: lane = token 32 q + lane, accumulator columns 32 j .. 32 j + 31 = k of the next operand ----
       {
-        mbar_wait(&bars[MB_D2AFULL], par);
+        mbar_wait(&bars[MB_D2AFULL + j], par);
         if (warp == 0) TRM(n, 14);
         tc_fence_after();
         uint32_t v[32];
@@ -264,7 +280,7 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
         for (int oc = 0; oc < 4; ++oc) split8_store(v + 8 * oc, dst + oc * 2048, kPart);
         tc_fence_before();
         fence_async_smem();
-        mbar_arrive(&bars[MB_HFULL]);
+        mbar_arrive(&bars[MB_HFULL + j]);
         if (warp == 0) TRM(n, 15);
       }
       {
