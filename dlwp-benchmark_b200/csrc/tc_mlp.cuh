@@ -198,11 +198,14 @@ __device__ __forceinline__ void epi_mlp_tile(uint64_t* b, const EpiId& id, uint3
       TRE(nc, 4);
       tmem_st8(tmem_lane + 64u * db + 32u * j, h);
       tmem_st8(tmem_lane + 64u * db + 32u * j + 8u, l);
-      tmem_st_wait();
-      TRE(nc, 6);
-      tc_fence_before();
-      mbar_arrive(&b[MB_A2FULL + (nc & 3)]);
-      TRE(nc, 7);
+      if (j == 1) {      // one wait for the stores of both chunks: chunk 0's store latency hides behind chunk 1's arithmetic
+        tmem_st_wait();
+        TRE(nc, 6);
+        tc_fence_before();
+        mbar_arrive(&b[MB_A2FULL + ((nc - 1) & 3)]);
+        mbar_arrive(&b[MB_A2FULL + (nc & 3)]);
+        TRE(nc, 7);
+      }
     }
     after_pass(p);
   }
