@@ -267,6 +267,8 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
         # the tcgen05 forms of the W-DFT kernels move the same tensors
         table["afno_fwd_tc_kernel"] = table["afno_fwd_kernel"]
         table["afno_inv_tc_kernel"] = table["afno_inv_kernel"]
+        # split-bf16 operand images both ways: the bytes of the fp32 spectrum; (re|im)-stacked filter weights of both layers
+        table["afno_mid_tc_kernel"] = b * D * (2 * spec + 2 * 2 * 4 * E * (E // kw["num_blocks"]))
         return table.get(name)
     cin, C, L, P, Cg, N, m1, m2 = fno_dims(kw, H, W)
     px = B * S

@@ -14,3 +14,11 @@ ncu --metrics gpu__time_duration.sum --clock-control none -s 620 -c 201 --csv --
 ncu --set full --clock-control none --import-source on -k regex:"fno_layer|fno_lift|fno_mid|fno_proj" -s 20 -c 10 -o gpurun_out/r02_prof_c4_$tag -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_f_$tag.log 2>&1; echo "ncu2 rc=$?"
 python tools/ncu_summary_csv.py gpurun_out/r02_prof_c4_$tag.ncu-rep gpurun_out/r02_ncu_full_c4_$tag.csv > /dev/null 2>&1; echo "summary rc=$?"
 tail -3 gpurun_out/r02_tests_gpu_$tag.log; cut -c1-200 gpurun_out/r02_bench_c4_$tag.json
+# AFNO (config c3): bench lines at 8 (above) and 256 members, A/B against the fp32 mid kernel, --set full of one block's four kernels
+python bench.py --workload c3 --members 256 --no-cpu-baseline > gpurun_out/r02_bench_c3m256_$tag.json 2>> gpurun_out/r02_bench_$tag.err; echo "c3m256 rc=$?"
+DLWP_MID_FMA=1 python bench.py --workload c3 --members 256 --no-cpu-baseline --no-eager > gpurun_out/r02_bench_c3m256_midfma_$tag.json 2>> gpurun_out/r02_bench_$tag.err
+ncu --set full --clock-control none --import-source on -k regex:afno -s 20 -c 4 -o gpurun_out/r02_prof_c3_$tag -f python bench.py --workload c3 --members 256 --steps 1 --warmup 3 --no-cpu-baseline --no-eager > gpurun_out/ncu_f_c3_$tag.log 2>&1; echo "ncu3 rc=$?"
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:afno -c 100 --csv --log-file gpurun_out/r02_ncu_launches_c3_$tag.csv python bench.py --workload c3 --members 256 --steps 1 --warmup 3 --no-cpu-baseline --no-eager > /dev/null 2>&1; echo "ncu4 rc=$?"
+(python tools/ncu_pipe.py gpurun_out/r02_prof_c4_$tag.ncu-rep; python tools/ncu_pipe.py gpurun_out/r02_prof_c3_$tag.ncu-rep) > gpurun_out/r02_data_pipe_$tag.txt 2>&1
+tools/ubench/umma > gpurun_out/r02_ubench_umma_$tag.txt 2>&1; tools/ubench/umma_ts >> gpurun_out/r02_ubench_umma_$tag.txt 2>&1
+cat gpurun_out/r02_data_pipe_$tag.txt

@@ -89,7 +89,7 @@ int main() {
     }
     const double cyc = (double)h / run, bytes = (c.M + c.N) * 32.0;
     printf("%5d %5d %7s %12.1f %12.1f %14.0f %12.1f\n", c.M, c.N, c.layout == 0 ? "none" : c.layout == 1 ? "none/Bmn" : "sw128", cyc,
-           (double)c.M * c.N * 16 / 8192.0, bytes, bytes / cyc);
+           (double)c.M * c.N * 16 / 4096.0, bytes, bytes / cyc);
   }
   return 0;
 }
