@@ -167,13 +167,27 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       uint8_t* stage = ws + AmSmem::A2;
       mbar_wait(&b[MB_D2FULL + (v_ & 1)], full_par(v_));
       tc_fence_after();
-      float hp[4][4];      // head: [row of the thread][output channel]
+      // head: [row of the thread][output channel], starting from the residual frame (lane 0 of a token's 8 lanes; the loads
+      // are issued here, ahead of the accumulator wait, not one by one in front of the stores)
+      // (a tile lies within one sample: HW is a multiple of the tile size)
+      const long long p0 = (long long)tile * kTcTile, bb = a.Wh != nullptr ? p0 / a.HW : 0, pix0 = p0 - bb * a.HW;
+      float hp[4][4];
 #pragma unroll
       for (int it = 0; it < 4; ++it)
 #pragma unroll
-        for (int co = 0; co < 4; ++co) hp[it][co] = 0.f;
+        for (int co = 0; co < 4; ++co)
+          hp[it][co] = (a.Wh != nullptr && a.last != nullptr && co < a.Cg && (ltid & 7) == 0)
+                           ? __ldg(a.last + bb * a.last_bstride + (long long)co * a.HW + pix0 + it * 32 + (ltid >> 3))
+                           : 0.f;
+      const int un = ltid & 7;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
+        float4 wh[4];      // head: this thread's 4 channels of the round, per output channel
+        if (a.Wh != nullptr) {
+#pragma unroll
+          for (int co = 0; co < 4; ++co)
+            wh[co] = co < a.Cg ? __ldg(reinterpret_cast<const float4*>(a.Wh + co * kAfnoE + 32 * h + 4 * un)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         if (id.half == h) {
           uint32_t r[32];
           tmem_ld32(tmem_row + 128u + 64u * (v_ & 1) + 32u * h, r);
@@ -188,7 +202,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
         bar_sync(1 + w, kEpi);
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
-          const int row = it * 32 + (ltid >> 3), un = ltid & 7, c = 32 * h + 4 * un;
+          const int row = it * 32 + (ltid >> 3), c = 32 * h + 4 * un;
           const float4 d = *reinterpret_cast<const float4*>(stage + row * 128 + ((un ^ (row & 7)) << 4));
           const size_t off = ((size_t)tile * kTcTile + row) * kAfnoE + c;
           const float4 xv = *reinterpret_cast<const float4*>(a.x + off);
@@ -198,10 +212,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
           } else {
 #pragma unroll
             for (int co = 0; co < 4; ++co)
-              if (co < a.Cg) {
-                const float4 wv = __ldg(reinterpret_cast<const float4*>(a.Wh + co * kAfnoE + c));
-                hp[it][co] = fmaf(v.x, wv.x, fmaf(v.y, wv.y, fmaf(v.z, wv.z, fmaf(v.w, wv.w, hp[it][co]))));
-              }
+              hp[it][co] = fmaf(v.x, wh[co].x, fmaf(v.y, wh[co].y, fmaf(v.z, wh[co].z, fmaf(v.w, wh[co].w, hp[it][co]))));
           }
         }
         bar_sync(1 + w, kEpi);      // the staging rows are rewritten by the next round / the next tile's first chunk
@@ -209,8 +220,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       if (a.Wh != nullptr) {
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
-          const long long p = (long long)tile * kTcTile + it * 32 + (ltid >> 3);
-          const long long bb = p / a.HW, pix = p - bb * a.HW;
+          const long long pix = pix0 + it * 32 + (ltid >> 3);
 #pragma unroll
           for (int co = 0; co < 4; ++co)
             if (co < a.Cg) {
@@ -218,10 +228,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
               s += __shfl_xor_sync(0xffffffffu, s, 1);
               s += __shfl_xor_sync(0xffffffffu, s, 2);
               s += __shfl_xor_sync(0xffffffffu, s, 4);
-              if ((ltid & 7) == 0) {
-                const float lastv = a.last != nullptr ? a.last[bb * a.last_bstride + (long long)co * a.HW + pix] : 0.f;
-                a.frame[bb * a.frame_bstride + (long long)co * a.HW + pix] = s + lastv;
-              }
+              if ((ltid & 7) == 0) a.frame[bb * a.frame_bstride + (long long)co * a.HW + pix] = s;
             }
         }
       }
@@ -253,7 +260,8 @@ int launch_afno_mlp(const AfnoMlpArgs& a, cudaStream_t st) {
   DLWP_TRY(current_sms(&sms));
   DLWP_TRY(ensure_dynamic_smem((const void*)afno_mlp_kernel, AmSmem::Total));
   DLWP_REQUIRE(a.ntiles > 0, "afno_mlp_kernel: empty problem");
-  DLWP_REQUIRE(a.Wh == nullptr || (a.Cg >= 1 && a.Cg <= 4 && a.HW > 0 && a.frame != nullptr), "afno_mlp_kernel: bad head arguments");
+  DLWP_REQUIRE(a.Wh == nullptr || (a.Cg >= 1 && a.Cg <= 4 && a.HW > 0 && a.HW % kTcTile == 0 && a.frame != nullptr),
+               "afno_mlp_kernel: bad head arguments");
   const int grid = a.ntiles < sms ? a.ntiles : sms;      // two workers per CTA: the second one has work when there are more tiles than CTAs
   DLWP_CUDA(launch_pdl(afno_mlp_kernel, dim3(grid), dim3(kAmCta), (size_t)AmSmem::Total, st, a));
   DLWP_LAUNCHED("afno_mlp_kernel");
