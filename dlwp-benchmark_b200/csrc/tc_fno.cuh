@@ -10,10 +10,10 @@
 //
 // Per model evaluation (reference: neuralop FNO.forward as called from fno.py:103):
 //   fno_lift_kernel    gather x_t from the NCHW sources (fno.py:49-62) -> lifting MLP
-//                      (1x1 conv, GELU, 1x1 conv; hidden stays in TMEM/SMEM) -> tile image
+//                      (1x1 conv, GELU, 1x1 conv; the hidden layer stays in tensor memory) -> tile image
 //                      + forward truncated W-DFT of the result (a third MMA on the same tile)
-//   fno_mid_kernel     H-DFT, per-mode channel mixing, inverse H-DFT on the retained columns
-//                      (fp32 FMA, weights in registers) -> split-bf16 operand image of Z
+//   fno_mid_tc_kernel  H-DFT, per-mode channel mixing, inverse H-DFT on the retained columns as three
+//                      chained GEMMs (tc_mid2.cu; fno_mid_kernel is the fp32 FMA form) -> split-bf16 operand image of Z
 //   fno_layer_kernel   inverse truncated W-DFT GEMM K-concatenated with the 1x1 skip conv,
 //                      + bias, GELU -> tile image + forward W-DFT for the next layer
 //   fno_proj_kernel    projection MLP + residual on the last context frame -> NCHW output
