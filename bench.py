@@ -236,7 +236,7 @@ def step_bytes(cls, kw, B, H, W, b=4):
     return act + wts
 
 
-def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
+def kernel_bytes(cls, kw, B, H, W, name, tcw=False, fused_tail=False):
     """Algorithmic bytes ONE model evaluation moves through the kernel called `name` (sum over
     its launches in the step), or None when bench.py has no model for that kernel."""
     S, b = H * W, 4
@@ -300,7 +300,11 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False):
     if name == "fno_lift_kernel":       # fused lifting MLP (+ forward W-DFT of its output)
         return b * px * (cin + C) + b * B * H * m2 * C * 2
     if name == "fno_layer_kernel":      # fused inverse W-DFT + skip + GELU (+ forward W-DFT, not after the last layer)
+        if fused_tail:                  # the last layer runs inside fno_layerproj_kernel: N - 1 launches, each with a forward W-DFT
+            return b * (N - 1) * (2 * px * C + 2 * B * H * m2 * C * 2)
         return b * (N * 2 * px * C + (2 * N - 1) * B * H * m2 * C * 2)
+    if name == "fno_layerproj_kernel":  # last layer (activation image + Z' in) + projection MLP + residual frame (NCHW in / out)
+        return b * (px * C + B * H * m2 * C * 2 + 2 * px * Cg)
     if name in ("fno_mid_kernel", "fno_mid_tc_kernel"):   # H-DFT, mode mixing, inverse H-DFT on the retained columns
         return b * N * (2 * B * H * m2 * C * 2 + m1 * m2 * C * C * 2)
     if name == "fno_tail_kernel":       # last layer + projection MLP + residual
@@ -564,7 +568,7 @@ def run_ours(args, wl):
         entries = prof.entries
         name, (kms, kn) = max(entries.items(), key=lambda kv: kv[1][0])
         tcw = "tcw_layer" in entries
-        kb = kernel_bytes(cls, kw, members, H, W, name, tcw)
+        kb = kernel_bytes(cls, kw, members, H, W, name, tcw, fused_tail="fno_layerproj_kernel" in entries)
         total_prof = sum(v[0] for v in entries.values())
         roof = {"bound": "hbm", "kernel": name, "achieved": None, "peak": hbm_peak, "unit": "GB/s", "frac": None,
                 "traffic": None, "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",

@@ -118,6 +118,14 @@ int launch_tc_mid2_pack(const float2* wm, uint8_t* Wimg, int R, int Kc, cudaStre
 void tc_mid2_pack_bases(const double* Fh_re, const double* Fh_im, const double* Gh_re, const double* Gh_im, int H, int R,
                         uint8_t* Fimg, uint8_t* Gimg);
 
+// last spectral layer + projection MLP in one kernel (tc_fno_lp.cu): the layer's output tile goes accumulator -> bias ->
+// split-bf16 pairs written back in place -> A operand of the projection's first GEMM, never to HBM
+struct TcLayerProjArgs {
+  TcLayerArgs layer;      // y_img, Aout, Fimg unused; gelu as given (0 for neuralop's last block)
+  TcProjArgs proj;        // x_img unused
+};
+int launch_tc_layerproj(const TcLayerProjArgs& a, cudaStream_t st);
+bool tc_layerproj_fits(int KZ);
 int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st);
 int launch_tc_layer(const TcLayerArgs& a, cudaStream_t st);
 int launch_tc_proj(const TcProjArgs& a, cudaStream_t st);

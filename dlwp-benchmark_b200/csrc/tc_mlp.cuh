@@ -132,6 +132,36 @@ struct MlpIssuer {
     __syncwarp();
   }
 
+  // The same with the A operand in tensor memory (fno_layerproj_kernel: the layer's output tile never leaves the SM):
+  // buffer u & 1 at tA1 + K1 * (u & 1), per K step of 16: [hi 8 columns | lo 8 columns].
+  template <int K1>
+  __device__ __forceinline__ void mma1_ts(uint32_t tA1, uint32_t u, int p, uint32_t gp) {
+    const int db = gp & 1, ub = u & 1;
+    mbar_wait(&b[MB_D1EMPTY + db], empty_par(gp));
+    if (p == 0) mbar_wait(&b[MB_A1FULL + ub], full_par(u));
+    tc_fence_after();
+    const uint32_t idesc = idesc_bf16(128, 64);
+    const uint32_t w_lo = (uint32_t)hid * K1 * 2;
+    const uint64_t dW = smem_desc(aW1 + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128);
+    const uint32_t a1 = tA1 + (uint32_t)K1 * ub;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int term = 0; term < 3; ++term) {
+      const uint32_t ao = term == 1 ? 8u : 0u, wo = term == 2 ? w_lo : 0u;
+#pragma unroll
+      for (int k0 = 0; k0 < K1; k0 += 16) {
+        umma_ts_bf16_p(leader, tmem + 64u * db, a1 + (uint32_t)k0 + ao, desc_off(dW, wo + (uint32_t)(k0 >> 3) * hid * 16), idesc, acc);
+        acc = 1;
+      }
+    }
+    if (aW1x != 0)
+      umma_bf16_p(leader, tmem + 64u * db, chunk_desc(aOnes, 128, 0),
+                  smem_desc(aW1x + (uint32_t)p * 64 * 16, (uint32_t)hid * 16, 128), idesc, 1);
+    umma_commit_p(leader, &b[MB_D1FULL + db]);
+    if (p == P - 1) umma_commit_p(leader, &b[MB_A1EMPTY + ub]);
+    __syncwarp();
+  }
+
   template <int N2>
   __device__ __forceinline__ void mma2(uint32_t u, int p) {
     const uint32_t idesc = idesc_bf16(128, N2);

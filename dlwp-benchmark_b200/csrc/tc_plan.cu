@@ -81,6 +81,8 @@ int plan_tc_build(dlwp_plan* p) {
   for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_skip[l], 4096));
   // H-DFT, mode mixing and inverse H-DFT on tcgen05 where the geometry allows it (DLWP_MID_FMA=1 keeps the fp32 FMA kernel: A/B runs)
   p->tc_mid2 = tc_mid2_samples(H, d.n_rows) != 0 && std::getenv("DLWP_MID_FMA") == nullptr;
+  // the last layer and the projection as one kernel (DLWP_NO_FUSE_PROJ=1 keeps the two launches: A/B runs)
+  p->tc_fuse_proj = d.n_layers >= 1 && tc_layerproj_fits(KZ) && std::getenv("DLWP_NO_FUSE_PROJ") == nullptr;
   if (p->tc_mid2) {
     const int R = d.n_rows;
     std::vector<double> fr((size_t)R * H), fi((size_t)R * H), gr((size_t)H * R), gi2((size_t)H * R);
@@ -225,6 +227,22 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
     ya.Wsimg = p->tc_skip[l];
     ya.bias = cbias + (size_t)l * C;
     ya.gelu = l < N - 1 ? 1 : 0;
+    if (l == N - 1 && p->tc_fuse_proj) {      // last layer + projection in one kernel: the layer's output tile never leaves the SM
+      TcLayerProjArgs fa{};
+      fa.layer = ya;
+      fa.proj.g = g;
+      fa.proj.hid = d.projection_channels;
+      fa.proj.Cg = d.prognostic_channels;
+      fa.proj.W1img = p->tc_projW1;
+      fa.proj.W1ximg = p->tc_projW1x;
+      fa.proj.W2img = p->tc_projW2;
+      fa.proj.b2 = pb2;
+      fa.proj.out = io.out;
+      fa.proj.out_bstride = io.out_bstride;
+      fa.proj.last = io.last;
+      fa.proj.last_bstride = io.last_bstride;
+      return launch_tc_layerproj(fa, st);
+    }
     DLWP_TRY(launch_tc_layer(ya, st));
     cur ^= 1;
   }
