@@ -211,3 +211,27 @@ def test_rollout_is_cuda_graph_capturable(pkg, case):
     graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(out, want1) and not torch.equal(want1, want0)
+
+
+@pytest.mark.parametrize("knob", ["DLWP_NO_FUSE_PROJ", "DLWP_MID_FMA"])
+def test_ab_kernel_forms_agree(pkg, knob, monkeypatch):
+    """The kernel forms kept for A/B runs (two launches for the last layer + projection instead of fno_layerproj_kernel;
+    the fp32 FMA mid kernel instead of fno_mid_tc_kernel) are selected when a plan is built: same increment as the default
+    forms and as the oracle."""
+    from oracle import wrappers as owrap
+    torch.manual_seed(1234)
+    ref = owrap.TFNO2DModule(**C2).eval()
+    x = torch.randn(40, _cin(C2), 32, 64, generator=torch.Generator().manual_seed(7))
+    outs = []
+    for on in (False, True):
+        if on:
+            monkeypatch.setenv(knob, "1")
+        mod = pkg.TFNO2DModule(**C2).cuda().eval()
+        mod.load_state_dict(ref.state_dict(), strict=True)
+        mod.precision = pkg.native.PREC_FP32_TC
+        with torch.no_grad():
+            outs.append(mod.backbone(x.cuda()).cpu())
+    with torch.no_grad():
+        want = ref.fno(x)
+    assert max_rel(outs[0], want) < TOL_INCR and max_rel(outs[1], want) < TOL_INCR
+    assert max_rel(outs[1], outs[0]) < TOL_INCR
