@@ -317,10 +317,10 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
       const bool live = lane < 16 && h2 < g.RT && kx < g.Kc;
       const int nd = tail.nd;
       for (uint32_t u = 0;; ++u) {
-        const int t0 = blockIdx.x * 2 + (int)u * stride;
+        const int t0 = (int)blockIdx.x + (int)u * stride;
         if (t0 >= g.ntiles) break;
         for (int w = 0; w < 2; ++w) {
-          const int tile = t0 + w;
+          const int tile = t0 + w * (int)gridDim.x;
           if (tile >= g.ntiles) break;
           uint64_t* b = bars + w * LB_PER;
           const uint32_t sl = d3_slot(u, nd);
@@ -377,7 +377,7 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
       uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
       const uint32_t tmem = tmem_s + 256u * w;
       const uint32_t aF = smem_u32(smem + L.F);
-      const int first = blockIdx.x * 2 + w;
+      const int first = (int)blockIdx.x + w * (int)gridDim.x;
 
       auto load_inputs = [&](int tile, uint32_t u) {
         const int s = u % kLayerSlots;
@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
       const uint32_t tmem = tmem_s + 256u * w;
       const uint32_t aG = smem_u32(smem + L.G), aW = smem_u32(smem + L.Ws);
       const uint64_t dG = chunk_desc(aG, 128, 0), dW = chunk_desc(aW, 32, 0);
-      const int first = blockIdx.x * 2 + w;
+      const int first = (int)blockIdx.x + w * (int)gridDim.x;
       mbar_wait(bar_const, 0);
       const uint32_t idesc = idesc_bf16(128, 32);
       const uint32_t g_lo = 128u * (uint32_t)g.KZ * 2u, z_lo = (uint32_t)g.KZ * 64u;
@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
     const uint32_t tmem = tmem_s + 256u * w + ((uint32_t)(id.q4 * 32) << 16) + 16u * id.half;
     uint32_t u = 0, n3 = 0;
     int prev_tile[2] = {0, 0};
-    for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
+    for (int tile = (int)blockIdx.x + w * (int)gridDim.x; tile < g.ntiles; tile += stride, ++u) {
       const int s = u & 1;
       mbar_wait(&b[LB_DFULL + s], full_par(u));
       if ((tid & 255) == 0) TR(w, u, 3);
@@ -491,8 +491,8 @@ int launch_tc_layer(const TcLayerArgs& a_in, cudaStream_t st) {
   DLWP_TRY(ensure_dynamic_smem((const void*)fno_layer_kernel, kLayerSmemMax));
   const LayerSmem L(a.g.KZ, a.ny);
   DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
-  const int want = (a.g.ntiles + 1) / 2;
-  const int grid = want < sms ? want : sms;
+  // tile t of a CTA's list goes to worker (t / grid) % 2: with fewer tiles than SMs every tile has an SM (and its issue slots) to itself
+  const int grid = a.g.ntiles < sms ? a.g.ntiles : sms;
   DLWP_CUDA(launch_pdl(fno_layer_kernel, dim3(grid), dim3(kCtaLayerAll), (size_t)L.Total, st, a));
   DLWP_LAUNCHED("fno_layer_kernel");
   return DLWP_OK;
@@ -569,7 +569,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       MlpIssuer is{b, smem_u32(ws + ProjSmem::X), (uint32_t)kTileBytes, smem_u32(smem + ProjSmem::W1),
                    smem_u32(smem + ProjSmem::W2), smem_u32(ws + ProjSmem::A2), tmem_s + 256u * w, hid, P, 0u,
                    smem_u32(smem + ProjSmem::Ones), smem_u32(smem + ProjSmem::W1x), leader};
-      const int first = blockIdx.x * 2 + w;
+      const int first = (int)blockIdx.x + w * (int)gridDim.x;
       mbar_wait(bar_const, 0);
       auto load_x = [&](int tile, uint32_t u) {
         const int s = u & 1;
@@ -651,7 +651,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       obase = bb * a.out_bstride + pix;
     };
     int prev = -1;
-    for (int tile = blockIdx.x * 2 + w; tile < g.ntiles; tile += stride, ++u) {
+    for (int tile = (int)blockIdx.x + w * (int)gridDim.x; tile < g.ntiles; tile += stride, ++u) {
       if (prev >= 0) load_last(prev);
       epi_mlp_tile(b, id, tmem_lane, P, gp, nc, [&](int pass) { if (pass == 0 && prev >= 0) finish(u - 1); });
       prev = tile;
@@ -673,8 +673,8 @@ int launch_tc_proj(const TcProjArgs& a_in, cudaStream_t st) {
   DLWP_TRY(current_sms(&sms));
   DLWP_TRY(ensure_dynamic_smem((const void*)fno_proj_kernel, ProjSmem::Total));
   DLWP_REQUIRE(a.hid == 128 || a.hid == 256, "tensor-core projection needs width 128 or 256, got %d", a.hid);
-  const int want = (a.g.ntiles + 1) / 2;
-  const int grid = want < sms ? want : sms;
+  // tile t of a CTA's list goes to worker (t / grid) % 2: with fewer tiles than SMs every tile has an SM (and its issue slots) to itself
+  const int grid = a.g.ntiles < sms ? a.g.ntiles : sms;
   DLWP_CUDA(launch_pdl(fno_proj_kernel, dim3(grid), dim3(kCta), (size_t)ProjSmem::Total, st, a));
   DLWP_LAUNCHED("fno_proj_kernel");
   return DLWP_OK;
@@ -748,7 +748,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
                    smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader};
       const uint32_t aF = smem_u32(smem + LiftSmem::F), d3 = tmem_s + 256u * w + 192u;
-      const int first = blockIdx.x * 2 + w;
+      const int first = (int)blockIdx.x + w * (int)gridDim.x;
       const bool dft = a.Aout != nullptr;
       auto finish = [&](int tile, uint32_t n) {
         ctrl_finish_tile(leader, dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
@@ -797,7 +797,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       mbar_arrive(&b[MB_A1FULL + s]);
     };
 
-    const int first = blockIdx.x * 2 + w;
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
     float nx[8];
     if (first < g.ntiles) {
       gather(first, nx);
@@ -849,8 +849,8 @@ int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
   DLWP_TRY(ensure_dynamic_smem((const void*)fno_lift_kernel, LiftSmem::Total));
   DLWP_REQUIRE(a.hid == 128 || a.hid == 256, "tensor-core lifting needs width 128 or 256, got %d", a.hid);
   DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 15 && a.ngrp >= 1, "tensor-core lifting needs 1..15 input channels, got %d", a.Cin);
-  const int want = (a.g.ntiles + 1) / 2;
-  const int grid = want < sms ? want : sms;
+  // tile t of a CTA's list goes to worker (t / grid) % 2: with fewer tiles than SMs every tile has an SM (and its issue slots) to itself
+  const int grid = a.g.ntiles < sms ? a.g.ntiles : sms;
   DLWP_CUDA(launch_pdl(fno_lift_kernel, dim3(grid), dim3(kCta), (size_t)LiftSmem::Total, st, a));
   DLWP_LAUNCHED("fno_lift_kernel");
   return DLWP_OK;

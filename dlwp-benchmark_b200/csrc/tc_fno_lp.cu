@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
     uint64_t* lb = lbars + w * PB_PER;
     uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
     const uint32_t tmem = tmem_s + 256u * w;
-    const int first = blockIdx.x * 2 + w;
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
     auto load_inputs = [&](int tile, uint32_t u) {
       const int s = u % kLpSlots;
       mbar_wait(&lb[PB_XFREE + s], ((u / kLpSlots) & 1u) ^ 1u);   // the UMMAs that read this slot last are done
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
     MlpIssuer is{b, 0u, 0u, smem_u32(smem + L.W1), smem_u32(smem + L.W2), 0u, tmem_s + 256u * w, hid, P, 0u,
                  smem_u32(smem + L.Ones), smem_u32(smem + L.W1x), leader};
     const uint32_t tA1 = tmem_s + 256u * w + 192u;
-    const int first = blockIdx.x * 2 + w;
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
     mbar_wait(bar_const, 0);
     // the tile's rows of the residual frame (128 consecutive pixels per channel) for the epilogue: bulk copies,
     // because a generic global load in flight in an epilogue thread would be waited for by its next proxy fence
@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
       obase = bb * a.proj.out_bstride + pix;
     };
     int prev = -1;
-    const int first = blockIdx.x * 2 + w;
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
     if (first < g.ntiles) make_a1(0);
     const int a1_pass = P >= 3 ? P - 2 : 0;
     for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
@@ -289,8 +289,7 @@ int launch_tc_layerproj(const TcLayerProjArgs& a_in, cudaStream_t st) {
   DLWP_REQUIRE(a.proj.hid == 128 || a.proj.hid == 256, "tensor-core projection needs width 128 or 256, got %d", a.proj.hid);
   DLWP_REQUIRE(a.layer.g.KZ >= 16 && a.layer.g.KZ % 16 == 0 && L.Total <= kLpSmemMax, "fno_layerproj_kernel: KZ=%d does not fit", a.layer.g.KZ);
   DLWP_TRY(ensure_dynamic_smem((const void*)fno_layerproj_kernel, kLpSmemMax));
-  const int want = (a.layer.g.ntiles + 1) / 2;
-  const int grid = want < sms ? want : sms;
+  const int grid = a.layer.g.ntiles < sms ? a.layer.g.ntiles : sms;      // (tile t of a CTA's list goes to worker (t / grid) % 2)
   DLWP_CUDA(launch_pdl(fno_layerproj_kernel, dim3(grid), dim3(kCtaLp), (size_t)L.Total, st, a));
   DLWP_LAUNCHED("fno_layerproj_kernel");
   return DLWP_OK;
