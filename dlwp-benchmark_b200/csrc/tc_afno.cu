@@ -19,22 +19,25 @@ __device__ unsigned long long* g_trace_afno = nullptr;   // [16 tiles][8 events]
 //   warps 0-7 / 8-15 : the epilogue groups of two workers (two threads per token: channel halves)
 //   warps 16 / 17    : their control warps
 // Both 64 KB weight operands ([hi | lo] split-bf16 images) stay in shared memory for the whole kernel and are
-// shared by the two workers, which take the CTA's tiles alternately: the TMEM -> GELU -> shared memory -> MMA
-// chain of one tile's four passes is a latency chain, so a second, independent tile per SM is what fills the
-// pipes (one worker: 9.4 us per tile).  What is left of shared memory is one A1 buffer (normalised tokens,
-// 32 KB; the next tile's tokens are stored after the last first-layer MMA of this tile has read it, two passes
-// before they are needed) and ONE A2 buffer (a 32-column hidden chunk, 16 KB) per worker: a chunk's store
-// waits for the second-layer MMAs of the chunk before it, which have had the chunk's GELU time to complete.
-// The hidden accumulator D1 [128 x 64] and the output accumulator D2 [128 x 64] are double-buffered in tensor
-// memory (256 columns per worker); a tile's output is taken over after the first pass of the worker's next tile.
-// LayerNorm: the two halves of a token are lanes l and l + 16 of a warp for the gather: each computes the mean and centred
-// sum of squares of its 32 channels, a shuffle brings the other half's, pairwise update (exact like two passes).
+// shared by the two workers, which take the CTA's tiles alternately: the TMEM -> GELU -> MMA chain of one tile's
+// four passes is a latency chain, so a second, independent tile per SM is what fills the pipes.  Per worker
+// there is one A1 buffer (normalised tokens, 32 KB; the next tile's tokens are stored after the last first-layer
+// MMA of this tile has read it, two passes before they are needed) and 16 KB of staging for the output rows.
+// The 256-wide hidden layer never touches shared memory: the GELU epilogue writes the split-bf16 pairs back into
+// the accumulator columns it has just read and the second GEMM takes its A operand from tensor memory
+// (tc_mlp.cuh).  The hidden accumulator D1 [128 x 64] and the output accumulator D2 [128 x 64] are double-buffered
+// in tensor memory (256 columns per worker).
+// LayerNorm: a warp takes 8 tokens per step, lane = token + 8 x channel-octet pair (a load instruction touches 8
+// lines of 128 bytes, not 32), statistics over the four lanes of a token by shuffles, two passes like torch.
+// The biases travel as kernel parameters (constant bank).  What bounds the kernel is the L1 data pipe
+// (DESIGN.md section 4d): every access pattern here is chosen for few 128-byte wavefronts.
 // =============================================================================================
 namespace {
 constexpr int kAmCta = kCta;      // 2 x 256 epilogue threads + 2 control warps
 struct AmSmem {
-  static constexpr int W1 = 0, W2 = W1 + kAfnoHid * kAfnoE * 4, Worker = W2 + kAfnoE * kAfnoHid * 4, A1 = 0, A2 = 32768,
-                       WorkerBytes = A2 + kTileBytes, Total = Worker + 2 * WorkerBytes;
+  static constexpr int W1 = 0, W2 = W1 + kAfnoHid * kAfnoE * 4, Worker = W2 + kAfnoE * kAfnoHid * 4, A1 = 0,
+                       Stage = 32768,      // 16 KB: the output rows on their way to coalesced stores
+                       WorkerBytes = Stage + kTileBytes, Total = Worker + 2 * WorkerBytes;
   static_assert(Total <= 224 * 1024, "afno_mlp_kernel shared memory");
 };
 }  // namespace
@@ -75,7 +78,7 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
     uint64_t* b = bars + w * MB_PER;
     uint8_t* ws = smem + AmSmem::Worker + w * AmSmem::WorkerBytes;
     MlpIssuer is{b, smem_u32(ws + AmSmem::A1), 32768u, smem_u32(smem + AmSmem::W1), smem_u32(smem + AmSmem::W2),
-                 smem_u32(ws + AmSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader, 1u};
+                 tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader, 1u};
     const int first = blockIdx.x + w * (int)gridDim.x;      // worker 1 starts on the CTA's second tile
     mbar_wait(bar_const, 0);
     if (first < a.ntiles) is.mma1<kAfnoE>(0, 0, 0);
@@ -157,14 +160,14 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
       gather(first, nx);
       store_a1(0, nx);
     }
-    // out = x + D2 + b2.  The accumulator rows pass through the worker's A2 buffer (free once D2 is complete), 32 channels
+    // out = x + D2 + b2.  The accumulator rows pass through the worker's staging buffer, 32 channels
     // at a time: thread (row, half) writes its 128 bytes (16-byte units XOR-swizzled by the row: conflict-free), then the
     // 256 threads of the worker add x and the bias and store with a token's 8 units on consecutive lanes: 4 lines of 128
     // bytes per load / store instruction instead of 32 (the L1 data pipe is what bounds this kernel).
     // Fused head (last block, 1x1 patches; fourcastnet.py:349-358): instead of storing `out`, the 8 lanes of a token reduce
     // their share of the 64-channel dot products by shuffles, over both rounds; lane 0 adds the residual frame and writes NCHW.
     auto finish = [&](int tile, uint32_t v_) {
-      uint8_t* stage = ws + AmSmem::A2;
+      uint8_t* stage = ws + AmSmem::Stage;
       mbar_wait(&b[MB_D2FULL + (v_ & 1)], full_par(v_));
       tc_fence_after();
       // head: [row of the thread][output channel], starting from the residual frame (lane 0 of a token's 8 lanes; the loads

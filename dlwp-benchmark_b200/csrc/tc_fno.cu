@@ -515,7 +515,7 @@ namespace {
 struct ProjSmem {   // sized for hid = 256
   static constexpr int W1 = 0, W2 = W1 + 256 * 32 * 4, W1x = W2 + 16 * 256 * 4, Ones = W1x + 256 * 16 * 2, B2 = Ones + 4096,
                        Worker = B2 + 64;
-  static constexpr int X = 0, A2 = X + 2 * kTileBytes, Last = A2 + 2 * kTileBytes, WorkerBytes = Last + 2 * 16 * 512;
+  static constexpr int X = 0, Last = X + 2 * kTileBytes, WorkerBytes = Last + 2 * 16 * 512;
   static constexpr int Total = Worker + 2 * WorkerBytes;      // Last: two slots of [16 channels][128 pixels] fp32
 };
 }  // namespace
@@ -567,7 +567,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + ProjSmem::Worker + w * ProjSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + ProjSmem::X), (uint32_t)kTileBytes, smem_u32(smem + ProjSmem::W1),
-                   smem_u32(smem + ProjSmem::W2), smem_u32(ws + ProjSmem::A2), tmem_s + 256u * w, hid, P, 0u,
+                   smem_u32(smem + ProjSmem::W2), tmem_s + 256u * w, hid, P, 0u,
                    smem_u32(smem + ProjSmem::Ones), smem_u32(smem + ProjSmem::W1x), leader};
       const int first = (int)blockIdx.x + w * (int)gridDim.x;
       mbar_wait(bar_const, 0);
@@ -686,7 +686,7 @@ int launch_tc_proj(const TcProjArgs& a_in, cudaStream_t st) {
 namespace {
 struct LiftSmem {   // sized for hid = 256
   static constexpr int W1 = 0, W2 = W1 + 256 * 16 * 4, F = W2 + 32 * 256 * 4, B2 = F + kFBytes, Worker = B2 + 128;
-  static constexpr int A1 = 0, A2 = A1 + 2 * 8192, Y = A2 + 2 * kTileBytes, WorkerBytes = Y + kTileBytes;
+  static constexpr int A1 = 0, Y = A1 + 2 * 8192, WorkerBytes = Y + kTileBytes;
   static constexpr int Total = Worker + 2 * WorkerBytes;
   static_assert(Total <= 226 * 1024, "lift kernel shared memory");
 };
@@ -746,7 +746,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
       uint64_t* b = bars + w * MB_PER;
       uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
       MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
-                   smem_u32(ws + LiftSmem::A2), tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader};
+                   tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader};
       const uint32_t aF = smem_u32(smem + LiftSmem::F), d3 = tmem_s + 256u * w + 192u;
       const int first = (int)blockIdx.x + w * (int)gridDim.x;
       const bool dft = a.Aout != nullptr;

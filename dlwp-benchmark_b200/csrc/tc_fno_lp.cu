@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
     const int w = warp - kCtlWarp;
     uint64_t* b = bars + w * MB_PER;
     uint8_t* ws = smem + L.Worker + w * L.WorkerBytes;
-    MlpIssuer is{b, 0u, 0u, smem_u32(smem + L.W1), smem_u32(smem + L.W2), 0u, tmem_s + 256u * w, hid, P, 0u,
+    MlpIssuer is{b, 0u, 0u, smem_u32(smem + L.W1), smem_u32(smem + L.W2), tmem_s + 256u * w, hid, P, 0u,
                  smem_u32(smem + L.Ones), smem_u32(smem + L.W1x), leader};
     const uint32_t tA1 = tmem_s + 256u * w + 192u;
     const int first = (int)blockIdx.x + w * (int)gridDim.x;

@@ -96,7 +96,7 @@ struct MlpIssuer {
   uint64_t* b;
   uint32_t aA1;        // two A1 buffers, `a1_stride` bytes apart; lo image at +128*K1*2
   uint32_t a1_stride;
-  uint32_t aW1, aW2, aA2, tmem;
+  uint32_t aW1, aW2, tmem;
   int hid, P;
   uint32_t nc;         // chunks issued so far
   uint32_t aOnes, aW1x;   // optional bias term of the first GEMM: Ones[128,16] * W1x[hid,16]^T (0 = none)
