@@ -692,7 +692,7 @@ struct LiftSmem {   // sized for hid = 256
 };
 }  // namespace
 
-__global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
+__global__ void __launch_bounds__(kCtaLayer, 1) fno_lift_kernel(const TcLiftArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_launch_dependents();
   __shared__ uint64_t bars[2 * MB_PER + 1];
@@ -739,36 +739,44 @@ __global__ void __launch_bounds__(kCta, 1) fno_lift_kernel(const TcLiftArgs a) {
   pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
   const int stride = gridDim.x * 2;
 
-  if (warp >= kCtlWarp) {
-    {
-      const uint32_t leader = elect_one();
-      const int w = warp - kCtlWarp;
-      uint64_t* b = bars + w * MB_PER;
-      uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
-      MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
-                   tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader};
-      const uint32_t aF = smem_u32(smem + LiftSmem::F), d3 = tmem_s + 256u * w + 192u;
-      const int first = (int)blockIdx.x + w * (int)gridDim.x;
-      const bool dft = a.Aout != nullptr;
-      auto finish = [&](int tile, uint32_t n) {
-        ctrl_finish_tile(leader, dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
-                         &b[MB_YFREE], n, TailCfg{1, 2, false});
-      };
-      mbar_wait(bar_const, 0);
-      if (first < g.ntiles) is.mma1<16>(0, 0, 0);
-      uint32_t u = 0;
-      for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
-        const bool has_next = tile + stride < g.ntiles;
-        for (int p = 0; p < P; ++p) {
-          const uint32_t gp = u * P + p;
-          if (p + 1 < P) is.mma1<16>(u, p + 1, gp + 1);
-          else if (has_next) is.mma1<16>(u + 1, 0, gp + 1);
-          if (p == 1 && u > 0) finish(tile - stride, u - 1);      // handed over after the epilogue's first pass of this tile
-          is.mma2<32>(u, p);
-        }
+  if (warp >= kCtlWarp + 2) {
+    // ---------------- finisher lane: forward W-DFT of a handed-over tile, image store ----------------
+    // (its own warp: in the issuer's loop the wait for the hand-over, the chain of W-DFT UMMAs and the bulk store's
+    //  read-completion wait delayed the MLP's UMMAs, and the epilogue group then waited for its next accumulator:
+    //  12 % of this kernel's stall samples)
+    const uint32_t leader = elect_one();
+    const int w = warp - kCtlWarp - 2;
+    uint64_t* b = bars + w * MB_PER;
+    uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
+    const uint32_t aF = smem_u32(smem + LiftSmem::F), d3 = tmem_s + 256u * w + 192u;
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
+    const bool dft = a.Aout != nullptr;
+    mbar_wait(bar_const, 0);
+    uint32_t u = 0;
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u)
+      ctrl_finish_tile(leader, dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
+                       &b[MB_YFREE], u, TailCfg{1, 2, false});
+    bulk_wait0();
+  } else if (warp >= kCtlWarp) {
+    // ---------------- issuer lane: the MLP's UMMAs ----------------
+    const uint32_t leader = elect_one();
+    const int w = warp - kCtlWarp;
+    uint64_t* b = bars + w * MB_PER;
+    uint8_t* ws = smem + LiftSmem::Worker + w * LiftSmem::WorkerBytes;
+    MlpIssuer is{b, smem_u32(ws + LiftSmem::A1), 8192u, smem_u32(smem + LiftSmem::W1), smem_u32(smem + LiftSmem::W2),
+                 tmem_s + 256u * w, hid, P, 0u, 0u, 0u, leader};
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
+    mbar_wait(bar_const, 0);
+    if (first < g.ntiles) is.mma1<16>(0, 0, 0);
+    uint32_t u = 0;
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+      const bool has_next = tile + stride < g.ntiles;
+      for (int p = 0; p < P; ++p) {
+        const uint32_t gp = u * P + p;
+        if (p + 1 < P) is.mma1<16>(u, p + 1, gp + 1);
+        else if (has_next) is.mma1<16>(u + 1, 0, gp + 1);
+        is.mma2<32>(u, p);
       }
-      if (u > 0) finish(first + (int)(u - 1) * stride, u - 1);
-      bulk_wait0();
     }
   } else {
     const EpiId id(tid);
@@ -851,7 +859,7 @@ int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 15 && a.ngrp >= 1, "tensor-core lifting needs 1..15 input channels, got %d", a.Cin);
   // tile t of a CTA's list goes to worker (t / grid) % 2: with fewer tiles than SMs every tile has an SM (and its issue slots) to itself
   const int grid = a.g.ntiles < sms ? a.g.ntiles : sms;
-  DLWP_CUDA(launch_pdl(fno_lift_kernel, dim3(grid), dim3(kCta), (size_t)LiftSmem::Total, st, a));
+  DLWP_CUDA(launch_pdl(fno_lift_kernel, dim3(grid), dim3(kCtaLayer), (size_t)LiftSmem::Total, st, a));
   DLWP_LAUNCHED("fno_lift_kernel");
   return DLWP_OK;
 }
