@@ -691,10 +691,12 @@ __global__ void __launch_bounds__(kWtCta, 1) afno_inv_tc_kernel(const AfnoWTcArg
 #pragma unroll
       for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
         const uint32_t ga = term == 1 ? g_lo : 0u, zb = term == 2 ? z_lo : 0u;
-#pragma unroll 4
-        for (int k0 = 0; k0 < a.KZ; k0 += 16) {
-          umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (k0 >> 4) * zstep), idesc, acc);
-          acc = 1;
+#pragma unroll
+        for (int k0 = 0; k0 < 128; k0 += 16) {      // unrolled with a uniform guard (KZ <= 128: RT * 2 * Kc <= 128)
+          if (k0 < a.KZ) {
+            umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (k0 >> 4) * zstep), idesc, acc);
+            acc = 1;
+          }
         }
       }
       umma_commit_p(leader, &b[IB_DFULL + s]);
@@ -802,7 +804,7 @@ int launch_afno_inv_tc(const AfnoWTcArgs& a, cudaStream_t st) {
   DLWP_TRY(current_sms(&sms));
   DLWP_TRY(ensure_dynamic_smem((const void*)afno_inv_tc_kernel, 226 * 1024));
   const InvSmem L(a.RT, a.Kc, a.KZ);
-  DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= a.KZ && a.KZ % 16 == 0 && L.Total <= 226 * 1024,
+  DLWP_REQUIRE(a.ntiles > 0 && a.RT * a.W == kTcTile && a.RT * 2 * a.Kc <= a.KZ && a.KZ % 16 == 0 && a.KZ <= 128 && L.Total <= 226 * 1024,
                "afno_inv_tc_kernel: unsupported shape");
   const int grid = a.ntiles < sms ? a.ntiles : sms;
   DLWP_CUDA(launch_pdl(afno_inv_tc_kernel, dim3(grid), dim3(kWtCta), (size_t)L.Total, st, a));

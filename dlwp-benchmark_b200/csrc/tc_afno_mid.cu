@@ -193,8 +193,10 @@ __global__ void __launch_bounds__(kThreads, 1) afno_mid_tc_kernel(const AfnoMid2
 #pragma unroll
             for (int term = 0; term < 3; ++term) {      // X_hi W_hi, X_lo W_hi, X_hi W_lo
               const uint32_t xo = term == 1 ? (uint32_t)kPart : 0u, wo = term == 2 ? wlo : 0u;
-              for (int k0 = 0; k0 < 2 * bs; k0 += 16)
-                umma_bf16_p(leader, d2, desc_off(dX, xo + (uint32_t)(k0 >> 3) * 2048u), desc_off(dW, wo + (uint32_t)(k0 >> 3) * wchunk), idesc2, (term | k0) != 0);
+#pragma unroll
+              for (int k0 = 0; k0 < 32; k0 += 16)      // (unrolled with a uniform guard: bs is 8 or 16)
+                if (k0 < 2 * bs)
+                  umma_bf16_p(leader, d2, desc_off(dX, xo + (uint32_t)(k0 >> 3) * 2048u), desc_off(dW, wo + (uint32_t)(k0 >> 3) * wchunk), idesc2, (term | k0) != 0);
             }
           }
           if (layer == 0) umma_commit_p(leader, &bars[MB_D2AFULL + g]);

@@ -431,10 +431,12 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
         for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
           const uint32_t ga = term == 1 ? g_lo : 0u, zb = term == 2 ? z_lo : 0u;
           const uint32_t xa = term == 1 ? (uint32_t)kImg : 0u, wb = term == 2 ? 2048u : 0u;
-#pragma unroll 4
-          for (int k0 = 0; k0 < g.KZ; k0 += 16) {     // operand chunks: 128 (32) rows x 16 bytes per 8 K
-            umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (uint32_t)k0 * 16u), idesc | kIdescBMnMajor, acc);
-            acc = 1;
+#pragma unroll
+          for (int k0 = 0; k0 < 128; k0 += 16) {     // operand chunks: 128 (32) rows x 16 bytes per 8 K; unrolled with a uniform guard
+            if (k0 < g.KZ) {                          // (descriptors stay in uniform registers: no R2UR moves per instruction)
+              umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (uint32_t)k0 * 16u), idesc | kIdescBMnMajor, acc);
+              acc = 1;
+            }
           }
 #pragma unroll
           for (int k0 = 0; k0 < 32; k0 += 16)
@@ -490,7 +492,7 @@ int launch_tc_layer(const TcLayerArgs& a_in, cudaStream_t st) {
   DLWP_TRY(current_sms(&sms));
   DLWP_TRY(ensure_dynamic_smem((const void*)fno_layer_kernel, kLayerSmemMax));
   const LayerSmem L(a.g.KZ, a.ny);
-  DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
+  DLWP_REQUIRE(a.g.KZ >= 16 && a.g.KZ % 16 == 0 && a.g.KZ <= 128 && L.Total <= kLayerSmemMax, "fno_layer_kernel: KZ=%d does not fit", a.g.KZ);
   // tile t of a CTA's list goes to worker (t / grid) % 2: with fewer tiles than SMs every tile has an SM (and its issue slots) to itself
   const int grid = a.g.ntiles < sms ? a.g.ntiles : sms;
   DLWP_CUDA(launch_pdl(fno_layer_kernel, dim3(grid), dim3(kCtaLayerAll), (size_t)L.Total, st, a));

@@ -140,9 +140,12 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
       for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
         const uint32_t ga = term == 1 ? g_lo : 0u, zb = term == 2 ? z_lo : 0u;
         const uint32_t xa = term == 1 ? (uint32_t)kImg : 0u, wb = term == 2 ? 2048u : 0u;
-        for (int k0 = 0; k0 < g.KZ; k0 += 16) {
-          umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (uint32_t)k0 * 16u), idesc | kIdescBMnMajor, acc);
-          acc = 1;
+#pragma unroll
+        for (int k0 = 0; k0 < 128; k0 += 16) {      // (unrolled with a uniform guard: descriptors stay in uniform registers)
+          if (k0 < g.KZ) {
+            umma_bf16_p(leader, d, desc_off(dG, ga + (k0 >> 3) * 2048), desc_off(dZ, zb + (uint32_t)k0 * 16u), idesc | kIdescBMnMajor, acc);
+            acc = 1;
+          }
         }
 #pragma unroll
         for (int k0 = 0; k0 < 32; k0 += 16)
@@ -296,6 +299,6 @@ int launch_tc_layerproj(const TcLayerProjArgs& a_in, cudaStream_t st) {
 }
 
 // largest KZ the fused kernel has shared memory for
-bool tc_layerproj_fits(int KZ) { return KZ >= 16 && KZ % 16 == 0 && LpSmem(KZ).Total <= kLpSmemMax; }
+bool tc_layerproj_fits(int KZ) { return KZ >= 16 && KZ % 16 == 0 && KZ <= 128 && LpSmem(KZ).Total <= kLpSmemMax; }
 
 }  // namespace dlwp

@@ -75,7 +75,7 @@ int main() {
   cudaMalloc(&d, 8);
   cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
   const Case cases[] = {{128, 256, 0, 4}, {128, 128, 0, 4}, {128, 64, 0, 4}, {128, 32, 0, 2}, {128, 16, 0, 1}, {64, 256, 0, 4}, {64, 64, 0, 4},
-                        {64, 256, 1, 4}, {128, 64, 1, 4}, {128, 256, 1, 4},
+                        {64, 256, 1, 4}, {128, 64, 1, 4}, {128, 256, 1, 4}, {64, 64, 1, 4}, {64, 128, 1, 4}, {64, 32, 1, 4},
                         {128, 256, 2, 4}, {128, 128, 2, 4}, {128, 64, 2, 4}, {128, 32, 2, 2}, {64, 256, 2, 4}};
   const int run = 512;
   printf("%5s %5s %7s %12s %12s %14s %12s\n", "M", "N", "layout", "cyc/UMMA", "math cyc", "operand bytes", "bytes/cyc");
