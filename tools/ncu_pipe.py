@@ -13,7 +13,11 @@ for r in rows[2:]:
     if n in seen and "--all" not in sys.argv:
         continue
     seen.add(n)
-    f = lambda k: float(d[k].replace(",", "")) if d.get(k) not in (None, "", "n/a") else 0.0
+    def f(k):
+        try:
+            return float(d.get(k, "").replace(",", ""))
+        except ValueError:      # "", "n/a", "no data"
+            return 0.0
     cyc = f("sm__cycles_elapsed.max")
     lsu = f("SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts.avg")
     lg = f("SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts_mem_lgds.avg")
