@@ -61,10 +61,10 @@ __device__ __forceinline__ void drain_d3(const EpiId& id, int tile, const TcGeom
     tmem_ld16(tmem_d3 + ((uint32_t)(q4 * 32) << 16) + 16u * id.half, r);
     tmem_ld_wait();
     const int row = q4 * 16 + lane;
-    const int h2 = row / g.KXP, rem = row - h2 * g.KXP, kx = rem >> 1, reim = rem & 1;
+    const int kxs = 31 - __clz(g.KXP);      // KXP = 32 / RT is a power of two
+    const int h2 = row >> kxs, rem = row - (h2 << kxs), kx = rem >> 1, reim = rem & 1;
     if (lane < 16 && h2 < g.RT && kx < g.Kc) {
-      const int grow = tile * g.RT + h2;
-      const int b = grow / g.H, h = grow - b * g.H;
+      const int b = tile / g.TPS, h = (tile - b * g.TPS) * g.RT + h2;
       if (g.abf) {
         // split-bf16 operand tiles of fno_mid_tc_kernel: [kx][hi | lo][b][channel group][k = 2h + (re|im)][8 channels]
         uint32_t hi[8], lo[8];
@@ -313,7 +313,8 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
     if (a.Aout != nullptr) {
       const int q = warp - kCtlWarp - 4, lane = tid & 31;
       const int row = q * 16 + lane;
-      const int h2 = row / g.KXP, rem = row - h2 * g.KXP, kx = rem >> 1, reim = rem & 1;
+      const int kxs = 31 - __clz(g.KXP);      // KXP = 32 / RT is a power of two
+      const int h2 = row >> kxs, rem = row - (h2 << kxs), kx = rem >> 1, reim = rem & 1;
       const bool live = lane < 16 && h2 < g.RT && kx < g.Kc;
       const int nd = tail.nd;
       for (uint32_t u = 0;; ++u) {
@@ -337,8 +338,7 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
           __syncwarp();
           if (lane == 0) mbar_arrive(&b[LB_D3EMPTY + sl]);
           if (live) {
-            const int grow = tile * g.RT + h2;
-            const int bb = grow / g.H, h = grow - bb * g.H;
+            const int bb = tile / g.TPS, h = (tile - bb * g.TPS) * g.RT + h2;
             if (g.abf) {
               // split-bf16 operand tiles of fno_mid_tc_kernel: [kx][hi | lo][b][channel group][k = 2h + (re|im)][8 channels]
               uint32_t hi[16], lo[16];
@@ -583,8 +583,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
       // because a generic global load in flight in an epilogue thread would be waited for by its next proxy fence
       auto load_last = [&](int tile, uint32_t u) {
         const int s = u & 1;
-        const long long p0 = (long long)tile * kTcTile;
-        const long long bb = p0 / g.HW, pix = p0 - bb * g.HW;
+        const long long bb = tile / g.TPS, pix = (long long)(tile - (int)bb * g.TPS) * kTcTile;
         mbar_wait(&b[MB_INEMPTY + s], empty_par(u));
         mbar_arrive_expect_tx_p(leader, &b[MB_INFULL + s], (uint32_t)a.Cg * 512u);
         for (int c = 0; c < a.Cg; ++c)
@@ -643,8 +642,7 @@ __global__ void __launch_bounds__(kCta, 1) fno_proj_kernel(const TcProjArgs a) {
         if (c0 + c < a.Cg) o[(long long)(c0 + c) * g.HW] = __uint_as_float(r[c]) + sB2[c0 + c] + lastv[c];
     };
     auto load_last = [&](int tile) {      // output position; without bulk copies also the residual frame values
-      const long long p = (long long)tile * kTcTile + id.row;
-      const long long bb = p / g.HW, pix = p - bb * g.HW;
+      const long long bb = tile / g.TPS, pix = (long long)(tile - (int)bb * g.TPS) * kTcTile + id.row;
       if (!bulk_last) {
 #pragma unroll
         for (int c = 0; c < 8; ++c)
@@ -789,8 +787,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_lift_kernel(const TcLiftArgs
     const int Cin = a.Cin, k0 = 8 * id.half;      // this thread's 8 input columns of its pixel
 
     auto gather = [&](int tile, float (&x)[8]) {
-      const long long p = (long long)tile * kTcTile + id.row;
-      const long long bb = p / g.HW, pix = p - bb * g.HW;
+      const long long bb = tile / g.TPS, pix = (long long)(tile - (int)bb * g.TPS) * kTcTile + id.row;
 #pragma unroll
       for (int k = 0; k < 8; ++k) x[k] = k0 + k < Cin ? kptr[k0 + k][bb * kbs[k0 + k] + pix] : (k0 + k == Cin ? 1.0f : 0.0f);
     };

@@ -38,6 +38,7 @@ struct TcGeom {
   int KZ;              // K extent of the inverse W-DFT operands: 8 per retained column, padded to 16
   int abf;             // the forward W-DFT leaves as split-bf16 operand tiles for fno_mid_tc_kernel (tc_mid2.cu) instead of planar fp32
   int Bn;              // samples of this launch (ntiles * 128 / HW)
+  int TPS;             // tiles per sample = HW / 128 = H / RT (a tile lies within one sample: 32-bit index arithmetic per tile)
 };
 
 struct TcLiftArgs {

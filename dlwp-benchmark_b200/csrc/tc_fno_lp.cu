@@ -171,8 +171,7 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
     // because a generic global load in flight in an epilogue thread would be waited for by its next proxy fence
     auto load_last = [&](int tile, uint32_t u) {
       const int s = u & 1;
-      const long long p0 = (long long)tile * kTcTile;
-      const long long bb = p0 / g.HW, pix = p0 - bb * g.HW;
+      const long long bb = tile / g.TPS, pix = (long long)(tile - (int)bb * g.TPS) * kTcTile;
       mbar_wait(&b[MB_INEMPTY + s], empty_par(u));
       mbar_arrive_expect_tx_p(leader, &b[MB_INFULL + s], (uint32_t)a.proj.Cg * 512u);
       for (int c = 0; c < a.proj.Cg; ++c)
@@ -250,8 +249,7 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
         if (c0 + c < a.proj.Cg) o[(long long)(c0 + c) * g.HW] = __uint_as_float(r[c]) + sB2[c0 + c] + lastv[c];
     };
     auto load_last = [&](int tile) {      // output position; without bulk copies also the residual frame values
-      const long long p = (long long)tile * kTcTile + id.row;
-      const long long bb = p / g.HW, pix = p - bb * g.HW;
+      const long long bb = tile / g.TPS, pix = (long long)(tile - (int)bb * g.TPS) * kTcTile + id.row;
       if (!bulk_last) {
 #pragma unroll
         for (int c = 0; c < 8; ++c)

@@ -30,7 +30,7 @@ int plan_tc_build(dlwp_plan* p) {
   const int KZ = (2 * RT * Kc + 15) & ~15;
   if (d.n_rows > 16 || H % 8 != 0 || KZ > 48 || tc_mid_smem_bytes(H, d.n_rows) > 220 * 1024) return DLWP_OK;
 
-  p->tcg = TcGeom{0, H * W, H, W, RT, KXP, Kc, KZ, 0, 0};
+  p->tcg = TcGeom{0, H * W, H, W, RT, KXP, Kc, KZ, 0, 0, H / RT};
   double s = 1.0, t = 1.0;
   const double hw = (double)H * (double)W;
   if (d.fft_norm == DLWP_FFT_NORM_BACKWARD) t = 1.0 / hw;
