@@ -95,6 +95,18 @@ def test_tc_shape_coverage_increment_matches_oracle(pkg, H, W, modes, lift, proj
     _check_backbone(pkg, "FNO2DModule", kw, B, H, W, seed=7)
 
 
+@pytest.mark.parametrize("layers,Cg,B", [(1, 12, 40), (2, 15, 24), (4, 1, 300)])
+def test_tc_fused_tail_layer_counts_and_output_widths(pkg, layers, Cg, B):
+    """fno_layerproj_kernel (last spectral layer + projection in one launch) right behind the lifting kernel (one layer), with
+    output channels in both column halves of its epilogue threads (12, 15) and with a single one; B = 300: ragged last round
+    of tiles over the CTAs' two workers."""
+    kw = dict(n_modes=[12, 12], constant_channels=2 if Cg == 12 else 0, prescribed_channels=1 if Cg == 12 else 0, prognostic_channels=Cg,
+              hidden_channels=32, lifting_channels=256, projection_channels=256, n_layers=layers, context_size=1)
+    if _cin(kw) > 15:
+        kw["constant_channels"] = kw["prescribed_channels"] = 0
+    _check_backbone(pkg, "FNO2DModule", kw, B, 32, 64, seed=11)
+
+
 def _traj_err(got, want, x0):
     """rms(got_t - want_t) / rms(want_t - x_0) per lead time."""
     d = (got.double() - want.double()).pow(2).mean(dim=(0, 2, 3, 4)).sqrt()
