@@ -191,6 +191,11 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
           for (int co = 0; co < 4; ++co)
             wh[co] = co < a.Cg ? __ldg(reinterpret_cast<const float4*>(a.Wh + co * kAfnoE + 32 * h + 4 * un)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        // the residual rows of the round: requested here, ahead of the accumulator round trip and the barrier
+        float4 xv[4];
+#pragma unroll
+        for (int it = 0; it < 4; ++it)
+          xv[it] = *reinterpret_cast<const float4*>(a.x + ((size_t)tile * kTcTile + it * 32 + (ltid >> 3)) * kAfnoE + 32 * h + 4 * un);
         if (id.half == h) {
           uint32_t r[32];
           tmem_ld32(tmem_row + 128u + 64u * (v_ & 1) + 32u * h, r);
@@ -208,8 +213,8 @@ __global__ void __launch_bounds__(kAmCta, 1) afno_mlp_kernel(const AfnoMlpArgs a
           const int row = it * 32 + (ltid >> 3), c = 32 * h + 4 * un;
           const float4 d = *reinterpret_cast<const float4*>(stage + row * 128 + ((un ^ (row & 7)) << 4));
           const size_t off = ((size_t)tile * kTcTile + row) * kAfnoE + c;
-          const float4 xv = *reinterpret_cast<const float4*>(a.x + off);
-          const float4 v = make_float4(d.x + a.b2c[c] + xv.x, d.y + a.b2c[c + 1] + xv.y, d.z + a.b2c[c + 2] + xv.z, d.w + a.b2c[c + 3] + xv.w);
+          const float4 v = make_float4(d.x + a.b2c[c] + xv[it].x, d.y + a.b2c[c + 1] + xv[it].y, d.z + a.b2c[c + 2] + xv[it].z,
+                                       d.w + a.b2c[c + 3] + xv[it].w);
           if (a.Wh == nullptr) {
             *reinterpret_cast<float4*>(a.out + off) = v;
           } else {
