@@ -30,4 +30,8 @@ struct SpecChain {
   int run(const float* xl, float* yl, const float* add1, const float* add2, const float* bias, int act, cudaStream_t st);
 };
 
+// adjoint bases of a chain whose bases are filled (train_ops.cu): GwH [Kc, W] = conj(Gw)^T, GhH [R, H] = conj(Gh)^T,
+// FhH [H, R] = conj(Fh)^T, FwH [W, Kc] = conj(Fw)^T
+int launch_adjoint_bases(const SpecChain& c, float2* GwH, float2* GhH, float2* FhH, float2* FwH, cudaStream_t st);
+
 }  // namespace dlwp

@@ -160,6 +160,12 @@ struct SpecTrain {
   }
 };
 }  // namespace
+
+int launch_adjoint_bases(const SpecChain& c, float2* GwH, float2* GhH, float2* FhH, float2* FwH, cudaStream_t st) {
+  adjoint_bases_kernel<<<ceil_div(2 * c.Kc * c.W + 2 * c.R * c.H, 256), 256, 0, st>>>(c.Fw, c.Fh, c.Gh, c.Gw, GwH, GhH, FhH, FwH, c.H, c.W, c.R, c.Kc);
+  DLWP_LAUNCHED("adjoint_bases_kernel");
+  return DLWP_OK;
+}
 }  // namespace dlwp
 
 extern "C" int dlwp_linear_forward(const float* x, const float* W, const float* b, const float* pre, float* y, float* z, int P, int K,
@@ -237,8 +243,7 @@ extern "C" int dlwp_spectral_backward(const float* x, const float* weight, const
   const int B = batch, R = n_rows, Kc = n_cols;
   const long long HW = (long long)H * W, K = Kc;
   DLWP_TRY(c.bases(st));
-  adjoint_bases_kernel<<<ceil_div(2 * Kc * W + 2 * R * H, 256), 256, 0, st>>>(c.Fw, c.Fh, c.Gh, c.Gw, t.GwH, t.GhH, t.FhH, t.FwH, H, W, R, Kc);
-  DLWP_LAUNCHED("adjoint_bases_kernel");
+  DLWP_TRY(launch_adjoint_bases(c, t.GwH, t.GhH, t.FhH, t.FwH, st));
   // forward spectrum of x on the retained modes (recomputed, not saved): A = Fw x, X = Fh A
   TdftArgs a{};
   a.in = x; a.out = c.A; a.T = c.Fw; a.N = W; a.K = Kc; a.C = Ci; a.nb0 = B; a.nb1 = H;

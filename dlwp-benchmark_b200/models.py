@@ -84,7 +84,7 @@ class _NativeRollout(nn.Module):
                 raise ValueError(f"{name} has shape {tuple(t.shape)}, expected {(B, frames, ch, H, W)}")
         return B, T, Cg, H, W
 
-    # training (scripts/train.py:263-271): FNO2DModule / TFNO2DModule route to training.py under grad mode
+    # training (scripts/train.py:263-271): the modules route to training.py under grad mode
     _trainable = False
 
     def _needs_grad(self, *tensors):
@@ -105,7 +105,7 @@ class _NativeRollout(nn.Module):
         if self._needs_grad(constants, prescribed, prognostic):      # autograd path on the fp32 training primitives
             from . import training
             with torch.cuda.device(dev):
-                return training.fno_rollout(self, constants, prescribed, prognostic)
+                return training.rollout(self, constants, prescribed, prognostic)
         with torch.cuda.device(dev):
             plan = self._plan_for(dev, B, H, W)
             c, p, g = self._f32c(constants), self._f32c(prescribed), self._f32c(prognostic)
@@ -140,7 +140,7 @@ class _NativeRollout(nn.Module):
                 raise NotImplementedError("forward-only: call under torch.no_grad()")
             from . import training
             with torch.cuda.device(x.device):
-                return training.fno_backbone(self, x)
+                return training.backbone(self, x)
         B, _, H, W = x.shape
         with torch.cuda.device(x.device):
             plan = self._plan_for(x.device, B, H, W)
@@ -379,6 +379,8 @@ class _PatchEmbedParams(nn.Module):
 class AFNONet(_NativeRollout):
     """``models/fourcastnet/fourcastnet.py:214-361`` with the ``AFNO2D`` filter (``:60-127``) or the ``FNO2D`` filter
     (``:130-153``: a one-layer neuralop FNO as the token mixer)."""
+
+    _trainable = True   # training.afno_backbone
 
     def __init__(self, img_height: int = 720, img_width: int = 1440, patch_size: tuple = (16, 16),
                  constant_channels: int = 4, prescribed_channels: int = 0, prognostic_channels: int = 1,

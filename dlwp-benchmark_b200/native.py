@@ -76,6 +76,12 @@ SYMBOLS = {
     "dlwp_spectral_train_workspace": (C.c_int, [C.c_int] * 7 + [C.POINTER(C.c_size_t)]),
     "dlwp_spectral_forward": (C.c_int, [_P] * 3 + [C.c_int] * 7 + [C.POINTER(C.c_int32)] * 2 + [C.c_int, _P, C.c_size_t, _P]),
     "dlwp_spectral_backward": (C.c_int, [_P] * 5 + [C.c_int] * 7 + [C.POINTER(C.c_int32)] * 2 + [C.c_int, _P, C.c_size_t, _P]),
+    "dlwp_layernorm_forward": (C.c_int, [_P] * 4 + [C.c_int, C.c_int, C.c_float, _P]),
+    "dlwp_layernorm_backward": (C.c_int, [_P] * 6 + [C.c_int, C.c_int, C.c_float, _P]),
+    "dlwp_afno_filter_workspace": (C.c_int, [C.c_int] * 7 + [C.POINTER(C.c_size_t)]),
+    "dlwp_afno_filter_forward": (C.c_int, [_P] * 7 + [C.c_int] * 6 + [C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_float, _P, C.c_size_t, _P]),
+    "dlwp_afno_filter_backward": (C.c_int, [_P] * 11 + [C.c_int] * 6 + [C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_float, _P, C.c_size_t,
+                                            _P]),
     "dlwp_nchw_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_nhwc_to_nchw": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dlwp_launch_count": (C.c_int64, []),

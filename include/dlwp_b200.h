@@ -238,6 +238,28 @@ int dlwp_spectral_forward(const float* x, const float* weight, float* y, int bat
 int dlwp_spectral_backward(const float* x, const float* weight, const float* dy, float* dx, float* dweight, int batch, int Ci, int Co,
                            int H, int W, int n_rows, int n_cols, const int32_t* rows_in, const int32_t* rows_out, int fft_norm,
                            void* workspace, size_t workspace_bytes, void* stream);
+/* LayerNorm over the channel axis of channels-last tokens x [P, C] (fourcastnet.py:170,174: nn.LayerNorm(dim, eps=1e-6)),
+ * biased variance, eps inside the square root.  backward recomputes the row statistics from x:
+ * dx = rstd (g - mean(g) - xhat mean(g xhat)) with g = dy gamma; dgamma = column sums of dy xhat, dbeta = column sums of dy. */
+int dlwp_layernorm_forward(const float* x, const float* gamma, const float* beta, float* y, int P, int C, float eps, void* stream);
+int dlwp_layernorm_backward(const float* dy, const float* x, const float* gamma, float* dx, float* dgamma, float* dbeta, int P,
+                            int C, float eps, void* stream);
+/* The AFNO2D token mixer (fourcastnet.py:60-127) on channels-last tokens x [B, h, w, C]:
+ *   y = irfft2( softshrink( relu(X w1 + b1) w2 + b2 ) ) + x (+ extra),  X = rfft2(x, norm="ortho")[rows, :n_cols]
+ * with the block-diagonal complex weights in the reference's layout: w1 [2, nb, bs, bs f], b1 [2, nb, bs f], w2 [2, nb, bs f, bs],
+ * b2 [2, nb, bs] (bs = C / nb), ReLU and softshrink on real and imaginary parts separately.  `rows` = the n_rows retained rows
+ * (the same bins on the way back), `extra` [B, h, w, C] | NULL is added to the result (Block's second skip, :185-187).
+ * backward: dx = adjoint chain + dy (NULL: skipped; the gradient of `extra` is dy itself), dw1 / db1 / dw2 / db2 in the
+ * parameters' own layouts.  The spectrum is recomputed from x, nothing is saved between the two calls.
+ * workspace: dlwp_afno_filter_workspace bytes (device, 256-byte aligned). */
+int dlwp_afno_filter_workspace(int batch, int C, int h, int w, int n_rows, int n_cols, int hidden_factor, size_t* bytes);
+int dlwp_afno_filter_forward(const float* x, const float* extra, const float* w1, const float* b1, const float* w2, const float* b2,
+                             float* y, int batch, int C, int h, int w, int n_rows, int n_cols, const int32_t* rows, int num_blocks,
+                             int hidden_factor, float lambda, void* workspace, size_t workspace_bytes, void* stream);
+int dlwp_afno_filter_backward(const float* x, const float* w1, const float* b1, const float* w2, const float* b2, const float* dy,
+                              float* dx, float* dw1, float* db1, float* dw2, float* db2, int batch, int C, int h, int w, int n_rows,
+                              int n_cols, const int32_t* rows, int num_blocks, int hidden_factor, float lambda, void* workspace,
+                              size_t workspace_bytes, void* stream);
 /* layout changes between the reference's NCHW tensors and the channels-last form above */
 int dlwp_nchw_to_nhwc(const float* in, float* out, int B, int C, int HW, void* stream);
 int dlwp_nhwc_to_nchw(const float* in, float* out, int B, int C, int HW, void* stream);

@@ -208,18 +208,19 @@ def test_tensor_core_mode_falls_back_to_fp32_kernels_on_other_shapes(pkg):
     assert max_rel(got, want) < TOL_STEP
 
 
-def test_fno_rejects_cpu_inputs_and_fourcastnet_rejects_grad_mode(pkg):
+def test_cpu_inputs_and_grad_mode_guards(pkg):
     _, mod, kw, (B, H, W) = _fno_pair(pkg, "odd")
     const, presc, prog = synthetic(B, 3, 1, 0, 2, H, W)
     with torch.no_grad(), pytest.raises(RuntimeError):
         mod(constants=const, prescribed=None, prognostic=prog)
     with pytest.raises(NotImplementedError):      # the host entry is inference-only
         mod.forward_host(constants=const, prescribed=None, prognostic=prog)
-    # FourCastNet has no training path: grad mode raises instead of returning a tensor without a graph
+    # grad mode returns a tensor with a graph (training path, tests/test_training_gpu.py), never one without
     amod = pkg.FourCastNet(img_height=16, img_width=32, patch_size=[1, 1], constant_channels=0, prescribed_channels=0,
                            prognostic_channels=3, embed_dim=32, depth=1, num_blocks=4, context_size=1).cuda()
+    assert amod(prognostic=torch.randn(1, 2, 3, 16, 32, device="cuda")).requires_grad
     with pytest.raises(NotImplementedError):
-        amod(prognostic=torch.randn(1, 2, 3, 16, 32, device="cuda"))
+        amod.forward_host(prognostic=torch.randn(1, 2, 3, 16, 32))
 
 
 # ---------------------------------------------------------------------------------------
