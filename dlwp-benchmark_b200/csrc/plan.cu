@@ -7,6 +7,7 @@
 #include "plan.cuh"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <utility>
@@ -30,6 +31,9 @@ int current_sms(int* sms) {
   std::lock_guard<std::mutex> lock(g_dev_mutex);
   if (!g_dev_sms[dev]) DLWP_CUDA(cudaDeviceGetAttribute(&g_dev_sms[dev], cudaDevAttrMultiProcessorCount, dev));
   *sms = g_dev_sms[dev];
+  // DLWP_SM_LIMIT=n: persistent grids of at most n CTAs (two plans on two streams then share the device side by side)
+  static const int cap = [] { const char* e = std::getenv("DLWP_SM_LIMIT"); return e ? std::atoi(e) : 0; }();
+  if (cap > 0 && cap < *sms) *sms = cap;
   return DLWP_OK;
 }
 

@@ -794,9 +794,15 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_lift_kernel(const TcLiftArgs
     auto store_a1 = [&](uint32_t u, const float (&x)[8]) {   // column Cin carries the 1 that multiplies the bias
       const int s = u & 1;
       mbar_wait(&b[MB_A1EMPTY + s], empty_par(u));
+      // the gathered values are first touched here: without this the compiler hoists the splits to right behind the loads and
+      // the epilogue group sits out the gather's latency at the top of every tile (6 % of the kernel's stall samples)
+      float xs[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) xs[k] = x[k];
+      asm volatile("" : "+f"(xs[0]), "+f"(xs[1]), "+f"(xs[2]), "+f"(xs[3]), "+f"(xs[4]), "+f"(xs[5]), "+f"(xs[6]), "+f"(xs[7]));
       uint32_t h[4], l[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) split2(x[2 * j], x[2 * j + 1], h[j], l[j]);
+      for (int j = 0; j < 4; ++j) split2(xs[2 * j], xs[2 * j + 1], h[j], l[j]);
       uint8_t* d = ws + LiftSmem::A1 + s * 8192 + id.half * 2048 + id.row * 16;
       *reinterpret_cast<uint4*>(d) = make_uint4(h[0], h[1], h[2], h[3]);
       *reinterpret_cast<uint4*>(d + 4096) = make_uint4(l[0], l[1], l[2], l[3]);
