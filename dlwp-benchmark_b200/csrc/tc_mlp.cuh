@@ -103,10 +103,21 @@ struct MlpIssuer {
   uint32_t leader;        // elect_one() of the (converged) control warp
   uint32_t a1_single;     // 1: one A1 buffer (ring of depth 1) instead of two
 
+  // Accumulator buffer gp & 1 was last the A operand of the second GEMM of pass gp - 2.  Those UMMAs were issued by this same
+  // thread before the ones that now overwrite the buffer, and tcgen05.mma instructions of one thread execute in issue order
+  // (operand reads at the head of the pipeline, accumulator writes at its tail), so no completion round trip through
+  // D1EMPTY is needed: it cost commit -> mbarrier -> wake-up per pass and left the epilogue group waiting for its next
+  // accumulator (7 % of the stall samples of the lift and layer+projection kernels).  -DDLWP_D1EMPTY_WAIT restores the wait.
+  __device__ __forceinline__ void d1_reuse_wait([[maybe_unused]] int db, [[maybe_unused]] uint32_t gp) {
+#ifdef DLWP_D1EMPTY_WAIT
+    mbar_wait(&b[MB_D1EMPTY + db], empty_par(gp));
+#endif
+  }
+
   template <int K1>
   __device__ __forceinline__ void mma1(uint32_t u, int p, uint32_t gp) {
     const int db = gp & 1, ub = a1_single ? 0 : (u & 1);
-    mbar_wait(&b[MB_D1EMPTY + db], empty_par(gp));
+    d1_reuse_wait(db, gp);
     if (p == 0) mbar_wait(&b[MB_A1FULL + ub], a1_single ? (u & 1u) : full_par(u));
     tc_fence_after();
     const uint32_t idesc = idesc_bf16(128, 64);
@@ -137,7 +148,7 @@ struct MlpIssuer {
   template <int K1>
   __device__ __forceinline__ void mma1_ts(uint32_t tA1, uint32_t u, int p, uint32_t gp) {
     const int db = gp & 1, ub = u & 1;
-    mbar_wait(&b[MB_D1EMPTY + db], empty_par(gp));
+    d1_reuse_wait(db, gp);
     if (p == 0) mbar_wait(&b[MB_A1FULL + ub], full_par(u));
     tc_fence_after();
     const uint32_t idesc = idesc_bf16(128, 64);
@@ -186,7 +197,9 @@ struct MlpIssuer {
       }
       __syncwarp();
     }
+#ifdef DLWP_D1EMPTY_WAIT
     umma_commit_p(leader, &b[MB_D1EMPTY + db]);      // the accumulator buffer (now the consumed A operand) goes back to the first GEMM
+#endif
     if (p == P - 1) umma_commit_p(leader, &b[MB_D2FULL + (u & 1)]);
   }
 };
