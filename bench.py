@@ -297,7 +297,7 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False, fused_tail=False):
         return b * N * ((px * C + half) + (half + modes) + (modes + half) + (half + 2 * px * C + px * C))
     if name == "mix_dense_kernel":
         return b * N * (2 * B * m1 * m2 * C * 2 + m1 * m2 * C * C * 2)
-    if name == "fno_lift_kernel":       # fused lifting MLP (+ forward W-DFT of its output)
+    if name in ("fno_lift_kernel", "fno_lift4_kernel"):       # fused lifting MLP (+ forward W-DFT of its output)
         return b * px * (cin + C) + b * B * H * m2 * C * 2
     if name == "fno_layer_kernel":      # fused inverse W-DFT + skip + GELU (+ forward W-DFT, not after the last layer)
         if fused_tail:                  # the last layer runs inside fno_layerproj_kernel: N - 1 launches, each with a forward W-DFT

@@ -30,7 +30,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
     # DLWP_TRACE=1: clock64 timestamps of the layer kernel's pipeline events (tools/trace_layer.py)
     trace = bool(os.environ.get("DLWP_TRACE"))
     extra = ["-DDLWP_TRACE"] if trace else []
-    objdir = os.path.join(HERE, "_build_trace" if trace else "_build")
+    more = os.environ.get("DLWP_NVCC_EXTRA", "").split()      # experiment builds (-DNAME=value), in their own object directory
+    extra += more
+    objdir = os.path.join(HERE, "_build_x" if more else "_build_trace" if trace else "_build")
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if not f.endswith(".cu")]
     headers.append(os.path.join(HERE, "..", "include", "dlwp_b200.h"))

@@ -68,6 +68,7 @@ struct dlwp_plan {
           *tc_projW1x = nullptr;
   std::vector<uint8_t*> tc_skip;                        // per layer skip-conv images
   bool tc_mid2 = false;                                 // the retained-column products run on tcgen05 (fno_mid_tc_kernel, tc_mid2.cu)
+  bool tc_lift4 = false;                                // lifting kernel with four workers per CTA (fno_lift4_kernel)
   bool tc_fuse_proj = false;                            // last layer + projection in one launch (fno_layerproj_kernel)
   uint8_t *tc_midF = nullptr, *tc_midG = nullptr;       // (re|im)-stacked forward / inverse H-DFT operand images
   std::vector<uint8_t*> tc_midW;                        // per layer mode-weight operand images [Kc][R][8 KB]

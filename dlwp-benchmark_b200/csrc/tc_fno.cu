@@ -1,6 +1,7 @@
 // tcgen05 kernels of the FNO / TFNO step (see tc_fno.cuh for the data layout and the split).
 #include "tc_fno.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 #include "tc_mlp.cuh"
@@ -856,6 +857,269 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_lift_kernel(const TcLiftArgs
   if (warp == kCtlWarp) tmem_dealloc(tmem_s, 512);
 }
 
+// =============================================================================================
+// fno_lift4_kernel: the same lifting MLP with FOUR workers of four epilogue warps per CTA.
+// What bounds the two-worker kernel is the FMA pipe while both workers are in their GELU passes, and nothing while one of
+// them gathers, hands a tile over or waits for an accumulator (a worker is in the GELU arithmetic 48 % of the time: the pipe
+// averages 0.23 x 1 + 0.5 x 0.5 = 48 %, ncu: 49.5 %).  Four workers with independent phases keep it fed: a thread owns its
+// pixel's whole 32-column chunk (one chunk per pass, two accumulator buffers), the tile's second accumulator is single
+// buffered and read at the end of the tile, and the W-DFT accumulator is drained before the next hand-over: 128
+// tensor-memory columns per worker.
+//   worker w: epilogue warps 4 w .. 4 w + 3, issuer warp 16 + w, finisher warp 20 + w;  tiles blockIdx.x + (w + 4 n) gridDim.x
+// =============================================================================================
+namespace {
+constexpr int kL4Workers = 4, kL4Epi = 128, kL4Iss = 16, kL4Fin = 20, kL4Cta = 24 * 32;
+enum { L4_A1FULL = 0 /* two */, L4_A1EMPTY = 2 /* two */, L4_D1FULL = 4 /* two */, L4_A2FULL = 6 /* two */, L4_D2FULL = 8, L4_D2EMPTY = 9,
+       L4_XTFULL = 10, L4_D3FULL = 11, L4_YFREE = 12, L4_PER = 13 };
+struct Lift4Smem {   // sized for hid = 256
+  static constexpr int W1 = 0, W2 = W1 + 256 * 16 * 4, F = W2 + 32 * 256 * 4, B2 = F + kFBytes, Worker = B2 + 128;
+  static constexpr int A1 = 0, Y = A1 + 2 * 8192, WorkerBytes = Y + kTileBytes;
+  static constexpr int Total = Worker + kL4Workers * WorkerBytes;
+  static_assert(Total <= 226 * 1024, "lift4 kernel shared memory");
+};
+}  // namespace
+
+__global__ void __launch_bounds__(kL4Cta, 1) fno_lift4_kernel(const TcLiftArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
+  __shared__ uint64_t bars[kL4Workers * L4_PER + 1];
+  __shared__ uint32_t tmem_s;
+  __shared__ const float* kptr[16];     // per input channel: plane base and batch stride
+  __shared__ long long kbs[16];
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform
+  const TcGeom g = a.g;
+  const int hid = a.hid, P = hid / 32;      // passes of one 32-column chunk
+  float* sB2 = reinterpret_cast<float*>(smem + Lift4Smem::B2);
+  uint64_t* bar_const = &bars[kL4Workers * L4_PER];
+
+  if (tid == 0) {
+    for (int w = 0; w < kL4Workers; ++w) {
+      uint64_t* b = bars + w * L4_PER;
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&b[L4_A1FULL + i], kL4Epi);
+        mbar_init(&b[L4_A1EMPTY + i], 1);
+        mbar_init(&b[L4_D1FULL + i], 1);
+        mbar_init(&b[L4_A2FULL + i], kL4Epi);
+      }
+      mbar_init(&b[L4_D2FULL], 1);
+      mbar_init(&b[L4_D2EMPTY], kL4Epi);
+      mbar_init(&b[L4_XTFULL], 2 * kL4Epi);      // finish_tile arrives once per 16-channel half
+      mbar_init(&b[L4_D3FULL], 1);
+      mbar_init(&b[L4_YFREE], 1);
+    }
+    mbar_init(bar_const, 1);
+    fence_mbar_init();
+    int k = 0;     // channel order: constants | prescribed (t, c) | prognostic (t, c)  (fno.py:58-62)
+    for (int gi = 0; gi < a.ngrp; ++gi)
+      for (int ch = 0; ch < a.grp[gi].nch && k < 16; ++ch, ++k) {
+        kptr[k] = a.grp[gi].base + (long long)ch * g.HW;
+        kbs[k] = a.grp[gi].bstride;
+      }
+    for (; k < 16; ++k) {
+      kptr[k] = a.grp[0].base;
+      kbs[k] = 0;
+    }
+  }
+  if (warp == kL4Iss) {
+    tmem_alloc(&tmem_s, 512);
+    tmem_relinquish();
+  }
+  if (tid < 32) sB2[tid] = a.b2[tid];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t w1_bytes = (uint32_t)hid * 16 * 4, w2_bytes = 32u * hid * 4;
+  if (tid == 0) {   // constant operands: requested before the programmatic-dependent-launch wait
+    mbar_arrive_expect_tx(bar_const, w1_bytes + w2_bytes + kFBytes);
+    bulk_g2s(smem + Lift4Smem::W1, a.W1img, w1_bytes, bar_const);
+    bulk_g2s(smem + Lift4Smem::W2, a.W2img, w2_bytes, bar_const);
+    bulk_g2s(smem + Lift4Smem::F, a.Fimg, kFBytes, bar_const);
+  }
+  pdl_wait();   // everything below reads what the previous kernel wrote (or overwrites what it read)
+  const int stride = gridDim.x * kL4Workers;
+  const bool dft = a.Aout != nullptr;
+
+  if (warp >= kL4Fin) {
+    // ---------------- finisher lane: forward W-DFT of a handed-over tile, image store ----------------
+    const uint32_t leader = elect_one();
+    const int w = warp - kL4Fin;
+    uint64_t* b = bars + w * L4_PER;
+    uint8_t* ws = smem + Lift4Smem::Worker + w * Lift4Smem::WorkerBytes;
+    const uint32_t aF = smem_u32(smem + Lift4Smem::F), d3 = tmem_s + 128u * w + 96u;
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
+    mbar_wait(bar_const, 0);
+    uint32_t u = 0;
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u)
+      ctrl_finish_tile(leader, dft, aF, ws + Lift4Smem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[L4_XTFULL], &b[L4_D3FULL],
+                       &b[L4_YFREE], u, TailCfg{1, 1, false});
+    bulk_wait0();
+  } else if (warp >= kL4Iss) {
+    // ---------------- issuer lane: the MLP's UMMAs, one 32-column chunk per pass ----------------
+    // (the first GEMM of pass n + 1 overwrites the buffer the second GEMM of pass n - 1 read as its operand: issued by this
+    //  thread after it, and tcgen05.mma instructions of one thread execute in issue order)
+    const uint32_t leader = elect_one();
+    const int w = warp - kL4Iss;
+    uint64_t* b = bars + w * L4_PER;
+    const uint32_t tmem_w = tmem_s + 128u * w;
+    const uint32_t aA1 = smem_u32(smem + Lift4Smem::Worker + w * Lift4Smem::WorkerBytes + Lift4Smem::A1);
+    const uint32_t aW1 = smem_u32(smem + Lift4Smem::W1), aW2 = smem_u32(smem + Lift4Smem::W2);
+    const uint32_t idesc = idesc_bf16(128, 32);
+    auto mma1 = [&](uint32_t u, int p, uint32_t gp) {
+      const uint32_t ub = u & 1u;
+      if (p == 0) mbar_wait(&b[L4_A1FULL + ub], full_par(u));
+      tc_fence_after();
+      const uint64_t dA = chunk_desc(aA1 + ub * 8192u, 128, 0), dW = smem_desc(aW1 + (uint32_t)p * 32 * 16, (uint32_t)hid * 16, 128);
+      const uint32_t d = tmem_w + 32u * (gp & 1u);
+      umma_bf16_p(leader, d, dA, dW, idesc, 0);                                           // hi * hi
+      umma_bf16_p(leader, d, desc_off(dA, 128 * 16 * 2), dW, idesc, 1);                   // lo * hi
+      umma_bf16_p(leader, d, dA, desc_off(dW, (uint32_t)hid * 16 * 2), idesc, 1);         // hi * lo
+      umma_commit_p(leader, &b[L4_D1FULL + (gp & 1u)]);
+      if (p == P - 1) umma_commit_p(leader, &b[L4_A1EMPTY + ub]);
+      __syncwarp();
+    };
+    auto mma2 = [&](uint32_t u, int p, uint32_t gp) {
+      mbar_wait(&b[L4_A2FULL + (gp & 1u)], (gp >> 1) & 1u);
+      if (p == 0) mbar_wait(&b[L4_D2EMPTY], (u & 1u) ^ 1u);
+      tc_fence_after();
+      const uint64_t dW = chunk_desc(aW2, 32, p * 32);
+      const uint32_t a2 = tmem_w + 32u * (gp & 1u), w_lo = 32u * (uint32_t)hid * 2;      // [K step 0: hi 8 columns | lo 8][K step 1: hi | lo]
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {      // hi*hi, lo*hi, hi*lo
+        const uint32_t ao = term == 1 ? 8u : 0u, wo = term == 2 ? w_lo : 0u;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk)
+          umma_ts_bf16_p(leader, tmem_w + 64u, a2 + 16u * kk + ao, desc_off(dW, wo + (uint32_t)kk * 2 * 32 * 16), idesc, (p | term | kk) != 0);
+      }
+      if (p == P - 1) umma_commit_p(leader, &b[L4_D2FULL]);
+      __syncwarp();
+    };
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
+    mbar_wait(bar_const, 0);
+    if (first < g.ntiles) mma1(0, 0, 0);
+    uint32_t u = 0;
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+      const bool has_next = tile + stride < g.ntiles;
+      for (int p = 0; p < P; ++p) {
+        const uint32_t gp = u * (uint32_t)P + (uint32_t)p;
+        if (p + 1 < P) mma1(u, p + 1, gp + 1);
+        else if (has_next) mma1(u + 1, 0, gp + 1);
+        mma2(u, p, gp);
+      }
+    }
+  } else {
+    // ------------------------------ epilogue warps: thread = pixel of the tile ------------------------------
+    const int w = warp >> 2, q4 = warp & 3, row = q4 * 32 + (tid & 31);
+    uint64_t* b = bars + w * L4_PER;
+    uint8_t* ws = smem + Lift4Smem::Worker + w * Lift4Smem::WorkerBytes;
+    const uint32_t tmem_w = tmem_s + 128u * w, tmem_lane = tmem_w + ((uint32_t)(q4 * 32) << 16);
+    const int Cin = a.Cin;
+    EpiId id(tid);      // for the shared tail helpers: .half selects the 16-channel half a call works on
+    id.w = w;
+    id.q4 = q4;
+    id.row = row;
+
+    // x_t of the thread's pixel (column Cin carries the 1 that multiplies the bias) -> split-bf16 operand rows.  Loaded and
+    // used in one go: the other three workers run meanwhile.
+    auto load_a1 = [&](int tile, uint32_t u) {
+      const long long bb = tile / g.TPS, pix = (long long)(tile - (int)bb * g.TPS) * kTcTile + row;
+      float x[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) x[k] = k < Cin ? kptr[k][bb * kbs[k] + pix] : (k == Cin ? 1.0f : 0.0f);
+      const int s = u & 1;
+      mbar_wait(&b[L4_A1EMPTY + s], empty_par(u));
+      uint8_t* d = ws + Lift4Smem::A1 + s * 8192 + row * 16;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {      // K chunks of 8 columns
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) split2(x[8 * c + 2 * j], x[8 * c + 2 * j + 1], h[j], l[j]);
+        *reinterpret_cast<uint4*>(d + c * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(d + 4096 + c * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
+      }
+      fence_async_smem();
+      mbar_arrive(&b[L4_A1FULL + s]);
+    };
+    // the tile's output: second accumulator + bias -> split-bf16 image for the finisher lane; the W-DFT accumulator of the
+    // tile before is drained first (one accumulator per worker)
+    int prev_tile = -1;
+    auto finish = [&](int tile, uint32_t u) {
+      if (dft && prev_tile >= 0) {
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          id.half = hf;
+          drain_d3(id, prev_tile, g, a.Aout, tmem_w + 96u, &b[L4_D3FULL], u - 1);
+        }
+      }
+      mbar_wait(&b[L4_D2FULL], u & 1u);
+      tc_fence_after();
+      uint32_t r[32];
+      tmem_ld32(tmem_lane + 64u, r);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&b[L4_D2EMPTY]);
+      if (u > 0) mbar_wait(&b[L4_YFREE], (u - 1) & 1u);      // the bulk store and the W-DFT UMMAs of the tile before have read the image
+      uint8_t* dst = ws + Lift4Smem::Y + row * 16;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {      // channel groups of 8
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int ch = 8 * c + 2 * j;
+          split2p(make_float2(__uint_as_float(r[ch]) + sB2[ch], __uint_as_float(r[ch + 1]) + sB2[ch + 1]), hi[j], lo[j]);
+        }
+        *reinterpret_cast<uint4*>(dst + c * 2048) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + kImg + c * 2048) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      }
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(&b[L4_XTFULL]);
+      mbar_arrive(&b[L4_XTFULL]);
+      prev_tile = tile;
+    };
+
+    const int first = (int)blockIdx.x + w * (int)gridDim.x;
+    if (first < g.ntiles) load_a1(first, 0);
+    const int a1_pass = P >= 4 ? P - 3 : 0;      // the issuer wants the next tile's operand behind this tile's last pass
+    uint32_t u = 0, gp = 0;
+    for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
+      const bool has_next = tile + stride < g.ntiles;
+      for (int p = 0; p < P; ++p, ++gp) {
+        const uint32_t buf = gp & 1u, t = tmem_lane + 32u * buf;
+        mbar_wait(&b[L4_D1FULL + buf], (gp >> 1) & 1u);
+        tc_fence_after();
+        uint32_t r[32];
+        tmem_ld32(t, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {      // K steps of the second GEMM: 16 hidden columns -> 8 columns of hi pairs + 8 of lo pairs
+          uint32_t h[8], l[8];
+          float2 g2[8];             // 2 * gelu: W2's operand image is packed with the factor 1/2
+          gelu2x_8(reinterpret_cast<const uint32_t (&)[16]>(r[16 * hf]), g2);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) split2p(g2[e], h[e], l[e]);
+          tmem_st8(t + 16u * hf, h);
+          tmem_st8(t + 16u * hf + 8u, l);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&b[L4_A2FULL + buf]);
+        if (p == a1_pass && has_next) load_a1(tile + stride, u + 1);
+      }
+      finish(tile, u);
+    }
+    if (dft && prev_tile >= 0) {      // the last tile's W-DFT accumulator
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        id.half = hf;
+        drain_d3(id, prev_tile, g, a.Aout, tmem_w + 96u, &b[L4_D3FULL], u - 1);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kL4Iss) tmem_dealloc(tmem_s, 512);
+}
+
 int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
   int sms = 0;
   DLWP_TRY(current_sms(&sms));
@@ -864,6 +1128,13 @@ int launch_tc_lift(const TcLiftArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 15 && a.ngrp >= 1, "tensor-core lifting needs 1..15 input channels, got %d", a.Cin);
   // tile t of a CTA's list goes to worker (t / grid) % 2: with fewer tiles than SMs every tile has an SM (and its issue slots) to itself
   const int grid = a.g.ntiles < sms ? a.g.ntiles : sms;
+  // four workers per CTA once each of them has a tile (a.workers4: plan option, DLWP_LIFT4=0 keeps the two-worker kernel)
+  if (a.workers4 && a.g.ntiles >= 4 * sms) {
+    DLWP_TRY(ensure_dynamic_smem((const void*)fno_lift4_kernel, Lift4Smem::Total));
+    DLWP_CUDA(launch_pdl(fno_lift4_kernel, dim3(grid), dim3(kL4Cta), (size_t)Lift4Smem::Total, st, a));
+    DLWP_LAUNCHED("fno_lift4_kernel");
+    return DLWP_OK;
+  }
   DLWP_CUDA(launch_pdl(fno_lift_kernel, dim3(grid), dim3(kCtaLayer), (size_t)LiftSmem::Total, st, a));
   DLWP_LAUNCHED("fno_lift_kernel");
   return DLWP_OK;

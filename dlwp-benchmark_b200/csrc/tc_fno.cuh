@@ -47,6 +47,7 @@ struct TcLiftArgs {
   int ngrp;
   int Cin;             // <= 15 (column Cin of the first GEMM carries the bias)
   int hid;             // lifting width: 128 or 256
+  int workers4;        // the four-worker kernel (fno_lift4_kernel) when every worker has a tile
   const uint8_t* W1img;   // [hi | lo] images, R = hid rows, K = 16
   const uint8_t* W2img;   // [hi | lo] images, R = 32 rows, K = hid
   const float* b2;        // [32]

@@ -81,6 +81,11 @@ int plan_tc_build(dlwp_plan* p) {
   for (int l = 0; l < d.n_layers; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tc_skip[l], 4096));
   // H-DFT, mode mixing and inverse H-DFT on tcgen05 where the geometry allows it (DLWP_MID_FMA=1 keeps the fp32 FMA kernel: A/B runs)
   p->tc_mid2 = tc_mid2_samples(H, d.n_rows) != 0 && std::getenv("DLWP_MID_FMA") == nullptr;
+  // DLWP_LIFT4=0 keeps the two-worker lifting kernel at every batch size (A/B runs)
+  {
+    const char* e = std::getenv("DLWP_LIFT4");
+    p->tc_lift4 = e == nullptr || std::atoi(e) != 0;
+  }
   // the last layer and the projection as one kernel (DLWP_NO_FUSE_PROJ=1 keeps the two launches: A/B runs)
   p->tc_fuse_proj = d.n_layers >= 1 && tc_layerproj_fits(KZ) && std::getenv("DLWP_NO_FUSE_PROJ") == nullptr;
   if (p->tc_mid2) {
@@ -193,6 +198,7 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   for (int i = 0; i < io.ngrp; ++i) la.grp[i] = io.grp[i];
   la.Cin = p->Cin;
   la.hid = d.lifting_channels;
+  la.workers4 = p->tc_lift4 ? 1 : 0;
   la.W1img = p->tc_liftW1;
   la.W2img = p->tc_liftW2;
   la.b2 = b2;

@@ -225,10 +225,11 @@ def test_rollout_is_cuda_graph_capturable(pkg, case):
     assert torch.equal(out, want1) and not torch.equal(want1, want0)
 
 
-@pytest.mark.parametrize("knob", ["DLWP_NO_FUSE_PROJ", "DLWP_MID_FMA"])
+@pytest.mark.parametrize("knob", ["DLWP_NO_FUSE_PROJ", "DLWP_MID_FMA", "DLWP_LIFT4=0"])
 def test_ab_kernel_forms_agree(pkg, knob, monkeypatch):
     """The kernel forms kept for A/B runs (two launches for the last layer + projection instead of fno_layerproj_kernel;
-    the fp32 FMA mid kernel instead of fno_mid_tc_kernel) are selected when a plan is built: same increment as the default
+    the fp32 FMA mid kernel instead of fno_mid_tc_kernel; the two-worker lifting kernel instead of fno_lift4_kernel, which a
+    batch of 40 samples = 640 tiles selects by default) are selected when a plan is built: same increment as the default
     forms and as the oracle."""
     from oracle import wrappers as owrap
     torch.manual_seed(1234)
@@ -237,7 +238,7 @@ def test_ab_kernel_forms_agree(pkg, knob, monkeypatch):
     outs = []
     for on in (False, True):
         if on:
-            monkeypatch.setenv(knob, "1")
+            monkeypatch.setenv(*(knob.split("=") if "=" in knob else (knob, "1")))
         mod = pkg.TFNO2DModule(**C2).cuda().eval()
         mod.load_state_dict(ref.state_dict(), strict=True)
         mod.precision = pkg.native.PREC_FP32_TC
