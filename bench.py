@@ -295,7 +295,7 @@ def kernel_bytes(cls, kw, B, H, W, name, tcw=False, fused_tail=False):
         half = B * H * m2 * C * 2       # complex [B, H, Kc, C]
         modes = B * m1 * m2 * C * 2
         return b * N * ((px * C + half) + (half + modes) + (modes + half) + (half + 2 * px * C + px * C))
-    if name == "mix_dense_kernel":
+    if name in ("mix_dense_kernel", "mix_few_tc_kernel"):
         return b * N * (2 * B * m1 * m2 * C * 2 + m1 * m2 * C * C * 2)
     if name in ("fno_lift_kernel", "fno_lift4_kernel"):       # fused lifting MLP (+ forward W-DFT of its output)
         return b * px * (cin + C) + b * B * H * m2 * C * 2

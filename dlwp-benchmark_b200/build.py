@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libdlwp_b200.so")
-SOURCES = ["kernels_fp32.cu", "plan.cu", "api.cu", "profile.cu", "tc_selftest.cu", "tc_fno.cu", "tc_mid.cu", "tc_mid2.cu", "tc_fno_lp.cu", "tc_afno_mid.cu", "tc_plan.cu", "tc_wide.cu", "tc_wide_plan.cu", "tc_afno.cu", "tc_afno_plan.cu", "afno_fused.cu", "static_scratch.cu", "spectral_ops.cu", "eval_ops.cu", "train_ops.cu", "train_afno.cu"]
+SOURCES = ["kernels_fp32.cu", "plan.cu", "api.cu", "profile.cu", "tc_selftest.cu", "tc_fno.cu", "tc_mid.cu", "tc_mid2.cu", "tc_fno_lp.cu", "tc_afno_mid.cu", "tc_plan.cu", "tc_wide.cu", "tc_wide_mix.cu", "tc_wide_plan.cu", "tc_afno.cu", "tc_afno_plan.cu", "afno_fused.cu", "static_scratch.cu", "spectral_ops.cu", "eval_ops.cu", "train_ops.cu", "train_afno.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
          "-diag-suppress", "550", "-shared"]
 

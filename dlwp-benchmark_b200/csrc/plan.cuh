@@ -84,7 +84,8 @@ struct dlwp_plan {
   uint8_t *tcw_W1 = nullptr, *tcw_W2 = nullptr, *tcw_b2 = nullptr, *tcw_P1 = nullptr, *tcw_pb1 = nullptr,
           *tcw_P2 = nullptr, *tcw_pb2 = nullptr;
   std::vector<uint8_t*> tcw_skip, tcw_cbias;            // per layer skip-conv and bias images
-  std::vector<uint32_t*> tcw_wm16;                      // per layer bf16 copy of the mode-major spectral weights
+  std::vector<uint32_t*> tcw_wm16;                      // per layer bf16 form of the mode-major spectral weights: (re, im) pairs, or
+  bool tcw_mix_tc = false;                              //   (tcw_mix_tc) the operand images of mix_few_tc_kernel (same size)
 
   // tensor-core AFNO kernels (tc_afno.cuh): precision == DLWP_PREC_FP32_TC, embed_dim 64, mlp hidden 256
   bool atc = false;

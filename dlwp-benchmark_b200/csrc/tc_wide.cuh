@@ -69,6 +69,12 @@ struct WideGatherArgs {
 };
 int launch_wide_gather(const WideGatherArgs& a, cudaStream_t st);
 
+// few-sample mode mixing on tcgen05 (tc_wide_mix.cu): weights as per-mode operand images [modes][64 KB] (launch_mix_few_pack from
+// the mode-major fp32 weights [modes][128][128] complex), spectrum X [modes, B, 128] complex -> the bf16 tile images `ys`
+bool mix_few_tc_covers(int modes, int B, int C, int Kc);
+int launch_mix_few_pack(const float2* wm, uint8_t* Wimg, int modes, cudaStream_t st);
+int launch_mix_few_tc(const float2* X, const uint8_t* Wimg, uint8_t* ys, int modes, int B, int Kc, cudaStream_t st);
+
 // host: chunk-major bf16 image of a row-major matrix `m` [rows, cols] padded to R x K with zeros
 void tcw_pack_image(const float* m, int rows, int cols, int ld, int R, int K, uint8_t* out);
 void tcw_pack_image_f64(const double* m, int rows, int cols, int ld, int R, int K, uint8_t* out);

@@ -2,6 +2,7 @@
 // W-DFT operand tiles, weight images and the per-step kernel sequence (reference: neuralop
 // FNO.forward behind fno.py:103, at BASELINE config 5's widths).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -207,7 +208,12 @@ int plan_tcw_commit(dlwp_plan* p, cudaStream_t st) {
       p->tcw_wm16.assign(N, nullptr);
       for (int l = 0; l < N; ++l) DLWP_TRY(plan_dev_alloc(p, (void**)&p->tcw_wm16[l], (size_t)n * 4));
     }
-    for (int l = 0; l < N; ++l) DLWP_TRY(launch_narrow_bf16(p->wm[l], p->tcw_wm16[l], n, st));
+    // few samples on tcgen05 (DLWP_MIX_FMA=1 keeps the CUDA-core kernel: A/B runs): the same bytes as operand images
+    p->tcw_mix_tc = mix_few_tc_covers(d.n_rows * d.n_cols, 1, C, d.n_cols) && std::getenv("DLWP_MIX_FMA") == nullptr;
+    for (int l = 0; l < N; ++l) {
+      if (p->tcw_mix_tc) DLWP_TRY(launch_mix_few_pack(p->wm[l], reinterpret_cast<uint8_t*>(p->tcw_wm16[l]), d.n_rows * d.n_cols, st));
+      else DLWP_TRY(launch_narrow_bf16(p->wm[l], p->tcw_wm16[l], n, st));
+    }
     DLWP_CUDA(cudaStreamSynchronize(st));
   }
   // the last block applies no GELU, so the projection reads a plain image
@@ -253,8 +259,11 @@ int backbone_fno_tcw(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
     a.nitems = B * d.n_cols;
     a.a_img = p->tcw_sa; a.g_img = p->tcw_Fs; a.spec = p->specX;
     DLWP_TRY(launch_tcw(TCW_HFWD, a, st));
-    DLWP_TRY(launch_mix_dense(p->specX, p->wm[l], p->specY, d.n_rows * d.n_cols, B, kWideC, kWideC, st,
-                              MixWideOpts{p->tcw_ys, d.n_cols, B <= 4 ? p->tcw_wm16[l] : nullptr}));
+    if (p->tcw_mix_tc && B <= 8)
+      DLWP_TRY(launch_mix_few_tc(p->specX, reinterpret_cast<const uint8_t*>(p->tcw_wm16[l]), p->tcw_ys, d.n_rows * d.n_cols, B, d.n_cols, st));
+    else
+      DLWP_TRY(launch_mix_dense(p->specX, p->wm[l], p->specY, d.n_rows * d.n_cols, B, kWideC, kWideC, st,
+                                MixWideOpts{p->tcw_ys, d.n_cols, (B <= 4 && !p->tcw_mix_tc) ? p->tcw_wm16[l] : nullptr}));
     a = base;
     a.nitems = B * d.n_cols * p->tcw_HB;
     a.a_img = p->tcw_ys; a.g_img = p->tcw_Gs; a.out_img = p->tcw_z;

@@ -124,3 +124,33 @@ def test_bf16_mode_rejects_other_widths(pkg):
     const, presc, prog = synthetic(1, 2, 2, 1, 3, 12, 200)
     with torch.no_grad(), pytest.raises(RuntimeError, match="DLWP_PREC_BF16"):
         mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog))
+
+
+@pytest.mark.parametrize("B", [1, 3, 7, 9])
+def test_few_sample_mode_mixing_forms_agree(pkg, B, monkeypatch):
+    """The per-mode channel mixing of the bf16 kernel set on tcgen05 (mix_few_tc_kernel: up to 8 samples; 9 take the CUDA-core
+    kernel) against the CUDA-core forms selected with DLWP_MIX_FMA=1 when the plan is built, and against the
+    oracle: the two differ by the bf16 rounding of the spectrum entering the product only."""
+    from oracle import wrappers as owrap
+    kw, (_, H, W) = CASES["c5like"]
+    torch.manual_seed(1234)
+    ref = owrap.FNO2DModule(**kw).eval()
+    const, presc, prog = synthetic(B, 2, kw["constant_channels"], kw["prescribed_channels"], kw["prognostic_channels"], H, W, seed=11)
+    outs = []
+    for fma in (False, True):
+        if fma:
+            monkeypatch.setenv("DLWP_MIX_FMA", "1")
+        mod = pkg.FNO2DModule(**kw).cuda().eval()
+        mod.load_state_dict(ref.state_dict(), strict=True)
+        mod.precision = pkg.native.PREC_BF16
+        with torch.no_grad():
+            outs.append(mod(constants=_dev(const), prescribed=_dev(presc), prognostic=_dev(prog)).cpu())
+    with torch.no_grad():
+        want = ref(constants=const, prescribed=presc, prognostic=prog)
+    incr = (want[:, 0] - prog[:, 0]).abs().max()
+    errs = [float((o[:, 0] - want[:, 0]).abs().max() / incr) for o in outs]
+    diff = float((outs[0] - outs[1]).abs().max() / incr)
+    print(f"B={B}: tcgen05 form {errs[0]:.3e}, CUDA-core form {errs[1]:.3e} of the increment scale; between them {diff:.3e}")
+    assert max(errs) < TOL_BF16 and diff < TOL_BF16
+    if B <= 8:
+        assert diff > 0.0      # two different kernels ran
