@@ -567,12 +567,14 @@ __global__ void __launch_bounds__(kMlpCta, 1) tcw_mlp_kernel(const TcwArgs a) {
 // columns 16..16+Cin-1 lo parts.
 __global__ void __launch_bounds__(128) wide_gather_kernel(const WideGatherArgs a) {
   pdl_launch_dependents();
-  const int tile = blockIdx.x, s = threadIdx.x;
+  pdl_wait();
+  // a CTA walks over tiles (one CTA per tile was bound by the rate at which 17 k CTAs of 128 threads are dispatched)
+  for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+  const int s = threadIdx.x;
   const int w = (tile % a.TW) * 128 + s, rid = tile / a.TW;
   const int b = rid / a.H, h = rid - b * a.H;
   const size_t plane = (size_t)a.H * a.W, px = (size_t)h * a.W + w;
   float x[14];
-  pdl_wait();
 #pragma unroll
   for (int c = 0; c < 14; ++c) {
     x[c] = 0.f;
@@ -596,6 +598,7 @@ __global__ void __launch_bounds__(128) wide_gather_kernel(const WideGatherArgs a
   uint8_t* img = a.in_img + (size_t)tile * 8192 + s * 16;   // [128 x 32] bf16 image
 #pragma unroll
   for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(img + j * 2048) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+  }
 }
 
 }  // namespace
@@ -651,7 +654,10 @@ int launch_tcw_mlp(int kind, const TcwArgs& a, cudaStream_t st) {
 int launch_wide_gather(const WideGatherArgs& a, cudaStream_t st) {
   DLWP_REQUIRE(a.Cin >= 1 && a.Cin <= 14 && a.ngrp >= 1 && a.ngrp <= 4, "wide_gather: %d input channels", a.Cin);
   void (*kern)(WideGatherArgs) = wide_gather_kernel;
-  DLWP_CUDA(launch_pdl(kern, dim3((unsigned)a.ntiles), dim3(128), 0, st, a));
+  int sms = 0;
+  DLWP_TRY(current_sms(&sms));
+  const int grid = a.ntiles < 16 * sms ? a.ntiles : 16 * sms;      // 16 CTAs of 128 threads per SM
+  DLWP_CUDA(launch_pdl(kern, dim3((unsigned)grid), dim3(128), 0, st, a));
   DLWP_LAUNCHED("wide_gather_kernel");
   return DLWP_OK;
 }
