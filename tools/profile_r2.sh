@@ -21,4 +21,9 @@ ncu --set full --clock-control none --import-source on -k regex:afno -s 20 -c 4 
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:afno -c 100 --csv --log-file gpurun_out/r02_ncu_launches_c3_$tag.csv python bench.py --workload c3 --members 256 --steps 1 --warmup 3 --no-cpu-baseline --no-eager > /dev/null 2>&1; echo "ncu4 rc=$?"
 (python tools/ncu_pipe.py gpurun_out/r02_prof_c4_$tag.ncu-rep; python tools/ncu_pipe.py gpurun_out/r02_prof_c3_$tag.ncu-rep) > gpurun_out/r02_data_pipe_$tag.txt 2>&1
 tools/ubench/umma > gpurun_out/r02_ubench_umma_$tag.txt 2>&1; tools/ubench/umma_ts >> gpurun_out/r02_ubench_umma_$tag.txt 2>&1
+tools/ubench/gelu_rate > gpurun_out/r02_ubench_gelu_$tag.txt 2>&1
+# config 5 on the bf16 kernel set, and the same with the CUDA-core few-sample mode mixing
+python bench.py --workload c5 --precision bf16 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r02_bench_c5_bf16_$tag.json 2>> gpurun_out/r02_bench_$tag.err; echo "c5 rc=$?"
+DLWP_MIX_FMA=1 python bench.py --workload c5 --precision bf16 --steps 3 --warmup 3 --no-cpu-baseline --no-eager > gpurun_out/r02_bench_c5_bf16_mixfma_$tag.json 2>> gpurun_out/r02_bench_$tag.err
+DLWP_LIFT4=0 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-eager > gpurun_out/r02_bench_c4_lift2_$tag.json 2>> gpurun_out/r02_bench_$tag.err
 cat gpurun_out/r02_data_pipe_$tag.txt
