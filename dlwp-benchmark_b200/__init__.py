@@ -8,6 +8,7 @@ from . import native                                             # noqa: F401
 from .models import AFNONet, FNO2DModule, FourCastNet, TFNO2DModule  # noqa: F401
 from .metrics import lat_weights, rollout_metrics                # noqa: F401
 from .spectral import FourierResidualBlock, SpectralConv2d       # noqa: F401
+from .prefetch import DevicePrefetcher                           # noqa: F401
 
 __all__ = ["FNO2DModule", "TFNO2DModule", "AFNONet", "FourCastNet", "lat_weights", "rollout_metrics", "native",
-           "SpectralConv2d", "FourierResidualBlock"]
+           "SpectralConv2d", "FourierResidualBlock", "DevicePrefetcher"]

@@ -167,3 +167,11 @@ def test_modules_build_from_the_reference_model_yaml(fname):
     assert got == want
     mod.load_state_dict(ref.state_dict(), strict=True)
     assert mod.context_size == cfg["context_size"] and mod.prognostic_channels == cfg["prognostic_channels"]
+
+
+def test_device_prefetcher_has_no_host_fallback():
+    with pytest.raises(native.NativeError):
+        pkg.DevicePrefetcher([(torch.zeros(1),)], "cpu")
+    if not torch.cuda.is_available():
+        with pytest.raises(native.NativeError):
+            pkg.DevicePrefetcher([(torch.zeros(1),)], "cuda")

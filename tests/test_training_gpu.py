@@ -176,3 +176,44 @@ def test_fourcastnet_training_steps(pkg):
     with torch.no_grad():      # the tensor-core inference plan on the updated weights
         out = mod(constants=const, prescribed=presc, prognostic=prog)
         assert abs(float(torch.nn.functional.mse_loss(out, tgt)) - losses[-1]) < abs(losses[-1])
+
+
+def test_device_prefetcher_feeds_the_training_loop(pkg):
+    """the loader's (constants, prescribed, prognostic, target) batches arrive on the device ahead of the consumer,
+    in order, bit-identical; a NaN tensor stands for an absent input (train.py:180-181) and arrives as None; a loader
+    exception reaches the consumer; stopping early does not hang."""
+    g = torch.Generator().manual_seed(0)
+    batches = []
+    for n in range(7):
+        B = 2 + n % 3
+        batches.append((torch.full((B, 1, 4, 8, 16), float("nan")) if n % 2 else torch.randn(B, 1, 4, 8, 16, generator=g),
+                        torch.randn(B, 3, 1, 8, 16, generator=g), torch.randn(B, 3, 8, 8, 16, generator=g),
+                        torch.randn(B, 2, 8, 8, 16, generator=g).double()))
+    got = list(pkg.DevicePrefetcher(batches, "cuda", depth=2))
+    assert len(got) == len(batches)
+    for n, (want, have) in enumerate(zip(batches, got)):
+        assert (have[0] is None) == bool(n % 2)
+        for w, h in zip(want[1:], have[1:]):
+            assert h.device.type == "cuda" and h.dtype == w.dtype and torch.equal(h.cpu(), w)
+        if have[0] is not None:
+            assert torch.equal(have[0].cpu(), want[0])
+    # early stop
+    it = iter(pkg.DevicePrefetcher(batches, "cuda", depth=1))
+    next(it)
+    it.close()
+
+    def bad():
+        yield batches[0]
+        raise RuntimeError("loader failed")
+    with pytest.raises(RuntimeError, match="loader failed"):
+        list(pkg.DevicePrefetcher(bad(), "cuda"))
+    # and the loop shape of train.py:176-271 on top of it
+    _, mod, kw, (B, H, W), T = _pair(pkg, "tfno-c2")
+    data = [synthetic(B, T, 4, 1, 8, H, W, seed=s) + (synthetic(B, T - 1, 0, 0, 8, H, W, seed=50 + s)[2],) for s in range(3)]
+    opt = torch.optim.Adam(mod.parameters(), lr=1e-3)
+    for constants, prescribed, prognostic, target in pkg.DevicePrefetcher(data, "cuda"):
+        opt.zero_grad()
+        loss = torch.nn.functional.mse_loss(mod(constants=constants, prescribed=prescribed, prognostic=prognostic), target)
+        loss.backward()
+        opt.step()
+    assert torch.isfinite(loss)
