@@ -68,6 +68,8 @@ struct dlwp_plan {
           *tc_projW1x = nullptr;
   std::vector<uint8_t*> tc_skip;                        // per layer skip-conv images
   bool tc_mid2 = false;                                 // the retained-column products run on tcgen05 (fno_mid_tc_kernel, tc_mid2.cu)
+  bool tc_layer_rev = false;                            // layer kernels walk the tile list alternately down and up
+  bool tc_l2hint = false;                               // L2 eviction priorities on the activation images' bulk copies
   bool tc_lift4 = false;                                // lifting kernel with four workers per CTA (fno_lift4_kernel)
   bool tc_fuse_proj = false;                            // last layer + projection in one launch (fno_layerproj_kernel)
   uint8_t *tc_midF = nullptr, *tc_midG = nullptr;       // (re|im)-stacked forward / inverse H-DFT operand images

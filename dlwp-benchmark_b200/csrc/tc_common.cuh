@@ -232,6 +232,38 @@ __device__ __forceinline__ void bulk_s2g_p(uint32_t leader, void* dst, const voi
       : "memory");
 }
 
+// ---- L2 eviction priorities for the bulk copies ------------------------------------------------
+// The activation images of a model evaluation are written by one kernel and read once, two kernels later; together with what
+// is written in between they are slightly more than the L2 holds, so in plain LRU order every line is evicted just before it
+// is read.  evict_last on the stores of the images and evict_first on everything that is dead after its one read keeps them.
+__device__ __forceinline__ uint64_t l2_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void bulk_g2s_hp(uint32_t leader, void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  if (policy == 0) return bulk_g2s_p(leader, dst_smem, src, bytes, bar);
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;\n\t}" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy), "r"(leader)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_s2g_hp(uint32_t leader, void* dst, const void* src_smem, uint32_t bytes, uint64_t policy) {
+  if (policy == 0) return bulk_s2g_p(leader, dst, src_smem, bytes);
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %4, 0;\n\t"
+      "@q cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;\n\t}" ::"l"(dst),
+      "r"(smem_u32(src_smem)), "r"(bytes), "l"(policy), "r"(leader)
+      : "memory");
+}
+
 // ---- split-bf16 arithmetic ------------------------------------------------------------------
 // v = hi + lo with hi = bf16(v), lo = bf16(v - hi): 16 mantissa bits survive, the products
 // hi*hi + lo*hi + hi*lo reproduce an fp32 product to ~2^-17 relative.

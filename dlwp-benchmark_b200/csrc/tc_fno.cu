@@ -161,7 +161,7 @@ __device__ __forceinline__ void drain_tail(const EpiId& id, const TcGeom& g, flo
 __device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint32_t aF, uint8_t* sY, uint8_t* y_dst,
                                                  uint32_t tmem_d3, uint64_t* xt_full, uint64_t* d3_full, uint64_t* y_free,
                                                  uint32_t n, const TailCfg cfg, bool tr_on = false, int tw = 0,
-                                                 uint64_t* d3_empty = nullptr) {
+                                                 uint64_t* d3_empty = nullptr, uint64_t y_policy = 0) {
   const int ny = cfg.ny, nd = cfg.nd;
   const uint32_t yb = ny == 2 ? (n & 1u) : 0u, use = ny == 2 ? (n >> 1) : n;
   sY += yb * kTileBytes;
@@ -195,7 +195,7 @@ __device__ __forceinline__ void ctrl_finish_tile(uint32_t leader, bool dft, uint
     }
     umma_commit_p(leader, &d3_full[d3_slot(n, nd)]);
   }
-  bulk_s2g_p(leader, y_dst, sY, kTileBytes);
+  bulk_s2g_hp(leader, y_dst, sY, kTileBytes, y_policy);
   bulk_commit();
   if (cfg.ext) {
     // y_free takes two arrivals per use: the UMMAs above have read the image / the bulk store has.  With two image
@@ -322,8 +322,9 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
         const int t0 = (int)blockIdx.x + (int)u * stride;
         if (t0 >= g.ntiles) break;
         for (int w = 0; w < 2; ++w) {
-          const int tile = t0 + w * (int)gridDim.x;
-          if (tile >= g.ntiles) break;
+          const int slot = t0 + w * (int)gridDim.x;
+          if (slot >= g.ntiles) break;
+          const int tile = g.rev ? g.ntiles - 1 - slot : slot;
           uint64_t* b = bars + w * LB_PER;
           const uint32_t sl = d3_slot(u, nd);
           mbar_wait(&b[LB_D3FULL + sl], d3_use(u, nd) & 1u);
@@ -380,13 +381,15 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
       const uint32_t aF = smem_u32(smem + L.F);
       const int first = (int)blockIdx.x + w * (int)gridDim.x;
 
+      const uint64_t pol_in = g.l2hint ? l2_evict_first() : 0, pol_out = g.l2hint ? l2_evict_last() : 0;
       auto load_inputs = [&](int tile, uint32_t u) {
         const int s = u % kLayerSlots;
         mbar_wait(&b[LB_XFREE + s], ((u / kLayerSlots) & 1u) ^ 1u);   // the UMMAs that read this slot last are done
         TR(w, u, 0);
         mbar_arrive_expect_tx_p(leader, &b[LB_XFULL + s], kTileBytes + z_bytes);
-        bulk_g2s_p(leader, ws + L.X + s * kTileBytes, a.x_img + (size_t)tile * kTileBytes, kTileBytes, &b[LB_XFULL + s]);
-        bulk_g2s_p(leader, ws + L.Z + s * z_bytes, a.Zimg + (size_t)tile * z_bytes, z_bytes, &b[LB_XFULL + s]);
+        const size_t t = (size_t)(g.rev ? g.ntiles - 1 - tile : tile);
+        bulk_g2s_hp(leader, ws + L.X + s * kTileBytes, a.x_img + t * kTileBytes, kTileBytes, &b[LB_XFULL + s], pol_in);
+        bulk_g2s_hp(leader, ws + L.Z + s * z_bytes, a.Zimg + t * z_bytes, z_bytes, &b[LB_XFULL + s], pol_in);
       };
 
       for (int i = 0; i < kLayerSlots; ++i)
@@ -395,8 +398,8 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
       uint32_t u = 0;
       for (int tile = first; tile < g.ntiles; tile += stride, ++u) {
         if (tile + kLayerSlots * stride < g.ntiles) load_inputs(tile + kLayerSlots * stride, u + kLayerSlots);
-        ctrl_finish_tile(leader, a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)tile * kTileBytes, tmem + 64,
-                         &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], u, tail, tr_on, w, &b[LB_D3EMPTY]);
+        ctrl_finish_tile(leader, a.Aout != nullptr, aF, ws + L.Y, a.y_img + (size_t)(g.rev ? g.ntiles - 1 - tile : tile) * kTileBytes, tmem + 64,
+                         &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], u, tail, tr_on, w, &b[LB_D3EMPTY], pol_out);
         TR(w, u, 6);
       }
       bulk_wait0();
@@ -477,8 +480,8 @@ __global__ void __launch_bounds__(kCtaLayerAll, 1) fno_layer_kernel(const TcLaye
           v[c] = a.gelu ? gelu2(x) : x;
         }
       }
-      finish_tile(v, id, tile, g, a.Aout, ws + L.Y, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL], &b[LB_YFREE], n3,
-                  prev_tile, tail, tr_on);
+      finish_tile(v, id, g.rev ? g.ntiles - 1 - tile : tile, g, a.Aout, ws + L.Y, tmem_s + 256u * w + 64, &b[LB_XTFULL], &b[LB_D3FULL],
+                  &b[LB_YFREE], n3, prev_tile, tail, tr_on);
     }
   }
   tc_fence_before();
@@ -756,7 +759,7 @@ __global__ void __launch_bounds__(kCtaLayer, 1) fno_lift_kernel(const TcLiftArgs
     uint32_t u = 0;
     for (int tile = first; tile < g.ntiles; tile += stride, ++u)
       ctrl_finish_tile(leader, dft, aF, ws + LiftSmem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[MB_XTFULL], &b[MB_D3FULL],
-                       &b[MB_YFREE], u, TailCfg{1, 2, false});
+                       &b[MB_YFREE], u, TailCfg{1, 2, false}, false, 0, nullptr, g.l2hint ? l2_evict_last() : 0);
     bulk_wait0();
   } else if (warp >= kCtlWarp) {
     // ---------------- issuer lane: the MLP's UMMAs ----------------
@@ -951,7 +954,7 @@ __global__ void __launch_bounds__(kL4Cta, 1) fno_lift4_kernel(const TcLiftArgs a
     uint32_t u = 0;
     for (int tile = first; tile < g.ntiles; tile += stride, ++u)
       ctrl_finish_tile(leader, dft, aF, ws + Lift4Smem::Y, a.y_img + (size_t)tile * kTileBytes, d3, &b[L4_XTFULL], &b[L4_D3FULL],
-                       &b[L4_YFREE], u, TailCfg{1, 1, false});
+                       &b[L4_YFREE], u, TailCfg{1, 1, false}, false, 0, nullptr, g.l2hint ? l2_evict_last() : 0);
     bulk_wait0();
   } else if (warp >= kL4Iss) {
     // ---------------- issuer lane: the MLP's UMMAs, one 32-column chunk per pass ----------------

@@ -39,6 +39,8 @@ struct TcGeom {
   int abf;             // the forward W-DFT leaves as split-bf16 operand tiles for fno_mid_tc_kernel (tc_mid2.cu) instead of planar fp32
   int Bn;              // samples of this launch (ntiles * 128 / HW)
   int TPS;             // tiles per sample = HW / 128 = H / RT (a tile lies within one sample: 32-bit index arithmetic per tile)
+  int l2hint;          // L2 eviction priorities on the bulk copies of the activation images (tc_common.cuh); DLWP_L2_HINTS=0 clears it
+  int rev;             // fno_layer_kernel: the tile list is walked from the last tile down (see tc_plan.cu)
 };
 
 struct TcLiftArgs {
@@ -110,6 +112,7 @@ struct TcMid2Args {
   const uint8_t* Gimg;    // inverse H-DFT, (re|im)-stacked: [hi | lo] images of max(2H, 64) rows x 32
   uint8_t* Zimg;          // as TcMidArgs
   int B, H, R, Kc, RT, KZ;
+  int l2hint;             // as TcGeom
 };
 // samples per work item (0 = this geometry is not covered: the fp32 FMA kernel runs instead)
 int tc_mid2_samples(int H, int R);

@@ -115,8 +115,9 @@ __global__ void __launch_bounds__(kCtaLp, 1) fno_layerproj_kernel(const TcLayerP
       const int s = u % kLpSlots;
       mbar_wait(&lb[PB_XFREE + s], ((u / kLpSlots) & 1u) ^ 1u);   // the UMMAs that read this slot last are done
       mbar_arrive_expect_tx_p(leader, &lb[PB_XFULL + s], kTileBytes + z_bytes);
-      bulk_g2s_p(leader, ws + L.X + s * kTileBytes, a.layer.x_img + (size_t)tile * kTileBytes, kTileBytes, &lb[PB_XFULL + s]);
-      bulk_g2s_p(leader, ws + L.Z + s * z_bytes, a.layer.Zimg + (size_t)tile * z_bytes, z_bytes, &lb[PB_XFULL + s]);
+      const uint64_t pol_in = g.l2hint ? l2_evict_first() : 0;      // dead after this read
+      bulk_g2s_hp(leader, ws + L.X + s * kTileBytes, a.layer.x_img + (size_t)tile * kTileBytes, kTileBytes, &lb[PB_XFULL + s], pol_in);
+      bulk_g2s_hp(leader, ws + L.Z + s * z_bytes, a.layer.Zimg + (size_t)tile * z_bytes, z_bytes, &lb[PB_XFULL + s], pol_in);
     };
     for (int i = 0; i < kLpSlots; ++i)
       if (first + i * stride < g.ntiles) load_inputs(first + i * stride, i);

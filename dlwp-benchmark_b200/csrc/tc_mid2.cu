@@ -140,14 +140,15 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
   if (warp == kEpiWarps) {
     // ------------------------------ control warp: tile loads and every tcgen05.mma ------------------------------
     const uint32_t leader = elect_one();
+    const uint64_t pol_in = a.l2hint ? l2_evict_first() : 0;
     auto load = [&](int grp) {      // one bulk copy per (sample, hi | lo), from 2 nb lanes
       const int b0 = grp * NB, nb = a.B - b0 < NB ? a.B - b0 : NB;
       mbar_arrive_expect_tx_p(leader, &bars[MB_AFULL], (uint32_t)(2 * nb * tile_b));
       __syncwarp();
       const int part = lane >> 3, bl = lane & 7;
-      if (lane < 16 && bl < nb)
-        bulk_g2s(smem + L.A + part * L.a_part + bl * tile_b, a.A + ((size_t)(kx * 2 + part) * a.B + b0 + bl) * tile_b, (uint32_t)tile_b,
-                 &bars[MB_AFULL]);
+      if (lane < 16 && bl < nb)      // (dead after this read: first in line for eviction from the L2)
+        bulk_g2s_hp(1u, smem + L.A + part * L.a_part + bl * tile_b, a.A + ((size_t)(kx * 2 + part) * a.B + b0 + bl) * tile_b, (uint32_t)tile_b,
+                    &bars[MB_AFULL], pol_in);
       __syncwarp();
     };
     if (chunk < ngroups) load(chunk);

@@ -85,6 +85,10 @@ int plan_tc_build(dlwp_plan* p) {
   {
     const char* e = std::getenv("DLWP_LIFT4");
     p->tc_lift4 = e == nullptr || std::atoi(e) != 0;
+    e = std::getenv("DLWP_LAYER_REV");
+    p->tc_layer_rev = e == nullptr || std::atoi(e) != 0;
+    e = std::getenv("DLWP_L2_HINTS");      // 0: the bulk copies of the activation images carry no L2 eviction priority (A/B runs)
+    p->tc_l2hint = e == nullptr || std::atoi(e) != 0;
   }
   // the last layer and the projection as one kernel (DLWP_NO_FUSE_PROJ=1 keeps the two launches: A/B runs)
   p->tc_fuse_proj = d.n_layers >= 1 && tc_layerproj_fits(KZ) && std::getenv("DLWP_NO_FUSE_PROJ") == nullptr;
@@ -187,6 +191,7 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
   g.ntiles = (int)((long long)B * g.HW / kTcTile);
   g.abf = p->tc_mid2 ? 1 : 0;
   g.Bn = B;
+  g.l2hint = p->tc_l2hint ? 1 : 0;
   const float *b2, *cbias, *pb2;
   DLWP_TRY(plan_need(p, "lifting.fcs.1.bias", C, &b2));
   DLWP_TRY(plan_need(p, "fno_blocks.convs.bias", (int64_t)N * C, &cbias));
@@ -214,6 +219,7 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
       TcMid2Args ma{};
       ma.A = reinterpret_cast<const uint8_t*>(p->specA); ma.Wimg = p->tc_midW[l]; ma.Fimg = p->tc_midF; ma.Gimg = p->tc_midG;
       ma.Zimg = p->tc_Z; ma.B = B; ma.H = H; ma.R = R; ma.Kc = Kc; ma.RT = g.RT; ma.KZ = g.KZ;
+      ma.l2hint = g.l2hint;
       DLWP_TRY(launch_tc_mid2(ma, st));
     } else {
     TcMidArgs ma{};
@@ -233,6 +239,10 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
     ya.Wsimg = p->tc_skip[l];
     ya.bias = cbias + (size_t)l * C;
     ya.gelu = l < N - 1 ? 1 : 0;
+    // Consecutive kernels walk the tile list in opposite directions: the lifting kernel and the fused tail upwards, the layer
+    // kernels alternately down and up, so that a kernel starts on the tiles its producer wrote last -- the ones the L2 still
+    // holds (an activation image set is larger than what survives the kernel in between).  DLWP_LAYER_REV=0: all upwards.
+    ya.g.rev = p->tc_layer_rev && ((N - 1 - l) & 1) ? 1 : 0;
     if (l == N - 1 && p->tc_fuse_proj) {      // last layer + projection in one kernel: the layer's output tile never leaves the SM
       TcLayerProjArgs fa{};
       fa.layer = ya;

@@ -225,12 +225,12 @@ def test_rollout_is_cuda_graph_capturable(pkg, case):
     assert torch.equal(out, want1) and not torch.equal(want1, want0)
 
 
-@pytest.mark.parametrize("knob", ["DLWP_NO_FUSE_PROJ", "DLWP_MID_FMA", "DLWP_LIFT4=0"])
+@pytest.mark.parametrize("knob", ["DLWP_NO_FUSE_PROJ", "DLWP_MID_FMA", "DLWP_LIFT4=0", "DLWP_LAYER_REV=0", "DLWP_L2_HINTS=0"])
 def test_ab_kernel_forms_agree(pkg, knob, monkeypatch):
     """The kernel forms kept for A/B runs (two launches for the last layer + projection instead of fno_layerproj_kernel;
     the fp32 FMA mid kernel instead of fno_mid_tc_kernel; the two-worker lifting kernel instead of fno_lift4_kernel, which a
-    batch of 40 samples = 640 tiles selects by default) are selected when a plan is built: same increment as the default
-    forms and as the oracle."""
+    batch of 40 samples = 640 tiles selects by default; every layer kernel walking its tiles upwards; bulk copies without L2
+    eviction priorities) are selected when a plan is built: same increment as the default forms and as the oracle."""
     from oracle import wrappers as owrap
     torch.manual_seed(1234)
     ref = owrap.TFNO2DModule(**C2).eval()
@@ -248,3 +248,5 @@ def test_ab_kernel_forms_agree(pkg, knob, monkeypatch):
         want = ref.fno(x)
     assert max_rel(outs[0], want) < TOL_INCR and max_rel(outs[1], want) < TOL_INCR
     assert max_rel(outs[1], outs[0]) < TOL_INCR
+    if knob in ("DLWP_LAYER_REV=0", "DLWP_L2_HINTS=0"):      # the same arithmetic in another order / with other cache hints
+        assert torch.equal(outs[0], outs[1])
