@@ -113,6 +113,7 @@ struct TcMid2Args {
   uint8_t* Zimg;          // as TcMidArgs
   int B, H, R, Kc, RT, KZ;
   int l2hint;             // as TcGeom
+  int rev;                // the sample groups are taken from the last one down
 };
 // samples per work item (0 = this geometry is not covered: the fp32 FMA kernel runs instead)
 int tc_mid2_samples(int H, int R);

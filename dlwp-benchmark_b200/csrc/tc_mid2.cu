@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
     const uint32_t leader = elect_one();
     const uint64_t pol_in = a.l2hint ? l2_evict_first() : 0;
     auto load = [&](int grp) {      // one bulk copy per (sample, hi | lo), from 2 nb lanes
-      const int b0 = grp * NB, nb = a.B - b0 < NB ? a.B - b0 : NB;
+      const int b0 = (a.rev ? ngroups - 1 - grp : grp) * NB, nb = a.B - b0 < NB ? a.B - b0 : NB;
       mbar_arrive_expect_tx_p(leader, &bars[MB_AFULL], (uint32_t)(2 * nb * tile_b));
       __syncwarp();
       const int part = lane >> 3, bl = lane & 7;
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(kMidThreads, 1) fno_mid_tc_kernel(const TcMid2
     uint32_t n = 0;
     for (int grp = chunk; grp < ngroups; grp += nchunks, ++n) {
       const uint32_t par = n & 1u;
-      const int b0 = grp * NB;
+      const int b0 = (a.rev ? ngroups - 1 - grp : grp) * NB;      // rev: the sample groups from the last one down (tc_plan.cu)
       {
         // ---- E 1: D1 row (copy q of X, r = lane) -> rows of the [P ; Q] operand images of mode r, NB / 4 samples per warp ----
         constexpr int MB = NB > 4 ? 2 : 1;      // warp j: samples j and j + 4 of the item (those below NB)

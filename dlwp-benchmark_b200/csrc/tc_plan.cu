@@ -220,6 +220,8 @@ int backbone_fno_tc(dlwp_plan* p, const StepIO& io, int B, cudaStream_t st) {
       ma.A = reinterpret_cast<const uint8_t*>(p->specA); ma.Wimg = p->tc_midW[l]; ma.Fimg = p->tc_midF; ma.Gimg = p->tc_midG;
       ma.Zimg = p->tc_Z; ma.B = B; ma.H = H; ma.R = R; ma.Kc = Kc; ma.RT = g.RT; ma.KZ = g.KZ;
       ma.l2hint = g.l2hint;
+      // its spectrum tiles were written by the lifting kernel (upwards) or by layer l - 1: the sample groups go the other way
+      ma.rev = p->tc_layer_rev && (l == 0 || !((N - l) & 1)) ? 1 : 0;
       DLWP_TRY(launch_tc_mid2(ma, st));
     } else {
     TcMidArgs ma{};
