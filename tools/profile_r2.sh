@@ -26,4 +26,6 @@ tools/ubench/gelu_rate > gpurun_out/r02_ubench_gelu_$tag.txt 2>&1
 python bench.py --workload c5 --precision bf16 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r02_bench_c5_bf16_$tag.json 2>> gpurun_out/r02_bench_$tag.err; echo "c5 rc=$?"
 DLWP_MIX_FMA=1 python bench.py --workload c5 --precision bf16 --steps 3 --warmup 3 --no-cpu-baseline --no-eager > gpurun_out/r02_bench_c5_bf16_mixfma_$tag.json 2>> gpurun_out/r02_bench_$tag.err
 DLWP_LIFT4=0 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-eager > gpurun_out/r02_bench_c4_lift2_$tag.json 2>> gpurun_out/r02_bench_$tag.err
+DLWP_L2_HINTS=0 DLWP_LAYER_REV=0 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-eager > gpurun_out/r02_bench_c4_nol2_$tag.json 2>> gpurun_out/r02_bench_$tag.err
+python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-eager > gpurun_out/r02_bench_c4_again_$tag.json 2>> gpurun_out/r02_bench_$tag.err
 cat gpurun_out/r02_data_pipe_$tag.txt
