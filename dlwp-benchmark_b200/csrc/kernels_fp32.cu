@@ -831,6 +831,8 @@ int launch_metrics(const float* o, const float* t, const float* clim, const floa
   DLWP_REQUIRE(B > 0 && T > 0 && C > 0 && H > 0 && W > 0, "metrics: empty problem");
   DLWP_REQUIRE((long long)T * C < (1ll << 31), "metrics: too many (lead time, variable) pairs");
   int by = B < 64 ? B : 64;
+  // many samples: fewer, longer CTAs (a CTA's fixed part -- start, block reduction, four fp64 atomics -- is paid per 64 KB otherwise)
+  while (by > 16 && (long long)T * C * (by / 2) >= 2 * 1184) by /= 2;
   // large planes with few samples: slice the plane so that the grid still covers the machine
   long long bz = (1184 + (long long)T * C * by - 1) / ((long long)T * C * by);
   const long long bz_max = ((long long)H * W + 4095) / 4096;
